@@ -1,0 +1,122 @@
+/* b200kkt — C ABI of the B200-native sparse symmetric-indefinite KKT solver.
+ *
+ * This is the drop-in boundary for the path behind Uno's
+ * DirectSymmetricIndefiniteLinearSolver<size_t,double>
+ * (reference: uno/ingredients/subproblem_solvers/DirectSymmetricIndefiniteLinearSolver.hpp:13-25,
+ *  uno/ingredients/subproblem_solvers/SymmetricIndefiniteLinearSolver.hpp:20-33).
+ * Every entry point below replaces one dmumps_c() call site or INFOG read of the reference's
+ * MUMPSSolver (uno/ingredients/subproblem_solvers/MUMPS/MUMPSSolver.cpp); the line cited beside
+ * each function is the reference interface it stands in for.
+ *
+ * Conventions: plain pointers and sizes only.  Matrix = upper-triangular COO, row <= col, 0-based
+ * 64-bit indices, duplicates are summed, explicit zeros are structural, the first reg_size entries
+ * are the (k,k) regularization slots (uno/linear_algebra/COOFormat.hpp:101-125).  Every function
+ * returns 0 on success, a negative B200KKT_E* code on failure (message via b200kkt_last_error).
+ * Singularity is NOT an error: it is reported through the inertia triple, as in the reference.
+ * Handles are independent (own stream, plan, workspaces); calls on one handle must not overlap.
+ * Host pointers are only borrowed for the duration of a call.
+ */
+#ifndef B200KKT_H
+#define B200KKT_H
+
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+typedef struct b200kkt_handle b200kkt_handle;
+
+enum {
+   B200KKT_OK = 0,
+   B200KKT_EINVAL = -1,      /* bad handle / argument / call order */
+   B200KKT_ECUDA = -2,       /* CUDA runtime error (no device, launch failure, ...) */
+   B200KKT_ENOMEM = -3,      /* host or device allocation failed */
+   B200KKT_EINTERNAL = -4    /* symbolic-phase failure */
+};
+
+/* Work figures and timings.  All counts are exact (computed from the plan), times in seconds. */
+typedef struct b200kkt_stats {
+   int64_t n, nnz, reg_size;
+   int64_t num_fronts, num_levels, max_front, max_pivots, num_pairs;
+   int64_t nnz_factor;         /* sum_s k_s f_s - k_s(k_s-1)/2 */
+   int64_t pool_doubles;       /* device front pool size */
+   int64_t assembly_distinct;  /* distinct destination slots of the scatter map */
+   double flops_factor;        /* sum_s k^3/3 + k^2 r + k r^2 */
+   double flops_tensor;        /* k^2 r + k r^2 over fronts with k >= 128 */
+   double t_ordering, t_symbolic, t_maps, t_upload;       /* analysis */
+   double t_factor_last, t_solve_last;                    /* device time of the last call (CUDA events) */
+   int64_t refine_steps_last;
+   double backward_error_last;
+   int64_t kernel_launches;    /* cumulative count of this library's kernel launches */
+   int64_t num_null_pivots_last, num_two_by_two_last;
+} b200kkt_stats;
+
+/* Handle life cycle.  Replaces JOB=-1 / JOB=-2 (MUMPSSolver.cpp:16-49).
+ * device >= 0: CUDA device ordinal.  device == -1: host-only handle (symbolic phase and plan
+ * getters work, every numeric call fails with B200KKT_ECUDA) — there is no CPU numeric path. */
+int b200kkt_create(b200kkt_handle** h, int device, int num_gpus);
+int b200kkt_destroy(b200kkt_handle* h);
+
+/* Options (defaults need no user action).  Names: "ordering" (0 METIS, 1 natural),
+ * "kkt_pairing", "relax_small", "relax_mid", "relax_big", "scaling_sweeps", "null_pivot_tol",
+ * "refine_max_steps", "refine_tol", "use_graph". */
+int b200kkt_set_option(b200kkt_handle* h, const char* name, double value);
+/* Optional user ordering for the next analyse (perm[new] = old, length N); NULL clears it. */
+int b200kkt_set_user_permutation(b200kkt_handle* h, const int64_t* perm, uint64_t n);
+
+/* Symbolic analysis.  Replaces do_symbolic_analysis -> JOB=1 (MUMPSSolver.cpp:72-83,149-157).
+ * Re-callable with another pattern/dimension (Preprocessing.cpp:60 then
+ * PrimalDualRegularization.hpp:147).  num_primal = number of primal rows n (rows >= n are
+ * multiplier rows); pass N (or 0) if unknown. */
+int b200kkt_analyse(b200kkt_handle* h, uint64_t n, uint64_t nnz, uint64_t reg_size, uint64_t num_primal,
+                    const uint64_t* row, const uint64_t* col);
+
+/* Numeric factorization.  Replaces do_numerical_factorization -> JOB=2 (MUMPSSolver.cpp:85-89).
+ * values: nnz doubles in analysis order (matrix.data_pointer()). */
+int b200kkt_factorize(b200kkt_handle* h, const double* values);
+/* Same, when only the leading reg_size slots changed since the last factorize (the inertia
+ * correction loop, PrimalDualRegularization.hpp:178-186,210-211): uploads reg_size doubles. */
+int b200kkt_refactorize_shifted(b200kkt_handle* h, const double* reg_values);
+/* Same as factorize, values already resident in device memory. */
+int b200kkt_factorize_device(b200kkt_handle* h, const double* d_values);
+
+/* Inertia of the last factorization.  Replaces get_inertia / number_negative_eigenvalues /
+ * matrix_is_singular / rank, i.e. INFOG(12) and INFOG(28) (MUMPSSolver.cpp:124-147). */
+int b200kkt_inertia(const b200kkt_handle* h, uint64_t* n_pos, uint64_t* n_neg, uint64_t* n_zero);
+
+/* Solve with the last factorization plus iterative refinement.  Replaces
+ * solve_indefinite_system(matrix, rhs, result) -> JOB=3 (MUMPSSolver.cpp:91-96).
+ * backward_error (may be NULL) receives ||b-Kx||_inf / (||K||_inf ||x||_inf + ||b||_inf). */
+int b200kkt_solve(b200kkt_handle* h, const double* rhs, double* x, double* backward_error);
+int b200kkt_solve_device(b200kkt_handle* h, const double* d_rhs, double* d_x, double* backward_error);
+
+/* Parity hooks: the assembly permutation.  perm[new] = old (length N); scatter_map[slot] = offset
+ * of COO slot in the front pool (length nnz).  Either pointer may be NULL. */
+int b200kkt_get_permutation(const b200kkt_handle* h, uint64_t* perm, uint64_t* scatter_map);
+int b200kkt_get_stats(const b200kkt_handle* h, b200kkt_stats* stats);
+const char* b200kkt_last_error(const b200kkt_handle* h);
+
+/* Plan getters (integer plan of the symbolic phase).  sizes[0..7] = number of fronts, total row
+ * entries, pool doubles, levels, sum of boundary rows, distinct assembly destinations, 0, 0. */
+int b200kkt_plan_sizes(const b200kkt_handle* h, int64_t sizes[8]);
+/* per front (length = number of fronts): pivots k, order f, leading dimension, pool offset,
+ * parent front (-1 root), level, first pivot column (new numbering).  Any pointer may be NULL. */
+int b200kkt_plan_fronts(const b200kkt_handle* h, int32_t* k, int32_t* f, int32_t* ld, int64_t* pool_offset,
+                        int32_t* parent, int32_t* level, int32_t* first_col);
+/* rows_off: number of fronts + 1; rows: total row entries (new numbering, pivots first). */
+int b200kkt_plan_rows(const b200kkt_handle* h, int64_t* rows_off, int32_t* rows);
+
+/* Debug/parity: run scaling + assembly only and copy the assembled front pool (pool_doubles) and
+ * the row scaling (length N, may be NULL) back to the host. */
+int b200kkt_debug_assemble(b200kkt_handle* h, const double* values, double* pool_out, double* scale_out);
+/* Debug/parity: after factorize, copy back the factored pool, D (diag, offdiag: length N each, new
+ * numbering incl. in-front pivoting), pivot types (0 1x1, 1/2 first/second of 2x2, 3 null) and the
+ * in-front pivot permutation.  Any pointer may be NULL. */
+int b200kkt_debug_factor(b200kkt_handle* h, double* pool_out, double* d_diag, double* d_off, int32_t* piv_type,
+                         int32_t* local_perm);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* B200KKT_H */

@@ -1,0 +1,235 @@
+"""numpy emulation of the device numeric phase, driven by the integer plan (test infrastructure).
+
+Mirrors the CUDA algorithm step by step (uno_b200/csrc/kernels.cu): assembly through the
+scatter map, extend-add through the front row lists, blocked Bunch-Kaufman with the pivot search
+confined to NBI x NBI diagonal blocks, null-pivot dropping, forward/diagonal/backward solves.
+It validates the plan and the pivoting strategy on the CPU; it is NOT bit-exact with the GPU
+(different summation order in the Schur updates) and it is far too slow for real sizes.
+"""
+from __future__ import annotations
+
+import numpy as np
+
+NBI = 32
+ALPHA = (1.0 + np.sqrt(17.0)) / 8.0
+
+
+def equilibrate(kkt, values, sweeps=3):
+    """Power-of-two Ruiz sweeps, same rule as k_scale_sweep."""
+    n = kkt.dim
+    r = kkt.row.astype(np.int64)
+    c = kkt.col.astype(np.int64)
+    a = np.abs(values)
+    sc = np.ones(n)
+    for _ in range(sweeps):
+        m = np.zeros(n)
+        np.maximum.at(m, r, a * sc[c])
+        np.maximum.at(m, c, a * sc[r])
+        m *= sc
+        ok = (m > 0) & (m < 1e300)
+        e = np.zeros(n, dtype=np.int64)
+        _, ex = np.frexp(m[ok])
+        e[ok] = ex - 1
+        sh = -((e + 1) >> 1)
+        sc = np.where(ok, np.ldexp(sc, sh), sc)
+    return sc
+
+
+def bk_block(B, n, tol):
+    """Bunch-Kaufman on the leading n x n of the full symmetric block B (modified in place).
+    Returns perm, d, e, ptype exactly like bk_factor_block."""
+    p = np.arange(B.shape[0])
+    d = np.ones(B.shape[0])
+    e = np.zeros(B.shape[0])
+    ty = np.zeros(B.shape[0], dtype=np.int32)
+    j = 0
+    while j < n:
+        absajj = abs(B[j, j])
+        if j + 1 < n:
+            colv = np.abs(B[j + 1 : n, j])
+            r = j + 1 + int(np.argmax(colv))
+            lam = colv[r - j - 1]
+        else:
+            r, lam = j, 0.0
+        kp, step, isnull = j, 1, False
+        if not (max(absajj, lam) > tol):
+            isnull = True
+        elif absajj >= ALPHA * lam:
+            pass
+        else:
+            mask = np.ones(n, dtype=bool)
+            mask[:j] = False
+            mask[r] = False
+            sigma = np.max(np.abs(B[:n, r][mask]))
+            if absajj * sigma >= ALPHA * lam * lam:
+                pass
+            elif abs(B[r, r]) >= ALPHA * sigma:
+                kp = r
+            else:
+                kp, step = r, 2
+        kk = j + step - 1
+        if kp != kk:
+            B[[kk, kp], :] = B[[kp, kk], :]
+            B[:, [kk, kp]] = B[:, [kp, kk]]
+            p[[kk, kp]] = p[[kp, kk]]
+        if step == 1:
+            dj = B[j, j]
+            if isnull:
+                B[j + 1 :, j] = 0.0
+                d[j], e[j], ty[j] = 1.0, 0.0, 3
+            else:
+                l = B[j + 1 : n, j] / dj
+                B[j + 1 : n, j + 1 : n] -= np.outer(l, B[j + 1 : n, j])
+                B[j + 1 : n, j] = l
+                d[j], e[j], ty[j] = dj, 0.0, 0
+        else:
+            a, b, c = B[j, j], B[j + 1, j], B[j + 1, j + 1]
+            det = a * c - b * b
+            w1 = B[j + 2 : n, j].copy()
+            w2 = B[j + 2 : n, j + 1].copy()
+            l1 = (c * w1 - b * w2) / det
+            l2 = (a * w2 - b * w1) / det
+            B[j + 2 : n, j + 2 : n] -= np.outer(l1, w1) + np.outer(l2, w2)
+            B[j + 2 : n, j] = l1
+            B[j + 2 : n, j + 1] = l2
+            B[j + 1, j] = 0.0
+            d[j], d[j + 1], e[j], e[j + 1] = a, c, b, 0.0
+            ty[j], ty[j + 1] = 1, 2
+        j += step
+    return p, d, e, ty
+
+
+class EmulatedFactorization:
+    def __init__(self, plan, perm, scatter, kkt, values, sweeps=3, null_tol=1e-14):
+        self.plan = plan
+        self.perm = np.asarray(perm)
+        self.n = kkt.dim
+        self.scale = equilibrate(kkt, values, sweeps)
+        k, f, ld, off = plan["k"], plan["f"], plan["ld"], plan["pool_offset"]
+        nsn = plan["num_fronts"]
+        pool = np.zeros(plan["pool_doubles"])
+        r = kkt.row.astype(np.int64)
+        c = kkt.col.astype(np.int64)
+        np.add.at(pool, scatter, values * self.scale[r] * self.scale[c])
+        self.assembled = pool.copy()
+        rows_off, rows = plan["rows_off"], plan["rows"]
+        first = plan["first_col"]
+        self.dd = np.ones(self.n)
+        self.de = np.zeros(self.n)
+        self.ptype = np.zeros(self.n, dtype=np.int32)
+        self.lperm = np.zeros(self.n, dtype=np.int64)
+        self.fronts = [None] * nsn
+        children = [[] for _ in range(nsn)]
+        for s in range(nsn):
+            if plan["parent"][s] >= 0:
+                children[plan["parent"][s]].append(s)
+        self.children = children
+        self.relmap = [None] * nsn
+        for s in range(nsn):
+            fs, ks = int(f[s]), int(k[s])
+            F = pool[off[s] : off[s] + ld[s] * fs].reshape(fs, ld[s]).T[:fs, :].copy()   # column-major -> F[row, col]
+            F = np.tril(F) + np.tril(F, -1).T
+            for ch in children[s]:
+                Fc = self.fronts[ch]
+                kc = int(k[ch])
+                crow = rows[rows_off[ch] + kc : rows_off[ch + 1]]
+                prow = rows[rows_off[s] : rows_off[s + 1]]
+                loc = np.searchsorted(prow[ks:], crow) + ks
+                inpiv = crow < first[s] + ks
+                loc = np.where(inpiv, crow - first[s], loc)
+                assert np.all(prow[loc] == crow)
+                self.relmap[ch] = loc
+                F[np.ix_(loc, loc)] += Fc["cb"]
+            # blocked restricted Bunch-Kaufman on the first ks columns
+            lp = np.arange(ks)
+            for j0 in range(0, ks, NBI):
+                nbw = min(NBI, ks - j0)
+                j1 = j0 + nbw
+                B = F[j0:j1, j0:j1].copy()
+                p, d, e, ty = bk_block(B, nbw, null_tol)
+                L11 = np.tril(B, -1) + np.eye(nbw)
+                q = first[s] + j0
+                self.dd[q : q + nbw], self.de[q : q + nbw], self.ptype[q : q + nbw] = d, e, ty
+                lp[j0:j1] = lp[j0:j1][p]
+                F[j0:j1, :j0] = F[j0:j1, :j0][p, :]
+                X = F[j1:, j0:j1][:, p]
+                Wm = np.linalg.solve(L11, X.T).T      # X L11^{-T}
+                D = np.diag(d) + np.diag(e[:-1], -1) + np.diag(e[:-1], 1)
+                Lm = np.linalg.solve(D, Wm.T).T
+                null = ty == 3
+                Lm[:, null] = 0.0
+                Wm[:, null] = 0.0
+                F[j0:j1, j0:j1] = np.tril(B, -1) + np.diag(d)
+                F[j1:, j0:j1] = Lm
+                F[j1:, j1:] -= Wm @ Lm.T
+            self.lperm[first[s] : first[s] + ks] = lp
+            self.fronts[s] = {"L": F[:, :ks].copy(), "cb": F[ks:, ks:].copy()}
+
+    def inertia(self):
+        pos = neg = zero = 0
+        q = 0
+        while q < self.n:
+            t = self.ptype[q]
+            if t == 0:
+                if self.dd[q] > 0: pos += 1
+                else: neg += 1
+                q += 1
+            elif t == 1:
+                a, b, c = self.dd[q], self.de[q], self.dd[q + 1]
+                det = a * c - b * b
+                if det < 0: pos += 1; neg += 1
+                elif a > 0: pos += 2
+                else: neg += 2
+                q += 2
+            else:
+                zero += 1
+                q += 1
+        return pos, neg, zero
+
+    def solve(self, b):
+        plan = self.plan
+        k, first = plan["k"], plan["first_col"]
+        rows_off, rows = plan["rows_off"], plan["rows"]
+        nsn = plan["num_fronts"]
+        zg = (self.scale * b)[self.perm]
+        z2 = np.zeros(self.n)
+        cvec = [None] * nsn
+        for s in range(nsn):
+            ks = int(k[s])
+            L = self.fronts[s]["L"]
+            v = np.zeros(L.shape[0])
+            v[:ks] = zg[first[s] : first[s] + ks]
+            for ch in self.children[s]:
+                v[self.relmap[ch]] += cvec[ch]
+            y = v[:ks][self.lperm[first[s] : first[s] + ks]]
+            L11 = np.tril(L[:ks, :], -1) + np.eye(ks)
+            y = np.linalg.solve(L11, y)
+            cvec[s] = v[ks:] - L[ks:, :] @ y
+            z2[first[s] : first[s] + ks] = y
+        xg = np.zeros(self.n)
+        for s in range(nsn - 1, -1, -1):
+            ks = int(k[s])
+            L = self.fronts[s]["L"]
+            y = z2[first[s] : first[s] + ks].copy()
+            q0 = first[s]
+            j = 0
+            while j < ks:
+                t = self.ptype[q0 + j]
+                if t == 0:
+                    y[j] /= self.dd[q0 + j]; j += 1
+                elif t == 1:
+                    a, bb, c = self.dd[q0 + j], self.de[q0 + j], self.dd[q0 + j + 1]
+                    det = a * c - bb * bb
+                    y1, y2 = y[j], y[j + 1]
+                    y[j], y[j + 1] = (c * y1 - bb * y2) / det, (a * y2 - bb * y1) / det
+                    j += 2
+                else:
+                    y[j] = 0.0; j += 1
+            xb = xg[rows[rows_off[s] + ks : rows_off[s + 1]]]
+            y -= L[ks:, :].T @ xb
+            L11 = np.tril(L[:ks, :], -1) + np.eye(ks)
+            y = np.linalg.solve(L11.T, y)
+            xg[first[s] + self.lperm[first[s] : first[s] + ks]] = y
+        x = np.zeros(self.n)
+        x[self.perm] = xg
+        return x * self.scale

@@ -1,0 +1,241 @@
+"""ctypes binding of include/b200kkt.h plus a thin test/bench-side mirror of the reference's
+solver interface (uno/ingredients/subproblem_solvers/DirectSymmetricIndefiniteLinearSolver.hpp:13-25).
+
+The product is the shared library; this file only marshals numpy arrays into it.  There is no
+fallback: if the library is missing or the handle has no CUDA device, numeric calls raise.
+"""
+from __future__ import annotations
+
+import ctypes as C
+from pathlib import Path
+
+import numpy as np
+
+_LIB_PATH = Path(__file__).resolve().parent / "lib" / "libb200kkt.so"
+
+EXPORTED_SYMBOLS = [
+    "b200kkt_create", "b200kkt_destroy", "b200kkt_set_option", "b200kkt_set_user_permutation", "b200kkt_analyse",
+    "b200kkt_factorize", "b200kkt_refactorize_shifted", "b200kkt_factorize_device", "b200kkt_inertia", "b200kkt_solve",
+    "b200kkt_solve_device", "b200kkt_get_permutation", "b200kkt_get_stats", "b200kkt_last_error", "b200kkt_plan_sizes",
+    "b200kkt_plan_fronts", "b200kkt_plan_rows", "b200kkt_debug_assemble", "b200kkt_debug_factor",
+]
+
+
+class Stats(C.Structure):
+    _fields_ = [
+        ("n", C.c_int64), ("nnz", C.c_int64), ("reg_size", C.c_int64),
+        ("num_fronts", C.c_int64), ("num_levels", C.c_int64), ("max_front", C.c_int64), ("max_pivots", C.c_int64),
+        ("num_pairs", C.c_int64), ("nnz_factor", C.c_int64), ("pool_doubles", C.c_int64), ("assembly_distinct", C.c_int64),
+        ("flops_factor", C.c_double), ("flops_tensor", C.c_double),
+        ("t_ordering", C.c_double), ("t_symbolic", C.c_double), ("t_maps", C.c_double), ("t_upload", C.c_double),
+        ("t_factor_last", C.c_double), ("t_solve_last", C.c_double),
+        ("refine_steps_last", C.c_int64), ("backward_error_last", C.c_double), ("kernel_launches", C.c_int64),
+        ("num_null_pivots_last", C.c_int64), ("num_two_by_two_last", C.c_int64),
+    ]
+
+    def as_dict(self):
+        return {name: getattr(self, name) for name, _ in self._fields_}
+
+
+_lib = None
+
+
+def load_library():
+    """Load libb200kkt.so (built in-tree by uno_b200.build).  Raises if it is missing."""
+    global _lib
+    if _lib is not None:
+        return _lib
+    if not _LIB_PATH.exists():
+        raise RuntimeError(f"{_LIB_PATH} is missing: run `python -m uno_b200.build` (there is no fallback path)")
+    lib = C.CDLL(str(_LIB_PATH))
+    H = C.c_void_p
+    P = C.POINTER
+    lib.b200kkt_create.argtypes = [P(H), C.c_int, C.c_int]
+    lib.b200kkt_destroy.argtypes = [H]
+    lib.b200kkt_set_option.argtypes = [H, C.c_char_p, C.c_double]
+    lib.b200kkt_set_user_permutation.argtypes = [H, C.c_void_p, C.c_uint64]
+    lib.b200kkt_analyse.argtypes = [H, C.c_uint64, C.c_uint64, C.c_uint64, C.c_uint64, C.c_void_p, C.c_void_p]
+    lib.b200kkt_factorize.argtypes = [H, C.c_void_p]
+    lib.b200kkt_refactorize_shifted.argtypes = [H, C.c_void_p]
+    lib.b200kkt_factorize_device.argtypes = [H, C.c_void_p]
+    lib.b200kkt_inertia.argtypes = [H, P(C.c_uint64), P(C.c_uint64), P(C.c_uint64)]
+    lib.b200kkt_solve.argtypes = [H, C.c_void_p, C.c_void_p, P(C.c_double)]
+    lib.b200kkt_solve_device.argtypes = [H, C.c_void_p, C.c_void_p, P(C.c_double)]
+    lib.b200kkt_get_permutation.argtypes = [H, C.c_void_p, C.c_void_p]
+    lib.b200kkt_get_stats.argtypes = [H, P(Stats)]
+    lib.b200kkt_last_error.argtypes = [H]
+    lib.b200kkt_last_error.restype = C.c_char_p
+    lib.b200kkt_plan_sizes.argtypes = [H, P(C.c_int64)]
+    lib.b200kkt_plan_fronts.argtypes = [H] + [C.c_void_p] * 7
+    lib.b200kkt_plan_rows.argtypes = [H, C.c_void_p, C.c_void_p]
+    lib.b200kkt_debug_assemble.argtypes = [H, C.c_void_p, C.c_void_p, C.c_void_p]
+    lib.b200kkt_debug_factor.argtypes = [H] + [C.c_void_p] * 5
+    for name in EXPORTED_SYMBOLS:
+        if name != "b200kkt_last_error":
+            getattr(lib, name).restype = C.c_int
+    _lib = lib
+    return lib
+
+
+class B200KKTError(RuntimeError):
+    pass
+
+
+def _ptr(a):
+    return None if a is None else a.ctypes.data_as(C.c_void_p)
+
+
+class KKTSolver:
+    """Python mirror of the reference solver interface, calling the C ABI.
+
+    Method names follow DirectSymmetricIndefiniteLinearSolver / MUMPSSolver
+    (uno/ingredients/subproblem_solvers/MUMPS/MUMPSSolver.hpp:17-40).  The matrix is passed as the
+    reference's COO triple (row <= col, 0-based, duplicates summed, leading regularization slots).
+    """
+
+    def __init__(self, device: int = 0, num_gpus: int = 1, **options):
+        self._lib = load_library()
+        self._h = C.c_void_p()
+        rc = self._lib.b200kkt_create(C.byref(self._h), device, num_gpus)
+        if rc != 0:
+            msg = self._lib.b200kkt_last_error(self._h).decode() if self._h else "create failed"
+            if self._h:
+                self._lib.b200kkt_destroy(self._h)
+                self._h = C.c_void_p()
+            raise B200KKTError(f"b200kkt_create failed ({rc}): {msg}")
+        self.n = 0
+        self.nnz = 0
+        self.reg_size = 0
+        for k, v in options.items():
+            self.set_option(k, v)
+
+    # -- life cycle --------------------------------------------------------------------------
+    def close(self):
+        if getattr(self, "_h", None):
+            self._lib.b200kkt_destroy(self._h)
+            self._h = C.c_void_p()
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass
+
+    def _check(self, rc, what):
+        if rc != 0:
+            raise B200KKTError(f"{what} failed ({rc}): {self._lib.b200kkt_last_error(self._h).decode()}")
+
+    def set_option(self, name: str, value: float):
+        self._check(self._lib.b200kkt_set_option(self._h, name.encode(), float(value)), "set_option")
+
+    def set_user_permutation(self, perm):
+        if perm is None:
+            self._check(self._lib.b200kkt_set_user_permutation(self._h, None, 0), "set_user_permutation")
+            return
+        p = np.ascontiguousarray(perm, dtype=np.int64)
+        self._check(self._lib.b200kkt_set_user_permutation(self._h, _ptr(p), p.size), "set_user_permutation")
+
+    # -- reference interface -----------------------------------------------------------------
+    def initialize_memory(self, number_variables, number_constraints, number_hessian_nonzeros, regularization_size):
+        """MUMPSSolver::initialize_memory (MUMPSSolver.cpp:51-70): sizes only; device memory is
+        allocated at analysis time, when the front sizes are known."""
+        self.number_variables = int(number_variables)
+        self.number_constraints = int(number_constraints)
+        self.dimension = self.number_variables + self.number_constraints
+        self.capacity = int(number_hessian_nonzeros) + int(regularization_size)
+        self.reg_size = int(regularization_size)
+
+    def do_symbolic_analysis(self, n, row, col, reg_size=0, num_primal=0):
+        row = np.ascontiguousarray(row, dtype=np.uint64)
+        col = np.ascontiguousarray(col, dtype=np.uint64)
+        assert row.shape == col.shape
+        self.n, self.nnz, self.reg_size = int(n), int(row.size), int(reg_size)
+        self._check(self._lib.b200kkt_analyse(self._h, self.n, self.nnz, self.reg_size, int(num_primal), _ptr(row), _ptr(col)), "analyse")
+
+    def do_numerical_factorization(self, values):
+        v = np.ascontiguousarray(values, dtype=np.float64)
+        assert v.size == self.nnz
+        self._check(self._lib.b200kkt_factorize(self._h, _ptr(v)), "factorize")
+
+    def refactorize_shifted(self, reg_values):
+        v = np.ascontiguousarray(reg_values, dtype=np.float64)
+        assert v.size == self.reg_size
+        self._check(self._lib.b200kkt_refactorize_shifted(self._h, _ptr(v)), "refactorize_shifted")
+
+    def factorize_device(self, device_ptr: int):
+        self._check(self._lib.b200kkt_factorize_device(self._h, C.c_void_p(device_ptr)), "factorize_device")
+
+    def get_inertia(self):
+        p, n, z = C.c_uint64(), C.c_uint64(), C.c_uint64()
+        self._check(self._lib.b200kkt_inertia(self._h, C.byref(p), C.byref(n), C.byref(z)), "inertia")
+        return int(p.value), int(n.value), int(z.value)
+
+    def number_negative_eigenvalues(self):
+        return self.get_inertia()[1]
+
+    def number_zero_eigenvalues(self):
+        return self.get_inertia()[2]
+
+    def matrix_is_singular(self):
+        return self.get_inertia()[2] > 0
+
+    def rank(self):
+        return self.n - self.get_inertia()[2]
+
+    def solve_indefinite_system(self, rhs, return_backward_error=False):
+        b = np.ascontiguousarray(rhs, dtype=np.float64)
+        assert b.size == self.n
+        x = np.empty(self.n, dtype=np.float64)
+        berr = C.c_double()
+        self._check(self._lib.b200kkt_solve(self._h, _ptr(b), _ptr(x), C.byref(berr)), "solve")
+        return (x, berr.value) if return_backward_error else x
+
+    def solve_device(self, rhs_ptr: int, x_ptr: int):
+        berr = C.c_double()
+        self._check(self._lib.b200kkt_solve_device(self._h, C.c_void_p(rhs_ptr), C.c_void_p(x_ptr), C.byref(berr)), "solve_device")
+        return berr.value
+
+    # -- parity hooks ------------------------------------------------------------------------
+    def stats(self):
+        s = Stats()
+        self._check(self._lib.b200kkt_get_stats(self._h, C.byref(s)), "get_stats")
+        return s.as_dict()
+
+    def permutation(self):
+        perm = np.empty(self.n, dtype=np.uint64)
+        scat = np.empty(self.nnz, dtype=np.uint64)
+        self._check(self._lib.b200kkt_get_permutation(self._h, _ptr(perm), _ptr(scat)), "get_permutation")
+        return perm.astype(np.int64), scat.astype(np.int64)
+
+    def plan(self):
+        sizes = (C.c_int64 * 8)()
+        self._check(self._lib.b200kkt_plan_sizes(self._h, sizes), "plan_sizes")
+        nsn, nrows = int(sizes[0]), int(sizes[1])
+        out = {"num_fronts": nsn, "pool_doubles": int(sizes[2]), "num_levels": int(sizes[3]), "sum_boundary": int(sizes[4]),
+               "assembly_distinct": int(sizes[5])}
+        i32 = lambda: np.empty(nsn, dtype=np.int32)  # noqa: E731
+        k, f, ld, parent, level, first = i32(), i32(), i32(), i32(), i32(), i32()
+        off = np.empty(nsn, dtype=np.int64)
+        self._check(self._lib.b200kkt_plan_fronts(self._h, _ptr(k), _ptr(f), _ptr(ld), _ptr(off), _ptr(parent), _ptr(level), _ptr(first)),
+                    "plan_fronts")
+        rows_off = np.empty(nsn + 1, dtype=np.int64)
+        rows = np.empty(nrows, dtype=np.int32)
+        self._check(self._lib.b200kkt_plan_rows(self._h, _ptr(rows_off), _ptr(rows)), "plan_rows")
+        out.update(k=k, f=f, ld=ld, pool_offset=off, parent=parent, level=level, first_col=first, rows_off=rows_off, rows=rows)
+        return out
+
+    def debug_assemble(self, values, want_scale=True):
+        v = np.ascontiguousarray(values, dtype=np.float64)
+        pool = np.empty(self.plan()["pool_doubles"], dtype=np.float64)
+        scale = np.empty(self.n, dtype=np.float64) if want_scale else None
+        self._check(self._lib.b200kkt_debug_assemble(self._h, _ptr(v), _ptr(pool), _ptr(scale)), "debug_assemble")
+        return pool, scale
+
+    def debug_factor(self, want_pool=True):
+        pool = np.empty(self.plan()["pool_doubles"], dtype=np.float64) if want_pool else None
+        dd = np.empty(self.n, dtype=np.float64)
+        de = np.empty(self.n, dtype=np.float64)
+        pt = np.empty(self.n, dtype=np.int32)
+        lp = np.empty(self.n, dtype=np.int32)
+        self._check(self._lib.b200kkt_debug_factor(self._h, _ptr(pool), _ptr(dd), _ptr(de), _ptr(pt), _ptr(lp)), "debug_factor")
+        return pool, dd, de, pt, lp

@@ -1,0 +1,762 @@
+// sm_100a numeric phase of the B200 KKT solver: assembly (K1/K1'), supernodal multifrontal
+// LDL^T with in-front Bunch-Kaufman pivoting (K3), FP64 tensor-core Schur updates (K4),
+// extend-add (K5), inertia (K6), level-scheduled solves (K7) and the residual for refinement (K8).
+//
+// Stands in for what dmumps_c does at JOB=2 / JOB=3 behind
+// uno/ingredients/subproblem_solvers/MUMPS/MUMPSSolver.cpp:85-96.  Nothing here is derived from
+// MUMPS; the algorithm is the textbook multifrontal method laid out for the GPU:
+// all fronts of an elimination-tree level are processed by the same batched launches.
+#include "kernels.hpp"
+
+#include <cstdio>
+
+namespace b200kkt {
+
+namespace {
+
+constexpr double BK_ALPHA = 0.6403882032022076;   // (1 + sqrt(17)) / 8
+constexpr int PANEL_THREADS = 256;
+constexpr int EA_CBW = 16;                        // parent columns owned by one extend-add CTA
+
+__device__ __forceinline__ unsigned long long ordered_bits(double v) {
+   // v >= 0: IEEE bit pattern is order preserving
+   return static_cast<unsigned long long>(__double_as_longlong(v));
+}
+
+// ------------------------------------------------------------------------------------------------
+// K1' equilibration, norms, K1 assembly, K8 residual
+// ------------------------------------------------------------------------------------------------
+__global__ void k_fill(double* p, int64_t n, double v) {
+   const int64_t i = blockIdx.x * static_cast<int64_t>(blockDim.x) + threadIdx.x;
+   if (i < n) p[i] = v;
+}
+
+// One Ruiz step with power-of-two factors: sc_out = sc_in * 2^(-ceil(e/2)), e = floor(log2(scaled row max)).
+// Powers of two keep the scaled entries exactly representable, so assembly stays bit-reproducible.
+__global__ void k_scale_sweep(CsrArrays A, const double* __restrict__ values, const double* __restrict__ sc_in,
+                              double* __restrict__ sc_out) {
+   const int64_t i = blockIdx.x * static_cast<int64_t>(blockDim.x) + threadIdx.x;
+   if (i >= A.n) return;
+   double m = 0.0;
+   for (int t = A.ptr[i]; t < A.ptr[i + 1]; ++t) m = fmax(m, fabs(values[A.slot[t]]) * sc_in[A.col[t]]);
+   const double si = sc_in[i];
+   m *= si;
+   double out = si;
+   if (m > 0.0 && m < 1.0e300) {
+      int ex;
+      frexp(m, &ex);              // m = fr * 2^ex, fr in [0.5, 1)  ->  floor(log2 m) = ex - 1
+      const int e = ex - 1;
+      const int sh = -((e + 1) >> 1);
+      out = ldexp(si, sh);
+   }
+   sc_out[i] = out;
+}
+
+__global__ void k_matrix_inf_norm(CsrArrays A, const double* __restrict__ values, unsigned long long* out_bits) {
+   const int64_t i = blockIdx.x * static_cast<int64_t>(blockDim.x) + threadIdx.x;
+   double s = 0.0;
+   if (i < A.n) for (int t = A.ptr[i]; t < A.ptr[i + 1]; ++t) s += fabs(values[A.slot[t]]);
+   for (int o = 16; o; o >>= 1) s = fmax(s, __shfl_xor_sync(0xffffffffu, s, o));
+   if ((threadIdx.x & 31) == 0 && s > 0.0) atomicMax(out_bits, ordered_bits(s));
+}
+
+__global__ void k_absmax(const double* __restrict__ v, int64_t n, unsigned long long* out_bits) {
+   double s = 0.0;
+   for (int64_t i = blockIdx.x * static_cast<int64_t>(blockDim.x) + threadIdx.x; i < n; i += static_cast<int64_t>(gridDim.x) * blockDim.x) {
+      const double a = fabs(v[i]);
+      s = (a > s || a != a) ? a : s;   // NaN propagates
+   }
+   if (s != s) s = __longlong_as_double(0x7ff0000000000000LL);   // report NaN as +inf
+   for (int o = 16; o; o >>= 1) s = fmax(s, __shfl_xor_sync(0xffffffffu, s, o));
+   if ((threadIdx.x & 31) == 0 && s > 0.0) atomicMax(out_bits, ordered_bits(s));
+}
+
+// One thread per distinct destination; its sources are summed in ascending COO slot order.
+__global__ void k_assemble(AssemblyArrays M, const double* __restrict__ values, const double* __restrict__ scale,
+                           double* __restrict__ pool) {
+   const int64_t d = blockIdx.x * static_cast<int64_t>(blockDim.x) + threadIdx.x;
+   if (d >= M.ndst) return;
+   double s = 0.0;
+   for (int t = M.seg[d]; t < M.seg[d + 1]; ++t) s += values[M.src[t]] * scale[M.row[t]] * scale[M.col[t]];
+   pool[M.dst[d]] = s;
+}
+
+__global__ void k_residual(CsrArrays A, const double* __restrict__ values, const double* __restrict__ x,
+                           const double* __restrict__ b, double* __restrict__ r) {
+   const int64_t i = blockIdx.x * static_cast<int64_t>(blockDim.x) + threadIdx.x;
+   if (i >= A.n) return;
+   double s = 0.0;
+   for (int t = A.ptr[i]; t < A.ptr[i + 1]; ++t) s += values[A.slot[t]] * x[A.col[t]];
+   r[i] = b[i] - s;
+}
+
+__global__ void k_solve_gather(int64_t n, const int* __restrict__ perm, const double* __restrict__ scale,
+                               const double* __restrict__ r, double* __restrict__ zg) {
+   const int64_t g = blockIdx.x * static_cast<int64_t>(blockDim.x) + threadIdx.x;
+   if (g >= n) return;
+   const int o = perm[g];
+   zg[g] = scale[o] * r[o];
+}
+
+__global__ void k_solve_scatter_add(int64_t n, const int* __restrict__ perm, const double* __restrict__ scale,
+                                    const double* __restrict__ xg, double* __restrict__ x) {
+   const int64_t g = blockIdx.x * static_cast<int64_t>(blockDim.x) + threadIdx.x;
+   if (g >= n) return;
+   const int o = perm[g];
+   x[o] += scale[o] * xg[g];
+}
+
+// ------------------------------------------------------------------------------------------------
+// K5 extend-add.  CTA (parent, column block) owns EA_CBW parent columns and pulls the matching
+// columns of every child's contribution block, children in ascending order -> no atomics, and the
+// summation order is fixed.
+// ------------------------------------------------------------------------------------------------
+__global__ void __launch_bounds__(256) k_extend_add(FrontArrays F, const int* __restrict__ list, double* __restrict__ pool) {
+   const int p = list[blockIdx.x];
+   const int fp = F.f[p];
+   const int cb0 = blockIdx.y * EA_CBW;
+   if (cb0 >= fp) return;
+   const int cb1 = min(cb0 + EA_CBW, fp);
+   const int ldp = F.ld[p];
+   double* Ap = pool + F.off[p];
+   const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+   for (int ci = F.child_ptr[p]; ci < F.child_ptr[p + 1]; ++ci) {
+      const int c = F.child_idx[ci];
+      const int kc = F.k[c], ldc = F.ld[c];
+      const int rc = F.f[c] - kc;
+      const int* __restrict__ rel = F.relmap + F.rel_off[c];
+      // rel is strictly increasing: columns of the child that land in [cb0, cb1) are a contiguous range
+      int lo = 0, hi = rc;
+      while (lo < hi) { const int mid = (lo + hi) >> 1; if (rel[mid] < cb0) lo = mid + 1; else hi = mid; }
+      const int jlo = lo;
+      hi = rc;
+      while (lo < hi) { const int mid = (lo + hi) >> 1; if (rel[mid] < cb1) lo = mid + 1; else hi = mid; }
+      const int jhi = lo;
+      const double* Ac = pool + F.off[c] + kc + static_cast<int64_t>(ldc) * kc;
+      for (int j = jlo + warp; j < jhi; j += 8) {
+         double* dst = Ap + static_cast<int64_t>(ldp) * rel[j];
+         const double* src = Ac + static_cast<int64_t>(ldc) * j;
+         for (int i = j + lane; i < rc; i += 32) dst[rel[i]] += src[i];
+      }
+      __syncthreads();   // next child may touch the same parent entries from another warp
+   }
+}
+
+// ------------------------------------------------------------------------------------------------
+// K3 panel kernel
+// ------------------------------------------------------------------------------------------------
+struct BkShared {
+   double B[NBI][NBI + 1];   // full symmetric diagonal block; after factorization: strict lower = L11
+   double d[NBI], e[NBI];
+   int p[NBI], type[NBI];
+   int nontrivial;
+};
+
+// Bunch-Kaufman (partial pivoting, pivot search confined to this block) by one warp.
+// Null pivots (whole remaining column <= tol) are dropped MUMPS-style: unit pivot, zero column,
+// reported as a zero eigenvalue.
+__device__ void bk_factor_block(BkShared& S, const int n, const int lane, const double tol) {
+   S.p[lane] = lane;
+   S.d[lane] = 1.0;
+   S.e[lane] = 0.0;
+   S.type[lane] = 0;
+   if (lane == 0) S.nontrivial = 0;
+   __syncwarp();
+   int j = 0;
+   while (j < n) {
+      const double absajj = fabs(S.B[j][j]);
+      double v = (lane > j && lane < n) ? fabs(S.B[lane][j]) : -1.0;
+      int r = lane;
+      for (int o = 16; o; o >>= 1) {
+         const double v2 = __shfl_xor_sync(0xffffffffu, v, o);
+         const int r2 = __shfl_xor_sync(0xffffffffu, r, o);
+         if (v2 > v || (v2 == v && r2 < r)) { v = v2; r = r2; }
+      }
+      double lam = v;
+      if (lam < 0.0) { lam = 0.0; r = j; }
+      int kp = j, step = 1;
+      bool isnull = false;
+      if (!(fmax(absajj, lam) > tol)) {
+         isnull = true;
+      } else if (absajj >= BK_ALPHA * lam) {
+         // 1x1 pivot, no interchange
+      } else {
+         double s2 = (lane >= j && lane < n && lane != r) ? fabs(S.B[lane][r]) : -1.0;
+         for (int o = 16; o; o >>= 1) s2 = fmax(s2, __shfl_xor_sync(0xffffffffu, s2, o));
+         const double sigma = s2;
+         if (absajj * sigma >= BK_ALPHA * lam * lam) {
+            // 1x1 pivot, no interchange
+         } else if (fabs(S.B[r][r]) >= BK_ALPHA * sigma) {
+            kp = r;
+         } else {
+            kp = r;
+            step = 2;
+         }
+      }
+      const int kk = j + step - 1;
+      if (kp != kk) {
+         // symmetric interchange kk <-> kp on the full block (rows carry the already computed L entries)
+         double t1 = S.B[kk][lane], t2 = S.B[kp][lane];
+         S.B[kk][lane] = t2;
+         S.B[kp][lane] = t1;
+         __syncwarp();
+         t1 = S.B[lane][kk];
+         t2 = S.B[lane][kp];
+         S.B[lane][kk] = t2;
+         S.B[lane][kp] = t1;
+         if (lane == 0) {
+            const int tp = S.p[kk];
+            S.p[kk] = S.p[kp];
+            S.p[kp] = tp;
+            S.nontrivial = 1;
+         }
+         __syncwarp();
+      }
+      if (step == 1) {
+         const double d = S.B[j][j];
+         if (isnull) {
+            if (lane > j) S.B[lane][j] = 0.0;
+            if (lane == 0) { S.d[j] = 1.0; S.e[j] = 0.0; S.type[j] = 3; }
+         } else {
+            double li = 0.0;
+            const bool act = lane > j && lane < n;
+            if (act) {
+               li = S.B[lane][j] / d;
+               for (int c = j + 1; c < n; ++c) S.B[lane][c] -= li * S.B[c][j];
+            }
+            __syncwarp();
+            if (act) S.B[lane][j] = li;
+            if (lane == 0) { S.d[j] = d; S.e[j] = 0.0; S.type[j] = 0; }
+         }
+      } else {
+         const double a = S.B[j][j], b = S.B[j + 1][j], c = S.B[j + 1][j + 1];
+         const double det = a * c - b * b;
+         double l1 = 0.0, l2 = 0.0;
+         const bool act = lane > j + 1 && lane < n;
+         if (act) {
+            const double w1 = S.B[lane][j], w2 = S.B[lane][j + 1];
+            l1 = (c * w1 - b * w2) / det;
+            l2 = (a * w2 - b * w1) / det;
+            for (int cc = j + 2; cc < n; ++cc) S.B[lane][cc] -= l1 * S.B[cc][j] + l2 * S.B[cc][j + 1];
+         }
+         __syncwarp();
+         if (act) { S.B[lane][j] = l1; S.B[lane][j + 1] = l2; }
+         if (lane == 0) {
+            S.B[j + 1][j] = 0.0;
+            S.d[j] = a; S.d[j + 1] = c; S.e[j] = b; S.e[j + 1] = 0.0;
+            S.type[j] = 1; S.type[j + 1] = 2;
+         }
+      }
+      __syncwarp();
+      j += step;
+   }
+}
+
+// grid = (front in batch, row chunk).  Every CTA factors the diagonal block redundantly (same
+// data, same instruction order -> identical results), chunk 0 writes it back.
+__global__ void __launch_bounds__(PANEL_THREADS) k_panel(FrontArrays F, const int* __restrict__ list, const int j0, const int J0,
+                                                         FactorArrays W, const double null_tol) {
+   __shared__ BkShared S;
+   const int s = list[blockIdx.x];
+   const int k = F.k[s], f = F.f[s], ld = F.ld[s];
+   const int nbw = min(NBI, k - j0), j1 = j0 + nbw;
+   const int ibeg = j1 + blockIdx.y * PANEL_THREADS;
+   if (blockIdx.y > 0 && ibeg >= f) return;
+   double* A = W.pool + F.off[s];
+   const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+
+   for (int idx = tid; idx < NBI * NBI; idx += PANEL_THREADS) {
+      const int r = idx % NBI, c = idx / NBI;
+      double v;
+      if (r < nbw && c < nbw) {
+         v = (r >= c) ? A[(j0 + r) + static_cast<int64_t>(ld) * (j0 + c)] : A[(j0 + c) + static_cast<int64_t>(ld) * (j0 + r)];
+      } else {
+         v = (r == c) ? 1.0 : 0.0;
+      }
+      S.B[r][c] = v;
+   }
+   __syncthreads();
+   if (warp == 0) bk_factor_block(S, nbw, lane, null_tol);
+   __syncthreads();
+
+   if (blockIdx.y == 0) {
+      for (int idx = tid; idx < NBI * NBI; idx += PANEL_THREADS) {
+         const int r = idx % NBI, c = idx / NBI;
+         if (r < nbw && c < nbw && r >= c) A[(j0 + r) + static_cast<int64_t>(ld) * (j0 + c)] = (r == c) ? S.d[c] : S.B[r][c];
+      }
+      if (tid < nbw) {
+         const int q = F.first[s] + j0 + tid;
+         W.dd[q] = S.d[tid];
+         W.de[q] = S.e[tid];
+         W.ptype[q] = S.type[tid];
+         W.lperm[q] = j0 + S.p[tid];
+      }
+      if (tid == 0) W.blkflag[F.first[s] + j0] = S.nontrivial;
+   }
+
+   const int i = ibeg + tid;
+   if (i >= f) return;
+   double w[NBI];
+#pragma unroll
+   for (int c = 0; c < NBI; ++c) w[c] = (c < nbw) ? A[i + static_cast<int64_t>(ld) * (j0 + S.p[c])] : 0.0;
+   // w <- w * L11^{-T}
+#pragma unroll
+   for (int c = 1; c < NBI; ++c) {
+      double acc = w[c];
+#pragma unroll
+      for (int t = 0; t < c; ++t) acc -= w[t] * S.B[c][t];
+      w[c] = acc;
+   }
+   // l = w * D^{-1}
+   double l[NBI];
+#pragma unroll
+   for (int c = 0; c < NBI; ++c) {
+      const int ty = S.type[c];
+      if (ty == 0) {
+         l[c] = w[c] / S.d[c];
+      } else if (ty == 1) {
+         if (c + 1 < NBI) {
+            const double a = S.d[c], b = S.e[c], cc = S.d[c + 1];
+            const double det = a * cc - b * b;
+            l[c] = (cc * w[c] - b * w[c + 1]) / det;
+            l[c + 1] = (a * w[c + 1] - b * w[c]) / det;
+         }
+      } else if (ty == 3) {
+         l[c] = 0.0;
+         w[c] = 0.0;
+      }
+   }
+   double* Wp = W.wpool + F.woff[s];
+#pragma unroll
+   for (int c = 0; c < NBI; ++c) {
+      if (c < nbw) {
+         A[i + static_cast<int64_t>(ld) * (j0 + c)] = l[c];
+         Wp[i + static_cast<int64_t>(ld) * (j0 - J0 + c)] = w[c];
+      }
+   }
+}
+
+// rows j0..j0+nbw of the already computed L columns [0, j0) follow the block's interchanges
+__global__ void __launch_bounds__(256) k_permute_rows(FrontArrays F, const int* __restrict__ list, const int j0, FactorArrays W) {
+   const int s = list[blockIdx.x];
+   const int first = F.first[s];
+   if (!W.blkflag[first + j0]) return;
+   const int c = blockIdx.y * 256 + threadIdx.x;
+   if (c >= j0) return;
+   const int nbw = min(NBI, F.k[s] - j0);
+   double* colp = W.pool + F.off[s] + static_cast<int64_t>(F.ld[s]) * c + j0;
+   const int* lp = W.lperm + first + j0;
+   double tmp[NBI];
+#pragma unroll
+   for (int t = 0; t < NBI; ++t) if (t < nbw) tmp[t] = colp[lp[t] - j0];
+#pragma unroll
+   for (int t = 0; t < NBI; ++t) if (t < nbw) colp[t] = tmp[t];
+}
+
+// ------------------------------------------------------------------------------------------------
+// K4 Schur-complement update on the FP64 tensor pipe:  C[m,n] -= sum_k W[m,k] * L[n,k]
+// (W = L*D panel, both operands column-major with m/n contiguous -> "NT" GEMM).
+// Tiles BM x BN x 16, 3-stage cp.async pipeline, warp-level mma.sync m8n8k4 f64 (SASS DMMA.8x8x4;
+// tcgen05 has no f64 kind).  Only tiles touching the lower triangle are computed.
+// ------------------------------------------------------------------------------------------------
+__device__ __forceinline__ void cp_async16(void* smem_dst, const void* gmem_src, bool pred) {
+   const unsigned saddr = static_cast<unsigned>(__cvta_generic_to_shared(smem_dst));
+   const int bytes = pred ? 16 : 0;
+   asm volatile("cp.async.cg.shared.global [%0], [%1], 16, %2;\n" ::"r"(saddr), "l"(gmem_src), "r"(bytes));
+}
+__device__ __forceinline__ void cp_async_commit() { asm volatile("cp.async.commit_group;\n" ::); }
+template <int N>
+__device__ __forceinline__ void cp_async_wait() { asm volatile("cp.async.wait_group %0;\n" ::"n"(N)); }
+
+__device__ __forceinline__ void dmma8x8x4(double& c0, double& c1, const double a, const double b) {
+   asm volatile("mma.sync.aligned.m8n8k4.row.col.f64.f64.f64.f64 {%0,%1}, {%2}, {%3}, {%0,%1};\n" : "+d"(c0), "+d"(c1) : "d"(a), "d"(b));
+}
+
+constexpr int UPD_BK = 16;
+constexpr int UPD_STAGES = 3;
+
+template <int BM, int BN, int WARPS_M, int WARPS_N>
+__global__ void __launch_bounds__(WARPS_M* WARPS_N * 32) k_update(FrontArrays F, const int* __restrict__ list, const int mode, const int j0,
+                                                                  const int J0, FactorArrays W) {
+   constexpr int NT = WARPS_M * WARPS_N * 32;
+   constexpr int LDA = BM + 4, LDB = BN + 4;   // +4 doubles: conflict-free fragment loads (LD mod 16 == 4)
+   constexpr int WTM = BM / WARPS_M, WTN = BN / WARPS_N, MF = WTM / 8, NF = WTN / 8;
+   constexpr int STAGE_DOUBLES = UPD_BK * (LDA + LDB);
+   extern __shared__ __align__(16) double smem[];
+
+   const int s = list[blockIdx.x];
+   const int k = F.k[s], f = F.f[s], ld = F.ld[s];
+   const int J1 = min(J0 + NBO, k);
+   int r0, c0, c1, kbeg, K;
+   if (mode == 0) {
+      const int j1 = min(j0 + NBI, k);
+      r0 = j1; c0 = j1; c1 = J1; kbeg = j0 - J0; K = j1 - j0;
+   } else {
+      r0 = J1; c0 = J1; c1 = f; kbeg = 0; K = J1 - J0;
+   }
+   if (c0 >= c1 || r0 >= f || K <= 0) return;
+   const int m0 = (r0 & ~1) + blockIdx.y * BM;
+   const int n0 = (c0 & ~1) + blockIdx.z * BN;
+   if (m0 >= f || n0 >= c1) return;
+   if (m0 + BM <= n0) return;   // tile entirely above the diagonal
+
+   double* A = W.pool + F.off[s];
+   const double* Wp = W.wpool + F.woff[s] + static_cast<int64_t>(ld) * kbeg;   // operand A: rows m, K columns
+   const double* Lp = A + static_cast<int64_t>(ld) * (J0 + kbeg);               // operand B: rows n, K columns
+
+   const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+   const int wm0 = (warp % WARPS_M) * WTM, wn0 = (warp / WARPS_M) * WTN;
+
+   auto load_stage = [&](const int stage, const int kt) {
+      double* As = smem + stage * STAGE_DOUBLES;
+      double* Bs = As + UPD_BK * LDA;
+      const int kbase = kt * UPD_BK;
+      for (int q = tid; q < UPD_BK * (BM / 2); q += NT) {
+         const int kk = q / (BM / 2), mm = (q % (BM / 2)) * 2;
+         const bool pred = (kbase + kk < K) && (m0 + mm < ld);
+         const double* src = pred ? (Wp + (m0 + mm) + static_cast<int64_t>(ld) * (kbase + kk)) : Wp;
+         cp_async16(As + kk * LDA + mm, src, pred);
+      }
+      for (int q = tid; q < UPD_BK * (BN / 2); q += NT) {
+         const int kk = q / (BN / 2), nn = (q % (BN / 2)) * 2;
+         const bool pred = (kbase + kk < K) && (n0 + nn < ld);
+         const double* src = pred ? (Lp + (n0 + nn) + static_cast<int64_t>(ld) * (kbase + kk)) : Lp;
+         cp_async16(Bs + kk * LDB + nn, src, pred);
+      }
+   };
+
+   double acc[MF][NF][2];
+#pragma unroll
+   for (int a = 0; a < MF; ++a)
+#pragma unroll
+      for (int b = 0; b < NF; ++b) { acc[a][b][0] = 0.0; acc[a][b][1] = 0.0; }
+
+   const int num_kt = (K + UPD_BK - 1) / UPD_BK;
+#pragma unroll
+   for (int st = 0; st < UPD_STAGES - 1; ++st) {
+      if (st < num_kt) load_stage(st, st);
+      cp_async_commit();
+   }
+   for (int kt = 0; kt < num_kt; ++kt) {
+      cp_async_wait<UPD_STAGES - 2>();
+      __syncthreads();
+      {
+         const int nk = kt + UPD_STAGES - 1;
+         if (nk < num_kt) load_stage(nk % UPD_STAGES, nk);
+         cp_async_commit();
+      }
+      const double* As = smem + (kt % UPD_STAGES) * STAGE_DOUBLES;
+      const double* Bs = As + UPD_BK * LDA;
+#pragma unroll
+      for (int k4 = 0; k4 < UPD_BK / 4; ++k4) {
+         const int krow = k4 * 4 + (lane & 3);
+         double af[MF], bf[NF];
+#pragma unroll
+         for (int a = 0; a < MF; ++a) af[a] = As[krow * LDA + wm0 + a * 8 + (lane >> 2)];
+#pragma unroll
+         for (int b = 0; b < NF; ++b) bf[b] = Bs[krow * LDB + wn0 + b * 8 + (lane >> 2)];
+#pragma unroll
+         for (int a = 0; a < MF; ++a)
+#pragma unroll
+            for (int b = 0; b < NF; ++b) dmma8x8x4(acc[a][b][0], acc[a][b][1], af[a], bf[b]);
+      }
+   }
+   cp_async_wait<0>();
+
+#pragma unroll
+   for (int a = 0; a < MF; ++a) {
+      const int m = m0 + wm0 + a * 8 + (lane >> 2);
+      if (m < r0 || m >= f) continue;
+#pragma unroll
+      for (int b = 0; b < NF; ++b) {
+#pragma unroll
+         for (int h = 0; h < 2; ++h) {
+            const int n = n0 + wn0 + b * 8 + 2 * (lane & 3) + h;
+            if (n >= c0 && n < c1 && m >= n) A[m + static_cast<int64_t>(ld) * n] -= acc[a][b][h];
+         }
+      }
+   }
+}
+
+// ------------------------------------------------------------------------------------------------
+// K6 inertia from the D blocks
+// ------------------------------------------------------------------------------------------------
+__global__ void k_inertia(int64_t n, FactorArrays W, int* counters) {
+   int pos = 0, neg = 0, zero = 0, two = 0;
+   for (int64_t q = blockIdx.x * static_cast<int64_t>(blockDim.x) + threadIdx.x; q < n; q += static_cast<int64_t>(gridDim.x) * blockDim.x) {
+      const int ty = W.ptype[q];
+      if (ty == 0) {
+         if (W.dd[q] > 0.0) ++pos; else ++neg;
+      } else if (ty == 1) {
+         const double a = W.dd[q], b = W.de[q], c = W.dd[q + 1];
+         const double det = a * c - b * b;
+         if (det < 0.0) { ++pos; ++neg; }
+         else if (a > 0.0) pos += 2;
+         else neg += 2;
+         ++two;
+      } else if (ty == 3) {
+         ++zero;
+      }
+   }
+   for (int o = 16; o; o >>= 1) {
+      pos += __shfl_xor_sync(0xffffffffu, pos, o);
+      neg += __shfl_xor_sync(0xffffffffu, neg, o);
+      zero += __shfl_xor_sync(0xffffffffu, zero, o);
+      two += __shfl_xor_sync(0xffffffffu, two, o);
+   }
+   if ((threadIdx.x & 31) == 0) {
+      if (pos) atomicAdd(counters + 0, pos);
+      if (neg) atomicAdd(counters + 1, neg);
+      if (zero) atomicAdd(counters + 2, zero);
+      if (two) atomicAdd(counters + 3, two);
+   }
+}
+
+// ------------------------------------------------------------------------------------------------
+// K7 solves.  One CTA per front; fronts of one level are independent.
+// Forward: v = [rhs pivots ; 0] + sum children boundary vectors, y1 = L11^{-1} P v1, boundary -= L21 y1.
+// Backward: y1 = D^{-1} y1 - L21^T x_boundary, x1 = L11^{-T} y1, scattered back through P^T.
+// ------------------------------------------------------------------------------------------------
+__global__ void __launch_bounds__(256) k_forward(FrontArrays F, const int* __restrict__ list, FactorArrays W, double* __restrict__ zg,
+                                                 double* __restrict__ z2, double* __restrict__ cpool) {
+   __shared__ double Ls[NBI][NBI + 1];
+   __shared__ double yp[NBI];
+   const int s = list[blockIdx.x];
+   const int k = F.k[s], f = F.f[s], ld = F.ld[s], first = F.first[s];
+   const int r = f - k;
+   const double* A = W.pool + F.off[s];
+   double* cb = cpool + F.rel_off[s];
+   const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+
+   for (int i = tid; i < r; i += 256) cb[i] = 0.0;
+   __syncthreads();
+   for (int ci = F.child_ptr[s]; ci < F.child_ptr[s + 1]; ++ci) {
+      const int c = F.child_idx[ci];
+      const int rc = F.f[c] - F.k[c];
+      const int* __restrict__ rel = F.relmap + F.rel_off[c];
+      const double* cc = cpool + F.rel_off[c];
+      for (int i = tid; i < rc; i += 256) {
+         const int loc = rel[i];
+         const double v = cc[i];
+         if (loc < k) zg[first + loc] += v; else cb[loc - k] += v;
+      }
+      __syncthreads();
+   }
+   double* y = z2 + first;
+   for (int j = tid; j < k; j += 256) y[j] = zg[first + W.lperm[first + j]];
+   __syncthreads();
+
+   for (int jb = 0; jb < k; jb += NBI) {
+      const int nb = min(NBI, k - jb);
+      for (int idx = tid; idx < NBI * NBI; idx += 256) {
+         const int rr = idx % NBI, c = idx / NBI;
+         Ls[rr][c] = (rr < nb && c < nb && rr > c) ? A[(jb + rr) + static_cast<int64_t>(ld) * (jb + c)] : 0.0;
+      }
+      __syncthreads();
+      if (warp == 0) {
+         double yv = (lane < nb) ? y[jb + lane] : 0.0;
+         for (int c = 0; c < nb; ++c) {
+            const double yc = __shfl_sync(0xffffffffu, yv, c);
+            if (lane > c) yv -= Ls[lane][c] * yc;
+         }
+         if (lane < nb) y[jb + lane] = yv;
+         yp[lane] = (lane < nb) ? yv : 0.0;
+      }
+      __syncthreads();
+      for (int i = jb + nb + tid; i < f; i += 256) {
+         double acc = 0.0;
+         for (int c = 0; c < nb; ++c) acc += A[i + static_cast<int64_t>(ld) * (jb + c)] * yp[c];
+         if (i < k) y[i] -= acc; else cb[i - k] -= acc;
+      }
+      __syncthreads();
+   }
+}
+
+__global__ void __launch_bounds__(256) k_backward(FrontArrays F, const int* __restrict__ list, FactorArrays W, double* __restrict__ z2,
+                                                  double* __restrict__ xg, double* __restrict__ cpool) {
+   __shared__ double Ls[NBI][NBI + 1];
+   __shared__ double red[NBI];
+   const int s = list[blockIdx.x];
+   const int k = F.k[s], f = F.f[s], ld = F.ld[s], first = F.first[s];
+   const int r = f - k;
+   const double* A = W.pool + F.off[s];
+   double* xb = cpool + F.rel_off[s];
+   const int* __restrict__ rows = F.rows + F.rows_off[s];
+   double* y = z2 + first;
+   const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+
+   for (int i = tid; i < r; i += 256) xb[i] = xg[rows[k + i]];
+   for (int j = tid; j < k; j += 256) {
+      const int q = first + j;
+      const int ty = W.ptype[q];
+      if (ty == 0) {
+         y[j] = y[j] / W.dd[q];
+      } else if (ty == 1) {
+         const double a = W.dd[q], b = W.de[q], c = W.dd[q + 1];
+         const double det = a * c - b * b;
+         const double y1 = y[j], y2 = y[j + 1];
+         y[j] = (c * y1 - b * y2) / det;
+         y[j + 1] = (a * y2 - b * y1) / det;
+      } else if (ty == 3) {
+         y[j] = 0.0;
+      }
+   }
+   __syncthreads();
+
+   const int nblocks = (k + NBI - 1) / NBI;
+   for (int bi = nblocks - 1; bi >= 0; --bi) {
+      const int jb = bi * NBI;
+      const int nb = min(NBI, k - jb);
+      // red[c] = sum_{i >= jb+nb} L[i][jb+c] * x(i)
+      for (int c = warp; c < nb; c += 8) {
+         const double* col = A + static_cast<int64_t>(ld) * (jb + c);
+         double acc = 0.0;
+         for (int i = jb + nb + lane; i < f; i += 32) acc += col[i] * ((i < k) ? y[i] : xb[i - k]);
+         for (int o = 16; o; o >>= 1) acc += __shfl_xor_sync(0xffffffffu, acc, o);
+         if (lane == 0) red[c] = acc;
+      }
+      for (int idx = tid; idx < NBI * NBI; idx += 256) {
+         const int rr = idx % NBI, c = idx / NBI;
+         Ls[rr][c] = (rr < nb && c < nb && rr > c) ? A[(jb + rr) + static_cast<int64_t>(ld) * (jb + c)] : 0.0;
+      }
+      __syncthreads();
+      if (warp == 0) {
+         double yv = (lane < nb) ? (y[jb + lane] - red[lane]) : 0.0;
+         for (int c = nb - 1; c >= 0; --c) {
+            const double yc = __shfl_sync(0xffffffffu, yv, c);
+            if (lane < c) yv -= Ls[c][lane] * yc;
+         }
+         if (lane < nb) y[jb + lane] = yv;
+      }
+      __syncthreads();
+   }
+   for (int j = tid; j < k; j += 256) xg[first + W.lperm[first + j]] = y[j];
+}
+
+inline int grid1d(int64_t n, int threads) { return static_cast<int>((n + threads - 1) / threads); }
+
+}  // namespace
+
+// ------------------------------------------------------------------------------------------------
+// launch wrappers
+// ------------------------------------------------------------------------------------------------
+int launch_fill(double* p, int64_t n, double v, cudaStream_t st) {
+   if (n <= 0) return 0;
+   k_fill<<<grid1d(n, 256), 256, 0, st>>>(p, n, v);
+   return 1;
+}
+
+int launch_scale_sweep(const CsrArrays& A, const double* values, const double* sc_in, double* sc_out, cudaStream_t st) {
+   k_scale_sweep<<<grid1d(A.n, 256), 256, 0, st>>>(A, values, sc_in, sc_out);
+   return 1;
+}
+
+int launch_matrix_inf_norm(const CsrArrays& A, const double* values, unsigned long long* out_bits, cudaStream_t st) {
+   k_matrix_inf_norm<<<grid1d(A.n, 256), 256, 0, st>>>(A, values, out_bits);
+   return 1;
+}
+
+int launch_assemble(const AssemblyArrays& M, const double* values, const double* scale, double* pool, cudaStream_t st) {
+   if (M.ndst <= 0) return 0;
+   k_assemble<<<grid1d(M.ndst, 256), 256, 0, st>>>(M, values, scale, pool);
+   return 1;
+}
+
+int launch_extend_add(const FrontArrays& F, const int* d_list, int nfronts, int max_f, double* pool, cudaStream_t st) {
+   if (nfronts <= 0) return 0;
+   dim3 grid(nfronts, (max_f + EA_CBW - 1) / EA_CBW);
+   k_extend_add<<<grid, 256, 0, st>>>(F, d_list, pool);
+   return 1;
+}
+
+int launch_panel(const FrontArrays& F, const int* d_list, int nfronts, int max_f, int j0, int J0, const FactorArrays& W, double null_tol,
+                 cudaStream_t st) {
+   if (nfronts <= 0) return 0;
+   int chunks = (max_f - j0 + PANEL_THREADS - 1) / PANEL_THREADS;
+   if (chunks < 1) chunks = 1;
+   dim3 grid(nfronts, chunks);
+   k_panel<<<grid, PANEL_THREADS, 0, st>>>(F, d_list, j0, J0, W, null_tol);
+   return 1;
+}
+
+int launch_permute_rows(const FrontArrays& F, const int* d_list, int nfronts, int j0, const FactorArrays& W, cudaStream_t st) {
+   if (nfronts <= 0 || j0 <= 0) return 0;
+   dim3 grid(nfronts, (j0 + 255) / 256);
+   k_permute_rows<<<grid, 256, 0, st>>>(F, d_list, j0, W);
+   return 1;
+}
+
+namespace {
+constexpr int smem_bytes(int bm, int bn) { return UPD_STAGES * UPD_BK * (bm + 4 + bn + 4) * static_cast<int>(sizeof(double)); }
+}
+
+int init_kernel_attributes() {
+   cudaError_t e = cudaFuncSetAttribute(k_update<128, 128, 2, 4>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem_bytes(128, 128));
+   if (e != cudaSuccess) return static_cast<int>(e);
+   e = cudaFuncSetAttribute(k_update<64, 64, 2, 2>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem_bytes(64, 64));
+   return static_cast<int>(e);
+}
+
+int launch_update(const FrontArrays& F, const int* d_list, int nfronts, int max_f, int mode, int j0, int J0, const FactorArrays& W,
+                  bool big_tiles, cudaStream_t st) {
+   if (nfronts <= 0) return 0;
+   // region extent upper bounds (per-front extents are resolved inside the kernel)
+   const int r0 = (mode == 0) ? j0 + 1 : J0 + 1;   // smallest possible region start (a front with k = r0)
+   const int rows = max_f - (r0 & ~1);
+   if (rows <= 0) return 0;
+   const int cols = (mode == 0) ? NBO : rows;
+   if (big_tiles) {
+      dim3 grid(nfronts, (rows + 127) / 128, (cols + 127) / 128);
+      k_update<128, 128, 2, 4><<<grid, 256, smem_bytes(128, 128), st>>>(F, d_list, mode, j0, J0, W);
+   } else {
+      dim3 grid(nfronts, (rows + 63) / 64, (cols + 63) / 64);
+      k_update<64, 64, 2, 2><<<grid, 128, smem_bytes(64, 64), st>>>(F, d_list, mode, j0, J0, W);
+   }
+   return 1;
+}
+
+int launch_inertia(int64_t n, const FactorArrays& W, int* counters, cudaStream_t st) {
+   int blocks = grid1d(n, 256);
+   if (blocks > 1184) blocks = 1184;
+   k_inertia<<<blocks, 256, 0, st>>>(n, W, counters);
+   return 1;
+}
+
+int launch_forward_level(const FrontArrays& F, const int* d_list, int nfronts, const FactorArrays& W, double* zg, double* z2, double* cpool,
+                         cudaStream_t st) {
+   if (nfronts <= 0) return 0;
+   k_forward<<<nfronts, 256, 0, st>>>(F, d_list, W, zg, z2, cpool);
+   return 1;
+}
+
+int launch_backward_level(const FrontArrays& F, const int* d_list, int nfronts, const FactorArrays& W, double* z2, double* xg, double* cpool,
+                          cudaStream_t st) {
+   if (nfronts <= 0) return 0;
+   k_backward<<<nfronts, 256, 0, st>>>(F, d_list, W, z2, xg, cpool);
+   return 1;
+}
+
+int launch_solve_gather(int64_t n, const int* perm, const double* scale, const double* r, double* zg, cudaStream_t st) {
+   k_solve_gather<<<grid1d(n, 256), 256, 0, st>>>(n, perm, scale, r, zg);
+   return 1;
+}
+
+int launch_solve_scatter_add(int64_t n, const int* perm, const double* scale, const double* xg, double* x, cudaStream_t st) {
+   k_solve_scatter_add<<<grid1d(n, 256), 256, 0, st>>>(n, perm, scale, xg, x);
+   return 1;
+}
+
+int launch_residual(const CsrArrays& A, const double* values, const double* x, const double* b, double* r, cudaStream_t st) {
+   k_residual<<<grid1d(A.n, 256), 256, 0, st>>>(A, values, x, b, r);
+   return 1;
+}
+
+int launch_absmax(const double* v, int64_t n, unsigned long long* out_bits, cudaStream_t st) {
+   int blocks = grid1d(n, 256);
+   if (blocks > 1184) blocks = 1184;
+   if (blocks < 1) blocks = 1;
+   k_absmax<<<blocks, 256, 0, st>>>(v, n, out_bits);
+   return 1;
+}
+
+}  // namespace b200kkt

@@ -1,0 +1,88 @@
+// Launch wrappers of the sm_100a numeric phase.  Everything here is asynchronous on the stream
+// passed in; no wrapper synchronizes.  Each wrapper returns the number of kernels it launched.
+#pragma once
+#include <cstdint>
+#include <cuda_runtime.h>
+
+namespace b200kkt {
+
+constexpr int NBI = 32;    // inner block: pivot search window of the in-front Bunch-Kaufman
+constexpr int NBO = 256;   // outer panel: K of the trailing FP64 tensor-core update
+
+// device-resident integer plan (SoA over fronts)
+struct FrontArrays {
+   const int64_t* off;        // pool offset
+   const int* k;              // pivots
+   const int* f;              // front order
+   const int* ld;             // leading dimension
+   const int* first;          // first pivot column (new numbering)
+   const int64_t* rows_off;
+   const int* rows;
+   const int64_t* rel_off;
+   const int* relmap;
+   const int* child_ptr;
+   const int* child_idx;
+   const int64_t* woff;       // offset of the front's ld x NBO W panel in wpool
+};
+
+struct AssemblyArrays {
+   int64_t ndst;
+   const int64_t* dst;
+   const int* seg;
+   const int* src;
+   const int* row;
+   const int* col;
+};
+
+struct CsrArrays {
+   int64_t n;
+   const int* ptr;
+   const int* col;
+   const int* slot;
+};
+
+struct FactorArrays {
+   double* pool;
+   double* wpool;
+   double* dd;       // D diagonal, per pivot position (new numbering + in-front pivoting)
+   double* de;       // D off-diagonal of 2x2 blocks (stored at the first column of the pair)
+   int* ptype;       // 0: 1x1, 1/2: first/second column of a 2x2, 3: null pivot (row/column dropped)
+   int* lperm;       // pivot position q = first+j holds original local column lperm[q] (0..k)
+   int* blkflag;     // per inner block (indexed by its first pivot position): non-identity permutation
+};
+
+// K1' equilibration sweep (power-of-two Ruiz step) and K-infinity norm
+int launch_scale_sweep(const CsrArrays& A, const double* values, const double* sc_in, double* sc_out, cudaStream_t st);
+int launch_fill(double* p, int64_t n, double v, cudaStream_t st);
+int launch_matrix_inf_norm(const CsrArrays& A, const double* values, unsigned long long* out_bits, cudaStream_t st);
+// K1 assembly: scatter COO values (scaled) into the zeroed front pool, duplicates summed in slot order
+int launch_assemble(const AssemblyArrays& M, const double* values, const double* scale, double* pool, cudaStream_t st);
+
+// K5 extend-add of all children into the fronts of one level
+int launch_extend_add(const FrontArrays& F, const int* d_list, int nfronts, int max_f, double* pool, cudaStream_t st);
+// K3 panel: Bunch-Kaufman on the NBI x NBI diagonal block at pivot column j0 + triangular solve of
+// the rows below it; writes L in place and W = L*D into the W panel
+int launch_panel(const FrontArrays& F, const int* d_list, int nfronts, int max_f, int j0, int J0, const FactorArrays& W,
+                 double null_tol, cudaStream_t st);
+int launch_permute_rows(const FrontArrays& F, const int* d_list, int nfronts, int j0, const FactorArrays& W, cudaStream_t st);
+// K4 Schur-complement update C -= W * L^T with FP64 tensor-core MMA.
+// mode 0: inside the outer panel (after inner block j0); mode 1: trailing matrix after outer panel J0.
+int launch_update(const FrontArrays& F, const int* d_list, int nfronts, int max_f, int mode, int j0, int J0,
+                  const FactorArrays& W, bool big_tiles, cudaStream_t st);
+int init_kernel_attributes();
+// K6 inertia from the D blocks: counters[0..4] = positive, negative, zero, number of 2x2, unused
+int launch_inertia(int64_t n, const FactorArrays& W, int* counters, cudaStream_t st);
+
+// K7 solves: one level at a time
+int launch_forward_level(const FrontArrays& F, const int* d_list, int nfronts, const FactorArrays& W, double* zg, double* z2,
+                         double* cpool, cudaStream_t st);
+int launch_backward_level(const FrontArrays& F, const int* d_list, int nfronts, const FactorArrays& W, double* z2, double* xg,
+                          double* cpool, cudaStream_t st);
+// permute+scale in, scale+permute out (accumulating into x)
+int launch_solve_gather(int64_t n, const int* perm, const double* scale, const double* r, double* zg, cudaStream_t st);
+int launch_solve_scatter_add(int64_t n, const int* perm, const double* scale, const double* xg, double* x, cudaStream_t st);
+// K8 residual r = b - K x on the COO-order values, and infinity norms as ordered bit patterns
+int launch_residual(const CsrArrays& A, const double* values, const double* x, const double* b, double* r, cudaStream_t st);
+int launch_absmax(const double* v, int64_t n, unsigned long long* out_bits, cudaStream_t st);
+
+}  // namespace b200kkt

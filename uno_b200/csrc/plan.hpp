@@ -1,0 +1,80 @@
+// Integer plan produced by the host symbolic phase and consumed by the CUDA numeric phase.
+//
+// Replaces what MUMPS builds internally at JOB=1 (reference call site:
+// uno/ingredients/subproblem_solvers/MUMPS/MUMPSSolver.cpp:72-83).  The plan is immutable once
+// built; the numeric phase never changes front sizes (pivoting is confined to the fully-summed
+// block of each front).
+#pragma once
+#include <cstdint>
+#include <string>
+#include <vector>
+
+namespace b200kkt {
+
+struct AnalyseOptions {
+   int ordering = 0;          // 0 = METIS nested dissection on the KKT-compressed graph, 1 = natural, 2 = user permutation
+   int kkt_pairing = 1;       // match each constraint row with a primal column (2x2 pivot candidates)
+   int relax_small = 16;      // always merge a child when the merged pivot count is <= this
+   int relax_mid = 64;        // merged pivot count <= this: accept up to relax_mid_zeros explicit zeros
+   double relax_mid_zeros = 0.5;
+   int relax_big = 256;
+   double relax_big_zeros = 0.15;
+   double relax_any_zeros = 0.03;
+   const int64_t* user_perm = nullptr;   // ordering == 2: perm[new] = old, length N
+};
+
+struct Plan {
+   int64_t N = 0, nnz = 0, reg_size = 0, num_primal = 0;
+   int32_t nsn = 0;        // number of supernodes == number of fronts
+   int32_t nlevels = 0;
+
+   // perm[new] = old, iperm[old] = new.  "new" is the final elimination numbering in which every
+   // supernode is a contiguous column range.
+   std::vector<int32_t> perm, iperm;
+   std::vector<int32_t> sn_first;   // nsn+1
+   std::vector<int32_t> sn_of;      // N, by new index
+
+   // per front
+   std::vector<int32_t> k, f, ld;   // pivots, front order, leading dimension (f rounded up to 4)
+   std::vector<int64_t> front_off;  // offset of the ld x f column-major front in the pool (doubles)
+   std::vector<int64_t> rows_off;   // nsn+1, into rows
+   std::vector<int32_t> rows;       // front row structure in new numbering; first k entries are the pivots
+   std::vector<int32_t> parent;     // supernodal parent (-1 for roots)
+   std::vector<int64_t> rel_off;    // nsn+1, into relmap (r = f - k entries per front)
+   std::vector<int32_t> relmap;     // boundary row i of front s -> local index in parent(s)
+   std::vector<int32_t> child_ptr, child_idx;     // children CSR, ascending child index
+   std::vector<int32_t> level;                    // per front; leaves are 0
+   std::vector<int32_t> level_ptr, level_fronts;  // fronts grouped by level, big fronts first
+
+   int64_t pool_size = 0;           // doubles
+
+   // Assembly ("assembly permutation"): COO slot -> pool offset, and the same map grouped by
+   // destination so that duplicates are summed in ascending slot order without atomics.
+   std::vector<int64_t> scatter;    // nnz
+   std::vector<int64_t> asm_dst;    // ndst
+   std::vector<int32_t> asm_seg;    // ndst+1
+   std::vector<int32_t> asm_src;    // nnz, slots grouped by destination
+   std::vector<int32_t> asm_row, asm_col;   // nnz, ORIGINAL indices of asm_src entries (for scaling)
+
+   // Full symmetric CSR of the COO in ORIGINAL numbering, duplicates kept, entries in ascending
+   // slot order inside a row.  Used for the residual SpMV and for equilibration.
+   std::vector<int32_t> csr_ptr;    // N+1
+   std::vector<int32_t> csr_col;    // 2*nnz - ndiag
+   std::vector<int32_t> csr_slot;
+
+   // exact work figures
+   int64_t nnz_L = 0;               // sum k*f - k(k-1)/2
+   double flops = 0.0;              // sum k^3/3 + k^2 r + k r^2
+   double flops_tc = 0.0;           // k^2 r + k r^2 over fronts with k >= 128
+   int64_t sum_r = 0;
+   int32_t max_f = 0, max_k = 0;
+   int64_t num_pairs = 0;
+   double t_order = 0, t_symbolic = 0, t_maps = 0;
+   std::string ordering_used;
+};
+
+// Throws std::runtime_error on malformed input (index out of range, lower-triangular entry).
+void analyse(int64_t N, int64_t nnz, int64_t reg_size, int64_t num_primal,
+             const uint64_t* row, const uint64_t* col, const AnalyseOptions& opt, Plan& plan);
+
+}  // namespace b200kkt

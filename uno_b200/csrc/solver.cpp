@@ -1,0 +1,663 @@
+// Host orchestration of the B200 KKT solver and its C ABI (include/b200kkt.h).
+//
+// Mirrors the call sequence of the reference's MUMPSSolver
+// (uno/ingredients/subproblem_solvers/MUMPS/MUMPSSolver.cpp): create <-> JOB=-1 (:16-44),
+// analyse <-> JOB=1 (:72-83), factorize <-> JOB=2 (:85-89), solve <-> JOB=3 (:91-96),
+// inertia <-> INFOG(12)/INFOG(28) (:124-147), destroy <-> JOB=-2 (:46-49).
+// There is no CPU numeric path: a handle without a CUDA device can only run the symbolic phase.
+#include "solver.hpp"
+
+#include <algorithm>
+#include <chrono>
+#include <cmath>
+#include <cstring>
+#include <exception>
+#include <new>
+#include <stdexcept>
+
+using namespace b200kkt;
+
+namespace b200kkt {
+int Batch::count_k_greater(int j) const {
+   // k is sorted descending: first index with k <= j
+   int lo = 0, hi = static_cast<int>(k.size());
+   while (lo < hi) {
+      const int mid = (lo + hi) >> 1;
+      if (k[mid] > j) lo = mid + 1; else hi = mid;
+   }
+   return lo;
+}
+}  // namespace b200kkt
+
+namespace {
+
+struct CudaError {
+   cudaError_t code;
+   const char* what;
+};
+
+#define CK(expr)                                                     \
+   do {                                                              \
+      const cudaError_t e__ = (expr);                                \
+      if (e__ != cudaSuccess) throw CudaError{e__, #expr};           \
+   } while (0)
+
+int fail(const b200kkt_handle* h, int code, const std::string& msg) {
+   if (h != nullptr) h->err = msg;
+   return code;
+}
+
+template <typename T>
+T* dev_upload(b200kkt_handle* h, const std::vector<T>& v, size_t min_count = 1) {
+   T* p = nullptr;
+   const size_t count = std::max(v.size(), min_count);
+   CK(cudaMalloc(reinterpret_cast<void**>(&p), count * sizeof(T)));
+   h->plan_allocs.push_back(p);
+   if (!v.empty()) CK(cudaMemcpyAsync(p, v.data(), v.size() * sizeof(T), cudaMemcpyHostToDevice, h->stream));
+   return p;
+}
+
+template <typename T>
+T* dev_alloc(b200kkt_handle* h, size_t count) {
+   T* p = nullptr;
+   CK(cudaMalloc(reinterpret_cast<void**>(&p), std::max<size_t>(count, 1) * sizeof(T)));
+   h->plan_allocs.push_back(p);
+   return p;
+}
+
+void free_plan_device(b200kkt_handle* h) {
+   if (h->factor_graph != nullptr) { cudaGraphExecDestroy(h->factor_graph); h->factor_graph = nullptr; }
+   for (void* p : h->plan_allocs) cudaFree(p);
+   h->plan_allocs.clear();
+   h->analysed = false;
+   h->values_resident = false;
+   h->factorized = false;
+}
+
+int size_class(int f) {
+   int c = 0;
+   int bound = 64;
+   while (f > bound) { bound *= 2; ++c; }
+   return c;
+}
+
+// group the fronts of every level into batches of similar order, pivot count descending
+void build_batches(b200kkt_handle* h, std::vector<int>& batch_list, std::vector<int64_t>& woff, int64_t& wpool_size) {
+   const Plan& P = h->plan;
+   h->batches.clear();
+   h->level_batch_ptr.assign(1, 0);
+   batch_list.clear();
+   woff.assign(static_cast<size_t>(P.nsn), 0);
+   wpool_size = 0;
+   std::vector<int> ids;
+   for (int l = 0; l < P.nlevels; ++l) {
+      ids.assign(P.level_fronts.begin() + P.level_ptr[l], P.level_fronts.begin() + P.level_ptr[l + 1]);
+      std::stable_sort(ids.begin(), ids.end(), [&](int a, int b) {
+         const int ca = size_class(P.f[a]), cb = size_class(P.f[b]);
+         if (ca != cb) return ca > cb;
+         if (P.k[a] != P.k[b]) return P.k[a] > P.k[b];
+         return P.f[a] > P.f[b];
+      });
+      int64_t level_w = 0;
+      size_t i = 0;
+      while (i < ids.size()) {
+         Batch b;
+         b.level = l;
+         b.begin = static_cast<int>(batch_list.size());
+         const int cls = size_class(P.f[ids[i]]);
+         while (i < ids.size() && size_class(P.f[ids[i]]) == cls) {
+            const int s = ids[i];
+            batch_list.push_back(s);
+            b.k.push_back(P.k[s]);
+            b.max_f = std::max(b.max_f, P.f[s]);
+            b.pmaxf.push_back(b.max_f);
+            b.max_k = std::max(b.max_k, P.k[s]);
+            if (P.child_ptr[s + 1] > P.child_ptr[s]) b.has_children = true;
+            woff[s] = level_w;
+            level_w += static_cast<int64_t>(P.ld[s]) * std::min(NBO, (P.k[s] + 3) & ~3);
+            ++i;
+         }
+         b.count = static_cast<int>(b.k.size());
+         b.big_tiles = b.max_f > 256;
+         h->batches.push_back(std::move(b));
+      }
+      wpool_size = std::max(wpool_size, level_w);
+      h->level_batch_ptr.push_back(static_cast<int>(h->batches.size()));
+   }
+}
+
+void upload_plan(b200kkt_handle* h) {
+   const Plan& P = h->plan;
+   const auto t0 = std::chrono::steady_clock::now();
+   std::vector<int> batch_list;
+   std::vector<int64_t> woff;
+   int64_t wpool_size = 0;
+   build_batches(h, batch_list, woff, wpool_size);
+
+   h->F.off = dev_upload(h, P.front_off);
+   h->F.k = dev_upload(h, P.k);
+   h->F.f = dev_upload(h, P.f);
+   h->F.ld = dev_upload(h, P.ld);
+   {
+      std::vector<int32_t> first(P.sn_first.begin(), P.sn_first.end() - 1);
+      h->F.first = dev_upload(h, first);
+   }
+   h->F.rows_off = dev_upload(h, P.rows_off);
+   h->F.rows = dev_upload(h, P.rows);
+   h->F.rel_off = dev_upload(h, P.rel_off);
+   h->F.relmap = dev_upload(h, P.relmap);
+   h->F.child_ptr = dev_upload(h, P.child_ptr);
+   h->F.child_idx = dev_upload(h, P.child_idx);
+   h->F.woff = dev_upload(h, woff);
+   h->d_perm = dev_upload(h, P.perm);
+   h->d_batch_list = dev_upload(h, batch_list);
+   h->d_solve_list = dev_upload(h, P.level_fronts);
+   h->solve_level_ptr.assign(P.level_ptr.begin(), P.level_ptr.end());
+
+   h->M.ndst = static_cast<int64_t>(P.asm_dst.size());
+   h->M.dst = dev_upload(h, P.asm_dst);
+   h->M.seg = dev_upload(h, P.asm_seg);
+   h->M.src = dev_upload(h, P.asm_src);
+   h->M.row = dev_upload(h, P.asm_row);
+   h->M.col = dev_upload(h, P.asm_col);
+   h->C.n = P.N;
+   h->C.ptr = dev_upload(h, P.csr_ptr);
+   h->C.col = dev_upload(h, P.csr_col);
+   h->C.slot = dev_upload(h, P.csr_slot);
+
+   const size_t n = static_cast<size_t>(P.N);
+   h->W.pool = dev_alloc<double>(h, static_cast<size_t>(P.pool_size));
+   h->W.wpool = dev_alloc<double>(h, static_cast<size_t>(wpool_size));
+   h->W.dd = dev_alloc<double>(h, n + 1);
+   h->W.de = dev_alloc<double>(h, n + 1);
+   h->W.ptype = dev_alloc<int>(h, n + 1);
+   h->W.lperm = dev_alloc<int>(h, n + 1);
+   h->W.blkflag = dev_alloc<int>(h, n + 1);
+   h->d_values = dev_alloc<double>(h, static_cast<size_t>(P.nnz));
+   h->d_scale = dev_alloc<double>(h, n);
+   h->d_scale_tmp = dev_alloc<double>(h, n);
+   h->d_zg = dev_alloc<double>(h, n);
+   h->d_z2 = dev_alloc<double>(h, n);
+   h->d_xg = dev_alloc<double>(h, n);
+   h->d_cpool = dev_alloc<double>(h, static_cast<size_t>(P.sum_r));
+   h->d_b = dev_alloc<double>(h, n);
+   h->d_x = dev_alloc<double>(h, n);
+   h->d_r = dev_alloc<double>(h, n);
+   h->d_counters = dev_alloc<int>(h, 8);
+   h->d_norms = dev_alloc<unsigned long long>(h, 4);
+   h->d_scale_final = h->d_scale;
+   CK(cudaMemsetAsync(h->W.wpool, 0, static_cast<size_t>(std::max<int64_t>(wpool_size, 1)) * sizeof(double), h->stream));
+   CK(cudaStreamSynchronize(h->stream));
+   h->stats.t_upload = std::chrono::duration<double>(std::chrono::steady_clock::now() - t0).count();
+}
+
+void fill_plan_stats(b200kkt_handle* h) {
+   const Plan& P = h->plan;
+   b200kkt_stats& s = h->stats;
+   const int64_t keep_launches = s.kernel_launches;
+   s = b200kkt_stats{};
+   s.kernel_launches = keep_launches;
+   s.n = P.N; s.nnz = P.nnz; s.reg_size = P.reg_size;
+   s.num_fronts = P.nsn; s.num_levels = P.nlevels; s.max_front = P.max_f; s.max_pivots = P.max_k;
+   s.num_pairs = P.num_pairs;
+   s.nnz_factor = P.nnz_L; s.pool_doubles = P.pool_size;
+   s.assembly_distinct = static_cast<int64_t>(P.asm_dst.size());
+   s.flops_factor = P.flops; s.flops_tensor = P.flops_tc;
+   s.t_ordering = P.t_order; s.t_symbolic = P.t_symbolic; s.t_maps = P.t_maps;
+}
+
+// ---- numeric factorization: enqueue everything on the handle's stream -------------------------
+void enqueue_factor(b200kkt_handle* h) {
+   const Plan& P = h->plan;
+   cudaStream_t st = h->stream;
+   int64_t& L = h->launches;
+   // K1' equilibration
+   L += launch_fill(h->d_scale, P.N, 1.0, st);
+   double* cur = h->d_scale;
+   double* nxt = h->d_scale_tmp;
+   for (int sw = 0; sw < h->scaling_sweeps; ++sw) {
+      L += launch_scale_sweep(h->C, h->d_values, cur, nxt, st);
+      std::swap(cur, nxt);
+   }
+   h->d_scale_final = cur;
+   CK(cudaMemsetAsync(h->d_norms, 0, 4 * sizeof(unsigned long long), st));
+   L += launch_matrix_inf_norm(h->C, h->d_values, h->d_norms + 0, st);
+   // K1 assembly into the zeroed pool
+   CK(cudaMemsetAsync(h->W.pool, 0, static_cast<size_t>(P.pool_size) * sizeof(double), st));
+   L += launch_assemble(h->M, h->d_values, cur, h->W.pool, st);
+   // K2-K5 level by level
+   for (int l = 0; l < P.nlevels; ++l) {
+      for (int bi = h->level_batch_ptr[l]; bi < h->level_batch_ptr[l + 1]; ++bi) {
+         const Batch& b = h->batches[bi];
+         const int* list = h->d_batch_list + b.begin;
+         if (b.has_children) L += launch_extend_add(h->F, list, b.count, b.max_f, h->W.pool, st);
+         for (int J0 = 0; J0 < b.max_k; J0 += NBO) {
+            const int nfP = b.count_k_greater(J0);
+            const int Jend = std::min(J0 + NBO, b.max_k);
+            for (int j0 = J0; j0 < Jend; j0 += NBI) {
+               const int nfb = b.count_k_greater(j0);
+               const int maxf_b = b.pmaxf[nfb - 1];
+               L += launch_panel(h->F, list, nfb, maxf_b, j0, J0, h->W, h->null_pivot_tol, st);
+               if (j0 > 0) L += launch_permute_rows(h->F, list, nfb, j0, h->W, st);
+               // in-panel update only where pivot columns remain right of this block inside the panel
+               const int nfu = b.count_k_greater(j0 + NBI);
+               if (nfu > 0 && j0 + NBI < J0 + NBO) L += launch_update(h->F, list, nfu, b.pmaxf[nfu - 1], 0, j0, J0, h->W, b.big_tiles, st);
+            }
+            L += launch_update(h->F, list, nfP, b.pmaxf[nfP - 1], 1, 0, J0, h->W, b.big_tiles, st);
+         }
+      }
+   }
+   // K6 inertia
+   CK(cudaMemsetAsync(h->d_counters, 0, 8 * sizeof(int), st));
+   L += launch_inertia(P.N, h->W, h->d_counters, st);
+   CK(cudaMemcpyAsync(h->h_counters, h->d_counters, 8 * sizeof(int), cudaMemcpyDeviceToHost, st));
+}
+
+}  // namespace
+
+namespace {
+
+double bits_to_double(unsigned long long b) {
+   double d;
+   std::memcpy(&d, &b, sizeof(d));
+   return d;
+}
+
+// run the numeric factorization on values already resident in h->d_values
+void run_factor(b200kkt_handle* h) {
+   cudaStream_t st = h->stream;
+   CK(cudaEventRecord(h->ev0, st));
+   if (h->use_graph) {
+      if (h->factor_graph == nullptr) {
+         const int64_t before = h->launches;
+         cudaGraph_t graph = nullptr;
+         CK(cudaStreamBeginCapture(st, cudaStreamCaptureModeThreadLocal));
+         try {
+            enqueue_factor(h);
+         } catch (...) {
+            cudaStreamEndCapture(st, &graph);
+            if (graph != nullptr) cudaGraphDestroy(graph);
+            throw;
+         }
+         CK(cudaStreamEndCapture(st, &graph));
+         const cudaError_t e = cudaGraphInstantiate(&h->factor_graph, graph, 0);
+         cudaGraphDestroy(graph);
+         if (e != cudaSuccess) throw CudaError{e, "cudaGraphInstantiate"};
+         h->graph_launches = h->launches - before;
+         h->launches = before;
+      }
+      CK(cudaGraphLaunch(h->factor_graph, st));
+      h->launches += h->graph_launches;
+   } else {
+      enqueue_factor(h);
+   }
+   CK(cudaEventRecord(h->ev1, st));
+   CK(cudaStreamSynchronize(st));
+   CK(cudaGetLastError());
+   float ms = 0.f;
+   CK(cudaEventElapsedTime(&ms, h->ev0, h->ev1));
+   h->stats.t_factor_last = ms * 1e-3;
+   h->inertia[0] = static_cast<uint64_t>(h->h_counters[0]);
+   h->inertia[1] = static_cast<uint64_t>(h->h_counters[1]);
+   h->inertia[2] = static_cast<uint64_t>(h->h_counters[2]);
+   h->factorized = true;
+}
+
+}  // namespace
+
+namespace {
+
+// x = K^{-1} b with iterative refinement; b and x are device pointers (x may alias nothing else)
+void run_solve(b200kkt_handle* h, const double* d_b, double* d_x, double* backward_error) {
+   const Plan& P = h->plan;
+   cudaStream_t st = h->stream;
+   int64_t& L = h->launches;
+   const size_t nbytes = static_cast<size_t>(P.N) * sizeof(double);
+   CK(cudaEventRecord(h->ev0, st));
+   CK(cudaMemsetAsync(d_x, 0, nbytes, st));
+   CK(cudaMemcpyAsync(h->d_r, d_b, nbytes, cudaMemcpyDeviceToDevice, st));
+   CK(cudaMemsetAsync(h->d_norms + 1, 0, 3 * sizeof(unsigned long long), st));
+   L += launch_absmax(d_b, P.N, h->d_norms + 3, st);
+   double berr = 0.0, prev = 0.0;
+   int steps = 0;
+   for (int it = 0; it <= h->refine_max_steps; ++it) {
+      L += launch_solve_gather(P.N, h->d_perm, h->d_scale_final, h->d_r, h->d_zg, st);
+      for (int l = 0; l < P.nlevels; ++l) {
+         const int n = h->solve_level_ptr[l + 1] - h->solve_level_ptr[l];
+         L += launch_forward_level(h->F, h->d_solve_list + h->solve_level_ptr[l], n, h->W, h->d_zg, h->d_z2, h->d_cpool, st);
+      }
+      for (int l = P.nlevels - 1; l >= 0; --l) {
+         const int n = h->solve_level_ptr[l + 1] - h->solve_level_ptr[l];
+         L += launch_backward_level(h->F, h->d_solve_list + h->solve_level_ptr[l], n, h->W, h->d_z2, h->d_xg, h->d_cpool, st);
+      }
+      L += launch_solve_scatter_add(P.N, h->d_perm, h->d_scale_final, h->d_xg, d_x, st);
+      // K8 residual and backward error
+      L += launch_residual(h->C, h->d_values, d_x, d_b, h->d_r, st);
+      CK(cudaMemsetAsync(h->d_norms + 1, 0, 2 * sizeof(unsigned long long), st));
+      L += launch_absmax(h->d_r, P.N, h->d_norms + 1, st);
+      L += launch_absmax(d_x, P.N, h->d_norms + 2, st);
+      CK(cudaMemcpyAsync(h->h_norms, h->d_norms, 4 * sizeof(unsigned long long), cudaMemcpyDeviceToHost, st));
+      CK(cudaStreamSynchronize(st));
+      const double knorm = bits_to_double(h->h_norms[0]), rnorm = bits_to_double(h->h_norms[1]);
+      const double xnorm = bits_to_double(h->h_norms[2]), bnorm = bits_to_double(h->h_norms[3]);
+      const double denom = knorm * xnorm + bnorm;
+      berr = (denom > 0.0) ? rnorm / denom : 0.0;
+      steps = it;
+      if (!(berr > h->refine_tol)) break;                  // converged (also leaves on berr == 0)
+      if (!std::isfinite(berr)) break;
+      if (it > 0 && berr > 0.5 * prev) break;              // stagnation
+      prev = berr;
+   }
+   CK(cudaEventRecord(h->ev1, st));
+   CK(cudaStreamSynchronize(st));
+   CK(cudaGetLastError());
+   float ms = 0.f;
+   CK(cudaEventElapsedTime(&ms, h->ev0, h->ev1));
+   h->stats.t_solve_last = ms * 1e-3;
+   h->stats.refine_steps_last = steps;
+   h->stats.backward_error_last = berr;
+   if (backward_error != nullptr) *backward_error = berr;
+}
+
+template <typename Fn>
+int guarded(b200kkt_handle* h, Fn&& fn) {
+   try {
+      fn();
+      return B200KKT_OK;
+   } catch (const CudaError& e) {
+      // a failed capture leaves the stream capturing: make sure it is terminated
+      cudaStreamCaptureStatus cs = cudaStreamCaptureStatusNone;
+      if (h->stream != nullptr && cudaStreamIsCapturing(h->stream, &cs) == cudaSuccess && cs != cudaStreamCaptureStatusNone) {
+         cudaGraph_t g = nullptr;
+         cudaStreamEndCapture(h->stream, &g);
+         if (g != nullptr) cudaGraphDestroy(g);
+      }
+      cudaGetLastError();
+      const bool oom = e.code == cudaErrorMemoryAllocation;
+      return fail(h, oom ? B200KKT_ENOMEM : B200KKT_ECUDA, std::string("CUDA error: ") + cudaGetErrorString(e.code) + " in " + e.what);
+   } catch (const std::bad_alloc&) {
+      return fail(h, B200KKT_ENOMEM, "host allocation failed");
+   } catch (const std::exception& e) {
+      return fail(h, B200KKT_EINTERNAL, e.what());
+   }
+}
+
+int need_device(const b200kkt_handle* h) {
+   if (h == nullptr) return B200KKT_EINVAL;
+   if (!h->has_device) return fail(h, B200KKT_ECUDA, "handle has no CUDA device: the numeric phase has no CPU path");
+   return B200KKT_OK;
+}
+
+}  // namespace
+
+// ================================================================================================
+// C ABI
+// ================================================================================================
+extern "C" {
+
+int b200kkt_create(b200kkt_handle** out, int device, int num_gpus) {
+   if (out == nullptr) return B200KKT_EINVAL;
+   *out = nullptr;
+   b200kkt_handle* h = new (std::nothrow) b200kkt_handle();
+   if (h == nullptr) return B200KKT_ENOMEM;
+   h->device = device;
+   h->num_gpus = num_gpus < 1 ? 1 : num_gpus;
+   h->refine_tol = 1e-13;
+   if (device >= 0) {
+      const int rc = guarded(h, [&] {
+         CK(cudaSetDevice(device));
+         CK(cudaStreamCreateWithFlags(&h->stream, cudaStreamNonBlocking));
+         CK(cudaEventCreate(&h->ev0));
+         CK(cudaEventCreate(&h->ev1));
+         CK(cudaMallocHost(reinterpret_cast<void**>(&h->h_counters), 8 * sizeof(int)));
+         CK(cudaMallocHost(reinterpret_cast<void**>(&h->h_norms), 4 * sizeof(unsigned long long)));
+         const int e = init_kernel_attributes();
+         if (e != 0) throw CudaError{static_cast<cudaError_t>(e), "cudaFuncSetAttribute(k_update)"};
+         h->has_device = true;
+      });
+      if (rc != B200KKT_OK) {
+         // keep the handle so that the caller can read last_error, but it stays host-only
+         h->has_device = false;
+         *out = h;
+         return rc;
+      }
+   }
+   *out = h;
+   return B200KKT_OK;
+}
+
+int b200kkt_destroy(b200kkt_handle* h) {
+   if (h == nullptr) return B200KKT_EINVAL;
+   if (h->has_device) {
+      cudaSetDevice(h->device);
+      if (h->stream != nullptr) cudaStreamSynchronize(h->stream);
+      free_plan_device(h);
+      if (h->h_counters != nullptr) cudaFreeHost(h->h_counters);
+      if (h->h_norms != nullptr) cudaFreeHost(h->h_norms);
+      if (h->ev0 != nullptr) cudaEventDestroy(h->ev0);
+      if (h->ev1 != nullptr) cudaEventDestroy(h->ev1);
+      if (h->stream != nullptr) cudaStreamDestroy(h->stream);
+   }
+   delete h;
+   return B200KKT_OK;
+}
+
+int b200kkt_set_option(b200kkt_handle* h, const char* name, double value) {
+   if (h == nullptr || name == nullptr) return B200KKT_EINVAL;
+   const std::string n(name);
+   if (n == "ordering") h->aopt.ordering = static_cast<int>(value);
+   else if (n == "kkt_pairing") h->aopt.kkt_pairing = static_cast<int>(value);
+   else if (n == "relax_small") h->aopt.relax_small = static_cast<int>(value);
+   else if (n == "relax_mid") h->aopt.relax_mid = static_cast<int>(value);
+   else if (n == "relax_big") h->aopt.relax_big = static_cast<int>(value);
+   else if (n == "relax_mid_zeros") h->aopt.relax_mid_zeros = value;
+   else if (n == "relax_big_zeros") h->aopt.relax_big_zeros = value;
+   else if (n == "relax_any_zeros") h->aopt.relax_any_zeros = value;
+   else if (n == "scaling_sweeps") h->scaling_sweeps = std::max(0, static_cast<int>(value));
+   else if (n == "null_pivot_tol") h->null_pivot_tol = value;
+   else if (n == "refine_max_steps") h->refine_max_steps = std::max(0, static_cast<int>(value));
+   else if (n == "refine_tol") h->refine_tol = value;
+   else if (n == "use_graph") h->use_graph = static_cast<int>(value);
+   else return fail(h, B200KKT_EINVAL, "unknown option: " + n);
+   // numeric options are baked into the captured graph
+   if (h->factor_graph != nullptr) { cudaGraphExecDestroy(h->factor_graph); h->factor_graph = nullptr; }
+   return B200KKT_OK;
+}
+
+int b200kkt_set_user_permutation(b200kkt_handle* h, const int64_t* perm, uint64_t n) {
+   if (h == nullptr) return B200KKT_EINVAL;
+   if (perm == nullptr) { h->user_perm.clear(); if (h->aopt.ordering == 2) h->aopt.ordering = 0; return B200KKT_OK; }
+   h->user_perm.assign(perm, perm + n);
+   h->aopt.ordering = 2;
+   return B200KKT_OK;
+}
+
+int b200kkt_analyse(b200kkt_handle* h, uint64_t n, uint64_t nnz, uint64_t reg_size, uint64_t num_primal, const uint64_t* row,
+                    const uint64_t* col) {
+   if (h == nullptr || (nnz > 0 && (row == nullptr || col == nullptr))) return B200KKT_EINVAL;
+   if (h->has_device) { cudaSetDevice(h->device); free_plan_device(h); }
+   h->analysed = false;
+   const int rc = guarded(h, [&] {
+      AnalyseOptions opt = h->aopt;
+      if (opt.ordering == 2) {
+         if (h->user_perm.size() != n) throw std::runtime_error("analyse: user permutation length differs from N");
+         opt.user_perm = h->user_perm.data();
+      }
+      analyse(static_cast<int64_t>(n), static_cast<int64_t>(nnz), static_cast<int64_t>(reg_size), static_cast<int64_t>(num_primal), row, col,
+              opt, h->plan);
+      fill_plan_stats(h);
+      if (h->has_device) upload_plan(h);
+      h->analysed = true;
+   });
+   if (rc != B200KKT_OK && h->has_device) free_plan_device(h);
+   return rc;
+}
+
+int b200kkt_factorize(b200kkt_handle* h, const double* values) {
+   if (int rc = need_device(h)) return rc;
+   if (!h->analysed) return fail(h, B200KKT_EINVAL, "factorize before analyse");
+   if (values == nullptr) return B200KKT_EINVAL;
+   return guarded(h, [&] {
+      CK(cudaSetDevice(h->device));
+      CK(cudaMemcpyAsync(h->d_values, values, static_cast<size_t>(h->plan.nnz) * sizeof(double), cudaMemcpyHostToDevice, h->stream));
+      h->values_resident = true;
+      run_factor(h);
+   });
+}
+
+int b200kkt_refactorize_shifted(b200kkt_handle* h, const double* reg_values) {
+   if (int rc = need_device(h)) return rc;
+   if (!h->analysed || !h->values_resident) return fail(h, B200KKT_EINVAL, "refactorize_shifted before factorize");
+   if (reg_values == nullptr && h->plan.reg_size > 0) return B200KKT_EINVAL;
+   return guarded(h, [&] {
+      CK(cudaSetDevice(h->device));
+      if (h->plan.reg_size > 0)
+         CK(cudaMemcpyAsync(h->d_values, reg_values, static_cast<size_t>(h->plan.reg_size) * sizeof(double), cudaMemcpyHostToDevice, h->stream));
+      run_factor(h);
+   });
+}
+
+int b200kkt_factorize_device(b200kkt_handle* h, const double* d_values) {
+   if (int rc = need_device(h)) return rc;
+   if (!h->analysed) return fail(h, B200KKT_EINVAL, "factorize before analyse");
+   if (d_values == nullptr) return B200KKT_EINVAL;
+   return guarded(h, [&] {
+      CK(cudaSetDevice(h->device));
+      if (d_values != h->d_values)
+         CK(cudaMemcpyAsync(h->d_values, d_values, static_cast<size_t>(h->plan.nnz) * sizeof(double), cudaMemcpyDeviceToDevice, h->stream));
+      h->values_resident = true;
+      run_factor(h);
+   });
+}
+
+int b200kkt_inertia(const b200kkt_handle* h, uint64_t* n_pos, uint64_t* n_neg, uint64_t* n_zero) {
+   if (h == nullptr) return B200KKT_EINVAL;
+   if (!h->factorized) return fail(h, B200KKT_EINVAL, "inertia before factorize");
+   if (n_pos != nullptr) *n_pos = h->inertia[0];
+   if (n_neg != nullptr) *n_neg = h->inertia[1];
+   if (n_zero != nullptr) *n_zero = h->inertia[2];
+   return B200KKT_OK;
+}
+
+int b200kkt_solve(b200kkt_handle* h, const double* rhs, double* x, double* backward_error) {
+   if (int rc = need_device(h)) return rc;
+   if (!h->factorized) return fail(h, B200KKT_EINVAL, "solve before factorize");
+   if (rhs == nullptr || x == nullptr) return B200KKT_EINVAL;
+   return guarded(h, [&] {
+      CK(cudaSetDevice(h->device));
+      const size_t nbytes = static_cast<size_t>(h->plan.N) * sizeof(double);
+      CK(cudaMemcpyAsync(h->d_b, rhs, nbytes, cudaMemcpyHostToDevice, h->stream));
+      run_solve(h, h->d_b, h->d_x, backward_error);
+      CK(cudaMemcpyAsync(x, h->d_x, nbytes, cudaMemcpyDeviceToHost, h->stream));
+      CK(cudaStreamSynchronize(h->stream));
+   });
+}
+
+int b200kkt_solve_device(b200kkt_handle* h, const double* d_rhs, double* d_x, double* backward_error) {
+   if (int rc = need_device(h)) return rc;
+   if (!h->factorized) return fail(h, B200KKT_EINVAL, "solve before factorize");
+   if (d_rhs == nullptr || d_x == nullptr) return B200KKT_EINVAL;
+   return guarded(h, [&] {
+      CK(cudaSetDevice(h->device));
+      run_solve(h, d_rhs, d_x, backward_error);
+   });
+}
+
+int b200kkt_get_permutation(const b200kkt_handle* h, uint64_t* perm, uint64_t* scatter_map) {
+   if (h == nullptr) return B200KKT_EINVAL;
+   if (!h->analysed) return fail(h, B200KKT_EINVAL, "get_permutation before analyse");
+   if (perm != nullptr) for (int64_t i = 0; i < h->plan.N; ++i) perm[i] = static_cast<uint64_t>(h->plan.perm[i]);
+   if (scatter_map != nullptr) for (int64_t e = 0; e < h->plan.nnz; ++e) scatter_map[e] = static_cast<uint64_t>(h->plan.scatter[e]);
+   return B200KKT_OK;
+}
+
+int b200kkt_get_stats(const b200kkt_handle* h, b200kkt_stats* stats) {
+   if (h == nullptr || stats == nullptr) return B200KKT_EINVAL;
+   *stats = h->stats;
+   stats->kernel_launches = h->launches;
+   if (h->factorized) { stats->num_null_pivots_last = h->h_counters[2]; stats->num_two_by_two_last = h->h_counters[3]; }
+   return B200KKT_OK;
+}
+
+const char* b200kkt_last_error(const b200kkt_handle* h) { return h == nullptr ? "null handle" : h->err.c_str(); }
+
+int b200kkt_plan_sizes(const b200kkt_handle* h, int64_t sizes[8]) {
+   if (h == nullptr || sizes == nullptr) return B200KKT_EINVAL;
+   if (!h->analysed) return fail(h, B200KKT_EINVAL, "plan getter before analyse");
+   const Plan& P = h->plan;
+   sizes[0] = P.nsn; sizes[1] = static_cast<int64_t>(P.rows.size()); sizes[2] = P.pool_size; sizes[3] = P.nlevels;
+   sizes[4] = P.sum_r; sizes[5] = static_cast<int64_t>(P.asm_dst.size()); sizes[6] = 0; sizes[7] = 0;
+   return B200KKT_OK;
+}
+
+int b200kkt_plan_fronts(const b200kkt_handle* h, int32_t* k, int32_t* f, int32_t* ld, int64_t* pool_offset, int32_t* parent, int32_t* level,
+                        int32_t* first_col) {
+   if (h == nullptr) return B200KKT_EINVAL;
+   if (!h->analysed) return fail(h, B200KKT_EINVAL, "plan getter before analyse");
+   const Plan& P = h->plan;
+   for (int32_t s = 0; s < P.nsn; ++s) {
+      if (k != nullptr) k[s] = P.k[s];
+      if (f != nullptr) f[s] = P.f[s];
+      if (ld != nullptr) ld[s] = P.ld[s];
+      if (pool_offset != nullptr) pool_offset[s] = P.front_off[s];
+      if (parent != nullptr) parent[s] = P.parent[s];
+      if (level != nullptr) level[s] = P.level[s];
+      if (first_col != nullptr) first_col[s] = P.sn_first[s];
+   }
+   return B200KKT_OK;
+}
+
+int b200kkt_plan_rows(const b200kkt_handle* h, int64_t* rows_off, int32_t* rows) {
+   if (h == nullptr) return B200KKT_EINVAL;
+   if (!h->analysed) return fail(h, B200KKT_EINVAL, "plan getter before analyse");
+   const Plan& P = h->plan;
+   if (rows_off != nullptr) std::copy(P.rows_off.begin(), P.rows_off.end(), rows_off);
+   if (rows != nullptr) std::copy(P.rows.begin(), P.rows.end(), rows);
+   return B200KKT_OK;
+}
+
+int b200kkt_debug_assemble(b200kkt_handle* h, const double* values, double* pool_out, double* scale_out) {
+   if (int rc = need_device(h)) return rc;
+   if (!h->analysed || values == nullptr) return B200KKT_EINVAL;
+   return guarded(h, [&] {
+      const Plan& P = h->plan;
+      cudaStream_t st = h->stream;
+      CK(cudaSetDevice(h->device));
+      CK(cudaMemcpyAsync(h->d_values, values, static_cast<size_t>(P.nnz) * sizeof(double), cudaMemcpyHostToDevice, st));
+      h->values_resident = true;
+      h->factorized = false;
+      h->launches += launch_fill(h->d_scale, P.N, 1.0, st);
+      double* cur = h->d_scale;
+      double* nxt = h->d_scale_tmp;
+      for (int sw = 0; sw < h->scaling_sweeps; ++sw) {
+         h->launches += launch_scale_sweep(h->C, h->d_values, cur, nxt, st);
+         std::swap(cur, nxt);
+      }
+      h->d_scale_final = cur;
+      CK(cudaMemsetAsync(h->W.pool, 0, static_cast<size_t>(P.pool_size) * sizeof(double), st));
+      h->launches += launch_assemble(h->M, h->d_values, cur, h->W.pool, st);
+      if (pool_out != nullptr) CK(cudaMemcpyAsync(pool_out, h->W.pool, static_cast<size_t>(P.pool_size) * sizeof(double), cudaMemcpyDeviceToHost, st));
+      if (scale_out != nullptr) CK(cudaMemcpyAsync(scale_out, cur, static_cast<size_t>(P.N) * sizeof(double), cudaMemcpyDeviceToHost, st));
+      CK(cudaStreamSynchronize(st));
+      CK(cudaGetLastError());
+   });
+}
+
+int b200kkt_debug_factor(b200kkt_handle* h, double* pool_out, double* d_diag, double* d_off, int32_t* piv_type, int32_t* local_perm) {
+   if (int rc = need_device(h)) return rc;
+   if (!h->factorized) return fail(h, B200KKT_EINVAL, "debug_factor before factorize");
+   return guarded(h, [&] {
+      const Plan& P = h->plan;
+      cudaStream_t st = h->stream;
+      CK(cudaSetDevice(h->device));
+      const size_t n = static_cast<size_t>(P.N);
+      if (pool_out != nullptr) CK(cudaMemcpyAsync(pool_out, h->W.pool, static_cast<size_t>(P.pool_size) * sizeof(double), cudaMemcpyDeviceToHost, st));
+      if (d_diag != nullptr) CK(cudaMemcpyAsync(d_diag, h->W.dd, n * sizeof(double), cudaMemcpyDeviceToHost, st));
+      if (d_off != nullptr) CK(cudaMemcpyAsync(d_off, h->W.de, n * sizeof(double), cudaMemcpyDeviceToHost, st));
+      if (piv_type != nullptr) CK(cudaMemcpyAsync(piv_type, h->W.ptype, n * sizeof(int), cudaMemcpyDeviceToHost, st));
+      if (local_perm != nullptr) CK(cudaMemcpyAsync(local_perm, h->W.lperm, n * sizeof(int), cudaMemcpyDeviceToHost, st));
+      CK(cudaStreamSynchronize(st));
+   });
+}
+
+}  // extern "C"

@@ -1,0 +1,85 @@
+// Solver handle: owns the plan, the device copy of it, the front pool and all workspaces.
+// One handle == one instance of Uno's DirectSymmetricIndefiniteLinearSolver (several coexist:
+// uno/ingredients/constraint_relaxation_strategies/FeasibilityRestoration.cpp:33-34), so there is
+// no global device state: every handle has its own stream and buffers.
+#pragma once
+#include <cstdint>
+#include <string>
+#include <vector>
+
+#include <cuda_runtime.h>
+
+#include "../../include/b200kkt.h"
+#include "kernels.hpp"
+#include "plan.hpp"
+
+namespace b200kkt {
+
+// fronts of one elimination-tree level with similar order f, sorted by pivot count descending
+struct Batch {
+   int level = 0;
+   int begin = 0, count = 0;      // range in the device batch list
+   int max_f = 0, max_k = 0;
+   bool has_children = false;
+   bool big_tiles = false;
+   std::vector<int> k;            // per front of the batch (descending)
+   std::vector<int> pmaxf;        // prefix maximum of f in batch order
+   int count_k_greater(int j) const;   // number of fronts with k > j (a prefix of the batch)
+};
+
+}  // namespace b200kkt
+
+struct b200kkt_handle {
+   int device = -1;
+   int num_gpus = 1;
+   bool has_device = false;
+   mutable std::string err;
+
+   // options
+   b200kkt::AnalyseOptions aopt;
+   std::vector<int64_t> user_perm;
+   int scaling_sweeps = 3;
+   double null_pivot_tol = 1e-14;
+   int refine_max_steps = 6;
+   double refine_tol = 1e-15;
+   int use_graph = 1;
+
+   b200kkt::Plan plan;
+   bool analysed = false, values_resident = false, factorized = false;
+   std::vector<b200kkt::Batch> batches;
+   std::vector<int> level_batch_ptr;       // batches grouped by level
+   std::vector<int> solve_level_ptr;       // ranges of d_solve_list per level
+
+   cudaStream_t stream = nullptr;
+   cudaEvent_t ev0 = nullptr, ev1 = nullptr;
+   cudaGraphExec_t factor_graph = nullptr;
+   std::vector<void*> plan_allocs;         // freed on re-analysis / destroy
+
+   b200kkt::FrontArrays F{};
+   b200kkt::AssemblyArrays M{};
+   b200kkt::CsrArrays C{};
+   b200kkt::FactorArrays W{};
+   int* d_perm = nullptr;
+   int* d_batch_list = nullptr;
+   int* d_solve_list = nullptr;
+   double* d_values = nullptr;
+   double* d_scale = nullptr;
+   double* d_scale_tmp = nullptr;
+   double* d_zg = nullptr;
+   double* d_z2 = nullptr;
+   double* d_xg = nullptr;
+   double* d_cpool = nullptr;
+   double* d_b = nullptr;
+   double* d_x = nullptr;
+   double* d_r = nullptr;
+   int* d_counters = nullptr;              // 8 ints
+   unsigned long long* d_norms = nullptr;  // 4 x u64: |K|_inf, |r|_inf, |x|_inf, |b|_inf
+   int* h_counters = nullptr;              // pinned mirrors
+   unsigned long long* h_norms = nullptr;
+   double* d_scale_final = nullptr;        // whichever of d_scale/d_scale_tmp holds the result
+
+   uint64_t inertia[3] = {0, 0, 0};
+   b200kkt_stats stats{};
+   int64_t launches = 0;
+   int64_t graph_launches = 0;             // kernels inside one replay of factor_graph
+};

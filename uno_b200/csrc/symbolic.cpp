@@ -1,0 +1,597 @@
+// Host symbolic phase: upper-triangular COO pattern -> integer plan.
+//
+// Takes the place of MUMPS JOB=1 behind MUMPSSolver::do_symbolic_analysis
+// (reference: uno/ingredients/subproblem_solvers/MUMPS/MUMPSSolver.cpp:72-83 and the index copy at
+// :149-157).  The input convention is the reference's COO: row <= col, 0-based, duplicates legal,
+// the first reg_size entries are (k,k) regularization placeholders
+// (uno/linear_algebra/COOFormat.hpp:101-125).  Explicit zeros are structural (never pruned).
+//
+// Pipeline: adjacency -> KKT pairing (constraint row matched to a primal column so that a 2x2
+// pivot is always available inside one front) -> METIS_NodeND on the pair-compressed graph ->
+// elimination tree -> postorder -> column counts -> fundamental supernodes -> relaxed
+// amalgamation -> final numbering (pairs first inside each supernode) -> front row structures ->
+// extend-add maps, level schedule, assembly scatter map, CSR for the residual.
+#include "plan.hpp"
+
+#include <algorithm>
+#include <chrono>
+#include <cstring>
+#include <numeric>
+#include <stdexcept>
+
+extern "C" {
+// CUDA ships libmetis_static.a (METIS 5.x, 64-bit idx_t) without a header.
+int METIS_NodeND(int64_t* nvtxs, int64_t* xadj, int64_t* adjncy, int64_t* vwgt, int64_t* options,
+                 int64_t* perm, int64_t* iperm);
+int METIS_SetDefaultOptions(int64_t* options);
+}
+
+namespace b200kkt {
+namespace {
+
+using clk = std::chrono::steady_clock;
+double secs(clk::time_point a, clk::time_point b) { return std::chrono::duration<double>(b - a).count(); }
+
+struct Graph {
+   std::vector<int64_t> ptr;
+   std::vector<int32_t> idx;
+};
+
+// symmetric off-diagonal adjacency, sorted, duplicates removed
+Graph build_adjacency(int64_t N, int64_t nnz, const uint64_t* row, const uint64_t* col) {
+   Graph g;
+   g.ptr.assign(static_cast<size_t>(N) + 1, 0);
+   for (int64_t e = 0; e < nnz; ++e) {
+      const uint64_t r = row[e], c = col[e];
+      if (r >= static_cast<uint64_t>(N) || c >= static_cast<uint64_t>(N)) throw std::runtime_error("analyse: index out of range");
+      if (r > c) throw std::runtime_error("analyse: entry below the diagonal (COO must be upper triangular)");
+      if (r != c) { ++g.ptr[r + 1]; ++g.ptr[c + 1]; }
+   }
+   for (int64_t i = 0; i < N; ++i) g.ptr[i + 1] += g.ptr[i];
+   g.idx.resize(static_cast<size_t>(g.ptr[N]));
+   std::vector<int64_t> fill(g.ptr.begin(), g.ptr.end() - 1);
+   for (int64_t e = 0; e < nnz; ++e) {
+      const uint64_t r = row[e], c = col[e];
+      if (r != c) {
+         g.idx[fill[r]++] = static_cast<int32_t>(c);
+         g.idx[fill[c]++] = static_cast<int32_t>(r);
+      }
+   }
+   // sort + unique per row, compact in place
+   int64_t out = 0;
+   int64_t begin = 0;
+   for (int64_t i = 0; i < N; ++i) {
+      const int64_t end = g.ptr[i + 1];
+      std::sort(g.idx.begin() + begin, g.idx.begin() + end);
+      const int64_t row_start = out;
+      for (int64_t p = begin; p < end; ++p) {
+         if (p == begin || g.idx[p] != g.idx[p - 1]) g.idx[out++] = g.idx[p];
+      }
+      begin = end;
+      g.ptr[i] = row_start;
+      if (i + 1 == N) g.ptr[N] = out;
+   }
+   // ptr[i] currently holds row starts for i<N and ptr[N]=out; nothing else to fix
+   g.idx.resize(static_cast<size_t>(out));
+   g.idx.shrink_to_fit();
+   return g;
+}
+
+// Match every constraint-like node with a distinct adjacent primal node (bipartite matching:
+// greedy by ascending primal degree, then augmenting paths).  partner[i] = matched node or -1.
+void kkt_pairing(int64_t N, const Graph& g, const std::vector<char>& is_con, std::vector<int32_t>& partner) {
+   partner.assign(static_cast<size_t>(N), -1);
+   auto degree = [&](int32_t v) { return g.ptr[v + 1] - g.ptr[v]; };
+   std::vector<int32_t> unmatched;
+   for (int64_t j = 0; j < N; ++j) {
+      if (!is_con[j]) continue;
+      int32_t best = -1;
+      int64_t best_deg = 0;
+      for (int64_t p = g.ptr[j]; p < g.ptr[j + 1]; ++p) {
+         const int32_t v = g.idx[p];
+         if (is_con[v] || partner[v] != -1) continue;
+         const int64_t d = degree(v);
+         if (best == -1 || d < best_deg) { best = v; best_deg = d; }
+      }
+      if (best != -1) { partner[j] = best; partner[best] = static_cast<int32_t>(j); }
+      else unmatched.push_back(static_cast<int32_t>(j));
+   }
+   if (unmatched.empty()) return;
+   // Augmenting paths (iterative Kuhn) for the constraints the greedy pass left unmatched.  The DFS
+   // stack holds constraint nodes; partner[stack[d]] (for d > 0) is the primal through which
+   // stack[d] was reached.  Work per root is bounded so analysis stays near-linear.
+   std::vector<int32_t> stamp(static_cast<size_t>(N), -1);
+   std::vector<int64_t> cursor(static_cast<size_t>(N), 0);
+   std::vector<int32_t> stack;
+   int32_t round = 0;
+   for (int32_t root : unmatched) {
+      ++round;
+      int64_t budget = 200000;
+      stack.assign(1, root);
+      cursor[root] = g.ptr[root];
+      bool found = false;
+      while (!stack.empty() && budget > 0 && !found) {
+         const int32_t j = stack.back();
+         bool descended = false;
+         while (cursor[j] < g.ptr[j + 1]) {
+            --budget;
+            const int32_t v = g.idx[cursor[j]++];
+            if (is_con[v] || stamp[v] == round) continue;
+            stamp[v] = round;
+            if (partner[v] == -1) {
+               // flip the alternating path: every constraint on the stack hands its old primal down
+               int32_t free_v = v;
+               for (int64_t d = static_cast<int64_t>(stack.size()) - 1; d >= 0; --d) {
+                  const int32_t cj = stack[d];
+                  const int32_t old_v = partner[cj];   // -1 for the root
+                  partner[cj] = free_v;
+                  partner[free_v] = cj;
+                  free_v = old_v;
+               }
+               found = true;
+            } else {
+               const int32_t next_con = partner[v];
+               stack.push_back(next_con);
+               cursor[next_con] = g.ptr[next_con];
+               descended = true;
+            }
+            break;
+         }
+         if (!found && !descended) stack.pop_back();
+      }
+   }
+}
+
+}  // namespace
+
+void analyse(int64_t N, int64_t nnz, int64_t reg_size, int64_t num_primal, const uint64_t* row, const uint64_t* col,
+             const AnalyseOptions& opt, Plan& P) {
+   if (N <= 0) throw std::runtime_error("analyse: empty matrix");
+   if (N >= (int64_t(1) << 31) - 8 || nnz >= (int64_t(1) << 31) - 8) throw std::runtime_error("analyse: dimension exceeds int32 plan indices");
+   if (reg_size > nnz) throw std::runtime_error("analyse: reg_size > nnz");
+   P = Plan();
+   P.N = N; P.nnz = nnz; P.reg_size = reg_size;
+   if (num_primal <= 0 || num_primal > N) num_primal = N;
+   P.num_primal = num_primal;
+   const auto t0 = clk::now();
+
+   Graph g = build_adjacency(N, nnz, row, col);
+
+   // ---- constraint-like nodes and KKT pairing --------------------------------------------------
+   std::vector<char> is_con(static_cast<size_t>(N), 0);
+   bool any_con = false;
+   if (num_primal < N) {
+      for (int64_t i = num_primal; i < N; ++i) is_con[i] = 1;
+      any_con = true;
+   } else {
+      // no hint: a row without any structural diagonal entry behaves like a multiplier row
+      std::vector<char> has_diag(static_cast<size_t>(N), 0);
+      for (int64_t e = 0; e < nnz; ++e) if (row[e] == col[e]) has_diag[row[e]] = 1;
+      for (int64_t i = 0; i < N; ++i) if (!has_diag[i] && g.ptr[i + 1] > g.ptr[i]) { is_con[i] = 1; any_con = true; }
+   }
+   std::vector<int32_t> partner(static_cast<size_t>(N), -1);
+   if (opt.kkt_pairing && any_con) kkt_pairing(N, g, is_con, partner);
+   for (int64_t i = 0; i < N; ++i) if (is_con[i] && partner[i] != -1) ++P.num_pairs;
+
+   // ---- fill-reducing ordering on the pair-compressed graph -----------------------------------
+   // compressed node = {primal, matched constraint} or a singleton
+   std::vector<int32_t> cid(static_cast<size_t>(N), -1);
+   std::vector<int32_t> cfirst;   // representative (primal first) of each compressed node
+   for (int64_t i = 0; i < N; ++i) {
+      if (cid[i] != -1) continue;
+      const int32_t p = partner[i];
+      const int32_t id = static_cast<int32_t>(cfirst.size());
+      if (p == -1) { cid[i] = id; cfirst.push_back(static_cast<int32_t>(i)); }
+      else {
+         const int32_t var = is_con[i] ? p : static_cast<int32_t>(i);
+         cid[var] = id; cid[partner[var]] = id; cfirst.push_back(var);
+      }
+   }
+   const int64_t cN = static_cast<int64_t>(cfirst.size());
+   std::vector<int64_t> corder(static_cast<size_t>(cN));   // corder[new] = compressed node
+   std::iota(corder.begin(), corder.end(), 0);
+   P.ordering_used = "natural";
+   if (opt.ordering == 2 && opt.user_perm != nullptr) {
+      // user permutation on ORIGINAL nodes; compressed order = first appearance of each compressed node
+      std::vector<char> seen(static_cast<size_t>(cN), 0);
+      int64_t out = 0;
+      std::vector<char> check(static_cast<size_t>(N), 0);
+      for (int64_t i = 0; i < N; ++i) {
+         const int64_t o = opt.user_perm[i];
+         if (o < 0 || o >= N || check[o]) throw std::runtime_error("analyse: user permutation is not a permutation");
+         check[o] = 1;
+         if (!seen[cid[o]]) { seen[cid[o]] = 1; corder[out++] = cid[o]; }
+      }
+      P.ordering_used = "user";
+   } else if (opt.ordering == 0 && cN > 2) {
+      std::vector<int64_t> xadj(static_cast<size_t>(cN) + 1, 0), adjncy, vwgt(static_cast<size_t>(cN), 1);
+      adjncy.reserve(g.idx.size());
+      std::vector<int32_t> mark(static_cast<size_t>(cN), -1);
+      for (int64_t c = 0; c < cN; ++c) {
+         const int32_t a = cfirst[c];
+         const int32_t members[2] = {a, partner[a]};
+         mark[c] = static_cast<int32_t>(c);
+         for (int32_t mnode : members) {
+            if (mnode < 0) continue;
+            if (mnode != a) vwgt[c] = 2;
+            for (int64_t p = g.ptr[mnode]; p < g.ptr[mnode + 1]; ++p) {
+               const int32_t t = cid[g.idx[p]];
+               if (mark[t] != c) { mark[t] = static_cast<int32_t>(c); adjncy.push_back(t); }
+            }
+         }
+         xadj[c + 1] = static_cast<int64_t>(adjncy.size());
+      }
+      if (!adjncy.empty()) {
+         std::vector<int64_t> options(40), mperm(static_cast<size_t>(cN)), miperm(static_cast<size_t>(cN));
+         METIS_SetDefaultOptions(options.data());
+         int64_t n = cN;
+         const int rc = METIS_NodeND(&n, xadj.data(), adjncy.data(), vwgt.data(), options.data(), mperm.data(), miperm.data());
+         if (rc == 1) { corder = mperm; P.ordering_used = "metis_nodend"; }
+      }
+   }
+   // expand: primal first, then its matched constraint
+   std::vector<int32_t> order(static_cast<size_t>(N)), ipos(static_cast<size_t>(N));
+   {
+      int64_t out = 0;
+      for (int64_t c = 0; c < cN; ++c) {
+         const int32_t a = cfirst[corder[c]];
+         order[out++] = a;
+         if (partner[a] != -1) order[out++] = partner[a];
+      }
+      for (int64_t i = 0; i < N; ++i) ipos[order[i]] = static_cast<int32_t>(i);
+   }
+   const auto t1 = clk::now();
+   P.t_order = secs(t0, t1);
+
+   // ---- elimination tree (Liu) ----------------------------------------------------------------
+   std::vector<int32_t> parent(static_cast<size_t>(N), -1);
+   {
+      std::vector<int32_t> ancestor(static_cast<size_t>(N), -1);
+      for (int64_t j = 0; j < N; ++j) {
+         const int32_t oj = order[j];
+         for (int64_t p = g.ptr[oj]; p < g.ptr[oj + 1]; ++p) {
+            int32_t i = ipos[g.idx[p]];
+            while (i != -1 && i < j) {
+               const int32_t inext = ancestor[i];
+               ancestor[i] = static_cast<int32_t>(j);
+               if (inext == -1) parent[i] = static_cast<int32_t>(j);
+               i = inext;
+            }
+         }
+      }
+   }
+   // ---- postorder and relabel -----------------------------------------------------------------
+   {
+      std::vector<int32_t> head(static_cast<size_t>(N), -1), next(static_cast<size_t>(N), -1), post(static_cast<size_t>(N));
+      for (int64_t j = N - 1; j >= 0; --j) {
+         if (parent[j] == -1) continue;
+         next[j] = head[parent[j]];
+         head[parent[j]] = static_cast<int32_t>(j);
+      }
+      int64_t kpos = 0;
+      std::vector<int32_t> stack;
+      for (int64_t root = 0; root < N; ++root) {
+         if (parent[root] != -1) continue;
+         stack.push_back(static_cast<int32_t>(root));
+         while (!stack.empty()) {
+            const int32_t p = stack.back();
+            const int32_t i = head[p];
+            if (i == -1) { stack.pop_back(); post[kpos++] = p; }
+            else { head[p] = next[i]; stack.push_back(i); }
+         }
+      }
+      std::vector<int32_t> ipost(static_cast<size_t>(N));
+      for (int64_t kk = 0; kk < N; ++kk) ipost[post[kk]] = static_cast<int32_t>(kk);
+      std::vector<int32_t> order2(static_cast<size_t>(N)), parent2(static_cast<size_t>(N));
+      for (int64_t kk = 0; kk < N; ++kk) {
+         order2[kk] = order[post[kk]];
+         const int32_t pp = parent[post[kk]];
+         parent2[kk] = (pp == -1) ? -1 : ipost[pp];
+      }
+      order.swap(order2);
+      parent.swap(parent2);
+      for (int64_t i = 0; i < N; ++i) ipos[order[i]] = static_cast<int32_t>(i);
+   }
+   // ---- column counts (Gilbert-Ng-Peyton, postordered so post = identity) ----------------------
+   std::vector<int32_t> colcount(static_cast<size_t>(N), 0);
+   {
+      std::vector<int32_t> ancestor(static_cast<size_t>(N)), maxfirst(static_cast<size_t>(N), -1), prevleaf(static_cast<size_t>(N), -1),
+         first(static_cast<size_t>(N), -1);
+      std::vector<int32_t>& delta = colcount;
+      for (int64_t kk = 0; kk < N; ++kk) {
+         int32_t j = static_cast<int32_t>(kk);
+         delta[j] = (first[j] == -1) ? 1 : 0;
+         for (; j != -1 && first[j] == -1; j = parent[j]) first[j] = static_cast<int32_t>(kk);
+      }
+      std::iota(ancestor.begin(), ancestor.end(), 0);
+      for (int64_t j = 0; j < N; ++j) {
+         if (parent[j] != -1) --delta[parent[j]];
+         const int32_t oj = order[j];
+         for (int64_t p = g.ptr[oj]; p < g.ptr[oj + 1]; ++p) {
+            const int32_t i = ipos[g.idx[p]];
+            if (i <= j || first[j] <= maxfirst[i]) continue;   // j is not a leaf of the i-th row subtree
+            maxfirst[i] = first[j];
+            const int32_t jprev = prevleaf[i];
+            prevleaf[i] = static_cast<int32_t>(j);
+            if (jprev == -1) { ++delta[j]; continue; }          // first leaf
+            int32_t q = jprev;
+            while (q != ancestor[q]) q = ancestor[q];
+            for (int32_t s = jprev; s != q;) { const int32_t sp = ancestor[s]; ancestor[s] = q; s = sp; }
+            ++delta[j];
+            --delta[q];
+         }
+         if (parent[j] != -1) ancestor[j] = parent[j];
+      }
+      for (int64_t j = 0; j < N; ++j) if (parent[j] != -1) colcount[parent[j]] += colcount[j];
+   }
+   // ---- fundamental supernodes ----------------------------------------------------------------
+   std::vector<int32_t> sfirst0;   // first column of each fundamental supernode
+   {
+      std::vector<int32_t> nchild(static_cast<size_t>(N), 0);
+      for (int64_t j = 0; j < N; ++j) if (parent[j] != -1) ++nchild[parent[j]];
+      for (int64_t j = 0; j < N; ++j) {
+         const bool chain = j > 0 && parent[j - 1] == j && colcount[j - 1] == colcount[j] + 1 && nchild[j] == 1;
+         if (!chain) sfirst0.push_back(static_cast<int32_t>(j));
+      }
+      sfirst0.push_back(static_cast<int32_t>(N));
+   }
+   const int32_t ns0 = static_cast<int32_t>(sfirst0.size()) - 1;
+   std::vector<int32_t> sn0_of(static_cast<size_t>(N));
+   for (int32_t s = 0; s < ns0; ++s) for (int32_t j = sfirst0[s]; j < sfirst0[s + 1]; ++j) sn0_of[j] = s;
+
+   // ---- relaxed amalgamation on the supernodal tree --------------------------------------------
+   std::vector<int64_t> kk(static_cast<size_t>(ns0)), ff(static_cast<size_t>(ns0)), zeros(static_cast<size_t>(ns0), 0);
+   std::vector<int32_t> sparent(static_cast<size_t>(ns0)), merged_into(static_cast<size_t>(ns0), -1);
+   std::vector<char> force(static_cast<size_t>(ns0), 0);
+   for (int32_t s = 0; s < ns0; ++s) {
+      kk[s] = sfirst0[s + 1] - sfirst0[s];
+      ff[s] = colcount[sfirst0[s]];
+      const int32_t last = sfirst0[s + 1] - 1;
+      sparent[s] = (parent[last] == -1) ? -1 : sn0_of[parent[last]];
+      // a paired primal column must end up in the same front as its constraint row (its etree parent)
+      const int32_t olast = order[last];
+      if (partner[olast] != -1 && !is_con[olast] && sparent[s] != -1 && ipos[partner[olast]] > last) force[s] = 1;
+   }
+   {
+      std::vector<std::vector<int32_t>> kids(static_cast<size_t>(ns0));
+      for (int32_t s = 0; s < ns0; ++s) if (sparent[s] != -1) kids[sparent[s]].push_back(s);
+      std::vector<int32_t> cand;
+      for (int32_t s = 0; s < ns0; ++s) {
+         cand = kids[s];
+         // best structural match first: fewest explicit zeros per merged column
+         std::sort(cand.begin(), cand.end(), [&](int32_t a, int32_t b) {
+            const int64_t za = kk[a] + ff[s] - ff[a], zb = kk[b] + ff[s] - ff[b];
+            if (force[a] != force[b]) return force[a] > force[b];
+            if (za != zb) return za < zb;
+            return a < b;
+         });
+         for (int32_t c : cand) {
+            const int64_t kn = kk[c] + kk[s], fn = kk[c] + ff[s];
+            const int64_t znew = zeros[c] + zeros[s] + kk[c] * (kk[c] + ff[s] - ff[c]);
+            const double nnzl = static_cast<double>(kn) * static_cast<double>(fn) - 0.5 * static_cast<double>(kn) * static_cast<double>(kn - 1);
+            const double ratio = static_cast<double>(znew) / nnzl;
+            bool merge = force[c] != 0;
+            if (!merge) {
+               if (kn <= opt.relax_small) merge = true;
+               else if (kn <= opt.relax_mid) merge = ratio <= opt.relax_mid_zeros;
+               else if (kn <= opt.relax_big) merge = ratio <= opt.relax_big_zeros;
+               else merge = ratio <= opt.relax_any_zeros;
+            }
+            if (!merge) continue;
+            merged_into[c] = s;
+            kk[s] = kn; ff[s] = fn; zeros[s] = znew;
+            for (int32_t gc : kids[c]) { sparent[gc] = s; kids[s].push_back(gc); }
+            kids[c].clear();
+         }
+      }
+   }
+   // ---- final numbering: postorder of the merged tree, pairs first inside each supernode -------
+   std::vector<int32_t> rep(static_cast<size_t>(ns0));
+   for (int32_t s = ns0 - 1; s >= 0; --s) rep[s] = (merged_into[s] == -1) ? s : rep[merged_into[s]];
+   std::vector<int32_t> final_order(static_cast<size_t>(N));
+   {
+      // members of each representative, ascending
+      std::vector<int32_t> mcount(static_cast<size_t>(ns0) + 1, 0);
+      for (int32_t s = 0; s < ns0; ++s) ++mcount[rep[s] + 1];
+      for (int32_t s = 0; s < ns0; ++s) mcount[s + 1] += mcount[s];
+      std::vector<int32_t> members(static_cast<size_t>(ns0)), mfill(mcount.begin(), mcount.end() - 1);
+      for (int32_t s = 0; s < ns0; ++s) members[mfill[rep[s]]++] = s;
+      // representatives are visited in ascending index = a postorder of the merged tree
+      // (a representative is the topmost = largest-index member of its group, and children < parents)
+      int32_t nsn = 0;
+      int64_t out = 0;
+      P.sn_first.clear();
+      std::vector<int32_t> singles;
+      for (int32_t s = 0; s < ns0; ++s) {
+         if (rep[s] != s) continue;
+         P.sn_first.push_back(static_cast<int32_t>(out));
+         singles.clear();
+         for (int32_t mi = mcount[s]; mi < mcount[s + 1]; ++mi) {
+            const int32_t ms = members[mi];
+            for (int32_t j = sfirst0[ms]; j < sfirst0[ms + 1]; ++j) {
+               const int32_t oj = order[j];
+               const int32_t pj = partner[oj];
+               if (pj == -1 || rep[sn0_of[ipos[pj]]] != s) { singles.push_back(oj); continue; }
+               if (!is_con[oj]) { final_order[out++] = oj; final_order[out++] = pj; }
+            }
+         }
+         for (int32_t oj : singles) final_order[out++] = oj;
+         ++nsn;
+      }
+      P.sn_first.push_back(static_cast<int32_t>(out));
+      if (out != N) throw std::runtime_error("analyse: internal error (final numbering incomplete)");
+      P.nsn = nsn;
+   }
+   P.perm = final_order;
+   P.iperm.resize(static_cast<size_t>(N));
+   for (int64_t i = 0; i < N; ++i) P.iperm[P.perm[i]] = static_cast<int32_t>(i);
+   P.sn_of.resize(static_cast<size_t>(N));
+   for (int32_t s = 0; s < P.nsn; ++s) for (int32_t j = P.sn_first[s]; j < P.sn_first[s + 1]; ++j) P.sn_of[j] = s;
+
+   // ---- front row structures (children before parents) ----------------------------------------
+   const int32_t nsn = P.nsn;
+   P.k.resize(nsn); P.f.resize(nsn); P.ld.resize(nsn); P.parent.assign(nsn, -1);
+   P.rows_off.assign(static_cast<size_t>(nsn) + 1, 0);
+   P.rows.clear();
+   {
+      std::vector<int32_t> mark(static_cast<size_t>(N), -1);
+      std::vector<std::vector<int32_t>> kids(static_cast<size_t>(nsn));
+      std::vector<int32_t> bnd;
+      for (int32_t s = 0; s < nsn; ++s) {
+         const int32_t c0 = P.sn_first[s], c1 = P.sn_first[s + 1];
+         bnd.clear();
+         for (int32_t j = c0; j < c1; ++j) {
+            const int32_t oj = P.perm[j];
+            for (int64_t p = g.ptr[oj]; p < g.ptr[oj + 1]; ++p) {
+               const int32_t i = P.iperm[g.idx[p]];
+               if (i >= c1 && mark[i] != s) { mark[i] = s; bnd.push_back(i); }
+            }
+         }
+         for (int32_t c : kids[s]) {
+            const int64_t b0 = P.rows_off[c] + P.k[c], b1 = P.rows_off[c + 1];
+            for (int64_t p = b0; p < b1; ++p) {
+               const int32_t i = P.rows[p];
+               if (i >= c1 && mark[i] != s) { mark[i] = s; bnd.push_back(i); }
+            }
+         }
+         std::sort(bnd.begin(), bnd.end());
+         P.k[s] = c1 - c0;
+         P.f[s] = P.k[s] + static_cast<int32_t>(bnd.size());
+         P.ld[s] = (P.f[s] + 3) & ~3;
+         for (int32_t j = c0; j < c1; ++j) P.rows.push_back(j);
+         P.rows.insert(P.rows.end(), bnd.begin(), bnd.end());
+         P.rows_off[s + 1] = static_cast<int64_t>(P.rows.size());
+         if (!bnd.empty()) {
+            P.parent[s] = P.sn_of[bnd[0]];
+            kids[P.parent[s]].push_back(s);
+         }
+      }
+      P.child_ptr.assign(static_cast<size_t>(nsn) + 1, 0);
+      for (int32_t s = 0; s < nsn; ++s) P.child_ptr[s + 1] = P.child_ptr[s] + static_cast<int32_t>(kids[s].size());
+      P.child_idx.resize(static_cast<size_t>(P.child_ptr[nsn]));
+      for (int32_t s = 0; s < nsn; ++s) std::copy(kids[s].begin(), kids[s].end(), P.child_idx.begin() + P.child_ptr[s]);
+   }
+   // ---- extend-add maps -------------------------------------------------------------------------
+   P.rel_off.assign(static_cast<size_t>(nsn) + 1, 0);
+   for (int32_t s = 0; s < nsn; ++s) P.rel_off[s + 1] = P.rel_off[s] + (P.f[s] - P.k[s]);
+   P.relmap.resize(static_cast<size_t>(P.rel_off[nsn]));
+   for (int32_t s = 0; s < nsn; ++s) {
+      const int32_t p = P.parent[s];
+      if (p == -1) continue;
+      const int32_t pc0 = P.sn_first[p], pc1 = P.sn_first[p + 1];
+      const int32_t* pb = P.rows.data() + P.rows_off[p] + P.k[p];
+      const int32_t* pe = P.rows.data() + P.rows_off[p + 1];
+      const int32_t* cur = pb;
+      for (int32_t i = 0; i < P.f[s] - P.k[s]; ++i) {
+         const int32_t grow = P.rows[P.rows_off[s] + P.k[s] + i];
+         int32_t loc;
+         if (grow < pc1) loc = grow - pc0;
+         else {
+            cur = std::lower_bound(cur, pe, grow);
+            if (cur == pe || *cur != grow) throw std::runtime_error("analyse: internal error (child row missing from parent front)");
+            loc = P.k[p] + static_cast<int32_t>(cur - pb);
+         }
+         P.relmap[P.rel_off[s] + i] = loc;
+      }
+   }
+   // ---- level schedule ------------------------------------------------------------------------
+   P.level.assign(nsn, 0);
+   for (int32_t s = 0; s < nsn; ++s) {
+      const int32_t p = P.parent[s];
+      if (p != -1) P.level[p] = std::max(P.level[p], P.level[s] + 1);
+   }
+   P.nlevels = 0;
+   for (int32_t s = 0; s < nsn; ++s) P.nlevels = std::max(P.nlevels, P.level[s] + 1);
+   P.level_ptr.assign(static_cast<size_t>(P.nlevels) + 1, 0);
+   for (int32_t s = 0; s < nsn; ++s) ++P.level_ptr[P.level[s] + 1];
+   for (int32_t l = 0; l < P.nlevels; ++l) P.level_ptr[l + 1] += P.level_ptr[l];
+   P.level_fronts.resize(nsn);
+   {
+      std::vector<int32_t> fillp(P.level_ptr.begin(), P.level_ptr.end() - 1);
+      for (int32_t s = 0; s < nsn; ++s) P.level_fronts[fillp[P.level[s]]++] = s;
+      for (int32_t l = 0; l < P.nlevels; ++l) {
+         std::stable_sort(P.level_fronts.begin() + P.level_ptr[l], P.level_fronts.begin() + P.level_ptr[l + 1],
+                          [&](int32_t a, int32_t b) { return P.f[a] != P.f[b] ? P.f[a] > P.f[b] : P.k[a] > P.k[b]; });
+      }
+   }
+   // ---- pool layout and work figures ----------------------------------------------------------
+   P.front_off.resize(nsn);
+   int64_t off = 0;
+   for (int32_t s = 0; s < nsn; ++s) {
+      P.front_off[s] = off;
+      off += static_cast<int64_t>(P.ld[s]) * P.f[s];
+      const double kd = P.k[s], rd = P.f[s] - P.k[s];
+      P.nnz_L += static_cast<int64_t>(P.k[s]) * P.f[s] - static_cast<int64_t>(P.k[s]) * (P.k[s] - 1) / 2;
+      const double fl = kd * kd * kd / 3.0 + kd * kd * rd + kd * rd * rd;
+      P.flops += fl;
+      if (P.k[s] >= 128) P.flops_tc += kd * kd * rd + kd * rd * rd;
+      P.sum_r += P.f[s] - P.k[s];
+      P.max_f = std::max(P.max_f, P.f[s]);
+      P.max_k = std::max(P.max_k, P.k[s]);
+   }
+   P.pool_size = off;
+   const auto t2 = clk::now();
+   P.t_symbolic = secs(t1, t2);
+
+   // ---- assembly scatter map --------------------------------------------------------------------
+   P.scatter.resize(static_cast<size_t>(nnz));
+   for (int64_t e = 0; e < nnz; ++e) {
+      const int32_t pr = P.iperm[row[e]], pc = P.iperm[col[e]];
+      const int32_t lo = std::min(pr, pc), hi = std::max(pr, pc);
+      const int32_t s = P.sn_of[lo];
+      const int32_t c1 = P.sn_first[s + 1];
+      int32_t lrow;
+      if (hi < c1) lrow = hi - P.sn_first[s];
+      else {
+         const int32_t* pb = P.rows.data() + P.rows_off[s] + P.k[s];
+         const int32_t* pe = P.rows.data() + P.rows_off[s + 1];
+         const int32_t* it = std::lower_bound(pb, pe, hi);
+         if (it == pe || *it != hi) throw std::runtime_error("analyse: internal error (entry outside its front)");
+         lrow = P.k[s] + static_cast<int32_t>(it - pb);
+      }
+      P.scatter[e] = P.front_off[s] + static_cast<int64_t>(lo - P.sn_first[s]) * P.ld[s] + lrow;
+   }
+   {
+      std::vector<int32_t> idx(static_cast<size_t>(nnz));
+      std::iota(idx.begin(), idx.end(), 0);
+      std::sort(idx.begin(), idx.end(), [&](int32_t a, int32_t b) {
+         if (P.scatter[a] != P.scatter[b]) return P.scatter[a] < P.scatter[b];
+         return a < b;
+      });
+      P.asm_src = idx;
+      P.asm_row.resize(static_cast<size_t>(nnz));
+      P.asm_col.resize(static_cast<size_t>(nnz));
+      P.asm_dst.clear();
+      P.asm_seg.clear();
+      for (int64_t t = 0; t < nnz; ++t) {
+         const int32_t e = idx[t];
+         P.asm_row[t] = static_cast<int32_t>(row[e]);
+         P.asm_col[t] = static_cast<int32_t>(col[e]);
+         if (t == 0 || P.scatter[e] != P.scatter[idx[t - 1]]) {
+            P.asm_dst.push_back(P.scatter[e]);
+            P.asm_seg.push_back(static_cast<int32_t>(t));
+         }
+      }
+      P.asm_seg.push_back(static_cast<int32_t>(nnz));
+   }
+   // ---- symmetric CSR (original numbering, duplicates kept, slot order) ------------------------
+   P.csr_ptr.assign(static_cast<size_t>(N) + 1, 0);
+   for (int64_t e = 0; e < nnz; ++e) {
+      ++P.csr_ptr[row[e] + 1];
+      if (row[e] != col[e]) ++P.csr_ptr[col[e] + 1];
+   }
+   for (int64_t i = 0; i < N; ++i) P.csr_ptr[i + 1] += P.csr_ptr[i];
+   P.csr_col.resize(static_cast<size_t>(P.csr_ptr[N]));
+   P.csr_slot.resize(static_cast<size_t>(P.csr_ptr[N]));
+   {
+      std::vector<int32_t> fillp(P.csr_ptr.begin(), P.csr_ptr.end() - 1);
+      for (int64_t e = 0; e < nnz; ++e) {
+         const int32_t r = static_cast<int32_t>(row[e]), c = static_cast<int32_t>(col[e]);
+         P.csr_col[fillp[r]] = c; P.csr_slot[fillp[r]++] = static_cast<int32_t>(e);
+         if (r != c) { P.csr_col[fillp[c]] = r; P.csr_slot[fillp[c]++] = static_cast<int32_t>(e); }
+      }
+   }
+   P.t_maps = secs(t2, clk::now());
+}
+
+}  // namespace b200kkt
