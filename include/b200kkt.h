@@ -50,6 +50,11 @@ typedef struct b200kkt_stats {
    double backward_error_last;
    int64_t kernel_launches;    /* cumulative count of this library's kernel launches */
    int64_t num_null_pivots_last, num_two_by_two_last;
+   /* option "profile_updates" = 1: CUDA-event time, algorithmic flops and launch count of the K4
+    * trailing-update launches on fronts of order >= 1024 during the last factorization */
+   double t_update_profiled, flops_update_profiled;
+   int64_t n_update_profiled;
+   double t_assemble_profiled;   /* K1 (memset excluded) under the same option */
 } b200kkt_stats;
 
 /* Handle life cycle.  Replaces JOB=-1 / JOB=-2 (MUMPSSolver.cpp:16-49).
@@ -60,7 +65,7 @@ int b200kkt_destroy(b200kkt_handle* h);
 
 /* Options (defaults need no user action).  Names: "ordering" (0 METIS, 1 natural),
  * "kkt_pairing", "relax_small", "relax_mid", "relax_big", "scaling_sweeps", "null_pivot_tol",
- * "refine_max_steps", "refine_tol", "use_graph". */
+ * "refine_max_steps", "refine_tol", "use_graph", "profile_updates". */
 int b200kkt_set_option(b200kkt_handle* h, const char* name, double value);
 /* Optional user ordering for the next analyse (perm[new] = old, length N); NULL clears it. */
 int b200kkt_set_user_permutation(b200kkt_handle* h, const int64_t* perm, uint64_t n);
@@ -96,6 +101,8 @@ int b200kkt_solve_device(b200kkt_handle* h, const double* d_rhs, double* d_x, do
 int b200kkt_get_permutation(const b200kkt_handle* h, uint64_t* perm, uint64_t* scatter_map);
 int b200kkt_get_stats(const b200kkt_handle* h, b200kkt_stats* stats);
 const char* b200kkt_last_error(const b200kkt_handle* h);
+/* The CUDA stream (cudaStream_t) every kernel of this handle is launched on, for event timing. */
+int b200kkt_get_stream(const b200kkt_handle* h, void** stream);
 
 /* Plan getters (integer plan of the symbolic phase).  sizes[0..7] = number of fronts, total row
  * entries, pool doubles, levels, sum of boundary rows, distinct assembly destinations, 0, 0. */

@@ -1,0 +1,605 @@
+// ORACLE — TEST INFRASTRUCTURE ONLY.  Never linked into, imported by or called from the product
+// (uno_b200/).  Only tests/, __graft_entry__.smoke() and bench.py's cpu_baseline / --impl reference
+// legs may build or call this file.
+//
+// CPU restatement of the reference's numeric path: what dmumps_c does for
+// MUMPSSolver::do_symbolic_analysis / do_numerical_factorization / solve_indefinite_system /
+// get_inertia (reference: uno/ingredients/subproblem_solvers/MUMPS/MUMPSSolver.cpp:72-96,124-147).
+// The arithmetic itself lives in MUMPS 5.8.0 (pinned by .github/workflows/unit-tests-ubuntu.yml:55),
+// a Fortran dependency that is NOT vendored under /root/reference and cannot be built here (no
+// gfortran).  This file therefore restates MUMPS' *published* algorithm (Amestoy, Duff, L'Excellent,
+// "Multifrontal parallel distributed symmetric and unsymmetric solvers", CMAME 2000; Duff & Reid,
+// "The multifrontal solution of indefinite sparse symmetric linear systems", TOMS 1983):
+//   * symmetric equilibration of the input (ICNTL(8): MUMPSSolver.cpp:82),
+//   * elimination tree + supernodes of the permuted pattern (ordering handed in, as with
+//     ICNTL(7)=1/PERM_IN, or METIS_NodeND when none is given),
+//   * multifrontal LDL^T (SYM=2: MUMPSSolver.cpp:17) with 1x1 and 2x2 pivots, threshold partial
+//     pivoting (CNTL(1), default 0.01) tested against the WHOLE front column, and delayed pivots
+//     passed to the parent front,
+//   * null-pivot detection at the root (ICNTL(24)=1: MUMPSSolver.cpp:36) -> INFOG(28),
+//     negative pivot count -> INFOG(12) (MUMPSSolver.cpp:131-139),
+//   * forward / diagonal / backward solve without iterative refinement (ICNTL(10)=0).
+// Parity pins: the three known-answer tests the reference keeps (commented out) in
+// unotest/functional_tests/MUMPSSolverTests.cpp:11-83 are checked in tests/test_oracle.py.
+// Parity against a real MUMPS binary is UNPINNED (none exists in this environment).
+//
+// It deliberately shares no code with the product: own symbolic phase, own pivoting (stronger:
+// full-column threshold test + delays, where the GPU path confines the search to 32x32 blocks).
+#include <algorithm>
+#include <chrono>
+#include <cmath>
+#include <cstdint>
+#include <cstdio>
+#include <cstring>
+#include <dlfcn.h>
+#include <numeric>
+#include <stdexcept>
+#include <string>
+#include <vector>
+#ifdef _OPENMP
+#include <omp.h>
+#endif
+
+extern "C" {
+int METIS_NodeND(int64_t*, int64_t*, int64_t*, int64_t*, int64_t*, int64_t*, int64_t*);
+int METIS_SetDefaultOptions(int64_t*);
+}
+
+namespace {
+
+// ---- optional BLAS (OpenBLAS shipped inside scipy), loaded at run time ---------------------------
+typedef void (*cblas_dgemm_t)(int, int, int, int, int, int, double, const double*, int, const double*, int, double, double*, int);
+typedef void (*set_threads_t)(int);
+cblas_dgemm_t g_dgemm = nullptr;
+set_threads_t g_set_threads = nullptr;
+
+// C[m x n] -= A[m x k] * B[n x k]^T, all column-major
+void gemm_nt_sub(int m, int n, int k, const double* A, int lda, const double* B, int ldb, double* C, int ldc) {
+   if (m <= 0 || n <= 0 || k <= 0) return;
+   if (g_dgemm != nullptr) {
+      g_dgemm(102 /*ColMajor*/, 111 /*NoTrans*/, 112 /*Trans*/, m, n, k, -1.0, A, lda, B, ldb, 1.0, C, ldc);
+      return;
+   }
+   for (int j = 0; j < n; ++j) {
+      double* c = C + static_cast<size_t>(ldc) * j;
+      for (int p = 0; p < k; ++p) {
+         const double b = B[j + static_cast<size_t>(ldb) * p];
+         if (b == 0.0) continue;
+         const double* a = A + static_cast<size_t>(lda) * p;
+         for (int i = 0; i < m; ++i) c[i] -= a[i] * b;
+      }
+   }
+}
+
+struct Front {
+   // static structure
+   int first = 0, ncol = 0;            // own columns [first, first+ncol) in elimination numbering
+   std::vector<int> bnd;               // static boundary rows (sorted)
+   int parent = -1;
+   std::vector<int> children;
+   // numeric result
+   int nf = 0, nelim = 0;
+   std::vector<int> idx;               // global ids of the front rows in final local order
+   std::vector<double> L;              // nf x nelim, column-major, unit diagonal implied
+   std::vector<double> d, e;           // D blocks: d diagonal, e[j] != 0 -> 2x2 block (j, j+1)
+   std::vector<char> ptype;            // 0 1x1, 1/2 first/second of 2x2, 3 null
+   // contribution block handed to the parent (freed once consumed)
+   int ncb = 0, ndelay = 0;
+   std::vector<int> cb_idx;
+   std::vector<double> cb;
+};
+
+struct Oracle {
+   int64_t N = 0, nnz = 0;
+   std::vector<int> perm, iperm;       // perm[new] = old
+   std::vector<int64_t> cptr;          // permuted lower CSC of the pattern with slot references
+   std::vector<int> crow, cslot;
+   std::vector<int> urow, ucol;        // original COO
+   std::vector<Front> fronts;
+   std::vector<int> order;             // fronts, children before parents
+   std::vector<std::vector<int>> levels;
+   std::vector<double> scale;
+   uint64_t pos = 0, neg = 0, zero = 0;
+   int64_t n2x2 = 0, ndelayed = 0;
+   double nnzL = 0, flops = 0, t_analyse = 0, t_factor = 0, t_solve = 0;
+   double u = 0.01, null_tol = 1e-20;
+   std::string err;
+};
+
+}  // namespace
+
+namespace {
+
+using clk = std::chrono::steady_clock;
+double since(clk::time_point t0) { return std::chrono::duration<double>(clk::now() - t0).count(); }
+
+// ---- symbolic phase (independent of the product's) -----------------------------------------------
+void analyse(Oracle& o, int64_t N, int64_t nnz, const uint64_t* row, const uint64_t* col, const int64_t* user_perm) {
+   const auto t0 = clk::now();
+   o.N = N; o.nnz = nnz;
+   o.urow.resize(nnz); o.ucol.resize(nnz);
+   std::vector<std::vector<int>> adj(N);
+   for (int64_t e = 0; e < nnz; ++e) {
+      if (row[e] >= static_cast<uint64_t>(N) || col[e] >= static_cast<uint64_t>(N) || row[e] > col[e]) throw std::runtime_error("oracle: bad COO entry");
+      o.urow[e] = static_cast<int>(row[e]); o.ucol[e] = static_cast<int>(col[e]);
+      if (row[e] != col[e]) { adj[row[e]].push_back(o.ucol[e]); adj[col[e]].push_back(o.urow[e]); }
+   }
+   for (auto& a : adj) { std::sort(a.begin(), a.end()); a.erase(std::unique(a.begin(), a.end()), a.end()); }
+   std::vector<int> perm(N);
+   if (user_perm != nullptr) {
+      for (int64_t i = 0; i < N; ++i) perm[i] = static_cast<int>(user_perm[i]);
+   } else {
+      std::iota(perm.begin(), perm.end(), 0);
+      std::vector<int64_t> xadj(N + 1, 0), adjncy;
+      for (int64_t i = 0; i < N; ++i) { for (int v : adj[i]) adjncy.push_back(v); xadj[i + 1] = static_cast<int64_t>(adjncy.size()); }
+      if (N > 2 && !adjncy.empty()) {
+         std::vector<int64_t> opt(40), mp(N), mip(N);
+         METIS_SetDefaultOptions(opt.data());
+         int64_t n = N;
+         if (METIS_NodeND(&n, xadj.data(), adjncy.data(), nullptr, opt.data(), mp.data(), mip.data()) == 1)
+            for (int64_t i = 0; i < N; ++i) perm[i] = static_cast<int>(mp[i]);
+      }
+   }
+   std::vector<int> ip(N);
+   for (int64_t i = 0; i < N; ++i) ip[perm[i]] = static_cast<int>(i);
+   // elimination tree (Liu 1990)
+   std::vector<int> parent(N, -1), anc(N, -1);
+   for (int j = 0; j < N; ++j)
+      for (int v : adj[perm[j]]) {
+         int i = ip[v];
+         while (i != -1 && i < j) { const int nx = anc[i]; anc[i] = j; if (nx == -1) parent[i] = j; i = nx; }
+      }
+   // postorder (children in ascending order), then relabel
+   {
+      std::vector<int> head(N, -1), next(N, -1), post; post.reserve(N);
+      for (int j = static_cast<int>(N) - 1; j >= 0; --j) if (parent[j] != -1) { next[j] = head[parent[j]]; head[parent[j]] = j; }
+      std::vector<int> st;
+      for (int r = 0; r < N; ++r) {
+         if (parent[r] != -1) continue;
+         st.push_back(r);
+         while (!st.empty()) {
+            const int p = st.back(), c = head[p];
+            if (c == -1) { st.pop_back(); post.push_back(p); } else { head[p] = next[c]; st.push_back(c); }
+         }
+      }
+      std::vector<int> ipost(N), perm2(N), parent2(N);
+      for (int k = 0; k < N; ++k) ipost[post[k]] = k;
+      for (int k = 0; k < N; ++k) { perm2[k] = perm[post[k]]; parent2[k] = parent[post[k]] == -1 ? -1 : ipost[parent[post[k]]]; }
+      perm.swap(perm2); parent.swap(parent2);
+      for (int64_t i = 0; i < N; ++i) ip[perm[i]] = static_cast<int>(i);
+   }
+   o.perm = perm; o.iperm = ip;
+   // column counts (Gilbert, Ng, Peyton 1994) on the postordered tree
+   std::vector<int> cc(N, 0);
+   {
+      std::vector<int> first(N, -1), maxfirst(N, -1), prevleaf(N, -1), uf(N);
+      for (int k = 0; k < N; ++k) { int j = k; cc[j] = first[j] == -1 ? 1 : 0; for (; j != -1 && first[j] == -1; j = parent[j]) first[j] = k; }
+      std::iota(uf.begin(), uf.end(), 0);
+      for (int j = 0; j < N; ++j) {
+         if (parent[j] != -1) --cc[parent[j]];
+         for (int v : adj[perm[j]]) {
+            const int i = ip[v];
+            if (i <= j || first[j] <= maxfirst[i]) continue;
+            maxfirst[i] = first[j];
+            const int jp = prevleaf[i];
+            prevleaf[i] = j;
+            ++cc[j];
+            if (jp != -1) {
+               int q = jp;
+               while (q != uf[q]) q = uf[q];
+               for (int s = jp; s != q;) { const int sp = uf[s]; uf[s] = q; s = sp; }
+               --cc[q];
+            }
+         }
+         if (parent[j] != -1) uf[j] = parent[j];
+      }
+      for (int j = 0; j < N; ++j) if (parent[j] != -1) cc[parent[j]] += cc[j];
+   }
+   // fundamental supernodes, then merge short chains (last child only: numbering stays contiguous)
+   std::vector<int> nchild(N, 0);
+   for (int j = 0; j < N; ++j) if (parent[j] != -1) ++nchild[parent[j]];
+   std::vector<int> sfirst;
+   for (int j = 0; j < N; ++j) {
+      bool glue = j > 0 && parent[j - 1] == j && nchild[j] == 1 && cc[j - 1] == cc[j] + 1;
+      if (!glue && j > 0 && parent[j - 1] == j && !sfirst.empty()) {
+         // relaxed: previous supernode is a child chain ending at j-1; glue when the merged block stays small
+         const int k_prev = j - sfirst.back();
+         if (k_prev + 1 <= 24 && cc[j - 1] - 1 <= cc[j] + 8) glue = true;
+      }
+      if (!glue) sfirst.push_back(j);
+   }
+   sfirst.push_back(static_cast<int>(N));
+   const int ns = static_cast<int>(sfirst.size()) - 1;
+   std::vector<int> snof(N);
+   for (int s = 0; s < ns; ++s) for (int j = sfirst[s]; j < sfirst[s + 1]; ++j) snof[j] = s;
+   o.fronts.assign(ns, Front());
+   std::vector<int> mark(N, -1);
+   for (int s = 0; s < ns; ++s) {
+      Front& F = o.fronts[s];
+      F.first = sfirst[s]; F.ncol = sfirst[s + 1] - sfirst[s];
+      const int c1 = sfirst[s + 1];
+      for (int j = F.first; j < c1; ++j)
+         for (int v : adj[perm[j]]) { const int i = ip[v]; if (i >= c1 && mark[i] != s) { mark[i] = s; F.bnd.push_back(i); } }
+      for (int c : F.children)
+         for (int i : o.fronts[c].bnd) if (i >= c1 && mark[i] != s) { mark[i] = s; F.bnd.push_back(i); }
+      std::sort(F.bnd.begin(), F.bnd.end());
+      if (!F.bnd.empty()) { F.parent = snof[F.bnd[0]]; o.fronts[F.parent].children.push_back(s); }
+   }
+   // levels (children before parents) for the threaded numeric phase
+   std::vector<int> lev(ns, 0);
+   int nlev = 0;
+   for (int s = 0; s < ns; ++s) { if (o.fronts[s].parent != -1) lev[o.fronts[s].parent] = std::max(lev[o.fronts[s].parent], lev[s] + 1); }
+   for (int s = 0; s < ns; ++s) nlev = std::max(nlev, lev[s] + 1);
+   o.levels.assign(nlev, {});
+   for (int s = 0; s < ns; ++s) o.levels[lev[s]].push_back(s);
+   // permuted lower-triangular CSC with references to the COO slots (duplicates kept)
+   o.cptr.assign(N + 1, 0);
+   for (int64_t e = 0; e < nnz; ++e) ++o.cptr[std::min(ip[o.urow[e]], ip[o.ucol[e]]) + 1];
+   for (int64_t j = 0; j < N; ++j) o.cptr[j + 1] += o.cptr[j];
+   o.crow.resize(nnz); o.cslot.resize(nnz);
+   std::vector<int64_t> fill(o.cptr.begin(), o.cptr.end() - 1);
+   for (int64_t e = 0; e < nnz; ++e) {
+      const int a = ip[o.urow[e]], b = ip[o.ucol[e]];
+      const int64_t p = fill[std::min(a, b)]++;
+      o.crow[p] = std::max(a, b); o.cslot[p] = static_cast<int>(e);
+   }
+   o.nnzL = 0; o.flops = 0;
+   for (const Front& F : o.fronts) {
+      const double k = F.ncol, r = static_cast<double>(F.bnd.size());
+      o.nnzL += k * (k + r) - k * (k - 1) / 2; o.flops += k * k * k / 3 + k * k * r + k * r * r;
+   }
+   o.t_analyse = since(t0);
+}
+
+}  // namespace
+
+namespace {
+
+// ---- numeric phase: multifrontal LDL^T, threshold pivoting, delayed pivots -----------------------
+struct Work {
+   std::vector<int> loc;
+   std::vector<double> A, W;
+};
+
+inline double& lower(double* A, int nf, int i, int j) { return (i >= j) ? A[i + static_cast<size_t>(nf) * j] : A[j + static_cast<size_t>(nf) * i]; }
+
+// symmetric interchange of indices a < b in a lower-stored nf x nf matrix
+void swap_sym(double* A, int nf, int a, int b, std::vector<int>& idx) {
+   if (a == b) return;
+   if (a > b) std::swap(a, b);
+   const size_t ld = static_cast<size_t>(nf);
+   for (int c = 0; c < a; ++c) std::swap(A[a + ld * c], A[b + ld * c]);
+   for (int i = a + 1; i < b; ++i) std::swap(A[i + ld * a], A[b + ld * i]);
+   std::swap(A[a + ld * a], A[b + ld * b]);
+   for (int i = b + 1; i < nf; ++i) std::swap(A[i + ld * a], A[i + ld * b]);
+   std::swap(idx[a], idx[b]);
+}
+
+void factor_front(Oracle& o, int s, const double* val, Work& w) {
+   Front& F = o.fronts[s];
+   const bool is_root = F.parent == -1;
+   F.idx.clear();
+   for (int c : F.children) { const Front& C = o.fronts[c]; F.idx.insert(F.idx.end(), C.cb_idx.begin(), C.cb_idx.begin() + C.ndelay); }
+   for (int j = F.first; j < F.first + F.ncol; ++j) F.idx.push_back(j);
+   const int nfs = static_cast<int>(F.idx.size());
+   F.idx.insert(F.idx.end(), F.bnd.begin(), F.bnd.end());
+   const int nf = static_cast<int>(F.idx.size());
+   F.nf = nf;
+   const size_t ld = static_cast<size_t>(nf);
+   w.A.assign(ld * nf, 0.0);
+   double* A = w.A.data();
+   for (int t = 0; t < nf; ++t) w.loc[F.idx[t]] = t;
+   // original entries of the own columns (equilibrated)
+   for (int j = F.first; j < F.first + F.ncol; ++j) {
+      const int lj = w.loc[j];
+      for (int64_t p = o.cptr[j]; p < o.cptr[j + 1]; ++p) {
+         const int e = o.cslot[p];
+         lower(A, nf, w.loc[o.crow[p]], lj) += val[e] * o.scale[o.urow[e]] * o.scale[o.ucol[e]];
+      }
+   }
+   // extend-add of the children's contribution blocks (delayed pivots included)
+   for (int c : F.children) {
+      Front& C = o.fronts[c];
+      const int ncb = C.ncb;
+      for (int cj = 0; cj < ncb; ++cj) {
+         const int gj = w.loc[C.cb_idx[cj]];
+         const double* col = C.cb.data() + static_cast<size_t>(ncb) * cj;
+         for (int ci = cj; ci < ncb; ++ci) lower(A, nf, w.loc[C.cb_idx[ci]], gj) += col[ci];
+      }
+      std::vector<double>().swap(C.cb);
+   }
+   F.d.assign(nfs, 1.0); F.e.assign(nfs, 0.0); F.ptype.assign(nfs, 0);
+   const int NB = 64;
+   w.W.assign(ld * NB, 0.0);
+   double* W = w.W.data();
+   int ne = 0, active_end = nfs, since_retry = 0;
+   double u = o.u;
+   bool forcing = false;
+   const double tol = o.null_tol;
+   while (true) {
+      while (ne < active_end) {
+         const int bstart = ne, bend = std::min(ne + NB, active_end);
+         int cand = ne;
+         while (cand < bend) {
+            // column maxima of candidate c over the not yet eliminated part of the front
+            const int c = cand;
+            double lam_all = 0.0, lam_fs = 0.0;
+            int r = -1;
+            for (int i = ne; i < nf; ++i) {
+               if (i == c) continue;
+               const double v = std::fabs(lower(A, nf, i, c));
+               if (v > lam_all) lam_all = v;
+               if (i < bend && v > lam_fs) { lam_fs = v; r = i; }
+            }
+            const double acc = A[c + ld * c];
+            int step = 0;
+            if (std::fabs(acc) > tol && std::fabs(acc) >= u * lam_all) {
+               step = 1;
+            } else if (r >= 0 && lam_fs > 0.0) {
+               const double b = lower(A, nf, r, c), dd = A[r + ld * r];
+               const double det = acc * dd - b * b;
+               double lc = 0.0, lr = 0.0;
+               for (int i = ne; i < nf; ++i) {
+                  if (i == c || i == r) continue;
+                  lc = std::max(lc, std::fabs(lower(A, nf, i, c)));
+                  lr = std::max(lr, std::fabs(lower(A, nf, i, r)));
+               }
+               const double g1 = std::fabs(dd) * lc + std::fabs(b) * lr, g2 = std::fabs(b) * lc + std::fabs(acc) * lr;
+               if (std::fabs(det) > tol * tol && std::fabs(b) > tol && u * std::max(g1, g2) <= std::fabs(det)) step = 2;
+            }
+            if (step == 0) { ++cand; continue; }
+            if (step == 1) {
+               swap_sym(A, nf, ne, c, F.idx);
+               const double piv = A[ne + ld * ne];
+               double* wc = W + ld * (ne - bstart);
+               for (int i = ne + 1; i < nf; ++i) { wc[i] = A[i + ld * ne]; A[i + ld * ne] = wc[i] / piv; }
+               for (int j = ne + 1; j < bend; ++j) {
+                  const double wj = wc[j];
+                  if (wj == 0.0) continue;
+                  double* cj = A + ld * j;
+                  const double* lcol = A + ld * ne;
+                  for (int i = j; i < nf; ++i) cj[i] -= lcol[i] * wj;
+               }
+               F.d[ne] = piv; F.e[ne] = 0.0; F.ptype[ne] = 0;
+               ne += 1;
+            } else {
+               int rr = r;
+               swap_sym(A, nf, ne, c, F.idx);
+               if (rr == ne) rr = c;            // the partner sat at position ne and moved to c
+               swap_sym(A, nf, ne + 1, rr, F.idx);
+               const double a = A[ne + ld * ne], b = A[ne + 1 + ld * ne], dd = A[ne + 1 + ld * (ne + 1)];
+               const double det = a * dd - b * b;
+               double* w1 = W + ld * (ne - bstart);
+               double* w2 = w1 + ld;
+               for (int i = ne + 2; i < nf; ++i) {
+                  w1[i] = A[i + ld * ne]; w2[i] = A[i + ld * (ne + 1)];
+                  A[i + ld * ne] = (dd * w1[i] - b * w2[i]) / det;
+                  A[i + ld * (ne + 1)] = (a * w2[i] - b * w1[i]) / det;
+               }
+               w1[ne + 1] = 0.0; w2[ne + 1] = 0.0;
+               A[ne + 1 + ld * ne] = 0.0;
+               for (int j = ne + 2; j < bend; ++j) {
+                  const double x1 = w1[j], x2 = w2[j];
+                  double* cj = A + ld * j;
+                  const double* l1 = A + ld * ne;
+                  const double* l2 = A + ld * (ne + 1);
+                  for (int i = j; i < nf; ++i) cj[i] -= l1[i] * x1 + l2[i] * x2;
+               }
+               F.d[ne] = a; F.d[ne + 1] = dd; F.e[ne] = b; F.e[ne + 1] = 0.0; F.ptype[ne] = 1; F.ptype[ne + 1] = 2;
+               ne += 2;
+            }
+            cand = std::max(cand + 1, ne);   // go on with untested candidates; failed ones are retried in the next block
+         }
+         const int nbw = ne - bstart;
+         if (nbw > 0) {
+            since_retry += nbw;
+            // rank-nbw update of everything right of the block: C -= W * L^T, in 256-column strips (lower part only)
+            for (int c0 = bend; c0 < nf; c0 += 256) {
+               const int c1 = std::min(c0 + 256, nf);
+               gemm_nt_sub(nf - c0, c1 - c0, nbw, W + c0, nf, A + c0 + ld * bstart, nf, A + c0 + ld * c0, nf);
+            }
+            // failed candidates [ne, bend) stay in front of the next block (already up to date)
+         } else {
+            // nothing could be eliminated in this block: set its columns aside and go on
+            const int cnt = bend - ne;
+            for (int t = 0; t < cnt; ++t) { const int a = ne + t, b = active_end - 1 - t; if (a < b) swap_sym(A, nf, a, b, F.idx); }
+            active_end -= cnt;
+         }
+      }
+      if (active_end < nfs && since_retry > 0) { active_end = nfs; since_retry = 0; continue; }   // retry postponed columns
+      if (is_root && ne < nfs && !forcing) { forcing = true; u = 0.0; active_end = nfs; since_retry = 0; continue; }
+      break;
+   }
+   if (is_root) {
+      // what is left at the root has no acceptable pivot even without threshold: null pivots
+      for (int j = ne; j < nfs; ++j) {
+         for (int i = j + 1; i < nf; ++i) A[i + ld * j] = 0.0;
+         F.d[j] = 1.0; F.e[j] = 0.0; F.ptype[j] = 3;
+      }
+      ne = nfs;
+   }
+   F.nelim = ne;
+   F.L.assign(ld * ne, 0.0);
+   for (int j = 0; j < ne; ++j) std::memcpy(F.L.data() + ld * j + j, A + ld * j + j, sizeof(double) * (nf - j));
+   F.d.resize(ne); F.e.resize(ne); F.ptype.resize(ne);
+   F.ncb = nf - ne; F.ndelay = nfs - ne;
+   F.cb_idx.assign(F.idx.begin() + ne, F.idx.end());
+   F.cb.assign(static_cast<size_t>(F.ncb) * F.ncb, 0.0);
+   for (int j = ne; j < nf; ++j) std::memcpy(F.cb.data() + static_cast<size_t>(F.ncb) * (j - ne) + (j - ne), A + ld * j + j, sizeof(double) * (nf - j));
+}
+
+void equilibrate(Oracle& o, const double* val, int sweeps) {
+   const int64_t N = o.N;
+   o.scale.assign(N, 1.0);
+   std::vector<double> m(N);
+   for (int it = 0; it < sweeps; ++it) {
+      std::fill(m.begin(), m.end(), 0.0);
+      for (int64_t e = 0; e < o.nnz; ++e) {
+         const int r = o.urow[e], c = o.ucol[e];
+         const double v = std::fabs(val[e]) * o.scale[r] * o.scale[c];
+         if (v > m[r]) m[r] = v;
+         if (v > m[c]) m[c] = v;
+      }
+      for (int64_t i = 0; i < N; ++i) if (m[i] > 0.0 && std::isfinite(m[i])) o.scale[i] /= std::sqrt(m[i]);
+   }
+}
+
+void factorize(Oracle& o, const double* val, int nthreads) {
+   const auto t0 = clk::now();
+   equilibrate(o, val, 3);
+   if (nthreads < 1) nthreads = 1;
+#ifdef _OPENMP
+   omp_set_num_threads(nthreads);
+#endif
+   std::vector<Work> works(nthreads);
+   for (auto& w : works) w.loc.assign(o.N, -1);
+   for (const auto& level : o.levels) {
+      const int nl = static_cast<int>(level.size());
+      if (nl >= 2 * nthreads && nthreads > 1) {
+         if (g_set_threads != nullptr) g_set_threads(1);
+#pragma omp parallel for schedule(dynamic, 1)
+         for (int t = 0; t < nl; ++t) {
+#ifdef _OPENMP
+            Work& w = works[omp_get_thread_num()];
+#else
+            Work& w = works[0];
+#endif
+            factor_front(o, level[t], val, w);
+         }
+      } else {
+         if (g_set_threads != nullptr) g_set_threads(nthreads);
+         for (int t = 0; t < nl; ++t) factor_front(o, level[t], val, works[0]);
+      }
+   }
+   o.pos = o.neg = o.zero = 0; o.n2x2 = 0; o.ndelayed = 0;
+   for (const Front& F : o.fronts) {
+      o.ndelayed += F.ndelay;
+      for (int j = 0; j < F.nelim; ++j) {
+         if (F.ptype[j] == 0) { if (F.d[j] > 0) ++o.pos; else ++o.neg; }
+         else if (F.ptype[j] == 1) {
+            const double det = F.d[j] * F.d[j + 1] - F.e[j] * F.e[j];
+            if (det < 0) { ++o.pos; ++o.neg; } else if (F.d[j] > 0) o.pos += 2; else o.neg += 2;
+            ++o.n2x2;
+         } else if (F.ptype[j] == 3) ++o.zero;
+      }
+   }
+   o.t_factor = since(t0);
+}
+
+void solve(Oracle& o, const double* rhs, double* x) {
+   const auto t0 = clk::now();
+   const int64_t N = o.N;
+   std::vector<double> y(N), xs;
+   for (int64_t g = 0; g < N; ++g) y[g] = rhs[o.perm[g]] * o.scale[o.perm[g]];
+   const int ns = static_cast<int>(o.fronts.size());
+   for (int s = 0; s < ns; ++s) {
+      const Front& F = o.fronts[s];
+      const int nf = F.nf, ne = F.nelim;
+      xs.resize(nf);
+      for (int t = 0; t < nf; ++t) xs[t] = y[F.idx[t]];
+      for (int j = 0; j < ne; ++j) {
+         const double yj = xs[j];
+         if (yj == 0.0) continue;
+         const double* l = F.L.data() + static_cast<size_t>(nf) * j;
+         for (int i = j + 1; i < nf; ++i) xs[i] -= l[i] * yj;
+      }
+      for (int t = 0; t < nf; ++t) y[F.idx[t]] = xs[t];
+   }
+   for (int s = 0; s < ns; ++s) {
+      const Front& F = o.fronts[s];
+      for (int j = 0; j < F.nelim; ++j) {
+         double& a = y[F.idx[j]];
+         if (F.ptype[j] == 0) a /= F.d[j];
+         else if (F.ptype[j] == 1) {
+            double& b = y[F.idx[j + 1]];
+            const double det = F.d[j] * F.d[j + 1] - F.e[j] * F.e[j];
+            const double y1 = a, y2 = b;
+            a = (F.d[j + 1] * y1 - F.e[j] * y2) / det;
+            b = (F.d[j] * y2 - F.e[j] * y1) / det;
+         } else if (F.ptype[j] == 3) a = 0.0;
+      }
+   }
+   for (int s = ns - 1; s >= 0; --s) {
+      const Front& F = o.fronts[s];
+      const int nf = F.nf, ne = F.nelim;
+      xs.resize(nf);
+      for (int t = 0; t < nf; ++t) xs[t] = y[F.idx[t]];
+      for (int j = ne - 1; j >= 0; --j) {
+         const double* l = F.L.data() + static_cast<size_t>(nf) * j;
+         double acc = xs[j];
+         for (int i = j + 1; i < nf; ++i) acc -= l[i] * xs[i];
+         xs[j] = acc;
+      }
+      for (int j = 0; j < ne; ++j) y[F.idx[j]] = xs[j];
+   }
+   for (int64_t g = 0; g < N; ++g) x[o.perm[g]] = y[g] * o.scale[o.perm[g]];
+   o.t_solve = since(t0);
+}
+
+}  // namespace
+
+extern "C" {
+
+void* oracle_create() { return new Oracle(); }
+void oracle_destroy(void* p) { delete static_cast<Oracle*>(p); }
+const char* oracle_last_error(void* p) { return static_cast<Oracle*>(p)->err.c_str(); }
+
+// path of a shared library exporting cblas_dgemm (optionally with a prefix, e.g. scipy_); returns 1 if bound
+int oracle_set_blas(const char* path, const char* prefix) {
+   void* lib = dlopen(path, RTLD_NOW | RTLD_LOCAL);
+   if (lib == nullptr) return 0;
+   const std::string pre = prefix == nullptr ? "" : prefix;
+   g_dgemm = reinterpret_cast<cblas_dgemm_t>(dlsym(lib, (pre + "cblas_dgemm").c_str()));
+   g_set_threads = reinterpret_cast<set_threads_t>(dlsym(lib, (pre + "openblas_set_num_threads").c_str()));
+   return g_dgemm != nullptr ? 1 : 0;
+}
+
+int oracle_analyse(void* p, int64_t n, int64_t nnz, const uint64_t* row, const uint64_t* col, const int64_t* perm) {
+   Oracle& o = *static_cast<Oracle*>(p);
+   try { analyse(o, n, nnz, row, col, perm); return 0; } catch (const std::exception& e) { o.err = e.what(); return -1; }
+}
+
+int oracle_set_parameters(void* p, double threshold_u, double null_tol) {
+   Oracle& o = *static_cast<Oracle*>(p);
+   if (threshold_u >= 0.0) o.u = threshold_u;
+   if (null_tol >= 0.0) o.null_tol = null_tol;
+   return 0;
+}
+
+int oracle_factorize(void* p, const double* values, int nthreads) {
+   Oracle& o = *static_cast<Oracle*>(p);
+   try { factorize(o, values, nthreads); return 0; } catch (const std::exception& e) { o.err = e.what(); return -1; }
+}
+
+int oracle_inertia(void* p, uint64_t* pos, uint64_t* neg, uint64_t* zero) {
+   const Oracle& o = *static_cast<Oracle*>(p);
+   *pos = o.pos; *neg = o.neg; *zero = o.zero;
+   return 0;
+}
+
+int oracle_solve(void* p, const double* rhs, double* x) {
+   Oracle& o = *static_cast<Oracle*>(p);
+   try { solve(o, rhs, x); return 0; } catch (const std::exception& e) { o.err = e.what(); return -1; }
+}
+
+int oracle_get_permutation(void* p, int64_t* perm) {
+   const Oracle& o = *static_cast<Oracle*>(p);
+   for (int64_t i = 0; i < o.N; ++i) perm[i] = o.perm[i];
+   return 0;
+}
+
+// out[0..9] = nnz(L) estimate, flops estimate, delayed pivots, 2x2 pivots, t_analyse, t_factor, t_solve, fronts, blas bound, threads
+int oracle_stats(void* p, double* out) {
+   const Oracle& o = *static_cast<Oracle*>(p);
+   out[0] = o.nnzL; out[1] = o.flops; out[2] = static_cast<double>(o.ndelayed); out[3] = static_cast<double>(o.n2x2);
+   out[4] = o.t_analyse; out[5] = o.t_factor; out[6] = o.t_solve; out[7] = static_cast<double>(o.fronts.size());
+   out[8] = g_dgemm != nullptr ? 1.0 : 0.0;
+#ifdef _OPENMP
+   out[9] = omp_get_max_threads();
+#else
+   out[9] = 1.0;
+#endif
+   return 0;
+}
+
+}  // extern "C"

@@ -1,0 +1,252 @@
+"""GPU parity tests: the CUDA path through the C ABI against the CPU oracle, the reference's golden
+vectors and size-independent properties.  Integer results (assembly permutation, inertia triple,
+pivot sequence) must be bit-exact; the solution must reach a relative backward error <= 1e-12
+(BASELINE.json north_star)."""
+import json
+from pathlib import Path
+
+import numpy as np
+import pytest
+
+from emulator import EmulatedFactorization, equilibrate
+from helpers import backward_error, inertia_correction_loop, kat_system
+from oracle import oracle as O
+from uno_b200 import B200KKTError, KKTSolver
+from uno_b200 import generators as G
+
+pytestmark = pytest.mark.gpu
+GOLDEN = Path(__file__).resolve().parent / "golden"
+KATS = json.loads((GOLDEN / "reference_kats.json").read_text())
+BERR_TOL = 1e-12    # north_star: relative backward error after refinement
+X_TOL = 1e-4        # agreement with the oracle's solution (the reference's own CI tolerance: runtests_uno_ipopt_mumps.jl:72-73)
+
+
+def gpu_solver(kkt, **opts):
+    s = KKTSolver(device=0, **opts)
+    s.do_symbolic_analysis(kkt.dim, kkt.row, kkt.col, kkt.reg_size, kkt.n if kkt.m else 0)
+    return s
+
+
+def oracle_solver(kkt, values, perm=None, **kw):
+    o = O.OracleSolver(**kw)
+    o.do_symbolic_analysis(kkt.dim, kkt.row, kkt.col, perm)
+    o.do_numerical_factorization(values)
+    return o
+
+
+def test_kat1_solution():
+    e = KATS["kat1_solve"]
+    kkt = kat_system(e)
+    s = gpu_solver(kkt)
+    s.do_numerical_factorization(kkt.val)
+    assert np.max(np.abs(s.solve_indefinite_system(kkt.rhs) - np.array(e["x"]))) <= e["tol"]
+
+
+def test_kat2_inertia():
+    e = KATS["kat2_inertia"]
+    kkt = kat_system(e)
+    s = gpu_solver(kkt)
+    s.do_numerical_factorization(kkt.val)
+    assert list(s.get_inertia()) == e["inertia"]
+    assert s.number_negative_eigenvalues() == 2 and not s.matrix_is_singular() and s.rank() == 5
+
+
+def test_kat3_singular_duplicates():
+    e = KATS["kat3_singular"]
+    kkt = kat_system(e)
+    s = gpu_solver(kkt)
+    s.do_numerical_factorization(kkt.val)
+    assert s.matrix_is_singular() and list(s.get_inertia()) == e["inertia"] and s.rank() == 2
+
+
+CASES = {
+    "ocp2d_k24": lambda: G.ocp_distributed(24, 2, seed=1),
+    "ocp3d_k9": lambda: G.ocp_distributed(9, 3, seed=2),
+    "ocp3d_boundary_k9": lambda: G.ocp_boundary_3d(9, seed=3),
+    "opf_like_b150": lambda: G.opf_like(150, 200, 30, seed=4),
+    "opf_like_b150_reg": lambda: G.opf_like(150, 200, 30, seed=4, delta_w=100.0),
+}
+
+
+@pytest.mark.parametrize("name", sorted(CASES))
+def test_assembly_permutation_bit_exact(name):
+    kkt = CASES[name]()
+    s = gpu_solver(kkt)
+    perm, scat = s.permutation()
+    pool, scale = s.debug_assemble(kkt.val)
+    assert np.array_equal(scale, equilibrate(kkt, kkt.val, 3))
+    ref = np.zeros_like(pool)
+    r, c = kkt.row.astype(np.int64), kkt.col.astype(np.int64)
+    np.add.at(ref, scat, kkt.val * scale[r] * scale[c])     # duplicates summed in ascending slot order
+    assert np.array_equal(pool, ref)
+    # and the destinations really are P K P^T: rebuild the matrix from the pool and compare with scipy
+    plan = s.plan()
+    iperm = np.empty(kkt.dim, dtype=np.int64)
+    iperm[perm] = np.arange(kkt.dim)
+    dense = np.zeros((kkt.dim, kkt.dim))
+    for sn in range(plan["num_fronts"]):
+        k, f, ld, off = plan["k"][sn], plan["f"][sn], plan["ld"][sn], plan["pool_offset"][sn]
+        rows = plan["rows"][plan["rows_off"][sn] : plan["rows_off"][sn + 1]]
+        F = pool[off : off + ld * f].reshape(f, ld).T[:f, :k]
+        for j in range(k):
+            dense[rows[j:], rows[j]] += F[j:, j]
+    dense = dense + np.tril(dense, -1).T
+    A = kkt.to_scipy(kkt.val).toarray() * scale[:, None] * scale[None, :]
+    assert np.allclose(dense, A[np.ix_(perm, perm)], rtol=1e-15, atol=0)
+
+
+@pytest.mark.parametrize("name", sorted(CASES))
+def test_inertia_and_solution_against_oracle(name):
+    kkt = CASES[name]()
+    s = gpu_solver(kkt)
+    s.do_numerical_factorization(kkt.val)
+    perm, _ = s.permutation()
+    for o in (oracle_solver(kkt, kkt.val), oracle_solver(kkt, kkt.val, perm=perm)):     # own METIS ordering, and the GPU's ordering
+        assert tuple(s.get_inertia()) == tuple(o.get_inertia())
+        x, berr = s.solve_indefinite_system(kkt.rhs, return_backward_error=True)
+        assert berr <= BERR_TOL and backward_error(kkt, kkt.val, x) <= BERR_TOL
+        xo = o.solve_indefinite_system(kkt.rhs)
+        assert np.max(np.abs(x - xo)) <= X_TOL * np.max(np.abs(xo))
+
+
+def test_pivot_sequence_matches_plan_emulation():
+    """Same plan, same pivoting rule -> identical pivot types and in-front permutations (integers: bit-exact)."""
+    kkt = G.opf_like(120, 160, 20, seed=9)
+    s = gpu_solver(kkt)
+    s.do_numerical_factorization(kkt.val)
+    perm, scat = s.permutation()
+    emu = EmulatedFactorization(s.plan(), perm, scat, kkt, kkt.val)
+    _, dd, de, pt, lp = s.debug_factor(want_pool=False)
+    assert np.array_equal(pt, emu.ptype) and np.array_equal(lp, emu.lperm)
+    assert tuple(s.get_inertia()) == emu.inertia()
+
+
+def test_refactorize_shifted_equals_full_factorize_bitwise():
+    kkt = G.opf_like(150, 200, 30, seed=5)
+    s = gpu_solver(kkt)
+    s.do_numerical_factorization(kkt.with_regularization(0.0, 0.0))
+    v = kkt.with_regularization(3.7, 1e-8)
+    s.refactorize_shifted(v[: kkt.reg_size])
+    a = s.debug_factor()
+    xa = s.solve_indefinite_system(kkt.rhs)
+    ia = s.get_inertia()
+    s2 = gpu_solver(kkt, use_graph=0)
+    s2.do_numerical_factorization(v)
+    b = s2.debug_factor()
+    assert ia == s2.get_inertia()
+    for u, w in zip(a[1:], b[1:]):
+        assert np.array_equal(u, w)
+    assert np.array_equal(xa, s2.solve_indefinite_system(kkt.rhs))     # graph replay == plain launches, bit for bit
+
+
+def test_factorization_is_deterministic():
+    kkt = G.ocp_distributed(12, 3, seed=6)
+    s = gpu_solver(kkt)
+    s.do_numerical_factorization(kkt.val)
+    a = s.debug_factor()
+    xa = s.solve_indefinite_system(kkt.rhs)
+    s.do_numerical_factorization(kkt.val)
+    b = s.debug_factor()
+    assert all(np.array_equal(u, w) for u, w in zip(a, b))
+    assert np.array_equal(xa, s.solve_indefinite_system(kkt.rhs))
+
+
+def test_inertia_correction_loop_matches_oracle_sequence():
+    """Indefinite Hessian: the caller's loop must see the same verdicts from both solvers, hence the same delta sequence."""
+    kkt = G.opf_like(150, 200, 30, seed=8)
+    s = gpu_solver(kkt)
+    hist_gpu, v_gpu = inertia_correction_loop(s, kkt)
+    o = O.OracleSolver()
+    o.do_symbolic_analysis(kkt.dim, kkt.row, kkt.col)
+    hist_cpu, _ = inertia_correction_loop(o, kkt)
+    assert len(hist_gpu) > 1 and hist_gpu == hist_cpu
+    assert s.get_inertia() == (kkt.n, kkt.m, 0)
+    x, berr = s.solve_indefinite_system(kkt.rhs, return_backward_error=True)
+    assert berr <= BERR_TOL
+    # the loop only changed the regularization slots: the fast path gives the same verdicts
+    s2 = gpu_solver(kkt)
+    state = {"first": True}
+
+    def fact(values):
+        if state["first"]:
+            s2.do_numerical_factorization(values)
+            state["first"] = False
+        else:
+            s2.refactorize_shifted(values[: kkt.reg_size])
+
+    hist_fast, _ = inertia_correction_loop(s2, kkt, factorize=fact)
+    assert hist_fast == hist_gpu
+
+
+def test_rank_deficient_jacobian_triggers_dual_regularization():
+    kkt = G.opf_like(120, 160, 20, seed=7, duplicate_rows=4)
+    s = gpu_solver(kkt)
+    s.do_numerical_factorization(kkt.with_regularization(100.0, 0.0))
+    pos, neg, zero = s.get_inertia()
+    assert zero == 4 and s.matrix_is_singular() and pos + neg + zero == kkt.dim and s.rank() == kkt.dim - 4
+    o = oracle_solver(kkt, kkt.with_regularization(100.0, 0.0), null_tol=1e-12)
+    assert o.get_inertia() == (pos, neg, zero)
+    hist, _ = inertia_correction_loop(s, kkt)
+    assert hist[-1][1] > 0.0 and s.get_inertia() == (kkt.n, kkt.m, 0)
+
+
+def test_two_interleaved_handles_and_reanalysis():
+    # optimality and feasibility IPMs each own a solver (FeasibilityRestoration.cpp:33-34); the pre-solve
+    # re-analyses another pattern on the same instance (Preprocessing.cpp:60)
+    a, b = G.ocp_distributed(10, 2, seed=1), G.opf_like(60, 80, 12, seed=2, delta_w=100.0)
+    sa, sb = gpu_solver(a), gpu_solver(b)
+    sa.do_numerical_factorization(a.val)
+    sb.do_numerical_factorization(b.val)
+    xa = sa.solve_indefinite_system(a.rhs)
+    xb = sb.solve_indefinite_system(b.rhs)
+    assert backward_error(a, a.val, xa) <= BERR_TOL and backward_error(b, b.val, xb) <= BERR_TOL
+    sub = slice(a.reg_size, None)
+    a2 = type(a)("noreg", a.n, a.m, 0, a.row[sub], a.col[sub], a.val[sub], a.rhs)
+    sa.do_symbolic_analysis(a2.dim, a2.row, a2.col, 0, a2.n)
+    with pytest.raises(B200KKTError):
+        sa.solve_indefinite_system(a2.rhs)          # new pattern: the old factors are gone
+    sa.do_numerical_factorization(a2.val)
+    assert sa.get_inertia() == (a.n, a.m, 0)
+    assert backward_error(a2, a2.val, sa.solve_indefinite_system(a2.rhs)) <= BERR_TOL
+    assert backward_error(b, b.val, sb.solve_indefinite_system(b.rhs)) <= BERR_TOL   # the other handle is untouched
+
+
+def test_hessian_only_positive_definite_path():
+    # byrd preset: PrimalRegularization factorizes the Hessian alone (m = 0) and expects (n, 0, 0)
+    rng = np.random.default_rng(3)
+    n = 300
+    import scipy.sparse as sp
+    M = sp.random(n, n, density=0.02, random_state=4, format="coo")
+    M = sp.triu(M + M.T, 1).tocoo()
+    row = np.concatenate([np.arange(n), M.row]).astype(np.uint64)
+    col = np.concatenate([np.arange(n), M.col]).astype(np.uint64)
+    val = np.concatenate([np.zeros(n), M.data])
+    kkt = G.KKTSystem("hess", n, 0, n, row, col, val, rng.standard_normal(n))
+    s = gpu_solver(kkt)
+    s.do_numerical_factorization(kkt.val)
+    assert s.get_inertia() != (n, 0, 0)
+    shift = 1.1 * abs(M).sum(axis=1).max() + abs(M).sum(axis=0).max()
+    s.refactorize_shifted(np.full(n, shift))
+    assert s.get_inertia() == (n, 0, 0)
+    v = kkt.with_regularization(shift, 0.0)
+    assert backward_error(kkt, v, s.solve_indefinite_system(kkt.rhs)) <= BERR_TOL
+
+
+@pytest.mark.parametrize("make,name", [(lambda: G.ocp_distributed(256, 2), "config2"), (lambda: G.ocp_distributed(32, 3), "3d_k32")])
+def test_full_size_properties(make, name):
+    """At BASELINE sizes the oracle is too slow: check structural inertia (convex OCP: exactly (n, m, 0)),
+    backward error, linearity of the solve and refactorization idempotence."""
+    kkt = make()
+    s = gpu_solver(kkt)
+    s.do_numerical_factorization(kkt.val)
+    assert s.get_inertia() == (kkt.n, kkt.m, 0)
+    x1, berr = s.solve_indefinite_system(kkt.rhs, return_backward_error=True)
+    assert berr <= BERR_TOL
+    rng = np.random.default_rng(0)
+    b2 = rng.standard_normal(kkt.dim)
+    x2 = s.solve_indefinite_system(b2)
+    x12 = s.solve_indefinite_system(kkt.rhs + 2.0 * b2)
+    assert backward_error(kkt, kkt.val, x12, kkt.rhs + 2.0 * b2) <= BERR_TOL
+    assert np.max(np.abs(x12 - (x1 + 2.0 * x2))) <= 1e-6 * np.max(np.abs(x12))
+    s.do_numerical_factorization(kkt.val)
+    assert np.array_equal(x1, s.solve_indefinite_system(kkt.rhs))

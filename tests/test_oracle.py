@@ -1,0 +1,93 @@
+"""The CPU oracle against the reference's golden vectors and dense numpy (CPU only)."""
+import json
+from pathlib import Path
+
+import numpy as np
+import pytest
+
+from helpers import backward_error, dense_inertia, kat_system
+from oracle import oracle as O
+from uno_b200 import generators as G
+
+GOLDEN = Path(__file__).resolve().parent / "golden"
+KATS = json.loads((GOLDEN / "reference_kats.json").read_text())
+VECTORS = json.loads((GOLDEN / "oracle_vectors.json").read_text())
+
+
+def oracle_run(kkt, values=None, perm=None, **kw):
+    s = O.OracleSolver(**kw)
+    s.do_symbolic_analysis(kkt.dim, kkt.row, kkt.col, perm)
+    s.do_numerical_factorization(kkt.val if values is None else values)
+    return s
+
+
+def test_kat1_solve_reference_vector():
+    # unotest/functional_tests/MUMPSSolverTests.cpp:11-38 (tolerance 1e-8 there)
+    e = KATS["kat1_solve"]
+    kkt = kat_system(e)
+    x = oracle_run(kkt).solve_indefinite_system(kkt.rhs)
+    assert np.max(np.abs(x - np.array(e["x"]))) <= e["tol"]
+
+
+def test_kat2_inertia_reference_vector():
+    # MUMPSSolverTests.cpp:40-61: inertia (3, 2, 0); eigenvalues in the comment at :86-100
+    e = KATS["kat2_inertia"]
+    kkt = kat_system(e)
+    assert list(oracle_run(kkt).get_inertia()) == e["inertia"]
+    w = np.linalg.eigvalsh(kkt.to_scipy().toarray())
+    assert np.allclose(np.sort(w), np.sort(e["eigenvalues"]), atol=1e-6)
+
+
+def test_kat3_singular_with_duplicates_reference_vector():
+    # MUMPSSolverTests.cpp:63-83: duplicates are summed, matrix_is_singular(), expected inertia (1, 1, 2)
+    e = KATS["kat3_singular"]
+    s = oracle_run(kat_system(e))
+    assert s.matrix_is_singular()
+    assert list(s.get_inertia()) == e["inertia"]
+
+
+@pytest.mark.parametrize("name", sorted(VECTORS))
+def test_oracle_matches_committed_vectors(name):
+    mk = {
+        "ocp2d_k12": lambda: G.ocp_distributed(12, 2, seed=1),
+        "ocp3d_k6": lambda: G.ocp_distributed(6, 3, seed=2),
+        "ocp3d_boundary_k6": lambda: G.ocp_boundary_3d(6, seed=3),
+        "opf_like_b40": lambda: G.opf_like(40, 55, 8, seed=4),
+        "opf_like_b40_reg": lambda: G.opf_like(40, 55, 8, seed=4, delta_w=50.0),
+    }[name]
+    kkt, e = mk(), VECTORS[name]
+    assert (kkt.n, kkt.m, kkt.nnz) == (e["n"], e["m"], e["nnz"])
+    s = oracle_run(kkt)
+    assert list(s.get_inertia()) == e["inertia"]
+    x = s.solve_indefinite_system(kkt.rhs)
+    assert np.allclose(x[:8], e["x_head"], rtol=1e-7, atol=1e-9 * e["x_norm_inf"])
+    assert backward_error(kkt, kkt.val, x) < 1e-13
+
+
+@pytest.mark.parametrize("seed", [0, 1, 2])
+def test_oracle_inertia_against_dense_eigenvalues(seed):
+    kkt = G.opf_like(50, 70, 10, seed=seed)
+    for dw in (0.0, 1.0, 100.0):
+        v = kkt.with_regularization(dw, 1e-8 if dw else 0.0)
+        assert oracle_run(kkt, v).get_inertia() == dense_inertia(kkt.to_scipy(v).toarray())
+
+
+def test_oracle_ordering_independence_and_threads():
+    kkt = G.ocp_distributed(10, 2, seed=5)
+    a = oracle_run(kkt)
+    rng = np.random.default_rng(0)
+    b = oracle_run(kkt, perm=rng.permutation(kkt.dim), threads=4)
+    assert a.get_inertia() == b.get_inertia() == (kkt.n, kkt.m, 0)
+    xa, xb = a.solve_indefinite_system(kkt.rhs), b.solve_indefinite_system(kkt.rhs)
+    assert backward_error(kkt, kkt.val, xa) < 1e-13 and backward_error(kkt, kkt.val, xb) < 1e-13
+
+
+def test_oracle_rank_deficient_jacobian_reports_zero_pivots():
+    kkt = G.opf_like(40, 55, 8, seed=7, duplicate_rows=3)
+    v = kkt.with_regularization(100.0, 0.0)
+    s = oracle_run(kkt, v, null_tol=1e-12)
+    pos, neg, zero = s.get_inertia()
+    assert zero == 3 and pos + neg + zero == kkt.dim
+    # with dual regularization the matrix is nonsingular again and the inertia is (n, m, 0)
+    v = kkt.with_regularization(100.0, 1e-6)
+    assert oracle_run(kkt, v, null_tol=1e-12).get_inertia() == (kkt.n, kkt.m, 0)

@@ -17,7 +17,7 @@ EXPORTED_SYMBOLS = [
     "b200kkt_create", "b200kkt_destroy", "b200kkt_set_option", "b200kkt_set_user_permutation", "b200kkt_analyse",
     "b200kkt_factorize", "b200kkt_refactorize_shifted", "b200kkt_factorize_device", "b200kkt_inertia", "b200kkt_solve",
     "b200kkt_solve_device", "b200kkt_get_permutation", "b200kkt_get_stats", "b200kkt_last_error", "b200kkt_plan_sizes",
-    "b200kkt_plan_fronts", "b200kkt_plan_rows", "b200kkt_debug_assemble", "b200kkt_debug_factor",
+    "b200kkt_plan_fronts", "b200kkt_plan_rows", "b200kkt_debug_assemble", "b200kkt_debug_factor", "b200kkt_get_stream",
 ]
 
 
@@ -31,6 +31,8 @@ class Stats(C.Structure):
         ("t_factor_last", C.c_double), ("t_solve_last", C.c_double),
         ("refine_steps_last", C.c_int64), ("backward_error_last", C.c_double), ("kernel_launches", C.c_int64),
         ("num_null_pivots_last", C.c_int64), ("num_two_by_two_last", C.c_int64),
+        ("t_update_profiled", C.c_double), ("flops_update_profiled", C.c_double), ("n_update_profiled", C.c_int64),
+        ("t_assemble_profiled", C.c_double),
     ]
 
     def as_dict(self):
@@ -65,6 +67,7 @@ def load_library():
     lib.b200kkt_get_stats.argtypes = [H, P(Stats)]
     lib.b200kkt_last_error.argtypes = [H]
     lib.b200kkt_last_error.restype = C.c_char_p
+    lib.b200kkt_get_stream.argtypes = [H, P(C.c_void_p)]
     lib.b200kkt_plan_sizes.argtypes = [H, P(C.c_int64)]
     lib.b200kkt_plan_fronts.argtypes = [H] + [C.c_void_p] * 7
     lib.b200kkt_plan_rows.argtypes = [H, C.c_void_p, C.c_void_p]
@@ -194,6 +197,11 @@ class KKTSolver:
         berr = C.c_double()
         self._check(self._lib.b200kkt_solve_device(self._h, C.c_void_p(rhs_ptr), C.c_void_p(x_ptr), C.byref(berr)), "solve_device")
         return berr.value
+
+    def stream(self) -> int:
+        p = C.c_void_p()
+        self._check(self._lib.b200kkt_get_stream(self._h, C.byref(p)), "get_stream")
+        return int(p.value or 0)
 
     # -- parity hooks ------------------------------------------------------------------------
     def stats(self):

@@ -151,6 +151,7 @@ void upload_plan(b200kkt_handle* h) {
    h->F.woff = dev_upload(h, woff);
    h->d_perm = dev_upload(h, P.perm);
    h->d_batch_list = dev_upload(h, batch_list);
+   h->batch_fronts_host = batch_list;
    h->d_solve_list = dev_upload(h, P.level_fronts);
    h->solve_level_ptr.assign(P.level_ptr.begin(), P.level_ptr.end());
 
@@ -224,7 +225,18 @@ void enqueue_factor(b200kkt_handle* h) {
    L += launch_matrix_inf_norm(h->C, h->d_values, h->d_norms + 0, st);
    // K1 assembly into the zeroed pool
    CK(cudaMemsetAsync(h->W.pool, 0, static_cast<size_t>(P.pool_size) * sizeof(double), st));
+   const bool prof = h->profile_updates != 0 && !h->use_graph;
+   auto prof_begin = [&](double flops, int kind) {
+      b200kkt_handle::ProfiledLaunch p{nullptr, nullptr, flops, kind};
+      CK(cudaEventCreate(&p.a));
+      CK(cudaEventCreate(&p.b));
+      CK(cudaEventRecord(p.a, st));
+      h->profiled.push_back(p);
+   };
+   auto prof_end = [&] { CK(cudaEventRecord(h->profiled.back().b, st)); };
+   if (prof) prof_begin(0.0, 1);
    L += launch_assemble(h->M, h->d_values, cur, h->W.pool, st);
+   if (prof) prof_end();
    // K2-K5 level by level
    for (int l = 0; l < P.nlevels; ++l) {
       for (int bi = h->level_batch_ptr[l]; bi < h->level_batch_ptr[l + 1]; ++bi) {
@@ -243,7 +255,18 @@ void enqueue_factor(b200kkt_handle* h) {
                const int nfu = b.count_k_greater(j0 + NBI);
                if (nfu > 0 && j0 + NBI < J0 + NBO) L += launch_update(h->F, list, nfu, b.pmaxf[nfu - 1], 0, j0, J0, h->W, b.big_tiles, st);
             }
+            const bool prof_this = prof && b.max_f >= 1024;
+            if (prof_this) {
+               double fl = 0.0;
+               for (int t = 0; t < nfP; ++t) {
+                  const int s_id = h->batch_fronts_host[b.begin + t];
+                  const double J1 = std::min(J0 + NBO, P.k[s_id]), rem = P.f[s_id] - J1;
+                  if (rem > 0) fl += 2.0 * (J1 - J0) * rem * (rem + 1.0) * 0.5;
+               }
+               prof_begin(fl, 0);
+            }
             L += launch_update(h->F, list, nfP, b.pmaxf[nfP - 1], 1, 0, J0, h->W, b.big_tiles, st);
+            if (prof_this) prof_end();
          }
       }
    }
@@ -297,6 +320,20 @@ void run_factor(b200kkt_handle* h) {
    float ms = 0.f;
    CK(cudaEventElapsedTime(&ms, h->ev0, h->ev1));
    h->stats.t_factor_last = ms * 1e-3;
+   if (!h->profiled.empty()) {
+      double tu = 0.0, fu = 0.0, ta = 0.0;
+      int64_t nu = 0;
+      for (auto& p : h->profiled) {
+         float pm = 0.f;
+         cudaEventElapsedTime(&pm, p.a, p.b);
+         if (p.kind == 0) { tu += pm * 1e-3; fu += p.flops; ++nu; } else ta += pm * 1e-3;
+         cudaEventDestroy(p.a);
+         cudaEventDestroy(p.b);
+      }
+      h->profiled.clear();
+      h->stats.t_update_profiled = tu; h->stats.flops_update_profiled = fu; h->stats.n_update_profiled = nu;
+      h->stats.t_assemble_profiled = ta;
+   }
    h->inertia[0] = static_cast<uint64_t>(h->h_counters[0]);
    h->inertia[1] = static_cast<uint64_t>(h->h_counters[1]);
    h->inertia[2] = static_cast<uint64_t>(h->h_counters[2]);
@@ -458,6 +495,7 @@ int b200kkt_set_option(b200kkt_handle* h, const char* name, double value) {
    else if (n == "refine_max_steps") h->refine_max_steps = std::max(0, static_cast<int>(value));
    else if (n == "refine_tol") h->refine_tol = value;
    else if (n == "use_graph") h->use_graph = static_cast<int>(value);
+   else if (n == "profile_updates") h->profile_updates = static_cast<int>(value);
    else return fail(h, B200KKT_EINVAL, "unknown option: " + n);
    // numeric options are baked into the captured graph
    if (h->factor_graph != nullptr) { cudaGraphExecDestroy(h->factor_graph); h->factor_graph = nullptr; }
@@ -580,6 +618,12 @@ int b200kkt_get_stats(const b200kkt_handle* h, b200kkt_stats* stats) {
 }
 
 const char* b200kkt_last_error(const b200kkt_handle* h) { return h == nullptr ? "null handle" : h->err.c_str(); }
+
+int b200kkt_get_stream(const b200kkt_handle* h, void** stream) {
+   if (h == nullptr || stream == nullptr) return B200KKT_EINVAL;
+   *stream = static_cast<void*>(h->stream);
+   return B200KKT_OK;
+}
 
 int b200kkt_plan_sizes(const b200kkt_handle* h, int64_t sizes[8]) {
    if (h == nullptr || sizes == nullptr) return B200KKT_EINVAL;

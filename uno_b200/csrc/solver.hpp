@@ -43,11 +43,15 @@ struct b200kkt_handle {
    int refine_max_steps = 6;
    double refine_tol = 1e-15;
    int use_graph = 1;
+   int profile_updates = 0;
+   struct ProfiledLaunch { cudaEvent_t a, b; double flops; int kind; };
+   std::vector<ProfiledLaunch> profiled;
 
    b200kkt::Plan plan;
    bool analysed = false, values_resident = false, factorized = false;
    std::vector<b200kkt::Batch> batches;
    std::vector<int> level_batch_ptr;       // batches grouped by level
+   std::vector<int> batch_fronts_host;     // host copy of d_batch_list
    std::vector<int> solve_level_ptr;       // ranges of d_solve_list per level
 
    cudaStream_t stream = nullptr;
