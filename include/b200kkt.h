@@ -40,7 +40,7 @@ typedef struct b200kkt_stats {
    int64_t n, nnz, reg_size;
    int64_t num_fronts, num_levels, max_front, max_pivots, num_pairs;
    int64_t nnz_factor;         /* sum_s k_s f_s - k_s(k_s-1)/2 */
-   int64_t pool_doubles;       /* device front pool size */
+   int64_t pool_doubles;       /* device factor pool size (sum of ld x k panels) */
    int64_t assembly_distinct;  /* distinct destination slots of the scatter map */
    double flops_factor;        /* sum_s k^3/3 + k^2 r + k r^2 */
    double flops_tensor;        /* k^2 r + k r^2 over fronts with k >= 128 */
@@ -105,9 +105,10 @@ const char* b200kkt_last_error(const b200kkt_handle* h);
 int b200kkt_get_stream(const b200kkt_handle* h, void** stream);
 
 /* Plan getters (integer plan of the symbolic phase).  sizes[0..7] = number of fronts, total row
- * entries, pool doubles, levels, sum of boundary rows, distinct assembly destinations, 0, 0. */
+ * entries, factor-pool doubles, levels, sum of boundary rows, distinct assembly destinations, contribution-block
+ * arena doubles, 0. */
 int b200kkt_plan_sizes(const b200kkt_handle* h, int64_t sizes[8]);
-/* per front (length = number of fronts): pivots k, order f, leading dimension, pool offset,
+/* per front (length = number of fronts): pivots k, order f, leading dimension and pool offset of the ld x k factor panel,
  * parent front (-1 root), level, first pivot column (new numbering).  Any pointer may be NULL. */
 int b200kkt_plan_fronts(const b200kkt_handle* h, int32_t* k, int32_t* f, int32_t* ld, int64_t* pool_offset,
                         int32_t* parent, int32_t* level, int32_t* first_col);

@@ -127,7 +127,8 @@ class EmulatedFactorization:
         self.relmap = [None] * nsn
         for s in range(nsn):
             fs, ks = int(f[s]), int(k[s])
-            F = pool[off[s] : off[s] + ld[s] * fs].reshape(fs, ld[s]).T[:fs, :].copy()   # column-major -> F[row, col]
+            F = np.zeros((fs, fs))
+            F[:, :ks] = pool[off[s] : off[s] + ld[s] * ks].reshape(ks, ld[s]).T[:fs, :]   # ld x k column-major factor panel
             F = np.tril(F) + np.tril(F, -1).T
             for ch in children[s]:
                 Fc = self.fronts[ch]

@@ -87,7 +87,7 @@ def test_assembly_permutation_bit_exact(name):
     for sn in range(plan["num_fronts"]):
         k, f, ld, off = plan["k"][sn], plan["f"][sn], plan["ld"][sn], plan["pool_offset"][sn]
         rows = plan["rows"][plan["rows_off"][sn] : plan["rows_off"][sn + 1]]
-        F = pool[off : off + ld * f].reshape(f, ld).T[:f, :k]
+        F = pool[off : off + ld * k].reshape(k, ld).T[:f, :k]
         for j in range(k):
             dense[rows[j:], rows[j]] += F[j:, j]
     dense = dense + np.tril(dense, -1).T

@@ -61,7 +61,7 @@ def check_plan_invariants(kkt, s):
     nsn = plan["num_fronts"]
     assert k.sum() == n and np.all(k >= 1) and np.all(f >= k) and np.all(ld >= f) and np.all(ld % 4 == 0)
     assert np.all(first == np.concatenate([[0], np.cumsum(k)[:-1]]))
-    assert np.all(off[1:] == off[:-1] + ld[:-1].astype(np.int64) * f[:-1]) and off[-1] + ld[-1] * f[-1] == plan["pool_doubles"]
+    assert np.all(off[1:] == off[:-1] + ld[:-1].astype(np.int64) * k[:-1]) and off[-1] + ld[-1] * k[-1] == plan["pool_doubles"]
     rows_off, rows = plan["rows_off"], plan["rows"]
     for sn in range(nsn):
         r = rows[rows_off[sn] : rows_off[sn + 1]]

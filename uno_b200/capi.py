@@ -220,7 +220,7 @@ class KKTSolver:
         self._check(self._lib.b200kkt_plan_sizes(self._h, sizes), "plan_sizes")
         nsn, nrows = int(sizes[0]), int(sizes[1])
         out = {"num_fronts": nsn, "pool_doubles": int(sizes[2]), "num_levels": int(sizes[3]), "sum_boundary": int(sizes[4]),
-               "assembly_distinct": int(sizes[5])}
+               "assembly_distinct": int(sizes[5]), "cb_arena_doubles": int(sizes[6])}
         i32 = lambda: np.empty(nsn, dtype=np.int32)  # noqa: E731
         k, f, ld, parent, level, first = i32(), i32(), i32(), i32(), i32(), i32()
         off = np.empty(nsn, dtype=np.int64)

@@ -16,6 +16,7 @@ namespace {
 
 constexpr double BK_ALPHA = 0.6403882032022076;   // (1 + sqrt(17)) / 8
 constexpr int PANEL_THREADS = 256;
+constexpr int DIAG_THREADS = 128;
 constexpr int EA_CBW = 16;                        // parent columns owned by one extend-add CTA
 
 __device__ __forceinline__ unsigned long long ordered_bits(double v) {
@@ -107,23 +108,31 @@ __global__ void k_solve_scatter_add(int64_t n, const int* __restrict__ perm, con
 }
 
 // ------------------------------------------------------------------------------------------------
-// K5 extend-add.  CTA (parent, column block) owns EA_CBW parent columns and pulls the matching
-// columns of every child's contribution block, children in ascending order -> no atomics, and the
-// summation order is fixed.
+// K5 prepare: zero the front's contribution block and extend-add the children into the front.
+// CTA (parent, column block) owns EA_CBW parent columns and pulls the matching columns of every
+// child's contribution block, children in ascending order -> no atomics, fixed summation order.
+// Parent column < k lands in the factor panel, column >= k in the parent's contribution block.
 // ------------------------------------------------------------------------------------------------
-__global__ void __launch_bounds__(256) k_extend_add(FrontArrays F, const int* __restrict__ list, double* __restrict__ pool) {
+__global__ void __launch_bounds__(256) k_prepare(FrontArrays F, const int* __restrict__ list, FactorArrays W) {
    const int p = list[blockIdx.x];
-   const int fp = F.f[p];
+   const int fp = F.f[p], kp = F.k[p];
    const int cb0 = blockIdx.y * EA_CBW;
    if (cb0 >= fp) return;
    const int cb1 = min(cb0 + EA_CBW, fp);
-   const int ldp = F.ld[p];
-   double* Ap = pool + F.off[p];
+   const int ldp = F.ld[p], ldcp = F.ldc[p];
+   double* Lp = W.lpool + F.off[p];
+   double* Cp = W.cbpool + F.cboff[p];
    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+   for (int col = max(cb0, kp) + warp; col < cb1; col += 8) {
+      double* dst = Cp + static_cast<int64_t>(ldcp) * (col - kp) - kp;
+      for (int i = col + lane; i < fp; i += 32) dst[i] = 0.0;
+   }
+   if (F.child_ptr[p] == F.child_ptr[p + 1]) return;
+   __syncthreads();
    for (int ci = F.child_ptr[p]; ci < F.child_ptr[p + 1]; ++ci) {
       const int c = F.child_idx[ci];
-      const int kc = F.k[c], ldc = F.ld[c];
-      const int rc = F.f[c] - kc;
+      const int ldcc = F.ldc[c];
+      const int rc = F.f[c] - F.k[c];
       const int* __restrict__ rel = F.relmap + F.rel_off[c];
       // rel is strictly increasing: columns of the child that land in [cb0, cb1) are a contiguous range
       int lo = 0, hi = rc;
@@ -132,10 +141,11 @@ __global__ void __launch_bounds__(256) k_extend_add(FrontArrays F, const int* __
       hi = rc;
       while (lo < hi) { const int mid = (lo + hi) >> 1; if (rel[mid] < cb1) lo = mid + 1; else hi = mid; }
       const int jhi = lo;
-      const double* Ac = pool + F.off[c] + kc + static_cast<int64_t>(ldc) * kc;
+      const double* Ac = W.cbpool + F.cboff[c];
       for (int j = jlo + warp; j < jhi; j += 8) {
-         double* dst = Ap + static_cast<int64_t>(ldp) * rel[j];
-         const double* src = Ac + static_cast<int64_t>(ldc) * j;
+         const int pc = rel[j];
+         double* dst = (pc < kp) ? (Lp + static_cast<int64_t>(ldp) * pc) : (Cp + static_cast<int64_t>(ldcp) * (pc - kp) - kp);
+         const double* src = Ac + static_cast<int64_t>(ldcc) * j;
          for (int i = j + lane; i < rc; i += 32) dst[rel[i]] += src[i];
       }
       __syncthreads();   // next child may touch the same parent entries from another warp
@@ -143,7 +153,7 @@ __global__ void __launch_bounds__(256) k_extend_add(FrontArrays F, const int* __
 }
 
 // ------------------------------------------------------------------------------------------------
-// K3 panel kernel
+// K3 panel kernels
 // ------------------------------------------------------------------------------------------------
 struct BkShared {
    double B[NBI][NBI + 1];   // full symmetric diagonal block; after factorization: strict lower = L11
@@ -252,20 +262,16 @@ __device__ void bk_factor_block(BkShared& S, const int n, const int lane, const 
    }
 }
 
-// grid = (front in batch, row chunk).  Every CTA factors the diagonal block redundantly (same
-// data, same instruction order -> identical results), chunk 0 writes it back.
-__global__ void __launch_bounds__(PANEL_THREADS) k_panel(FrontArrays F, const int* __restrict__ list, const int j0, const int J0,
-                                                         FactorArrays W, const double null_tol) {
+// One CTA per front: factor the NBI x NBI diagonal block at pivot column j0 in place.
+__global__ void __launch_bounds__(DIAG_THREADS) k_diag(FrontArrays F, const int* __restrict__ list, const int j0, FactorArrays W,
+                                                        const double null_tol) {
    __shared__ BkShared S;
    const int s = list[blockIdx.x];
-   const int k = F.k[s], f = F.f[s], ld = F.ld[s];
-   const int nbw = min(NBI, k - j0), j1 = j0 + nbw;
-   const int ibeg = j1 + blockIdx.y * PANEL_THREADS;
-   if (blockIdx.y > 0 && ibeg >= f) return;
-   double* A = W.pool + F.off[s];
-   const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
-
-   for (int idx = tid; idx < NBI * NBI; idx += PANEL_THREADS) {
+   const int k = F.k[s], ld = F.ld[s];
+   const int nbw = min(NBI, k - j0);
+   double* A = W.lpool + F.off[s];
+   const int tid = threadIdx.x;
+   for (int idx = tid; idx < NBI * NBI; idx += DIAG_THREADS) {
       const int r = idx % NBI, c = idx / NBI;
       double v;
       if (r < nbw && c < nbw) {
@@ -276,47 +282,72 @@ __global__ void __launch_bounds__(PANEL_THREADS) k_panel(FrontArrays F, const in
       S.B[r][c] = v;
    }
    __syncthreads();
-   if (warp == 0) bk_factor_block(S, nbw, lane, null_tol);
+   if (tid < 32) bk_factor_block(S, nbw, tid, null_tol);
    __syncthreads();
-
-   if (blockIdx.y == 0) {
-      for (int idx = tid; idx < NBI * NBI; idx += PANEL_THREADS) {
-         const int r = idx % NBI, c = idx / NBI;
-         if (r < nbw && c < nbw && r >= c) A[(j0 + r) + static_cast<int64_t>(ld) * (j0 + c)] = (r == c) ? S.d[c] : S.B[r][c];
-      }
-      if (tid < nbw) {
-         const int q = F.first[s] + j0 + tid;
-         W.dd[q] = S.d[tid];
-         W.de[q] = S.e[tid];
-         W.ptype[q] = S.type[tid];
-         W.lperm[q] = j0 + S.p[tid];
-      }
-      if (tid == 0) W.blkflag[F.first[s] + j0] = S.nontrivial;
+   for (int idx = tid; idx < NBI * NBI; idx += DIAG_THREADS) {
+      const int r = idx % NBI, c = idx / NBI;
+      if (r < nbw && c < nbw && r >= c) A[(j0 + r) + static_cast<int64_t>(ld) * (j0 + c)] = (r == c) ? S.d[c] : S.B[r][c];
    }
+   if (tid < nbw) {
+      const int q = F.first[s] + j0 + tid;
+      W.dd[q] = S.d[tid];
+      W.de[q] = S.e[tid];
+      W.ptype[q] = S.type[tid];
+      W.lperm[q] = j0 + S.p[tid];
+   }
+   if (tid == 0) W.blkflag[F.first[s] + j0] = S.nontrivial;
+}
 
+// grid = (front in batch, row chunk): rows below the diagonal block, one row per thread.
+//   w = a(p) L11^{-T} (a(p): the row's entries in the block's pivot order), l = w D^{-1}
+__global__ void __launch_bounds__(PANEL_THREADS) k_trsm(FrontArrays F, const int* __restrict__ list, const int j0, const int J0,
+                                                        FactorArrays W) {
+   __shared__ double L11[NBI][NBI + 1];
+   __shared__ double sd[NBI], se[NBI];
+   __shared__ int sp[NBI], stype[NBI];
+   const int s = list[blockIdx.x];
+   const int k = F.k[s], f = F.f[s], ld = F.ld[s];
+   const int nbw = min(NBI, k - j0), j1 = j0 + nbw;
+   const int ibeg = j1 + blockIdx.y * PANEL_THREADS;
+   if (ibeg >= f) return;
+   double* A = W.lpool + F.off[s];
+   const int tid = threadIdx.x;
+   for (int idx = tid; idx < NBI * NBI; idx += PANEL_THREADS) {
+      const int r = idx % NBI, c = idx / NBI;
+      L11[r][c] = (r < nbw && c < nbw && r > c) ? A[(j0 + r) + static_cast<int64_t>(ld) * (j0 + c)] : 0.0;
+   }
+   if (tid < NBI) {
+      const int q = F.first[s] + j0 + tid;
+      const bool in = tid < nbw;
+      sd[tid] = in ? W.dd[q] : 1.0;
+      se[tid] = in ? W.de[q] : 0.0;
+      stype[tid] = in ? W.ptype[q] : 0;
+      sp[tid] = in ? (W.lperm[q] - j0) : tid;
+   }
+   __syncthreads();
    const int i = ibeg + tid;
    if (i >= f) return;
    double w[NBI];
 #pragma unroll
-   for (int c = 0; c < NBI; ++c) w[c] = (c < nbw) ? A[i + static_cast<int64_t>(ld) * (j0 + S.p[c])] : 0.0;
+   for (int c = 0; c < NBI; ++c) w[c] = (c < nbw) ? A[i + static_cast<int64_t>(ld) * (j0 + sp[c])] : 0.0;
    // w <- w * L11^{-T}
 #pragma unroll
    for (int c = 1; c < NBI; ++c) {
       double acc = w[c];
 #pragma unroll
-      for (int t = 0; t < c; ++t) acc -= w[t] * S.B[c][t];
+      for (int t = 0; t < c; ++t) acc -= w[t] * L11[c][t];
       w[c] = acc;
    }
    // l = w * D^{-1}
    double l[NBI];
 #pragma unroll
    for (int c = 0; c < NBI; ++c) {
-      const int ty = S.type[c];
+      const int ty = stype[c];
       if (ty == 0) {
-         l[c] = w[c] / S.d[c];
+         l[c] = w[c] / sd[c];
       } else if (ty == 1) {
          if (c + 1 < NBI) {
-            const double a = S.d[c], b = S.e[c], cc = S.d[c + 1];
+            const double a = sd[c], b = se[c], cc = sd[c + 1];
             const double det = a * cc - b * b;
             l[c] = (cc * w[c] - b * w[c + 1]) / det;
             l[c + 1] = (a * w[c + 1] - b * w[c]) / det;
@@ -336,21 +367,28 @@ __global__ void __launch_bounds__(PANEL_THREADS) k_panel(FrontArrays F, const in
    }
 }
 
-// rows j0..j0+nbw of the already computed L columns [0, j0) follow the block's interchanges
-__global__ void __launch_bounds__(256) k_permute_rows(FrontArrays F, const int* __restrict__ list, const int j0, FactorArrays W) {
+// Deferred row interchanges: the rows of an inner block were permuted among themselves by its
+// Bunch-Kaufman; the L columns left of the block must follow.  Blocks touch disjoint rows, so all
+// of them are applied in one launch: grid = (front, inner block, 32-column chunk); one warp moves
+// the 32 rows of the block in one column (lanes along rows: coalesced).
+__global__ void __launch_bounds__(256) k_permute_rows(FrontArrays F, const int* __restrict__ list, FactorArrays W) {
    const int s = list[blockIdx.x];
+   const int k = F.k[s];
+   const int j0 = (blockIdx.y + 1) * NBI;
+   if (j0 >= k) return;
    const int first = F.first[s];
    if (!W.blkflag[first + j0]) return;
-   const int c = blockIdx.y * 256 + threadIdx.x;
-   if (c >= j0) return;
-   const int nbw = min(NBI, F.k[s] - j0);
-   double* colp = W.pool + F.off[s] + static_cast<int64_t>(F.ld[s]) * c + j0;
-   const int* lp = W.lperm + first + j0;
-   double tmp[NBI];
-#pragma unroll
-   for (int t = 0; t < NBI; ++t) if (t < nbw) tmp[t] = colp[lp[t] - j0];
-#pragma unroll
-   for (int t = 0; t < NBI; ++t) if (t < nbw) colp[t] = tmp[t];
+   const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+   const int nbw = min(NBI, k - j0);
+   const int src = (lane < nbw) ? (W.lperm[first + j0 + lane] - j0) : lane;
+   const int ld = F.ld[s];
+   double* A = W.lpool + F.off[s];
+   for (int c = blockIdx.z * 64 + warp; c < min(j0, blockIdx.z * 64 + 64); c += 8) {
+      double* colp = A + static_cast<int64_t>(ld) * c + j0;
+      const double v = (lane < nbw) ? colp[src] : 0.0;
+      __syncwarp();
+      if (lane < nbw) colp[lane] = v;
+   }
 }
 
 // ------------------------------------------------------------------------------------------------
@@ -400,7 +438,10 @@ __global__ void __launch_bounds__(WARPS_M* WARPS_N * 32) k_update(FrontArrays F,
    if (m0 >= f || n0 >= c1) return;
    if (m0 + BM <= n0) return;   // tile entirely above the diagonal
 
-   double* A = W.pool + F.off[s];
+   double* A = W.lpool + F.off[s];
+   // columns >= k of the trailing matrix live in the contribution block (rows and columns shifted by k)
+   const int ldc = F.ldc[s];
+   double* Cb = W.cbpool + F.cboff[s] - k - static_cast<int64_t>(ldc) * k;
    const double* Wp = W.wpool + F.woff[s] + static_cast<int64_t>(ld) * kbeg;   // operand A: rows m, K columns
    const double* Lp = A + static_cast<int64_t>(ld) * (J0 + kbeg);               // operand B: rows n, K columns
 
@@ -472,7 +513,10 @@ __global__ void __launch_bounds__(WARPS_M* WARPS_N * 32) k_update(FrontArrays F,
 #pragma unroll
          for (int h = 0; h < 2; ++h) {
             const int n = n0 + wn0 + b * 8 + 2 * (lane & 3) + h;
-            if (n >= c0 && n < c1 && m >= n) A[m + static_cast<int64_t>(ld) * n] -= acc[a][b][h];
+            if (n >= c0 && n < c1 && m >= n) {
+               double* dst = (n < k) ? (A + m + static_cast<int64_t>(ld) * n) : (Cb + m + static_cast<int64_t>(ldc) * n);
+               *dst -= acc[a][b][h];
+            }
          }
       }
    }
@@ -524,7 +568,7 @@ __global__ void __launch_bounds__(256) k_forward(FrontArrays F, const int* __res
    const int s = list[blockIdx.x];
    const int k = F.k[s], f = F.f[s], ld = F.ld[s], first = F.first[s];
    const int r = f - k;
-   const double* A = W.pool + F.off[s];
+   const double* A = W.lpool + F.off[s];
    double* cb = cpool + F.rel_off[s];
    const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
 
@@ -579,7 +623,7 @@ __global__ void __launch_bounds__(256) k_backward(FrontArrays F, const int* __re
    const int s = list[blockIdx.x];
    const int k = F.k[s], f = F.f[s], ld = F.ld[s], first = F.first[s];
    const int r = f - k;
-   const double* A = W.pool + F.off[s];
+   const double* A = W.lpool + F.off[s];
    double* xb = cpool + F.rel_off[s];
    const int* __restrict__ rows = F.rows + F.rows_off[s];
    double* y = z2 + first;
@@ -633,6 +677,220 @@ __global__ void __launch_bounds__(256) k_backward(FrontArrays F, const int* __re
    for (int j = tid; j < k; j += 256) xg[first + W.lperm[first + j]] = y[j];
 }
 
+// ------------------------------------------------------------------------------------------------
+// K7 for big fronts: many CTAs per front, NBS-wide panel steps (HBM-bound: every L entry is read
+// once per sweep, coalesced along the rows).
+// ------------------------------------------------------------------------------------------------
+constexpr int GATHER_SPAN = 1024;   // parent-local destinations owned by one gather CTA
+
+// v = [rhs pivots ; 0] + sum over children of their boundary vectors.  CTA (front, destination range):
+// children in ascending order, each child hits a destination at most once -> no atomics.
+__global__ void __launch_bounds__(256) k_fwd_big_gather(FrontArrays F, const int* __restrict__ list, double* __restrict__ zg,
+                                                         double* __restrict__ cpool) {
+   const int s = list[blockIdx.x];
+   const int k = F.k[s], f = F.f[s], first = F.first[s];
+   const int d0 = blockIdx.y * GATHER_SPAN;
+   if (d0 >= f) return;
+   const int d1 = min(d0 + GATHER_SPAN, f);
+   double* cb = cpool + F.rel_off[s];
+   const int tid = threadIdx.x;
+   for (int d = max(d0, k) + tid; d < d1; d += 256) cb[d - k] = 0.0;
+   __syncthreads();
+   for (int ci = F.child_ptr[s]; ci < F.child_ptr[s + 1]; ++ci) {
+      const int c = F.child_idx[ci];
+      const int rc = F.f[c] - F.k[c];
+      const int* __restrict__ rel = F.relmap + F.rel_off[c];
+      const double* cc = cpool + F.rel_off[c];
+      int lo = 0, hi = rc;
+      while (lo < hi) { const int mid = (lo + hi) >> 1; if (rel[mid] < d0) lo = mid + 1; else hi = mid; }
+      const int ilo = lo;
+      hi = rc;
+      while (lo < hi) { const int mid = (lo + hi) >> 1; if (rel[mid] < d1) lo = mid + 1; else hi = mid; }
+      const int ihi = lo;
+      for (int i = ilo + tid; i < ihi; i += 256) {
+         const int loc = rel[i];
+         const double v = cc[i];
+         if (loc < k) zg[first + loc] += v; else cb[loc - k] += v;
+      }
+      __syncthreads();
+   }
+}
+
+__global__ void __launch_bounds__(256) k_fwd_big_permute(FrontArrays F, const int* __restrict__ list, FactorArrays W,
+                                                          const double* __restrict__ zg, double* __restrict__ z2) {
+   const int s = list[blockIdx.x];
+   const int j = blockIdx.y * 256 + threadIdx.x;
+   if (j >= F.k[s]) return;
+   const int first = F.first[s];
+   z2[first + j] = zg[first + W.lperm[first + j]];
+}
+
+// One CTA per front: y_P <- L11[P,P]^{-1} y_P for the NBS-wide pivot panel starting at jp.
+__global__ void __launch_bounds__(256) k_fwd_big_diag(FrontArrays F, const int* __restrict__ list, const int jp, FactorArrays W,
+                                                       double* __restrict__ z2) {
+   __shared__ double Ls[NBI][NBI + 1];
+   __shared__ double ys[NBS];
+   const int s = list[blockIdx.x];
+   const int k = F.k[s], ld = F.ld[s];
+   const int nb = min(NBS, k - jp);
+   const double* A = W.lpool + F.off[s];
+   double* y = z2 + F.first[s] + jp;
+   const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+   if (tid < nb) ys[tid] = y[tid];
+   for (int sb = 0; sb * NBI < nb; ++sb) {
+      const int base = sb * NBI;
+      const int nbb = min(NBI, nb - base);
+      for (int idx = tid; idx < NBI * NBI; idx += 256) {
+         const int rr = idx % NBI, c = idx / NBI;
+         Ls[rr][c] = (rr < nbb && c < nbb && rr > c) ? A[(jp + base + rr) + static_cast<int64_t>(ld) * (jp + base + c)] : 0.0;
+      }
+      __syncthreads();
+      if (warp == 0) {
+         double yv = (lane < nbb) ? ys[base + lane] : 0.0;
+         for (int c = 0; c < nbb; ++c) {
+            const double yc = __shfl_sync(0xffffffffu, yv, c);
+            if (lane > c) yv -= Ls[lane][c] * yc;
+         }
+         if (lane < nbb) ys[base + lane] = yv;
+      }
+      __syncthreads();
+      const int i = base + nbb + tid;
+      if (i < nb) {
+         double acc = 0.0;
+         for (int c = 0; c < nbb; ++c) acc += A[(jp + i) + static_cast<int64_t>(ld) * (jp + base + c)] * ys[base + c];
+         ys[i] -= acc;
+      }
+      __syncthreads();
+   }
+   if (tid < nb) y[tid] = ys[tid];
+}
+
+// rows below the panel: v(i) -= L[i, P] . y_P.  CTA = 64 rows x 4 column quarters.
+__global__ void __launch_bounds__(256) k_fwd_big_gemv(FrontArrays F, const int* __restrict__ list, const int jp, FactorArrays W,
+                                                       double* __restrict__ z2, double* __restrict__ cpool) {
+   __shared__ double ys[NBS];
+   __shared__ double red[4][64];
+   const int s = list[blockIdx.x];
+   const int k = F.k[s], f = F.f[s], ld = F.ld[s], first = F.first[s];
+   const int nb = min(NBS, k - jp);
+   const int r0 = jp + nb + blockIdx.y * 64;
+   if (r0 >= f) return;
+   const double* A = W.lpool + F.off[s];
+   const int tid = threadIdx.x;
+   ys[tid] = (tid < nb) ? z2[first + jp + tid] : 0.0;
+   __syncthreads();
+   const int i = r0 + (tid & 63), q = tid >> 6;
+   double acc = 0.0;
+   if (i < f) {
+      const int c1 = min(nb, q * 64 + 64);
+      const double* row = A + i + static_cast<int64_t>(ld) * jp;
+#pragma unroll 4
+      for (int c = q * 64; c < c1; ++c) acc += row[static_cast<int64_t>(ld) * c] * ys[c];
+   }
+   red[q][tid & 63] = acc;
+   __syncthreads();
+   if (q == 0 && i < f) {
+      const double sum = (red[0][tid] + red[1][tid]) + (red[2][tid] + red[3][tid]);
+      if (i < k) z2[first + i] -= sum; else cpool[F.rel_off[s] + (i - k)] -= sum;
+   }
+}
+
+// backward sweep, big fronts: boundary gather + block-diagonal solve
+__global__ void __launch_bounds__(256) k_bwd_big_begin(FrontArrays F, const int* __restrict__ list, FactorArrays W, double* __restrict__ z2,
+                                                        const double* __restrict__ xg, double* __restrict__ cpool) {
+   const int s = list[blockIdx.x];
+   const int k = F.k[s], f = F.f[s], first = F.first[s];
+   const int idx = blockIdx.y * 256 + threadIdx.x;
+   if (idx >= f) return;
+   if (idx >= k) {
+      cpool[F.rel_off[s] + (idx - k)] = xg[F.rows[F.rows_off[s] + idx]];
+      return;
+   }
+   const int q = first + idx;
+   const int ty = W.ptype[q];
+   double* y = z2 + q;
+   if (ty == 0) {
+      y[0] = y[0] / W.dd[q];
+   } else if (ty == 1) {
+      const double a = W.dd[q], b = W.de[q], c = W.dd[q + 1];
+      const double det = a * c - b * b;
+      const double y1 = y[0], y2 = y[1];
+      y[0] = (c * y1 - b * y2) / det;
+      y[1] = (a * y2 - b * y1) / det;
+   } else if (ty == 3) {
+      y[0] = 0.0;
+   }
+}
+
+// y(c) -= sum_{i below the panel} L[i, c] x(i) for the panel columns c.  CTA = 8 columns, one warp each.
+__global__ void __launch_bounds__(256) k_bwd_big_gemv(FrontArrays F, const int* __restrict__ list, const int jp, FactorArrays W,
+                                                       double* __restrict__ z2, const double* __restrict__ cpool) {
+   const int s = list[blockIdx.x];
+   const int k = F.k[s], f = F.f[s], ld = F.ld[s], first = F.first[s];
+   const int nb = min(NBS, k - jp);
+   const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+   const int c = blockIdx.y * 8 + warp;
+   if (c >= nb) return;
+   const double* col = W.lpool + F.off[s] + static_cast<int64_t>(ld) * (jp + c);
+   const double* y = z2 + first;
+   const double* xb = cpool + F.rel_off[s] - k;
+   double acc = 0.0;
+   for (int i = jp + nb + lane; i < f; i += 32) acc += col[i] * ((i < k) ? y[i] : xb[i]);
+   for (int o = 16; o; o >>= 1) acc += __shfl_xor_sync(0xffffffffu, acc, o);
+   if (lane == 0) z2[first + jp + c] -= acc;
+}
+
+// One CTA per front: x_P <- L11[P,P]^{-T} y_P, sub-blocks from last to first.
+__global__ void __launch_bounds__(256) k_bwd_big_diag(FrontArrays F, const int* __restrict__ list, const int jp, FactorArrays W,
+                                                       double* __restrict__ z2) {
+   __shared__ double Ls[NBI][NBI + 1];
+   __shared__ double ys[NBS];
+   const int s = list[blockIdx.x];
+   const int k = F.k[s], ld = F.ld[s];
+   const int nb = min(NBS, k - jp);
+   const double* A = W.lpool + F.off[s];
+   double* y = z2 + F.first[s] + jp;
+   const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+   if (tid < nb) ys[tid] = y[tid];
+   const int nsb = (nb + NBI - 1) / NBI;
+   for (int sb = nsb - 1; sb >= 0; --sb) {
+      const int base = sb * NBI;
+      const int nbb = min(NBI, nb - base);
+      for (int idx = tid; idx < NBI * NBI; idx += 256) {
+         const int rr = idx % NBI, c = idx / NBI;
+         Ls[rr][c] = (rr < nbb && c < nbb && rr > c) ? A[(jp + base + rr) + static_cast<int64_t>(ld) * (jp + base + c)] : 0.0;
+      }
+      __syncthreads();
+      if (warp == 0) {
+         double yv = (lane < nbb) ? ys[base + lane] : 0.0;
+         for (int c = nbb - 1; c >= 0; --c) {
+            const double yc = __shfl_sync(0xffffffffu, yv, c);
+            if (lane < c) yv -= Ls[c][lane] * yc;
+         }
+         if (lane < nbb) ys[base + lane] = yv;
+      }
+      __syncthreads();
+      // earlier columns of the panel: y(c) -= sum_t L[base+t, c] x(base+t)
+      if (tid < base) {
+         const double* col = A + (jp + base) + static_cast<int64_t>(ld) * (jp + tid);
+         double acc = 0.0;
+         for (int t = 0; t < nbb; ++t) acc += col[t] * ys[base + t];
+         ys[tid] -= acc;
+      }
+      __syncthreads();
+   }
+   if (tid < nb) y[tid] = ys[tid];
+}
+
+__global__ void __launch_bounds__(256) k_bwd_big_scatter(FrontArrays F, const int* __restrict__ list, FactorArrays W,
+                                                          const double* __restrict__ z2, double* __restrict__ xg) {
+   const int s = list[blockIdx.x];
+   const int j = blockIdx.y * 256 + threadIdx.x;
+   if (j >= F.k[s]) return;
+   const int first = F.first[s];
+   xg[first + W.lperm[first + j]] = z2[first + j];
+}
+
 inline int grid1d(int64_t n, int threads) { return static_cast<int>((n + threads - 1) / threads); }
 
 }  // namespace
@@ -662,27 +920,34 @@ int launch_assemble(const AssemblyArrays& M, const double* values, const double*
    return 1;
 }
 
-int launch_extend_add(const FrontArrays& F, const int* d_list, int nfronts, int max_f, double* pool, cudaStream_t st) {
+int launch_prepare(const FrontArrays& F, const int* d_list, int nfronts, int max_f, const FactorArrays& W, cudaStream_t st) {
    if (nfronts <= 0) return 0;
    dim3 grid(nfronts, (max_f + EA_CBW - 1) / EA_CBW);
-   k_extend_add<<<grid, 256, 0, st>>>(F, d_list, pool);
+   k_prepare<<<grid, 256, 0, st>>>(F, d_list, W);
    return 1;
 }
 
-int launch_panel(const FrontArrays& F, const int* d_list, int nfronts, int max_f, int j0, int J0, const FactorArrays& W, double null_tol,
-                 cudaStream_t st) {
+int launch_diag(const FrontArrays& F, const int* d_list, int nfronts, int j0, const FactorArrays& W, double null_tol, cudaStream_t st) {
    if (nfronts <= 0) return 0;
-   int chunks = (max_f - j0 + PANEL_THREADS - 1) / PANEL_THREADS;
-   if (chunks < 1) chunks = 1;
-   dim3 grid(nfronts, chunks);
-   k_panel<<<grid, PANEL_THREADS, 0, st>>>(F, d_list, j0, J0, W, null_tol);
+   k_diag<<<nfronts, DIAG_THREADS, 0, st>>>(F, d_list, j0, W, null_tol);
    return 1;
 }
 
-int launch_permute_rows(const FrontArrays& F, const int* d_list, int nfronts, int j0, const FactorArrays& W, cudaStream_t st) {
-   if (nfronts <= 0 || j0 <= 0) return 0;
-   dim3 grid(nfronts, (j0 + 255) / 256);
-   k_permute_rows<<<grid, 256, 0, st>>>(F, d_list, j0, W);
+int launch_trsm(const FrontArrays& F, const int* d_list, int nfronts, int max_f, int j0, int J0, const FactorArrays& W, cudaStream_t st) {
+   if (nfronts <= 0) return 0;
+   // a front of the list has k > j0, hence at least min(NBI, k - j0) >= 1 block columns: rows start at j0 + 1 at the earliest
+   const int chunks = (max_f - (j0 + 1) + PANEL_THREADS - 1) / PANEL_THREADS;
+   if (chunks < 1) return 0;
+   dim3 grid(nfronts, chunks);
+   k_trsm<<<grid, PANEL_THREADS, 0, st>>>(F, d_list, j0, J0, W);
+   return 1;
+}
+
+int launch_permute_rows(const FrontArrays& F, const int* d_list, int nfronts, int max_k, const FactorArrays& W, cudaStream_t st) {
+   if (nfronts <= 0 || max_k <= NBI) return 0;
+   const int nblocks = (max_k + NBI - 1) / NBI - 1;   // inner blocks 1 .. last
+   dim3 grid(nfronts, nblocks, (max_k + 63) / 64);
+   k_permute_rows<<<grid, 256, 0, st>>>(F, d_list, W);
    return 1;
 }
 
@@ -733,6 +998,68 @@ int launch_backward_level(const FrontArrays& F, const int* d_list, int nfronts, 
                           cudaStream_t st) {
    if (nfronts <= 0) return 0;
    k_backward<<<nfronts, 256, 0, st>>>(F, d_list, W, z2, xg, cpool);
+   return 1;
+}
+
+int launch_fwd_big_gather(const FrontArrays& F, const int* d_list, int nfronts, int max_f, const FactorArrays&, double* zg, double*,
+                          double* cpool, cudaStream_t st) {
+   if (nfronts <= 0) return 0;
+   dim3 grid(nfronts, (max_f + GATHER_SPAN - 1) / GATHER_SPAN);
+   k_fwd_big_gather<<<grid, 256, 0, st>>>(F, d_list, zg, cpool);
+   return 1;
+}
+
+int launch_fwd_big_permute(const FrontArrays& F, const int* d_list, int nfronts, int max_k, const FactorArrays& W, const double* zg,
+                           double* z2, cudaStream_t st) {
+   if (nfronts <= 0) return 0;
+   dim3 grid(nfronts, (max_k + 255) / 256);
+   k_fwd_big_permute<<<grid, 256, 0, st>>>(F, d_list, W, zg, z2);
+   return 1;
+}
+
+int launch_fwd_big_diag(const FrontArrays& F, const int* d_list, int nfronts, int jp, const FactorArrays& W, double* z2, cudaStream_t st) {
+   if (nfronts <= 0) return 0;
+   k_fwd_big_diag<<<nfronts, 256, 0, st>>>(F, d_list, jp, W, z2);
+   return 1;
+}
+
+int launch_fwd_big_gemv(const FrontArrays& F, const int* d_list, int nfronts, int max_f, int jp, const FactorArrays& W, double* z2,
+                        double* cpool, cudaStream_t st) {
+   if (nfronts <= 0) return 0;
+   const int chunks = (max_f - (jp + 1) + 63) / 64;
+   if (chunks < 1) return 0;
+   dim3 grid(nfronts, chunks);
+   k_fwd_big_gemv<<<grid, 256, 0, st>>>(F, d_list, jp, W, z2, cpool);
+   return 1;
+}
+
+int launch_bwd_big_begin(const FrontArrays& F, const int* d_list, int nfronts, int max_f, const FactorArrays& W, double* z2,
+                         const double* xg, double* cpool, cudaStream_t st) {
+   if (nfronts <= 0) return 0;
+   dim3 grid(nfronts, (max_f + 255) / 256);
+   k_bwd_big_begin<<<grid, 256, 0, st>>>(F, d_list, W, z2, xg, cpool);
+   return 1;
+}
+
+int launch_bwd_big_gemv(const FrontArrays& F, const int* d_list, int nfronts, int jp, const FactorArrays& W, double* z2,
+                        const double* cpool, cudaStream_t st) {
+   if (nfronts <= 0) return 0;
+   dim3 grid(nfronts, NBS / 8);
+   k_bwd_big_gemv<<<grid, 256, 0, st>>>(F, d_list, jp, W, z2, cpool);
+   return 1;
+}
+
+int launch_bwd_big_diag(const FrontArrays& F, const int* d_list, int nfronts, int jp, const FactorArrays& W, double* z2, cudaStream_t st) {
+   if (nfronts <= 0) return 0;
+   k_bwd_big_diag<<<nfronts, 256, 0, st>>>(F, d_list, jp, W, z2);
+   return 1;
+}
+
+int launch_bwd_big_scatter(const FrontArrays& F, const int* d_list, int nfronts, int max_k, const FactorArrays& W, const double* z2,
+                           double* xg, cudaStream_t st) {
+   if (nfronts <= 0) return 0;
+   dim3 grid(nfronts, (max_k + 255) / 256);
+   k_bwd_big_scatter<<<grid, 256, 0, st>>>(F, d_list, W, z2, xg);
    return 1;
 }
 

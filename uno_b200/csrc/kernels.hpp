@@ -8,13 +8,16 @@ namespace b200kkt {
 
 constexpr int NBI = 32;    // inner block: pivot search window of the in-front Bunch-Kaufman
 constexpr int NBO = 256;   // outer panel: K of the trailing FP64 tensor-core update
+constexpr int NBS = 256;   // panel width of the multi-CTA triangular solves
 
 // device-resident integer plan (SoA over fronts)
 struct FrontArrays {
-   const int64_t* off;        // pool offset
+   const int64_t* off;        // factor panel offset in lpool (ld x k, column-major, rows = all f front rows)
    const int* k;              // pivots
    const int* f;              // front order
-   const int* ld;             // leading dimension
+   const int* ld;             // leading dimension of the factor panel
+   const int64_t* cboff;      // contribution block offset in cbpool (ldc x r, lower triangle used)
+   const int* ldc;
    const int* first;          // first pivot column (new numbering)
    const int64_t* rows_off;
    const int* rows;
@@ -42,8 +45,9 @@ struct CsrArrays {
 };
 
 struct FactorArrays {
-   double* pool;
-   double* wpool;
+   double* lpool;    // factor panels
+   double* cbpool;   // contribution-block arena
+   double* wpool;    // W = L*D panels of the level being factorized
    double* dd;       // D diagonal, per pivot position (new numbering + in-front pivoting)
    double* de;       // D off-diagonal of 2x2 blocks (stored at the first column of the pair)
    int* ptype;       // 0: 1x1, 1/2: first/second column of a 2x2, 3: null pivot (row/column dropped)
@@ -55,16 +59,17 @@ struct FactorArrays {
 int launch_scale_sweep(const CsrArrays& A, const double* values, const double* sc_in, double* sc_out, cudaStream_t st);
 int launch_fill(double* p, int64_t n, double v, cudaStream_t st);
 int launch_matrix_inf_norm(const CsrArrays& A, const double* values, unsigned long long* out_bits, cudaStream_t st);
-// K1 assembly: scatter COO values (scaled) into the zeroed front pool, duplicates summed in slot order
-int launch_assemble(const AssemblyArrays& M, const double* values, const double* scale, double* pool, cudaStream_t st);
+// K1 assembly: scatter COO values (scaled) into the zeroed factor pool, duplicates summed in slot order
+int launch_assemble(const AssemblyArrays& M, const double* values, const double* scale, double* lpool, cudaStream_t st);
 
-// K5 extend-add of all children into the fronts of one level
-int launch_extend_add(const FrontArrays& F, const int* d_list, int nfronts, int max_f, double* pool, cudaStream_t st);
-// K3 panel: Bunch-Kaufman on the NBI x NBI diagonal block at pivot column j0 + triangular solve of
-// the rows below it; writes L in place and W = L*D into the W panel
-int launch_panel(const FrontArrays& F, const int* d_list, int nfronts, int max_f, int j0, int J0, const FactorArrays& W,
-                 double null_tol, cudaStream_t st);
-int launch_permute_rows(const FrontArrays& F, const int* d_list, int nfronts, int j0, const FactorArrays& W, cudaStream_t st);
+// K5: zero the contribution blocks of the listed fronts and extend-add all their children into them
+int launch_prepare(const FrontArrays& F, const int* d_list, int nfronts, int max_f, const FactorArrays& W, cudaStream_t st);
+// K3 panel step at pivot column j0: (a) Bunch-Kaufman on the NBI x NBI diagonal block, in place;
+// (b) triangular solve of the rows below it: writes L in place and W = L*D into the W panel
+int launch_diag(const FrontArrays& F, const int* d_list, int nfronts, int j0, const FactorArrays& W, double null_tol, cudaStream_t st);
+int launch_trsm(const FrontArrays& F, const int* d_list, int nfronts, int max_f, int j0, int J0, const FactorArrays& W, cudaStream_t st);
+// rows of the L columns left of each inner block follow the block's interchanges (all blocks at once)
+int launch_permute_rows(const FrontArrays& F, const int* d_list, int nfronts, int max_k, const FactorArrays& W, cudaStream_t st);
 // K4 Schur-complement update C -= W * L^T with FP64 tensor-core MMA.
 // mode 0: inside the outer panel (after inner block j0); mode 1: trailing matrix after outer panel J0.
 int launch_update(const FrontArrays& F, const int* d_list, int nfronts, int max_f, int mode, int j0, int J0,
@@ -73,11 +78,26 @@ int init_kernel_attributes();
 // K6 inertia from the D blocks: counters[0..4] = positive, negative, zero, number of 2x2, unused
 int launch_inertia(int64_t n, const FactorArrays& W, int* counters, cudaStream_t st);
 
-// K7 solves: one level at a time
+// K7 solves, one level at a time.  Small fronts: one CTA per front.
 int launch_forward_level(const FrontArrays& F, const int* d_list, int nfronts, const FactorArrays& W, double* zg, double* z2,
                          double* cpool, cudaStream_t st);
 int launch_backward_level(const FrontArrays& F, const int* d_list, int nfronts, const FactorArrays& W, double* z2, double* xg,
                           double* cpool, cudaStream_t st);
+// Big fronts: many CTAs per front, NBS-wide panel steps.
+int launch_fwd_big_gather(const FrontArrays& F, const int* d_list, int nfronts, int max_f, const FactorArrays& W, double* zg, double* z2,
+                          double* cpool, cudaStream_t st);
+int launch_fwd_big_permute(const FrontArrays& F, const int* d_list, int nfronts, int max_k, const FactorArrays& W, const double* zg,
+                           double* z2, cudaStream_t st);
+int launch_fwd_big_diag(const FrontArrays& F, const int* d_list, int nfronts, int jp, const FactorArrays& W, double* z2, cudaStream_t st);
+int launch_fwd_big_gemv(const FrontArrays& F, const int* d_list, int nfronts, int max_f, int jp, const FactorArrays& W, double* z2,
+                        double* cpool, cudaStream_t st);
+int launch_bwd_big_begin(const FrontArrays& F, const int* d_list, int nfronts, int max_f, const FactorArrays& W, double* z2,
+                         const double* xg, double* cpool, cudaStream_t st);
+int launch_bwd_big_gemv(const FrontArrays& F, const int* d_list, int nfronts, int jp, const FactorArrays& W, double* z2,
+                        const double* cpool, cudaStream_t st);
+int launch_bwd_big_diag(const FrontArrays& F, const int* d_list, int nfronts, int jp, const FactorArrays& W, double* z2, cudaStream_t st);
+int launch_bwd_big_scatter(const FrontArrays& F, const int* d_list, int nfronts, int max_k, const FactorArrays& W, const double* z2,
+                           double* xg, cudaStream_t st);
 // permute+scale in, scale+permute out (accumulating into x)
 int launch_solve_gather(int64_t n, const int* perm, const double* scale, const double* r, double* zg, cudaStream_t st);
 int launch_solve_scatter_add(int64_t n, const int* perm, const double* scale, const double* xg, double* x, cudaStream_t st);

@@ -35,8 +35,10 @@ struct Plan {
    std::vector<int32_t> sn_of;      // N, by new index
 
    // per front
-   std::vector<int32_t> k, f, ld;   // pivots, front order, leading dimension (f rounded up to 4)
-   std::vector<int64_t> front_off;  // offset of the ld x f column-major front in the pool (doubles)
+   std::vector<int32_t> k, f, ld;   // pivots, front order, leading dimension of the factor panel (f rounded up to 4)
+   std::vector<int64_t> front_off;  // offset of the ld x k column-major factor panel [L11; L21] in the factor pool (doubles)
+   std::vector<int32_t> ldc;        // leading dimension of the r x r contribution block (r = f - k rounded up to 4)
+   std::vector<int64_t> cb_off;     // offset of the contribution block in the transient arena (lifetime: own level .. parent's level)
    std::vector<int64_t> rows_off;   // nsn+1, into rows
    std::vector<int32_t> rows;       // front row structure in new numbering; first k entries are the pivots
    std::vector<int32_t> parent;     // supernodal parent (-1 for roots)
@@ -46,7 +48,8 @@ struct Plan {
    std::vector<int32_t> level;                    // per front; leaves are 0
    std::vector<int32_t> level_ptr, level_fronts;  // fronts grouped by level, big fronts first
 
-   int64_t pool_size = 0;           // doubles
+   int64_t pool_size = 0;           // factor pool, doubles: sum ld*k
+   int64_t cb_pool_size = 0;        // contribution-block arena, doubles (peak of the level-order schedule)
 
    // Assembly ("assembly permutation"): COO slot -> pool offset, and the same map grouped by
    // destination so that duplicates are summed in ascending slot order without atomics.

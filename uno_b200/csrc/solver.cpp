@@ -113,6 +113,7 @@ void build_batches(b200kkt_handle* h, std::vector<int>& batch_list, std::vector<
             b.pmaxf.push_back(b.max_f);
             b.max_k = std::max(b.max_k, P.k[s]);
             if (P.child_ptr[s + 1] > P.child_ptr[s]) b.has_children = true;
+            if (P.f[s] > P.k[s]) b.has_cb = true;
             woff[s] = level_w;
             level_w += static_cast<int64_t>(P.ld[s]) * std::min(NBO, (P.k[s] + 3) & ~3);
             ++i;
@@ -138,6 +139,8 @@ void upload_plan(b200kkt_handle* h) {
    h->F.k = dev_upload(h, P.k);
    h->F.f = dev_upload(h, P.f);
    h->F.ld = dev_upload(h, P.ld);
+   h->F.cboff = dev_upload(h, P.cb_off);
+   h->F.ldc = dev_upload(h, P.ldc);
    {
       std::vector<int32_t> first(P.sn_first.begin(), P.sn_first.end() - 1);
       h->F.first = dev_upload(h, first);
@@ -152,8 +155,35 @@ void upload_plan(b200kkt_handle* h) {
    h->d_perm = dev_upload(h, P.perm);
    h->d_batch_list = dev_upload(h, batch_list);
    h->batch_fronts_host = batch_list;
-   h->d_solve_list = dev_upload(h, P.level_fronts);
-   h->solve_level_ptr.assign(P.level_ptr.begin(), P.level_ptr.end());
+   {
+      // solve schedule: per level small fronts first, then big fronts by descending pivot count
+      std::vector<int> solve_list;
+      solve_list.reserve(static_cast<size_t>(P.nsn));
+      h->solve_levels.assign(static_cast<size_t>(P.nlevels), b200kkt_handle::SolveLevel());
+      std::vector<int> big;
+      for (int l = 0; l < P.nlevels; ++l) {
+         b200kkt_handle::SolveLevel& SL = h->solve_levels[l];
+         SL.small_begin = static_cast<int>(solve_list.size());
+         big.clear();
+         for (int t = P.level_ptr[l]; t < P.level_ptr[l + 1]; ++t) {
+            const int s = P.level_fronts[t];
+            const bool is_big = P.k[s] > NBS || static_cast<int64_t>(P.f[s]) * P.k[s] > 98304;
+            if (is_big) big.push_back(s); else solve_list.push_back(s);
+         }
+         SL.small_count = static_cast<int>(solve_list.size()) - SL.small_begin;
+         std::stable_sort(big.begin(), big.end(), [&](int a, int b) { return P.k[a] > P.k[b]; });
+         SL.big_begin = static_cast<int>(solve_list.size());
+         SL.big_count = static_cast<int>(big.size());
+         for (int s : big) {
+            solve_list.push_back(s);
+            SL.big_k.push_back(P.k[s]);
+            SL.big_max_f = std::max(SL.big_max_f, P.f[s]);
+            SL.big_max_k = std::max(SL.big_max_k, P.k[s]);
+            SL.big_pmaxf.push_back(SL.big_max_f);
+         }
+      }
+      h->d_solve_list = dev_upload(h, solve_list);
+   }
 
    h->M.ndst = static_cast<int64_t>(P.asm_dst.size());
    h->M.dst = dev_upload(h, P.asm_dst);
@@ -167,7 +197,8 @@ void upload_plan(b200kkt_handle* h) {
    h->C.slot = dev_upload(h, P.csr_slot);
 
    const size_t n = static_cast<size_t>(P.N);
-   h->W.pool = dev_alloc<double>(h, static_cast<size_t>(P.pool_size));
+   h->W.lpool = dev_alloc<double>(h, static_cast<size_t>(P.pool_size));
+   h->W.cbpool = dev_alloc<double>(h, static_cast<size_t>(P.cb_pool_size));
    h->W.wpool = dev_alloc<double>(h, static_cast<size_t>(wpool_size));
    h->W.dd = dev_alloc<double>(h, n + 1);
    h->W.de = dev_alloc<double>(h, n + 1);
@@ -223,8 +254,8 @@ void enqueue_factor(b200kkt_handle* h) {
    h->d_scale_final = cur;
    CK(cudaMemsetAsync(h->d_norms, 0, 4 * sizeof(unsigned long long), st));
    L += launch_matrix_inf_norm(h->C, h->d_values, h->d_norms + 0, st);
-   // K1 assembly into the zeroed pool
-   CK(cudaMemsetAsync(h->W.pool, 0, static_cast<size_t>(P.pool_size) * sizeof(double), st));
+   // K1 assembly into the zeroed factor pool
+   CK(cudaMemsetAsync(h->W.lpool, 0, static_cast<size_t>(P.pool_size) * sizeof(double), st));
    const bool prof = h->profile_updates != 0 && !h->use_graph;
    auto prof_begin = [&](double flops, int kind) {
       b200kkt_handle::ProfiledLaunch p{nullptr, nullptr, flops, kind};
@@ -235,22 +266,22 @@ void enqueue_factor(b200kkt_handle* h) {
    };
    auto prof_end = [&] { CK(cudaEventRecord(h->profiled.back().b, st)); };
    if (prof) prof_begin(0.0, 1);
-   L += launch_assemble(h->M, h->d_values, cur, h->W.pool, st);
+   L += launch_assemble(h->M, h->d_values, cur, h->W.lpool, st);
    if (prof) prof_end();
    // K2-K5 level by level
    for (int l = 0; l < P.nlevels; ++l) {
       for (int bi = h->level_batch_ptr[l]; bi < h->level_batch_ptr[l + 1]; ++bi) {
          const Batch& b = h->batches[bi];
          const int* list = h->d_batch_list + b.begin;
-         if (b.has_children) L += launch_extend_add(h->F, list, b.count, b.max_f, h->W.pool, st);
+         if (b.has_cb || b.has_children) L += launch_prepare(h->F, list, b.count, b.max_f, h->W, st);
          for (int J0 = 0; J0 < b.max_k; J0 += NBO) {
             const int nfP = b.count_k_greater(J0);
             const int Jend = std::min(J0 + NBO, b.max_k);
             for (int j0 = J0; j0 < Jend; j0 += NBI) {
                const int nfb = b.count_k_greater(j0);
                const int maxf_b = b.pmaxf[nfb - 1];
-               L += launch_panel(h->F, list, nfb, maxf_b, j0, J0, h->W, h->null_pivot_tol, st);
-               if (j0 > 0) L += launch_permute_rows(h->F, list, nfb, j0, h->W, st);
+               L += launch_diag(h->F, list, nfb, j0, h->W, h->null_pivot_tol, st);
+               L += launch_trsm(h->F, list, nfb, maxf_b, j0, J0, h->W, st);
                // in-panel update only where pivot columns remain right of this block inside the panel
                const int nfu = b.count_k_greater(j0 + NBI);
                if (nfu > 0 && j0 + NBI < J0 + NBO) L += launch_update(h->F, list, nfu, b.pmaxf[nfu - 1], 0, j0, J0, h->W, b.big_tiles, st);
@@ -268,6 +299,7 @@ void enqueue_factor(b200kkt_handle* h) {
             L += launch_update(h->F, list, nfP, b.pmaxf[nfP - 1], 1, 0, J0, h->W, b.big_tiles, st);
             if (prof_this) prof_end();
          }
+         L += launch_permute_rows(h->F, list, b.count_k_greater(NBI), b.max_k, h->W, st);
       }
    }
    // K6 inertia
@@ -344,6 +376,16 @@ void run_factor(b200kkt_handle* h) {
 
 namespace {
 
+// number of entries > j in a descending list
+int count_greater(const std::vector<int>& k, int j) {
+   int lo = 0, hi = static_cast<int>(k.size());
+   while (lo < hi) {
+      const int mid = (lo + hi) >> 1;
+      if (k[mid] > j) lo = mid + 1; else hi = mid;
+   }
+   return lo;
+}
+
 // x = K^{-1} b with iterative refinement; b and x are device pointers (x may alias nothing else)
 void run_solve(b200kkt_handle* h, const double* d_b, double* d_x, double* backward_error) {
    const Plan& P = h->plan;
@@ -360,12 +402,33 @@ void run_solve(b200kkt_handle* h, const double* d_b, double* d_x, double* backwa
    for (int it = 0; it <= h->refine_max_steps; ++it) {
       L += launch_solve_gather(P.N, h->d_perm, h->d_scale_final, h->d_r, h->d_zg, st);
       for (int l = 0; l < P.nlevels; ++l) {
-         const int n = h->solve_level_ptr[l + 1] - h->solve_level_ptr[l];
-         L += launch_forward_level(h->F, h->d_solve_list + h->solve_level_ptr[l], n, h->W, h->d_zg, h->d_z2, h->d_cpool, st);
+         const b200kkt_handle::SolveLevel& SL = h->solve_levels[l];
+         L += launch_forward_level(h->F, h->d_solve_list + SL.small_begin, SL.small_count, h->W, h->d_zg, h->d_z2, h->d_cpool, st);
+         if (SL.big_count > 0) {
+            const int* list = h->d_solve_list + SL.big_begin;
+            L += launch_fwd_big_gather(h->F, list, SL.big_count, SL.big_max_f, h->W, h->d_zg, h->d_z2, h->d_cpool, st);
+            L += launch_fwd_big_permute(h->F, list, SL.big_count, SL.big_max_k, h->W, h->d_zg, h->d_z2, st);
+            for (int jp = 0; jp < SL.big_max_k; jp += NBS) {
+               const int nf = count_greater(SL.big_k, jp);
+               L += launch_fwd_big_diag(h->F, list, nf, jp, h->W, h->d_z2, st);
+               L += launch_fwd_big_gemv(h->F, list, nf, SL.big_pmaxf[nf - 1], jp, h->W, h->d_z2, h->d_cpool, st);
+            }
+         }
       }
       for (int l = P.nlevels - 1; l >= 0; --l) {
-         const int n = h->solve_level_ptr[l + 1] - h->solve_level_ptr[l];
-         L += launch_backward_level(h->F, h->d_solve_list + h->solve_level_ptr[l], n, h->W, h->d_z2, h->d_xg, h->d_cpool, st);
+         const b200kkt_handle::SolveLevel& SL = h->solve_levels[l];
+         L += launch_backward_level(h->F, h->d_solve_list + SL.small_begin, SL.small_count, h->W, h->d_z2, h->d_xg, h->d_cpool, st);
+         if (SL.big_count > 0) {
+            const int* list = h->d_solve_list + SL.big_begin;
+            L += launch_bwd_big_begin(h->F, list, SL.big_count, SL.big_max_f, h->W, h->d_z2, h->d_xg, h->d_cpool, st);
+            const int last = ((SL.big_max_k - 1) / NBS) * NBS;
+            for (int jp = last; jp >= 0; jp -= NBS) {
+               const int nf = count_greater(SL.big_k, jp);
+               L += launch_bwd_big_gemv(h->F, list, nf, jp, h->W, h->d_z2, h->d_cpool, st);
+               L += launch_bwd_big_diag(h->F, list, nf, jp, h->W, h->d_z2, st);
+            }
+            L += launch_bwd_big_scatter(h->F, list, SL.big_count, SL.big_max_k, h->W, h->d_z2, h->d_xg, st);
+         }
       }
       L += launch_solve_scatter_add(P.N, h->d_perm, h->d_scale_final, h->d_xg, d_x, st);
       // K8 residual and backward error
@@ -630,7 +693,7 @@ int b200kkt_plan_sizes(const b200kkt_handle* h, int64_t sizes[8]) {
    if (!h->analysed) return fail(h, B200KKT_EINVAL, "plan getter before analyse");
    const Plan& P = h->plan;
    sizes[0] = P.nsn; sizes[1] = static_cast<int64_t>(P.rows.size()); sizes[2] = P.pool_size; sizes[3] = P.nlevels;
-   sizes[4] = P.sum_r; sizes[5] = static_cast<int64_t>(P.asm_dst.size()); sizes[6] = 0; sizes[7] = 0;
+   sizes[4] = P.sum_r; sizes[5] = static_cast<int64_t>(P.asm_dst.size()); sizes[6] = P.cb_pool_size; sizes[7] = 0;
    return B200KKT_OK;
 }
 
@@ -678,9 +741,9 @@ int b200kkt_debug_assemble(b200kkt_handle* h, const double* values, double* pool
          std::swap(cur, nxt);
       }
       h->d_scale_final = cur;
-      CK(cudaMemsetAsync(h->W.pool, 0, static_cast<size_t>(P.pool_size) * sizeof(double), st));
-      h->launches += launch_assemble(h->M, h->d_values, cur, h->W.pool, st);
-      if (pool_out != nullptr) CK(cudaMemcpyAsync(pool_out, h->W.pool, static_cast<size_t>(P.pool_size) * sizeof(double), cudaMemcpyDeviceToHost, st));
+      CK(cudaMemsetAsync(h->W.lpool, 0, static_cast<size_t>(P.pool_size) * sizeof(double), st));
+      h->launches += launch_assemble(h->M, h->d_values, cur, h->W.lpool, st);
+      if (pool_out != nullptr) CK(cudaMemcpyAsync(pool_out, h->W.lpool, static_cast<size_t>(P.pool_size) * sizeof(double), cudaMemcpyDeviceToHost, st));
       if (scale_out != nullptr) CK(cudaMemcpyAsync(scale_out, cur, static_cast<size_t>(P.N) * sizeof(double), cudaMemcpyDeviceToHost, st));
       CK(cudaStreamSynchronize(st));
       CK(cudaGetLastError());
@@ -695,7 +758,7 @@ int b200kkt_debug_factor(b200kkt_handle* h, double* pool_out, double* d_diag, do
       cudaStream_t st = h->stream;
       CK(cudaSetDevice(h->device));
       const size_t n = static_cast<size_t>(P.N);
-      if (pool_out != nullptr) CK(cudaMemcpyAsync(pool_out, h->W.pool, static_cast<size_t>(P.pool_size) * sizeof(double), cudaMemcpyDeviceToHost, st));
+      if (pool_out != nullptr) CK(cudaMemcpyAsync(pool_out, h->W.lpool, static_cast<size_t>(P.pool_size) * sizeof(double), cudaMemcpyDeviceToHost, st));
       if (d_diag != nullptr) CK(cudaMemcpyAsync(d_diag, h->W.dd, n * sizeof(double), cudaMemcpyDeviceToHost, st));
       if (d_off != nullptr) CK(cudaMemcpyAsync(d_off, h->W.de, n * sizeof(double), cudaMemcpyDeviceToHost, st));
       if (piv_type != nullptr) CK(cudaMemcpyAsync(piv_type, h->W.ptype, n * sizeof(int), cudaMemcpyDeviceToHost, st));

@@ -21,6 +21,7 @@ struct Batch {
    int begin = 0, count = 0;      // range in the device batch list
    int max_f = 0, max_k = 0;
    bool has_children = false;
+   bool has_cb = false;
    bool big_tiles = false;
    std::vector<int> k;            // per front of the batch (descending)
    std::vector<int> pmaxf;        // prefix maximum of f in batch order
@@ -52,7 +53,16 @@ struct b200kkt_handle {
    std::vector<b200kkt::Batch> batches;
    std::vector<int> level_batch_ptr;       // batches grouped by level
    std::vector<int> batch_fronts_host;     // host copy of d_batch_list
-   std::vector<int> solve_level_ptr;       // ranges of d_solve_list per level
+   // solve schedule: per level, a list of small fronts (one CTA each) and a list of big fronts
+   // (k descending; NBS-wide panel steps over many CTAs)
+   struct SolveLevel {
+      int small_begin = 0, small_count = 0;
+      int big_begin = 0, big_count = 0;
+      int big_max_f = 0, big_max_k = 0;
+      std::vector<int> big_k;              // descending
+      std::vector<int> big_pmaxf;          // prefix maximum of f
+   };
+   std::vector<SolveLevel> solve_levels;
 
    cudaStream_t stream = nullptr;
    cudaEvent_t ev0 = nullptr, ev1 = nullptr;

@@ -16,6 +16,7 @@
 #include <algorithm>
 #include <chrono>
 #include <cstring>
+#include <map>
 #include <numeric>
 #include <stdexcept>
 
@@ -514,12 +515,14 @@ void analyse(int64_t N, int64_t nnz, int64_t reg_size, int64_t num_primal, const
                           [&](int32_t a, int32_t b) { return P.f[a] != P.f[b] ? P.f[a] > P.f[b] : P.k[a] > P.k[b]; });
       }
    }
-   // ---- pool layout and work figures ----------------------------------------------------------
+   // ---- factor pool layout and work figures ----------------------------------------------------
    P.front_off.resize(nsn);
+   P.ldc.resize(nsn);
    int64_t off = 0;
    for (int32_t s = 0; s < nsn; ++s) {
       P.front_off[s] = off;
-      off += static_cast<int64_t>(P.ld[s]) * P.f[s];
+      off += static_cast<int64_t>(P.ld[s]) * P.k[s];
+      P.ldc[s] = (P.f[s] - P.k[s] + 3) & ~3;
       const double kd = P.k[s], rd = P.f[s] - P.k[s];
       P.nnz_L += static_cast<int64_t>(P.k[s]) * P.f[s] - static_cast<int64_t>(P.k[s]) * (P.k[s] - 1) / 2;
       const double fl = kd * kd * kd / 3.0 + kd * kd * rd + kd * rd * rd;
@@ -530,6 +533,63 @@ void analyse(int64_t N, int64_t nnz, int64_t reg_size, int64_t num_primal, const
       P.max_k = std::max(P.max_k, P.k[s]);
    }
    P.pool_size = off;
+   // ---- contribution-block arena: first-fit over the level-order schedule ------------------------
+   // A block lives from the level of its front until the level of its parent (where it is consumed by
+   // the extend-add); the numeric phase runs level by level, so the offsets can be fixed here.
+   {
+      P.cb_off.assign(nsn, 0);
+      std::map<int64_t, int64_t> free_list;   // offset -> size, coalesced
+      int64_t top = 0;
+      auto cb_size = [&](int32_t s) { return static_cast<int64_t>(P.ldc[s]) * (P.f[s] - P.k[s]); };
+      auto alloc = [&](int64_t size) {
+         for (auto it = free_list.begin(); it != free_list.end(); ++it) {
+            if (it->second >= size) {
+               const int64_t o = it->first, rest = it->second - size;
+               free_list.erase(it);
+               if (rest > 0) free_list.emplace(o + size, rest);
+               return o;
+            }
+         }
+         // grow: extend a free block that touches the top, if any
+         if (!free_list.empty()) {
+            auto last = std::prev(free_list.end());
+            if (last->first + last->second == top) {
+               const int64_t o = last->first;
+               free_list.erase(last);
+               top = o + size;
+               return o;
+            }
+         }
+         const int64_t o = top;
+         top += size;
+         return o;
+      };
+      auto release = [&](int64_t o, int64_t size) {
+         auto it = free_list.emplace(o, size).first;
+         auto nx = std::next(it);
+         if (nx != free_list.end() && it->first + it->second == nx->first) { it->second += nx->second; free_list.erase(nx); }
+         if (it != free_list.begin()) {
+            auto pv = std::prev(it);
+            if (pv->first + pv->second == it->first) { pv->second += it->second; free_list.erase(it); }
+         }
+      };
+      for (int32_t l = 0; l < P.nlevels; ++l) {
+         for (int32_t t = P.level_ptr[l]; t < P.level_ptr[l + 1]; ++t) {
+            const int32_t s = P.level_fronts[t];
+            const int64_t sz = cb_size(s);
+            if (sz > 0) P.cb_off[s] = alloc(sz);
+         }
+         for (int32_t t = P.level_ptr[l]; t < P.level_ptr[l + 1]; ++t) {
+            const int32_t s = P.level_fronts[t];
+            for (int32_t ci = P.child_ptr[s]; ci < P.child_ptr[s + 1]; ++ci) {
+               const int32_t c = P.child_idx[ci];
+               const int64_t sz = cb_size(c);
+               if (sz > 0) release(P.cb_off[c], sz);
+            }
+         }
+      }
+      P.cb_pool_size = top;
+   }
    const auto t2 = clk::now();
    P.t_symbolic = secs(t1, t2);
 
