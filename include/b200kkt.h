@@ -124,6 +124,10 @@ int b200kkt_debug_assemble(b200kkt_handle* h, const double* values, double* pool
 int b200kkt_debug_factor(b200kkt_handle* h, double* pool_out, double* d_diag, double* d_off, int32_t* piv_type,
                          int32_t* local_perm);
 
+/* Profiling hook: times `reps` launches of the K4 trailing update (FP64 tensor-core Schur update, K = k <= 256)
+ * on one synthetic front of order f; returns seconds and algorithmic flops per launch. */
+int b200kkt_debug_bench_update(int device, int f, int k, int reps, int big_tiles, double* seconds_per_launch, double* flops_per_launch);
+
 #ifdef __cplusplus
 }
 #endif

@@ -155,7 +155,7 @@ def test_factorization_is_deterministic():
 
 def test_inertia_correction_loop_matches_oracle_sequence():
     """Indefinite Hessian: the caller's loop must see the same verdicts from both solvers, hence the same delta sequence."""
-    kkt = G.opf_like(150, 200, 30, seed=8)
+    kkt = G.opf_like(150, 200, 30, seed=8, barrier_exp=(-8.0, 0.0))
     s = gpu_solver(kkt)
     hist_gpu, v_gpu = inertia_correction_loop(s, kkt)
     o = O.OracleSolver()

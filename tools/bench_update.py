@@ -1,0 +1,12 @@
+"""K4 trailing-update microbenchmark through the C ABI hook (run under gpurun)."""
+import ctypes as C, sys
+sys.path.insert(0, ".")
+from uno_b200 import capi
+lib = capi.load_library()
+lib.b200kkt_debug_bench_update.argtypes = [C.c_int, C.c_int, C.c_int, C.c_int, C.c_int, C.POINTER(C.c_double), C.POINTER(C.c_double)]
+sizes = [int(a) for a in sys.argv[1:]] or [2048, 4096, 8192, 12288]
+for f in sizes:
+    for k in (256, 64):
+        s, fl = C.c_double(), C.c_double()
+        rc = lib.b200kkt_debug_bench_update(0, f + k, k, 5, 1, C.byref(s), C.byref(fl))
+        print(f"update r={f} K={k}: rc={rc} {s.value*1e3:.3f} ms  {fl.value/s.value/1e12:.2f} TFLOP/s (lower triangle only)", flush=True)

@@ -466,6 +466,15 @@ __global__ void __launch_bounds__(WARPS_M* WARPS_N * 32) k_update(FrontArrays F,
       }
    };
 
+   // pull the C tile towards L2 while the K loop runs: the epilogue's read-modify-write then hits L2
+   for (int q = tid; q < BN * (BM / 16); q += NT) {
+      const int n = n0 + q / (BM / 16), m = m0 + (q % (BM / 16)) * 16;
+      if (n < c1 && m < f && m + 15 >= n) {
+         const double* pc = (n < k) ? (A + m + static_cast<int64_t>(ld) * n) : (Cb + m + static_cast<int64_t>(ldc) * n);
+         asm volatile("prefetch.global.L2 [%0];" ::"l"(pc));
+      }
+   }
+
    double acc[MF][NF][2];
 #pragma unroll
    for (int a = 0; a < MF; ++a)
@@ -504,6 +513,29 @@ __global__ void __launch_bounds__(WARPS_M* WARPS_N * 32) k_update(FrontArrays F,
    }
    cp_async_wait<0>();
 
+   // Interior tiles (fully inside the region, strictly below the diagonal, on one side of column k):
+   // no per-element predicates, loads batched 2*MF deep so that the read-modify-write is not a chain
+   // of dependent round trips.
+   const bool interior = m0 >= r0 && m0 + BM <= f && n0 >= c0 && n0 + BN <= c1 && m0 >= n0 + BN && (n0 + BN <= k || n0 >= k);
+   if (interior) {
+      double* base;
+      int64_t ldo;
+      if (n0 < k) { base = A; ldo = ld; } else { base = Cb; ldo = ldc; }
+      base += (m0 + wm0 + (lane >> 2)) + ldo * (n0 + wn0 + 2 * (lane & 3));
+#pragma unroll
+      for (int b = 0; b < NF; ++b) {
+         double v[MF][2];
+#pragma unroll
+         for (int a = 0; a < MF; ++a)
+#pragma unroll
+            for (int h = 0; h < 2; ++h) v[a][h] = base[a * 8 + ldo * (b * 8 + h)];
+#pragma unroll
+         for (int a = 0; a < MF; ++a)
+#pragma unroll
+            for (int h = 0; h < 2; ++h) base[a * 8 + ldo * (b * 8 + h)] = v[a][h] - acc[a][b][h];
+      }
+      return;
+   }
 #pragma unroll
    for (int a = 0; a < MF; ++a) {
       const int m = m0 + wm0 + a * 8 + (lane >> 2);

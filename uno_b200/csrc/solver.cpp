@@ -768,3 +768,61 @@ int b200kkt_debug_factor(b200kkt_handle* h, double* pool_out, double* d_diag, do
 }
 
 }  // extern "C"
+
+// ================================================================================================
+// Kernel microbenchmark hook (profiling only): one synthetic front of order f with k pivots, random
+// panel data, times `reps` launches of the K4 trailing update (mode 1, J0 = 0) with CUDA events.
+// ================================================================================================
+extern "C" int b200kkt_debug_bench_update(int device, int f, int k, int reps, int big_tiles, double* seconds_per_launch, double* flops_per_launch) {
+   if (f <= 0 || k <= 0 || k > NBO || k >= f || reps <= 0) return B200KKT_EINVAL;
+   try {
+      CK(cudaSetDevice(device));
+      if (init_kernel_attributes() != 0) return B200KKT_ECUDA;
+      const int ld = (f + 3) & ~3, r = f - k, ldc = (r + 3) & ~3;
+      std::vector<double> hl(static_cast<size_t>(ld) * k), hw(static_cast<size_t>(ld) * NBO);
+      uint64_t sd = 88172645463325252ull;
+      auto rnd = [&] { sd ^= sd << 13; sd ^= sd >> 7; sd ^= sd << 17; return (static_cast<double>(sd >> 11) / 9007199254740992.0) - 0.5; };
+      for (auto& v : hl) v = rnd();
+      for (auto& v : hw) v = rnd();
+      double *lpool, *cbpool, *wpool;
+      CK(cudaMalloc(reinterpret_cast<void**>(&lpool), hl.size() * sizeof(double)));
+      CK(cudaMalloc(reinterpret_cast<void**>(&wpool), hw.size() * sizeof(double)));
+      CK(cudaMalloc(reinterpret_cast<void**>(&cbpool), static_cast<size_t>(ldc) * r * sizeof(double)));
+      CK(cudaMemcpy(lpool, hl.data(), hl.size() * sizeof(double), cudaMemcpyHostToDevice));
+      CK(cudaMemcpy(wpool, hw.data(), hw.size() * sizeof(double), cudaMemcpyHostToDevice));
+      CK(cudaMemset(cbpool, 0, static_cast<size_t>(ldc) * r * sizeof(double)));
+      const int64_t zero64 = 0;
+      const int hk = k, hf = f, hld = ld, hldc = ldc, hlist = 0;
+      int64_t* d64; int* d32;
+      CK(cudaMalloc(reinterpret_cast<void**>(&d64), 8 * sizeof(int64_t)));
+      CK(cudaMalloc(reinterpret_cast<void**>(&d32), 8 * sizeof(int)));
+      CK(cudaMemcpy(d64, &zero64, sizeof(int64_t), cudaMemcpyHostToDevice));
+      const int h32[5] = {hk, hf, hld, hldc, hlist};
+      CK(cudaMemcpy(d32, h32, sizeof(h32), cudaMemcpyHostToDevice));
+      FrontArrays F{};
+      F.off = d64; F.cboff = d64; F.woff = d64;
+      F.k = d32; F.f = d32 + 1; F.ld = d32 + 2; F.ldc = d32 + 3;
+      FactorArrays W{};
+      W.lpool = lpool; W.cbpool = cbpool; W.wpool = wpool;
+      cudaStream_t st;
+      CK(cudaStreamCreate(&st));
+      cudaEvent_t e0, e1;
+      CK(cudaEventCreate(&e0)); CK(cudaEventCreate(&e1));
+      for (int i = 0; i < 2; ++i) launch_update(F, d32 + 4, 1, f, 1, 0, 0, W, big_tiles != 0, st);
+      CK(cudaEventRecord(e0, st));
+      for (int i = 0; i < reps; ++i) launch_update(F, d32 + 4, 1, f, 1, 0, 0, W, big_tiles != 0, st);
+      CK(cudaEventRecord(e1, st));
+      CK(cudaStreamSynchronize(st));
+      CK(cudaGetLastError());
+      float ms = 0.f;
+      CK(cudaEventElapsedTime(&ms, e0, e1));
+      if (seconds_per_launch != nullptr) *seconds_per_launch = ms * 1e-3 / reps;
+      if (flops_per_launch != nullptr) *flops_per_launch = 2.0 * k * (static_cast<double>(r) * (r + 1.0) * 0.5);
+      cudaEventDestroy(e0); cudaEventDestroy(e1); cudaStreamDestroy(st);
+      cudaFree(lpool); cudaFree(wpool); cudaFree(cbpool); cudaFree(d64); cudaFree(d32);
+      return B200KKT_OK;
+   } catch (const CudaError&) {
+      cudaGetLastError();
+      return B200KKT_ECUDA;
+   }
+}

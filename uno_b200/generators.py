@@ -82,9 +82,9 @@ def _laplacian(k: int, dim: int) -> sp.csr_matrix:
     return (h2inv * lap).tocsr()
 
 
-def _barrier_sigma(rng, count):
-    # late-IPM spread of z/(x-l): log-uniform over 16 decades
-    return 10.0 ** rng.uniform(-8.0, 8.0, size=count)
+def _barrier_sigma(rng, count, lo=-8.0, hi=8.0):
+    # late-IPM spread of z/(x-l): log-uniform over 16 decades by default
+    return 10.0 ** rng.uniform(lo, hi, size=count)
 
 
 def ocp_distributed(k: int, dim: int, alpha: float = 1e-3, seed: int = 0) -> KKTSystem:
@@ -123,12 +123,14 @@ def ocp_boundary_3d(k: int, alpha: float = 1e-3, seed: int = 0) -> KKTSystem:
 
 
 def opf_like(buses: int = 10000, branches: int = 13500, gens: int = 2000, seed: int = 0, duplicate_rows: int = 0,
-             delta_w: float = 0.0) -> KKTSystem:
+             delta_w: float = 0.0, curvature: float = 1.0, barrier_exp=(-8.0, 8.0)) -> KKTSystem:
     """AC-OPF-like KKT on a random connected network (config 3).  Variables: (V, theta) per bus,
     (Pg, Qg) per generator, one slack per flow limit (2 per branch).  Constraints: 2 balance rows
     per bus, 2 flow rows per branch.  The Hessian has an indefinite 4x4 block per branch (scaled
     by random multipliers), so the inertia is generally wrong without regularization.
-    duplicate_rows > 0 copies that many constraint rows (rank-deficient Jacobian -> zero pivots)."""
+    duplicate_rows > 0 copies that many constraint rows (rank-deficient Jacobian -> zero pivots);
+    curvature scales the indefinite branch blocks (large values leave negative curvature in the
+    null space of the Jacobian, which the caller's inertia-correction loop has to regularize away)."""
     rng = np.random.default_rng(seed)
     # random spanning tree + extra edges
     parents = np.array([rng.integers(0, i) for i in range(1, buses)], dtype=np.int64)
@@ -156,7 +158,7 @@ def opf_like(buses: int = 10000, branches: int = 13500, gens: int = 2000, seed: 
     for e in range(ne):
         a, b = edges[e]
         vs = np.sort(np.array([iV[a], iV[b], iT[a], iT[b]]))
-        blk = rng.uniform(-1.0, 1.0, size=(4, 4)) * ymul[e]
+        blk = rng.uniform(-1.0, 1.0, size=(4, 4)) * (ymul[e] * curvature)
         for q in range(4):          # column by column, upper triangle
             for p in range(q + 1):
                 hr.append(vs[p]); hc.append(vs[q]); hv.append(blk[p, q])
@@ -169,7 +171,7 @@ def opf_like(buses: int = 10000, branches: int = 13500, gens: int = 2000, seed: 
     # barrier terms on V, Pg, Qg, slacks
     barrier_idx = np.concatenate([iV, iPg, iQg, iS]).astype(np.int64)
     barrier_idx.sort()
-    barrier_val = _barrier_sigma(rng, barrier_idx.size)
+    barrier_val = _barrier_sigma(rng, barrier_idx.size, *barrier_exp)
     # Jacobian
     jr, jc, jv = [], [], []
     inc = [[] for _ in range(nb)]
