@@ -128,6 +128,9 @@ int b200kkt_debug_factor(b200kkt_handle* h, double* pool_out, double* d_diag, do
  * on one synthetic front of order f; returns seconds and algorithmic flops per launch. */
 int b200kkt_debug_bench_update(int device, int f, int k, int reps, int big_tiles, double* seconds_per_launch, double* flops_per_launch);
 
+/* Profiling hook: cycle counters of the panel-kernel phases; returns 0 unless the library was built with -DB200KKT_PHASES. */
+int b200kkt_debug_phase_cycles(unsigned long long* out16, int reset);
+
 #ifdef __cplusplus
 }
 #endif

@@ -2,7 +2,8 @@
 import ctypes as C, sys
 sys.path.insert(0, ".")
 from uno_b200 import capi
-lib = capi.load_library()
+import os
+lib = C.CDLL(os.environ['B200KKT_LIB']) if os.environ.get('B200KKT_LIB') else capi.load_library()
 lib.b200kkt_debug_bench_update.argtypes = [C.c_int, C.c_int, C.c_int, C.c_int, C.c_int, C.POINTER(C.c_double), C.POINTER(C.c_double)]
 sizes = [int(a) for a in sys.argv[1:]] or [2048, 4096, 8192, 12288]
 for f in sizes:

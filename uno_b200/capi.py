@@ -7,11 +7,12 @@ fallback: if the library is missing or the handle has no CUDA device, numeric ca
 from __future__ import annotations
 
 import ctypes as C
+import os
 from pathlib import Path
 
 import numpy as np
 
-_LIB_PATH = Path(__file__).resolve().parent / "lib" / "libb200kkt.so"
+_LIB_PATH = Path(os.environ["B200KKT_LIB"]) if os.environ.get("B200KKT_LIB") else Path(__file__).resolve().parent / "lib" / "libb200kkt.so"   # B200KKT_LIB: instrumented build variants (profiling)
 
 EXPORTED_SYMBOLS = [
     "b200kkt_create", "b200kkt_destroy", "b200kkt_set_option", "b200kkt_set_user_permutation", "b200kkt_analyse",

@@ -146,7 +146,14 @@ __global__ void __launch_bounds__(256) k_prepare(FrontArrays F, const int* __res
          const int pc = rel[j];
          double* dst = (pc < kp) ? (Lp + static_cast<int64_t>(ldp) * pc) : (Cp + static_cast<int64_t>(ldcp) * (pc - kp) - kp);
          const double* src = Ac + static_cast<int64_t>(ldcc) * j;
-         for (int i = j + lane; i < rc; i += 32) dst[rel[i]] += src[i];
+         int i = j + lane;
+         for (; i + 96 < rc; i += 128) {
+            const int r0 = rel[i], r1 = rel[i + 32], r2 = rel[i + 64], r3 = rel[i + 96];
+            const double s0 = src[i], s1 = src[i + 32], s2 = src[i + 64], s3 = src[i + 96];
+            const double d0 = dst[r0], d1 = dst[r1], d2 = dst[r2], d3 = dst[r3];
+            dst[r0] = d0 + s0; dst[r1] = d1 + s1; dst[r2] = d2 + s2; dst[r3] = d3 + s3;
+         }
+         for (; i < rc; i += 32) dst[rel[i]] += src[i];
       }
       __syncthreads();   // next child may touch the same parent entries from another warp
    }
@@ -162,9 +169,25 @@ struct BkShared {
    int nontrivial;
 };
 
+// max over the warp of non-negative doubles (negative inputs count as "absent" and give -1):
+// the IEEE order of non-negative doubles is the order of their bit patterns, so two 32-bit REDUX
+// operations (high words, then low words among the lanes holding the maximal high word) replace
+// a five-step 64-bit shuffle butterfly.
+__device__ __forceinline__ double warp_max(const double v) {
+   const bool present = v >= 0.0;
+   const unsigned hi = present ? static_cast<unsigned>(__double2hiint(v)) + 1u : 0u;   // +1: distinguishes +0.0 from absent
+   const unsigned mhi = __reduce_max_sync(0xffffffffu, hi);
+   if (mhi == 0u) return -1.0;
+   const unsigned lo = (hi == mhi) ? static_cast<unsigned>(__double2loint(v)) : 0u;
+   const unsigned mlo = __reduce_max_sync(0xffffffffu, lo);
+   return __hiloint2double(static_cast<int>(mhi - 1u), static_cast<int>(mlo));
+}
+
 // Bunch-Kaufman (partial pivoting, pivot search confined to this block) by one warp.
 // Null pivots (whole remaining column <= tol) are dropped MUMPS-style: unit pivot, zero column,
-// reported as a zero eigenvalue.
+// reported as a zero eigenvalue.  Lane i owns row i of the block; the rank-1/rank-2 updates read
+// the pivot column(s) and the own row into registers first and store afterwards, so that the
+// shared-memory traffic of one step is pipelined instead of a chain of dependent round trips.
 __device__ void bk_factor_block(BkShared& S, const int n, const int lane, const double tol) {
    S.p[lane] = lane;
    S.d[lane] = 1.0;
@@ -175,15 +198,11 @@ __device__ void bk_factor_block(BkShared& S, const int n, const int lane, const 
    int j = 0;
    while (j < n) {
       const double absajj = fabs(S.B[j][j]);
-      double v = (lane > j && lane < n) ? fabs(S.B[lane][j]) : -1.0;
-      int r = lane;
-      for (int o = 16; o; o >>= 1) {
-         const double v2 = __shfl_xor_sync(0xffffffffu, v, o);
-         const int r2 = __shfl_xor_sync(0xffffffffu, r, o);
-         if (v2 > v || (v2 == v && r2 < r)) { v = v2; r = r2; }
-      }
-      double lam = v;
-      if (lam < 0.0) { lam = 0.0; r = j; }
+      // lambda = largest off-diagonal magnitude of column j, r = its first row
+      const double v = (lane > j && lane < n) ? fabs(S.B[lane][j]) : -1.0;
+      double lam = warp_max(v);
+      int r = j;
+      if (lam >= 0.0) r = __ffs(__ballot_sync(0xffffffffu, v == lam)) - 1; else lam = 0.0;
       int kp = j, step = 1;
       bool isnull = false;
       if (!(fmax(absajj, lam) > tol)) {
@@ -191,9 +210,7 @@ __device__ void bk_factor_block(BkShared& S, const int n, const int lane, const 
       } else if (absajj >= BK_ALPHA * lam) {
          // 1x1 pivot, no interchange
       } else {
-         double s2 = (lane >= j && lane < n && lane != r) ? fabs(S.B[lane][r]) : -1.0;
-         for (int o = 16; o; o >>= 1) s2 = fmax(s2, __shfl_xor_sync(0xffffffffu, s2, o));
-         const double sigma = s2;
+         const double sigma = warp_max((lane >= j && lane < n && lane != r) ? fabs(S.B[lane][r]) : -1.0);
          if (absajj * sigma >= BK_ALPHA * lam * lam) {
             // 1x1 pivot, no interchange
          } else if (fabs(S.B[r][r]) >= BK_ALPHA * sigma) {
@@ -228,28 +245,34 @@ __device__ void bk_factor_block(BkShared& S, const int n, const int lane, const 
             if (lane > j) S.B[lane][j] = 0.0;
             if (lane == 0) { S.d[j] = 1.0; S.e[j] = 0.0; S.type[j] = 3; }
          } else {
-            double li = 0.0;
             const bool act = lane > j && lane < n;
-            if (act) {
-               li = S.B[lane][j] / d;
-               for (int c = j + 1; c < n; ++c) S.B[lane][c] -= li * S.B[c][j];
-            }
+            const double li = S.B[lane][j] / d;
+            double col[NBI], row[NBI];
+#pragma unroll
+            for (int c = 0; c < NBI; ++c) col[c] = S.B[c][j];
+#pragma unroll
+            for (int c = 0; c < NBI; ++c) row[c] = S.B[lane][c];
             __syncwarp();
+#pragma unroll
+            for (int c = 0; c < NBI; ++c) if (act && c > j && c < n) S.B[lane][c] = row[c] - li * col[c];
             if (act) S.B[lane][j] = li;
             if (lane == 0) { S.d[j] = d; S.e[j] = 0.0; S.type[j] = 0; }
          }
       } else {
          const double a = S.B[j][j], b = S.B[j + 1][j], c = S.B[j + 1][j + 1];
          const double det = a * c - b * b;
-         double l1 = 0.0, l2 = 0.0;
          const bool act = lane > j + 1 && lane < n;
-         if (act) {
-            const double w1 = S.B[lane][j], w2 = S.B[lane][j + 1];
-            l1 = (c * w1 - b * w2) / det;
-            l2 = (a * w2 - b * w1) / det;
-            for (int cc = j + 2; cc < n; ++cc) S.B[lane][cc] -= l1 * S.B[cc][j] + l2 * S.B[cc][j + 1];
-         }
+         const double w1 = S.B[lane][j], w2 = S.B[lane][j + 1];
+         const double l1 = (c * w1 - b * w2) / det;
+         const double l2 = (a * w2 - b * w1) / det;
+         double col1[NBI], col2[NBI], row[NBI];
+#pragma unroll
+         for (int cc = 0; cc < NBI; ++cc) { col1[cc] = S.B[cc][j]; col2[cc] = S.B[cc][j + 1]; }
+#pragma unroll
+         for (int cc = 0; cc < NBI; ++cc) row[cc] = S.B[lane][cc];
          __syncwarp();
+#pragma unroll
+         for (int cc = 0; cc < NBI; ++cc) if (act && cc > j + 1 && cc < n) S.B[lane][cc] = row[cc] - (l1 * col1[cc] + l2 * col2[cc]);
          if (act) { S.B[lane][j] = l1; S.B[lane][j + 1] = l2; }
          if (lane == 0) {
             S.B[j + 1][j] = 0.0;
@@ -262,75 +285,10 @@ __device__ void bk_factor_block(BkShared& S, const int n, const int lane, const 
    }
 }
 
-// One CTA per front: factor the NBI x NBI diagonal block at pivot column j0 in place.
-__global__ void __launch_bounds__(DIAG_THREADS) k_diag(FrontArrays F, const int* __restrict__ list, const int j0, FactorArrays W,
-                                                        const double null_tol) {
-   __shared__ BkShared S;
-   const int s = list[blockIdx.x];
-   const int k = F.k[s], ld = F.ld[s];
-   const int nbw = min(NBI, k - j0);
-   double* A = W.lpool + F.off[s];
-   const int tid = threadIdx.x;
-   for (int idx = tid; idx < NBI * NBI; idx += DIAG_THREADS) {
-      const int r = idx % NBI, c = idx / NBI;
-      double v;
-      if (r < nbw && c < nbw) {
-         v = (r >= c) ? A[(j0 + r) + static_cast<int64_t>(ld) * (j0 + c)] : A[(j0 + c) + static_cast<int64_t>(ld) * (j0 + r)];
-      } else {
-         v = (r == c) ? 1.0 : 0.0;
-      }
-      S.B[r][c] = v;
-   }
-   __syncthreads();
-   if (tid < 32) bk_factor_block(S, nbw, tid, null_tol);
-   __syncthreads();
-   for (int idx = tid; idx < NBI * NBI; idx += DIAG_THREADS) {
-      const int r = idx % NBI, c = idx / NBI;
-      if (r < nbw && c < nbw && r >= c) A[(j0 + r) + static_cast<int64_t>(ld) * (j0 + c)] = (r == c) ? S.d[c] : S.B[r][c];
-   }
-   if (tid < nbw) {
-      const int q = F.first[s] + j0 + tid;
-      W.dd[q] = S.d[tid];
-      W.de[q] = S.e[tid];
-      W.ptype[q] = S.type[tid];
-      W.lperm[q] = j0 + S.p[tid];
-   }
-   if (tid == 0) W.blkflag[F.first[s] + j0] = S.nontrivial;
-}
-
-// grid = (front in batch, row chunk): rows below the diagonal block, one row per thread.
-//   w = a(p) L11^{-T} (a(p): the row's entries in the block's pivot order), l = w D^{-1}
-__global__ void __launch_bounds__(PANEL_THREADS) k_trsm(FrontArrays F, const int* __restrict__ list, const int j0, const int J0,
-                                                        FactorArrays W) {
-   __shared__ double L11[NBI][NBI + 1];
-   __shared__ double sd[NBI], se[NBI];
-   __shared__ int sp[NBI], stype[NBI];
-   const int s = list[blockIdx.x];
-   const int k = F.k[s], f = F.f[s], ld = F.ld[s];
-   const int nbw = min(NBI, k - j0), j1 = j0 + nbw;
-   const int ibeg = j1 + blockIdx.y * PANEL_THREADS;
-   if (ibeg >= f) return;
-   double* A = W.lpool + F.off[s];
-   const int tid = threadIdx.x;
-   for (int idx = tid; idx < NBI * NBI; idx += PANEL_THREADS) {
-      const int r = idx % NBI, c = idx / NBI;
-      L11[r][c] = (r < nbw && c < nbw && r > c) ? A[(j0 + r) + static_cast<int64_t>(ld) * (j0 + c)] : 0.0;
-   }
-   if (tid < NBI) {
-      const int q = F.first[s] + j0 + tid;
-      const bool in = tid < nbw;
-      sd[tid] = in ? W.dd[q] : 1.0;
-      se[tid] = in ? W.de[q] : 0.0;
-      stype[tid] = in ? W.ptype[q] : 0;
-      sp[tid] = in ? (W.lperm[q] - j0) : tid;
-   }
-   __syncthreads();
-   const int i = ibeg + tid;
-   if (i >= f) return;
-   double w[NBI];
-#pragma unroll
-   for (int c = 0; c < NBI; ++c) w[c] = (c < nbw) ? A[i + static_cast<int64_t>(ld) * (j0 + sp[c])] : 0.0;
-   // w <- w * L11^{-T}
+// Row-per-thread triangular solve against one factored NBI x NBI diagonal block held in shared memory:
+//   w <- w L11^{-T},  l = w D^{-1}   (null pivots: both zero)
+__device__ __forceinline__ void row_trsm(double (&w)[NBI], double (&l)[NBI], const double (*L11)[NBI + 1], const double* sd, const double* se,
+                                         const int* stype) {
 #pragma unroll
    for (int c = 1; c < NBI; ++c) {
       double acc = w[c];
@@ -338,8 +296,6 @@ __global__ void __launch_bounds__(PANEL_THREADS) k_trsm(FrontArrays F, const int
       for (int t = 0; t < c; ++t) acc -= w[t] * L11[c][t];
       w[c] = acc;
    }
-   // l = w * D^{-1}
-   double l[NBI];
 #pragma unroll
    for (int c = 0; c < NBI; ++c) {
       const int ty = stype[c];
@@ -357,14 +313,278 @@ __global__ void __launch_bounds__(PANEL_THREADS) k_trsm(FrontArrays F, const int
          w[c] = 0.0;
       }
    }
-   double* Wp = W.wpool + F.woff[s];
+}
+
+#ifdef B200KKT_PHASES
+__device__ unsigned long long g_phase[16];
+#define PHASE_BEGIN() long long ph_t = clock64()
+#define PHASE_MARK(i) do { if (threadIdx.x == 0) { const long long ph_n = clock64(); atomicAdd(g_phase + (i), static_cast<unsigned long long>(ph_n - ph_t)); ph_t = ph_n; } } while (0)
+#else
+#define PHASE_BEGIN() do {} while (0)
+#define PHASE_MARK(i) do {} while (0)
+#endif
+
+constexpr int DP_THREADS = 256;
+constexpr int DP_LD = NBO - NBI + 4;   // rows of the in-panel W/L staging (c-major: [c][row])
+constexpr int DP_SMEM = static_cast<int>(sizeof(BkShared)) + 2 * NBI * DP_LD * static_cast<int>(sizeof(double));
+
+// Kernel A of a panel step.  One CTA per front factors the NBO x NBO diagonal block of the outer
+// panel starting at pivot column J0, in place: for every NBI-wide inner block Bunch-Kaufman (one
+// warp), interchanges applied to the panel's earlier L columns, triangular solve of the rows of the
+// diagonal block below it, and the update of the rest of the diagonal block.  Rows below the
+// diagonal block are left to k_trsmpanel.
+__global__ void __launch_bounds__(DP_THREADS) k_diagpanel(FrontArrays F, const int* __restrict__ list, const int J0, FactorArrays W,
+                                                          const double null_tol) {
+   extern __shared__ __align__(16) unsigned char dp_smem[];
+   BkShared& S = *reinterpret_cast<BkShared*>(dp_smem);
+   double* Ws = reinterpret_cast<double*>(dp_smem + ((sizeof(BkShared) + 15) & ~size_t(15)));   // [c][row]
+   double* Ls = Ws + NBI * DP_LD;
+   const int s = list[blockIdx.x];
+   const int k = F.k[s], ld = F.ld[s], first = F.first[s];
+   const int J1 = min(J0 + NBO, k);
+   double* A = W.lpool + F.off[s];
+   const int tid = threadIdx.x;
+   PHASE_BEGIN();
+   for (int j0 = J0; j0 < J1; j0 += NBI) {
+      const int nbw = min(NBI, k - j0), j1 = j0 + nbw;
+      for (int idx = tid; idx < NBI * NBI; idx += DP_THREADS) {
+         const int r = idx % NBI, c = idx / NBI;
+         double v;
+         if (r < nbw && c < nbw) {
+            v = (r >= c) ? A[(j0 + r) + static_cast<int64_t>(ld) * (j0 + c)] : A[(j0 + c) + static_cast<int64_t>(ld) * (j0 + r)];
+         } else {
+            v = (r == c) ? 1.0 : 0.0;
+         }
+         S.B[r][c] = v;
+      }
+      __syncthreads();
+      PHASE_MARK(0);
+      if (tid < 32) bk_factor_block(S, nbw, tid, null_tol);
+      __syncthreads();
+      PHASE_MARK(1);
+      for (int idx = tid; idx < NBI * NBI; idx += DP_THREADS) {
+         const int r = idx % NBI, c = idx / NBI;
+         if (r < nbw && c < nbw && r >= c) A[(j0 + r) + static_cast<int64_t>(ld) * (j0 + c)] = (r == c) ? S.d[c] : S.B[r][c];
+      }
+      if (tid < nbw) {
+         const int q = first + j0 + tid;
+         W.dd[q] = S.d[tid];
+         W.de[q] = S.e[tid];
+         W.ptype[q] = S.type[tid];
+         W.lperm[q] = j0 + S.p[tid];
+      }
+      if (tid == 0) W.blkflag[first + j0] = S.nontrivial;
+      // the block's interchanges on the panel's earlier L columns (columns left of J0 are deferred)
+      if (S.nontrivial) {
+         for (int c = J0 + tid; c < j0; c += DP_THREADS) {
+            double* colp = A + static_cast<int64_t>(ld) * c + j0;
+            double tmp[NBI];
 #pragma unroll
-   for (int c = 0; c < NBI; ++c) {
-      if (c < nbw) {
-         A[i + static_cast<int64_t>(ld) * (j0 + c)] = l[c];
-         Wp[i + static_cast<int64_t>(ld) * (j0 - J0 + c)] = w[c];
+            for (int t = 0; t < NBI; ++t) tmp[t] = (t < nbw) ? colp[S.p[t]] : 0.0;
+#pragma unroll
+            for (int t = 0; t < NBI; ++t) if (t < nbw) colp[t] = tmp[t];
+         }
+      }
+      __syncthreads();
+      PHASE_MARK(2);
+      const int rem = J1 - j1;   // rows (and columns) of the diagonal block still to be factored
+      if (rem <= 0) break;
+      // rows of the diagonal block below the inner block
+      if (tid < rem) {
+         const int i = j1 + tid;
+         double w[NBI], l[NBI];
+#pragma unroll
+         for (int c = 0; c < NBI; ++c) w[c] = (c < nbw) ? A[i + static_cast<int64_t>(ld) * (j0 + S.p[c])] : 0.0;
+         row_trsm(w, l, S.B, S.d, S.e, S.type);
+#pragma unroll
+         for (int c = 0; c < NBI; ++c) {
+            if (c < nbw) A[i + static_cast<int64_t>(ld) * (j0 + c)] = l[c];
+            Ws[c * DP_LD + tid] = (c < nbw) ? w[c] : 0.0;
+            Ls[c * DP_LD + tid] = (c < nbw) ? l[c] : 0.0;
+         }
+      } else if (tid < ((rem + 3) & ~3)) {
+#pragma unroll
+         for (int c = 0; c < NBI; ++c) { Ws[c * DP_LD + tid] = 0.0; Ls[c * DP_LD + tid] = 0.0; }
+      }
+      __syncthreads();
+      PHASE_MARK(3);
+      // A[m, n] -= sum_c W[m, c] L[n, c] on the lower triangle of the remaining diagonal block, 4 x 4 tiles
+      const int T = (rem + 3) >> 2;
+      for (int idx = tid; idx < T * T; idx += DP_THREADS) {
+         const int tm = idx / T, tn = idx % T;
+         if (tn > tm) continue;
+         double acc[4][4];
+#pragma unroll
+         for (int a = 0; a < 4; ++a)
+#pragma unroll
+            for (int b = 0; b < 4; ++b) acc[a][b] = 0.0;
+#pragma unroll 4
+         for (int c = 0; c < NBI; ++c) {
+            const double2 w01 = *reinterpret_cast<const double2*>(Ws + c * DP_LD + tm * 4);
+            const double2 w23 = *reinterpret_cast<const double2*>(Ws + c * DP_LD + tm * 4 + 2);
+            const double2 l01 = *reinterpret_cast<const double2*>(Ls + c * DP_LD + tn * 4);
+            const double2 l23 = *reinterpret_cast<const double2*>(Ls + c * DP_LD + tn * 4 + 2);
+            const double wv[4] = {w01.x, w01.y, w23.x, w23.y};
+            const double lv[4] = {l01.x, l01.y, l23.x, l23.y};
+#pragma unroll
+            for (int a = 0; a < 4; ++a)
+#pragma unroll
+               for (int b = 0; b < 4; ++b) acc[a][b] += wv[a] * lv[b];
+         }
+         // read-modify-write with all 16 loads in flight (predicated, no branches between them)
+         double* tile = A + (j1 + tm * 4) + static_cast<int64_t>(ld) * (j1 + tn * 4);
+         double cur[4][4];
+         bool ok[4][4];
+#pragma unroll
+         for (int b = 0; b < 4; ++b)
+#pragma unroll
+            for (int a = 0; a < 4; ++a) {
+               const int m = tm * 4 + a, n = tn * 4 + b;
+               ok[a][b] = m < rem && n < rem && m >= n;
+               cur[a][b] = ok[a][b] ? tile[a + static_cast<int64_t>(ld) * b] : 0.0;
+            }
+#pragma unroll
+         for (int b = 0; b < 4; ++b)
+#pragma unroll
+            for (int a = 0; a < 4; ++a)
+               if (ok[a][b]) tile[a + static_cast<int64_t>(ld) * b] = cur[a][b] - acc[a][b];
+      }
+      __syncthreads();
+      PHASE_MARK(4);
+   }
+}
+
+constexpr int TP_THREADS = 128;
+constexpr int TP_LDP = NBO - NBI + 2;   // [c][kk] staging of the block rows' earlier L entries
+constexpr int TP_SMEM_BASE = static_cast<int>(sizeof(double)) * (NBI * (NBI + 1) + 2 * NBI) + 2 * NBI * static_cast<int>(sizeof(int));
+constexpr int TP_SMEM = TP_SMEM_BASE + static_cast<int>(sizeof(double)) * NBI * TP_LDP;
+
+// Kernel B of a panel step.  grid = (front, row chunk): rows below the diagonal block of the outer
+// panel at J0, one row per thread, all inner blocks in sequence (left-looking inside the panel):
+//   a(b) -= sum over earlier blocks of w(b') L[block b rows, block b']^T ; w(b) = a(b) L11(b)^{-T} ; l(b) = w(b) D(b)^{-1}
+// Writes L in place and W = L*D into the W panel for the trailing update.
+// Launched with TP_SMEM_BASE bytes when no front of the batch has more than NBI pivots (no earlier blocks).
+__global__ void __launch_bounds__(TP_THREADS) k_trsmpanel(FrontArrays F, const int* __restrict__ list, const int J0, FactorArrays W) {
+   extern __shared__ __align__(16) unsigned char tp_smem[];
+   double (*L11)[NBI + 1] = reinterpret_cast<double (*)[NBI + 1]>(tp_smem);
+   double* sd = reinterpret_cast<double*>(tp_smem) + NBI * (NBI + 1);
+   double* se = sd + NBI;
+   int* sp = reinterpret_cast<int*>(se + NBI);
+   int* stype = sp + NBI;
+   double* Lp = reinterpret_cast<double*>(stype + NBI);          // [c][kk], kk < j0 - J0
+   const int s = list[blockIdx.x];
+   const int k = F.k[s], f = F.f[s], ld = F.ld[s], first = F.first[s];
+   const int J1 = min(J0 + NBO, k);
+   const int ibeg = J1 + blockIdx.y * TP_THREADS;
+   if (ibeg >= f) return;
+   double* A = W.lpool + F.off[s];
+   double* Wp = W.wpool + F.woff[s];
+   const int tid = threadIdx.x;
+   const int i = ibeg + tid;
+   const bool act = i < f;
+   for (int j0 = J0; j0 < J1; j0 += NBI) {
+      const int nbw = min(NBI, k - j0);
+      const int kprev = j0 - J0;
+      __syncthreads();
+      for (int idx = tid; idx < NBI * NBI; idx += TP_THREADS) {
+         const int r = idx % NBI, c = idx / NBI;
+         L11[r][c] = (r < nbw && c < nbw && r > c) ? A[(j0 + r) + static_cast<int64_t>(ld) * (j0 + c)] : 0.0;
+      }
+      {
+         // TP_THREADS / NBI columns per pass, 8 passes in flight
+         const int c = tid % NBI, kq = tid / NBI;
+         constexpr int KSTEP = TP_THREADS / NBI;
+         const double* src = A + (j0 + c) + static_cast<int64_t>(ld) * J0;
+         for (int kk = kq; kk < kprev; kk += 8 * KSTEP) {
+            double t[8];
+#pragma unroll
+            for (int u = 0; u < 8; ++u) t[u] = (c < nbw && kk + u * KSTEP < kprev) ? src[static_cast<int64_t>(ld) * (kk + u * KSTEP)] : 0.0;
+#pragma unroll
+            for (int u = 0; u < 8; ++u) if (kk + u * KSTEP < kprev) Lp[c * TP_LDP + kk + u * KSTEP] = t[u];
+         }
+      }
+      if (tid < NBI) {
+         const int q = first + j0 + tid;
+         const bool in = tid < nbw;
+         sd[tid] = in ? W.dd[q] : 1.0;
+         se[tid] = in ? W.de[q] : 0.0;
+         stype[tid] = in ? W.ptype[q] : 0;
+         sp[tid] = in ? (W.lperm[q] - j0) : tid;
+      }
+      __syncthreads();
+      if (!act) continue;
+      double w[NBI], l[NBI];
+#pragma unroll
+      for (int c = 0; c < NBI; ++c) w[c] = (c < nbw) ? A[i + static_cast<int64_t>(ld) * (j0 + sp[c])] : 0.0;
+      if (kprev > 0) {
+         // the row's W entries of the earlier blocks, 8 at a time, next batch in flight while this one is used
+         const double* wrow = Wp + i;
+         double wn[8];
+#pragma unroll
+         for (int u = 0; u < 8; ++u) wn[u] = wrow[static_cast<int64_t>(ld) * u];
+         for (int kk = 0; kk < kprev; kk += 8) {
+            double wv[8];
+#pragma unroll
+            for (int u = 0; u < 8; ++u) wv[u] = wn[u];
+            if (kk + 8 < kprev) {
+#pragma unroll
+               for (int u = 0; u < 8; ++u) wn[u] = wrow[static_cast<int64_t>(ld) * (kk + 8 + u)];
+            }
+#pragma unroll
+            for (int u = 0; u < 8; u += 2) {
+#pragma unroll
+               for (int c = 0; c < NBI; ++c) {
+                  const double2 lv = *reinterpret_cast<const double2*>(Lp + c * TP_LDP + kk + u);
+                  w[c] = fma(-wv[u + 1], lv.y, fma(-wv[u], lv.x, w[c]));
+               }
+            }
+         }
+      }
+      row_trsm(w, l, L11, sd, se, stype);
+#pragma unroll
+      for (int c = 0; c < NBI; ++c) {
+         if (c < nbw) {
+            A[i + static_cast<int64_t>(ld) * (j0 + c)] = l[c];
+            Wp[i + static_cast<int64_t>(ld) * (kprev + c)] = w[c];
+         }
       }
    }
+}
+
+// Light variant of kernel A for batches whose fronts have at most NBI pivots (the bulk of the tree):
+// one warp per front, several fronts per CTA would need more shared memory than it saves; 64 threads.
+__global__ void __launch_bounds__(64) k_diag32(FrontArrays F, const int* __restrict__ list, FactorArrays W, const double null_tol) {
+   __shared__ BkShared S;
+   const int s = list[blockIdx.x];
+   const int k = F.k[s], ld = F.ld[s];
+   const int nbw = min(NBI, k);
+   double* A = W.lpool + F.off[s];
+   const int tid = threadIdx.x;
+   for (int idx = tid; idx < NBI * NBI; idx += 64) {
+      const int r = idx % NBI, c = idx / NBI;
+      double v;
+      if (r < nbw && c < nbw) {
+         v = (r >= c) ? A[r + static_cast<int64_t>(ld) * c] : A[c + static_cast<int64_t>(ld) * r];
+      } else {
+         v = (r == c) ? 1.0 : 0.0;
+      }
+      S.B[r][c] = v;
+   }
+   __syncthreads();
+   if (tid < 32) bk_factor_block(S, nbw, tid, null_tol);
+   __syncthreads();
+   for (int idx = tid; idx < NBI * NBI; idx += 64) {
+      const int r = idx % NBI, c = idx / NBI;
+      if (r < nbw && c < nbw && r >= c) A[r + static_cast<int64_t>(ld) * c] = (r == c) ? S.d[c] : S.B[r][c];
+   }
+   if (tid < nbw) {
+      const int q = F.first[s] + tid;
+      W.dd[q] = S.d[tid];
+      W.de[q] = S.e[tid];
+      W.ptype[q] = S.type[tid];
+      W.lperm[q] = S.p[tid];
+   }
+   if (tid == 0) W.blkflag[F.first[s]] = S.nontrivial;
 }
 
 // Deferred row interchanges: the rows of an inner block were permuted among themselves by its
@@ -383,7 +603,8 @@ __global__ void __launch_bounds__(256) k_permute_rows(FrontArrays F, const int* 
    const int src = (lane < nbw) ? (W.lperm[first + j0 + lane] - j0) : lane;
    const int ld = F.ld[s];
    double* A = W.lpool + F.off[s];
-   for (int c = blockIdx.z * 64 + warp; c < min(j0, blockIdx.z * 64 + 64); c += 8) {
+   const int cend = (j0 / NBO) * NBO;   // columns of the block's own outer panel were permuted by k_diagpanel
+   for (int c = blockIdx.z * 64 + warp; c < min(cend, blockIdx.z * 64 + 64); c += 8) {
       double* colp = A + static_cast<int64_t>(ld) * c + j0;
       const double v = (lane < nbw) ? colp[src] : 0.0;
       __syncwarp();
@@ -410,10 +631,9 @@ __device__ __forceinline__ void dmma8x8x4(double& c0, double& c1, const double a
    asm volatile("mma.sync.aligned.m8n8k4.row.col.f64.f64.f64.f64 {%0,%1}, {%2}, {%3}, {%0,%1};\n" : "+d"(c0), "+d"(c1) : "d"(a), "d"(b));
 }
 
-constexpr int UPD_BK = 16;
 constexpr int UPD_STAGES = 3;
 
-template <int BM, int BN, int WARPS_M, int WARPS_N>
+template <int BM, int BN, int WARPS_M, int WARPS_N, int UPD_BK>
 __global__ void __launch_bounds__(WARPS_M* WARPS_N * 32) k_update(FrontArrays F, const int* __restrict__ list, const int mode, const int j0,
                                                                   const int J0, FactorArrays W) {
    constexpr int NT = WARPS_M * WARPS_N * 32;
@@ -537,20 +757,28 @@ __global__ void __launch_bounds__(WARPS_M* WARPS_N * 32) k_update(FrontArrays F,
       return;
    }
 #pragma unroll
-   for (int a = 0; a < MF; ++a) {
-      const int m = m0 + wm0 + a * 8 + (lane >> 2);
-      if (m < r0 || m >= f) continue;
+   for (int b = 0; b < NF; ++b) {
+      double v[MF][2];
+      bool ok[MF][2];
+      double* dst[2];
 #pragma unroll
-      for (int b = 0; b < NF; ++b) {
+      for (int h = 0; h < 2; ++h) {
+         const int n = n0 + wn0 + b * 8 + 2 * (lane & 3) + h;
+         dst[h] = (n < k) ? (A + static_cast<int64_t>(ld) * n) : (Cb + static_cast<int64_t>(ldc) * n);
 #pragma unroll
-         for (int h = 0; h < 2; ++h) {
-            const int n = n0 + wn0 + b * 8 + 2 * (lane & 3) + h;
-            if (n >= c0 && n < c1 && m >= n) {
-               double* dst = (n < k) ? (A + m + static_cast<int64_t>(ld) * n) : (Cb + m + static_cast<int64_t>(ldc) * n);
-               *dst -= acc[a][b][h];
-            }
+         for (int a = 0; a < MF; ++a) {
+            const int m = m0 + wm0 + a * 8 + (lane >> 2);
+            ok[a][h] = m >= r0 && m < f && n >= c0 && n < c1 && m >= n;
+            v[a][h] = ok[a][h] ? dst[h][m] : 0.0;
          }
       }
+#pragma unroll
+      for (int h = 0; h < 2; ++h)
+#pragma unroll
+         for (int a = 0; a < MF; ++a) {
+            const int m = m0 + wm0 + a * 8 + (lane >> 2);
+            if (ok[a][h]) dst[h][m] = v[a][h] - acc[a][b][h];
+         }
    }
 }
 
@@ -959,24 +1187,27 @@ int launch_prepare(const FrontArrays& F, const int* d_list, int nfronts, int max
    return 1;
 }
 
-int launch_diag(const FrontArrays& F, const int* d_list, int nfronts, int j0, const FactorArrays& W, double null_tol, cudaStream_t st) {
+int launch_diagpanel(const FrontArrays& F, const int* d_list, int nfronts, int max_k, int J0, const FactorArrays& W, double null_tol,
+                     cudaStream_t st) {
    if (nfronts <= 0) return 0;
-   k_diag<<<nfronts, DIAG_THREADS, 0, st>>>(F, d_list, j0, W, null_tol);
+   if (max_k <= NBI) k_diag32<<<nfronts, 64, 0, st>>>(F, d_list, W, null_tol);
+   else k_diagpanel<<<nfronts, DP_THREADS, DP_SMEM, st>>>(F, d_list, J0, W, null_tol);
    return 1;
 }
 
-int launch_trsm(const FrontArrays& F, const int* d_list, int nfronts, int max_f, int j0, int J0, const FactorArrays& W, cudaStream_t st) {
+int launch_trsmpanel(const FrontArrays& F, const int* d_list, int nfronts, int max_f, int max_k, int J0, const FactorArrays& W,
+                     cudaStream_t st) {
    if (nfronts <= 0) return 0;
-   // a front of the list has k > j0, hence at least min(NBI, k - j0) >= 1 block columns: rows start at j0 + 1 at the earliest
-   const int chunks = (max_f - (j0 + 1) + PANEL_THREADS - 1) / PANEL_THREADS;
+   // a front of the list has k > J0: its rows below the diagonal block start at J0 + 1 at the earliest
+   const int chunks = (max_f - (J0 + 1) + TP_THREADS - 1) / TP_THREADS;
    if (chunks < 1) return 0;
    dim3 grid(nfronts, chunks);
-   k_trsm<<<grid, PANEL_THREADS, 0, st>>>(F, d_list, j0, J0, W);
+   k_trsmpanel<<<grid, TP_THREADS, max_k <= NBI ? TP_SMEM_BASE : TP_SMEM, st>>>(F, d_list, J0, W);
    return 1;
 }
 
 int launch_permute_rows(const FrontArrays& F, const int* d_list, int nfronts, int max_k, const FactorArrays& W, cudaStream_t st) {
-   if (nfronts <= 0 || max_k <= NBI) return 0;
+   if (nfronts <= 0 || max_k <= NBO) return 0;
    const int nblocks = (max_k + NBI - 1) / NBI - 1;   // inner blocks 1 .. last
    dim3 grid(nfronts, nblocks, (max_k + 63) / 64);
    k_permute_rows<<<grid, 256, 0, st>>>(F, d_list, W);
@@ -984,13 +1215,28 @@ int launch_permute_rows(const FrontArrays& F, const int* d_list, int nfronts, in
 }
 
 namespace {
-constexpr int smem_bytes(int bm, int bn) { return UPD_STAGES * UPD_BK * (bm + 4 + bn + 4) * static_cast<int>(sizeof(double)); }
+constexpr int smem_bytes(int bm, int bn, int bk) { return UPD_STAGES * bk * (bm + 4 + bn + 4) * static_cast<int>(sizeof(double)); }
+}
+
+int debug_phase_cycles(unsigned long long* out16, bool reset) {
+#ifdef B200KKT_PHASES
+   if (out16 != nullptr) cudaMemcpyFromSymbol(out16, g_phase, sizeof(g_phase));
+   if (reset) { unsigned long long z[16] = {0}; cudaMemcpyToSymbol(g_phase, z, sizeof(z)); }
+   return 1;
+#else
+   (void)out16; (void)reset;
+   return 0;
+#endif
 }
 
 int init_kernel_attributes() {
-   cudaError_t e = cudaFuncSetAttribute(k_update<128, 128, 2, 4>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem_bytes(128, 128));
+   cudaError_t e = cudaFuncSetAttribute(k_diagpanel, cudaFuncAttributeMaxDynamicSharedMemorySize, DP_SMEM);
    if (e != cudaSuccess) return static_cast<int>(e);
-   e = cudaFuncSetAttribute(k_update<64, 64, 2, 2>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem_bytes(64, 64));
+   e = cudaFuncSetAttribute(k_trsmpanel, cudaFuncAttributeMaxDynamicSharedMemorySize, TP_SMEM);
+   if (e != cudaSuccess) return static_cast<int>(e);
+   e = cudaFuncSetAttribute(k_update<128, 128, 2, 4, 32>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem_bytes(128, 128, 32));
+   if (e != cudaSuccess) return static_cast<int>(e);
+   e = cudaFuncSetAttribute(k_update<64, 64, 2, 2, 16>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem_bytes(64, 64, 16));
    return static_cast<int>(e);
 }
 
@@ -1004,10 +1250,10 @@ int launch_update(const FrontArrays& F, const int* d_list, int nfronts, int max_
    const int cols = (mode == 0) ? NBO : rows;
    if (big_tiles) {
       dim3 grid(nfronts, (rows + 127) / 128, (cols + 127) / 128);
-      k_update<128, 128, 2, 4><<<grid, 256, smem_bytes(128, 128), st>>>(F, d_list, mode, j0, J0, W);
+      k_update<128, 128, 2, 4, 32><<<grid, 256, smem_bytes(128, 128, 32), st>>>(F, d_list, mode, j0, J0, W);
    } else {
       dim3 grid(nfronts, (rows + 63) / 64, (cols + 63) / 64);
-      k_update<64, 64, 2, 2><<<grid, 128, smem_bytes(64, 64), st>>>(F, d_list, mode, j0, J0, W);
+      k_update<64, 64, 2, 2, 16><<<grid, 128, smem_bytes(64, 64, 16), st>>>(F, d_list, mode, j0, J0, W);
    }
    return 1;
 }

@@ -64,10 +64,13 @@ int launch_assemble(const AssemblyArrays& M, const double* values, const double*
 
 // K5: zero the contribution blocks of the listed fronts and extend-add all their children into them
 int launch_prepare(const FrontArrays& F, const int* d_list, int nfronts, int max_f, const FactorArrays& W, cudaStream_t st);
-// K3 panel step at pivot column j0: (a) Bunch-Kaufman on the NBI x NBI diagonal block, in place;
-// (b) triangular solve of the rows below it: writes L in place and W = L*D into the W panel
-int launch_diag(const FrontArrays& F, const int* d_list, int nfronts, int j0, const FactorArrays& W, double null_tol, cudaStream_t st);
-int launch_trsm(const FrontArrays& F, const int* d_list, int nfronts, int max_f, int j0, int J0, const FactorArrays& W, cudaStream_t st);
+// K3 panel step for the outer panel at pivot column J0: (A) one CTA per front factors the NBO x NBO
+// diagonal block (Bunch-Kaufman confined to NBI x NBI inner blocks), in place; (B) the rows below it:
+// writes L in place and W = L*D into the W panel
+int launch_diagpanel(const FrontArrays& F, const int* d_list, int nfronts, int max_k, int J0, const FactorArrays& W, double null_tol,
+                     cudaStream_t st);
+int launch_trsmpanel(const FrontArrays& F, const int* d_list, int nfronts, int max_f, int max_k, int J0, const FactorArrays& W,
+                     cudaStream_t st);
 // rows of the L columns left of each inner block follow the block's interchanges (all blocks at once)
 int launch_permute_rows(const FrontArrays& F, const int* d_list, int nfronts, int max_k, const FactorArrays& W, cudaStream_t st);
 // K4 Schur-complement update C -= W * L^T with FP64 tensor-core MMA.
@@ -75,6 +78,8 @@ int launch_permute_rows(const FrontArrays& F, const int* d_list, int nfronts, in
 int launch_update(const FrontArrays& F, const int* d_list, int nfronts, int max_f, int mode, int j0, int J0,
                   const FactorArrays& W, bool big_tiles, cudaStream_t st);
 int init_kernel_attributes();
+// phase cycle counters of the panel kernels (only when built with -DB200KKT_PHASES); returns 0 when not compiled in
+int debug_phase_cycles(unsigned long long* out16, bool reset);
 // K6 inertia from the D blocks: counters[0..4] = positive, negative, zero, number of 2x2, unused
 int launch_inertia(int64_t n, const FactorArrays& W, int* counters, cudaStream_t st);
 

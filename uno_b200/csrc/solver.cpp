@@ -268,24 +268,26 @@ void enqueue_factor(b200kkt_handle* h) {
    if (prof) prof_begin(0.0, 1);
    L += launch_assemble(h->M, h->d_values, cur, h->W.lpool, st);
    if (prof) prof_end();
-   // K2-K5 level by level
+   // K2-K5 level by level; the batches of one level are independent and go round-robin over the
+   // handle's streams (fork/join with events, which stream capture turns into graph edges)
+   const bool multi = h->multi_stream != 0 && !prof;
    for (int l = 0; l < P.nlevels; ++l) {
+      const int nb = h->level_batch_ptr[l + 1] - h->level_batch_ptr[l];
+      const int nside = multi ? std::min(nb - 1, static_cast<int>(b200kkt_handle::NUM_AUX)) : 0;
+      if (nside > 0) {
+         CK(cudaEventRecord(h->ev_fork, h->stream));
+         for (int a = 0; a < nside; ++a) CK(cudaStreamWaitEvent(h->aux[a], h->ev_fork, 0));
+      }
       for (int bi = h->level_batch_ptr[l]; bi < h->level_batch_ptr[l + 1]; ++bi) {
          const Batch& b = h->batches[bi];
          const int* list = h->d_batch_list + b.begin;
+         const int lane = (bi - h->level_batch_ptr[l]) % (nside + 1);
+         cudaStream_t st = (lane == 0) ? h->stream : h->aux[lane - 1];
          if (b.has_cb || b.has_children) L += launch_prepare(h->F, list, b.count, b.max_f, h->W, st);
          for (int J0 = 0; J0 < b.max_k; J0 += NBO) {
             const int nfP = b.count_k_greater(J0);
-            const int Jend = std::min(J0 + NBO, b.max_k);
-            for (int j0 = J0; j0 < Jend; j0 += NBI) {
-               const int nfb = b.count_k_greater(j0);
-               const int maxf_b = b.pmaxf[nfb - 1];
-               L += launch_diag(h->F, list, nfb, j0, h->W, h->null_pivot_tol, st);
-               L += launch_trsm(h->F, list, nfb, maxf_b, j0, J0, h->W, st);
-               // in-panel update only where pivot columns remain right of this block inside the panel
-               const int nfu = b.count_k_greater(j0 + NBI);
-               if (nfu > 0 && j0 + NBI < J0 + NBO) L += launch_update(h->F, list, nfu, b.pmaxf[nfu - 1], 0, j0, J0, h->W, b.big_tiles, st);
-            }
+            L += launch_diagpanel(h->F, list, nfP, b.max_k, J0, h->W, h->null_pivot_tol, st);
+            L += launch_trsmpanel(h->F, list, nfP, b.pmaxf[nfP - 1], b.max_k, J0, h->W, st);
             const bool prof_this = prof && b.max_f >= 1024;
             if (prof_this) {
                double fl = 0.0;
@@ -299,7 +301,11 @@ void enqueue_factor(b200kkt_handle* h) {
             L += launch_update(h->F, list, nfP, b.pmaxf[nfP - 1], 1, 0, J0, h->W, b.big_tiles, st);
             if (prof_this) prof_end();
          }
-         L += launch_permute_rows(h->F, list, b.count_k_greater(NBI), b.max_k, h->W, st);
+         L += launch_permute_rows(h->F, list, b.count_k_greater(NBO), b.max_k, h->W, st);
+      }
+      for (int a = 0; a < nside; ++a) {
+         CK(cudaEventRecord(h->ev_join[a], h->aux[a]));
+         CK(cudaStreamWaitEvent(h->stream, h->ev_join[a], 0));
       }
    }
    // K6 inertia
@@ -507,6 +513,11 @@ int b200kkt_create(b200kkt_handle** out, int device, int num_gpus) {
       const int rc = guarded(h, [&] {
          CK(cudaSetDevice(device));
          CK(cudaStreamCreateWithFlags(&h->stream, cudaStreamNonBlocking));
+         for (int a = 0; a < b200kkt_handle::NUM_AUX; ++a) {
+            CK(cudaStreamCreateWithFlags(&h->aux[a], cudaStreamNonBlocking));
+            CK(cudaEventCreateWithFlags(&h->ev_join[a], cudaEventDisableTiming));
+         }
+         CK(cudaEventCreateWithFlags(&h->ev_fork, cudaEventDisableTiming));
          CK(cudaEventCreate(&h->ev0));
          CK(cudaEventCreate(&h->ev1));
          CK(cudaMallocHost(reinterpret_cast<void**>(&h->h_counters), 8 * sizeof(int)));
@@ -536,6 +547,11 @@ int b200kkt_destroy(b200kkt_handle* h) {
       if (h->h_norms != nullptr) cudaFreeHost(h->h_norms);
       if (h->ev0 != nullptr) cudaEventDestroy(h->ev0);
       if (h->ev1 != nullptr) cudaEventDestroy(h->ev1);
+      for (int a = 0; a < b200kkt_handle::NUM_AUX; ++a) {
+         if (h->ev_join[a] != nullptr) cudaEventDestroy(h->ev_join[a]);
+         if (h->aux[a] != nullptr) cudaStreamDestroy(h->aux[a]);
+      }
+      if (h->ev_fork != nullptr) cudaEventDestroy(h->ev_fork);
       if (h->stream != nullptr) cudaStreamDestroy(h->stream);
    }
    delete h;
@@ -559,6 +575,7 @@ int b200kkt_set_option(b200kkt_handle* h, const char* name, double value) {
    else if (n == "refine_tol") h->refine_tol = value;
    else if (n == "use_graph") h->use_graph = static_cast<int>(value);
    else if (n == "profile_updates") h->profile_updates = static_cast<int>(value);
+   else if (n == "multi_stream") h->multi_stream = static_cast<int>(value);
    else return fail(h, B200KKT_EINVAL, "unknown option: " + n);
    // numeric options are baked into the captured graph
    if (h->factor_graph != nullptr) { cudaGraphExecDestroy(h->factor_graph); h->factor_graph = nullptr; }
@@ -826,3 +843,5 @@ extern "C" int b200kkt_debug_bench_update(int device, int f, int k, int reps, in
       return B200KKT_ECUDA;
    }
 }
+
+extern "C" int b200kkt_debug_phase_cycles(unsigned long long* out16, int reset) { return debug_phase_cycles(out16, reset != 0); }

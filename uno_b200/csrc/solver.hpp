@@ -65,6 +65,10 @@ struct b200kkt_handle {
    std::vector<SolveLevel> solve_levels;
 
    cudaStream_t stream = nullptr;
+   static constexpr int NUM_AUX = 3;       // side streams: independent batches of one tree level run concurrently
+   cudaStream_t aux[NUM_AUX] = {nullptr, nullptr, nullptr};
+   cudaEvent_t ev_fork = nullptr, ev_join[NUM_AUX] = {nullptr, nullptr, nullptr};
+   int multi_stream = 1;
    cudaEvent_t ev0 = nullptr, ev1 = nullptr;
    cudaGraphExec_t factor_graph = nullptr;
    std::vector<void*> plan_allocs;         // freed on re-analysis / destroy
