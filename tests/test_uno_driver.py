@@ -1,0 +1,51 @@
+"""End-to-end parity through the UNCHANGED Uno host code (last row): the bundled examples must
+reach the same iteration count, termination status and per-iteration regularization with the B200 solver as the
+reference run (Uno + CPU oracle, golden in tests/golden/uno_examples.json).  The driver binary is built by
+oracle/build_ref.py where /root/reference exists and travels to the GPU box prebuilt."""
+import json
+from pathlib import Path
+
+import pytest
+
+from uno_driver_util import DRIVER, run_driver
+
+GOLDEN = json.loads((Path(__file__).resolve().parent / "golden" / "uno_examples.json").read_text())
+MODELS = ["hs015", "polak5", "control2d:16", "control3d:6"]
+needs_driver = pytest.mark.skipif(not DRIVER.exists(), reason="oracle/_ref/uno_driver not built (needs /root/reference at build time)")
+
+
+def same_run(result, golden):
+    assert result["iterations"] == golden["iterations"]
+    assert result["optimization_status"] == golden["optimization_status"]
+    assert result["iterate_status"] == golden["iterate_status"]
+    assert result["regularization_per_iteration"] == golden["regularization_per_iteration"]
+    assert abs(result["objective"] - golden["objective"]) <= 1e-6 * max(1.0, abs(golden["objective"]))   # reference CI uses 1e-4
+
+
+@needs_driver
+@pytest.mark.parametrize("model", MODELS)
+def test_reference_run_reproduces_golden(model):
+    same_run(run_driver(model, "ORACLE"), GOLDEN[model])
+
+
+def test_known_optima():
+    # hs015: f* = 306.5 (Hock & Schittkowski), polak5: f* = 50
+    assert abs(GOLDEN["hs015"]["objective"] - 306.5) <= 1e-4
+    assert abs(GOLDEN["polak5"]["objective"] - 50.0) <= 1e-4
+    assert GOLDEN["hs015"]["iterate_status"] == GOLDEN["polak5"]["iterate_status"] == "Feasible KKT point"
+
+
+@pytest.mark.gpu
+@needs_driver
+@pytest.mark.parametrize("model", MODELS)
+def test_b200_solver_matches_reference_run(model):
+    same_run(run_driver(model, "B200"), GOLDEN[model])
+
+
+@pytest.mark.gpu
+@needs_driver
+def test_b200_is_default_linear_solver():
+    # first (here: only product) entry of available_solvers() becomes the default (DefaultOptions.cpp:203-206)
+    import subprocess
+    out = subprocess.run([str(DRIVER)], capture_output=True, text=True).stdout
+    assert "Linear solvers: B200" in out
