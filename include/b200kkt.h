@@ -131,6 +131,9 @@ int b200kkt_debug_bench_update(int device, int f, int k, int reps, int big_tiles
 /* Profiling hook: cycle counters of the panel-kernel phases; returns 0 unless the library was built with -DB200KKT_PHASES. */
 int b200kkt_debug_phase_cycles(unsigned long long* out16, int reset);
 
+/* Profiling hook: cycles per 32 x 32 Bunch-Kaufman block factorization (one warp), for three kinds of blocks. */
+int b200kkt_debug_bench_bk(int variant, int reps, long long* cycles);
+
 #ifdef __cplusplus
 }
 #endif

@@ -13,8 +13,8 @@ out = (C.c_ulonglong * 16)()
 lib.b200kkt_debug_phase_cycles(out, 1)
 s.do_numerical_factorization(kkt.val)
 rc = lib.b200kkt_debug_phase_cycles(out, 0)
-tot = sum(out)
-names = ["diag load", "bunch-kaufman", "writeback+interchange", "row trsm", "in-block update"]
+tot = sum(out[:8])
+names = ["diag load", "bunch-kaufman", "writeback+interchange", "row trsm", "in-block update", "", "", "", "bk: loop overhead", "bk: pivot search", "bk: interchange", "bk: 1x1 update", "bk: 2x2 update"]
 print("compiled in:", rc, "factor ms", s.stats()["t_factor_last"] * 1e3)
 for i, n in enumerate(names):
     print(f"  {n:24s} {out[i]/1e6:10.2f} Mcycles {100*out[i]/max(tot,1):5.1f}%")

@@ -249,6 +249,7 @@ def test_full_size_properties(make, name):
     x2 = s.solve_indefinite_system(b2)
     x12 = s.solve_indefinite_system(kkt.rhs + 2.0 * b2)
     assert backward_error(kkt, kkt.val, x12, kkt.rhs + 2.0 * b2) <= BERR_TOL
-    assert np.max(np.abs(x12 - (x1 + 2.0 * x2))) <= 1e-6 * np.max(np.abs(x12))
+    # forward error ~ cond(K) * backward error; the barrier terms spread over 16 decades, so only the reference's own 1e-4 is asked
+    assert np.max(np.abs(x12 - (x1 + 2.0 * x2))) <= X_TOL * np.max(np.abs(x12))
     s.do_numerical_factorization(kkt.val)
     assert np.array_equal(x1, s.solve_indefinite_system(kkt.rhs))

@@ -19,7 +19,7 @@ EXPORTED_SYMBOLS = [
     "b200kkt_factorize", "b200kkt_refactorize_shifted", "b200kkt_factorize_device", "b200kkt_inertia", "b200kkt_solve",
     "b200kkt_solve_device", "b200kkt_get_permutation", "b200kkt_get_stats", "b200kkt_last_error", "b200kkt_plan_sizes",
     "b200kkt_plan_fronts", "b200kkt_plan_rows", "b200kkt_debug_assemble", "b200kkt_debug_factor", "b200kkt_get_stream",
-    "b200kkt_debug_bench_update", "b200kkt_debug_phase_cycles",
+    "b200kkt_debug_bench_update", "b200kkt_debug_phase_cycles", "b200kkt_debug_bench_bk",
 ]
 
 

@@ -169,6 +169,15 @@ struct BkShared {
    int nontrivial;
 };
 
+#ifdef B200KKT_PHASES
+__device__ unsigned long long g_phase[16];
+#define PHASE_BEGIN() long long ph_t = clock64()
+#define PHASE_MARK(i) do { if (threadIdx.x == 0) { const long long ph_n = clock64(); atomicAdd(g_phase + (i), static_cast<unsigned long long>(ph_n - ph_t)); ph_t = ph_n; } } while (0)
+#else
+#define PHASE_BEGIN() do {} while (0)
+#define PHASE_MARK(i) do {} while (0)
+#endif
+
 // max over the warp of non-negative doubles (negative inputs count as "absent" and give -1):
 // the IEEE order of non-negative doubles is the order of their bit patterns, so two 32-bit REDUX
 // operations (high words, then low words among the lanes holding the maximal high word) replace
@@ -196,7 +205,9 @@ __device__ void bk_factor_block(BkShared& S, const int n, const int lane, const 
    if (lane == 0) S.nontrivial = 0;
    __syncwarp();
    int j = 0;
+   PHASE_BEGIN();
    while (j < n) {
+      PHASE_MARK(8);
       const double absajj = fabs(S.B[j][j]);
       // lambda = largest off-diagonal magnitude of column j, r = its first row
       const double v = (lane > j && lane < n) ? fabs(S.B[lane][j]) : -1.0;
@@ -220,6 +231,7 @@ __device__ void bk_factor_block(BkShared& S, const int n, const int lane, const 
             step = 2;
          }
       }
+      PHASE_MARK(9);
       const int kk = j + step - 1;
       if (kp != kk) {
          // symmetric interchange kk <-> kp on the full block (rows carry the already computed L entries)
@@ -239,6 +251,7 @@ __device__ void bk_factor_block(BkShared& S, const int n, const int lane, const 
          }
          __syncwarp();
       }
+      PHASE_MARK(10);
       if (step == 1) {
          const double d = S.B[j][j];
          if (isnull) {
@@ -281,7 +294,50 @@ __device__ void bk_factor_block(BkShared& S, const int n, const int lane, const 
          }
       }
       __syncwarp();
+      PHASE_MARK(step == 1 ? 11 : 12);
       j += step;
+   }
+}
+
+// Lane t computes column t of X = L11^{-1} (unit lower triangular, strict lower part in S.B) by forward
+// substitution, then X2 = D^{-1} X (1x1 and 2x2 blocks; null pivots give zero rows in both).  Results go to
+// shared memory ([c][t], row stride NBI + 1) and, row-major 32 x 32 each, to the front's scratch for kernel B.
+__device__ void invert_block(const BkShared& S, const int n, const int t, double* Xs, double* X2s, double* Xg) {
+   double x[NBI];
+#pragma unroll
+   for (int i = 0; i < NBI; ++i) x[i] = (i == t) ? 1.0 : 0.0;
+#pragma unroll
+   for (int j = 0; j < NBI - 1; ++j) {
+      const double xj = x[j];
+#pragma unroll
+      for (int i = j + 1; i < NBI; ++i) x[i] = fma(-S.B[i][j], xj, x[i]);   // S.B[i][j] = 0 above the diagonal of L? no: strict lower only is read
+   }
+   double x2[NBI];
+#pragma unroll
+   for (int i = 0; i < NBI; ++i) {
+      const int ty = S.type[i];
+      if (ty == 0) {
+         x2[i] = x[i] / S.d[i];
+      } else if (ty == 1) {
+         if (i + 1 < NBI) {
+            const double a = S.d[i], b = S.e[i], c = S.d[i + 1];
+            const double det = a * c - b * b;
+            x2[i] = (c * x[i] - b * x[i + 1]) / det;
+            x2[i + 1] = (a * x[i + 1] - b * x[i]) / det;
+         }
+      } else if (ty == 3) {
+         x[i] = 0.0;
+         x2[i] = 0.0;
+      }
+   }
+#pragma unroll
+   for (int i = 0; i < NBI; ++i) {
+      const bool in = i < n && t < n;
+      const double v = in ? x[i] : 0.0, v2 = in ? x2[i] : 0.0;
+      Xs[i * (NBI + 1) + t] = v;
+      X2s[i * (NBI + 1) + t] = v2;
+      Xg[i * NBI + t] = v;
+      Xg[NBI * NBI + i * NBI + t] = v2;
    }
 }
 
@@ -289,12 +345,13 @@ __device__ void bk_factor_block(BkShared& S, const int n, const int lane, const 
 //   w <- w L11^{-T},  l = w D^{-1}   (null pivots: both zero)
 __device__ __forceinline__ void row_trsm(double (&w)[NBI], double (&l)[NBI], const double (*L11)[NBI + 1], const double* sd, const double* se,
                                          const int* stype) {
+   // right-looking order: once w[t] is final it is eliminated from all later columns at once, so the
+   // dependent chain is NBI fused multiply-adds long instead of NBI^2 / 2
 #pragma unroll
-   for (int c = 1; c < NBI; ++c) {
-      double acc = w[c];
+   for (int t = 0; t < NBI - 1; ++t) {
+      const double wt = w[t];
 #pragma unroll
-      for (int t = 0; t < c; ++t) acc -= w[t] * L11[c][t];
-      w[c] = acc;
+      for (int c = t + 1; c < NBI; ++c) w[c] = fma(-wt, L11[c][t], w[c]);
    }
 #pragma unroll
    for (int c = 0; c < NBI; ++c) {
@@ -315,18 +372,9 @@ __device__ __forceinline__ void row_trsm(double (&w)[NBI], double (&l)[NBI], con
    }
 }
 
-#ifdef B200KKT_PHASES
-__device__ unsigned long long g_phase[16];
-#define PHASE_BEGIN() long long ph_t = clock64()
-#define PHASE_MARK(i) do { if (threadIdx.x == 0) { const long long ph_n = clock64(); atomicAdd(g_phase + (i), static_cast<unsigned long long>(ph_n - ph_t)); ph_t = ph_n; } } while (0)
-#else
-#define PHASE_BEGIN() do {} while (0)
-#define PHASE_MARK(i) do {} while (0)
-#endif
-
 constexpr int DP_THREADS = 256;
 constexpr int DP_LD = NBO - NBI + 4;   // rows of the in-panel W/L staging (c-major: [c][row])
-constexpr int DP_SMEM = static_cast<int>(sizeof(BkShared)) + 2 * NBI * DP_LD * static_cast<int>(sizeof(double));
+constexpr int DP_SMEM = static_cast<int>(sizeof(BkShared)) + 16 + (2 * NBI * DP_LD + 2 * NBI * (NBI + 1)) * static_cast<int>(sizeof(double));
 
 // Kernel A of a panel step.  One CTA per front factors the NBO x NBO diagonal block of the outer
 // panel starting at pivot column J0, in place: for every NBI-wide inner block Bunch-Kaufman (one
@@ -339,10 +387,13 @@ __global__ void __launch_bounds__(DP_THREADS) k_diagpanel(FrontArrays F, const i
    BkShared& S = *reinterpret_cast<BkShared*>(dp_smem);
    double* Ws = reinterpret_cast<double*>(dp_smem + ((sizeof(BkShared) + 15) & ~size_t(15)));   // [c][row]
    double* Ls = Ws + NBI * DP_LD;
+   double* Xs = Ls + NBI * DP_LD;            // [c][t], row stride NBI + 1: X = L11^{-1} of the inner block
+   double* X2s = Xs + NBI * (NBI + 1);       // D^{-1} X
    const int s = list[blockIdx.x];
    const int k = F.k[s], ld = F.ld[s], first = F.first[s];
    const int J1 = min(J0 + NBO, k);
    double* A = W.lpool + F.off[s];
+   double* Xg = W.wpool + F.woff[s] + static_cast<int64_t>(ld) * min(NBO, (k + 3) & ~3);   // behind the W panel
    const int tid = threadIdx.x;
    PHASE_BEGIN();
    for (int j0 = J0; j0 < J1; j0 += NBI) {
@@ -362,6 +413,7 @@ __global__ void __launch_bounds__(DP_THREADS) k_diagpanel(FrontArrays F, const i
       if (tid < 32) bk_factor_block(S, nbw, tid, null_tol);
       __syncthreads();
       PHASE_MARK(1);
+      if (tid >= 32 && tid < 64) invert_block(S, nbw, tid - 32, Xs, X2s, Xg + ((j0 - J0) / NBI) * 2 * NBI * NBI);
       for (int idx = tid; idx < NBI * NBI; idx += DP_THREADS) {
          const int r = idx % NBI, c = idx / NBI;
          if (r < nbw && c < nbw && r >= c) A[(j0 + r) + static_cast<int64_t>(ld) * (j0 + c)] = (r == c) ? S.d[c] : S.B[r][c];
@@ -389,18 +441,23 @@ __global__ void __launch_bounds__(DP_THREADS) k_diagpanel(FrontArrays F, const i
       PHASE_MARK(2);
       const int rem = J1 - j1;   // rows (and columns) of the diagonal block still to be factored
       if (rem <= 0) break;
-      // rows of the diagonal block below the inner block
+      // rows of the diagonal block below the inner block: w = a X^T, l = a X2^T (independent dot products)
       if (tid < rem) {
          const int i = j1 + tid;
-         double w[NBI], l[NBI];
+         double a[NBI];
 #pragma unroll
-         for (int c = 0; c < NBI; ++c) w[c] = (c < nbw) ? A[i + static_cast<int64_t>(ld) * (j0 + S.p[c])] : 0.0;
-         row_trsm(w, l, S.B, S.d, S.e, S.type);
+         for (int c = 0; c < NBI; ++c) a[c] = (c < nbw) ? A[i + static_cast<int64_t>(ld) * (j0 + S.p[c])] : 0.0;
 #pragma unroll
          for (int c = 0; c < NBI; ++c) {
-            if (c < nbw) A[i + static_cast<int64_t>(ld) * (j0 + c)] = l[c];
-            Ws[c * DP_LD + tid] = (c < nbw) ? w[c] : 0.0;
-            Ls[c * DP_LD + tid] = (c < nbw) ? l[c] : 0.0;
+            double w = 0.0, l = 0.0;
+#pragma unroll
+            for (int t = 0; t <= c; ++t) w = fma(a[t], Xs[c * (NBI + 1) + t], w);
+            // X2 rows of a 2x2 pair reach one column further than the diagonal
+#pragma unroll
+            for (int t = 0; t <= ((c + 1 < NBI) ? c + 1 : c); ++t) l = fma(a[t], X2s[c * (NBI + 1) + t], l);
+            if (c < nbw) A[i + static_cast<int64_t>(ld) * (j0 + c)] = l;
+            Ws[c * DP_LD + tid] = w;
+            Ls[c * DP_LD + tid] = l;
          }
       } else if (tid < ((rem + 3) & ~3)) {
 #pragma unroll
@@ -551,6 +608,153 @@ __global__ void __launch_bounds__(TP_THREADS) k_trsmpanel(FrontArrays F, const i
    }
 }
 
+__device__ __forceinline__ void dmma8x8x4(double& c0, double& c1, const double a, const double b) {
+   asm volatile("mma.sync.aligned.m8n8k4.row.col.f64.f64.f64.f64 {%0,%1}, {%2}, {%3}, {%0,%1};\n" : "+d"(c0), "+d"(c1) : "d"(a), "d"(b));
+}
+
+// Kernel B, tensor-core variant for fronts with more than NBI pivots.  CTA = 64 rows below the diagonal
+// block, 4 warps.  The CTA's W rows of the whole outer panel stay in shared memory; per inner block:
+//   T = A[rows, block] - Wsm[rows, 0:kprev] * L[block rows, 0:kprev]^T     (DMMA.8x8x4, 16 rows per warp)
+//   w = T L11^{-T}, l = w D^{-1}                                            (row per lane, 16 lanes per warp)
+constexpr int TD_ROWS = 64;
+constexpr int TD_THREADS = 128;
+constexpr int TD_LDW = NBO + 4;          // row stride of Wsm: 4 mod 16 -> conflict-free fragment loads
+constexpr int TD_LDP = NBO - NBI + 4;    // row stride of the staged L rows of the block
+constexpr int TD_LDT = NBI + 4;          // row stride of T, X, X2
+constexpr int TD_SMEM = static_cast<int>(sizeof(double)) * (TD_ROWS * TD_LDW + NBI * TD_LDP + TD_ROWS * TD_LDT + 2 * NBI * TD_LDT) +
+                        NBI * static_cast<int>(sizeof(int));
+
+__global__ void __launch_bounds__(TD_THREADS) k_trsmpanel_mma(FrontArrays F, const int* __restrict__ list, const int J0, FactorArrays W) {
+   extern __shared__ __align__(16) unsigned char td_smem[];
+   double* Wsm = reinterpret_cast<double*>(td_smem);                 // [row][kk]
+   double* Lp = Wsm + TD_ROWS * TD_LDW;                              // [c][kk]
+   double* T = Lp + NBI * TD_LDP;                                    // [row][c]
+   double* Xb = T + TD_ROWS * TD_LDT;                                // [c][t]: X = L11^{-1}
+   double* X2b = Xb + NBI * TD_LDT;                                  // D^{-1} X
+   int* sp = reinterpret_cast<int*>(X2b + NBI * TD_LDT);
+   const int s = list[blockIdx.x];
+   const int k = F.k[s], f = F.f[s], ld = F.ld[s], first = F.first[s];
+   const int J1 = min(J0 + NBO, k);
+   const int i0 = J1 + blockIdx.y * TD_ROWS;
+   if (i0 >= f) return;
+   double* A = W.lpool + F.off[s];
+   double* Wp = W.wpool + F.woff[s];
+   const double* Xg = Wp + static_cast<int64_t>(ld) * min(NBO, (k + 3) & ~3);
+   const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+   for (int j0 = J0; j0 < J1; j0 += NBI) {
+      const int nbw = min(NBI, k - j0);
+      const int kprev = j0 - J0;
+      __syncthreads();
+      if (tid < NBI) sp[tid] = (tid < nbw) ? (W.lperm[first + j0 + tid] - j0) : tid;
+      __syncthreads();
+      // stage: inverted diagonal block, the block rows' earlier L entries, the CTA's rows of the block columns (pivot order)
+      {
+         const double* xg = Xg + (kprev / NBI) * 2 * NBI * NBI;
+         for (int idx = tid; idx < 2 * NBI * NBI; idx += TD_THREADS) {
+            const int which = idx / (NBI * NBI), c = (idx / NBI) % NBI, t = idx % NBI;
+            (which ? X2b : Xb)[c * TD_LDT + t] = xg[idx];
+         }
+      }
+      {
+         const int c = tid % NBI, kq = tid / NBI;
+         constexpr int KSTEP = TD_THREADS / NBI;
+         const double* src = A + (j0 + c) + static_cast<int64_t>(ld) * J0;
+         for (int kk = kq; kk < kprev; kk += 8 * KSTEP) {
+            double t[8];
+#pragma unroll
+            for (int u = 0; u < 8; ++u) t[u] = (c < nbw && kk + u * KSTEP < kprev) ? src[static_cast<int64_t>(ld) * (kk + u * KSTEP)] : 0.0;
+#pragma unroll
+            for (int u = 0; u < 8; ++u) if (kk + u * KSTEP < kprev) Lp[c * TD_LDP + kk + u * KSTEP] = t[u];
+         }
+      }
+      {
+         const int r = tid % TD_ROWS, cq = tid / TD_ROWS;   // 2 column phases
+         const bool rin = i0 + r < f;
+         double t[NBI / 2];
+#pragma unroll
+         for (int u = 0; u < NBI / 2; ++u) {
+            const int c = cq + 2 * u;
+            t[u] = (rin && c < nbw) ? A[(i0 + r) + static_cast<int64_t>(ld) * (j0 + sp[c])] : 0.0;
+         }
+#pragma unroll
+         for (int u = 0; u < NBI / 2; ++u) T[r * TD_LDT + cq + 2 * u] = t[u];
+      }
+      __syncthreads();
+      const int r0 = warp * 16 + (lane >> 2);   // this lane's fragment rows: r0, r0 + 8
+      // T[16 rows of this warp] -= Wsm * Lp^T
+      if (kprev > 0) {
+         double acc[2][4][2];
+#pragma unroll
+         for (int a = 0; a < 2; ++a)
+#pragma unroll
+            for (int b = 0; b < 4; ++b) { acc[a][b][0] = 0.0; acc[a][b][1] = 0.0; }
+         const double* wa = Wsm + r0 * TD_LDW + (lane & 3);
+         const double* lb = Lp + (lane >> 2) * TD_LDP + (lane & 3);
+#pragma unroll 4
+         for (int kk = 0; kk < kprev; kk += 4) {
+            double af[2], bf[4];
+#pragma unroll
+            for (int a = 0; a < 2; ++a) af[a] = wa[a * 8 * TD_LDW + kk];
+#pragma unroll
+            for (int b = 0; b < 4; ++b) bf[b] = lb[b * 8 * TD_LDP + kk];
+#pragma unroll
+            for (int a = 0; a < 2; ++a)
+#pragma unroll
+               for (int b = 0; b < 4; ++b) dmma8x8x4(acc[a][b][0], acc[a][b][1], af[a], bf[b]);
+         }
+#pragma unroll
+         for (int a = 0; a < 2; ++a)
+#pragma unroll
+            for (int b = 0; b < 4; ++b)
+#pragma unroll
+               for (int h = 0; h < 2; ++h) T[(r0 + a * 8) * TD_LDT + b * 8 + 2 * (lane & 3) + h] -= acc[a][b][h];
+         __syncwarp();
+      }
+      // w = T X^T, l = T X2^T (both on the tensor pipe)
+      double aw[2][4][2], al[2][4][2];
+#pragma unroll
+      for (int a = 0; a < 2; ++a)
+#pragma unroll
+         for (int b = 0; b < 4; ++b) { aw[a][b][0] = 0.0; aw[a][b][1] = 0.0; al[a][b][0] = 0.0; al[a][b][1] = 0.0; }
+      {
+         const double* ta = T + r0 * TD_LDT + (lane & 3);
+         const double* xb = Xb + (lane >> 2) * TD_LDT + (lane & 3);
+         const double* x2b = X2b + (lane >> 2) * TD_LDT + (lane & 3);
+#pragma unroll
+         for (int kk = 0; kk < NBI; kk += 4) {
+            double af[2], bf[4], b2f[4];
+#pragma unroll
+            for (int a = 0; a < 2; ++a) af[a] = ta[a * 8 * TD_LDT + kk];
+#pragma unroll
+            for (int b = 0; b < 4; ++b) { bf[b] = xb[b * 8 * TD_LDT + kk]; b2f[b] = x2b[b * 8 * TD_LDT + kk]; }
+#pragma unroll
+            for (int a = 0; a < 2; ++a)
+#pragma unroll
+               for (int b = 0; b < 4; ++b) {
+                  dmma8x8x4(aw[a][b][0], aw[a][b][1], af[a], bf[b]);
+                  dmma8x8x4(al[a][b][0], al[a][b][1], af[a], b2f[b]);
+               }
+         }
+      }
+#pragma unroll
+      for (int a = 0; a < 2; ++a) {
+         const int r = r0 + a * 8;
+         const int i = i0 + r;
+#pragma unroll
+         for (int b = 0; b < 4; ++b)
+#pragma unroll
+            for (int h = 0; h < 2; ++h) {
+               const int c = b * 8 + 2 * (lane & 3) + h;
+               Wsm[r * TD_LDW + kprev + c] = aw[a][b][h];
+               if (i < f && c < nbw) {
+                  A[i + static_cast<int64_t>(ld) * (j0 + c)] = al[a][b][h];
+                  Wp[i + static_cast<int64_t>(ld) * (kprev + c)] = aw[a][b][h];
+               }
+            }
+      }
+   }
+}
+
 // Light variant of kernel A for batches whose fronts have at most NBI pivots (the bulk of the tree):
 // one warp per front, several fronts per CTA would need more shared memory than it saves; 64 threads.
 __global__ void __launch_bounds__(64) k_diag32(FrontArrays F, const int* __restrict__ list, FactorArrays W, const double null_tol) {
@@ -627,9 +831,6 @@ __device__ __forceinline__ void cp_async_commit() { asm volatile("cp.async.commi
 template <int N>
 __device__ __forceinline__ void cp_async_wait() { asm volatile("cp.async.wait_group %0;\n" ::"n"(N)); }
 
-__device__ __forceinline__ void dmma8x8x4(double& c0, double& c1, const double a, const double b) {
-   asm volatile("mma.sync.aligned.m8n8k4.row.col.f64.f64.f64.f64 {%0,%1}, {%2}, {%3}, {%0,%1};\n" : "+d"(c0), "+d"(c1) : "d"(a), "d"(b));
-}
 
 constexpr int UPD_STAGES = 3;
 
@@ -985,39 +1186,63 @@ __global__ void __launch_bounds__(256) k_fwd_big_permute(FrontArrays F, const in
    z2[first + j] = zg[first + W.lperm[first + j]];
 }
 
+constexpr int SD_SMEM = static_cast<int>(sizeof(double)) * ((NBS / NBI) * NBI * (NBI + 1) + NBS);
+
+// prefetch the lower triangle of the NBS x NBS diagonal block of the panel at jp towards L2
+__device__ __forceinline__ void prefetch_diag_block(const double* A, const int ld, const int jp, const int nb) {
+   for (int q = threadIdx.x; q < nb * (NBS / 16); q += blockDim.x) {
+      const int c = q / (NBS / 16), r = (q % (NBS / 16)) * 16;
+      if (r + 15 >= c && r < nb) asm volatile("prefetch.global.L2 [%0];" ::"l"(A + (jp + r) + static_cast<int64_t>(ld) * (jp + c)));
+   }
+}
+
+// all NBI x NBI diagonal blocks (strict lower parts) of the panel into shared memory with one batch of loads
+__device__ __forceinline__ void load_diag_blocks(double* Ls, const double* A, const int ld, const int jp, const int nb) {
+   for (int idx = threadIdx.x; idx < (NBS / NBI) * NBI * NBI; idx += blockDim.x) {
+      const int sb = idx / (NBI * NBI), rr = idx % NBI, c = (idx / NBI) % NBI;
+      const int gr = sb * NBI + rr, gc = sb * NBI + c;
+      Ls[(sb * NBI + rr) * (NBI + 1) + c] = (gr < nb && gc < nb && rr > c) ? A[(jp + gr) + static_cast<int64_t>(ld) * (jp + gc)] : 0.0;
+   }
+}
+
 // One CTA per front: y_P <- L11[P,P]^{-1} y_P for the NBS-wide pivot panel starting at jp.
 __global__ void __launch_bounds__(256) k_fwd_big_diag(FrontArrays F, const int* __restrict__ list, const int jp, FactorArrays W,
                                                        double* __restrict__ z2) {
-   __shared__ double Ls[NBI][NBI + 1];
-   __shared__ double ys[NBS];
+   extern __shared__ __align__(16) double sd_smem[];
+   double* Ls = sd_smem;                                   // [sb][rr][c], row stride NBI + 1
+   double* ys = sd_smem + (NBS / NBI) * NBI * (NBI + 1);
    const int s = list[blockIdx.x];
    const int k = F.k[s], ld = F.ld[s];
    const int nb = min(NBS, k - jp);
    const double* A = W.lpool + F.off[s];
    double* y = z2 + F.first[s] + jp;
    const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
-   if (tid < nb) ys[tid] = y[tid];
+   prefetch_diag_block(A, ld, jp, nb);
+   load_diag_blocks(Ls, A, ld, jp, nb);
+   ys[tid] = (tid < nb) ? y[tid] : 0.0;
+   __syncthreads();
    for (int sb = 0; sb * NBI < nb; ++sb) {
       const int base = sb * NBI;
       const int nbb = min(NBI, nb - base);
-      for (int idx = tid; idx < NBI * NBI; idx += 256) {
-         const int rr = idx % NBI, c = idx / NBI;
-         Ls[rr][c] = (rr < nbb && c < nbb && rr > c) ? A[(jp + base + rr) + static_cast<int64_t>(ld) * (jp + base + c)] : 0.0;
-      }
-      __syncthreads();
       if (warp == 0) {
+         const double* Lb = Ls + base * (NBI + 1);
          double yv = (lane < nbb) ? ys[base + lane] : 0.0;
          for (int c = 0; c < nbb; ++c) {
             const double yc = __shfl_sync(0xffffffffu, yv, c);
-            if (lane > c) yv -= Ls[lane][c] * yc;
+            if (lane > c) yv -= Lb[lane * (NBI + 1) + c] * yc;
          }
          if (lane < nbb) ys[base + lane] = yv;
       }
       __syncthreads();
       const int i = base + nbb + tid;
       if (i < nb) {
+         const double* row = A + (jp + i) + static_cast<int64_t>(ld) * (jp + base);
+         double v[NBI];
+#pragma unroll
+         for (int c = 0; c < NBI; ++c) v[c] = (c < nbb) ? row[static_cast<int64_t>(ld) * c] : 0.0;
          double acc = 0.0;
-         for (int c = 0; c < nbb; ++c) acc += A[(jp + i) + static_cast<int64_t>(ld) * (jp + base + c)] * ys[base + c];
+#pragma unroll
+         for (int c = 0; c < NBI; ++c) acc += v[c] * ys[base + c];
          ys[i] -= acc;
       }
       __syncthreads();
@@ -1044,8 +1269,15 @@ __global__ void __launch_bounds__(256) k_fwd_big_gemv(FrontArrays F, const int* 
    if (i < f) {
       const int c1 = min(nb, q * 64 + 64);
       const double* row = A + i + static_cast<int64_t>(ld) * jp;
-#pragma unroll 4
-      for (int c = q * 64; c < c1; ++c) acc += row[static_cast<int64_t>(ld) * c] * ys[c];
+      int c = q * 64;
+      for (; c + 8 <= c1; c += 8) {
+         double v[8];
+#pragma unroll
+         for (int u = 0; u < 8; ++u) v[u] = row[static_cast<int64_t>(ld) * (c + u)];
+#pragma unroll
+         for (int u = 0; u < 8; ++u) acc += v[u] * ys[c + u];
+      }
+      for (; c < c1; ++c) acc += row[static_cast<int64_t>(ld) * c] * ys[c];
    }
    red[q][tid & 63] = acc;
    __syncthreads();
@@ -1082,50 +1314,77 @@ __global__ void __launch_bounds__(256) k_bwd_big_begin(FrontArrays F, const int*
    }
 }
 
-// y(c) -= sum_{i below the panel} L[i, c] x(i) for the panel columns c.  CTA = 8 columns, one warp each.
+constexpr int BW_SPLITS = 8;   // row splits of the backward panel product (partial sums, reduced in fixed order)
+
+// partial(split, c) = sum over the split's rows i below the panel of L[i, c] x(i), for the panel columns c.
+// grid = (front, NBS / 8 column groups, BW_SPLITS): one warp per column, lanes along the rows (coalesced).
 __global__ void __launch_bounds__(256) k_bwd_big_gemv(FrontArrays F, const int* __restrict__ list, const int jp, FactorArrays W,
-                                                       double* __restrict__ z2, const double* __restrict__ cpool) {
+                                                       const double* __restrict__ z2, const double* __restrict__ cpool,
+                                                       double* __restrict__ partial) {
    const int s = list[blockIdx.x];
    const int k = F.k[s], f = F.f[s], ld = F.ld[s], first = F.first[s];
    const int nb = min(NBS, k - jp);
    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
    const int c = blockIdx.y * 8 + warp;
    if (c >= nb) return;
+   const int rbeg = jp + nb, rows = f - rbeg;
+   const int chunk = ((rows + BW_SPLITS - 1) / BW_SPLITS + 31) & ~31;
+   const int i0 = rbeg + blockIdx.z * chunk, i1 = min(f, i0 + chunk);
    const double* col = W.lpool + F.off[s] + static_cast<int64_t>(ld) * (jp + c);
    const double* y = z2 + first;
    const double* xb = cpool + F.rel_off[s] - k;
    double acc = 0.0;
-   for (int i = jp + nb + lane; i < f; i += 32) acc += col[i] * ((i < k) ? y[i] : xb[i]);
+   int i = i0 + lane;
+   for (; i + 96 < i1; i += 128) {
+      const double l0 = col[i], l1 = col[i + 32], l2 = col[i + 64], l3 = col[i + 96];
+      const double x0 = (i < k) ? y[i] : xb[i], x1 = (i + 32 < k) ? y[i + 32] : xb[i + 32];
+      const double x2 = (i + 64 < k) ? y[i + 64] : xb[i + 64], x3 = (i + 96 < k) ? y[i + 96] : xb[i + 96];
+      acc += l0 * x0 + l1 * x1 + l2 * x2 + l3 * x3;
+   }
+   for (; i < i1; i += 32) acc += col[i] * ((i < k) ? y[i] : xb[i]);
    for (int o = 16; o; o >>= 1) acc += __shfl_xor_sync(0xffffffffu, acc, o);
-   if (lane == 0) z2[first + jp + c] -= acc;
+   if (lane == 0) partial[(static_cast<int64_t>(blockIdx.x) * BW_SPLITS + blockIdx.z) * NBS + c] = acc;
 }
 
-// One CTA per front: x_P <- L11[P,P]^{-T} y_P, sub-blocks from last to first.
+// One CTA per front: y_P -= sum of the partial products, then x_P <- L11[P,P]^{-T} y_P, sub-blocks from last to first.
 __global__ void __launch_bounds__(256) k_bwd_big_diag(FrontArrays F, const int* __restrict__ list, const int jp, FactorArrays W,
-                                                       double* __restrict__ z2) {
-   __shared__ double Ls[NBI][NBI + 1];
-   __shared__ double ys[NBS];
+                                                       double* __restrict__ z2, const double* __restrict__ partial) {
+   extern __shared__ __align__(16) double sd_smem[];
+   double* Ls = sd_smem;
+   double* ys = sd_smem + (NBS / NBI) * NBI * (NBI + 1);
    const int s = list[blockIdx.x];
-   const int k = F.k[s], ld = F.ld[s];
+   const int k = F.k[s], f = F.f[s], ld = F.ld[s];
    const int nb = min(NBS, k - jp);
    const double* A = W.lpool + F.off[s];
    double* y = z2 + F.first[s] + jp;
    const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
-   if (tid < nb) ys[tid] = y[tid];
+   prefetch_diag_block(A, ld, jp, nb);
+   load_diag_blocks(Ls, A, ld, jp, nb);
+   {
+      double v = 0.0;
+      if (tid < nb) {
+         v = y[tid];
+         if (jp + nb < f) {
+            const double* pp = partial + static_cast<int64_t>(blockIdx.x) * BW_SPLITS * NBS + tid;
+            double sum = 0.0;
+#pragma unroll
+            for (int q = 0; q < BW_SPLITS; ++q) sum += pp[q * NBS];
+            v -= sum;
+         }
+      }
+      ys[tid] = v;
+   }
+   __syncthreads();
    const int nsb = (nb + NBI - 1) / NBI;
    for (int sb = nsb - 1; sb >= 0; --sb) {
       const int base = sb * NBI;
       const int nbb = min(NBI, nb - base);
-      for (int idx = tid; idx < NBI * NBI; idx += 256) {
-         const int rr = idx % NBI, c = idx / NBI;
-         Ls[rr][c] = (rr < nbb && c < nbb && rr > c) ? A[(jp + base + rr) + static_cast<int64_t>(ld) * (jp + base + c)] : 0.0;
-      }
-      __syncthreads();
       if (warp == 0) {
+         const double* Lb = Ls + base * (NBI + 1);
          double yv = (lane < nbb) ? ys[base + lane] : 0.0;
          for (int c = nbb - 1; c >= 0; --c) {
             const double yc = __shfl_sync(0xffffffffu, yv, c);
-            if (lane < c) yv -= Ls[c][lane] * yc;
+            if (lane < c) yv -= Lb[c * (NBI + 1) + lane] * yc;
          }
          if (lane < nbb) ys[base + lane] = yv;
       }
@@ -1133,8 +1392,12 @@ __global__ void __launch_bounds__(256) k_bwd_big_diag(FrontArrays F, const int* 
       // earlier columns of the panel: y(c) -= sum_t L[base+t, c] x(base+t)
       if (tid < base) {
          const double* col = A + (jp + base) + static_cast<int64_t>(ld) * (jp + tid);
+         double v[NBI];
+#pragma unroll
+         for (int t = 0; t < NBI; ++t) v[t] = (t < nbb) ? col[t] : 0.0;
          double acc = 0.0;
-         for (int t = 0; t < nbb; ++t) acc += col[t] * ys[base + t];
+#pragma unroll
+         for (int t = 0; t < NBI; ++t) acc += v[t] * ys[base + t];
          ys[tid] -= acc;
       }
       __syncthreads();
@@ -1199,10 +1462,15 @@ int launch_trsmpanel(const FrontArrays& F, const int* d_list, int nfronts, int m
                      cudaStream_t st) {
    if (nfronts <= 0) return 0;
    // a front of the list has k > J0: its rows below the diagonal block start at J0 + 1 at the earliest
-   const int chunks = (max_f - (J0 + 1) + TP_THREADS - 1) / TP_THREADS;
-   if (chunks < 1) return 0;
-   dim3 grid(nfronts, chunks);
-   k_trsmpanel<<<grid, TP_THREADS, max_k <= NBI ? TP_SMEM_BASE : TP_SMEM, st>>>(F, d_list, J0, W);
+   const int rows = max_f - (J0 + 1);
+   if (rows < 1) return 0;
+   if (max_k <= NBI) {
+      dim3 grid(nfronts, (rows + TP_THREADS - 1) / TP_THREADS);
+      k_trsmpanel<<<grid, TP_THREADS, TP_SMEM_BASE, st>>>(F, d_list, J0, W);
+   } else {
+      dim3 grid(nfronts, (rows + TD_ROWS - 1) / TD_ROWS);
+      k_trsmpanel_mma<<<grid, TD_THREADS, TD_SMEM, st>>>(F, d_list, J0, W);
+   }
    return 1;
 }
 
@@ -1216,6 +1484,48 @@ int launch_permute_rows(const FrontArrays& F, const int* d_list, int nfronts, in
 
 namespace {
 constexpr int smem_bytes(int bm, int bn, int bk) { return UPD_STAGES * bk * (bm + 4 + bn + 4) * static_cast<int>(sizeof(double)); }
+}
+
+// micro-benchmark: one warp factors the same random symmetric 32 x 32 block `reps` times; cycles per factorization
+__global__ void k_bench_bk(const double* __restrict__ M, int reps, long long* cycles, double* sink) {
+   __shared__ BkShared S;
+   const int lane = threadIdx.x;
+   long long total = 0;
+   double acc = 0.0;
+   for (int r = 0; r < reps; ++r) {
+      for (int c = 0; c < NBI; ++c) S.B[lane][c] = M[lane * NBI + c];
+      __syncwarp();
+      const long long t0 = clock64();
+      bk_factor_block(S, NBI, lane, 1e-14);
+      total += clock64() - t0;
+      acc += S.d[lane] + S.B[lane][(lane + 5) & 31];
+      __syncwarp();
+   }
+   sink[lane] = acc;
+   if (lane == 0) *cycles = total / reps;
+}
+
+int debug_bench_bk(int variant, int reps, long long* cycles_out, int* n2x2) {
+   double h[NBI * NBI];
+   unsigned long long sd = 1234567ull + 977ull * static_cast<unsigned long long>(variant);
+   auto rnd = [&] { sd ^= sd << 13; sd ^= sd >> 7; sd ^= sd << 17; return (static_cast<double>(sd >> 11) / 9007199254740992.0) - 0.5; };
+   for (int i = 0; i < NBI; ++i)
+      for (int j = 0; j <= i; ++j) {
+         double v = rnd();
+         if (variant == 0 && i == j) v += 20.0;                    // diagonally dominant: 1x1 pivots, no interchanges
+         if (variant == 1 && i == j) v = (i & 1) ? 1e-9 * v : v;   // KKT-like: every second diagonal tiny
+         h[i * NBI + j] = v; h[j * NBI + i] = v;
+      }
+   double *dM, *dsink; long long* dc;
+   cudaMalloc(reinterpret_cast<void**>(&dM), sizeof(h)); cudaMalloc(reinterpret_cast<void**>(&dsink), 32 * sizeof(double));
+   cudaMalloc(reinterpret_cast<void**>(&dc), sizeof(long long));
+   cudaMemcpy(dM, h, sizeof(h), cudaMemcpyHostToDevice);
+   k_bench_bk<<<1, 32>>>(dM, reps, dc, dsink);
+   k_bench_bk<<<1, 32>>>(dM, reps, dc, dsink);
+   cudaMemcpy(cycles_out, dc, sizeof(long long), cudaMemcpyDeviceToHost);
+   if (n2x2 != nullptr) *n2x2 = 0;
+   cudaFree(dM); cudaFree(dsink); cudaFree(dc);
+   return cudaGetLastError() == cudaSuccess ? 0 : -1;
 }
 
 int debug_phase_cycles(unsigned long long* out16, bool reset) {
@@ -1232,7 +1542,13 @@ int debug_phase_cycles(unsigned long long* out16, bool reset) {
 int init_kernel_attributes() {
    cudaError_t e = cudaFuncSetAttribute(k_diagpanel, cudaFuncAttributeMaxDynamicSharedMemorySize, DP_SMEM);
    if (e != cudaSuccess) return static_cast<int>(e);
+   e = cudaFuncSetAttribute(k_fwd_big_diag, cudaFuncAttributeMaxDynamicSharedMemorySize, SD_SMEM);
+   if (e != cudaSuccess) return static_cast<int>(e);
+   e = cudaFuncSetAttribute(k_bwd_big_diag, cudaFuncAttributeMaxDynamicSharedMemorySize, SD_SMEM);
+   if (e != cudaSuccess) return static_cast<int>(e);
    e = cudaFuncSetAttribute(k_trsmpanel, cudaFuncAttributeMaxDynamicSharedMemorySize, TP_SMEM);
+   if (e != cudaSuccess) return static_cast<int>(e);
+   e = cudaFuncSetAttribute(k_trsmpanel_mma, cudaFuncAttributeMaxDynamicSharedMemorySize, TD_SMEM);
    if (e != cudaSuccess) return static_cast<int>(e);
    e = cudaFuncSetAttribute(k_update<128, 128, 2, 4, 32>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem_bytes(128, 128, 32));
    if (e != cudaSuccess) return static_cast<int>(e);
@@ -1297,7 +1613,7 @@ int launch_fwd_big_permute(const FrontArrays& F, const int* d_list, int nfronts,
 
 int launch_fwd_big_diag(const FrontArrays& F, const int* d_list, int nfronts, int jp, const FactorArrays& W, double* z2, cudaStream_t st) {
    if (nfronts <= 0) return 0;
-   k_fwd_big_diag<<<nfronts, 256, 0, st>>>(F, d_list, jp, W, z2);
+   k_fwd_big_diag<<<nfronts, 256, SD_SMEM, st>>>(F, d_list, jp, W, z2);
    return 1;
 }
 
@@ -1320,18 +1636,21 @@ int launch_bwd_big_begin(const FrontArrays& F, const int* d_list, int nfronts, i
 }
 
 int launch_bwd_big_gemv(const FrontArrays& F, const int* d_list, int nfronts, int jp, const FactorArrays& W, double* z2,
-                        const double* cpool, cudaStream_t st) {
+                        const double* cpool, double* partial, cudaStream_t st) {
    if (nfronts <= 0) return 0;
-   dim3 grid(nfronts, NBS / 8);
-   k_bwd_big_gemv<<<grid, 256, 0, st>>>(F, d_list, jp, W, z2, cpool);
+   dim3 grid(nfronts, NBS / 8, BW_SPLITS);
+   k_bwd_big_gemv<<<grid, 256, 0, st>>>(F, d_list, jp, W, z2, cpool, partial);
    return 1;
 }
 
-int launch_bwd_big_diag(const FrontArrays& F, const int* d_list, int nfronts, int jp, const FactorArrays& W, double* z2, cudaStream_t st) {
+int launch_bwd_big_diag(const FrontArrays& F, const int* d_list, int nfronts, int jp, const FactorArrays& W, double* z2,
+                        const double* partial, cudaStream_t st) {
    if (nfronts <= 0) return 0;
-   k_bwd_big_diag<<<nfronts, 256, 0, st>>>(F, d_list, jp, W, z2);
+   k_bwd_big_diag<<<nfronts, 256, SD_SMEM, st>>>(F, d_list, jp, W, z2, partial);
    return 1;
 }
+
+int bwd_partial_doubles_per_front() { return BW_SPLITS * NBS; }
 
 int launch_bwd_big_scatter(const FrontArrays& F, const int* d_list, int nfronts, int max_k, const FactorArrays& W, const double* z2,
                            double* xg, cudaStream_t st) {

@@ -9,6 +9,8 @@ namespace b200kkt {
 constexpr int NBI = 32;    // inner block: pivot search window of the in-front Bunch-Kaufman
 constexpr int NBO = 256;   // outer panel: K of the trailing FP64 tensor-core update
 constexpr int NBS = 256;   // panel width of the multi-CTA triangular solves
+// per front with more than NBI pivots, behind its W panel: X = L11^{-1} and X2 = D^{-1} L11^{-1} of every inner block of the current outer panel
+constexpr int XINV_DOUBLES = 2 * (NBO / NBI) * NBI * NBI;
 
 // device-resident integer plan (SoA over fronts)
 struct FrontArrays {
@@ -80,6 +82,8 @@ int launch_update(const FrontArrays& F, const int* d_list, int nfronts, int max_
 int init_kernel_attributes();
 // phase cycle counters of the panel kernels (only when built with -DB200KKT_PHASES); returns 0 when not compiled in
 int debug_phase_cycles(unsigned long long* out16, bool reset);
+// micro-benchmark of the 32 x 32 Bunch-Kaufman block kernel: cycles per block (variant 0 dominant diagonal, 1 KKT-like, 2 random)
+int debug_bench_bk(int variant, int reps, long long* cycles_out, int* n2x2);
 // K6 inertia from the D blocks: counters[0..4] = positive, negative, zero, number of 2x2, unused
 int launch_inertia(int64_t n, const FactorArrays& W, int* counters, cudaStream_t st);
 
@@ -99,8 +103,10 @@ int launch_fwd_big_gemv(const FrontArrays& F, const int* d_list, int nfronts, in
 int launch_bwd_big_begin(const FrontArrays& F, const int* d_list, int nfronts, int max_f, const FactorArrays& W, double* z2,
                          const double* xg, double* cpool, cudaStream_t st);
 int launch_bwd_big_gemv(const FrontArrays& F, const int* d_list, int nfronts, int jp, const FactorArrays& W, double* z2,
-                        const double* cpool, cudaStream_t st);
-int launch_bwd_big_diag(const FrontArrays& F, const int* d_list, int nfronts, int jp, const FactorArrays& W, double* z2, cudaStream_t st);
+                        const double* cpool, double* partial, cudaStream_t st);
+int launch_bwd_big_diag(const FrontArrays& F, const int* d_list, int nfronts, int jp, const FactorArrays& W, double* z2,
+                        const double* partial, cudaStream_t st);
+int bwd_partial_doubles_per_front();   // size of the partial-sum scratch of the backward panel product, per front of a level
 int launch_bwd_big_scatter(const FrontArrays& F, const int* d_list, int nfronts, int max_k, const FactorArrays& W, const double* z2,
                            double* xg, cudaStream_t st);
 // permute+scale in, scale+permute out (accumulating into x)

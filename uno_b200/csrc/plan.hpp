@@ -21,6 +21,8 @@ struct AnalyseOptions {
    double relax_big_zeros = 0.15;
    double relax_any_zeros = 0.03;
    const int64_t* user_perm = nullptr;   // ordering == 2: perm[new] = old, length N
+   // METIS_NodeND tuning (0 = METIS default): separators tried per bisection, refinement iterations, allowed imbalance (1/1000)
+   int metis_nseps = 0, metis_niter = 0, metis_ufactor = 0;
 };
 
 struct Plan {

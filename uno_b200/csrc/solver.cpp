@@ -114,11 +114,17 @@ void build_batches(b200kkt_handle* h, std::vector<int>& batch_list, std::vector<
             b.max_k = std::max(b.max_k, P.k[s]);
             if (P.child_ptr[s + 1] > P.child_ptr[s]) b.has_children = true;
             if (P.f[s] > P.k[s]) b.has_cb = true;
-            woff[s] = level_w;
-            level_w += static_cast<int64_t>(P.ld[s]) * std::min(NBO, (P.k[s] + 3) & ~3);
             ++i;
          }
          b.count = static_cast<int>(b.k.size());
+         // W panels; a batch that runs the panel kernels (some front with more than NBI pivots) also gets room for the
+         // inverted diagonal blocks of the current outer panel behind every W panel
+         for (int t = 0; t < b.count; ++t) {
+            const int s = batch_list[static_cast<size_t>(b.begin + t)];
+            woff[s] = level_w;
+            level_w += static_cast<int64_t>(P.ld[s]) * std::min(NBO, (P.k[s] + 3) & ~3);
+            if (b.max_k > NBI) level_w += XINV_DOUBLES;
+         }
          b.big_tiles = b.max_f > 256;
          h->batches.push_back(std::move(b));
       }
@@ -183,6 +189,9 @@ void upload_plan(b200kkt_handle* h) {
          }
       }
       h->d_solve_list = dev_upload(h, solve_list);
+      int max_big = 1;
+      for (const auto& SL : h->solve_levels) max_big = std::max(max_big, SL.big_count);
+      h->d_partial = dev_alloc<double>(h, static_cast<size_t>(max_big) * bwd_partial_doubles_per_front());
    }
 
    h->M.ndst = static_cast<int64_t>(P.asm_dst.size());
@@ -430,8 +439,8 @@ void run_solve(b200kkt_handle* h, const double* d_b, double* d_x, double* backwa
             const int last = ((SL.big_max_k - 1) / NBS) * NBS;
             for (int jp = last; jp >= 0; jp -= NBS) {
                const int nf = count_greater(SL.big_k, jp);
-               L += launch_bwd_big_gemv(h->F, list, nf, jp, h->W, h->d_z2, h->d_cpool, st);
-               L += launch_bwd_big_diag(h->F, list, nf, jp, h->W, h->d_z2, st);
+               L += launch_bwd_big_gemv(h->F, list, nf, jp, h->W, h->d_z2, h->d_cpool, h->d_partial, st);
+               L += launch_bwd_big_diag(h->F, list, nf, jp, h->W, h->d_z2, h->d_partial, st);
             }
             L += launch_bwd_big_scatter(h->F, list, SL.big_count, SL.big_max_k, h->W, h->d_z2, h->d_xg, st);
          }
@@ -569,6 +578,9 @@ int b200kkt_set_option(b200kkt_handle* h, const char* name, double value) {
    else if (n == "relax_mid_zeros") h->aopt.relax_mid_zeros = value;
    else if (n == "relax_big_zeros") h->aopt.relax_big_zeros = value;
    else if (n == "relax_any_zeros") h->aopt.relax_any_zeros = value;
+   else if (n == "metis_nseps") h->aopt.metis_nseps = static_cast<int>(value);
+   else if (n == "metis_niter") h->aopt.metis_niter = static_cast<int>(value);
+   else if (n == "metis_ufactor") h->aopt.metis_ufactor = static_cast<int>(value);
    else if (n == "scaling_sweeps") h->scaling_sweeps = std::max(0, static_cast<int>(value));
    else if (n == "null_pivot_tol") h->null_pivot_tol = value;
    else if (n == "refine_max_steps") h->refine_max_steps = std::max(0, static_cast<int>(value));
@@ -845,3 +857,5 @@ extern "C" int b200kkt_debug_bench_update(int device, int f, int k, int reps, in
 }
 
 extern "C" int b200kkt_debug_phase_cycles(unsigned long long* out16, int reset) { return debug_phase_cycles(out16, reset != 0); }
+
+extern "C" int b200kkt_debug_bench_bk(int variant, int reps, long long* cycles) { return debug_bench_bk(variant, reps, cycles, nullptr); }

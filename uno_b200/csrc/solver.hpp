@@ -87,6 +87,7 @@ struct b200kkt_handle {
    double* d_z2 = nullptr;
    double* d_xg = nullptr;
    double* d_cpool = nullptr;
+   double* d_partial = nullptr;            // partial sums of the backward panel products
    double* d_b = nullptr;
    double* d_x = nullptr;
    double* d_r = nullptr;

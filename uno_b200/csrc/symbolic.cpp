@@ -84,15 +84,21 @@ void kkt_pairing(int64_t N, const Graph& g, const std::vector<char>& is_con, std
    partner.assign(static_cast<size_t>(N), -1);
    auto degree = [&](int32_t v) { return g.ptr[v + 1] - g.ptr[v]; };
    std::vector<int32_t> unmatched;
+   int64_t first_con = 0;
+   while (first_con < N && !is_con[first_con]) ++first_con;
    for (int64_t j = 0; j < N; ++j) {
       if (!is_con[j]) continue;
+      // lowest primal degree first; ties go to the primal whose index is closest to the constraint's ordinal
+      // (states and their equations are usually numbered alike, which keeps the compressed graph grid-like)
       int32_t best = -1;
-      int64_t best_deg = 0;
+      int64_t best_deg = 0, best_dist = 0;
+      const int64_t ordinal = j - first_con;
       for (int64_t p = g.ptr[j]; p < g.ptr[j + 1]; ++p) {
          const int32_t v = g.idx[p];
          if (is_con[v] || partner[v] != -1) continue;
          const int64_t d = degree(v);
-         if (best == -1 || d < best_deg) { best = v; best_deg = d; }
+         const int64_t dist = (v > ordinal) ? v - ordinal : ordinal - v;
+         if (best == -1 || d < best_deg || (d == best_deg && dist < best_dist)) { best = v; best_deg = d; best_dist = dist; }
       }
       if (best != -1) { partner[j] = best; partner[best] = static_cast<int32_t>(j); }
       else unmatched.push_back(static_cast<int32_t>(j));
@@ -225,6 +231,10 @@ void analyse(int64_t N, int64_t nnz, int64_t reg_size, int64_t num_primal, const
       if (!adjncy.empty()) {
          std::vector<int64_t> options(40), mperm(static_cast<size_t>(cN)), miperm(static_cast<size_t>(cN));
          METIS_SetDefaultOptions(options.data());
+         // option slots of METIS 5.1 (metis.h: NITER = 6, NSEPS = 15, UFACTOR = 16)
+         if (opt.metis_niter > 0) options[6] = opt.metis_niter;
+         if (opt.metis_nseps > 0) options[15] = opt.metis_nseps;
+         if (opt.metis_ufactor > 0) options[16] = opt.metis_ufactor;
          int64_t n = cN;
          const int rc = METIS_NodeND(&n, xadj.data(), adjncy.data(), vwgt.data(), options.data(), mperm.data(), miperm.data());
          if (rc == 1) { corder = mperm; P.ordering_used = "metis_nodend"; }
