@@ -162,8 +162,12 @@ __global__ void __launch_bounds__(256) k_prepare(FrontArrays F, const int* __res
 // ------------------------------------------------------------------------------------------------
 // K3 panel kernels
 // ------------------------------------------------------------------------------------------------
-struct BkShared {
-   double B[NBI][NBI + 1];   // full symmetric diagonal block; after factorization: strict lower = L11
+__device__ __forceinline__ void dmma8x8x4(double& c0, double& c1, const double a, const double b) {
+   asm volatile("mma.sync.aligned.m8n8k4.row.col.f64.f64.f64.f64 {%0,%1}, {%2}, {%3}, {%0,%1};\n" : "+d"(c0), "+d"(c1) : "d"(a), "d"(b));
+}
+
+struct alignas(16) BkShared {
+   double B[NBI][NBI + 2];   // full symmetric diagonal block (rows 16-byte aligned); after factorization: strict lower = L11
    double d[NBI], e[NBI];
    int p[NBI], type[NBI];
    int nontrivial;
@@ -194,23 +198,33 @@ __device__ __forceinline__ double warp_max(const double v) {
 
 // Bunch-Kaufman (partial pivoting, pivot search confined to this block) by one warp.
 // Null pivots (whole remaining column <= tol) are dropped MUMPS-style: unit pivot, zero column,
-// reported as a zero eigenvalue.  Lane i owns row i of the block; the rank-1/rank-2 updates read
-// the pivot column(s) and the own row into registers first and store afterwards, so that the
-// shared-memory traffic of one step is pipelined instead of a chain of dependent round trips.
+// reported as a zero eigenvalue.
+// Lane i keeps row i of the (full, symmetric) Schur complement in registers; shared memory holds the mirror
+// M[c][i] = a_i[c] (conflict-free stores), which by symmetry is also the matrix itself.  Everything indexed by a
+// run-time column (pivot search, pivot row broadcast, interchanges) goes through the mirror, everything indexed
+// statically through the registers: one elimination step costs 16 broadcast 128-bit loads, 32 fused
+// multiply-adds and 32 stores per lane instead of 64 loads + 32 stores, and the division overlaps the loads.
+// During the factorization column j of L lives in M[j][i] (i > j); the block is transposed at the end so that
+// callers find L11 in the strict lower triangle S.B[i][j].
 __device__ void bk_factor_block(BkShared& S, const int n, const int lane, const double tol) {
    S.p[lane] = lane;
    S.d[lane] = 1.0;
    S.e[lane] = 0.0;
    S.type[lane] = 0;
    if (lane == 0) S.nontrivial = 0;
+   double a[NBI];
+#pragma unroll
+   for (int c = 0; c < NBI; ++c) a[c] = S.B[c][lane];
    __syncwarp();
    int j = 0;
    PHASE_BEGIN();
    while (j < n) {
       PHASE_MARK(8);
+      const bool below = lane > j && lane < n;
+      const double vj = S.B[j][lane];
       const double absajj = fabs(S.B[j][j]);
       // lambda = largest off-diagonal magnitude of column j, r = its first row
-      const double v = (lane > j && lane < n) ? fabs(S.B[lane][j]) : -1.0;
+      const double v = below ? fabs(vj) : -1.0;
       double lam = warp_max(v);
       int r = j;
       if (lam >= 0.0) r = __ffs(__ballot_sync(0xffffffffu, v == lam)) - 1; else lam = 0.0;
@@ -221,7 +235,7 @@ __device__ void bk_factor_block(BkShared& S, const int n, const int lane, const 
       } else if (absajj >= BK_ALPHA * lam) {
          // 1x1 pivot, no interchange
       } else {
-         const double sigma = warp_max((lane >= j && lane < n && lane != r) ? fabs(S.B[lane][r]) : -1.0);
+         const double sigma = warp_max((lane >= j && lane < n && lane != r) ? fabs(S.B[r][lane]) : -1.0);
          if (absajj * sigma >= BK_ALPHA * lam * lam) {
             // 1x1 pivot, no interchange
          } else if (fabs(S.B[r][r]) >= BK_ALPHA * sigma) {
@@ -234,7 +248,7 @@ __device__ void bk_factor_block(BkShared& S, const int n, const int lane, const 
       PHASE_MARK(9);
       const int kk = j + step - 1;
       if (kp != kk) {
-         // symmetric interchange kk <-> kp on the full block (rows carry the already computed L entries)
+         // symmetric interchange kk <-> kp on the mirror (its columns carry the already computed L rows), then reload the rows
          double t1 = S.B[kk][lane], t2 = S.B[kp][lane];
          S.B[kk][lane] = t2;
          S.B[kp][lane] = t1;
@@ -250,46 +264,53 @@ __device__ void bk_factor_block(BkShared& S, const int n, const int lane, const 
             S.nontrivial = 1;
          }
          __syncwarp();
+#pragma unroll
+         for (int c = 0; c < NBI; ++c) a[c] = S.B[c][lane];
       }
       PHASE_MARK(10);
       if (step == 1) {
          const double d = S.B[j][j];
          if (isnull) {
-            if (lane > j) S.B[lane][j] = 0.0;
+            __syncwarp();
+            if (lane > j) S.B[j][lane] = 0.0;
             if (lane == 0) { S.d[j] = 1.0; S.e[j] = 0.0; S.type[j] = 3; }
          } else {
-            const bool act = lane > j && lane < n;
-            const double li = S.B[lane][j] / d;
-            double col[NBI], row[NBI];
+            const double li = below ? S.B[j][lane] / d : 0.0;
+            const double2* prow = reinterpret_cast<const double2*>(S.B[j]);
 #pragma unroll
-            for (int c = 0; c < NBI; ++c) col[c] = S.B[c][j];
+            for (int c = 0; c < NBI; c += 2) {
+               const double2 pc = prow[c >> 1];
+               a[c] = a[c] - li * pc.x;
+               a[c + 1] = a[c + 1] - li * pc.y;
+            }
+            __syncwarp();   // every lane has read the pivot row before the L column replaces it
 #pragma unroll
-            for (int c = 0; c < NBI; ++c) row[c] = S.B[lane][c];
-            __syncwarp();
-#pragma unroll
-            for (int c = 0; c < NBI; ++c) if (act && c > j && c < n) S.B[lane][c] = row[c] - li * col[c];
-            if (act) S.B[lane][j] = li;
+            for (int c = 0; c < NBI; ++c) if (below && c > j && c < n) S.B[c][lane] = a[c];
+            if (below) S.B[j][lane] = li;
             if (lane == 0) { S.d[j] = d; S.e[j] = 0.0; S.type[j] = 0; }
          }
       } else {
-         const double a = S.B[j][j], b = S.B[j + 1][j], c = S.B[j + 1][j + 1];
-         const double det = a * c - b * b;
+         const double pa = S.B[j][j], pb = S.B[j][j + 1], pc = S.B[j + 1][j + 1];
+         const double det = pa * pc - pb * pb;
          const bool act = lane > j + 1 && lane < n;
-         const double w1 = S.B[lane][j], w2 = S.B[lane][j + 1];
-         const double l1 = (c * w1 - b * w2) / det;
-         const double l2 = (a * w2 - b * w1) / det;
-         double col1[NBI], col2[NBI], row[NBI];
+         const double w1 = S.B[j][lane], w2 = S.B[j + 1][lane];
+         const double l1 = act ? (pc * w1 - pb * w2) / det : 0.0;
+         const double l2 = act ? (pa * w2 - pb * w1) / det : 0.0;
+         const double2* prow1 = reinterpret_cast<const double2*>(S.B[j]);
+         const double2* prow2 = reinterpret_cast<const double2*>(S.B[j + 1]);
 #pragma unroll
-         for (int cc = 0; cc < NBI; ++cc) { col1[cc] = S.B[cc][j]; col2[cc] = S.B[cc][j + 1]; }
-#pragma unroll
-         for (int cc = 0; cc < NBI; ++cc) row[cc] = S.B[lane][cc];
+         for (int cc = 0; cc < NBI; cc += 2) {
+            const double2 c1 = prow1[cc >> 1], c2 = prow2[cc >> 1];
+            a[cc] = a[cc] - (l1 * c1.x + l2 * c2.x);
+            a[cc + 1] = a[cc + 1] - (l1 * c1.y + l2 * c2.y);
+         }
          __syncwarp();
 #pragma unroll
-         for (int cc = 0; cc < NBI; ++cc) if (act && cc > j + 1 && cc < n) S.B[lane][cc] = row[cc] - (l1 * col1[cc] + l2 * col2[cc]);
-         if (act) { S.B[lane][j] = l1; S.B[lane][j + 1] = l2; }
+         for (int cc = 0; cc < NBI; ++cc) if (act && cc > j + 1 && cc < n) S.B[cc][lane] = a[cc];
+         if (act) { S.B[j][lane] = l1; S.B[j + 1][lane] = l2; }
          if (lane == 0) {
-            S.B[j + 1][j] = 0.0;
-            S.d[j] = a; S.d[j + 1] = c; S.e[j] = b; S.e[j + 1] = 0.0;
+            S.B[j][j + 1] = 0.0;
+            S.d[j] = pa; S.d[j + 1] = pc; S.e[j] = pb; S.e[j + 1] = 0.0;
             S.type[j] = 1; S.type[j + 1] = 2;
          }
       }
@@ -297,6 +318,13 @@ __device__ void bk_factor_block(BkShared& S, const int n, const int lane, const 
       PHASE_MARK(step == 1 ? 11 : 12);
       j += step;
    }
+   // transpose: S.B[i][c] = L(i, c) for c < i
+#pragma unroll
+   for (int c = 0; c < NBI; ++c) a[c] = S.B[c][lane];
+   __syncwarp();
+#pragma unroll
+   for (int c = 0; c < NBI; ++c) S.B[lane][c] = a[c];
+   __syncwarp();
 }
 
 // Lane t computes column t of X = L11^{-1} (unit lower triangular, strict lower part in S.B) by forward
@@ -372,142 +400,447 @@ __device__ __forceinline__ void row_trsm(double (&w)[NBI], double (&l)[NBI], con
    }
 }
 
-constexpr int DP_THREADS = 256;
-constexpr int DP_LD = NBO - NBI + 4;   // rows of the in-panel W/L staging (c-major: [c][row])
-constexpr int DP_SMEM = static_cast<int>(sizeof(BkShared)) + 16 + (2 * NBI * DP_LD + 2 * NBI * (NBI + 1)) * static_cast<int>(sizeof(double));
+// ------------------------------------------------------------------------------------------------
+// Kernel A of a panel step, warp-specialised.
+//   warps 0-3 ("pivot group"): Bunch-Kaufman of one NBI x NBI inner block after the other, the inverse
+//     X = L11^{-1} carried along by the same row operations, X2 = D^{-1} X;
+//   warps 4-7 ("update group"): for the block just factored, the rows of the NBO x NBO diagonal block
+//     below it (w = a X^T, l = a X2^T) and the rank-NBI update of the rest of the diagonal block, both on
+//     the FP64 tensor pipe; the next inner block is updated first and handed to the pivot group through
+//     shared memory, so the Bunch-Kaufman chain - the latency-bound critical path - never waits for the bulk.
+// Named barriers: 1 pivot group, 2 "X of block b ready", 3 "diagonal block b+1 ready", 4 update group.
+// ------------------------------------------------------------------------------------------------
+constexpr int BK4_THREADS = 128;
+constexpr int XB_LD = NBI + 4;   // row stride of the X / X2 blocks: conflict-free B fragments
 
-// Kernel A of a panel step.  One CTA per front factors the NBO x NBO diagonal block of the outer
-// panel starting at pivot column J0, in place: for every NBI-wide inner block Bunch-Kaufman (one
-// warp), interchanges applied to the panel's earlier L columns, triangular solve of the rows of the
-// diagonal block below it, and the update of the rest of the diagonal block.  Rows below the
-// diagonal block are left to k_trsmpanel.
+struct alignas(16) Bk4Shared {
+   double B[NBI][NBI + 2];    // mirror M[c][i] = row i, column c of the (symmetric) Schur complement
+   double Lm[NBI][NBI + 2];   // Lm[j][i] = L(i, j)
+   double d[NBI], e[NBI];
+   int p[NBI], type[NBI];
+   int nontrivial;
+};
+
+template <int ID, int COUNT>
+__device__ __forceinline__ void named_sync() { asm volatile("bar.sync %0, %1;" ::"n"(ID), "n"(COUNT) : "memory"); }
+template <int ID, int COUNT>
+__device__ __forceinline__ void named_arrive() { asm volatile("bar.arrive %0, %1;" ::"n"(ID), "n"(COUNT) : "memory"); }
+
+// branch-free reciprocal / quotient for normal arguments well inside the exponent range (accepted pivots
+// exceed the null-pivot tolerance in the equilibrated matrix); the quotient carries one correction step
+__device__ __forceinline__ double fast_rcp(const double d) {
+   double r;
+   asm("rcp.approx.ftz.f64 %0, %1;" : "=d"(r) : "d"(d));
+   r = fma(fma(-d, r, 1.0), r, r);
+   r = fma(fma(-d, r, 1.0), r, r);
+   return r;
+}
+__device__ __forceinline__ double fast_div(const double x, const double d, const double r) {
+   const double q = x * r;
+   return fma(fma(-q, d, x), r, q);
+}
+
+// Bunch-Kaufman by four warps: lane i owns row i, warp w the columns [8w, 8w + 8) of the Schur complement
+// (registers a[]) and of the inverse (registers x[]).  The mirror in shared memory serves everything that is
+// indexed by a run-time column: pivot search, pivot row broadcast, interchanges.  One barrier per step.
+__device__ void bk_factor_block4(Bk4Shared& S, const int n, const int tid, const double tol, double (&x)[8]) {
+   const int lane = tid & 31, w = tid >> 5, c0 = 8 * w;
+   if (w == 0) {
+      S.p[lane] = lane; S.d[lane] = 1.0; S.e[lane] = 0.0; S.type[lane] = 0;
+      if (lane == 0) S.nontrivial = 0;
+   }
+   double a[8];
+#pragma unroll
+   for (int c = 0; c < 8; ++c) {
+      a[c] = S.B[c0 + c][lane];
+      x[c] = (c0 + c == lane) ? 1.0 : 0.0;
+   }
+   named_sync<1, BK4_THREADS>();
+   int j = 0;
+   while (j < n) {
+      const bool below = lane > j && lane < n;
+      const double vj = S.B[j][lane];
+      const double djj = S.B[j][j];
+      double rd = fast_rcp(djj);
+      const double absajj = fabs(djj);
+      // lambda = largest off-diagonal magnitude of column j, r = its first row
+      const double v = below ? fabs(vj) : -1.0;
+      double lam = warp_max(v);
+      int r = j;
+      if (lam >= 0.0) r = __ffs(__ballot_sync(0xffffffffu, v == lam)) - 1; else lam = 0.0;
+      int kp = j, step = 1;
+      bool isnull = false, looked = false;
+      if (!(fmax(absajj, lam) > tol)) {
+         isnull = true;
+      } else if (absajj >= BK_ALPHA * lam) {
+         // 1x1 pivot, no interchange
+      } else {
+         looked = true;
+         const double sigma = warp_max((lane >= j && lane < n && lane != r) ? fabs(S.B[r][lane]) : -1.0);
+         if (absajj * sigma >= BK_ALPHA * lam * lam) {
+            // 1x1 pivot, no interchange
+         } else if (fabs(S.B[r][r]) >= BK_ALPHA * sigma) {
+            kp = r;
+         } else {
+            kp = r;
+            step = 2;
+         }
+      }
+      const int kk = j + step - 1;
+      if (kp != kk) {
+         named_sync<1, BK4_THREADS>();   // every warp is done reading the block for the search
+         if (w == 0) {
+            // symmetric interchange kk <-> kp on the mirror; the L rows follow
+            double t1 = S.B[kk][lane], t2 = S.B[kp][lane];
+            S.B[kk][lane] = t2;
+            S.B[kp][lane] = t1;
+            __syncwarp();
+            t1 = S.B[lane][kk];
+            t2 = S.B[lane][kp];
+            S.B[lane][kk] = t2;
+            S.B[lane][kp] = t1;
+            t1 = S.Lm[lane][kk];
+            t2 = S.Lm[lane][kp];
+            S.Lm[lane][kk] = t2;
+            S.Lm[lane][kp] = t1;
+            if (lane == 0) {
+               const int tp = S.p[kk];
+               S.p[kk] = S.p[kp];
+               S.p[kp] = tp;
+               S.nontrivial = 1;
+            }
+         }
+         // rows kk and kp of the inverse: only the columns < j differ from the identity
+         if (c0 < j) {
+            const int partner = (lane == kk) ? kp : ((lane == kp) ? kk : lane);
+#pragma unroll
+            for (int c = 0; c < 8; ++c) {
+               const double other = __shfl_sync(0xffffffffu, x[c], partner);
+               if (c0 + c < j) x[c] = other;
+            }
+         }
+         named_sync<1, BK4_THREADS>();
+#pragma unroll
+         for (int c = 0; c < 8; ++c) a[c] = S.B[c0 + c][lane];
+         if (step == 1) rd = fast_rcp(S.B[j][j]);
+      } else if (looked) {
+         named_sync<1, BK4_THREADS>();   // row r has been read by everybody before its owner overwrites it
+      }
+      if (step == 1) {
+         if (isnull) {
+            if (w == 0) {
+               S.Lm[j][lane] = 0.0;
+               if (lane == 0) { S.d[j] = 1.0; S.e[j] = 0.0; S.type[j] = 3; }
+            }
+         } else {
+            const double d = S.B[j][j];
+            const double li = below ? fast_div(S.B[j][lane], d, rd) : 0.0;
+            const double2* prow = reinterpret_cast<const double2*>(&S.B[j][c0]);
+#pragma unroll
+            for (int c = 0; c < 8; c += 2) {
+               const double2 pc = prow[c >> 1];
+               a[c] = a[c] - li * pc.x;
+               a[c + 1] = a[c + 1] - li * pc.y;
+            }
+#pragma unroll
+            for (int c = 0; c < 8; ++c) if (below && c0 + c > j && c0 + c < n) S.B[c0 + c][lane] = a[c];
+            if (w == 0) {
+               S.Lm[j][lane] = li;
+               if (lane == 0) { S.d[j] = d; S.e[j] = 0.0; S.type[j] = 0; }
+            }
+            if (c0 <= j) {   // row j of the inverse is zero right of column j
+#pragma unroll
+               for (int c = 0; c < 8; ++c) x[c] = fma(-li, __shfl_sync(0xffffffffu, x[c], j), x[c]);
+            }
+         }
+      } else {
+         const double pa = S.B[j][j], pb = S.B[j][j + 1], pc = S.B[j + 1][j + 1];
+         const double det = pa * pc - pb * pb;
+         const double rdet = fast_rcp(det);
+         const bool act = lane > j + 1 && lane < n;
+         const double w1 = S.B[j][lane], w2 = S.B[j + 1][lane];
+         const double l1 = act ? fast_div(pc * w1 - pb * w2, det, rdet) : 0.0;
+         const double l2 = act ? fast_div(pa * w2 - pb * w1, det, rdet) : 0.0;
+         const double2* prow1 = reinterpret_cast<const double2*>(&S.B[j][c0]);
+         const double2* prow2 = reinterpret_cast<const double2*>(&S.B[j + 1][c0]);
+#pragma unroll
+         for (int c = 0; c < 8; c += 2) {
+            const double2 q1 = prow1[c >> 1], q2 = prow2[c >> 1];
+            a[c] = a[c] - (l1 * q1.x + l2 * q2.x);
+            a[c + 1] = a[c + 1] - (l1 * q1.y + l2 * q2.y);
+         }
+#pragma unroll
+         for (int c = 0; c < 8; ++c) if (act && c0 + c > j + 1 && c0 + c < n) S.B[c0 + c][lane] = a[c];
+         if (w == 0) {
+            S.Lm[j][lane] = l1;
+            S.Lm[j + 1][lane] = l2;
+            if (lane == 0) {
+               S.d[j] = pa; S.d[j + 1] = pc; S.e[j] = pb; S.e[j + 1] = 0.0;
+               S.type[j] = 1; S.type[j + 1] = 2;
+            }
+         }
+         if (c0 <= j + 1) {
+#pragma unroll
+            for (int c = 0; c < 8; ++c) {
+               const double xa = __shfl_sync(0xffffffffu, x[c], j), xb = __shfl_sync(0xffffffffu, x[c], j + 1);
+               x[c] = x[c] - (l1 * xa + l2 * xb);
+            }
+         }
+      }
+      named_sync<1, BK4_THREADS>();
+      j += step;
+   }
+}
+
+// X (rows of the inverse in registers) -> X2 = D^{-1} X; both to shared memory ([c][t], row stride XB_LD) for the
+// update group and, row-major NBI x NBI each, to the front's scratch for kernel B.  Null pivots: zero rows.
+__device__ void publish_inverse(const Bk4Shared& S, const int n, const int tid, double (&x)[8], double* Xx, double* Xl, double* Xg) {
+   const int lane = tid & 31, c0 = 8 * (tid >> 5);
+   const int ty = S.type[lane];
+   const int first = (ty == 2) ? lane - 1 : lane;   // first row of the pivot block this row belongs to
+   const double pa = S.d[first], pb = S.e[first], pc = S.d[(first + 1) & 31];
+   const double det = pa * pc - pb * pb;
+#pragma unroll
+   for (int c = 0; c < 8; ++c) {
+      const double dn = __shfl_down_sync(0xffffffffu, x[c], 1), up = __shfl_up_sync(0xffffffffu, x[c], 1);
+      double v = x[c], v2;
+      if (ty == 0) v2 = v / pa;
+      else if (ty == 1) v2 = (pc * v - pb * dn) / det;
+      else if (ty == 2) v2 = (pa * v - pb * up) / det;
+      else { v = 0.0; v2 = 0.0; }
+      if (lane >= n || c0 + c >= n) { v = 0.0; v2 = 0.0; }
+      Xx[lane * XB_LD + c0 + c] = v;
+      Xl[lane * XB_LD + c0 + c] = v2;
+      Xg[lane * NBI + c0 + c] = v;
+      Xg[NBI * NBI + lane * NBI + c0 + c] = v2;
+   }
+}
+
+constexpr int DP_THREADS = 256;
+constexpr int DP_LD = NBO - NBI + 8;   // rows of the in-panel W/L staging ([c][row]); DP_LD mod 16 == 8: conflict-free fragments
+constexpr int DP_SMEM = static_cast<int>((sizeof(Bk4Shared) + 15) & ~size_t(15)) +
+                        (4 * NBI * XB_LD + 2 * NBI * DP_LD) * static_cast<int>(sizeof(double)) + 2 * (NBI + 1) * static_cast<int>(sizeof(int)) + 16;
+
+// rows [row0, row0 + 8 MT) of the diagonal block against the inner block at j0: w = a X^T, l = a X2^T with
+// a = A[row, j0 + p[.]] (the block's pivot order); results to the staging (row index rel0 + ...) and l to the factor panel
+template <int MT>
+__device__ __forceinline__ void panel_rows_trsm(double* __restrict__ A, const int ld, const int row0, const int rowend, const int j0, const int nbw,
+                                                const int* __restrict__ pb, const double* __restrict__ Xx, const double* __restrict__ Xl,
+                                                double* __restrict__ Ws, double* __restrict__ Ls, const int rel0, const int lane) {
+   const int g = lane >> 2, q = lane & 3;
+   double af[MT][8];
+#pragma unroll
+   for (int ks = 0; ks < 8; ++ks) {
+      const int t = 4 * ks + q;
+      const double* colp = A + static_cast<int64_t>(ld) * (j0 + pb[t]);
+#pragma unroll
+      for (int mt = 0; mt < MT; ++mt) {
+         const int row = row0 + 8 * mt + g;
+         af[mt][ks] = (row < rowend && t < nbw) ? colp[row] : 0.0;
+      }
+   }
+#pragma unroll
+   for (int nt = 0; nt < 4; ++nt) {
+      double cw[MT][2], cl[MT][2];
+#pragma unroll
+      for (int mt = 0; mt < MT; ++mt) { cw[mt][0] = 0.0; cw[mt][1] = 0.0; cl[mt][0] = 0.0; cl[mt][1] = 0.0; }
+#pragma unroll
+      for (int ks = 0; ks < 8; ++ks) {
+         // X is lower triangular, X2 reaches one column further (2x2 pivots)
+         if (ks <= 2 * nt + 2) {
+            const double bl = Xl[(8 * nt + g) * XB_LD + 4 * ks + q];
+#pragma unroll
+            for (int mt = 0; mt < MT; ++mt) dmma8x8x4(cl[mt][0], cl[mt][1], af[mt][ks], bl);
+            if (ks <= 2 * nt + 1) {
+               const double bx = Xx[(8 * nt + g) * XB_LD + 4 * ks + q];
+#pragma unroll
+               for (int mt = 0; mt < MT; ++mt) dmma8x8x4(cw[mt][0], cw[mt][1], af[mt][ks], bx);
+            }
+         }
+      }
+#pragma unroll
+      for (int mt = 0; mt < MT; ++mt)
+#pragma unroll
+         for (int e = 0; e < 2; ++e) {
+            const int cc = 8 * nt + 2 * q + e, rel = rel0 + 8 * mt + g;
+            Ws[cc * DP_LD + rel] = cw[mt][e];
+            Ls[cc * DP_LD + rel] = cl[mt][e];
+         }
+   }
+   __syncwarp();
+   // l back to the factor panel, rows contiguous (every a of these rows has been consumed by now)
+   constexpr int R = 8 * MT;
+   for (int idx = lane; idx < R * NBI; idx += 32) {
+      const int rr = idx % R, cc = idx / R;
+      if (row0 + rr < rowend && cc < nbw) A[(row0 + rr) + static_cast<int64_t>(ld) * (j0 + cc)] = Ls[cc * DP_LD + rel0 + rr];
+   }
+}
+
 __global__ void __launch_bounds__(DP_THREADS) k_diagpanel(FrontArrays F, const int* __restrict__ list, const int J0, FactorArrays W,
                                                           const double null_tol) {
    extern __shared__ __align__(16) unsigned char dp_smem[];
-   BkShared& S = *reinterpret_cast<BkShared*>(dp_smem);
-   double* Ws = reinterpret_cast<double*>(dp_smem + ((sizeof(BkShared) + 15) & ~size_t(15)));   // [c][row]
+   Bk4Shared& S = *reinterpret_cast<Bk4Shared*>(dp_smem);
+   double* XB = reinterpret_cast<double*>(dp_smem + ((sizeof(Bk4Shared) + 15) & ~size_t(15)));   // [buffer][X | X2][c][t]
+   double* Ws = XB + 4 * NBI * XB_LD;                                                           // [c][row]
    double* Ls = Ws + NBI * DP_LD;
-   double* Xs = Ls + NBI * DP_LD;            // [c][t], row stride NBI + 1: X = L11^{-1} of the inner block
-   double* X2s = Xs + NBI * (NBI + 1);       // D^{-1} X
+   int* pbuf = reinterpret_cast<int*>(Ls + NBI * DP_LD);   // [buffer][NBI + 1]: pivot order of the block, then its "nontrivial" flag
    const int s = list[blockIdx.x];
    const int k = F.k[s], ld = F.ld[s], first = F.first[s];
    const int J1 = min(J0 + NBO, k);
    double* A = W.lpool + F.off[s];
    double* Xg = W.wpool + F.woff[s] + static_cast<int64_t>(ld) * min(NBO, (k + 3) & ~3);   // behind the W panel
    const int tid = threadIdx.x;
-   PHASE_BEGIN();
-   for (int j0 = J0; j0 < J1; j0 += NBI) {
-      const int nbw = min(NBI, k - j0), j1 = j0 + nbw;
-      for (int idx = tid; idx < NBI * NBI; idx += DP_THREADS) {
-         const int r = idx % NBI, c = idx / NBI;
-         double v;
-         if (r < nbw && c < nbw) {
-            v = (r >= c) ? A[(j0 + r) + static_cast<int64_t>(ld) * (j0 + c)] : A[(j0 + c) + static_cast<int64_t>(ld) * (j0 + r)];
-         } else {
-            v = (r == c) ? 1.0 : 0.0;
-         }
-         S.B[r][c] = v;
-      }
-      __syncthreads();
-      PHASE_MARK(0);
-      if (tid < 32) bk_factor_block(S, nbw, tid, null_tol);
-      __syncthreads();
-      PHASE_MARK(1);
-      if (tid >= 32 && tid < 64) invert_block(S, nbw, tid - 32, Xs, X2s, Xg + ((j0 - J0) / NBI) * 2 * NBI * NBI);
-      for (int idx = tid; idx < NBI * NBI; idx += DP_THREADS) {
-         const int r = idx % NBI, c = idx / NBI;
-         if (r < nbw && c < nbw && r >= c) A[(j0 + r) + static_cast<int64_t>(ld) * (j0 + c)] = (r == c) ? S.d[c] : S.B[r][c];
-      }
-      if (tid < nbw) {
-         const int q = first + j0 + tid;
-         W.dd[q] = S.d[tid];
-         W.de[q] = S.e[tid];
-         W.ptype[q] = S.type[tid];
-         W.lperm[q] = j0 + S.p[tid];
-      }
-      if (tid == 0) W.blkflag[first + j0] = S.nontrivial;
-      // the block's interchanges on the panel's earlier L columns (columns left of J0 are deferred)
-      if (S.nontrivial) {
-         for (int c = J0 + tid; c < j0; c += DP_THREADS) {
-            double* colp = A + static_cast<int64_t>(ld) * c + j0;
-            double tmp[NBI];
-#pragma unroll
-            for (int t = 0; t < NBI; ++t) tmp[t] = (t < nbw) ? colp[S.p[t]] : 0.0;
-#pragma unroll
-            for (int t = 0; t < NBI; ++t) if (t < nbw) colp[t] = tmp[t];
-         }
-      }
-      __syncthreads();
-      PHASE_MARK(2);
-      const int rem = J1 - j1;   // rows (and columns) of the diagonal block still to be factored
-      if (rem <= 0) break;
-      // rows of the diagonal block below the inner block: w = a X^T, l = a X2^T (independent dot products)
-      if (tid < rem) {
-         const int i = j1 + tid;
-         double a[NBI];
-#pragma unroll
-         for (int c = 0; c < NBI; ++c) a[c] = (c < nbw) ? A[i + static_cast<int64_t>(ld) * (j0 + S.p[c])] : 0.0;
-#pragma unroll
-         for (int c = 0; c < NBI; ++c) {
-            double w = 0.0, l = 0.0;
-#pragma unroll
-            for (int t = 0; t <= c; ++t) w = fma(a[t], Xs[c * (NBI + 1) + t], w);
-            // X2 rows of a 2x2 pair reach one column further than the diagonal
-#pragma unroll
-            for (int t = 0; t <= ((c + 1 < NBI) ? c + 1 : c); ++t) l = fma(a[t], X2s[c * (NBI + 1) + t], l);
-            if (c < nbw) A[i + static_cast<int64_t>(ld) * (j0 + c)] = l;
-            Ws[c * DP_LD + tid] = w;
-            Ls[c * DP_LD + tid] = l;
-         }
-      } else if (tid < ((rem + 3) & ~3)) {
-#pragma unroll
-         for (int c = 0; c < NBI; ++c) { Ws[c * DP_LD + tid] = 0.0; Ls[c * DP_LD + tid] = 0.0; }
-      }
-      __syncthreads();
-      PHASE_MARK(3);
-      // A[m, n] -= sum_c W[m, c] L[n, c] on the lower triangle of the remaining diagonal block, 4 x 4 tiles
-      const int T = (rem + 3) >> 2;
-      for (int idx = tid; idx < T * T; idx += DP_THREADS) {
-         const int tm = idx / T, tn = idx % T;
-         if (tn > tm) continue;
-         double acc[4][4];
-#pragma unroll
-         for (int a = 0; a < 4; ++a)
-#pragma unroll
-            for (int b = 0; b < 4; ++b) acc[a][b] = 0.0;
-#pragma unroll 4
-         for (int c = 0; c < NBI; ++c) {
-            const double2 w01 = *reinterpret_cast<const double2*>(Ws + c * DP_LD + tm * 4);
-            const double2 w23 = *reinterpret_cast<const double2*>(Ws + c * DP_LD + tm * 4 + 2);
-            const double2 l01 = *reinterpret_cast<const double2*>(Ls + c * DP_LD + tn * 4);
-            const double2 l23 = *reinterpret_cast<const double2*>(Ls + c * DP_LD + tn * 4 + 2);
-            const double wv[4] = {w01.x, w01.y, w23.x, w23.y};
-            const double lv[4] = {l01.x, l01.y, l23.x, l23.y};
-#pragma unroll
-            for (int a = 0; a < 4; ++a)
-#pragma unroll
-               for (int b = 0; b < 4; ++b) acc[a][b] += wv[a] * lv[b];
-         }
-         // read-modify-write with all 16 loads in flight (predicated, no branches between them)
-         double* tile = A + (j1 + tm * 4) + static_cast<int64_t>(ld) * (j1 + tn * 4);
-         double cur[4][4];
-         bool ok[4][4];
-#pragma unroll
-         for (int b = 0; b < 4; ++b)
-#pragma unroll
-            for (int a = 0; a < 4; ++a) {
-               const int m = tm * 4 + a, n = tn * 4 + b;
-               ok[a][b] = m < rem && n < rem && m >= n;
-               cur[a][b] = ok[a][b] ? tile[a + static_cast<int64_t>(ld) * b] : 0.0;
+   if (tid < BK4_THREADS) {
+      // ---------------- pivot group ----------------
+      int b = 0;
+      for (int j0 = J0; j0 < J1; j0 += NBI, ++b) {
+         const int nbw = min(NBI, k - j0);
+         if (b == 0) {
+            for (int idx = tid; idx < NBI * NBI; idx += BK4_THREADS) {
+               const int r = idx % NBI, c = idx / NBI;
+               double v;
+               if (r < nbw && c < nbw) {
+                  v = (r >= c) ? A[(j0 + r) + static_cast<int64_t>(ld) * (j0 + c)] : A[(j0 + c) + static_cast<int64_t>(ld) * (j0 + r)];
+               } else {
+                  v = (r == c) ? 1.0 : 0.0;
+               }
+               S.B[c][r] = v;
             }
-#pragma unroll
-         for (int b = 0; b < 4; ++b)
-#pragma unroll
-            for (int a = 0; a < 4; ++a)
-               if (ok[a][b]) tile[a + static_cast<int64_t>(ld) * b] = cur[a][b] - acc[a][b];
+            named_sync<1, BK4_THREADS>();
+         } else {
+            named_sync<3, DP_THREADS>();   // the update group has written this block into S.B
+         }
+         double x[8];
+         bk_factor_block4(S, nbw, tid, null_tol, x);
+         double* Xx = XB + (b & 1) * 2 * NBI * XB_LD;
+         publish_inverse(S, nbw, tid, x, Xx, Xx + NBI * XB_LD, Xg + b * 2 * NBI * NBI);
+         // the factored block back to the panel: D on the diagonal, L11 below it
+         for (int idx = tid; idx < NBI * NBI; idx += BK4_THREADS) {
+            const int r = idx % NBI, c = idx / NBI;
+            if (r < nbw && c < nbw && r >= c) A[(j0 + r) + static_cast<int64_t>(ld) * (j0 + c)] = (r == c) ? S.d[c] : S.Lm[c][r];
+         }
+         if (tid < nbw) {
+            const int q = first + j0 + tid;
+            W.dd[q] = S.d[tid];
+            W.de[q] = S.e[tid];
+            W.ptype[q] = S.type[tid];
+            W.lperm[q] = j0 + S.p[tid];
+         }
+         int* pb = pbuf + (b & 1) * (NBI + 1);
+         if (tid < NBI) pb[tid] = S.p[tid];
+         if (tid == 0) { W.blkflag[first + j0] = S.nontrivial; pb[NBI] = S.nontrivial; }
+         named_arrive<2, DP_THREADS>();
       }
-      __syncthreads();
-      PHASE_MARK(4);
+   } else {
+      // ---------------- update group ----------------
+      const int wt = tid - BK4_THREADS, ww = wt >> 5, lane = wt & 31, g = lane >> 2, q = lane & 3;
+      int b = 0;
+      for (int j0 = J0; j0 < J1; j0 += NBI, ++b) {
+         const int nbw = min(NBI, k - j0), j1 = j0 + nbw;
+         const int rem = J1 - j1;   // rows (and columns) of the diagonal block still to be factored
+         named_sync<2, DP_THREADS>();
+         const double* Xx = XB + (b & 1) * 2 * NBI * XB_LD;
+         const double* Xl = Xx + NBI * XB_LD;
+         const int* pb = pbuf + (b & 1) * (NBI + 1);
+         if (rem > 0) {
+            // the next NBI rows first: 8 per warp
+            panel_rows_trsm<1>(A, ld, j1 + 8 * ww, J1, j0, nbw, pb, Xx, Xl, Ws, Ls, 8 * ww, lane);
+            named_sync<4, BK4_THREADS>();
+            {
+               // next inner block: S.B = A[j1.., j1..] - Ws Ls^T, exactly symmetric (the lower triangle is mirrored)
+               const int nbn = min(NBI, k - j1);
+               double acc[4][2];
+#pragma unroll
+               for (int nt = 0; nt < 4; ++nt) { acc[nt][0] = 0.0; acc[nt][1] = 0.0; }
+               double cur[4][2];
+#pragma unroll
+               for (int nt = 0; nt < 4; ++nt)
+#pragma unroll
+                  for (int e = 0; e < 2; ++e) {
+                     const int r = 8 * ww + g, c = 8 * nt + 2 * q + e;
+                     cur[nt][e] = (r >= c && r < nbn) ? A[(j1 + r) + static_cast<int64_t>(ld) * (j1 + c)] : 0.0;
+                  }
+#pragma unroll
+               for (int ks = 0; ks < 8; ++ks) {
+                  const double af = Ws[(4 * ks + q) * DP_LD + 8 * ww + g];
+#pragma unroll
+                  for (int nt = 0; nt < 4; ++nt) dmma8x8x4(acc[nt][0], acc[nt][1], af, Ls[(4 * ks + q) * DP_LD + 8 * nt + g]);
+               }
+#pragma unroll
+               for (int nt = 0; nt < 4; ++nt)
+#pragma unroll
+                  for (int e = 0; e < 2; ++e) {
+                     const int r = 8 * ww + g, c = 8 * nt + 2 * q + e;
+                     if (r >= c) {
+                        const double v = (r < nbn) ? cur[nt][e] - acc[nt][e] : ((r == c) ? 1.0 : 0.0);
+                        S.B[r][c] = v;
+                        S.B[c][r] = v;
+                     }
+                  }
+            }
+            named_arrive<3, DP_THREADS>();
+            // the remaining rows, 32 per warp pass
+            for (int slab = 1 + ww; 32 * slab < rem; slab += 4)
+               panel_rows_trsm<4>(A, ld, j1 + 32 * slab, J1, j0, nbw, pb, Xx, Xl, Ws, Ls, 32 * slab, lane);
+            named_sync<4, BK4_THREADS>();
+            // rank-NBI update of the rest of the diagonal block: 32 x 32 tiles of the lower triangle, tile (0,0) is done
+            const int T32 = (rem + 31) >> 5;
+            int cnt = 0;
+            for (int tm = 1; tm < T32; ++tm)
+               for (int tn = 0; tn <= tm; ++tn) {
+                  if ((cnt++ & 3) != ww) continue;
+                  double* tile = A + (j1 + 32 * tm) + static_cast<int64_t>(ld) * (j1 + 32 * tn);
+                  double cur[4][4][2];
+#pragma unroll
+                  for (int mt = 0; mt < 4; ++mt)
+#pragma unroll
+                     for (int nt = 0; nt < 4; ++nt)
+#pragma unroll
+                        for (int e = 0; e < 2; ++e) {
+                           const int row = 32 * tm + 8 * mt + g, col = 32 * tn + 8 * nt + 2 * q + e;
+                           cur[mt][nt][e] = (row < rem && row >= col) ? tile[(8 * mt + g) + static_cast<int64_t>(ld) * (8 * nt + 2 * q + e)] : 0.0;
+                        }
+                  double acc[4][4][2];
+#pragma unroll
+                  for (int mt = 0; mt < 4; ++mt)
+#pragma unroll
+                     for (int nt = 0; nt < 4; ++nt) { acc[mt][nt][0] = 0.0; acc[mt][nt][1] = 0.0; }
+#pragma unroll
+                  for (int ks = 0; ks < 8; ++ks) {
+                     double af[4], bf[4];
+#pragma unroll
+                     for (int mt = 0; mt < 4; ++mt) af[mt] = Ws[(4 * ks + q) * DP_LD + 32 * tm + 8 * mt + g];
+#pragma unroll
+                     for (int nt = 0; nt < 4; ++nt) bf[nt] = Ls[(4 * ks + q) * DP_LD + 32 * tn + 8 * nt + g];
+#pragma unroll
+                     for (int mt = 0; mt < 4; ++mt)
+#pragma unroll
+                        for (int nt = 0; nt < 4; ++nt) dmma8x8x4(acc[mt][nt][0], acc[mt][nt][1], af[mt], bf[nt]);
+                  }
+#pragma unroll
+                  for (int mt = 0; mt < 4; ++mt)
+#pragma unroll
+                     for (int nt = 0; nt < 4; ++nt)
+#pragma unroll
+                        for (int e = 0; e < 2; ++e) {
+                           const int row = 32 * tm + 8 * mt + g, col = 32 * tn + 8 * nt + 2 * q + e;
+                           if (row < rem && row >= col) tile[(8 * mt + g) + static_cast<int64_t>(ld) * (8 * nt + 2 * q + e)] = cur[mt][nt][e] - acc[mt][nt][e];
+                        }
+               }
+         }
+         // the block's interchanges on the panel's earlier L columns (columns left of J0 are deferred)
+         if (pb[NBI]) {
+            for (int c = J0 + wt; c < j0; c += BK4_THREADS) {
+               double* colp = A + static_cast<int64_t>(ld) * c + j0;
+               double tmp[NBI];
+#pragma unroll
+               for (int t = 0; t < NBI; ++t) tmp[t] = (t < nbw) ? colp[pb[t]] : 0.0;
+#pragma unroll
+               for (int t = 0; t < NBI; ++t) if (t < nbw) colp[t] = tmp[t];
+            }
+         }
+         named_sync<4, BK4_THREADS>();   // panel writes of this block are visible to the group before the next block's reads
+      }
    }
 }
 
@@ -608,9 +941,6 @@ __global__ void __launch_bounds__(TP_THREADS) k_trsmpanel(FrontArrays F, const i
    }
 }
 
-__device__ __forceinline__ void dmma8x8x4(double& c0, double& c1, const double a, const double b) {
-   asm volatile("mma.sync.aligned.m8n8k4.row.col.f64.f64.f64.f64 {%0,%1}, {%2}, {%3}, {%0,%1};\n" : "+d"(c0), "+d"(c1) : "d"(a), "d"(b));
-}
 
 // Kernel B, tensor-core variant for fronts with more than NBI pivots.  CTA = 64 rows below the diagonal
 // block, 4 warps.  The CTA's W rows of the whole outer panel stay in shared memory; per inner block:
