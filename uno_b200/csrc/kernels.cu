@@ -617,7 +617,7 @@ __device__ void publish_inverse(const Bk4Shared& S, const int n, const int tid, 
 }
 
 constexpr int DP_THREADS = 256;
-constexpr int DP_LD = NBO - NBI + 8;   // rows of the in-panel W/L staging ([c][row]); DP_LD mod 16 == 8: conflict-free fragments
+constexpr int DP_LD = NBO - NBI + 4;   // rows of the in-panel W/L staging ([c][row]); DP_LD mod 16 == 4: conflict-free fragments
 constexpr int DP_SMEM = static_cast<int>((sizeof(Bk4Shared) + 15) & ~size_t(15)) +
                         (4 * NBI * XB_LD + 2 * NBI * DP_LD) * static_cast<int>(sizeof(double)) + 2 * (NBI + 1) * static_cast<int>(sizeof(int)) + 16;
 
@@ -1164,8 +1164,8 @@ __device__ __forceinline__ void cp_async_wait() { asm volatile("cp.async.wait_gr
 
 constexpr int UPD_STAGES = 3;
 
-template <int BM, int BN, int WARPS_M, int WARPS_N, int UPD_BK>
-__global__ void __launch_bounds__(WARPS_M* WARPS_N * 32) k_update(FrontArrays F, const int* __restrict__ list, const int mode, const int j0,
+template <int BM, int BN, int WARPS_M, int WARPS_N, int UPD_BK, int MINB = 1>
+__global__ void __launch_bounds__(WARPS_M* WARPS_N * 32, MINB) k_update(FrontArrays F, const int* __restrict__ list, const int mode, const int j0,
                                                                   const int J0, FactorArrays W) {
    constexpr int NT = WARPS_M * WARPS_N * 32;
    constexpr int LDA = BM + 4, LDB = BN + 4;   // +4 doubles: conflict-free fragment loads (LD mod 16 == 4)
@@ -1310,6 +1310,200 @@ __global__ void __launch_bounds__(WARPS_M* WARPS_N * 32) k_update(FrontArrays F,
             const int m = m0 + wm0 + a * 8 + (lane >> 2);
             if (ok[a][h]) dst[h][m] = v[a][h] - acc[a][b][h];
          }
+   }
+}
+
+// ------------------------------------------------------------------------------------------------
+// K4, warp-specialised persistent variant for the trailing update of big fronts (mode 1).
+//   CTA = 4 consumer warps (2 x 2, warp tile 64 x 32, DMMA) + 1 producer warp; tile 128 x 64 x 16, 4-stage ring.
+//   The producer moves one operand row (contiguous in the column-major panels) per lane and stage with
+//   cp.async.bulk, completion counted on an mbarrier; consumers never touch addresses of the operands, never
+//   hit a CTA-wide barrier, and the producer runs ahead into the next tile while they read-modify-write C.
+//   Two CTAs are co-resident per SM, so one tile's epilogue overlaps the other's K loop.
+//   Tiles of the lower triangle are enumerated directly (no empty CTAs), statically strided over the grid.
+// ------------------------------------------------------------------------------------------------
+constexpr int WS_BM = 128, WS_BN = 64, WS_BK = 16, WS_STAGES = 4;
+constexpr int WS_LDA = WS_BM + 4, WS_LDB = WS_BN + 4;
+constexpr int WS_STAGE_DOUBLES = WS_BK * (WS_LDA + WS_LDB);
+constexpr int WS_CONSUMER_WARPS = 4;
+constexpr int WS_THREADS = (WS_CONSUMER_WARPS + 1) * 32;
+constexpr int WS_SMEM = WS_STAGES * WS_STAGE_DOUBLES * static_cast<int>(sizeof(double)) + 2 * WS_STAGES * 8;
+
+__device__ __forceinline__ void mbar_init(const unsigned bar, const int count) { asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" ::"r"(bar), "r"(count)); }
+__device__ __forceinline__ void mbar_arrive(const unsigned bar) { asm volatile("mbarrier.arrive.shared::cta.b64 _, [%0];" ::"r"(bar) : "memory"); }
+__device__ __forceinline__ void mbar_arrive_expect_tx(const unsigned bar, const unsigned bytes) {
+   asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(bar), "r"(bytes) : "memory");
+}
+__device__ __forceinline__ void mbar_wait(const unsigned bar, const unsigned parity) {
+   asm volatile(
+       "{\n"
+       ".reg .pred p;\n"
+       "WAIT_LOOP:\n"
+       "mbarrier.try_wait.parity.shared::cta.b64 p, [%0], %1;\n"
+       "@p bra WAIT_DONE;\n"
+       "bra WAIT_LOOP;\n"
+       "WAIT_DONE:\n"
+       "}\n" ::"r"(bar), "r"(parity) : "memory");
+}
+__device__ __forceinline__ void bulk_g2s(const unsigned dst, const void* src, const unsigned bytes, const unsigned bar) {
+   asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];" ::"r"(dst), "l"(src), "r"(bytes), "r"(bar) : "memory");
+}
+
+// tile t of a lower triangle whose row tm holds the column tiles 0 .. 2 tm + 1
+__device__ __forceinline__ void decode_tile(const int t, int& tm, int& tn) {
+   int r = static_cast<int>((sqrtf(4.0f * static_cast<float>(t) + 1.0f) - 1.0f) * 0.5f);
+   while (r * (r + 1) > t) --r;
+   while ((r + 1) * (r + 2) <= t) ++r;
+   tm = r;
+   tn = t - r * (r + 1);
+}
+
+__global__ void __maxnreg__(200) k_update_ws(FrontArrays F, const int* __restrict__ list, const int nfronts, const int J0, FactorArrays W) {
+   extern __shared__ __align__(128) double smem[];
+   const unsigned smem_base = static_cast<unsigned>(__cvta_generic_to_shared(smem));
+   const unsigned bar_full = smem_base + WS_STAGES * WS_STAGE_DOUBLES * static_cast<unsigned>(sizeof(double));
+   const unsigned bar_empty = bar_full + WS_STAGES * 8;
+   const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+   if (tid == 0) {
+      for (int i = 0; i < WS_STAGES; ++i) {
+         mbar_init(bar_full + 8 * i, 32);                  // every producer lane arrives (with its byte count)
+         mbar_init(bar_empty + 8 * i, WS_CONSUMER_WARPS);  // one arrival per consumer warp
+      }
+      asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+   }
+   __syncthreads();
+   int stage = 0;
+   unsigned phase = 0;
+   int base = 0;   // tiles of the fronts before the current one
+   for (int fi = 0; fi < nfronts; ++fi) {
+      const int s = list[fi];
+      const int k = F.k[s], f = F.f[s], ld = F.ld[s];
+      const int J1 = min(J0 + NBO, k);
+      const int K = J1 - J0;
+      if (K <= 0 || J1 >= f) continue;
+      const int mbase = J1 & ~1;
+      const int Tm = (f - mbase + WS_BM - 1) / WS_BM, Tn = (f - mbase + WS_BN - 1) / WS_BN;
+      const int ntiles = Tm * (Tm + 1) - (2 * Tm - Tn);
+      double* A = W.lpool + F.off[s];
+      const int ldc = F.ldc[s];
+      double* Cb = W.cbpool + F.cboff[s] - k - static_cast<int64_t>(ldc) * k;   // columns >= k live in the contribution block
+      const double* Wp = W.wpool + F.woff[s];                  // operand A: rows m, K columns
+      const double* Lp = A + static_cast<int64_t>(ld) * J0;    // operand B: rows n, K columns
+      const int num_kt = (K + WS_BK - 1) / WS_BK;
+      int g = base + ((static_cast<int>(blockIdx.x) - base) % static_cast<int>(gridDim.x) + static_cast<int>(gridDim.x)) % static_cast<int>(gridDim.x);
+      base += ntiles;
+      for (; g < base; g += gridDim.x) {
+         int tm, tn;
+         decode_tile(g - (base - ntiles), tm, tn);
+         const int m0 = mbase + tm * WS_BM, n0 = mbase + tn * WS_BN;
+         if (warp == WS_CONSUMER_WARPS) {
+            // ---------------- producer ----------------
+            const bool isA = lane < WS_BK;
+            const int kk = isA ? lane : lane - WS_BK;
+            const unsigned bytes = static_cast<unsigned>(isA ? min(WS_BM, ld - m0) : min(WS_BN, ld - n0)) * 8u;
+            const double* src = isA ? (Wp + m0 + static_cast<int64_t>(ld) * kk) : (Lp + n0 + static_cast<int64_t>(ld) * kk);
+            const unsigned dst_off = static_cast<unsigned>(isA ? kk * WS_LDA : WS_BK * WS_LDA + kk * WS_LDB) * 8u;
+            // pull the C tile towards L2: the epilogue's read-modify-write then hits L2
+            for (int q = lane; q < WS_BN * (WS_BM / 16); q += 32) {
+               const int n = n0 + q / (WS_BM / 16), m = m0 + (q % (WS_BM / 16)) * 16;
+               if (n < f && m < f && m + 15 >= n) {
+                  const double* pc = (n < k) ? (A + m + static_cast<int64_t>(ld) * n) : (Cb + m + static_cast<int64_t>(ldc) * n);
+                  asm volatile("prefetch.global.L2 [%0];" ::"l"(pc));
+               }
+            }
+            for (int kt = 0; kt < num_kt; ++kt) {
+               mbar_wait(bar_empty + 8 * stage, phase ^ 1u);
+               const unsigned dst = smem_base + static_cast<unsigned>(stage * WS_STAGE_DOUBLES) * 8u + dst_off;
+               if (kt * WS_BK + kk < K) {
+                  mbar_arrive_expect_tx(bar_full + 8 * stage, bytes);
+                  bulk_g2s(dst, src + static_cast<int64_t>(ld) * (kt * WS_BK), bytes, bar_full + 8 * stage);
+               } else {
+                  // K tail: this operand row does not exist, the consumers must see zeros
+                  double* z = smem + stage * WS_STAGE_DOUBLES + (dst_off >> 3);
+                  for (int i = 0; i < (isA ? WS_BM : WS_BN); i += 2) *reinterpret_cast<double2*>(z + i) = make_double2(0.0, 0.0);
+                  mbar_arrive(bar_full + 8 * stage);
+               }
+               if (++stage == WS_STAGES) { stage = 0; phase ^= 1u; }
+            }
+         } else {
+            // ---------------- consumers ----------------
+            constexpr int MF = 8, NF = 4;
+            const int wm0 = (warp & 1) * 64, wn0 = (warp >> 1) * 32;
+            double acc[MF][NF][2];
+#pragma unroll
+            for (int a = 0; a < MF; ++a)
+#pragma unroll
+               for (int b = 0; b < NF; ++b) { acc[a][b][0] = 0.0; acc[a][b][1] = 0.0; }
+            for (int kt = 0; kt < num_kt; ++kt) {
+               mbar_wait(bar_full + 8 * stage, phase);
+               const double* As = smem + stage * WS_STAGE_DOUBLES;
+               const double* Bs = As + WS_BK * WS_LDA;
+#pragma unroll
+               for (int k4 = 0; k4 < WS_BK / 4; ++k4) {
+                  const int krow = k4 * 4 + (lane & 3);
+                  double af[MF], bf[NF];
+#pragma unroll
+                  for (int a = 0; a < MF; ++a) af[a] = As[krow * WS_LDA + wm0 + a * 8 + (lane >> 2)];
+#pragma unroll
+                  for (int b = 0; b < NF; ++b) bf[b] = Bs[krow * WS_LDB + wn0 + b * 8 + (lane >> 2)];
+#pragma unroll
+                  for (int a = 0; a < MF; ++a)
+#pragma unroll
+                     for (int b = 0; b < NF; ++b) dmma8x8x4(acc[a][b][0], acc[a][b][1], af[a], bf[b]);
+               }
+               __syncwarp();
+               if (lane == 0) mbar_arrive(bar_empty + 8 * stage);
+               if (++stage == WS_STAGES) { stage = 0; phase ^= 1u; }
+            }
+            // epilogue: C -= acc.  Interior tiles (strictly below the diagonal, fully inside, on one side of column k)
+            // take the path without per-element predicates; loads are batched so that the read-modify-write is not a
+            // chain of dependent round trips.
+            const bool interior = m0 >= J1 && m0 + WS_BM <= f && n0 >= J1 && n0 + WS_BN <= f && m0 >= n0 + WS_BN && (n0 + WS_BN <= k || n0 >= k);
+            if (interior) {
+               double* cbase;
+               int64_t ldo;
+               if (n0 < k) { cbase = A; ldo = ld; } else { cbase = Cb; ldo = ldc; }
+               cbase += (m0 + wm0 + (lane >> 2)) + ldo * (n0 + wn0 + 2 * (lane & 3));
+#pragma unroll
+               for (int b = 0; b < NF; ++b) {
+                  double v[MF][2];
+#pragma unroll
+                  for (int a = 0; a < MF; ++a)
+#pragma unroll
+                     for (int h = 0; h < 2; ++h) v[a][h] = cbase[a * 8 + ldo * (b * 8 + h)];
+#pragma unroll
+                  for (int a = 0; a < MF; ++a)
+#pragma unroll
+                     for (int h = 0; h < 2; ++h) cbase[a * 8 + ldo * (b * 8 + h)] = v[a][h] - acc[a][b][h];
+               }
+            } else {
+#pragma unroll
+               for (int b = 0; b < NF; ++b) {
+                  double v[MF][2];
+                  bool ok[MF][2];
+                  double* dst[2];
+#pragma unroll
+                  for (int h = 0; h < 2; ++h) {
+                     const int n = n0 + wn0 + b * 8 + 2 * (lane & 3) + h;
+                     dst[h] = (n < k) ? (A + static_cast<int64_t>(ld) * n) : (Cb + static_cast<int64_t>(ldc) * n);
+#pragma unroll
+                     for (int a = 0; a < MF; ++a) {
+                        const int m = m0 + wm0 + a * 8 + (lane >> 2);
+                        ok[a][h] = m >= J1 && m < f && n >= J1 && n < f && m >= n;
+                        v[a][h] = ok[a][h] ? dst[h][m] : 0.0;
+                     }
+                  }
+#pragma unroll
+                  for (int h = 0; h < 2; ++h)
+#pragma unroll
+                     for (int a = 0; a < MF; ++a) {
+                        const int m = m0 + wm0 + a * 8 + (lane >> 2);
+                        if (ok[a][h]) dst[h][m] = v[a][h] - acc[a][b][h];
+                     }
+               }
+            }
+         }
+      }
    }
 }
 
@@ -1883,18 +2077,38 @@ int init_kernel_attributes() {
    e = cudaFuncSetAttribute(k_update<128, 128, 2, 4, 32>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem_bytes(128, 128, 32));
    if (e != cudaSuccess) return static_cast<int>(e);
    e = cudaFuncSetAttribute(k_update<64, 64, 2, 2, 16>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem_bytes(64, 64, 16));
+   if (e != cudaSuccess) return static_cast<int>(e);
+   e = cudaFuncSetAttribute(k_update<128, 64, 2, 2, 16, 2>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem_bytes(128, 64, 16));
+   if (e != cudaSuccess) return static_cast<int>(e);
+   e = cudaFuncSetAttribute(k_update<128, 64, 4, 2, 16, 2>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem_bytes(128, 64, 16));
+   if (e != cudaSuccess) return static_cast<int>(e);
+   e = cudaFuncSetAttribute(k_update<128, 128, 4, 4, 32, 1>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem_bytes(128, 128, 32));
+   if (e != cudaSuccess) return static_cast<int>(e);
+   e = cudaFuncSetAttribute(k_update_ws, cudaFuncAttributeMaxDynamicSharedMemorySize, WS_SMEM);
    return static_cast<int>(e);
 }
 
 int launch_update(const FrontArrays& F, const int* d_list, int nfronts, int max_f, int mode, int j0, int J0, const FactorArrays& W,
-                  bool big_tiles, cudaStream_t st) {
+                  int tile_mode, cudaStream_t st) {
    if (nfronts <= 0) return 0;
    // region extent upper bounds (per-front extents are resolved inside the kernel)
    const int r0 = (mode == 0) ? j0 + 1 : J0 + 1;   // smallest possible region start (a front with k = r0)
    const int rows = max_f - (r0 & ~1);
    if (rows <= 0) return 0;
    const int cols = (mode == 0) ? NBO : rows;
-   if (big_tiles) {
+   if (tile_mode == 4) {
+      dim3 grid(nfronts, (rows + 127) / 128, (cols + 63) / 64);
+      k_update<128, 64, 4, 2, 16, 2><<<grid, 256, smem_bytes(128, 64, 16), st>>>(F, d_list, mode, j0, J0, W);
+   } else if (tile_mode == 5) {
+      dim3 grid(nfronts, (rows + 127) / 128, (cols + 127) / 128);
+      k_update<128, 128, 4, 4, 32, 1><<<grid, 512, smem_bytes(128, 128, 32), st>>>(F, d_list, mode, j0, J0, W);
+   } else if (tile_mode == 3 && mode == 1) {
+      k_update_ws<<<296, WS_THREADS, WS_SMEM, st>>>(F, d_list, nfronts, J0, W);
+   } else if (tile_mode == 2) {
+      // two co-resident CTAs per SM: the read-modify-write epilogue of one tile overlaps the K loop of the other
+      dim3 grid(nfronts, (rows + 127) / 128, (cols + 63) / 64);
+      k_update<128, 64, 2, 2, 16, 2><<<grid, 128, smem_bytes(128, 64, 16), st>>>(F, d_list, mode, j0, J0, W);
+   } else if (tile_mode == 1) {
       dim3 grid(nfronts, (rows + 127) / 128, (cols + 127) / 128);
       k_update<128, 128, 2, 4, 32><<<grid, 256, smem_bytes(128, 128, 32), st>>>(F, d_list, mode, j0, J0, W);
    } else {

@@ -78,7 +78,7 @@ int launch_permute_rows(const FrontArrays& F, const int* d_list, int nfronts, in
 // K4 Schur-complement update C -= W * L^T with FP64 tensor-core MMA.
 // mode 0: inside the outer panel (after inner block j0); mode 1: trailing matrix after outer panel J0.
 int launch_update(const FrontArrays& F, const int* d_list, int nfronts, int max_f, int mode, int j0, int J0,
-                  const FactorArrays& W, bool big_tiles, cudaStream_t st);
+                  const FactorArrays& W, int tile_mode, cudaStream_t st);   // tile_mode 0: 64x64, 1: 128x128, 2: 128x64 with two CTAs per SM
 int init_kernel_attributes();
 // phase cycle counters of the panel kernels (only when built with -DB200KKT_PHASES); returns 0 when not compiled in
 int debug_phase_cycles(unsigned long long* out16, bool reset);

@@ -125,7 +125,7 @@ void build_batches(b200kkt_handle* h, std::vector<int>& batch_list, std::vector<
             level_w += static_cast<int64_t>(P.ld[s]) * std::min(NBO, (P.k[s] + 3) & ~3);
             if (b.max_k > NBI) level_w += XINV_DOUBLES;
          }
-         b.big_tiles = b.max_f > 256;
+         b.big_tiles = (b.max_f > 256) ? h->update_tile_mode : 0;
          h->batches.push_back(std::move(b));
       }
       wpool_size = std::max(wpool_size, level_w);
@@ -588,6 +588,7 @@ int b200kkt_set_option(b200kkt_handle* h, const char* name, double value) {
    else if (n == "use_graph") h->use_graph = static_cast<int>(value);
    else if (n == "profile_updates") h->profile_updates = static_cast<int>(value);
    else if (n == "multi_stream") h->multi_stream = static_cast<int>(value);
+   else if (n == "update_tile_mode") h->update_tile_mode = static_cast<int>(value);
    else return fail(h, B200KKT_EINVAL, "unknown option: " + n);
    // numeric options are baked into the captured graph
    if (h->factor_graph != nullptr) { cudaGraphExecDestroy(h->factor_graph); h->factor_graph = nullptr; }
@@ -837,9 +838,9 @@ extern "C" int b200kkt_debug_bench_update(int device, int f, int k, int reps, in
       CK(cudaStreamCreate(&st));
       cudaEvent_t e0, e1;
       CK(cudaEventCreate(&e0)); CK(cudaEventCreate(&e1));
-      for (int i = 0; i < 2; ++i) launch_update(F, d32 + 4, 1, f, 1, 0, 0, W, big_tiles != 0, st);
+      for (int i = 0; i < 2; ++i) launch_update(F, d32 + 4, 1, f, 1, 0, 0, W, big_tiles, st);
       CK(cudaEventRecord(e0, st));
-      for (int i = 0; i < reps; ++i) launch_update(F, d32 + 4, 1, f, 1, 0, 0, W, big_tiles != 0, st);
+      for (int i = 0; i < reps; ++i) launch_update(F, d32 + 4, 1, f, 1, 0, 0, W, big_tiles, st);
       CK(cudaEventRecord(e1, st));
       CK(cudaStreamSynchronize(st));
       CK(cudaGetLastError());

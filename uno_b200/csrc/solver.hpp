@@ -22,7 +22,7 @@ struct Batch {
    int max_f = 0, max_k = 0;
    bool has_children = false;
    bool has_cb = false;
-   bool big_tiles = false;
+   int big_tiles = 0;   // K4 tile mode (see launch_update)
    std::vector<int> k;            // per front of the batch (descending)
    std::vector<int> pmaxf;        // prefix maximum of f in batch order
    int count_k_greater(int j) const;   // number of fronts with k > j (a prefix of the batch)
@@ -69,6 +69,7 @@ struct b200kkt_handle {
    cudaStream_t aux[NUM_AUX] = {nullptr, nullptr, nullptr};
    cudaEvent_t ev_fork = nullptr, ev_join[NUM_AUX] = {nullptr, nullptr, nullptr};
    int multi_stream = 1;
+   int update_tile_mode = 4;   // K4 variant for fronts wider than 256: 1 = 128x128 tiles (8 warps), 2 = 128x64 (4 warps, two CTAs per SM), 3 = warp-specialised persistent, 4 = 128x64 (8 warps, two CTAs per SM), 5 = 128x128 (16 warps)
    cudaEvent_t ev0 = nullptr, ev1 = nullptr;
    cudaGraphExec_t factor_graph = nullptr;
    std::vector<void*> plan_allocs;         // freed on re-analysis / destroy
