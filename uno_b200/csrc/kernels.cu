@@ -1181,7 +1181,10 @@ __global__ void __launch_bounds__(WARPS_M* WARPS_N * 32, MINB) k_update(FrontArr
       const int j1 = min(j0 + NBI, k);
       r0 = j1; c0 = j1; c1 = J1; kbeg = j0 - J0; K = j1 - j0;
    } else {
+      // trailing matrix; modes 2 and 3 split it by columns (look-ahead: the next outer panel's columns first)
       r0 = J1; c0 = J1; c1 = f; kbeg = 0; K = J1 - J0;
+      if (mode == 2) c1 = min(f, J1 + NBO);
+      else if (mode == 3) c0 = J1 + NBO;
    }
    if (c0 >= c1 || r0 >= f || K <= 0) return;
    const int m0 = (r0 & ~1) + blockIdx.y * BM;
@@ -2095,7 +2098,8 @@ int launch_update(const FrontArrays& F, const int* d_list, int nfronts, int max_
    const int r0 = (mode == 0) ? j0 + 1 : J0 + 1;   // smallest possible region start (a front with k = r0)
    const int rows = max_f - (r0 & ~1);
    if (rows <= 0) return 0;
-   const int cols = (mode == 0) ? NBO : rows;
+   const int cols = (mode == 0) ? NBO : ((mode == 2) ? std::min(rows, NBO + 2) : ((mode == 3) ? rows - NBO : rows));
+   if (cols <= 0) return 0;
    if (tile_mode == 4) {
       dim3 grid(nfronts, (rows + 127) / 128, (cols + 63) / 64);
       k_update<128, 64, 4, 2, 16, 2><<<grid, 256, smem_bytes(128, 64, 16), st>>>(F, d_list, mode, j0, J0, W);

@@ -76,7 +76,8 @@ int launch_trsmpanel(const FrontArrays& F, const int* d_list, int nfronts, int m
 // rows of the L columns left of each inner block follow the block's interchanges (all blocks at once)
 int launch_permute_rows(const FrontArrays& F, const int* d_list, int nfronts, int max_k, const FactorArrays& W, cudaStream_t st);
 // K4 Schur-complement update C -= W * L^T with FP64 tensor-core MMA.
-// mode 0: inside the outer panel (after inner block j0); mode 1: trailing matrix after outer panel J0.
+// mode 0: inside the outer panel (after inner block j0); mode 1: trailing matrix after outer panel J0;
+// modes 2 / 3: the first NBO columns of the trailing matrix / the rest of it (look-ahead split of mode 1).
 int launch_update(const FrontArrays& F, const int* d_list, int nfronts, int max_f, int mode, int j0, int J0,
                   const FactorArrays& W, int tile_mode, cudaStream_t st);   // tile_mode 0: 64x64, 1: 128x128, 2: 128x64 with two CTAs per SM
 int init_kernel_attributes();

@@ -208,7 +208,8 @@ void upload_plan(b200kkt_handle* h) {
    const size_t n = static_cast<size_t>(P.N);
    h->W.lpool = dev_alloc<double>(h, static_cast<size_t>(P.pool_size));
    h->W.cbpool = dev_alloc<double>(h, static_cast<size_t>(P.cb_pool_size));
-   h->W.wpool = dev_alloc<double>(h, static_cast<size_t>(wpool_size));
+   h->wpool_size = (wpool_size + 1) & ~int64_t(1);
+   h->W.wpool = dev_alloc<double>(h, static_cast<size_t>(2 * h->wpool_size));
    h->W.dd = dev_alloc<double>(h, n + 1);
    h->W.de = dev_alloc<double>(h, n + 1);
    h->W.ptype = dev_alloc<int>(h, n + 1);
@@ -227,7 +228,7 @@ void upload_plan(b200kkt_handle* h) {
    h->d_counters = dev_alloc<int>(h, 8);
    h->d_norms = dev_alloc<unsigned long long>(h, 4);
    h->d_scale_final = h->d_scale;
-   CK(cudaMemsetAsync(h->W.wpool, 0, static_cast<size_t>(std::max<int64_t>(wpool_size, 1)) * sizeof(double), h->stream));
+   CK(cudaMemsetAsync(h->W.wpool, 0, static_cast<size_t>(std::max<int64_t>(2 * h->wpool_size, 1)) * sizeof(double), h->stream));
    CK(cudaStreamSynchronize(h->stream));
    h->stats.t_upload = std::chrono::duration<double>(std::chrono::steady_clock::now() - t0).count();
 }
@@ -293,10 +294,19 @@ void enqueue_factor(b200kkt_handle* h) {
          const int lane = (bi - h->level_batch_ptr[l]) % (nside + 1);
          cudaStream_t st = (lane == 0) ? h->stream : h->aux[lane - 1];
          if (b.has_cb || b.has_children) L += launch_prepare(h->F, list, b.count, b.max_f, h->W, st);
-         for (int J0 = 0; J0 < b.max_k; J0 += NBO) {
+         // W panels are double-buffered: panel p of a front lives in buffer p & 1
+         FactorArrays Wbuf[2] = {h->W, h->W};
+         Wbuf[1].wpool += h->wpool_size;
+         const bool ahead = h->lookahead != 0 && !prof && b.max_k > NBO && b.max_f >= 2048;
+         cudaStream_t pst = h->panel_stream[lane];
+         int p = 0;
+         for (int J0 = 0; J0 < b.max_k; J0 += NBO, ++p) {
             const int nfP = b.count_k_greater(J0);
-            L += launch_diagpanel(h->F, list, nfP, b.max_k, J0, h->W, h->null_pivot_tol, st);
-            L += launch_trsmpanel(h->F, list, nfP, b.pmaxf[nfP - 1], b.max_k, J0, h->W, st);
+            const FactorArrays& Wp = Wbuf[p & 1];
+            if (!ahead || J0 == 0) {
+               L += launch_diagpanel(h->F, list, nfP, b.max_k, J0, Wp, h->null_pivot_tol, st);
+               L += launch_trsmpanel(h->F, list, nfP, b.pmaxf[nfP - 1], b.max_k, J0, Wp, st);
+            }
             const bool prof_this = prof && b.max_f >= 1024;
             if (prof_this) {
                double fl = 0.0;
@@ -307,7 +317,21 @@ void enqueue_factor(b200kkt_handle* h) {
                }
                prof_begin(fl, 0);
             }
-            L += launch_update(h->F, list, nfP, b.pmaxf[nfP - 1], 1, 0, J0, h->W, b.big_tiles, st);
+            if (ahead && J0 + NBO < b.max_k) {
+               // look-ahead: update the next panel's columns, factor that panel on the panel stream while the rest of
+               // the trailing matrix is updated here
+               const int nfN = b.count_k_greater(J0 + NBO);
+               L += launch_update(h->F, list, nfP, b.pmaxf[nfP - 1], 2, 0, J0, Wp, b.big_tiles, st);
+               CK(cudaEventRecord(h->ev_next_cols[lane], st));
+               CK(cudaStreamWaitEvent(pst, h->ev_next_cols[lane], 0));
+               L += launch_diagpanel(h->F, list, nfN, b.max_k, J0 + NBO, Wbuf[(p + 1) & 1], h->null_pivot_tol, pst);
+               L += launch_trsmpanel(h->F, list, nfN, b.pmaxf[nfN - 1], b.max_k, J0 + NBO, Wbuf[(p + 1) & 1], pst);
+               CK(cudaEventRecord(h->ev_panel[lane], pst));
+               L += launch_update(h->F, list, nfP, b.pmaxf[nfP - 1], 3, 0, J0, Wp, b.big_tiles, st);
+               CK(cudaStreamWaitEvent(st, h->ev_panel[lane], 0));
+            } else {
+               L += launch_update(h->F, list, nfP, b.pmaxf[nfP - 1], 1, 0, J0, Wp, b.big_tiles, st);
+            }
             if (prof_this) prof_end();
          }
          L += launch_permute_rows(h->F, list, b.count_k_greater(NBO), b.max_k, h->W, st);
@@ -527,6 +551,14 @@ int b200kkt_create(b200kkt_handle** out, int device, int num_gpus) {
             CK(cudaEventCreateWithFlags(&h->ev_join[a], cudaEventDisableTiming));
          }
          CK(cudaEventCreateWithFlags(&h->ev_fork, cudaEventDisableTiming));
+         int prio_least = 0, prio_greatest = 0;
+         CK(cudaDeviceGetStreamPriorityRange(&prio_least, &prio_greatest));
+         for (int a = 0; a <= b200kkt_handle::NUM_AUX; ++a) {
+            // the panel chain is the critical path: its CTAs go first whenever an SM frees up under a running update
+            CK(cudaStreamCreateWithPriority(&h->panel_stream[a], cudaStreamNonBlocking, prio_greatest));
+            CK(cudaEventCreateWithFlags(&h->ev_next_cols[a], cudaEventDisableTiming));
+            CK(cudaEventCreateWithFlags(&h->ev_panel[a], cudaEventDisableTiming));
+         }
          CK(cudaEventCreate(&h->ev0));
          CK(cudaEventCreate(&h->ev1));
          CK(cudaMallocHost(reinterpret_cast<void**>(&h->h_counters), 8 * sizeof(int)));
@@ -561,6 +593,11 @@ int b200kkt_destroy(b200kkt_handle* h) {
          if (h->aux[a] != nullptr) cudaStreamDestroy(h->aux[a]);
       }
       if (h->ev_fork != nullptr) cudaEventDestroy(h->ev_fork);
+      for (int a = 0; a <= b200kkt_handle::NUM_AUX; ++a) {
+         if (h->ev_next_cols[a] != nullptr) cudaEventDestroy(h->ev_next_cols[a]);
+         if (h->ev_panel[a] != nullptr) cudaEventDestroy(h->ev_panel[a]);
+         if (h->panel_stream[a] != nullptr) cudaStreamDestroy(h->panel_stream[a]);
+      }
       if (h->stream != nullptr) cudaStreamDestroy(h->stream);
    }
    delete h;
@@ -589,6 +626,7 @@ int b200kkt_set_option(b200kkt_handle* h, const char* name, double value) {
    else if (n == "profile_updates") h->profile_updates = static_cast<int>(value);
    else if (n == "multi_stream") h->multi_stream = static_cast<int>(value);
    else if (n == "update_tile_mode") h->update_tile_mode = static_cast<int>(value);
+   else if (n == "lookahead") h->lookahead = static_cast<int>(value);
    else return fail(h, B200KKT_EINVAL, "unknown option: " + n);
    // numeric options are baked into the captured graph
    if (h->factor_graph != nullptr) { cudaGraphExecDestroy(h->factor_graph); h->factor_graph = nullptr; }
