@@ -688,7 +688,7 @@ __global__ void __launch_bounds__(DP_THREADS) k_diagpanel(FrontArrays F, const i
    const int k = F.k[s], ld = F.ld[s], first = F.first[s];
    const int J1 = min(J0 + NBO, k);
    double* A = W.lpool + F.off[s];
-   double* Xg = W.wpool + F.woff[s] + static_cast<int64_t>(ld) * min(NBO, (k + 3) & ~3);   // behind the W panel
+   double* Xg = W.xinv + F.xoff[s] + static_cast<int64_t>(J0 / NBI) * XINV_BLOCK_DOUBLES;
    const int tid = threadIdx.x;
    if (tid < BK4_THREADS) {
       // ---------------- pivot group ----------------
@@ -969,7 +969,7 @@ __global__ void __launch_bounds__(TD_THREADS) k_trsmpanel_mma(FrontArrays F, con
    if (i0 >= f) return;
    double* A = W.lpool + F.off[s];
    double* Wp = W.wpool + F.woff[s];
-   const double* Xg = Wp + static_cast<int64_t>(ld) * min(NBO, (k + 3) & ~3);
+   const double* Xg = W.xinv + F.xoff[s] + static_cast<int64_t>(J0 / NBI) * XINV_BLOCK_DOUBLES;
    const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
    for (int j0 = J0; j0 < J1; j0 += NBI) {
       const int nbw = min(NBI, k - j0);
@@ -1732,7 +1732,18 @@ __device__ __forceinline__ void load_diag_blocks(double* Ls, const double* A, co
    }
 }
 
+// inverted diagonal blocks X of the panel at jp into shared memory: [block][r][c], row stride NBI + 1
+__device__ __forceinline__ void load_inverse_blocks(double* Xs, const double* Xg, const int nsb) {
+   for (int idx = threadIdx.x; idx < nsb * NBI * NBI; idx += blockDim.x) {
+      const int sb = idx / (NBI * NBI), r = (idx / NBI) % NBI, c = idx % NBI;
+      Xs[(sb * NBI + r) * (NBI + 1) + c] = Xg[static_cast<int64_t>(sb) * XINV_BLOCK_DOUBLES + r * NBI + c];
+   }
+}
+
 // One CTA per front: y_P <- L11[P,P]^{-1} y_P for the NBS-wide pivot panel starting at jp.
+// Fronts factored by the panel kernels carry X = inverse of every NBI x NBI diagonal block: a block step is a
+// matrix-vector product instead of a 32-step substitution, and the strip of L below the next block is in flight
+// (registers) while the current block is applied.
 __global__ void __launch_bounds__(256) k_fwd_big_diag(FrontArrays F, const int* __restrict__ list, const int jp, FactorArrays W,
                                                        double* __restrict__ z2) {
    extern __shared__ __align__(16) double sd_smem[];
@@ -1744,6 +1755,53 @@ __global__ void __launch_bounds__(256) k_fwd_big_diag(FrontArrays F, const int* 
    const double* A = W.lpool + F.off[s];
    double* y = z2 + F.first[s] + jp;
    const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+   const int64_t xoff = F.xoff[s];
+   if (xoff >= 0) {
+      const int nsb = (nb + NBI - 1) / NBI;
+      load_inverse_blocks(Ls, W.xinv + xoff + static_cast<int64_t>(jp / NBI) * XINV_BLOCK_DOUBLES, nsb);
+      ys[tid] = (tid < nb) ? y[tid] : 0.0;
+      const double* row = A + (jp + tid) + static_cast<int64_t>(ld) * jp;   // this thread's row of the diagonal block
+      double v[NBI];
+#pragma unroll
+      for (int c = 0; c < NBI; ++c) v[c] = (tid >= NBI && tid < nb) ? row[static_cast<int64_t>(ld) * c] : 0.0;
+      __syncthreads();
+      for (int sb = 0; sb < nsb; ++sb) {
+         const int base = sb * NBI;
+         if (warp == 0) {
+            const double* Xr = Ls + (base + lane) * (NBI + 1);
+            double a0 = 0.0, a1 = 0.0, a2 = 0.0, a3 = 0.0;
+#pragma unroll
+            for (int c = 0; c < NBI; c += 4) {
+               a0 = fma(Xr[c], ys[base + c], a0);
+               a1 = fma(Xr[c + 1], ys[base + c + 1], a1);
+               a2 = fma(Xr[c + 2], ys[base + c + 2], a2);
+               a3 = fma(Xr[c + 3], ys[base + c + 3], a3);
+            }
+            __syncwarp();
+            ys[base + lane] = (a0 + a1) + (a2 + a3);
+         }
+         __syncthreads();
+         // next strip in flight, then this block applied to the rows below it
+         double vn[NBI];
+         const bool more = tid >= base + 2 * NBI && tid < nb;
+#pragma unroll
+         for (int c = 0; c < NBI; ++c) vn[c] = (more && base + NBI + c < nb) ? row[static_cast<int64_t>(ld) * (base + NBI + c)] : 0.0;
+         if (tid >= base + NBI && tid < nb) {
+            double a0 = 0.0, a1 = 0.0;
+#pragma unroll
+            for (int c = 0; c < NBI; c += 2) {
+               a0 = fma(v[c], ys[base + c], a0);
+               a1 = fma(v[c + 1], ys[base + c + 1], a1);
+            }
+            ys[tid] -= a0 + a1;
+         }
+         __syncthreads();
+#pragma unroll
+         for (int c = 0; c < NBI; ++c) v[c] = vn[c];
+      }
+      if (tid < nb) y[tid] = ys[tid];
+      return;
+   }
    prefetch_diag_block(A, ld, jp, nb);
    load_diag_blocks(Ls, A, ld, jp, nb);
    ys[tid] = (tid < nb) ? y[tid] : 0.0;
@@ -1885,8 +1943,13 @@ __global__ void __launch_bounds__(256) k_bwd_big_diag(FrontArrays F, const int* 
    const double* A = W.lpool + F.off[s];
    double* y = z2 + F.first[s] + jp;
    const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
-   prefetch_diag_block(A, ld, jp, nb);
-   load_diag_blocks(Ls, A, ld, jp, nb);
+   const int64_t xoff = F.xoff[s];
+   if (xoff >= 0) {
+      load_inverse_blocks(Ls, W.xinv + xoff + static_cast<int64_t>(jp / NBI) * XINV_BLOCK_DOUBLES, (nb + NBI - 1) / NBI);
+   } else {
+      prefetch_diag_block(A, ld, jp, nb);
+      load_diag_blocks(Ls, A, ld, jp, nb);
+   }
    {
       double v = 0.0;
       if (tid < nb) {
@@ -1901,8 +1964,53 @@ __global__ void __launch_bounds__(256) k_bwd_big_diag(FrontArrays F, const int* 
       }
       ys[tid] = v;
    }
-   __syncthreads();
    const int nsb = (nb + NBI - 1) / NBI;
+   if (xoff >= 0) {
+      // x_b = X_b^T t_b, blocks from last to first; the strip of L left of the next block is in flight meanwhile
+      const double* col = A + jp + static_cast<int64_t>(ld) * (jp + tid);   // this thread's column of the diagonal block
+      double v[NBI];
+      {
+         const int base = (nsb - 1) * NBI;
+#pragma unroll
+         for (int t = 0; t < NBI; ++t) v[t] = (tid < base && base + t < nb) ? col[base + t] : 0.0;
+      }
+      __syncthreads();
+      for (int sb = nsb - 1; sb >= 0; --sb) {
+         const int base = sb * NBI;
+         if (warp == 0) {
+            const double* Xc = Ls + base * (NBI + 1) + lane;
+            double a0 = 0.0, a1 = 0.0, a2 = 0.0, a3 = 0.0;
+#pragma unroll
+            for (int r = 0; r < NBI; r += 4) {
+               a0 = fma(Xc[r * (NBI + 1)], ys[base + r], a0);
+               a1 = fma(Xc[(r + 1) * (NBI + 1)], ys[base + r + 1], a1);
+               a2 = fma(Xc[(r + 2) * (NBI + 1)], ys[base + r + 2], a2);
+               a3 = fma(Xc[(r + 3) * (NBI + 1)], ys[base + r + 3], a3);
+            }
+            __syncwarp();
+            ys[base + lane] = (a0 + a1) + (a2 + a3);
+         }
+         __syncthreads();
+         double vn[NBI];
+#pragma unroll
+         for (int t = 0; t < NBI; ++t) vn[t] = (sb > 0 && tid < base - NBI) ? col[base - NBI + t] : 0.0;
+         if (tid < base) {
+            double a0 = 0.0, a1 = 0.0;
+#pragma unroll
+            for (int t = 0; t < NBI; t += 2) {
+               a0 = fma(v[t], ys[base + t], a0);
+               a1 = fma(v[t + 1], ys[base + t + 1], a1);
+            }
+            ys[tid] -= a0 + a1;
+         }
+         __syncthreads();
+#pragma unroll
+         for (int t = 0; t < NBI; ++t) v[t] = vn[t];
+      }
+      if (tid < nb) y[tid] = ys[tid];
+      return;
+   }
+   __syncthreads();
    for (int sb = nsb - 1; sb >= 0; --sb) {
       const int base = sb * NBI;
       const int nbb = min(NBI, nb - base);

@@ -9,8 +9,9 @@ namespace b200kkt {
 constexpr int NBI = 32;    // inner block: pivot search window of the in-front Bunch-Kaufman
 constexpr int NBO = 256;   // outer panel: K of the trailing FP64 tensor-core update
 constexpr int NBS = 256;   // panel width of the multi-CTA triangular solves
-// per front with more than NBI pivots, behind its W panel: X = L11^{-1} and X2 = D^{-1} L11^{-1} of every inner block of the current outer panel
-constexpr int XINV_DOUBLES = 2 * (NBO / NBI) * NBI * NBI;
+// per inner block of a front factored by the panel kernels: X = L11^{-1} and X2 = D^{-1} L11^{-1}, row-major NBI x NBI each;
+// kept after the factorization: the triangular solves of big fronts multiply by X instead of substituting
+constexpr int XINV_BLOCK_DOUBLES = 2 * NBI * NBI;
 
 // device-resident integer plan (SoA over fronts)
 struct FrontArrays {
@@ -28,6 +29,7 @@ struct FrontArrays {
    const int* child_ptr;
    const int* child_idx;
    const int64_t* woff;       // offset of the front's ld x NBO W panel in wpool
+   const int64_t* xoff;       // offset of the front's inverted diagonal blocks in xinv, -1: none (front factored by the light kernels)
 };
 
 struct AssemblyArrays {
@@ -50,6 +52,7 @@ struct FactorArrays {
    double* lpool;    // factor panels
    double* cbpool;   // contribution-block arena
    double* wpool;    // W = L*D panels of the level being factorized
+   double* xinv;     // inverted diagonal blocks (XINV_BLOCK_DOUBLES per inner block)
    double* dd;       // D diagonal, per pivot position (new numbering + in-front pivoting)
    double* de;       // D off-diagonal of 2x2 blocks (stored at the first column of the pair)
    int* ptype;       // 0: 1x1, 1/2: first/second column of a 2x2, 3: null pivot (row/column dropped)

@@ -82,12 +82,15 @@ int size_class(int f) {
 }
 
 // group the fronts of every level into batches of similar order, pivot count descending
-void build_batches(b200kkt_handle* h, std::vector<int>& batch_list, std::vector<int64_t>& woff, int64_t& wpool_size) {
+void build_batches(b200kkt_handle* h, std::vector<int>& batch_list, std::vector<int64_t>& woff, int64_t& wpool_size, std::vector<int64_t>& xoff,
+                   int64_t& xinv_size) {
    const Plan& P = h->plan;
    h->batches.clear();
    h->level_batch_ptr.assign(1, 0);
    batch_list.clear();
    woff.assign(static_cast<size_t>(P.nsn), 0);
+   xoff.assign(static_cast<size_t>(P.nsn), -1);
+   xinv_size = 0;
    wpool_size = 0;
    std::vector<int> ids;
    for (int l = 0; l < P.nlevels; ++l) {
@@ -123,7 +126,10 @@ void build_batches(b200kkt_handle* h, std::vector<int>& batch_list, std::vector<
             const int s = batch_list[static_cast<size_t>(b.begin + t)];
             woff[s] = level_w;
             level_w += static_cast<int64_t>(P.ld[s]) * std::min(NBO, (P.k[s] + 3) & ~3);
-            if (b.max_k > NBI) level_w += XINV_DOUBLES;
+            if (b.max_k > NBI) {
+               xoff[s] = xinv_size;
+               xinv_size += static_cast<int64_t>((P.k[s] + NBI - 1) / NBI) * XINV_BLOCK_DOUBLES;
+            }
          }
          b.big_tiles = (b.max_f > 256) ? h->update_tile_mode : 0;
          h->batches.push_back(std::move(b));
@@ -138,8 +144,9 @@ void upload_plan(b200kkt_handle* h) {
    const auto t0 = std::chrono::steady_clock::now();
    std::vector<int> batch_list;
    std::vector<int64_t> woff;
-   int64_t wpool_size = 0;
-   build_batches(h, batch_list, woff, wpool_size);
+   std::vector<int64_t> xoff;
+   int64_t wpool_size = 0, xinv_size = 0;
+   build_batches(h, batch_list, woff, wpool_size, xoff, xinv_size);
 
    h->F.off = dev_upload(h, P.front_off);
    h->F.k = dev_upload(h, P.k);
@@ -158,6 +165,7 @@ void upload_plan(b200kkt_handle* h) {
    h->F.child_ptr = dev_upload(h, P.child_ptr);
    h->F.child_idx = dev_upload(h, P.child_idx);
    h->F.woff = dev_upload(h, woff);
+   h->F.xoff = dev_upload(h, xoff);
    h->d_perm = dev_upload(h, P.perm);
    h->d_batch_list = dev_upload(h, batch_list);
    h->batch_fronts_host = batch_list;
@@ -210,6 +218,8 @@ void upload_plan(b200kkt_handle* h) {
    h->W.cbpool = dev_alloc<double>(h, static_cast<size_t>(P.cb_pool_size));
    h->wpool_size = (wpool_size + 1) & ~int64_t(1);
    h->W.wpool = dev_alloc<double>(h, static_cast<size_t>(2 * h->wpool_size));
+   h->W.xinv = dev_alloc<double>(h, static_cast<size_t>(std::max<int64_t>(xinv_size, 1)));
+   h->xinv_size = xinv_size;
    h->W.dd = dev_alloc<double>(h, n + 1);
    h->W.de = dev_alloc<double>(h, n + 1);
    h->W.ptype = dev_alloc<int>(h, n + 1);
@@ -868,7 +878,7 @@ extern "C" int b200kkt_debug_bench_update(int device, int f, int k, int reps, in
       const int h32[5] = {hk, hf, hld, hldc, hlist};
       CK(cudaMemcpy(d32, h32, sizeof(h32), cudaMemcpyHostToDevice));
       FrontArrays F{};
-      F.off = d64; F.cboff = d64; F.woff = d64;
+      F.off = d64; F.cboff = d64; F.woff = d64; F.xoff = d64;
       F.k = d32; F.f = d32 + 1; F.ld = d32 + 2; F.ldc = d32 + 3;
       FactorArrays W{};
       W.lpool = lpool; W.cbpool = cbpool; W.wpool = wpool;

@@ -72,6 +72,7 @@ struct b200kkt_handle {
    cudaStream_t panel_stream[NUM_AUX + 1] = {nullptr, nullptr, nullptr, nullptr};
    cudaEvent_t ev_next_cols[NUM_AUX + 1] = {nullptr, nullptr, nullptr, nullptr}, ev_panel[NUM_AUX + 1] = {nullptr, nullptr, nullptr, nullptr};
    int lookahead = 1;
+   int64_t xinv_size = 0;    // doubles of inverted diagonal blocks
    int64_t wpool_size = 0;   // doubles per W-panel buffer (two buffers: panel p uses buffer p & 1)
    int multi_stream = 1;
    int update_tile_mode = 4;   // K4 variant for fronts wider than 256: 1 = 128x128 tiles (8 warps), 2 = 128x64 (4 warps, two CTAs per SM), 3 = warp-specialised persistent, 4 = 128x64 (8 warps, two CTAs per SM), 5 = 128x128 (16 warps)
