@@ -17,6 +17,9 @@ for variant in sys.argv[2:] or [""]:
     for _ in range(4):
         s.do_numerical_factorization(kkt.val)
         ts.append(s.stats()["t_factor_last"] * 1e3)
-    x, berr = s.solve_indefinite_system(kkt.rhs, return_backward_error=True)
-    print(f"{kkt.name} [{variant}]: factor {min(ts[1:]):.1f} ms (first {ts[0]:.1f}) solve {s.stats()['t_solve_last']*1e3:.1f} ms inertia={s.get_inertia()} berr={berr:.2e}", flush=True)
+    tsol = []
+    for _ in range(3):
+        x, berr = s.solve_indefinite_system(kkt.rhs, return_backward_error=True)
+        tsol.append(s.stats()['t_solve_last'] * 1e3)
+    print(f"{kkt.name} [{variant}]: factor {min(ts[1:]):.1f} ms (first {ts[0]:.1f}) solve {min(tsol[1:]):.1f} ms (first {tsol[0]:.1f}) inertia={s.get_inertia()} berr={berr:.2e}", flush=True)
     del s

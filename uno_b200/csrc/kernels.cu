@@ -1157,6 +1157,10 @@ __device__ __forceinline__ void cp_async16(void* smem_dst, const void* gmem_src,
    const int bytes = pred ? 16 : 0;
    asm volatile("cp.async.cg.shared.global [%0], [%1], 16, %2;\n" ::"r"(saddr), "l"(gmem_src), "r"(bytes));
 }
+__device__ __forceinline__ void cp_async16_n(void* smem_dst, const void* gmem_src, const int bytes) {
+   const unsigned saddr = static_cast<unsigned>(__cvta_generic_to_shared(smem_dst));
+   asm volatile("cp.async.cg.shared.global [%0], [%1], 16, %2;\n" ::"r"(saddr), "l"(gmem_src), "r"(bytes));
+}
 __device__ __forceinline__ void cp_async_commit() { asm volatile("cp.async.commit_group;\n" ::); }
 template <int N>
 __device__ __forceinline__ void cp_async_wait() { asm volatile("cp.async.wait_group %0;\n" ::"n"(N)); }
@@ -1713,7 +1717,11 @@ __global__ void __launch_bounds__(256) k_fwd_big_permute(FrontArrays F, const in
    z2[first + j] = zg[first + W.lperm[first + j]];
 }
 
-constexpr int SD_SMEM = static_cast<int>(sizeof(double)) * ((NBS / NBI) * NBI * (NBI + 1) + NBS);
+// the strict block-lower triangle of an NBS x NBS diagonal block in NBI-wide strips (28 blocks of NBI x NBI) plus the panel's vector
+constexpr int SD_STRIP_DOUBLES = NBI * NBI * ((NBS / NBI) * (NBS / NBI - 1) / 2);
+constexpr int SD_SMEM = static_cast<int>(sizeof(double)) * (SD_STRIP_DOUBLES + (NBS / NBI) * 2 + NBS);
+static_assert(SD_SMEM <= 232448, "solve panel kernels: shared memory");
+static_assert(SD_STRIP_DOUBLES >= (NBS / NBI) * NBI * (NBI + 1), "fallback path of the solve panel kernels uses the same buffer");
 
 // prefetch the lower triangle of the NBS x NBS diagonal block of the panel at jp towards L2
 __device__ __forceinline__ void prefetch_diag_block(const double* A, const int ld, const int jp, const int nb) {
@@ -1747,8 +1755,8 @@ __device__ __forceinline__ void load_inverse_blocks(double* Xs, const double* Xg
 __global__ void __launch_bounds__(256) k_fwd_big_diag(FrontArrays F, const int* __restrict__ list, const int jp, FactorArrays W,
                                                        double* __restrict__ z2) {
    extern __shared__ __align__(16) double sd_smem[];
-   double* Ls = sd_smem;                                   // [sb][rr][c], row stride NBI + 1
-   double* ys = sd_smem + (NBS / NBI) * NBI * (NBI + 1);
+   double* Ls = sd_smem;                                   // strips of L (or, fallback, [sb][rr][c] with row stride NBI + 1)
+   double* ys = sd_smem + SD_STRIP_DOUBLES + (NBS / NBI) * 2;
    const int s = list[blockIdx.x];
    const int k = F.k[s], ld = F.ld[s];
    const int nb = min(NBS, k - jp);
@@ -1757,47 +1765,72 @@ __global__ void __launch_bounds__(256) k_fwd_big_diag(FrontArrays F, const int* 
    const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
    const int64_t xoff = F.xoff[s];
    if (xoff >= 0) {
+      // everything the panel needs is requested at once: the strips of L below every inner block (cp.async, rows contiguous)
+      // and, by warp 0, the rows of the inverted diagonal blocks one block ahead; then 8 short steps out of shared memory
       const int nsb = (nb + NBI - 1) / NBI;
-      load_inverse_blocks(Ls, W.xinv + xoff + static_cast<int64_t>(jp / NBI) * XINV_BLOCK_DOUBLES, nsb);
+      const double* Xg = W.xinv + xoff + static_cast<int64_t>(jp / NBI) * XINV_BLOCK_DOUBLES;
+      {
+         int off = 0;
+         for (int b = 0; b + 1 < nsb; ++b) {
+            const int r0 = (b + 1) * NBI, R = nb - r0, Rp = (R + 1) & ~1, chunks = Rp >> 1;
+            for (int idx = tid; idx < NBI * chunks; idx += 256) {
+               const int c = idx / chunks, ch = idx % chunks;
+               cp_async16_n(Ls + off + c * Rp + 2 * ch, A + (jp + r0 + 2 * ch) + static_cast<int64_t>(ld) * (jp + b * NBI + c), (2 * ch + 1 < R) ? 16 : 8);
+            }
+            off += NBI * Rp;
+         }
+         cp_async_commit();
+      }
       ys[tid] = (tid < nb) ? y[tid] : 0.0;
-      const double* row = A + (jp + tid) + static_cast<int64_t>(ld) * jp;   // this thread's row of the diagonal block
-      double v[NBI];
+      double2 xr[NBI / 2];
+      if (warp == 0) {
+         const double2* xp = reinterpret_cast<const double2*>(Xg + lane * NBI);
 #pragma unroll
-      for (int c = 0; c < NBI; ++c) v[c] = (tid >= NBI && tid < nb) ? row[static_cast<int64_t>(ld) * c] : 0.0;
+         for (int c = 0; c < NBI / 2; ++c) xr[c] = xp[c];
+      }
+      cp_async_wait<0>();
       __syncthreads();
+      int off = 0;
       for (int sb = 0; sb < nsb; ++sb) {
          const int base = sb * NBI;
          if (warp == 0) {
-            const double* Xr = Ls + (base + lane) * (NBI + 1);
+            double2 xn[NBI / 2];
+            if (sb + 1 < nsb) {
+               const double2* xp = reinterpret_cast<const double2*>(Xg + static_cast<int64_t>(sb + 1) * XINV_BLOCK_DOUBLES + lane * NBI);
+#pragma unroll
+               for (int c = 0; c < NBI / 2; ++c) xn[c] = xp[c];
+            }
             double a0 = 0.0, a1 = 0.0, a2 = 0.0, a3 = 0.0;
 #pragma unroll
-            for (int c = 0; c < NBI; c += 4) {
-               a0 = fma(Xr[c], ys[base + c], a0);
-               a1 = fma(Xr[c + 1], ys[base + c + 1], a1);
-               a2 = fma(Xr[c + 2], ys[base + c + 2], a2);
-               a3 = fma(Xr[c + 3], ys[base + c + 3], a3);
+            for (int c = 0; c < NBI / 2; c += 2) {
+               a0 = fma(xr[c].x, ys[base + 2 * c], a0);
+               a1 = fma(xr[c].y, ys[base + 2 * c + 1], a1);
+               a2 = fma(xr[c + 1].x, ys[base + 2 * c + 2], a2);
+               a3 = fma(xr[c + 1].y, ys[base + 2 * c + 3], a3);
             }
             __syncwarp();
             ys[base + lane] = (a0 + a1) + (a2 + a3);
-         }
-         __syncthreads();
-         // next strip in flight, then this block applied to the rows below it
-         double vn[NBI];
-         const bool more = tid >= base + 2 * NBI && tid < nb;
+            if (sb + 1 < nsb) {
 #pragma unroll
-         for (int c = 0; c < NBI; ++c) vn[c] = (more && base + NBI + c < nb) ? row[static_cast<int64_t>(ld) * (base + NBI + c)] : 0.0;
-         if (tid >= base + NBI && tid < nb) {
-            double a0 = 0.0, a1 = 0.0;
-#pragma unroll
-            for (int c = 0; c < NBI; c += 2) {
-               a0 = fma(v[c], ys[base + c], a0);
-               a1 = fma(v[c + 1], ys[base + c + 1], a1);
+               for (int c = 0; c < NBI / 2; ++c) xr[c] = xn[c];
             }
-            ys[tid] -= a0 + a1;
          }
          __syncthreads();
+         if (sb + 1 < nsb) {
+            const int r0 = base + NBI, R = nb - r0, Rp = (R + 1) & ~1;
+            if (tid >= r0 && tid < nb) {
+               const double* S = Ls + off + (tid - r0);
+               double a0 = 0.0, a1 = 0.0;
 #pragma unroll
-         for (int c = 0; c < NBI; ++c) v[c] = vn[c];
+               for (int c = 0; c < NBI; c += 2) {
+                  a0 = fma(S[c * Rp], ys[base + c], a0);
+                  a1 = fma(S[(c + 1) * Rp], ys[base + c + 1], a1);
+               }
+               ys[tid] -= a0 + a1;
+            }
+            off += NBI * Rp;
+            __syncthreads();
+         }
       }
       if (tid < nb) y[tid] = ys[tid];
       return;
@@ -1936,7 +1969,7 @@ __global__ void __launch_bounds__(256) k_bwd_big_diag(FrontArrays F, const int* 
                                                        double* __restrict__ z2, const double* __restrict__ partial) {
    extern __shared__ __align__(16) double sd_smem[];
    double* Ls = sd_smem;
-   double* ys = sd_smem + (NBS / NBI) * NBI * (NBI + 1);
+   double* ys = sd_smem + SD_STRIP_DOUBLES + (NBS / NBI) * 2;
    const int s = list[blockIdx.x];
    const int k = F.k[s], f = F.f[s], ld = F.ld[s];
    const int nb = min(NBS, k - jp);
@@ -1944,8 +1977,21 @@ __global__ void __launch_bounds__(256) k_bwd_big_diag(FrontArrays F, const int* 
    double* y = z2 + F.first[s] + jp;
    const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
    const int64_t xoff = F.xoff[s];
+   const int nsb = (nb + NBI - 1) / NBI;
+   const double* Xg = W.xinv + xoff + static_cast<int64_t>(jp / NBI) * XINV_BLOCK_DOUBLES;
    if (xoff >= 0) {
-      load_inverse_blocks(Ls, W.xinv + xoff + static_cast<int64_t>(jp / NBI) * XINV_BLOCK_DOUBLES, (nb + NBI - 1) / NBI);
+      // block rows of L left of every inner block: [column][pair of rows], 16-byte pairs XOR-swizzled by the column so that
+      // the 128-bit reads of a quarter warp (one column per lane) fall into distinct banks
+      for (int b = 1; b < nsb; ++b) {
+         const int base = b * NBI, nbb = min(NBI, nb - base);
+         double* T = Ls + NBI * NBI * (b * (b - 1) / 2);
+         for (int idx = tid; idx < base * (NBI / 2); idx += 256) {
+            const int c = idx / (NBI / 2), pr = idx % (NBI / 2);
+            const int bytes = (2 * pr + 1 < nbb) ? 16 : ((2 * pr < nbb) ? 8 : 0);
+            cp_async16_n(T + c * NBI + 2 * (pr ^ (c & 15)), bytes ? (A + (jp + base + 2 * pr) + static_cast<int64_t>(ld) * (jp + c)) : A, bytes);
+         }
+      }
+      cp_async_commit();
    } else {
       prefetch_diag_block(A, ld, jp, nb);
       load_diag_blocks(Ls, A, ld, jp, nb);
@@ -1964,48 +2010,55 @@ __global__ void __launch_bounds__(256) k_bwd_big_diag(FrontArrays F, const int* 
       }
       ys[tid] = v;
    }
-   const int nsb = (nb + NBI - 1) / NBI;
    if (xoff >= 0) {
-      // x_b = X_b^T t_b, blocks from last to first; the strip of L left of the next block is in flight meanwhile
-      const double* col = A + jp + static_cast<int64_t>(ld) * (jp + tid);   // this thread's column of the diagonal block
-      double v[NBI];
-      {
-         const int base = (nsb - 1) * NBI;
+      // x_b = X_b^T t_b, blocks from last to first; lane c of warp 0 holds column c of the block's inverse, one block ahead
+      double xc[NBI];
+      if (warp == 0) {
+         const double* xp = Xg + static_cast<int64_t>(nsb - 1) * XINV_BLOCK_DOUBLES + lane;
 #pragma unroll
-         for (int t = 0; t < NBI; ++t) v[t] = (tid < base && base + t < nb) ? col[base + t] : 0.0;
+         for (int r = 0; r < NBI; ++r) xc[r] = xp[r * NBI];
       }
+      cp_async_wait<0>();
       __syncthreads();
       for (int sb = nsb - 1; sb >= 0; --sb) {
          const int base = sb * NBI;
          if (warp == 0) {
-            const double* Xc = Ls + base * (NBI + 1) + lane;
+            double xn[NBI];
+            if (sb > 0) {
+               const double* xp = Xg + static_cast<int64_t>(sb - 1) * XINV_BLOCK_DOUBLES + lane;
+#pragma unroll
+               for (int r = 0; r < NBI; ++r) xn[r] = xp[r * NBI];
+            }
             double a0 = 0.0, a1 = 0.0, a2 = 0.0, a3 = 0.0;
 #pragma unroll
             for (int r = 0; r < NBI; r += 4) {
-               a0 = fma(Xc[r * (NBI + 1)], ys[base + r], a0);
-               a1 = fma(Xc[(r + 1) * (NBI + 1)], ys[base + r + 1], a1);
-               a2 = fma(Xc[(r + 2) * (NBI + 1)], ys[base + r + 2], a2);
-               a3 = fma(Xc[(r + 3) * (NBI + 1)], ys[base + r + 3], a3);
+               a0 = fma(xc[r], ys[base + r], a0);
+               a1 = fma(xc[r + 1], ys[base + r + 1], a1);
+               a2 = fma(xc[r + 2], ys[base + r + 2], a2);
+               a3 = fma(xc[r + 3], ys[base + r + 3], a3);
             }
             __syncwarp();
             ys[base + lane] = (a0 + a1) + (a2 + a3);
-         }
-         __syncthreads();
-         double vn[NBI];
+            if (sb > 0) {
 #pragma unroll
-         for (int t = 0; t < NBI; ++t) vn[t] = (sb > 0 && tid < base - NBI) ? col[base - NBI + t] : 0.0;
-         if (tid < base) {
-            double a0 = 0.0, a1 = 0.0;
-#pragma unroll
-            for (int t = 0; t < NBI; t += 2) {
-               a0 = fma(v[t], ys[base + t], a0);
-               a1 = fma(v[t + 1], ys[base + t + 1], a1);
+               for (int r = 0; r < NBI; ++r) xc[r] = xn[r];
             }
-            ys[tid] -= a0 + a1;
          }
          __syncthreads();
+         if (sb > 0) {
+            if (tid < base) {
+               const double* T = Ls + NBI * NBI * (sb * (sb - 1) / 2) + tid * NBI;
+               double a0 = 0.0, a1 = 0.0;
 #pragma unroll
-         for (int t = 0; t < NBI; ++t) v[t] = vn[t];
+               for (int pr = 0; pr < NBI / 2; ++pr) {
+                  const double2 l2 = *reinterpret_cast<const double2*>(T + 2 * (pr ^ (tid & 15)));
+                  a0 = fma(l2.x, ys[base + 2 * pr], a0);
+                  a1 = fma(l2.y, ys[base + 2 * pr + 1], a1);
+               }
+               ys[tid] -= a0 + a1;
+            }
+            __syncthreads();
+         }
       }
       if (tid < nb) y[tid] = ys[tid];
       return;

@@ -14,7 +14,10 @@ namespace b200kkt {
 struct AnalyseOptions {
    int ordering = 0;          // 0 = METIS nested dissection on the KKT-compressed graph, 1 = natural, 2 = user permutation
    int kkt_pairing = 1;       // match each constraint row with a primal column (2x2 pivot candidates)
-   int relax_small = 16;      // always merge a child when the merged pivot count is <= this
+   int relax_small = 16;      // always merge a child when the merged pivot count is <= this (fronts up to relax_small_front rows)
+   int relax_small_front = 256;
+   double relax_chain_zeros = 0.02;   // wide fronts: merge when this step alone adds at most this fraction of explicit zeros ...
+   int relax_chain_max_k = 256;       // ... and the merged front keeps at most this many pivots
    int relax_mid = 64;        // merged pivot count <= this: accept up to relax_mid_zeros explicit zeros
    double relax_mid_zeros = 0.5;
    int relax_big = 256;

@@ -67,6 +67,7 @@ T* dev_alloc(b200kkt_handle* h, size_t count) {
 
 void free_plan_device(b200kkt_handle* h) {
    if (h->factor_graph != nullptr) { cudaGraphExecDestroy(h->factor_graph); h->factor_graph = nullptr; }
+   if (h->solve_graph != nullptr) { cudaGraphExecDestroy(h->solve_graph); h->solve_graph = nullptr; }
    for (void* p : h->plan_allocs) cudaFree(p);
    h->plan_allocs.clear();
    h->analysed = false;
@@ -446,9 +447,8 @@ void run_solve(b200kkt_handle* h, const double* d_b, double* d_x, double* backwa
    CK(cudaMemcpyAsync(h->d_r, d_b, nbytes, cudaMemcpyDeviceToDevice, st));
    CK(cudaMemsetAsync(h->d_norms + 1, 0, 3 * sizeof(unsigned long long), st));
    L += launch_absmax(d_b, P.N, h->d_norms + 3, st);
-   double berr = 0.0, prev = 0.0;
-   int steps = 0;
-   for (int it = 0; it <= h->refine_max_steps; ++it) {
+   // one sweep: permute+scale in, forward, block-diagonal, backward, scale+permute out (accumulating into x)
+   auto enqueue_sweep = [&] {
       L += launch_solve_gather(P.N, h->d_perm, h->d_scale_final, h->d_r, h->d_zg, st);
       for (int l = 0; l < P.nlevels; ++l) {
          const b200kkt_handle::SolveLevel& SL = h->solve_levels[l];
@@ -480,6 +480,31 @@ void run_solve(b200kkt_handle* h, const double* d_b, double* d_x, double* backwa
          }
       }
       L += launch_solve_scatter_add(P.N, h->d_perm, h->d_scale_final, h->d_xg, d_x, st);
+   };
+   double berr = 0.0, prev = 0.0;
+   int steps = 0;
+   for (int it = 0; it <= h->refine_max_steps; ++it) {
+      if (h->use_graph) {
+         // the sweep is a long chain of short kernels: replayed as a CUDA graph (re-captured when the output vector moves)
+         if (h->solve_graph == nullptr || h->solve_graph_x != d_x || h->solve_graph_scale != h->d_scale_final) {
+            if (h->solve_graph != nullptr) { cudaGraphExecDestroy(h->solve_graph); h->solve_graph = nullptr; }
+            const int64_t before = L;
+            cudaGraph_t graph = nullptr;
+            CK(cudaStreamBeginCapture(st, cudaStreamCaptureModeThreadLocal));
+            enqueue_sweep();
+            CK(cudaStreamEndCapture(st, &graph));
+            CK(cudaGraphInstantiate(&h->solve_graph, graph, 0));
+            cudaGraphDestroy(graph);
+            h->solve_graph_launches = L - before;
+            L = before;
+            h->solve_graph_x = d_x;
+            h->solve_graph_scale = h->d_scale_final;
+         }
+         CK(cudaGraphLaunch(h->solve_graph, st));
+         L += h->solve_graph_launches;
+      } else {
+         enqueue_sweep();
+      }
       // K8 residual and backward error
       L += launch_residual(h->C, h->d_values, d_x, d_b, h->d_r, st);
       CK(cudaMemsetAsync(h->d_norms + 1, 0, 2 * sizeof(unsigned long long), st));
@@ -625,6 +650,9 @@ int b200kkt_set_option(b200kkt_handle* h, const char* name, double value) {
    else if (n == "relax_mid_zeros") h->aopt.relax_mid_zeros = value;
    else if (n == "relax_big_zeros") h->aopt.relax_big_zeros = value;
    else if (n == "relax_any_zeros") h->aopt.relax_any_zeros = value;
+   else if (n == "relax_small_front") h->aopt.relax_small_front = static_cast<int>(value);
+   else if (n == "relax_chain_zeros") h->aopt.relax_chain_zeros = value;
+   else if (n == "relax_chain_max_k") h->aopt.relax_chain_max_k = static_cast<int>(value);
    else if (n == "metis_nseps") h->aopt.metis_nseps = static_cast<int>(value);
    else if (n == "metis_niter") h->aopt.metis_niter = static_cast<int>(value);
    else if (n == "metis_ufactor") h->aopt.metis_ufactor = static_cast<int>(value);
@@ -638,8 +666,9 @@ int b200kkt_set_option(b200kkt_handle* h, const char* name, double value) {
    else if (n == "update_tile_mode") h->update_tile_mode = static_cast<int>(value);
    else if (n == "lookahead") h->lookahead = static_cast<int>(value);
    else return fail(h, B200KKT_EINVAL, "unknown option: " + n);
-   // numeric options are baked into the captured graph
+   // numeric options are baked into the captured graphs
    if (h->factor_graph != nullptr) { cudaGraphExecDestroy(h->factor_graph); h->factor_graph = nullptr; }
+   if (h->solve_graph != nullptr) { cudaGraphExecDestroy(h->solve_graph); h->solve_graph = nullptr; }
    return B200KKT_OK;
 }
 

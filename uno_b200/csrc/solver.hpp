@@ -72,6 +72,10 @@ struct b200kkt_handle {
    cudaStream_t panel_stream[NUM_AUX + 1] = {nullptr, nullptr, nullptr, nullptr};
    cudaEvent_t ev_next_cols[NUM_AUX + 1] = {nullptr, nullptr, nullptr, nullptr}, ev_panel[NUM_AUX + 1] = {nullptr, nullptr, nullptr, nullptr};
    int lookahead = 1;
+   cudaGraphExec_t solve_graph = nullptr;   // one solve sweep, captured on first use
+   double* solve_graph_x = nullptr;
+   const double* solve_graph_scale = nullptr;
+   int64_t solve_graph_launches = 0;
    int64_t xinv_size = 0;    // doubles of inverted diagonal blocks
    int64_t wpool_size = 0;   // doubles per W-panel buffer (two buffers: panel p uses buffer p & 1)
    int multi_stream = 1;

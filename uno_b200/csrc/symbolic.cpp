@@ -383,10 +383,14 @@ void analyse(int64_t N, int64_t nnz, int64_t reg_size, int64_t num_primal, const
             const double ratio = static_cast<double>(znew) / nnzl;
             bool merge = force[c] != 0;
             if (!merge) {
-               if (kn <= opt.relax_small) merge = true;
+               // the zeros this merge adds by itself, against the merged front: a nearly nested chain of wide fronts (many small
+               // fronts hanging off a big separator) must not be kept apart by the zeros its leaves brought in earlier
+               const double step = static_cast<double>(kk[c]) * static_cast<double>(kk[c] + ff[s] - ff[c]) / nnzl;
+               if (kn <= opt.relax_small && fn <= opt.relax_small_front) merge = true;
                else if (kn <= opt.relax_mid) merge = ratio <= opt.relax_mid_zeros;
                else if (kn <= opt.relax_big) merge = ratio <= opt.relax_big_zeros;
                else merge = ratio <= opt.relax_any_zeros;
+               if (!merge && fn > opt.relax_small_front && kn <= opt.relax_chain_max_k) merge = step <= opt.relax_chain_zeros;
             }
             if (!merge) continue;
             merged_into[c] = s;
