@@ -280,7 +280,7 @@ def main():
     peak64 = fp64_dgemm_peak(torch)
     hbm_peak, hbm_src = measured_peaks()
     ach = sp["flops_update_profiled"] / sp["t_update_profiled"] / 1e12 if sp["t_update_profiled"] > 0 else 0.0
-    roofline = {"bound": "tensor", "kernel": "k_update<128,128> (K4 Schur update, DMMA.8x8x4)", "achieved": ach, "peak": peak64, "unit": "TFLOP/s",
+    roofline = {"bound": "tensor", "kernel": "k_update<128,64,4,2,16,2> (K4 Schur update, DMMA.8x8x4, 8 warps, two CTAs per SM)", "achieved": ach, "peak": peak64, "unit": "TFLOP/s",
                 "frac": ach / peak64 if peak64 > 0 else None, "traffic": None,
                 "peak_source": "cuBLAS DGEMM 8192^3 via torch.matmul(float64), best of 6, measured in this run (MEASURED_PEAKS.json has no FP64 entry)",
                 "launches_profiled": sp["n_update_profiled"], "flops_profiled": sp["flops_update_profiled"], "seconds_profiled": sp["t_update_profiled"],

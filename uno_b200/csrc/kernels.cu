@@ -1868,39 +1868,39 @@ __global__ void __launch_bounds__(256) k_fwd_big_diag(FrontArrays F, const int* 
    if (tid < nb) y[tid] = ys[tid];
 }
 
-// rows below the panel: v(i) -= L[i, P] . y_P.  CTA = 64 rows x 4 column quarters.
+// rows below the panel: v(i) -= L[i, P] . y_P.  CTA = 32 rows x 8 column groups of 32: every thread has its 32 loads in
+// flight at once (one DRAM round trip per CTA), lanes along the rows (coalesced), partial sums reduced through shared memory.
 __global__ void __launch_bounds__(256) k_fwd_big_gemv(FrontArrays F, const int* __restrict__ list, const int jp, FactorArrays W,
                                                        double* __restrict__ z2, double* __restrict__ cpool) {
    __shared__ double ys[NBS];
-   __shared__ double red[4][64];
+   __shared__ double red[8][32];
    const int s = list[blockIdx.x];
    const int k = F.k[s], f = F.f[s], ld = F.ld[s], first = F.first[s];
    const int nb = min(NBS, k - jp);
-   const int r0 = jp + nb + blockIdx.y * 64;
+   const int r0 = jp + nb + blockIdx.y * 32;
    if (r0 >= f) return;
    const double* A = W.lpool + F.off[s];
    const int tid = threadIdx.x;
+   const int i = r0 + (tid & 31), q = tid >> 5;
+   const int c0 = q * 32;
+   double v[32];
+   const double* row = A + i + static_cast<int64_t>(ld) * (jp + c0);
+#pragma unroll
+   for (int u = 0; u < 32; ++u) v[u] = (i < f && c0 + u < nb) ? row[static_cast<int64_t>(ld) * u] : 0.0;
    ys[tid] = (tid < nb) ? z2[first + jp + tid] : 0.0;
    __syncthreads();
-   const int i = r0 + (tid & 63), q = tid >> 6;
-   double acc = 0.0;
-   if (i < f) {
-      const int c1 = min(nb, q * 64 + 64);
-      const double* row = A + i + static_cast<int64_t>(ld) * jp;
-      int c = q * 64;
-      for (; c + 8 <= c1; c += 8) {
-         double v[8];
+   double a0 = 0.0, a1 = 0.0, a2 = 0.0, a3 = 0.0;
 #pragma unroll
-         for (int u = 0; u < 8; ++u) v[u] = row[static_cast<int64_t>(ld) * (c + u)];
-#pragma unroll
-         for (int u = 0; u < 8; ++u) acc += v[u] * ys[c + u];
-      }
-      for (; c < c1; ++c) acc += row[static_cast<int64_t>(ld) * c] * ys[c];
+   for (int u = 0; u < 32; u += 4) {
+      a0 = fma(v[u], ys[c0 + u], a0);
+      a1 = fma(v[u + 1], ys[c0 + u + 1], a1);
+      a2 = fma(v[u + 2], ys[c0 + u + 2], a2);
+      a3 = fma(v[u + 3], ys[c0 + u + 3], a3);
    }
-   red[q][tid & 63] = acc;
+   red[q][tid & 31] = (a0 + a1) + (a2 + a3);
    __syncthreads();
    if (q == 0 && i < f) {
-      const double sum = (red[0][tid] + red[1][tid]) + (red[2][tid] + red[3][tid]);
+      const double sum = ((red[0][tid] + red[1][tid]) + (red[2][tid] + red[3][tid])) + ((red[4][tid] + red[5][tid]) + (red[6][tid] + red[7][tid]));
       if (i < k) z2[first + i] -= sum; else cpool[F.rel_off[s] + (i - k)] -= sum;
    }
 }
@@ -1932,7 +1932,7 @@ __global__ void __launch_bounds__(256) k_bwd_big_begin(FrontArrays F, const int*
    }
 }
 
-constexpr int BW_SPLITS = 8;   // row splits of the backward panel product (partial sums, reduced in fixed order)
+constexpr int BW_SPLITS = 16;   // row splits of the backward panel product (partial sums, reduced in fixed order)
 
 // partial(split, c) = sum over the split's rows i below the panel of L[i, c] x(i), for the panel columns c.
 // grid = (front, NBS / 8 column groups, BW_SPLITS): one warp per column, lanes along the rows (coalesced).
@@ -1953,6 +1953,15 @@ __global__ void __launch_bounds__(256) k_bwd_big_gemv(FrontArrays F, const int* 
    const double* xb = cpool + F.rel_off[s] - k;
    double acc = 0.0;
    int i = i0 + lane;
+   for (; i + 224 < i1; i += 256) {
+      double l[8], x[8];
+#pragma unroll
+      for (int u = 0; u < 8; ++u) l[u] = col[i + 32 * u];
+#pragma unroll
+      for (int u = 0; u < 8; ++u) x[u] = (i + 32 * u < k) ? y[i + 32 * u] : xb[i + 32 * u];
+#pragma unroll
+      for (int u = 0; u < 8; ++u) acc = fma(l[u], x[u], acc);
+   }
    for (; i + 96 < i1; i += 128) {
       const double l0 = col[i], l1 = col[i + 32], l2 = col[i + 64], l3 = col[i + 96];
       const double x0 = (i < k) ? y[i] : xb[i], x1 = (i + 32 < k) ? y[i + 32] : xb[i + 32];
@@ -2329,7 +2338,7 @@ int launch_fwd_big_diag(const FrontArrays& F, const int* d_list, int nfronts, in
 int launch_fwd_big_gemv(const FrontArrays& F, const int* d_list, int nfronts, int max_f, int jp, const FactorArrays& W, double* z2,
                         double* cpool, cudaStream_t st) {
    if (nfronts <= 0) return 0;
-   const int chunks = (max_f - (jp + 1) + 63) / 64;
+   const int chunks = (max_f - (jp + 1) + 31) / 32;
    if (chunks < 1) return 0;
    dim3 grid(nfronts, chunks);
    k_fwd_big_gemv<<<grid, 256, 0, st>>>(F, d_list, jp, W, z2, cpool);
