@@ -113,25 +113,30 @@ __global__ void k_solve_scatter_add(int64_t n, const int* __restrict__ perm, con
 // child's contribution block, children in ascending order -> no atomics, fixed summation order.
 // Parent column < k lands in the factor panel, column >= k in the parent's contribution block.
 // ------------------------------------------------------------------------------------------------
+// Contribution blocks are stored packed: the lower triangle of the r x r block by columns, column j holding rows j .. r-1.
+// cb_col(r, j) + i is the position of entry (i, j), i >= j.
+__device__ __forceinline__ int64_t cb_col(const int r, const int j) {
+   return static_cast<int64_t>(j) * r - (static_cast<int64_t>(j) * (j - 1)) / 2 - j;
+}
+
 __global__ void __launch_bounds__(256) k_prepare(FrontArrays F, const int* __restrict__ list, FactorArrays W) {
    const int p = list[blockIdx.x];
    const int fp = F.f[p], kp = F.k[p];
    const int cb0 = blockIdx.y * EA_CBW;
    if (cb0 >= fp) return;
    const int cb1 = min(cb0 + EA_CBW, fp);
-   const int ldp = F.ld[p], ldcp = F.ldc[p];
+   const int ldp = F.ld[p], rp = fp - kp;
    double* Lp = W.lpool + F.off[p];
    double* Cp = W.cbpool + F.cboff[p];
    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
    for (int col = max(cb0, kp) + warp; col < cb1; col += 8) {
-      double* dst = Cp + static_cast<int64_t>(ldcp) * (col - kp) - kp;
+      double* dst = Cp + cb_col(rp, col - kp) - kp;
       for (int i = col + lane; i < fp; i += 32) dst[i] = 0.0;
    }
    if (F.child_ptr[p] == F.child_ptr[p + 1]) return;
    __syncthreads();
    for (int ci = F.child_ptr[p]; ci < F.child_ptr[p + 1]; ++ci) {
       const int c = F.child_idx[ci];
-      const int ldcc = F.ldc[c];
       const int rc = F.f[c] - F.k[c];
       const int* __restrict__ rel = F.relmap + F.rel_off[c];
       // rel is strictly increasing: columns of the child that land in [cb0, cb1) are a contiguous range
@@ -144,8 +149,8 @@ __global__ void __launch_bounds__(256) k_prepare(FrontArrays F, const int* __res
       const double* Ac = W.cbpool + F.cboff[c];
       for (int j = jlo + warp; j < jhi; j += 8) {
          const int pc = rel[j];
-         double* dst = (pc < kp) ? (Lp + static_cast<int64_t>(ldp) * pc) : (Cp + static_cast<int64_t>(ldcp) * (pc - kp) - kp);
-         const double* src = Ac + static_cast<int64_t>(ldcc) * j;
+         double* dst = (pc < kp) ? (Lp + static_cast<int64_t>(ldp) * pc) : (Cp + cb_col(rp, pc - kp) - kp);
+         const double* src = Ac + cb_col(rc, j);
          int i = j + lane;
          for (; i + 96 < rc; i += 128) {
             const int r0 = rel[i], r1 = rel[i + 32], r2 = rel[i + 64], r3 = rel[i + 96];
@@ -1198,8 +1203,10 @@ __global__ void __launch_bounds__(WARPS_M* WARPS_N * 32, MINB) k_update(FrontArr
 
    double* A = W.lpool + F.off[s];
    // columns >= k of the trailing matrix live in the contribution block (rows and columns shifted by k)
-   const int ldc = F.ldc[s];
-   double* Cb = W.cbpool + F.cboff[s] - k - static_cast<int64_t>(ldc) * k;
+   double* Cb = W.cbpool + F.cboff[s] - k;
+   const int rcb = f - k;
+   // column n of the trailing matrix: in the factor panel (n < k) or in the packed contribution block
+   auto col_ptr = [&](const int n) -> double* { return (n < k) ? (A + static_cast<int64_t>(ld) * n) : (Cb + cb_col(rcb, n - k)); };
    const double* Wp = W.wpool + F.woff[s] + static_cast<int64_t>(ld) * kbeg;   // operand A: rows m, K columns
    const double* Lp = A + static_cast<int64_t>(ld) * (J0 + kbeg);               // operand B: rows n, K columns
 
@@ -1228,7 +1235,7 @@ __global__ void __launch_bounds__(WARPS_M* WARPS_N * 32, MINB) k_update(FrontArr
    for (int q = tid; q < BN * (BM / 16); q += NT) {
       const int n = n0 + q / (BM / 16), m = m0 + (q % (BM / 16)) * 16;
       if (n < c1 && m < f && m + 15 >= n) {
-         const double* pc = (n < k) ? (A + m + static_cast<int64_t>(ld) * n) : (Cb + m + static_cast<int64_t>(ldc) * n);
+         const double* pc = col_ptr(n) + m;
          asm volatile("prefetch.global.L2 [%0];" ::"l"(pc));
       }
    }
@@ -1274,23 +1281,23 @@ __global__ void __launch_bounds__(WARPS_M* WARPS_N * 32, MINB) k_update(FrontArr
    // Interior tiles (fully inside the region, strictly below the diagonal, on one side of column k):
    // no per-element predicates, loads batched 2*MF deep so that the read-modify-write is not a chain
    // of dependent round trips.
-   const bool interior = m0 >= r0 && m0 + BM <= f && n0 >= c0 && n0 + BN <= c1 && m0 >= n0 + BN && (n0 + BN <= k || n0 >= k);
+   const bool interior = m0 >= r0 && m0 + BM <= f && n0 >= c0 && n0 + BN <= c1 && m0 >= n0 + BN;
    if (interior) {
-      double* base;
-      int64_t ldo;
-      if (n0 < k) { base = A; ldo = ld; } else { base = Cb; ldo = ldc; }
-      base += (m0 + wm0 + (lane >> 2)) + ldo * (n0 + wn0 + 2 * (lane & 3));
+      const int mrow = m0 + wm0 + (lane >> 2);
 #pragma unroll
       for (int b = 0; b < NF; ++b) {
+         double* cp[2];
+#pragma unroll
+         for (int h = 0; h < 2; ++h) cp[h] = col_ptr(n0 + wn0 + b * 8 + 2 * (lane & 3) + h) + mrow;
          double v[MF][2];
 #pragma unroll
          for (int a = 0; a < MF; ++a)
 #pragma unroll
-            for (int h = 0; h < 2; ++h) v[a][h] = base[a * 8 + ldo * (b * 8 + h)];
+            for (int h = 0; h < 2; ++h) v[a][h] = cp[h][a * 8];
 #pragma unroll
          for (int a = 0; a < MF; ++a)
 #pragma unroll
-            for (int h = 0; h < 2; ++h) base[a * 8 + ldo * (b * 8 + h)] = v[a][h] - acc[a][b][h];
+            for (int h = 0; h < 2; ++h) cp[h][a * 8] = v[a][h] - acc[a][b][h];
       }
       return;
    }
@@ -1302,7 +1309,7 @@ __global__ void __launch_bounds__(WARPS_M* WARPS_N * 32, MINB) k_update(FrontArr
 #pragma unroll
       for (int h = 0; h < 2; ++h) {
          const int n = n0 + wn0 + b * 8 + 2 * (lane & 3) + h;
-         dst[h] = (n < k) ? (A + static_cast<int64_t>(ld) * n) : (Cb + static_cast<int64_t>(ldc) * n);
+         dst[h] = col_ptr(n);
 #pragma unroll
          for (int a = 0; a < MF; ++a) {
             const int m = m0 + wm0 + a * 8 + (lane >> 2);
@@ -1392,8 +1399,9 @@ __global__ void __maxnreg__(200) k_update_ws(FrontArrays F, const int* __restric
       const int Tm = (f - mbase + WS_BM - 1) / WS_BM, Tn = (f - mbase + WS_BN - 1) / WS_BN;
       const int ntiles = Tm * (Tm + 1) - (2 * Tm - Tn);
       double* A = W.lpool + F.off[s];
-      const int ldc = F.ldc[s];
-      double* Cb = W.cbpool + F.cboff[s] - k - static_cast<int64_t>(ldc) * k;   // columns >= k live in the contribution block
+      double* Cb = W.cbpool + F.cboff[s] - k;   // columns >= k live in the packed contribution block
+      const int rcb = f - k;
+      auto col_ptr = [&](const int n) -> double* { return (n < k) ? (A + static_cast<int64_t>(ld) * n) : (Cb + cb_col(rcb, n - k)); };
       const double* Wp = W.wpool + F.woff[s];                  // operand A: rows m, K columns
       const double* Lp = A + static_cast<int64_t>(ld) * J0;    // operand B: rows n, K columns
       const int num_kt = (K + WS_BK - 1) / WS_BK;
@@ -1414,7 +1422,7 @@ __global__ void __maxnreg__(200) k_update_ws(FrontArrays F, const int* __restric
             for (int q = lane; q < WS_BN * (WS_BM / 16); q += 32) {
                const int n = n0 + q / (WS_BM / 16), m = m0 + (q % (WS_BM / 16)) * 16;
                if (n < f && m < f && m + 15 >= n) {
-                  const double* pc = (n < k) ? (A + m + static_cast<int64_t>(ld) * n) : (Cb + m + static_cast<int64_t>(ldc) * n);
+                  const double* pc = col_ptr(n) + m;
                   asm volatile("prefetch.global.L2 [%0];" ::"l"(pc));
                }
             }
@@ -1465,23 +1473,23 @@ __global__ void __maxnreg__(200) k_update_ws(FrontArrays F, const int* __restric
             // epilogue: C -= acc.  Interior tiles (strictly below the diagonal, fully inside, on one side of column k)
             // take the path without per-element predicates; loads are batched so that the read-modify-write is not a
             // chain of dependent round trips.
-            const bool interior = m0 >= J1 && m0 + WS_BM <= f && n0 >= J1 && n0 + WS_BN <= f && m0 >= n0 + WS_BN && (n0 + WS_BN <= k || n0 >= k);
+            const bool interior = m0 >= J1 && m0 + WS_BM <= f && n0 >= J1 && n0 + WS_BN <= f && m0 >= n0 + WS_BN;
             if (interior) {
-               double* cbase;
-               int64_t ldo;
-               if (n0 < k) { cbase = A; ldo = ld; } else { cbase = Cb; ldo = ldc; }
-               cbase += (m0 + wm0 + (lane >> 2)) + ldo * (n0 + wn0 + 2 * (lane & 3));
+               const int mrow = m0 + wm0 + (lane >> 2);
 #pragma unroll
                for (int b = 0; b < NF; ++b) {
+                  double* cp[2];
+#pragma unroll
+                  for (int h = 0; h < 2; ++h) cp[h] = col_ptr(n0 + wn0 + b * 8 + 2 * (lane & 3) + h) + mrow;
                   double v[MF][2];
 #pragma unroll
                   for (int a = 0; a < MF; ++a)
 #pragma unroll
-                     for (int h = 0; h < 2; ++h) v[a][h] = cbase[a * 8 + ldo * (b * 8 + h)];
+                     for (int h = 0; h < 2; ++h) v[a][h] = cp[h][a * 8];
 #pragma unroll
                   for (int a = 0; a < MF; ++a)
 #pragma unroll
-                     for (int h = 0; h < 2; ++h) cbase[a * 8 + ldo * (b * 8 + h)] = v[a][h] - acc[a][b][h];
+                     for (int h = 0; h < 2; ++h) cp[h][a * 8] = v[a][h] - acc[a][b][h];
                }
             } else {
 #pragma unroll
@@ -1492,7 +1500,7 @@ __global__ void __maxnreg__(200) k_update_ws(FrontArrays F, const int* __restric
 #pragma unroll
                   for (int h = 0; h < 2; ++h) {
                      const int n = n0 + wn0 + b * 8 + 2 * (lane & 3) + h;
-                     dst[h] = (n < k) ? (A + static_cast<int64_t>(ld) * n) : (Cb + static_cast<int64_t>(ldc) * n);
+                     dst[h] = col_ptr(n);
 #pragma unroll
                      for (int a = 0; a < MF; ++a) {
                         const int m = m0 + wm0 + a * 8 + (lane >> 2);

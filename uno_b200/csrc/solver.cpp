@@ -304,7 +304,7 @@ void enqueue_factor(b200kkt_handle* h) {
          const int* list = h->d_batch_list + b.begin;
          const int lane = (bi - h->level_batch_ptr[l]) % (nside + 1);
          cudaStream_t st = (lane == 0) ? h->stream : h->aux[lane - 1];
-         if (b.has_cb || b.has_children) L += launch_prepare(h->F, list, b.count, b.max_f, h->W, st);
+         if ((b.has_cb || b.has_children) && !(h->debug_skip & 4)) L += launch_prepare(h->F, list, b.count, b.max_f, h->W, st);
          // W panels are double-buffered: panel p of a front lives in buffer p & 1
          FactorArrays Wbuf[2] = {h->W, h->W};
          Wbuf[1].wpool += h->wpool_size;
@@ -314,9 +314,9 @@ void enqueue_factor(b200kkt_handle* h) {
          for (int J0 = 0; J0 < b.max_k; J0 += NBO, ++p) {
             const int nfP = b.count_k_greater(J0);
             const FactorArrays& Wp = Wbuf[p & 1];
-            if (!ahead || J0 == 0) {
-               L += launch_diagpanel(h->F, list, nfP, b.max_k, J0, Wp, h->null_pivot_tol, st);
-               L += launch_trsmpanel(h->F, list, nfP, b.pmaxf[nfP - 1], b.max_k, J0, Wp, st);
+            if ((!ahead || J0 == 0) && !(h->debug_skip & 2)) {
+               if (!(h->debug_skip & 16)) L += launch_diagpanel(h->F, list, nfP, b.max_k, J0, Wp, h->null_pivot_tol, st);
+               if (!(h->debug_skip & 8)) L += launch_trsmpanel(h->F, list, nfP, b.pmaxf[nfP - 1], b.max_k, J0, Wp, st);
             }
             const bool prof_this = prof && b.max_f >= 1024;
             if (prof_this) {
@@ -332,15 +332,17 @@ void enqueue_factor(b200kkt_handle* h) {
                // look-ahead: update the next panel's columns, factor that panel on the panel stream while the rest of
                // the trailing matrix is updated here
                const int nfN = b.count_k_greater(J0 + NBO);
-               L += launch_update(h->F, list, nfP, b.pmaxf[nfP - 1], 2, 0, J0, Wp, b.big_tiles, st);
+               if (!(h->debug_skip & 1)) L += launch_update(h->F, list, nfP, b.pmaxf[nfP - 1], 2, 0, J0, Wp, b.big_tiles, st);
                CK(cudaEventRecord(h->ev_next_cols[lane], st));
                CK(cudaStreamWaitEvent(pst, h->ev_next_cols[lane], 0));
-               L += launch_diagpanel(h->F, list, nfN, b.max_k, J0 + NBO, Wbuf[(p + 1) & 1], h->null_pivot_tol, pst);
-               L += launch_trsmpanel(h->F, list, nfN, b.pmaxf[nfN - 1], b.max_k, J0 + NBO, Wbuf[(p + 1) & 1], pst);
+               if (!(h->debug_skip & 2)) {
+                  if (!(h->debug_skip & 16)) L += launch_diagpanel(h->F, list, nfN, b.max_k, J0 + NBO, Wbuf[(p + 1) & 1], h->null_pivot_tol, pst);
+                  if (!(h->debug_skip & 8)) L += launch_trsmpanel(h->F, list, nfN, b.pmaxf[nfN - 1], b.max_k, J0 + NBO, Wbuf[(p + 1) & 1], pst);
+               }
                CK(cudaEventRecord(h->ev_panel[lane], pst));
-               L += launch_update(h->F, list, nfP, b.pmaxf[nfP - 1], 3, 0, J0, Wp, b.big_tiles, st);
+               if (!(h->debug_skip & 1)) L += launch_update(h->F, list, nfP, b.pmaxf[nfP - 1], 3, 0, J0, Wp, b.big_tiles, st);
                CK(cudaStreamWaitEvent(st, h->ev_panel[lane], 0));
-            } else {
+            } else if (!(h->debug_skip & 1)) {
                L += launch_update(h->F, list, nfP, b.pmaxf[nfP - 1], 1, 0, J0, Wp, b.big_tiles, st);
             }
             if (prof_this) prof_end();
@@ -665,6 +667,7 @@ int b200kkt_set_option(b200kkt_handle* h, const char* name, double value) {
    else if (n == "multi_stream") h->multi_stream = static_cast<int>(value);
    else if (n == "update_tile_mode") h->update_tile_mode = static_cast<int>(value);
    else if (n == "lookahead") h->lookahead = static_cast<int>(value);
+   else if (n == "debug_skip") h->debug_skip = static_cast<int>(value);   // timing experiments only: 1 no K4, 2 no panel kernels, 4 no K5
    else return fail(h, B200KKT_EINVAL, "unknown option: " + n);
    // numeric options are baked into the captured graphs
    if (h->factor_graph != nullptr) { cudaGraphExecDestroy(h->factor_graph); h->factor_graph = nullptr; }
@@ -885,7 +888,7 @@ extern "C" int b200kkt_debug_bench_update(int device, int f, int k, int reps, in
    try {
       CK(cudaSetDevice(device));
       if (init_kernel_attributes() != 0) return B200KKT_ECUDA;
-      const int ld = (f + 3) & ~3, r = f - k, ldc = (r + 3) & ~3;
+      const int ld = (f + 3) & ~3, r = f - k, ldc = r;
       std::vector<double> hl(static_cast<size_t>(ld) * k), hw(static_cast<size_t>(ld) * NBO);
       uint64_t sd = 88172645463325252ull;
       auto rnd = [&] { sd ^= sd << 13; sd ^= sd >> 7; sd ^= sd << 17; return (static_cast<double>(sd >> 11) / 9007199254740992.0) - 0.5; };

@@ -72,6 +72,7 @@ struct b200kkt_handle {
    cudaStream_t panel_stream[NUM_AUX + 1] = {nullptr, nullptr, nullptr, nullptr};
    cudaEvent_t ev_next_cols[NUM_AUX + 1] = {nullptr, nullptr, nullptr, nullptr}, ev_panel[NUM_AUX + 1] = {nullptr, nullptr, nullptr, nullptr};
    int lookahead = 1;
+   int debug_skip = 0;
    cudaGraphExec_t solve_graph = nullptr;   // one solve sweep, captured on first use
    double* solve_graph_x = nullptr;
    const double* solve_graph_scale = nullptr;

@@ -536,7 +536,7 @@ void analyse(int64_t N, int64_t nnz, int64_t reg_size, int64_t num_primal, const
    for (int32_t s = 0; s < nsn; ++s) {
       P.front_off[s] = off;
       off += static_cast<int64_t>(P.ld[s]) * P.k[s];
-      P.ldc[s] = (P.f[s] - P.k[s] + 3) & ~3;
+      P.ldc[s] = P.f[s] - P.k[s];   // contribution blocks are packed lower triangles: no padding
       const double kd = P.k[s], rd = P.f[s] - P.k[s];
       P.nnz_L += static_cast<int64_t>(P.k[s]) * P.f[s] - static_cast<int64_t>(P.k[s]) * (P.k[s] - 1) / 2;
       const double fl = kd * kd * kd / 3.0 + kd * kd * rd + kd * rd * rd;
@@ -554,7 +554,10 @@ void analyse(int64_t N, int64_t nnz, int64_t reg_size, int64_t num_primal, const
       P.cb_off.assign(nsn, 0);
       std::map<int64_t, int64_t> free_list;   // offset -> size, coalesced
       int64_t top = 0;
-      auto cb_size = [&](int32_t s) { return static_cast<int64_t>(P.ldc[s]) * (P.f[s] - P.k[s]); };
+      auto cb_size = [&](int32_t s) {
+         const int64_t r = P.f[s] - P.k[s];
+         return (r * (r + 1) / 2 + 1) & ~int64_t(1);   // packed lower triangle, even number of doubles
+      };
       auto alloc = [&](int64_t size) {
          for (auto it = free_list.begin(); it != free_list.end(); ++it) {
             if (it->second >= size) {
