@@ -196,7 +196,7 @@ def main():
 
     import torch
     import torch.distributed as dist
-    from uno_b200 import KKTSolver
+    from uno_b200 import KKTSolver, replicas
     if not torch.cuda.is_available():
         raise SystemExit("bench.py --impl b200 needs a CUDA device: the numeric phase has no CPU path")
     torch.cuda.set_device(local_rank)
@@ -205,7 +205,7 @@ def main():
     fallback_note = None
     while True:
         desc = WORKLOADS[args.workload][0]
-        kkt = WORKLOADS[args.workload][1](G, rank)       # one independent KKT system per rank (replicas)
+        kkt = WORKLOADS[args.workload][1](G, replicas.rank_seed(rank))   # one independent KKT system per rank (replicas)
         solver = KKTSolver(device=local_rank)
         t0 = time.perf_counter()
         ok = True
@@ -214,10 +214,7 @@ def main():
         except Exception as exc:   # device pools do not fit
             ok = False
             fallback_note = f"{args.workload} did not fit this device ({exc}); fell back to ocp3d_k64"
-        if world > 1:
-            flag = torch.tensor([1 if ok else 0], device="cuda")
-            dist.all_reduce(flag, op=dist.ReduceOp.MIN)
-            ok = bool(flag.item())
+        ok = replicas.all_ranks_ok(ok, dist, "cuda")
         if ok or not auto or args.workload == "ocp3d_k64":
             if not ok:
                 raise SystemExit(fallback_note or "analysis failed on another rank")
@@ -273,11 +270,8 @@ def main():
     barrier()
     clocks = sampler.stop()
     launches = solver.stats()["kernel_launches"] - launches0
-    elapsed = torch.tensor([e0.elapsed_time(e1) * 1e-3], device="cuda")
-    if world > 1:
-        dist.all_reduce(elapsed, op=dist.ReduceOp.MAX)
-    elapsed = float(elapsed.item())
-    value = world * args.steps / elapsed
+    elapsed = replicas.max_over_ranks(e0.elapsed_time(e1) * 1e-3, dist, "cuda")
+    value = replicas.aggregate_throughput(args.steps, world, elapsed)
 
     # end to end through the C ABI with host buffers
     step_host()
@@ -286,10 +280,7 @@ def main():
     for _ in range(args.steps):
         ine_h, berr_h = step_host()
     torch.cuda.synchronize()
-    t_e2e = torch.tensor([time.perf_counter() - t0], device="cuda")
-    if world > 1:
-        dist.all_reduce(t_e2e, op=dist.ReduceOp.MAX)
-    e2e_value = world * args.steps / float(t_e2e.item())
+    e2e_value = replicas.aggregate_throughput(args.steps, world, replicas.max_over_ranks(time.perf_counter() - t0, dist, "cuda"))
     x_ok = bool(np.isfinite(h_x.numpy()).all())
 
     if rank != 0:
