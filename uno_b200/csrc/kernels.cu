@@ -1171,9 +1171,8 @@ template <int N>
 __device__ __forceinline__ void cp_async_wait() { asm volatile("cp.async.wait_group %0;\n" ::"n"(N)); }
 
 
-constexpr int UPD_STAGES = 3;
 
-template <int BM, int BN, int WARPS_M, int WARPS_N, int UPD_BK, int MINB = 1>
+template <int BM, int BN, int WARPS_M, int WARPS_N, int UPD_BK, int MINB = 1, int UPD_STAGES = 3>
 __global__ void __launch_bounds__(WARPS_M* WARPS_N * 32, MINB) k_update(FrontArrays F, const int* __restrict__ list, const int mode, const int j0,
                                                                   const int J0, FactorArrays W) {
    constexpr int NT = WARPS_M * WARPS_N * 32;
@@ -1213,21 +1212,42 @@ __global__ void __launch_bounds__(WARPS_M* WARPS_N * 32, MINB) k_update(FrontArr
    const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
    const int wm0 = (warp % WARPS_M) * WTM, wn0 = (warp / WARPS_M) * WTN;
 
+   // every thread moves the same chunks of every stage: source pointers and row predicates are fixed per thread,
+   // a stage refill is a handful of pointer increments
+   constexpr int A_CHUNKS = UPD_BK * (BM / 2) / NT, B_CHUNKS = UPD_BK * (BN / 2) / NT;
+   static_assert(UPD_BK * (BM / 2) % NT == 0 && UPD_BK * (BN / 2) % NT == 0, "stage chunks must divide evenly over the threads");
+   const double* a_src[A_CHUNKS];
+   const double* b_src[B_CHUNKS];
+   int a_dst[A_CHUNKS], b_dst[B_CHUNKS], a_kk[A_CHUNKS], b_kk[B_CHUNKS];
+#pragma unroll
+   for (int c = 0; c < A_CHUNKS; ++c) {
+      const int q = tid + c * NT, kk = q / (BM / 2), mm = (q % (BM / 2)) * 2;
+      const bool rowok = m0 + mm < ld;
+      a_kk[c] = rowok ? kk : (1 << 20);   // out-of-range rows never pass the k test
+      a_src[c] = Wp + (rowok ? (m0 + mm) : 0) + static_cast<int64_t>(ld) * kk;
+      a_dst[c] = kk * LDA + mm;
+   }
+#pragma unroll
+   for (int c = 0; c < B_CHUNKS; ++c) {
+      const int q = tid + c * NT, kk = q / (BN / 2), nn = (q % (BN / 2)) * 2;
+      const bool rowok = n0 + nn < ld;
+      b_kk[c] = rowok ? kk : (1 << 20);
+      b_src[c] = Lp + (rowok ? (n0 + nn) : 0) + static_cast<int64_t>(ld) * kk;
+      b_dst[c] = UPD_BK * LDA + kk * LDB + nn;
+   }
+   const int64_t kstride = static_cast<int64_t>(ld) * UPD_BK;
    auto load_stage = [&](const int stage, const int kt) {
-      double* As = smem + stage * STAGE_DOUBLES;
-      double* Bs = As + UPD_BK * LDA;
+      double* base = smem + stage * STAGE_DOUBLES;
       const int kbase = kt * UPD_BK;
-      for (int q = tid; q < UPD_BK * (BM / 2); q += NT) {
-         const int kk = q / (BM / 2), mm = (q % (BM / 2)) * 2;
-         const bool pred = (kbase + kk < K) && (m0 + mm < ld);
-         const double* src = pred ? (Wp + (m0 + mm) + static_cast<int64_t>(ld) * (kbase + kk)) : Wp;
-         cp_async16(As + kk * LDA + mm, src, pred);
+#pragma unroll
+      for (int c = 0; c < A_CHUNKS; ++c) {
+         const bool pred = kbase + a_kk[c] < K;
+         cp_async16(base + a_dst[c], pred ? (a_src[c] + kstride * kt) : Wp, pred);
       }
-      for (int q = tid; q < UPD_BK * (BN / 2); q += NT) {
-         const int kk = q / (BN / 2), nn = (q % (BN / 2)) * 2;
-         const bool pred = (kbase + kk < K) && (n0 + nn < ld);
-         const double* src = pred ? (Lp + (n0 + nn) + static_cast<int64_t>(ld) * (kbase + kk)) : Lp;
-         cp_async16(Bs + kk * LDB + nn, src, pred);
+#pragma unroll
+      for (int c = 0; c < B_CHUNKS; ++c) {
+         const bool pred = kbase + b_kk[c] < K;
+         cp_async16(base + b_dst[c], pred ? (b_src[c] + kstride * kt) : Lp, pred);
       }
    };
 
@@ -1255,11 +1275,6 @@ __global__ void __launch_bounds__(WARPS_M* WARPS_N * 32, MINB) k_update(FrontArr
    for (int kt = 0; kt < num_kt; ++kt) {
       cp_async_wait<UPD_STAGES - 2>();
       __syncthreads();
-      {
-         const int nk = kt + UPD_STAGES - 1;
-         if (nk < num_kt) load_stage(nk % UPD_STAGES, nk);
-         cp_async_commit();
-      }
       const double* As = smem + (kt % UPD_STAGES) * STAGE_DOUBLES;
       const double* Bs = As + UPD_BK * LDA;
 #pragma unroll
@@ -1274,6 +1289,13 @@ __global__ void __launch_bounds__(WARPS_M* WARPS_N * 32, MINB) k_update(FrontArr
          for (int a = 0; a < MF; ++a)
 #pragma unroll
             for (int b = 0; b < NF; ++b) dmma8x8x4(acc[a][b][0], acc[a][b][1], af[a], bf[b]);
+         if (k4 == 0) {
+            // refill the stage consumed in the previous iteration behind the first DMMA group: the address arithmetic
+            // issues in the pipe's 16-cycle slots instead of holding the tensor pipe up after the barrier
+            const int nk = kt + UPD_STAGES - 1;
+            if (nk < num_kt) load_stage(nk % UPD_STAGES, nk);
+            cp_async_commit();
+         }
       }
    }
    cp_async_wait<0>();
@@ -2188,7 +2210,7 @@ int launch_permute_rows(const FrontArrays& F, const int* d_list, int nfronts, in
 }
 
 namespace {
-constexpr int smem_bytes(int bm, int bn, int bk) { return UPD_STAGES * bk * (bm + 4 + bn + 4) * static_cast<int>(sizeof(double)); }
+constexpr int smem_bytes(int bm, int bn, int bk, int stages = 3) { return stages * bk * (bm + 4 + bn + 4) * static_cast<int>(sizeof(double)); }
 }
 
 // micro-benchmark: one warp factors the same random symmetric 32 x 32 block `reps` times; cycles per factorization
@@ -2265,6 +2287,8 @@ int init_kernel_attributes() {
    if (e != cudaSuccess) return static_cast<int>(e);
    e = cudaFuncSetAttribute(k_update<128, 128, 4, 4, 32, 1>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem_bytes(128, 128, 32));
    if (e != cudaSuccess) return static_cast<int>(e);
+   e = cudaFuncSetAttribute(k_update<128, 64, 4, 2, 32, 2, 2>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem_bytes(128, 64, 32, 2));
+   if (e != cudaSuccess) return static_cast<int>(e);
    e = cudaFuncSetAttribute(k_update_ws, cudaFuncAttributeMaxDynamicSharedMemorySize, WS_SMEM);
    return static_cast<int>(e);
 }
@@ -2278,7 +2302,10 @@ int launch_update(const FrontArrays& F, const int* d_list, int nfronts, int max_
    if (rows <= 0) return 0;
    const int cols = (mode == 0) ? NBO : ((mode == 2) ? std::min(rows, NBO + 2) : ((mode == 3) ? rows - NBO : rows));
    if (cols <= 0) return 0;
-   if (tile_mode == 4) {
+   if (tile_mode == 6) {
+      dim3 grid(nfronts, (rows + 127) / 128, (cols + 63) / 64);
+      k_update<128, 64, 4, 2, 32, 2, 2><<<grid, 256, smem_bytes(128, 64, 32, 2), st>>>(F, d_list, mode, j0, J0, W);
+   } else if (tile_mode == 4) {
       dim3 grid(nfronts, (rows + 127) / 128, (cols + 63) / 64);
       k_update<128, 64, 4, 2, 16, 2><<<grid, 256, smem_bytes(128, 64, 16), st>>>(F, d_list, mode, j0, J0, W);
    } else if (tile_mode == 5) {
