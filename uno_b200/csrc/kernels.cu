@@ -1174,7 +1174,7 @@ __device__ __forceinline__ void cp_async_wait() { asm volatile("cp.async.wait_gr
 
 template <int BM, int BN, int WARPS_M, int WARPS_N, int UPD_BK, int MINB = 1, int UPD_STAGES = 3>
 __global__ void __launch_bounds__(WARPS_M* WARPS_N * 32, MINB) k_update(FrontArrays F, const int* __restrict__ list, const int mode, const int j0,
-                                                                  const int J0, FactorArrays W) {
+                                                                  const int J0, FactorArrays W, const UpdateRange R) {
    constexpr int NT = WARPS_M * WARPS_N * 32;
    constexpr int LDA = BM + 4, LDB = BN + 4;   // +4 doubles: conflict-free fragment loads (LD mod 16 == 4)
    constexpr int WTM = BM / WARPS_M, WTN = BN / WARPS_N, MF = WTM / 8, NF = WTN / 8;
@@ -1183,16 +1183,23 @@ __global__ void __launch_bounds__(WARPS_M* WARPS_N * 32, MINB) k_update(FrontArr
 
    const int s = list[blockIdx.x];
    const int k = F.k[s], f = F.f[s], ld = F.ld[s];
-   const int J1 = min(J0 + NBO, k);
+   const int J1 = min(J0 + R.kpanels * NBO, k);   // end of the K range: one outer panel, or two taken together
    int r0, c0, c1, kbeg, K;
    if (mode == 0) {
       const int j1 = min(j0 + NBI, k);
-      r0 = j1; c0 = j1; c1 = J1; kbeg = j0 - J0; K = j1 - j0;
+      r0 = j1; c0 = j1; c1 = min(J0 + NBO, k); kbeg = j0 - J0; K = j1 - j0;
    } else {
-      // trailing matrix; modes 2 and 3 split it by columns (look-ahead: the next outer panel's columns first)
+      // trailing matrix behind the K range, columns [J1 + clo NBO, J1 + chi NBO); R.policy: see UpdateRange.
+      // A front without the second panel of a pair is not part of a two-panel update.
+      if (R.kpanels == 2 && k <= J0 + NBO) return;
       r0 = J1; c0 = J1; c1 = f; kbeg = 0; K = J1 - J0;
-      if (mode == 2) c1 = min(f, J1 + NBO);
-      else if (mode == 3) c0 = J1 + NBO;
+      const bool last = k <= J0 + R.kpanels * NBO;
+      if ((R.policy == 2 && last) || (R.policy == 3 && !last)) return;
+      if (!(R.policy == 1 && last)) {
+         c0 = J1 + R.clo * NBO;
+         if (R.chi >= 0) c1 = min(f, J1 + R.chi * NBO);
+         if (R.clip_to_pivots) c1 = min(c1, k);
+      }
    }
    if (c0 >= c1 || r0 >= f || K <= 0) return;
    const int m0 = (r0 & ~1) + blockIdx.y * BM;
@@ -1207,6 +1214,8 @@ __global__ void __launch_bounds__(WARPS_M* WARPS_N * 32, MINB) k_update(FrontArr
    // column n of the trailing matrix: in the factor panel (n < k) or in the packed contribution block
    auto col_ptr = [&](const int n) -> double* { return (n < k) ? (A + static_cast<int64_t>(ld) * n) : (Cb + cb_col(rcb, n - k)); };
    const double* Wp = W.wpool + F.woff[s] + static_cast<int64_t>(ld) * kbeg;   // operand A: rows m, K columns
+   // second panel of a pair: its W panel lives in another buffer; k-tiles from NBO on read it
+   const int64_t w2delta = (R.kpanels == 2) ? ((R.wpool2 + F.woff[s] - static_cast<int64_t>(ld) * NBO) - Wp) : 0;
    const double* Lp = A + static_cast<int64_t>(ld) * (J0 + kbeg);               // operand B: rows n, K columns
 
    const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
@@ -1242,7 +1251,7 @@ __global__ void __launch_bounds__(WARPS_M* WARPS_N * 32, MINB) k_update(FrontArr
 #pragma unroll
       for (int c = 0; c < A_CHUNKS; ++c) {
          const bool pred = kbase + a_kk[c] < K;
-         cp_async16(base + a_dst[c], pred ? (a_src[c] + kstride * kt) : Wp, pred);
+         cp_async16(base + a_dst[c], pred ? (a_src[c] + kstride * kt + ((kbase >= NBO) ? w2delta : 0)) : Wp, pred);
       }
 #pragma unroll
       for (int c = 0; c < B_CHUNKS; ++c) {
@@ -2294,35 +2303,36 @@ int init_kernel_attributes() {
 }
 
 int launch_update(const FrontArrays& F, const int* d_list, int nfronts, int max_f, int mode, int j0, int J0, const FactorArrays& W,
-                  int tile_mode, cudaStream_t st) {
+                  int tile_mode, cudaStream_t st, const UpdateRange& R) {
    if (nfronts <= 0) return 0;
    // region extent upper bounds (per-front extents are resolved inside the kernel)
    const int r0 = (mode == 0) ? j0 + 1 : J0 + 1;   // smallest possible region start (a front with k = r0)
    const int rows = max_f - (r0 & ~1);
    if (rows <= 0) return 0;
-   const int cols = (mode == 0) ? NBO : ((mode == 2) ? std::min(rows, NBO + 2) : ((mode == 3) ? rows - NBO : rows));
+   // columns: a later part starts clo panels in; the first part may have to cover a whole trailing matrix (last-panel fronts)
+   const int cols = (mode == 0) ? NBO : ((R.policy == 1 || R.chi < 0) ? rows - R.clo * NBO : std::min(rows - R.clo * NBO, (R.chi - R.clo) * NBO + 2));
    if (cols <= 0) return 0;
    if (tile_mode == 6) {
       dim3 grid(nfronts, (rows + 127) / 128, (cols + 63) / 64);
-      k_update<128, 64, 4, 2, 32, 2, 2><<<grid, 256, smem_bytes(128, 64, 32, 2), st>>>(F, d_list, mode, j0, J0, W);
+      k_update<128, 64, 4, 2, 32, 2, 2><<<grid, 256, smem_bytes(128, 64, 32, 2), st>>>(F, d_list, mode, j0, J0, W, R);
    } else if (tile_mode == 4) {
       dim3 grid(nfronts, (rows + 127) / 128, (cols + 63) / 64);
-      k_update<128, 64, 4, 2, 16, 2><<<grid, 256, smem_bytes(128, 64, 16), st>>>(F, d_list, mode, j0, J0, W);
+      k_update<128, 64, 4, 2, 16, 2><<<grid, 256, smem_bytes(128, 64, 16), st>>>(F, d_list, mode, j0, J0, W, R);
    } else if (tile_mode == 5) {
       dim3 grid(nfronts, (rows + 127) / 128, (cols + 127) / 128);
-      k_update<128, 128, 4, 4, 32, 1><<<grid, 512, smem_bytes(128, 128, 32), st>>>(F, d_list, mode, j0, J0, W);
-   } else if (tile_mode == 3 && mode == 1) {
+      k_update<128, 128, 4, 4, 32, 1><<<grid, 512, smem_bytes(128, 128, 32), st>>>(F, d_list, mode, j0, J0, W, R);
+   } else if (tile_mode == 3 && mode == 1 && R.kpanels == 1 && R.clo == 0 && R.chi < 0) {
       k_update_ws<<<296, WS_THREADS, WS_SMEM, st>>>(F, d_list, nfronts, J0, W);
-   } else if (tile_mode == 2) {
+   } else if (tile_mode == 2 || tile_mode == 3) {
       // two co-resident CTAs per SM: the read-modify-write epilogue of one tile overlaps the K loop of the other
       dim3 grid(nfronts, (rows + 127) / 128, (cols + 63) / 64);
-      k_update<128, 64, 2, 2, 16, 2><<<grid, 128, smem_bytes(128, 64, 16), st>>>(F, d_list, mode, j0, J0, W);
+      k_update<128, 64, 2, 2, 16, 2><<<grid, 128, smem_bytes(128, 64, 16), st>>>(F, d_list, mode, j0, J0, W, R);
    } else if (tile_mode == 1) {
       dim3 grid(nfronts, (rows + 127) / 128, (cols + 127) / 128);
-      k_update<128, 128, 2, 4, 32><<<grid, 256, smem_bytes(128, 128, 32), st>>>(F, d_list, mode, j0, J0, W);
+      k_update<128, 128, 2, 4, 32><<<grid, 256, smem_bytes(128, 128, 32), st>>>(F, d_list, mode, j0, J0, W, R);
    } else {
       dim3 grid(nfronts, (rows + 63) / 64, (cols + 63) / 64);
-      k_update<64, 64, 2, 2, 16><<<grid, 128, smem_bytes(64, 64, 16), st>>>(F, d_list, mode, j0, J0, W);
+      k_update<64, 64, 2, 2, 16><<<grid, 128, smem_bytes(64, 64, 16), st>>>(F, d_list, mode, j0, J0, W, R);
    }
    return 1;
 }

@@ -79,10 +79,22 @@ int launch_trsmpanel(const FrontArrays& F, const int* d_list, int nfronts, int m
 // rows of the L columns left of each inner block follow the block's interchanges (all blocks at once)
 int launch_permute_rows(const FrontArrays& F, const int* d_list, int nfronts, int max_k, const FactorArrays& W, cudaStream_t st);
 // K4 Schur-complement update C -= W * L^T with FP64 tensor-core MMA.
-// mode 0: inside the outer panel (after inner block j0); mode 1: trailing matrix after outer panel J0;
-// modes 2 / 3: the first NBO columns of the trailing matrix / the rest of it (look-ahead split of mode 1).
-int launch_update(const FrontArrays& F, const int* d_list, int nfronts, int max_f, int mode, int j0, int J0,
-                  const FactorArrays& W, int tile_mode, cudaStream_t st);   // tile_mode 0: 64x64, 1: 128x128, 2: 128x64 with two CTAs per SM
+// mode 0: inside the outer panel (after inner block j0); mode 1: trailing matrix behind the K range that starts at outer panel J0.
+// The K range is one outer panel or two taken together (the second one's W panel in another buffer: wpool2); the columns of the
+// trailing matrix can be restricted to [clo, chi) outer panels behind the K range (chi < 0: to the end) - look-ahead splits.
+// policy decides what happens to fronts whose last panel lies in the K range ("last" fronts): 0 = the column range applies
+// to every front alike, 1 = last fronts get their whole trailing matrix, 2 = last fronts are skipped, 3 = only last fronts.
+struct UpdateRange {
+   int kpanels = 1;
+   int clo = 0, chi = -1;
+   const double* wpool2 = nullptr;
+   int policy = 0;
+   int clip_to_pivots = 0;   // 1: the column range ends at the front's last pivot column (only factor-panel columns)
+};
+int launch_update(const FrontArrays& F, const int* d_list, int nfronts, int max_f, int mode, int j0, int J0, const FactorArrays& W,
+                  int tile_mode, cudaStream_t st, const UpdateRange& R = UpdateRange());
+// tile_mode 0: 64x64 (4 warps), 1: 128x128 (8 warps), 2: 128x64 (4 warps, two CTAs per SM), 3: warp-specialised persistent,
+// 4: 128x64 (8 warps, two CTAs per SM), 5: 128x128 (16 warps), 6: 128x64 (8 warps), K tiles of 32 double-buffered
 int init_kernel_attributes();
 // phase cycle counters of the panel kernels (only when built with -DB200KKT_PHASES); returns 0 when not compiled in
 int debug_phase_cycles(unsigned long long* out16, bool reset);

@@ -218,7 +218,7 @@ void upload_plan(b200kkt_handle* h) {
    h->W.lpool = dev_alloc<double>(h, static_cast<size_t>(P.pool_size));
    h->W.cbpool = dev_alloc<double>(h, static_cast<size_t>(P.cb_pool_size));
    h->wpool_size = (wpool_size + 1) & ~int64_t(1);
-   h->W.wpool = dev_alloc<double>(h, static_cast<size_t>(2 * h->wpool_size));
+   h->W.wpool = dev_alloc<double>(h, static_cast<size_t>(4 * h->wpool_size));
    h->W.xinv = dev_alloc<double>(h, static_cast<size_t>(std::max<int64_t>(xinv_size, 1)));
    h->xinv_size = xinv_size;
    h->W.dd = dev_alloc<double>(h, n + 1);
@@ -239,7 +239,7 @@ void upload_plan(b200kkt_handle* h) {
    h->d_counters = dev_alloc<int>(h, 8);
    h->d_norms = dev_alloc<unsigned long long>(h, 4);
    h->d_scale_final = h->d_scale;
-   CK(cudaMemsetAsync(h->W.wpool, 0, static_cast<size_t>(std::max<int64_t>(2 * h->wpool_size, 1)) * sizeof(double), h->stream));
+   CK(cudaMemsetAsync(h->W.wpool, 0, static_cast<size_t>(std::max<int64_t>(4 * h->wpool_size, 1)) * sizeof(double), h->stream));
    CK(cudaStreamSynchronize(h->stream));
    h->stats.t_upload = std::chrono::duration<double>(std::chrono::steady_clock::now() - t0).count();
 }
@@ -305,47 +305,96 @@ void enqueue_factor(b200kkt_handle* h) {
          const int lane = (bi - h->level_batch_ptr[l]) % (nside + 1);
          cudaStream_t st = (lane == 0) ? h->stream : h->aux[lane - 1];
          if ((b.has_cb || b.has_children) && !(h->debug_skip & 4)) L += launch_prepare(h->F, list, b.count, b.max_f, h->W, st);
-         // W panels are double-buffered: panel p of a front lives in buffer p & 1
-         FactorArrays Wbuf[2] = {h->W, h->W};
-         Wbuf[1].wpool += h->wpool_size;
+         // W panels: panel p of a front lives in buffer p & 3 (two panels of a pair + the pair factored ahead)
+         FactorArrays Wbuf[4] = {h->W, h->W, h->W, h->W};
+         for (int t = 1; t < 4; ++t) Wbuf[t].wpool += t * h->wpool_size;
          const bool ahead = h->lookahead != 0 && !prof && b.max_k > NBO && b.max_f >= 2048;
          cudaStream_t pst = h->panel_stream[lane];
-         int p = 0;
-         for (int J0 = 0; J0 < b.max_k; J0 += NBO, ++p) {
-            const int nfP = b.count_k_greater(J0);
-            const FactorArrays& Wp = Wbuf[p & 1];
-            if ((!ahead || J0 == 0) && !(h->debug_skip & 2)) {
-               if (!(h->debug_skip & 16)) L += launch_diagpanel(h->F, list, nfP, b.max_k, J0, Wp, h->null_pivot_tol, st);
-               if (!(h->debug_skip & 8)) L += launch_trsmpanel(h->F, list, nfP, b.pmaxf[nfP - 1], b.max_k, J0, Wp, st);
+         const bool prof_this = prof && b.max_f >= 1024;
+         auto trailing_flops = [&](int Jbeg, int kpanels, int nf) {
+            double fl = 0.0;
+            for (int t = 0; t < nf; ++t) {
+               const int s_id = h->batch_fronts_host[b.begin + t];
+               if (kpanels == 2 && P.k[s_id] <= Jbeg + NBO) continue;
+               const double J1 = std::min(Jbeg + kpanels * NBO, P.k[s_id]), rem = P.f[s_id] - J1;
+               if (rem > 0) fl += 2.0 * (J1 - Jbeg) * rem * (rem + 1.0) * 0.5;
             }
-            const bool prof_this = prof && b.max_f >= 1024;
-            if (prof_this) {
-               double fl = 0.0;
-               for (int t = 0; t < nfP; ++t) {
-                  const int s_id = h->batch_fronts_host[b.begin + t];
-                  const double J1 = std::min(J0 + NBO, P.k[s_id]), rem = P.f[s_id] - J1;
-                  if (rem > 0) fl += 2.0 * (J1 - J0) * rem * (rem + 1.0) * 0.5;
+            return fl;
+         };
+         auto panel = [&](int J0, int nf, const FactorArrays& Wp, cudaStream_t s_) {
+            if (h->debug_skip & 2) return;
+            if (!(h->debug_skip & 16)) L += launch_diagpanel(h->F, list, nf, b.max_k, J0, Wp, h->null_pivot_tol, s_);
+            if (!(h->debug_skip & 8)) L += launch_trsmpanel(h->F, list, nf, b.pmaxf[nf - 1], b.max_k, J0, Wp, s_);
+         };
+         auto update = [&](int J0, int nf, const FactorArrays& Wp, cudaStream_t s_, const UpdateRange& R) {
+            if (h->debug_skip & 1) return;
+            L += launch_update(h->F, list, nf, b.pmaxf[nf - 1], 1, 0, J0, Wp, b.big_tiles, s_, R);
+         };
+         if (h->pair_panels != 0 && b.max_k > NBO && b.max_f >= h->pair_min_front) {
+            // Outer panels are taken in pairs: panel p0, the update of panel p1's columns (K = 256, narrow), panel p1, then ONE
+            // trailing update with K <= 512 - half the read-modify-write traffic and half the per-tile fill/epilogue overhead of
+            // two K = 256 updates.  With look-ahead the next pair's chain runs on the panel stream under the bulk of that update.
+            auto chain = [&](int q, cudaStream_t s_) {
+               const int p0 = 2 * q, J0 = p0 * NBO, J0b = J0 + NBO;
+               const int nf0 = b.count_k_greater(J0);
+               panel(J0, nf0, Wbuf[p0 & 3], s_);
+               if (J0b < b.max_k) {
+                  update(J0, nf0, Wbuf[p0 & 3], s_, UpdateRange{1, 0, 1, nullptr, 0, 1});   // panel p1's pivot columns only
+                  panel(J0b, b.count_k_greater(J0b), Wbuf[(p0 + 1) & 3], s_);
                }
-               prof_begin(fl, 0);
-            }
-            if (ahead && J0 + NBO < b.max_k) {
-               // look-ahead: update the next panel's columns, factor that panel on the panel stream while the rest of
-               // the trailing matrix is updated here
-               const int nfN = b.count_k_greater(J0 + NBO);
-               if (!(h->debug_skip & 1)) L += launch_update(h->F, list, nfP, b.pmaxf[nfP - 1], 2, 0, J0, Wp, b.big_tiles, st);
-               CK(cudaEventRecord(h->ev_next_cols[lane], st));
-               CK(cudaStreamWaitEvent(pst, h->ev_next_cols[lane], 0));
-               if (!(h->debug_skip & 2)) {
-                  if (!(h->debug_skip & 16)) L += launch_diagpanel(h->F, list, nfN, b.max_k, J0 + NBO, Wbuf[(p + 1) & 1], h->null_pivot_tol, pst);
-                  if (!(h->debug_skip & 8)) L += launch_trsmpanel(h->F, list, nfN, b.pmaxf[nfN - 1], b.max_k, J0 + NBO, Wbuf[(p + 1) & 1], pst);
+            };
+            chain(0, st);
+            for (int q = 0; 2 * q * NBO < b.max_k; ++q) {
+               const int p0 = 2 * q, J0 = p0 * NBO, J0b = J0 + NBO;
+               const int nf0 = b.count_k_greater(J0);
+               if (J0b >= b.max_k) {
+                  // single last panel
+                  if (prof_this) prof_begin(trailing_flops(J0, 1, nf0), 0);
+                  update(J0, nf0, Wbuf[p0 & 3], st, UpdateRange{1, 0, -1, nullptr, 0});
+                  if (prof_this) prof_end();
+                  break;
                }
-               CK(cudaEventRecord(h->ev_panel[lane], pst));
-               if (!(h->debug_skip & 1)) L += launch_update(h->F, list, nfP, b.pmaxf[nfP - 1], 3, 0, J0, Wp, b.big_tiles, st);
-               CK(cudaStreamWaitEvent(st, h->ev_panel[lane], 0));
-            } else if (!(h->debug_skip & 1)) {
-               L += launch_update(h->F, list, nfP, b.pmaxf[nfP - 1], 1, 0, J0, Wp, b.big_tiles, st);
+               const int nf1 = b.count_k_greater(J0b);
+               // fronts whose last panel was p0: their whole trailing matrix (the chain only touched pivot columns)
+               if (nf0 > nf1) update(J0, nf0, Wbuf[p0 & 3], st, UpdateRange{1, 0, -1, nullptr, 3});
+               const double* w2 = Wbuf[(p0 + 1) & 3].wpool;
+               if (ahead && J0 + 2 * NBO < b.max_k) {
+                  update(J0, nf1, Wbuf[p0 & 3], st, UpdateRange{2, 0, 2, w2, 1});
+                  CK(cudaEventRecord(h->ev_next_cols[lane], st));
+                  CK(cudaStreamWaitEvent(pst, h->ev_next_cols[lane], 0));
+                  chain(q + 1, pst);
+                  CK(cudaEventRecord(h->ev_panel[lane], pst));
+                  update(J0, nf1, Wbuf[p0 & 3], st, UpdateRange{2, 2, -1, w2, 2});
+                  CK(cudaStreamWaitEvent(st, h->ev_panel[lane], 0));
+               } else {
+                  if (prof_this) prof_begin(trailing_flops(J0, 2, nf1), 0);
+                  update(J0, nf1, Wbuf[p0 & 3], st, UpdateRange{2, 0, -1, w2, 0});
+                  if (prof_this) prof_end();
+                  if (J0 + 2 * NBO < b.max_k) chain(q + 1, st);
+               }
             }
-            if (prof_this) prof_end();
+         } else {
+            int p = 0;
+            for (int J0 = 0; J0 < b.max_k; J0 += NBO, ++p) {
+               const int nfP = b.count_k_greater(J0);
+               const FactorArrays& Wp = Wbuf[p & 1];
+               if (!ahead || J0 == 0) panel(J0, nfP, Wp, st);
+               if (prof_this) prof_begin(trailing_flops(J0, 1, nfP), 0);
+               if (ahead && J0 + NBO < b.max_k) {
+                  // look-ahead: update the next panel's columns, factor that panel on the panel stream while the rest of
+                  // the trailing matrix is updated here
+                  update(J0, nfP, Wp, st, UpdateRange{1, 0, 1, nullptr, 0});
+                  CK(cudaEventRecord(h->ev_next_cols[lane], st));
+                  CK(cudaStreamWaitEvent(pst, h->ev_next_cols[lane], 0));
+                  panel(J0 + NBO, b.count_k_greater(J0 + NBO), Wbuf[(p + 1) & 1], pst);
+                  CK(cudaEventRecord(h->ev_panel[lane], pst));
+                  update(J0, nfP, Wp, st, UpdateRange{1, 1, -1, nullptr, 0});
+                  CK(cudaStreamWaitEvent(st, h->ev_panel[lane], 0));
+               } else {
+                  update(J0, nfP, Wp, st, UpdateRange{1, 0, -1, nullptr, 0});
+               }
+               if (prof_this) prof_end();
+            }
          }
          L += launch_permute_rows(h->F, list, b.count_k_greater(NBO), b.max_k, h->W, st);
       }
@@ -667,6 +716,8 @@ int b200kkt_set_option(b200kkt_handle* h, const char* name, double value) {
    else if (n == "multi_stream") h->multi_stream = static_cast<int>(value);
    else if (n == "update_tile_mode") h->update_tile_mode = static_cast<int>(value);
    else if (n == "lookahead") h->lookahead = static_cast<int>(value);
+   else if (n == "pair_panels") h->pair_panels = static_cast<int>(value);
+   else if (n == "pair_min_front") h->pair_min_front = static_cast<int>(value);
    else if (n == "debug_skip") h->debug_skip = static_cast<int>(value);   // timing experiments only: 1 no K4, 2 no panel kernels, 4 no K5
    else return fail(h, B200KKT_EINVAL, "unknown option: " + n);
    // numeric options are baked into the captured graphs

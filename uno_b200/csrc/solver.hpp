@@ -72,13 +72,15 @@ struct b200kkt_handle {
    cudaStream_t panel_stream[NUM_AUX + 1] = {nullptr, nullptr, nullptr, nullptr};
    cudaEvent_t ev_next_cols[NUM_AUX + 1] = {nullptr, nullptr, nullptr, nullptr}, ev_panel[NUM_AUX + 1] = {nullptr, nullptr, nullptr, nullptr};
    int lookahead = 1;
+   int pair_panels = 1;      // trailing updates of very big fronts take two outer panels at once (K <= 512): +3 % on 128^3, -3 % on 64^3
+   int pair_min_front = 16384;
    int debug_skip = 0;
    cudaGraphExec_t solve_graph = nullptr;   // one solve sweep, captured on first use
    double* solve_graph_x = nullptr;
    const double* solve_graph_scale = nullptr;
    int64_t solve_graph_launches = 0;
    int64_t xinv_size = 0;    // doubles of inverted diagonal blocks
-   int64_t wpool_size = 0;   // doubles per W-panel buffer (two buffers: panel p uses buffer p & 1)
+   int64_t wpool_size = 0;   // doubles per W-panel buffer (four buffers: panel p uses buffer p & 3)
    int multi_stream = 1;
    int update_tile_mode = 4;   // K4 variant for fronts wider than 256: 1 = 128x128 tiles (8 warps), 2 = 128x64 (4 warps, two CTAs per SM), 3 = warp-specialised persistent, 4 = 128x64 (8 warps, two CTAs per SM), 5 = 128x128 (16 warps)
    cudaEvent_t ev0 = nullptr, ev1 = nullptr;
