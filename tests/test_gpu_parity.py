@@ -255,3 +255,33 @@ def test_full_size_properties(make, name):
     assert np.max(np.abs(x12 - (x1 + 2.0 * x2))) <= X_TOL * np.max(np.abs(x12))
     s.do_numerical_factorization(kkt.val)
     assert np.array_equal(x1, s.solve_indefinite_system(kkt.rhs))
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize("options", [
+    {"lookahead": 0, "multi_stream": 0, "pair_panels": 0, "use_graph": 0},       # plain level-by-level, one stream
+    {"lookahead": 1, "pair_panels": 0},                                           # look-ahead by single panels
+    {"lookahead": 1, "pair_panels": 1, "pair_min_front": 512},                    # two outer panels per trailing update
+    {"lookahead": 0, "pair_panels": 1, "pair_min_front": 512},
+    {"update_tile_mode": 1}, {"update_tile_mode": 2}, {"update_tile_mode": 3}, {"update_tile_mode": 6},
+])
+def test_schedule_and_kernel_variants_agree(options):
+    """Streams, look-ahead, panel pairing and the K4 tile variants only reorder independent work (and, for pairing, the
+    summation order of the trailing update): same pivots, same inertia, same solution to rounding."""
+    kkt = G.ocp_distributed(26, 3, seed=3)         # fronts up to ~2000 rows, several outer panels per top front
+    ref = gpu_solver(kkt)
+    ref.do_numerical_factorization(kkt.val)
+    xr, berr_r = ref.solve_indefinite_system(kkt.rhs, return_backward_error=True)
+    s = gpu_solver(kkt)
+    for name, value in options.items():
+        s.set_option(name, value)
+    s.do_numerical_factorization(kkt.val)
+    x, berr = s.solve_indefinite_system(kkt.rhs, return_backward_error=True)
+    assert s.get_inertia() == ref.get_inertia() == (kkt.n, kkt.m, 0)
+    assert berr <= BERR_TOL and berr_r <= BERR_TOL
+    if "pair_min_front" not in options and "update_tile_mode" not in options:
+        # pure re-scheduling: every entry of the factor sees the same operations in the same order
+        a, b = ref.debug_factor(), s.debug_factor()
+        assert all(np.array_equal(u, w) for u, w in zip(a, b))
+        assert np.array_equal(x, xr)
+    assert np.max(np.abs(x - xr)) <= X_TOL * np.max(np.abs(xr))
