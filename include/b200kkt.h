@@ -55,6 +55,11 @@ typedef struct b200kkt_stats {
    double t_update_profiled, flops_update_profiled;
    int64_t n_update_profiled;
    double t_assemble_profiled;   /* K1 (memset excluded) under the same option */
+   /* subtree partition (num_gpus > 1): this rank's share, the estimated critical path, and the bytes this rank sends and
+    * receives over NVLink per factorization / per solve sweep */
+   int64_t num_parts, part_rank, num_cut_fronts;
+   double flops_own, flops_critical;
+   int64_t comm_bytes_factor, comm_bytes_sweep;
 } b200kkt_stats;
 
 /* Handle life cycle.  Replaces JOB=-1 / JOB=-2 (MUMPSSolver.cpp:16-49).
@@ -62,6 +67,21 @@ typedef struct b200kkt_stats {
  * getters work, every numeric call fails with B200KKT_ECUDA) — there is no CPU numeric path. */
 int b200kkt_create(b200kkt_handle** h, int device, int num_gpus);
 int b200kkt_destroy(b200kkt_handle* h);
+
+/* Multi-GPU (num_gpus = 2, 4, 8 in b200kkt_create): one process per GPU, every process creates a handle with the same
+ * num_gpus and runs the same call sequence on the same matrix (SPMD, as the reference's MUMPS does over MPI ranks:
+ * MUMPSSolver.cpp:20 "comm_fortran = USE_COMM_WORLD").  Independent elimination subtrees are mapped to the ranks, the
+ * contribution blocks of the cut fronts travel over NVLink (NCCL send/recv), inertia and solution are summed over ranks, so
+ * every rank returns the same inertia and the same x.  Rank 0 calls b200kkt_comm_unique_id, the host program hands the 128
+ * bytes to the other ranks by whatever means it has (MPI_Bcast, torch.distributed, a file), every rank calls
+ * b200kkt_comm_init before b200kkt_analyse.  libnccl.so.2 is opened at run time by these two calls only. */
+int b200kkt_comm_unique_id(char id[128]);
+int b200kkt_comm_init(b200kkt_handle* h, int rank, int world, const char id[128]);
+/* The subtree map of the last analysis: owner[s] per front (length = number of fronts), the cut fronts (owner differs from
+ * the parent's; at most number of fronts entries, *num_cut receives the count), factor flops per rank (length num_gpus).
+ * Works on host-only handles; any pointer may be NULL. */
+int b200kkt_plan_partition(const b200kkt_handle* h, int32_t* owner, int64_t* num_cut, int32_t* cut_fronts, double* part_flops,
+                           double* critical_flops);
 
 /* Options (defaults need no user action).  Names: "ordering" (0 METIS, 1 natural),
  * "kkt_pairing", "relax_small", "relax_mid", "relax_big", "scaling_sweeps", "null_pivot_tol",

@@ -100,20 +100,18 @@ def bk_block(B, n, tol):
 
 
 class EmulatedFactorization:
-    def __init__(self, plan, perm, scatter, kkt, values, sweeps=3, null_tol=1e-14):
+    def __init__(self, plan, perm, scatter, kkt, values, sweeps=3, null_tol=1e-14, defer=False):
         self.plan = plan
         self.perm = np.asarray(perm)
         self.n = kkt.dim
+        self.null_tol = null_tol
         self.scale = equilibrate(kkt, values, sweeps)
-        k, f, ld, off = plan["k"], plan["f"], plan["ld"], plan["pool_offset"]
         nsn = plan["num_fronts"]
         pool = np.zeros(plan["pool_doubles"])
         r = kkt.row.astype(np.int64)
         c = kkt.col.astype(np.int64)
         np.add.at(pool, scatter, values * self.scale[r] * self.scale[c])
         self.assembled = pool.copy()
-        rows_off, rows = plan["rows_off"], plan["rows"]
-        first = plan["first_col"]
         self.dd = np.ones(self.n)
         self.de = np.zeros(self.n)
         self.ptype = np.zeros(self.n, dtype=np.int32)
@@ -125,20 +123,36 @@ class EmulatedFactorization:
                 children[plan["parent"][s]].append(s)
         self.children = children
         self.relmap = [None] * nsn
-        for s in range(nsn):
+        if not defer:
+            for s in range(nsn):
+                self.factor_front(s)
+
+    def child_map(self, ch):
+        """Local index in the parent front of every boundary row of front ch (the extend-add map)."""
+        plan = self.plan
+        k, rows_off, rows, first = plan["k"], plan["rows_off"], plan["rows"], plan["first_col"]
+        s = int(plan["parent"][ch])
+        ks, kc = int(k[s]), int(k[ch])
+        crow = rows[rows_off[ch] + kc : rows_off[ch + 1]]
+        prow = rows[rows_off[s] : rows_off[s + 1]]
+        loc = np.searchsorted(prow[ks:], crow) + ks
+        inpiv = crow < first[s] + ks
+        loc = np.where(inpiv, crow - first[s], loc)
+        assert np.all(prow[loc] == crow)
+        return loc
+
+    def factor_front(self, s):
+        """Assemble front s (its children's contribution blocks must be in self.fronts) and factor its pivot columns."""
+        plan, pool, null_tol = self.plan, self.assembled, self.null_tol
+        k, f, ld, off, first = plan["k"], plan["f"], plan["ld"], plan["pool_offset"], plan["first_col"]
+        if True:
             fs, ks = int(f[s]), int(k[s])
             F = np.zeros((fs, fs))
             F[:, :ks] = pool[off[s] : off[s] + ld[s] * ks].reshape(ks, ld[s]).T[:fs, :]   # ld x k column-major factor panel
             F = np.tril(F) + np.tril(F, -1).T
-            for ch in children[s]:
+            for ch in self.children[s]:
                 Fc = self.fronts[ch]
-                kc = int(k[ch])
-                crow = rows[rows_off[ch] + kc : rows_off[ch + 1]]
-                prow = rows[rows_off[s] : rows_off[s + 1]]
-                loc = np.searchsorted(prow[ks:], crow) + ks
-                inpiv = crow < first[s] + ks
-                loc = np.where(inpiv, crow - first[s], loc)
-                assert np.all(prow[loc] == crow)
+                loc = self.child_map(ch)
                 self.relmap[ch] = loc
                 F[np.ix_(loc, loc)] += Fc["cb"]
             # blocked restricted Bunch-Kaufman on the first ks columns
@@ -187,50 +201,160 @@ class EmulatedFactorization:
                 q += 1
         return pos, neg, zero
 
-    def solve(self, b):
+    def forward_front(self, s, zg, z2, cvec):
+        plan = self.plan
+        k, first = plan["k"], plan["first_col"]
+        ks = int(k[s])
+        L = self.fronts[s]["L"]
+        v = np.zeros(L.shape[0])
+        v[:ks] = zg[first[s] : first[s] + ks]
+        for ch in self.children[s]:
+            v[self.child_map(ch)] += cvec[ch]
+        y = v[:ks][self.lperm[first[s] : first[s] + ks]]
+        L11 = np.tril(L[:ks, :], -1) + np.eye(ks)
+        y = np.linalg.solve(L11, y)
+        cvec[s] = v[ks:] - L[ks:, :] @ y
+        z2[first[s] : first[s] + ks] = y
+
+    def backward_front(self, s, z2, xg):
         plan = self.plan
         k, first = plan["k"], plan["first_col"]
         rows_off, rows = plan["rows_off"], plan["rows"]
-        nsn = plan["num_fronts"]
+        ks = int(k[s])
+        L = self.fronts[s]["L"]
+        y = z2[first[s] : first[s] + ks].copy()
+        q0 = first[s]
+        j = 0
+        while j < ks:
+            t = self.ptype[q0 + j]
+            if t == 0:
+                y[j] /= self.dd[q0 + j]; j += 1
+            elif t == 1:
+                a, bb, c = self.dd[q0 + j], self.de[q0 + j], self.dd[q0 + j + 1]
+                det = a * c - bb * bb
+                y1, y2 = y[j], y[j + 1]
+                y[j], y[j + 1] = (c * y1 - bb * y2) / det, (a * y2 - bb * y1) / det
+                j += 2
+            else:
+                y[j] = 0.0; j += 1
+        xb = xg[rows[rows_off[s] + ks : rows_off[s + 1]]]
+        y -= L[ks:, :].T @ xb
+        L11 = np.tril(L[:ks, :], -1) + np.eye(ks)
+        y = np.linalg.solve(L11.T, y)
+        xg[first[s] + self.lperm[first[s] : first[s] + ks]] = y
+
+    def solve(self, b):
+        nsn = self.plan["num_fronts"]
         zg = (self.scale * b)[self.perm]
         z2 = np.zeros(self.n)
         cvec = [None] * nsn
         for s in range(nsn):
-            ks = int(k[s])
-            L = self.fronts[s]["L"]
-            v = np.zeros(L.shape[0])
-            v[:ks] = zg[first[s] : first[s] + ks]
-            for ch in self.children[s]:
-                v[self.relmap[ch]] += cvec[ch]
-            y = v[:ks][self.lperm[first[s] : first[s] + ks]]
-            L11 = np.tril(L[:ks, :], -1) + np.eye(ks)
-            y = np.linalg.solve(L11, y)
-            cvec[s] = v[ks:] - L[ks:, :] @ y
-            z2[first[s] : first[s] + ks] = y
+            self.forward_front(s, zg, z2, cvec)
         xg = np.zeros(self.n)
         for s in range(nsn - 1, -1, -1):
-            ks = int(k[s])
-            L = self.fronts[s]["L"]
-            y = z2[first[s] : first[s] + ks].copy()
-            q0 = first[s]
-            j = 0
-            while j < ks:
-                t = self.ptype[q0 + j]
-                if t == 0:
-                    y[j] /= self.dd[q0 + j]; j += 1
-                elif t == 1:
-                    a, bb, c = self.dd[q0 + j], self.de[q0 + j], self.dd[q0 + j + 1]
-                    det = a * c - bb * bb
-                    y1, y2 = y[j], y[j + 1]
-                    y[j], y[j + 1] = (c * y1 - bb * y2) / det, (a * y2 - bb * y1) / det
-                    j += 2
-                else:
-                    y[j] = 0.0; j += 1
-            xb = xg[rows[rows_off[s] + ks : rows_off[s + 1]]]
-            y -= L[ks:, :].T @ xb
-            L11 = np.tril(L[:ks, :], -1) + np.eye(ks)
-            y = np.linalg.solve(L11.T, y)
-            xg[first[s] + self.lperm[first[s] : first[s] + ks]] = y
+            self.backward_front(s, z2, xg)
+        x = np.zeros(self.n)
+        x[self.perm] = xg
+        return x * self.scale
+
+
+class PartitionedEmulation(EmulatedFactorization):
+    """The same numeric phase run the way the library runs it on several GPUs (solver.cpp: enqueue_factor / run_solve with
+    a subtree partition): every rank walks the tree levels in ascending order over ITS fronts, the cut fronts of a level hand
+    their contribution block (factorization) or boundary partial sums (forward solve) to the parent's rank, the backward sweep
+    ships the boundary solution the other way, the solution is put together by a sum over ranks of the owned entries.
+    `transport.exchange(sends, recvs)` moves arrays between ranks (sends: [(peer, array)], recvs: [(peer, shape)] -> arrays),
+    `transport.allreduce_sum(array)` sums over ranks."""
+
+    def __init__(self, plan, part, rank, transport, perm, scatter, kkt, values, **kw):
+        super().__init__(plan, perm, scatter, kkt, values, defer=True, **kw)
+        self.rank, self.transport = rank, transport
+        self.owner = np.asarray(part["owner"])
+        nlev = plan["num_levels"]
+        self.level_fronts = [np.flatnonzero(plan["level"] == l) for l in range(nlev)]
+        self.cut_at = [[] for _ in range(nlev)]      # cut fronts touching this rank, per level, ascending front index
+        for s in part["cut_fronts"]:
+            s = int(s)
+            if rank in (int(self.owner[s]), int(self.owner[plan["parent"][s]])):
+                self.cut_at[int(plan["level"][s])].append(s)
+        self.dd[:] = 0.0
+        self.ptype[:] = -1                           # other ranks' pivots: skipped by the inertia count
+        for l in range(nlev):
+            for s in self.level_fronts[l]:
+                if self.owner[s] == rank:
+                    self.factor_front(int(s))
+            self._transfer(l, lambda s: self.fronts[s]["cb"], self._store_cb, up=True)
+
+    def _r(self, s):
+        return int(self.plan["f"][s] - self.plan["k"][s])
+
+    def _store_cb(self, s, a):
+        self.fronts[s] = {"L": None, "cb": a}
+
+    def _transfer(self, l, payload, store, up):
+        sends, recvs, targets = [], [], []
+        for s in self.cut_at[l]:
+            mine = self.owner[s] == self.rank
+            peer = int(self.owner[self.plan["parent"][s]] if mine else self.owner[s])
+            if mine == up:
+                sends.append((peer, np.ascontiguousarray(payload(s))))
+            else:
+                recvs.append((peer, s))
+                targets.append(s)
+        got = self.transport.exchange(sends, [(peer, self._shape(s)) for peer, s in recvs])
+        for s, a in zip(targets, got):
+            store(s, a)
+
+    _mode = "cb"
+
+    def _shape(self, s):
+        r = self._r(s)
+        return (r, r) if self._mode == "cb" else (r,)
+
+    def inertia(self):
+        pos = neg = zero = 0
+        for q in range(self.n):
+            t = self.ptype[q]
+            if t == 0:
+                if self.dd[q] > 0: pos += 1
+                else: neg += 1
+            elif t == 1:
+                a, b, c = self.dd[q], self.de[q], self.dd[q + 1]
+                det = a * c - b * b
+                if det < 0: pos += 1; neg += 1
+                elif a > 0: pos += 2
+                else: neg += 2
+            elif t == 3:
+                zero += 1
+        tot = self.transport.allreduce_sum(np.array([pos, neg, zero], dtype=np.float64))
+        return tuple(int(v) for v in tot)
+
+    def solve(self, b):
+        plan = self.plan
+        nsn, nlev = plan["num_fronts"], plan["num_levels"]
+        rows_off, rows, k = plan["rows_off"], plan["rows"], plan["k"]
+        zg = (self.scale * b)[self.perm]
+        z2 = np.zeros(self.n)
+        cvec = [None] * nsn
+        self._mode = "vec"
+        try:
+            for l in range(nlev):
+                for s in self.level_fronts[l]:
+                    if self.owner[s] == self.rank:
+                        self.forward_front(int(s), zg, z2, cvec)
+                self._transfer(l, lambda s: cvec[s], lambda s, a: cvec.__setitem__(s, a), up=True)
+            xg = np.zeros(self.n)
+            boundary = lambda s: rows[rows_off[s] + int(k[s]) : rows_off[s + 1]]   # noqa: E731
+            for l in range(nlev - 1, -1, -1):
+                self._transfer(l, lambda s: xg[boundary(s)], lambda s, a: xg.__setitem__(boundary(s), a), up=False)
+                for s in self.level_fronts[l]:
+                    if self.owner[s] == self.rank:
+                        self.backward_front(int(s), z2, xg)
+        finally:
+            self._mode = "cb"
+        col_owner = np.repeat(self.owner, np.diff(np.append(plan["first_col"], self.n)))
+        xg[col_owner != self.rank] = 0.0
+        xg = self.transport.allreduce_sum(xg)
         x = np.zeros(self.n)
         x[self.perm] = xg
         return x * self.scale

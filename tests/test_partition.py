@@ -1,0 +1,167 @@
+"""Subtree partition: the map computed by the symbolic phase, and the transfer protocol of the N > 1 path
+run by two gloo ranks on CPU through the numpy emulation of the numeric phase (the CUDA path itself: tests/gpu_partition.py
+under torchrun on the GPU box, and test_gpu_parity.py::test_partitioned_two_gpus where two devices are visible)."""
+import os
+import socket
+import sys
+from pathlib import Path
+
+import numpy as np
+import pytest
+import torch
+import torch.distributed as dist
+import torch.multiprocessing as mp
+
+ROOT = Path(__file__).resolve().parent.parent
+sys.path.insert(0, str(ROOT))
+sys.path.insert(0, str(ROOT / "tests"))
+
+
+def _systems():
+    from uno_b200 import generators as G
+    return {"ocp3d_12": G.ocp_distributed(12, 3, seed=0), "bnd3d_12": G.ocp_boundary_3d(12, seed=0), "ocp2d_48": G.ocp_distributed(48, 2, seed=0),
+            "opf_600": G.opf_like(600, 810, 120, seed=0, delta_w=100.0)}
+
+
+@pytest.mark.parametrize("parts", [1, 2, 4, 8])
+@pytest.mark.parametrize("name", ["ocp3d_12", "bnd3d_12", "ocp2d_48", "opf_600"])
+def test_subtree_map_invariants(lib, name, parts):
+    from uno_b200 import KKTSolver, partition
+    kkt = _systems()[name]
+    h = KKTSolver(device=-1, num_gpus=parts)
+    h.do_symbolic_analysis(kkt.dim, kkt.row, kkt.col, kkt.reg_size, kkt.n)
+    plan, part, st = h.plan(), h.partition(), h.stats()
+    owner, parent, level = part["owner"], plan["parent"], plan["level"]
+    nsn = plan["num_fronts"]
+    assert owner.shape == (nsn,) and owner.min() >= 0 and owner.max() < parts
+    assert np.all((parent < 0) | (parent > np.arange(nsn)))               # children are numbered before their parents
+    has_parent = parent >= 0
+    is_cut = np.zeros(nsn, dtype=bool)
+    is_cut[has_parent] = owner[has_parent] != owner[parent[has_parent]]
+    assert sorted(part["cut_fronts"].tolist()) == np.flatnonzero(is_cut).tolist()
+    keys = [(int(level[s]), int(s)) for s in part["cut_fronts"]]
+    assert keys == sorted(keys)                                           # the order every rank walks them in
+    assert st["num_cut_fronts"] == len(keys) and st["num_parts"] == parts
+    total = st["flops_factor"]
+    assert abs(part["part_flops"].sum() - total) <= 1e-9 * total
+    assert part["critical_flops"] <= total * (1 + 1e-12)
+    assert part["critical_flops"] >= part["part_flops"].max() * (1 - 1e-12) or parts == 1 or len(keys) > 0
+    if parts == 1:
+        assert len(keys) == 0 and part["critical_flops"] == pytest.approx(total)
+    # below a cut front everything belongs to one rank: independent subtrees, no exchange inside
+    sub_owner_ok = np.ones(nsn, dtype=bool)
+    for s in range(nsn):                                                  # children first
+        p = parent[s]
+        if p >= 0 and not is_cut[s] and owner[s] != owner[p]:
+            sub_owner_ok[s] = False
+    assert sub_owner_ok.all()
+    # every rank's send list is its peers' receive list, in the same order
+    sched = [partition.transfer_schedule(plan, part, r) for r in range(parts)]
+    for r in range(parts):
+        for q in range(parts):
+            a = [(l, s, n) for (l, s, peer, d, n, _) in sched[r] if peer == q and d == "send"]
+            b = [(l, s, n) for (l, s, peer, d, n, _) in sched[q] if peer == r and d == "recv"]
+            assert a == b
+    summ = partition.summarize(plan, part, total)
+    assert summ["cut_fronts"] == len(keys) and abs(sum(summ["flops_share_per_rank"]) - 1.0) < 1e-9
+    h.close()
+
+
+def test_map_is_deterministic(lib):
+    from uno_b200 import KKTSolver
+    kkt = _systems()["ocp3d_12"]
+    maps = []
+    for _ in range(2):
+        h = KKTSolver(device=-1, num_gpus=4)
+        h.do_symbolic_analysis(kkt.dim, kkt.row, kkt.col, kkt.reg_size, kkt.n)
+        maps.append(h.partition()["owner"].copy())
+        h.close()
+    assert np.array_equal(maps[0], maps[1])
+
+
+def test_multi_gpu_handle_needs_communicator_and_device(lib):
+    """No CPU numeric path and no silent single-GPU fallback: a host-only multi-GPU handle analyses but does not factorize."""
+    from uno_b200 import B200KKTError, KKTSolver
+    kkt = _systems()["ocp3d_12"]
+    h = KKTSolver(device=-1, num_gpus=2)
+    h.do_symbolic_analysis(kkt.dim, kkt.row, kkt.col, kkt.reg_size, kkt.n)
+    with pytest.raises(B200KKTError):
+        h.do_numerical_factorization(kkt.val)
+    with pytest.raises(B200KKTError):
+        h.comm_init(0, 2, b"\0" * 128)
+    h.close()
+
+
+# ---- world_size 2, gloo: the transfer protocol of the partitioned numeric phase ----------------------------------------
+class GlooTransport:
+    def exchange(self, sends, recvs):
+        bufs = [torch.empty(shape, dtype=torch.float64) for _, shape in recvs]
+        ops = [dist.P2POp(dist.isend, torch.from_numpy(np.array(a, dtype=np.float64)), peer) for peer, a in sends]
+        ops += [dist.P2POp(dist.irecv, b, peer) for (peer, _), b in zip(recvs, bufs)]
+        if ops:
+            for w in dist.batch_isend_irecv(ops):
+                w.wait()
+        return [b.numpy() for b in bufs]
+
+    def allreduce_sum(self, a):
+        t = torch.from_numpy(np.array(a, dtype=np.float64))
+        dist.all_reduce(t)
+        return t.numpy()
+
+
+def _free_port():
+    with socket.socket() as s:
+        s.bind(("127.0.0.1", 0))
+        return s.getsockname()[1]
+
+
+def _worker(rank, world, port, out):
+    os.environ.update(MASTER_ADDR="127.0.0.1", MASTER_PORT=str(port), RANK=str(rank), WORLD_SIZE=str(world))
+    dist.init_process_group("gloo", rank=rank, world_size=world)
+    sys.path.insert(0, str(ROOT))
+    sys.path.insert(0, str(ROOT / "tests"))
+    import emulator
+    from helpers import backward_error
+    from uno_b200 import KKTSolver, partition
+    from uno_b200 import generators as G
+    uid = partition.share_unique_id(dist, lambda: bytes(range(128)))        # the id hand-over bench.py uses (NCCL id there)
+    res = {"rank": rank, "uid_ok": uid == bytes(range(128))}
+    for name, kkt in (("ocp3d_8", G.ocp_distributed(8, 3, seed=1)), ("bnd3d_8", G.ocp_boundary_3d(8, seed=2))):
+        host = KKTSolver(device=-1, num_gpus=world)
+        host.do_symbolic_analysis(kkt.dim, kkt.row, kkt.col, kkt.reg_size, kkt.n)
+        plan, part = host.plan(), host.partition()
+        perm, scatter = host.permutation()
+        emu = emulator.PartitionedEmulation(plan, part, rank, GlooTransport(), perm, scatter, kkt, kkt.val)
+        ine = emu.inertia()
+        x = emu.solve(kkt.rhs)
+        whole = emulator.EmulatedFactorization(plan, perm, scatter, kkt, kkt.val)   # the unpartitioned run of the same plan
+        x1 = whole.solve(kkt.rhs)
+        res[name] = {"inertia": ine, "inertia_whole": whole.inertia(), "expected": (kkt.n, kkt.m, 0), "berr": float(backward_error(kkt, kkt.val, x)),
+                     "diff": float(np.max(np.abs(x - x1)) / np.max(np.abs(x1))), "cuts": len(part["cut_fronts"]),
+                     "checksum": float(np.sum(x)), "own_fronts": int((part["owner"] == rank).sum())}
+        host.close()
+    out.put(res)
+    dist.destroy_process_group()
+
+
+def test_partitioned_protocol_world_size_two_gloo(lib):
+    world = 2
+    ctx = mp.get_context("spawn")
+    out = ctx.Queue()
+    port = _free_port()
+    procs = [ctx.Process(target=_worker, args=(r, world, port, out)) for r in range(world)]
+    for p in procs:
+        p.start()
+    res = sorted((out.get(timeout=300) for _ in range(world)), key=lambda r: r["rank"])
+    for p in procs:
+        p.join(timeout=60)
+        assert p.exitcode == 0
+    for name in ("ocp3d_8", "bnd3d_8"):
+        a, b = res[0][name], res[1][name]
+        assert a["cuts"] >= 1 and a["own_fronts"] > 0 and b["own_fronts"] > 0
+        for r in (a, b):
+            assert tuple(r["inertia"]) == tuple(r["inertia_whole"]) == tuple(r["expected"])
+            assert r["berr"] <= 1e-12
+            assert r["diff"] <= 1e-9
+        assert a["checksum"] == b["checksum"]            # both ranks end up with the same solution vector
+    assert res[0]["uid_ok"] and res[1]["uid_ok"]

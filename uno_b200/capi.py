@@ -20,6 +20,7 @@ EXPORTED_SYMBOLS = [
     "b200kkt_solve_device", "b200kkt_get_permutation", "b200kkt_get_stats", "b200kkt_last_error", "b200kkt_plan_sizes",
     "b200kkt_plan_fronts", "b200kkt_plan_rows", "b200kkt_debug_assemble", "b200kkt_debug_factor", "b200kkt_get_stream",
     "b200kkt_debug_bench_update", "b200kkt_debug_phase_cycles", "b200kkt_debug_bench_bk",
+    "b200kkt_comm_unique_id", "b200kkt_comm_init", "b200kkt_plan_partition",
 ]
 
 
@@ -35,6 +36,9 @@ class Stats(C.Structure):
         ("num_null_pivots_last", C.c_int64), ("num_two_by_two_last", C.c_int64),
         ("t_update_profiled", C.c_double), ("flops_update_profiled", C.c_double), ("n_update_profiled", C.c_int64),
         ("t_assemble_profiled", C.c_double),
+        ("num_parts", C.c_int64), ("part_rank", C.c_int64), ("num_cut_fronts", C.c_int64),
+        ("flops_own", C.c_double), ("flops_critical", C.c_double),
+        ("comm_bytes_factor", C.c_int64), ("comm_bytes_sweep", C.c_int64),
     ]
 
     def as_dict(self):
@@ -75,6 +79,9 @@ def load_library():
     lib.b200kkt_plan_rows.argtypes = [H, C.c_void_p, C.c_void_p]
     lib.b200kkt_debug_assemble.argtypes = [H, C.c_void_p, C.c_void_p, C.c_void_p]
     lib.b200kkt_debug_factor.argtypes = [H] + [C.c_void_p] * 5
+    lib.b200kkt_comm_unique_id.argtypes = [C.c_void_p]
+    lib.b200kkt_comm_init.argtypes = [H, C.c_int, C.c_int, C.c_void_p]
+    lib.b200kkt_plan_partition.argtypes = [H, C.c_void_p, P(C.c_int64), C.c_void_p, C.c_void_p, P(C.c_double)]
     for name in EXPORTED_SYMBOLS:
         if name != "b200kkt_last_error":
             getattr(lib, name).restype = C.c_int
@@ -84,6 +91,16 @@ def load_library():
 
 class B200KKTError(RuntimeError):
     pass
+
+
+def comm_unique_id() -> bytes:
+    """128-byte NCCL unique id (rank 0 creates it, the host program hands it to the other ranks)."""
+    lib = load_library()
+    buf = C.create_string_buffer(128)
+    rc = lib.b200kkt_comm_unique_id(buf)
+    if rc != 0:
+        raise B200KKTError(f"b200kkt_comm_unique_id failed ({rc}): libnccl.so.2 could not be opened")
+    return buf.raw
 
 
 def _ptr(a):
@@ -139,6 +156,24 @@ class KKTSolver:
             return
         p = np.ascontiguousarray(perm, dtype=np.int64)
         self._check(self._lib.b200kkt_set_user_permutation(self._h, _ptr(p), p.size), "set_user_permutation")
+
+    # -- multi-GPU (one process per GPU) ---------------------------------------------------------
+    def comm_init(self, rank: int, world: int, unique_id: bytes):
+        """Join the NCCL communicator of a subtree-partitioned solve; `unique_id` = rank 0's comm_unique_id()."""
+        assert len(unique_id) == 128
+        buf = C.create_string_buffer(bytes(unique_id), 128)
+        self._check(self._lib.b200kkt_comm_init(self._h, int(rank), int(world), buf), "comm_init")
+
+    def partition(self):
+        """Subtree map of the last analysis: owner per front, cut fronts, factor flops per rank, critical-path flops."""
+        nsn = self.plan()["num_fronts"]
+        owner = np.empty(nsn, dtype=np.int32)
+        cut = np.empty(nsn, dtype=np.int32)
+        ncut = C.c_int64()
+        parts = np.zeros(max(1, int(self.stats()["num_parts"])), dtype=np.float64)
+        crit = C.c_double()
+        self._check(self._lib.b200kkt_plan_partition(self._h, _ptr(owner), C.byref(ncut), _ptr(cut), _ptr(parts), C.byref(crit)), "plan_partition")
+        return {"owner": owner, "cut_fronts": cut[:ncut.value].copy(), "part_flops": parts, "critical_flops": crit.value}
 
     # -- reference interface -----------------------------------------------------------------
     def initialize_memory(self, number_variables, number_constraints, number_hessian_nonzeros, regularization_size):

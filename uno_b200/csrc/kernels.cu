@@ -108,6 +108,35 @@ __global__ void k_solve_scatter_add(int64_t n, const int* __restrict__ perm, con
 }
 
 // ------------------------------------------------------------------------------------------------
+// K9 helpers of the subtree-partitioned solve (one rank per GPU).  At a cut edge (front s whose parent lives on another
+// rank) the backward sweep ships the solution on s's boundary rows: the parent's rank packs it into s's slot of the boundary
+// pool, NCCL moves the slot, s's rank unpacks it into its own solution vector.  One CTA per cut front.
+// ------------------------------------------------------------------------------------------------
+__global__ void __launch_bounds__(256) k_boundary_pack(FrontArrays F, const int* __restrict__ list, const double* __restrict__ xg,
+                                                       double* __restrict__ cpool) {
+   const int s = list[blockIdx.x];
+   const int k = F.k[s], r = F.f[s] - k;
+   const int* __restrict__ rows = F.rows + F.rows_off[s] + k;
+   double* slot = cpool + F.rel_off[s];
+   for (int i = threadIdx.x; i < r; i += 256) slot[i] = xg[rows[i]];
+}
+
+__global__ void __launch_bounds__(256) k_boundary_unpack(FrontArrays F, const int* __restrict__ list, const double* __restrict__ cpool,
+                                                         double* __restrict__ xg) {
+   const int s = list[blockIdx.x];
+   const int k = F.k[s], r = F.f[s] - k;
+   const int* __restrict__ rows = F.rows + F.rows_off[s] + k;
+   const double* slot = cpool + F.rel_off[s];
+   for (int i = threadIdx.x; i < r; i += 256) xg[rows[i]] = slot[i];
+}
+
+// solution entries of pivots owned by other ranks are zeroed before the sum over ranks puts the vector together
+__global__ void k_keep_owned(int64_t n, const signed char* __restrict__ col_owner, const int rank, double* __restrict__ xg) {
+   const int64_t g = blockIdx.x * static_cast<int64_t>(blockDim.x) + threadIdx.x;
+   if (g < n && col_owner[g] != rank) xg[g] = 0.0;
+}
+
+// ------------------------------------------------------------------------------------------------
 // K5 prepare: zero the front's contribution block and extend-add the children into the front.
 // CTA (parent, column block) owns EA_CBW parent columns and pulls the matching columns of every
 // child's contribution block, children in ascending order -> no atomics, fixed summation order.
@@ -2430,6 +2459,23 @@ int launch_solve_gather(int64_t n, const int* perm, const double* scale, const d
 
 int launch_solve_scatter_add(int64_t n, const int* perm, const double* scale, const double* xg, double* x, cudaStream_t st) {
    k_solve_scatter_add<<<grid1d(n, 256), 256, 0, st>>>(n, perm, scale, xg, x);
+   return 1;
+}
+
+int launch_boundary_pack(const FrontArrays& F, const int* d_list, int nfronts, const double* xg, double* cpool, cudaStream_t st) {
+   if (nfronts <= 0) return 0;
+   k_boundary_pack<<<nfronts, 256, 0, st>>>(F, d_list, xg, cpool);
+   return 1;
+}
+
+int launch_boundary_unpack(const FrontArrays& F, const int* d_list, int nfronts, const double* cpool, double* xg, cudaStream_t st) {
+   if (nfronts <= 0) return 0;
+   k_boundary_unpack<<<nfronts, 256, 0, st>>>(F, d_list, cpool, xg);
+   return 1;
+}
+
+int launch_keep_owned(int64_t n, const signed char* col_owner, int rank, double* xg, cudaStream_t st) {
+   k_keep_owned<<<grid1d(n, 256), 256, 0, st>>>(n, col_owner, rank, xg);
    return 1;
 }
 

@@ -128,6 +128,11 @@ int launch_bwd_big_scatter(const FrontArrays& F, const int* d_list, int nfronts,
 // permute+scale in, scale+permute out (accumulating into x)
 int launch_solve_gather(int64_t n, const int* perm, const double* scale, const double* r, double* zg, cudaStream_t st);
 int launch_solve_scatter_add(int64_t n, const int* perm, const double* scale, const double* xg, double* x, cudaStream_t st);
+// K9 (subtree partition): boundary solution of cut fronts into / out of their slot of the boundary pool; zero the solution
+// entries of pivots owned by other ranks (col_owner: rank per pivot position)
+int launch_boundary_pack(const FrontArrays& F, const int* d_list, int nfronts, const double* xg, double* cpool, cudaStream_t st);
+int launch_boundary_unpack(const FrontArrays& F, const int* d_list, int nfronts, const double* cpool, double* xg, cudaStream_t st);
+int launch_keep_owned(int64_t n, const signed char* col_owner, int rank, double* xg, cudaStream_t st);
 // K8 residual r = b - K x on the COO-order values, and infinity norms as ordered bit patterns
 int launch_residual(const CsrArrays& A, const double* values, const double* x, const double* b, double* r, cudaStream_t st);
 int launch_absmax(const double* v, int64_t n, unsigned long long* out_bits, cudaStream_t st);

@@ -77,6 +77,15 @@ struct Plan {
    int64_t sum_r = 0;
    int32_t max_f = 0, max_k = 0;
    int64_t num_pairs = 0;
+
+   // Subtree-to-GPU mapping; filled by map_subtrees.  owner[s] = rank that assembles, factorizes and solves
+   // front s.  A "cut edge" is a front whose parent lives on another rank: its contribution block (factorization), its boundary
+   // partial sums (forward solve) and its boundary solution (backward solve) cross NVLink there and nowhere else.
+   int32_t num_parts = 1;
+   std::vector<int32_t> owner;       // nsn
+   std::vector<int32_t> cut_edges;   // fronts s with owner[s] != owner[parent[s]], ascending (level[s], s)
+   std::vector<double> part_flops;   // factor flops per rank
+   double critical_flops = 0.0;      // factor flops on the longest chain of dependent work (subtree + top fronts above it)
    double t_order = 0, t_symbolic = 0, t_maps = 0;
    std::string ordering_used;
 };
@@ -84,5 +93,10 @@ struct Plan {
 // Throws std::runtime_error on malformed input (index out of range, lower-triangular entry).
 void analyse(int64_t N, int64_t nnz, int64_t reg_size, int64_t num_primal,
              const uint64_t* row, const uint64_t* col, const AnalyseOptions& opt, Plan& plan);
+
+// Proportional mapping of the assembly tree onto `parts` ranks: the tree is opened from the roots (heaviest subtree first)
+// until the open subtrees can be packed evenly, the subtrees are packed by decreasing flop count (LPT), and every front above
+// the cut goes to the owner of its heaviest child.  Deterministic: every rank computes the same map from the same plan.
+void map_subtrees(Plan& plan, int parts);
 
 }  // namespace b200kkt

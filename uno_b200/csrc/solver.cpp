@@ -42,6 +42,13 @@ struct CudaError {
       if (e__ != cudaSuccess) throw CudaError{e__, #expr};           \
    } while (0)
 
+// NCCL wrappers return non-zero with a message; surface them as an internal error of the call in progress
+#define CKN(expr)                                                    \
+   do {                                                              \
+      std::string e__;                                               \
+      if ((expr) != 0) throw std::runtime_error(e__);                \
+   } while (0)
+
 int fail(const b200kkt_handle* h, int code, const std::string& msg) {
    if (h != nullptr) h->err = msg;
    return code;
@@ -70,6 +77,8 @@ void free_plan_device(b200kkt_handle* h) {
    if (h->solve_graph != nullptr) { cudaGraphExecDestroy(h->solve_graph); h->solve_graph = nullptr; }
    for (void* p : h->plan_allocs) cudaFree(p);
    h->plan_allocs.clear();
+   for (cudaEvent_t e : h->ev_comm) if (e != nullptr) cudaEventDestroy(e);
+   h->ev_comm.clear();
    h->analysed = false;
    h->values_resident = false;
    h->factorized = false;
@@ -95,7 +104,9 @@ void build_batches(b200kkt_handle* h, std::vector<int>& batch_list, std::vector<
    wpool_size = 0;
    std::vector<int> ids;
    for (int l = 0; l < P.nlevels; ++l) {
-      ids.assign(P.level_fronts.begin() + P.level_ptr[l], P.level_fronts.begin() + P.level_ptr[l + 1]);
+      ids.clear();
+      for (int t = P.level_ptr[l]; t < P.level_ptr[l + 1]; ++t)
+         if (P.owner[P.level_fronts[t]] == h->rank) ids.push_back(P.level_fronts[t]);   // subtree partition: this rank's fronts only
       std::stable_sort(ids.begin(), ids.end(), [&](int a, int b) {
          const int ca = size_class(P.f[a]), cb = size_class(P.f[b]);
          if (ca != cb) return ca > cb;
@@ -140,6 +151,70 @@ void build_batches(b200kkt_handle* h, std::vector<int>& batch_list, std::vector<
    }
 }
 
+int64_t cb_doubles(const Plan& P, int s) {
+   const int64_t r = P.f[s] - P.k[s];
+   return r * (r + 1) / 2;
+}
+
+// Subtree partition: which cut fronts this rank sends or receives at which tree level, the device lists for the boundary
+// pack/unpack kernels, and the rank of every pivot position (for the sum of the solution over ranks).
+void build_cut_schedule(b200kkt_handle* h) {
+   const Plan& P = h->plan;
+   for (cudaEvent_t e : h->ev_comm) if (e != nullptr) cudaEventDestroy(e);
+   h->ev_comm.assign(static_cast<size_t>(P.nlevels), nullptr);
+   h->cut_levels.assign(static_cast<size_t>(P.nlevels), b200kkt_handle::CutLevel());
+   h->wait_level.assign(static_cast<size_t>(P.nlevels), -1);
+   h->comm_bytes_factor = h->comm_bytes_solve = 0;
+   h->d_cut_list = nullptr;
+   h->d_col_owner = nullptr;
+   if (!h->partitioned()) return;
+   for (const int s : P.cut_edges) {   // ascending (level, front)
+      const int p = P.parent[s];
+      if (P.owner[s] != h->rank && P.owner[p] != h->rank) continue;
+      h->cut_levels[P.level[s]].fronts.push_back(s);
+      h->comm_bytes_factor += 8 * cb_doubles(P, s);
+      h->comm_bytes_solve += 2 * 8 * static_cast<int64_t>(P.f[s] - P.k[s]);
+      if (P.owner[p] == h->rank) h->wait_level[P.level[p]] = std::max(h->wait_level[P.level[p]], P.level[s]);
+   }
+   std::vector<int> cut_list;
+   for (int l = 0; l < P.nlevels; ++l) {
+      b200kkt_handle::CutLevel& CL = h->cut_levels[l];
+      if (CL.fronts.empty()) continue;
+      CK(cudaEventCreateWithFlags(&h->ev_comm[l], cudaEventDisableTiming));
+      CL.out_begin = static_cast<int>(cut_list.size());
+      for (const int s : CL.fronts) if (P.owner[s] == h->rank) cut_list.push_back(s);
+      CL.out_count = static_cast<int>(cut_list.size()) - CL.out_begin;
+      CL.in_begin = static_cast<int>(cut_list.size());
+      for (const int s : CL.fronts) if (P.owner[s] != h->rank) cut_list.push_back(s);
+      CL.in_count = static_cast<int>(cut_list.size()) - CL.in_begin;
+   }
+   h->d_cut_list = dev_upload(h, cut_list);
+   std::vector<signed char> col_owner(static_cast<size_t>(P.N));
+   for (int32_t s = 0; s < P.nsn; ++s)
+      for (int32_t q = P.sn_first[s]; q < P.sn_first[s + 1]; ++q) col_owner[q] = static_cast<signed char>(P.owner[s]);
+   h->d_col_owner = dev_upload(h, col_owner);
+}
+
+// NCCL group with the transfers of the cut fronts of tree level l: `what` 0 = contribution blocks child -> parent (factorization),
+// 1 = boundary partial sums child -> parent (forward solve), 2 = boundary solution parent -> child (backward solve)
+void enqueue_cut_transfers(b200kkt_handle* h, int l, int what, double* pool, cudaStream_t st) {
+   const Plan& P = h->plan;
+   const b200kkt_handle::CutLevel& CL = h->cut_levels[l];
+   if (CL.fronts.empty()) return;
+   CKN(comm_group_start(e__));
+   for (const int s : CL.fronts) {
+      const bool mine = P.owner[s] == h->rank;
+      const int peer = mine ? P.owner[P.parent[s]] : P.owner[s];
+      const int64_t count = what == 0 ? cb_doubles(P, s) : static_cast<int64_t>(P.f[s] - P.k[s]);
+      if (count <= 0) continue;
+      double* ptr = pool + (what == 0 ? P.cb_off[s] : P.rel_off[s]);
+      const bool send = (what == 2) ? !mine : mine;
+      if (send) CKN(comm_send_f64(h->comm, ptr, static_cast<size_t>(count), peer, st, e__));
+      else CKN(comm_recv_f64(h->comm, ptr, static_cast<size_t>(count), peer, st, e__));
+   }
+   CKN(comm_group_end(e__));
+}
+
 void upload_plan(b200kkt_handle* h) {
    const Plan& P = h->plan;
    const auto t0 = std::chrono::steady_clock::now();
@@ -182,6 +257,7 @@ void upload_plan(b200kkt_handle* h) {
          big.clear();
          for (int t = P.level_ptr[l]; t < P.level_ptr[l + 1]; ++t) {
             const int s = P.level_fronts[t];
+            if (P.owner[s] != h->rank) continue;
             const bool is_big = P.k[s] > NBS || static_cast<int64_t>(P.f[s]) * P.k[s] > 98304;
             if (is_big) big.push_back(s); else solve_list.push_back(s);
          }
@@ -239,6 +315,7 @@ void upload_plan(b200kkt_handle* h) {
    h->d_counters = dev_alloc<int>(h, 8);
    h->d_norms = dev_alloc<unsigned long long>(h, 4);
    h->d_scale_final = h->d_scale;
+   build_cut_schedule(h);
    CK(cudaMemsetAsync(h->W.wpool, 0, static_cast<size_t>(std::max<int64_t>(4 * h->wpool_size, 1)) * sizeof(double), h->stream));
    CK(cudaStreamSynchronize(h->stream));
    h->stats.t_upload = std::chrono::duration<double>(std::chrono::steady_clock::now() - t0).count();
@@ -257,6 +334,9 @@ void fill_plan_stats(b200kkt_handle* h) {
    s.assembly_distinct = static_cast<int64_t>(P.asm_dst.size());
    s.flops_factor = P.flops; s.flops_tensor = P.flops_tc;
    s.t_ordering = P.t_order; s.t_symbolic = P.t_symbolic; s.t_maps = P.t_maps;
+   s.num_parts = P.num_parts; s.part_rank = h->rank; s.num_cut_fronts = static_cast<int64_t>(P.cut_edges.size());
+   s.flops_own = P.part_flops.empty() ? P.flops : P.part_flops[static_cast<size_t>(h->rank)];
+   s.flops_critical = P.critical_flops;
 }
 
 // ---- numeric factorization: enqueue everything on the handle's stream -------------------------
@@ -277,6 +357,8 @@ void enqueue_factor(b200kkt_handle* h) {
    L += launch_matrix_inf_norm(h->C, h->d_values, h->d_norms + 0, st);
    // K1 assembly into the zeroed factor pool
    CK(cudaMemsetAsync(h->W.lpool, 0, static_cast<size_t>(P.pool_size) * sizeof(double), st));
+   // subtree partition: pivot positions of other ranks' fronts carry no pivot type here (K6 skips them)
+   if (h->partitioned()) CK(cudaMemsetAsync(h->W.ptype, 0xFF, static_cast<size_t>(P.N) * sizeof(int), st));
    const bool prof = h->profile_updates != 0 && !h->use_graph;
    auto prof_begin = [&](double flops, int kind) {
       b200kkt_handle::ProfiledLaunch p{nullptr, nullptr, flops, kind};
@@ -293,6 +375,8 @@ void enqueue_factor(b200kkt_handle* h) {
    // handle's streams (fork/join with events, which stream capture turns into graph edges)
    const bool multi = h->multi_stream != 0 && !prof;
    for (int l = 0; l < P.nlevels; ++l) {
+      // contribution blocks of cut fronts that a front of this level assembles: wait until they have arrived
+      if (h->partitioned() && h->wait_level[l] >= 0) CK(cudaStreamWaitEvent(h->stream, h->ev_comm[h->wait_level[l]], 0));
       const int nb = h->level_batch_ptr[l + 1] - h->level_batch_ptr[l];
       const int nside = multi ? std::min(nb - 1, static_cast<int>(b200kkt_handle::NUM_AUX)) : 0;
       if (nside > 0) {
@@ -402,10 +486,24 @@ void enqueue_factor(b200kkt_handle* h) {
          CK(cudaEventRecord(h->ev_join[a], h->aux[a]));
          CK(cudaStreamWaitEvent(h->stream, h->ev_join[a], 0));
       }
+      // K9: the cut fronts of this level hand their contribution blocks to the parent's rank over NVLink, on the
+      // communication stream, while this rank goes on with its next levels
+      if (h->partitioned() && !h->cut_levels[l].fronts.empty()) {
+         CK(cudaEventRecord(h->ev_level_done, h->stream));
+         CK(cudaStreamWaitEvent(h->comm_stream, h->ev_level_done, 0));
+         enqueue_cut_transfers(h, l, 0, h->W.cbpool, h->comm_stream);
+         CK(cudaEventRecord(h->ev_comm[l], h->comm_stream));
+      }
    }
-   // K6 inertia
+   if (h->partitioned()) {
+      // nothing of this factorization may still be in flight when the caller starts the next one
+      CK(cudaEventRecord(h->ev_level_done, h->comm_stream));
+      CK(cudaStreamWaitEvent(h->stream, h->ev_level_done, 0));
+   }
+   // K6 inertia (partitioned: this rank's pivots, then summed over ranks)
    CK(cudaMemsetAsync(h->d_counters, 0, 8 * sizeof(int), st));
    L += launch_inertia(P.N, h->W, h->d_counters, st);
+   if (h->partitioned()) CKN(comm_allreduce_sum_i32(h->comm, h->d_counters, 8, st, e__));
    CK(cudaMemcpyAsync(h->h_counters, h->d_counters, 8 * sizeof(int), cudaMemcpyDeviceToHost, st));
 }
 
@@ -423,7 +521,7 @@ double bits_to_double(unsigned long long b) {
 void run_factor(b200kkt_handle* h) {
    cudaStream_t st = h->stream;
    CK(cudaEventRecord(h->ev0, st));
-   if (h->use_graph) {
+   if (h->use_graph && !h->partitioned()) {   // partitioned: NCCL calls between the levels, launched directly
       if (h->factor_graph == nullptr) {
          const int64_t before = h->launches;
          cudaGraph_t graph = nullptr;
@@ -500,6 +598,7 @@ void run_solve(b200kkt_handle* h, const double* d_b, double* d_x, double* backwa
    L += launch_absmax(d_b, P.N, h->d_norms + 3, st);
    // one sweep: permute+scale in, forward, block-diagonal, backward, scale+permute out (accumulating into x)
    auto enqueue_sweep = [&] {
+      const bool parts = h->partitioned();
       L += launch_solve_gather(P.N, h->d_perm, h->d_scale_final, h->d_r, h->d_zg, st);
       for (int l = 0; l < P.nlevels; ++l) {
          const b200kkt_handle::SolveLevel& SL = h->solve_levels[l];
@@ -514,9 +613,18 @@ void run_solve(b200kkt_handle* h, const double* d_b, double* d_x, double* backwa
                L += launch_fwd_big_gemv(h->F, list, nf, SL.big_pmaxf[nf - 1], jp, h->W, h->d_z2, h->d_cpool, st);
             }
          }
+         // K9: boundary partial sums of this level's cut fronts go to the parent's rank
+         if (parts) enqueue_cut_transfers(h, l, 1, h->d_cpool, st);
       }
       for (int l = P.nlevels - 1; l >= 0; --l) {
          const b200kkt_handle::SolveLevel& SL = h->solve_levels[l];
+         if (parts && !h->cut_levels[l].fronts.empty()) {
+            // K9: the parent's rank ships the solution on the cut front's boundary rows
+            const b200kkt_handle::CutLevel& CL = h->cut_levels[l];
+            L += launch_boundary_pack(h->F, h->d_cut_list + CL.in_begin, CL.in_count, h->d_xg, h->d_cpool, st);
+            enqueue_cut_transfers(h, l, 2, h->d_cpool, st);
+            L += launch_boundary_unpack(h->F, h->d_cut_list + CL.out_begin, CL.out_count, h->d_cpool, h->d_xg, st);
+         }
          L += launch_backward_level(h->F, h->d_solve_list + SL.small_begin, SL.small_count, h->W, h->d_z2, h->d_xg, h->d_cpool, st);
          if (SL.big_count > 0) {
             const int* list = h->d_solve_list + SL.big_begin;
@@ -530,12 +638,17 @@ void run_solve(b200kkt_handle* h, const double* d_b, double* d_x, double* backwa
             L += launch_bwd_big_scatter(h->F, list, SL.big_count, SL.big_max_k, h->W, h->d_z2, h->d_xg, st);
          }
       }
+      if (parts) {
+         // every rank holds the solution of its own pivots: zero the rest, sum over ranks, and all ranks carry the same x
+         L += launch_keep_owned(P.N, h->d_col_owner, h->rank, h->d_xg, st);
+         CKN(comm_allreduce_sum_f64(h->comm, h->d_xg, static_cast<size_t>(P.N), st, e__));
+      }
       L += launch_solve_scatter_add(P.N, h->d_perm, h->d_scale_final, h->d_xg, d_x, st);
    };
    double berr = 0.0, prev = 0.0;
    int steps = 0;
    for (int it = 0; it <= h->refine_max_steps; ++it) {
-      if (h->use_graph) {
+      if (h->use_graph && !h->partitioned()) {
          // the sweep is a long chain of short kernels: replayed as a CUDA graph (re-captured when the output vector moves)
          if (h->solve_graph == nullptr || h->solve_graph_x != d_x || h->solve_graph_scale != h->d_scale_final) {
             if (h->solve_graph != nullptr) { cudaGraphExecDestroy(h->solve_graph); h->solve_graph = nullptr; }
@@ -647,6 +760,10 @@ int b200kkt_create(b200kkt_handle** out, int device, int num_gpus) {
          }
          CK(cudaEventCreate(&h->ev0));
          CK(cudaEventCreate(&h->ev1));
+         if (h->num_gpus > 1) {
+            CK(cudaStreamCreateWithPriority(&h->comm_stream, cudaStreamNonBlocking, prio_greatest));
+            CK(cudaEventCreateWithFlags(&h->ev_level_done, cudaEventDisableTiming));
+         }
          CK(cudaMallocHost(reinterpret_cast<void**>(&h->h_counters), 8 * sizeof(int)));
          CK(cudaMallocHost(reinterpret_cast<void**>(&h->h_norms), 4 * sizeof(unsigned long long)));
          const int e = init_kernel_attributes();
@@ -670,6 +787,9 @@ int b200kkt_destroy(b200kkt_handle* h) {
       cudaSetDevice(h->device);
       if (h->stream != nullptr) cudaStreamSynchronize(h->stream);
       free_plan_device(h);
+      b200kkt::comm_destroy(h->comm);
+      if (h->comm_stream != nullptr) cudaStreamDestroy(h->comm_stream);
+      if (h->ev_level_done != nullptr) cudaEventDestroy(h->ev_level_done);
       if (h->h_counters != nullptr) cudaFreeHost(h->h_counters);
       if (h->h_norms != nullptr) cudaFreeHost(h->h_norms);
       if (h->ev0 != nullptr) cudaEventDestroy(h->ev0);
@@ -687,6 +807,38 @@ int b200kkt_destroy(b200kkt_handle* h) {
       if (h->stream != nullptr) cudaStreamDestroy(h->stream);
    }
    delete h;
+   return B200KKT_OK;
+}
+
+int b200kkt_comm_unique_id(char id[128]) {
+   if (id == nullptr) return B200KKT_EINVAL;
+   std::string err;
+   return b200kkt::comm_unique_id(id, err) == 0 ? B200KKT_OK : B200KKT_ECUDA;
+}
+
+int b200kkt_comm_init(b200kkt_handle* h, int rank, int world, const char id[128]) {
+   if (int rc = need_device(h)) return rc;
+   if (id == nullptr || world != h->num_gpus || rank < 0 || rank >= world)
+      return fail(h, B200KKT_EINVAL, "comm_init: world must equal the handle's num_gpus and 0 <= rank < world");
+   if (h->analysed) return fail(h, B200KKT_EINVAL, "comm_init after analyse");
+   return guarded(h, [&] {
+      CK(cudaSetDevice(h->device));
+      std::string err;
+      if (b200kkt::comm_init(h->comm, rank, world, id, err) != 0) throw std::runtime_error(err);
+      h->rank = rank;
+   });
+}
+
+int b200kkt_plan_partition(const b200kkt_handle* h, int32_t* owner, int64_t* num_cut, int32_t* cut_fronts, double* part_flops,
+                           double* critical_flops) {
+   if (h == nullptr) return B200KKT_EINVAL;
+   if (!h->analysed) return fail(h, B200KKT_EINVAL, "plan getter before analyse");
+   const Plan& P = h->plan;
+   if (owner != nullptr) std::copy(P.owner.begin(), P.owner.end(), owner);
+   if (num_cut != nullptr) *num_cut = static_cast<int64_t>(P.cut_edges.size());
+   if (cut_fronts != nullptr) std::copy(P.cut_edges.begin(), P.cut_edges.end(), cut_fronts);
+   if (part_flops != nullptr) std::copy(P.part_flops.begin(), P.part_flops.end(), part_flops);
+   if (critical_flops != nullptr) *critical_flops = P.critical_flops;
    return B200KKT_OK;
 }
 
@@ -739,6 +891,8 @@ int b200kkt_analyse(b200kkt_handle* h, uint64_t n, uint64_t nnz, uint64_t reg_si
    if (h == nullptr || (nnz > 0 && (row == nullptr || col == nullptr))) return B200KKT_EINVAL;
    if (h->has_device) { cudaSetDevice(h->device); free_plan_device(h); }
    h->analysed = false;
+   if (h->has_device && h->partitioned() && !h->comm.active())
+      return fail(h, B200KKT_EINVAL, "multi-GPU handle: b200kkt_comm_init must be called before b200kkt_analyse");
    const int rc = guarded(h, [&] {
       AnalyseOptions opt = h->aopt;
       if (opt.ordering == 2) {
@@ -747,6 +901,7 @@ int b200kkt_analyse(b200kkt_handle* h, uint64_t n, uint64_t nnz, uint64_t reg_si
       }
       analyse(static_cast<int64_t>(n), static_cast<int64_t>(nnz), static_cast<int64_t>(reg_size), static_cast<int64_t>(num_primal), row, col,
               opt, h->plan);
+      map_subtrees(h->plan, h->num_gpus);
       fill_plan_stats(h);
       if (h->has_device) upload_plan(h);
       h->analysed = true;
@@ -837,6 +992,8 @@ int b200kkt_get_stats(const b200kkt_handle* h, b200kkt_stats* stats) {
    if (h == nullptr || stats == nullptr) return B200KKT_EINVAL;
    *stats = h->stats;
    stats->kernel_launches = h->launches;
+   stats->comm_bytes_factor = h->comm_bytes_factor;
+   stats->comm_bytes_sweep = h->comm_bytes_solve;
    if (h->factorized) { stats->num_null_pivots_last = h->h_counters[2]; stats->num_two_by_two_last = h->h_counters[3]; }
    return B200KKT_OK;
 }

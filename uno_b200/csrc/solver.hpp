@@ -10,6 +10,7 @@
 #include <cuda_runtime.h>
 
 #include "../../include/b200kkt.h"
+#include "comm.hpp"
 #include "kernels.hpp"
 #include "plan.hpp"
 
@@ -110,6 +111,27 @@ struct b200kkt_handle {
    int* h_counters = nullptr;              // pinned mirrors
    unsigned long long* h_norms = nullptr;
    double* d_scale_final = nullptr;        // whichever of d_scale/d_scale_tmp holds the result
+
+   // ---- subtree partition over num_gpus ranks (one process per GPU) ------------------------------------
+   // Every rank holds the whole integer plan and owns the fronts plan.owner assigns to it.  Contribution blocks of cut fronts
+   // travel on comm_stream (NCCL send/recv straight between the two arenas: same plan, same offsets), so a rank keeps working
+   // on its own levels while a block is in flight; the solve ships boundary vectors on the main stream.
+   b200kkt::Comm comm;
+   int rank = 0;
+   bool partitioned() const { return num_gpus > 1; }
+   struct CutLevel {                      // cut fronts of one tree level that touch this rank, ascending front index
+      std::vector<int> fronts;
+      int out_begin = 0, out_count = 0;   // ranges in d_cut_list: fronts this rank owns (sends CB / boundary sums, receives x)
+      int in_begin = 0, in_count = 0;     // fronts whose parent this rank owns
+   };
+   std::vector<CutLevel> cut_levels;      // per level
+   std::vector<int> wait_level;           // per level L: last child level with a block received for a front of level L (-1: none)
+   std::vector<cudaEvent_t> ev_comm;      // per level: transfers of that level's cut fronts done (null where there are none)
+   cudaStream_t comm_stream = nullptr;
+   cudaEvent_t ev_level_done = nullptr;
+   int* d_cut_list = nullptr;
+   signed char* d_col_owner = nullptr;
+   int64_t comm_bytes_factor = 0, comm_bytes_solve = 0;   // per factorization / per sweep, sent + received by this rank
 
    uint64_t inertia[3] = {0, 0, 0};
    b200kkt_stats stats{};

@@ -671,4 +671,109 @@ void analyse(int64_t N, int64_t nnz, int64_t reg_size, int64_t num_primal, const
    P.t_maps = secs(t2, clk::now());
 }
 
+// ------------------------------------------------------------------------------------------------
+// Subtree-to-GPU mapping: independent elimination subtrees go to different ranks,
+// the separators above the cut to the owner of their heaviest child.
+// ------------------------------------------------------------------------------------------------
+void map_subtrees(Plan& P, int parts) {
+   const int32_t nsn = P.nsn;
+   parts = std::max(1, parts);
+   P.num_parts = parts;
+   P.owner.assign(static_cast<size_t>(nsn), 0);
+   P.cut_edges.clear();
+   P.part_flops.assign(static_cast<size_t>(parts), 0.0);
+   std::vector<double> own(static_cast<size_t>(nsn)), sub(static_cast<size_t>(nsn));
+   for (int32_t s = 0; s < nsn; ++s) {
+      const double kd = P.k[s], rd = P.f[s] - P.k[s];
+      own[s] = kd * kd * kd / 3.0 + kd * kd * rd + kd * rd * rd + 1.0;   // + 1: empty fronts still cost a launch slot
+      sub[s] = own[s];
+   }
+   // children precede parents in the final numbering (postorder)
+   for (int32_t s = 0; s < nsn; ++s) if (P.parent[s] >= 0) sub[P.parent[s]] += sub[s];
+   if (parts > 1 && nsn > 0) {
+      // open the tree from the roots: `open` holds the roots of the subtrees below the cut
+      auto heavier = [&](int32_t a, int32_t b) { return sub[a] != sub[b] ? sub[a] < sub[b] : a > b; };   // max-heap on weight, ties by index
+      std::vector<int32_t> open;
+      std::vector<char> above(static_cast<size_t>(nsn), 0);
+      double total = 0.0;
+      for (int32_t s = 0; s < nsn; ++s) if (P.parent[s] < 0) { open.push_back(s); total += sub[s]; }
+      std::make_heap(open.begin(), open.end(), heavier);
+      double open_weight = total;
+      // stop when the heaviest open subtree fits its share (with 5 % slack) or cannot be opened any further
+      while (!open.empty()) {
+         const int32_t top = open.front();
+         const bool enough = static_cast<int>(open.size()) >= parts && sub[top] <= 1.05 * open_weight / parts;
+         if (enough || P.child_ptr[top + 1] == P.child_ptr[top]) break;
+         std::pop_heap(open.begin(), open.end(), heavier);
+         open.pop_back();
+         above[top] = 1;
+         open_weight -= own[top];
+         for (int32_t ci = P.child_ptr[top]; ci < P.child_ptr[top + 1]; ++ci) {
+            open.push_back(P.child_idx[ci]);
+            std::push_heap(open.begin(), open.end(), heavier);
+         }
+      }
+      // LPT packing of the open subtrees that are worth a transfer; a light one (under 1 % of an even share) hanging off a
+      // separator stays with that separator
+      std::sort(open.begin(), open.end(), [&](int32_t a, int32_t b) { return sub[a] != sub[b] ? sub[a] > sub[b] : a < b; });
+      std::vector<double> load(static_cast<size_t>(parts), 0.0);
+      std::fill(P.owner.begin(), P.owner.end(), -1);
+      const double light = 0.01 * total / parts;
+      for (const int32_t s : open) {
+         if (sub[s] < light && P.parent[s] >= 0) continue;
+         int best = 0;
+         for (int p = 1; p < parts; ++p) if (load[p] < load[best]) best = p;
+         load[best] += sub[s];
+         P.owner[s] = best;
+      }
+      // bottom-up: a front above the cut goes where its heaviest placed child is
+      for (int32_t s = 0; s < nsn; ++s) {
+         if (!above[s]) continue;
+         int32_t best = -1;
+         for (int32_t ci = P.child_ptr[s]; ci < P.child_ptr[s + 1]; ++ci) {
+            const int32_t c = P.child_idx[ci];
+            if (P.owner[c] >= 0 && (best < 0 || sub[c] > sub[best])) best = c;
+         }
+         if (best >= 0) P.owner[s] = P.owner[best];
+      }
+      // top-down (parents have higher numbers): everything not placed yet follows its parent
+      for (int32_t s = nsn - 1; s >= 0; --s) {
+         if (P.owner[s] >= 0) continue;
+         if (P.parent[s] >= 0) { P.owner[s] = P.owner[P.parent[s]]; continue; }
+         int best = 0;
+         for (int p = 1; p < parts; ++p) if (load[p] < load[best]) best = p;
+         load[best] += sub[s];
+         P.owner[s] = best;
+      }
+   }
+   // cut edges in the order every rank walks them, work per rank, critical path
+   for (int32_t s = 0; s < nsn; ++s) {
+      P.part_flops[P.owner[s]] += own[s] - 1.0;
+      if (P.parent[s] >= 0 && P.owner[P.parent[s]] != P.owner[s]) P.cut_edges.push_back(s);
+   }
+   // critical path estimate: a front can start when all its children are done; children on the same rank run one after the
+   // other, children on different ranks side by side:  finish(s) = flops(s) + max over ranks q of sum of finish(children on q)
+   {
+      P.critical_flops = 0.0;
+      std::vector<double> finish(static_cast<size_t>(nsn), 0.0);
+      std::vector<double> by_rank(static_cast<size_t>(parts), 0.0);
+      for (int32_t s = 0; s < nsn; ++s) {
+         double longest = 0.0;
+         if (P.child_ptr[s + 1] > P.child_ptr[s]) {
+            for (int32_t ci = P.child_ptr[s]; ci < P.child_ptr[s + 1]; ++ci) by_rank[P.owner[P.child_idx[ci]]] = 0.0;
+            for (int32_t ci = P.child_ptr[s]; ci < P.child_ptr[s + 1]; ++ci) {
+               const int32_t c = P.child_idx[ci];
+               by_rank[P.owner[c]] += finish[c];
+               longest = std::max(longest, by_rank[P.owner[c]]);
+            }
+         }
+         finish[s] = own[s] - 1.0 + longest;
+         if (P.parent[s] < 0) P.critical_flops = std::max(P.critical_flops, finish[s]);
+      }
+   }
+   std::stable_sort(P.cut_edges.begin(), P.cut_edges.end(), [&](int32_t a, int32_t b) {
+      return P.level[a] != P.level[b] ? P.level[a] < P.level[b] : a < b;
+   });
+}
+
 }  // namespace b200kkt
