@@ -166,6 +166,9 @@ def main():
     ap.add_argument("--workload", default=os.environ.get("B200KKT_WORKLOAD", "auto"), choices=sorted(WORKLOADS) + ["auto"],
                     help="auto = BASELINE configs[4] (128^3, needs ~150 GB of HBM), falling back to configs[3] (64^3) if it does not fit")
     ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--multi", default=os.environ.get("B200KKT_MULTI", "partition"), choices=["partition", "replicas"],
+                    help="N > 1: 'partition' = ONE system, elimination subtrees mapped to the GPUs, top fronts shared, NCCL over NVLink (strong "
+                         "scaling, BASELINE configs[4]); 'replicas' = one independent system per GPU (weak scaling)")
     args = ap.parse_args()
     rank = int(os.environ.get("RANK", "0"))
     local_rank = int(os.environ.get("LOCAL_RANK", "0"))
@@ -196,17 +199,19 @@ def main():
 
     import torch
     import torch.distributed as dist
-    from uno_b200 import KKTSolver, replicas
+    from uno_b200 import KKTSolver, partition, replicas
     if not torch.cuda.is_available():
         raise SystemExit("bench.py --impl b200 needs a CUDA device: the numeric phase has no CPU path")
     torch.cuda.set_device(local_rank)
     if world > 1:
         dist.init_process_group("nccl", device_id=torch.device("cuda", local_rank))
     fallback_note = None
+    parted = world > 1 and args.multi == "partition"
     while True:
         desc = WORKLOADS[args.workload][0]
-        kkt = WORKLOADS[args.workload][1](G, replicas.rank_seed(rank))   # one independent KKT system per rank (replicas)
-        solver = KKTSolver(device=local_rank)
+        # partition: every rank holds the same system (SPMD, like the reference's MUMPS over MPI); replicas: one system per rank
+        kkt = WORKLOADS[args.workload][1](G, 0 if parted else replicas.rank_seed(rank))
+        solver = partition.create_solver(dist, local_rank) if parted else KKTSolver(device=local_rank)
         t0 = time.perf_counter()
         ok = True
         try:
@@ -271,7 +276,8 @@ def main():
     clocks = sampler.stop()
     launches = solver.stats()["kernel_launches"] - launches0
     elapsed = replicas.max_over_ranks(e0.elapsed_time(e1) * 1e-3, dist, "cuda")
-    value = replicas.aggregate_throughput(args.steps, world, elapsed)
+    units = 1 if parted else world     # systems factorized per step by the whole job
+    value = replicas.aggregate_throughput(args.steps, units, elapsed)
 
     # end to end through the C ABI with host buffers
     step_host()
@@ -280,21 +286,32 @@ def main():
     for _ in range(args.steps):
         ine_h, berr_h = step_host()
     torch.cuda.synchronize()
-    e2e_value = replicas.aggregate_throughput(args.steps, world, replicas.max_over_ranks(time.perf_counter() - t0, dist, "cuda"))
+    e2e_value = replicas.aggregate_throughput(args.steps, units, replicas.max_over_ranks(time.perf_counter() - t0, dist, "cuda"))
     x_ok = bool(np.isfinite(h_x.numpy()).all())
 
+    def profile_k4():
+        # roofline of the dominant kernel (K4): one extra, un-graphed factorization with event pairs around its big-front launches
+        solver.set_option("use_graph", 0)
+        solver.set_option("profile_updates", 1)
+        solver.factorize_device(d_val.data_ptr())
+        sp_ = solver.stats()
+        solver.set_option("profile_updates", 0)
+        solver.set_option("use_graph", 1)
+        return sp_
+
+    part_info = None
+    if parted:
+        sp = profile_k4()        # a partitioned factorization is a collective: every rank runs it
+        part_info = partition.summarize(solver.plan(), solver.partition(), st0["flops_factor"])
+        part_info["comm_bytes_per_factorization_rank0"] = int(solver.stats()["comm_bytes_factor"])
+        part_info["comm_bytes_per_solve_sweep_rank0"] = int(solver.stats()["comm_bytes_sweep"])
     if rank != 0:
         if world > 1:
+            dist.barrier()
             dist.destroy_process_group()
         return 0
-
-    # roofline of the dominant kernel (K4): one extra, un-graphed factorization with event pairs around its big-front launches
-    solver.set_option("use_graph", 0)
-    solver.set_option("profile_updates", 1)
-    solver.factorize_device(d_val.data_ptr())
-    sp = solver.stats()
-    solver.set_option("profile_updates", 0)
-    solver.set_option("use_graph", 1)
+    if not parted:
+        sp = profile_k4()
     peak64 = fp64_dgemm_peak(torch)
     # DRAM traffic of the dominant kernel from the committed ncu --set full capture of one representative launch
     k4_traffic = {}
@@ -316,10 +333,14 @@ def main():
                                  "peak_gbs": hbm_peak, "peak_source": hbm_src}}
     line = {
         "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": args.steps, "warmup": max(args.warmup, 3),
-        "ms_per_step": 1e3 * elapsed / args.steps, "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f64", "data": "synthetic",
+        "ms_per_step": 1e3 * elapsed / args.steps, "higher_is_better": True, "scaling": "strong" if parted else "weak", "vs_baseline": None, "dtype": "f64", "data": "synthetic",
         "config": {"workload": f"{args.workload}: {desc}", "N": kkt.dim, "n": kkt.n, "m": kkt.m, "nnz": kkt.nnz, "fronts": st0["num_fronts"],
                    "max_front": st0["max_front"], "nnz_factor": st0["nnz_factor"], "factor_flops": st0["flops_factor"],
-                   "parallelism": "single GPU" if world == 1 else f"{world} independent replicas (one KKT system per GPU, no data-path collective)",
+                   "parallelism": "single GPU" if world == 1 else
+                   (f"ONE system over {world} GPUs: elimination subtrees mapped to the ranks, big top fronts factorized by all ranks together "
+                    f"(column chunks, panels broadcast), contribution blocks and boundary vectors over NCCL/NVLink" if parted else
+                    f"{world} independent replicas (one KKT system per GPU, no data-path collective)"),
+                   "partition": part_info,
                    "l2": f"front pool {st0['pool_doubles'] * 8 / 1e9:.1f} GB per step >> 126 MB L2 (inputs larger than L2, no explicit flush)",
                    "analysis_seconds_untimed": t_analyse, "ordering": "METIS_NodeND on the KKT-pair-compressed graph", "fallback": fallback_note},
         "clocks": clocks, "gpu_launches": int(launches),
@@ -336,6 +357,7 @@ def main():
             line["cpu_baseline"] = {"value": None, "unit": UNIT, "cores": os.cpu_count(), "kind": "port", "sample": f"failed: {exc}"}
     print(json.dumps(line))
     if world > 1:
+        dist.barrier()
         dist.destroy_process_group()
     return 0
 

@@ -77,11 +77,14 @@ int b200kkt_destroy(b200kkt_handle* h);
  * b200kkt_comm_init before b200kkt_analyse.  libnccl.so.2 is opened at run time by these two calls only. */
 int b200kkt_comm_unique_id(char id[128]);
 int b200kkt_comm_init(b200kkt_handle* h, int rank, int world, const char id[128]);
-/* The subtree map of the last analysis: owner[s] per front (length = number of fronts), the cut fronts (owner differs from
- * the parent's; at most number of fronts entries, *num_cut receives the count), factor flops per rank (length num_gpus).
- * Works on host-only handles; any pointer may be NULL. */
-int b200kkt_plan_partition(const b200kkt_handle* h, int32_t* owner, int64_t* num_cut, int32_t* cut_fronts, double* part_flops,
-                           double* critical_flops);
+/* The subtree map of the last analysis: owner[s] per front (length = number of fronts), shared[s] = 1 for the big fronts above
+ * the cut that all ranks factorize together (column chunks of the trailing matrix per rank, factored panels broadcast; owner[s]
+ * then names the rank that solves with it), the cut fronts (owner differs from the parent's; at most number of fronts entries,
+ * *num_cut receives the count), factor flops per rank (length num_gpus), flops on the critical path.
+ * Works on host-only handles; any pointer may be NULL.
+ * Options: "share_top_fronts" (1), "share_min_pivots" (1024), "share_min_flops" (5e10), "share_chunk_panels" (2). */
+int b200kkt_plan_partition(const b200kkt_handle* h, int32_t* owner, int8_t* shared, int64_t* num_cut, int32_t* cut_fronts,
+                           double* part_flops, double* critical_flops);
 
 /* Options (defaults need no user action).  Names: "ordering" (0 METIS, 1 natural),
  * "kkt_pairing", "relax_small", "relax_mid", "relax_big", "scaling_sweeps", "null_pivot_tol",

@@ -22,7 +22,8 @@ from uno_b200 import generators as G  # noqa: E402
 
 
 def main():
-    names = sys.argv[1:] or ["ocp3d:16", "bnd3d:20", "opf", "ocp3d:32"]
+    names = [a for a in sys.argv[1:] if "=" not in a] or ["ocp3d:16", "bnd3d:20", "opf", "ocp3d:32"]
+    options = {a.split("=")[0]: float(a.split("=")[1]) for a in sys.argv[1:] if "=" in a}   # e.g. share_min_pivots=512
     rank, world, local = int(os.environ["RANK"]), int(os.environ["WORLD_SIZE"]), int(os.environ["LOCAL_RANK"])
     torch.cuda.set_device(local)
     dist.init_process_group("nccl", device_id=torch.device("cuda", local))
@@ -37,7 +38,7 @@ def main():
             kkt = G.ocp_distributed(int(arg), 2, seed=0)
         else:
             kkt = G.opf_like(3000, 4050, 600, seed=0, delta_w=100.0)
-        multi = partition.create_solver(dist, local)
+        multi = partition.create_solver(dist, local, **options)
         multi.do_symbolic_analysis(kkt.dim, kkt.row, kkt.col, kkt.reg_size, kkt.n)
         st = multi.stats()
         times = []
@@ -75,7 +76,8 @@ def main():
                           "share": st["flops_own"] / st["flops_factor"], "critical_share": st["flops_critical"] / st["flops_factor"],
                           "factor_ms": 1e3 * stm["t_factor_last"], "solve_ms": 1e3 * stm["t_solve_last"], "factor_ms_1gpu": 1e3 * st1["t_factor_last"],
                           "solve_ms_1gpu": 1e3 * st1["t_solve_last"], "wall_ms": 1e3 * min(times), "comm_MB_factor": stm["comm_bytes_factor"] / 1e6,
-                          "owners": np.bincount(part["owner"], minlength=world).tolist()}), flush=True)
+                          "owners": np.bincount(part["owner"], minlength=world).tolist(), "shared_fronts": int(part["shared"].sum()),
+                          "speedup_factor": st1["t_factor_last"] / stm["t_factor_last"]}), flush=True)
         multi.close(); single.close()
     dist.barrier()
     dist.destroy_process_group()

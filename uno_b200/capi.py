@@ -81,7 +81,7 @@ def load_library():
     lib.b200kkt_debug_factor.argtypes = [H] + [C.c_void_p] * 5
     lib.b200kkt_comm_unique_id.argtypes = [C.c_void_p]
     lib.b200kkt_comm_init.argtypes = [H, C.c_int, C.c_int, C.c_void_p]
-    lib.b200kkt_plan_partition.argtypes = [H, C.c_void_p, P(C.c_int64), C.c_void_p, C.c_void_p, P(C.c_double)]
+    lib.b200kkt_plan_partition.argtypes = [H, C.c_void_p, C.c_void_p, P(C.c_int64), C.c_void_p, C.c_void_p, P(C.c_double)]
     for name in EXPORTED_SYMBOLS:
         if name != "b200kkt_last_error":
             getattr(lib, name).restype = C.c_int
@@ -168,12 +168,13 @@ class KKTSolver:
         """Subtree map of the last analysis: owner per front, cut fronts, factor flops per rank, critical-path flops."""
         nsn = self.plan()["num_fronts"]
         owner = np.empty(nsn, dtype=np.int32)
+        shared = np.empty(nsn, dtype=np.int8)
         cut = np.empty(nsn, dtype=np.int32)
         ncut = C.c_int64()
         parts = np.zeros(max(1, int(self.stats()["num_parts"])), dtype=np.float64)
         crit = C.c_double()
-        self._check(self._lib.b200kkt_plan_partition(self._h, _ptr(owner), C.byref(ncut), _ptr(cut), _ptr(parts), C.byref(crit)), "plan_partition")
-        return {"owner": owner, "cut_fronts": cut[:ncut.value].copy(), "part_flops": parts, "critical_flops": crit.value}
+        self._check(self._lib.b200kkt_plan_partition(self._h, _ptr(owner), _ptr(shared), C.byref(ncut), _ptr(cut), _ptr(parts), C.byref(crit)), "plan_partition")
+        return {"owner": owner, "shared": shared.astype(bool), "cut_fronts": cut[:ncut.value].copy(), "part_flops": parts, "critical_flops": crit.value}
 
     # -- reference interface -----------------------------------------------------------------
     def initialize_memory(self, number_variables, number_constraints, number_hessian_nonzeros, regularization_size):

@@ -13,7 +13,7 @@ namespace {
 
 struct UniqueId { char internal[COMM_ID_BYTES]; };
 using comm_t = void*;
-constexpr int kInt32 = 2, kFloat64 = 8, kSum = 0;
+constexpr int kInt8 = 0, kInt32 = 2, kFloat64 = 8, kSum = 0;
 
 struct Api {
    void* lib = nullptr;
@@ -26,6 +26,7 @@ struct Api {
    int (*Send)(const void*, size_t, int, int, comm_t, cudaStream_t) = nullptr;
    int (*Recv)(void*, size_t, int, int, comm_t, cudaStream_t) = nullptr;
    int (*AllReduce)(const void*, void*, size_t, int, int, comm_t, cudaStream_t) = nullptr;
+   int (*Broadcast)(const void*, void*, size_t, int, int, comm_t, cudaStream_t) = nullptr;
    std::string load_error;
 };
 
@@ -57,6 +58,7 @@ Api& api() {
       a.Send = reinterpret_cast<decltype(a.Send)>(sym("ncclSend"));
       a.Recv = reinterpret_cast<decltype(a.Recv)>(sym("ncclRecv"));
       a.AllReduce = reinterpret_cast<decltype(a.AllReduce)>(sym("ncclAllReduce"));
+      a.Broadcast = reinterpret_cast<decltype(a.Broadcast)>(sym("ncclBroadcast"));
       if (!ok) { dlclose(a.lib); a.lib = nullptr; }
    });
    return a;
@@ -112,6 +114,12 @@ int comm_send_f64(const Comm& c, const double* p, size_t count, int peer, cudaSt
 
 int comm_recv_f64(const Comm& c, double* p, size_t count, int peer, cudaStream_t st, std::string& err) {
    return check(api().Recv(p, count, kFloat64, peer, c.nccl, st), "ncclRecv", err);
+}
+
+int comm_bcast_bytes(const Comm& c, void* p, size_t bytes, int root, cudaStream_t st, std::string& err) {
+   // whole doubles where possible: NCCL moves the same bytes either way, the count stays small
+   if (bytes % 8 == 0) return check(api().Broadcast(p, p, bytes / 8, kFloat64, root, c.nccl, st), "ncclBroadcast", err);
+   return check(api().Broadcast(p, p, bytes, kInt8, root, c.nccl, st), "ncclBroadcast", err);
 }
 
 int comm_allreduce_sum_f64(const Comm& c, double* p, size_t count, cudaStream_t st, std::string& err) {

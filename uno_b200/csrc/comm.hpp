@@ -32,6 +32,7 @@ int comm_group_start(std::string& err);
 int comm_group_end(std::string& err);
 int comm_send_f64(const Comm& c, const double* p, size_t count, int peer, cudaStream_t st, std::string& err);
 int comm_recv_f64(const Comm& c, double* p, size_t count, int peer, cudaStream_t st, std::string& err);
+int comm_bcast_bytes(const Comm& c, void* p, size_t bytes, int root, cudaStream_t st, std::string& err);   // in place
 int comm_allreduce_sum_f64(const Comm& c, double* p, size_t count, cudaStream_t st, std::string& err);
 int comm_allreduce_sum_i32(const Comm& c, int* p, size_t count, cudaStream_t st, std::string& err);
 

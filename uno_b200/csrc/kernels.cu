@@ -1229,6 +1229,7 @@ __global__ void __launch_bounds__(WARPS_M* WARPS_N * 32, MINB) k_update(FrontArr
          if (R.chi >= 0) c1 = min(f, J1 + R.chi * NBO);
          if (R.clip_to_pivots) c1 = min(c1, k);
       }
+      if (R.abs_hi > 0) { c0 = max(c0, R.abs_lo); c1 = min(c1, R.abs_hi); }
    }
    if (c0 >= c1 || r0 >= f || K <= 0) return;
    const int m0 = (r0 & ~1) + blockIdx.y * BM;
@@ -1585,9 +1586,10 @@ __global__ void __maxnreg__(200) k_update_ws(FrontArrays F, const int* __restric
 // ------------------------------------------------------------------------------------------------
 // K6 inertia from the D blocks
 // ------------------------------------------------------------------------------------------------
-__global__ void k_inertia(int64_t n, FactorArrays W, int* counters) {
+__global__ void k_inertia(int64_t n, FactorArrays W, int* counters, const signed char* __restrict__ col_owner, const int rank) {
    int pos = 0, neg = 0, zero = 0, two = 0;
    for (int64_t q = blockIdx.x * static_cast<int64_t>(blockDim.x) + threadIdx.x; q < n; q += static_cast<int64_t>(gridDim.x) * blockDim.x) {
+      if (col_owner != nullptr && col_owner[q] != rank) continue;
       const int ty = W.ptype[q];
       if (ty == 0) {
          if (W.dd[q] > 0.0) ++pos; else ++neg;
@@ -2339,7 +2341,8 @@ int launch_update(const FrontArrays& F, const int* d_list, int nfronts, int max_
    const int rows = max_f - (r0 & ~1);
    if (rows <= 0) return 0;
    // columns: a later part starts clo panels in; the first part may have to cover a whole trailing matrix (last-panel fronts)
-   const int cols = (mode == 0) ? NBO : ((R.policy == 1 || R.chi < 0) ? rows - R.clo * NBO : std::min(rows - R.clo * NBO, (R.chi - R.clo) * NBO + 2));
+   int cols = (mode == 0) ? NBO : ((R.policy == 1 || R.chi < 0) ? rows - R.clo * NBO : std::min(rows - R.clo * NBO, (R.chi - R.clo) * NBO + 2));
+   if (mode == 1 && R.abs_hi > 0) cols = std::min(cols, R.abs_hi - std::max(R.abs_lo, r0 & ~1) + 2);
    if (cols <= 0) return 0;
    if (tile_mode == 6) {
       dim3 grid(nfronts, (rows + 127) / 128, (cols + 63) / 64);
@@ -2366,10 +2369,10 @@ int launch_update(const FrontArrays& F, const int* d_list, int nfronts, int max_
    return 1;
 }
 
-int launch_inertia(int64_t n, const FactorArrays& W, int* counters, cudaStream_t st) {
+int launch_inertia(int64_t n, const FactorArrays& W, int* counters, cudaStream_t st, const signed char* col_owner, int rank) {
    int blocks = grid1d(n, 256);
    if (blocks > 1184) blocks = 1184;
-   k_inertia<<<blocks, 256, 0, st>>>(n, W, counters);
+   k_inertia<<<blocks, 256, 0, st>>>(n, W, counters, col_owner, rank);
    return 1;
 }
 

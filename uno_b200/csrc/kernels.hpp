@@ -90,6 +90,9 @@ struct UpdateRange {
    const double* wpool2 = nullptr;
    int policy = 0;
    int clip_to_pivots = 0;   // 1: the column range ends at the front's last pivot column (only factor-panel columns)
+   // abs_hi > 0: additionally only columns [abs_lo, abs_hi) of the front (absolute front columns, multiples of NBO) - the column
+   // chunks one rank owns when a front is shared by several GPUs
+   int abs_lo = 0, abs_hi = 0;
 };
 int launch_update(const FrontArrays& F, const int* d_list, int nfronts, int max_f, int mode, int j0, int J0, const FactorArrays& W,
                   int tile_mode, cudaStream_t st, const UpdateRange& R = UpdateRange());
@@ -101,7 +104,8 @@ int debug_phase_cycles(unsigned long long* out16, bool reset);
 // micro-benchmark of the 32 x 32 Bunch-Kaufman block kernel: cycles per block (variant 0 dominant diagonal, 1 KKT-like, 2 random)
 int debug_bench_bk(int variant, int reps, long long* cycles_out, int* n2x2);
 // K6 inertia from the D blocks: counters[0..4] = positive, negative, zero, number of 2x2, unused
-int launch_inertia(int64_t n, const FactorArrays& W, int* counters, cudaStream_t st);
+// col_owner != nullptr (subtree partition): only pivot positions of fronts this rank owns are counted
+int launch_inertia(int64_t n, const FactorArrays& W, int* counters, cudaStream_t st, const signed char* col_owner = nullptr, int rank = 0);
 
 // K7 solves, one level at a time.  Small fronts: one CTA per front.
 int launch_forward_level(const FrontArrays& F, const int* d_list, int nfronts, const FactorArrays& W, double* zg, double* z2,

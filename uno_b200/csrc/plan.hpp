@@ -83,6 +83,12 @@ struct Plan {
    // partial sums (forward solve) and its boundary solution (backward solve) cross NVLink there and nowhere else.
    int32_t num_parts = 1;
    std::vector<int32_t> owner;       // nsn
+   // shared[s] = 1: a big front above the cut, factorized by ALL ranks together: every rank holds the whole front, owns a
+   // cyclic set of column chunks of its trailing matrix and factors the outer panels inside its chunks; each factored panel
+   // is broadcast.  owner[s] of a shared front is the rank that counts its inertia and runs its triangular solves.
+   std::vector<char> shared;         // nsn
+   int64_t share_min_pivots = 1024;  // a front above the cut is shared when it has at least this many pivots ...
+   double share_min_flops = 5e10;    // ... and this much work
    std::vector<int32_t> cut_edges;   // fronts s with owner[s] != owner[parent[s]], ascending (level[s], s)
    std::vector<double> part_flops;   // factor flops per rank
    double critical_flops = 0.0;      // factor flops on the longest chain of dependent work (subtree + top fronts above it)
@@ -97,6 +103,6 @@ void analyse(int64_t N, int64_t nnz, int64_t reg_size, int64_t num_primal,
 // Proportional mapping of the assembly tree onto `parts` ranks: the tree is opened from the roots (heaviest subtree first)
 // until the open subtrees can be packed evenly, the subtrees are packed by decreasing flop count (LPT), and every front above
 // the cut goes to the owner of its heaviest child.  Deterministic: every rank computes the same map from the same plan.
-void map_subtrees(Plan& plan, int parts);
+void map_subtrees(Plan& plan, int parts, bool share_top_fronts = true);
 
 }  // namespace b200kkt

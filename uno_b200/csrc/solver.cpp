@@ -106,8 +106,9 @@ void build_batches(b200kkt_handle* h, std::vector<int>& batch_list, std::vector<
    for (int l = 0; l < P.nlevels; ++l) {
       ids.clear();
       for (int t = P.level_ptr[l]; t < P.level_ptr[l + 1]; ++t)
-         if (P.owner[P.level_fronts[t]] == h->rank) ids.push_back(P.level_fronts[t]);   // subtree partition: this rank's fronts only
+         if (P.owner[P.level_fronts[t]] == h->rank || P.shared[P.level_fronts[t]]) ids.push_back(P.level_fronts[t]);   // subtree partition: this rank's fronts and the shared ones
       std::stable_sort(ids.begin(), ids.end(), [&](int a, int b) {
+         if (P.shared[a] != P.shared[b]) return P.shared[a] > P.shared[b];   // shared batches first, the same on every rank
          const int ca = size_class(P.f[a]), cb = size_class(P.f[b]);
          if (ca != cb) return ca > cb;
          if (P.k[a] != P.k[b]) return P.k[a] > P.k[b];
@@ -120,7 +121,8 @@ void build_batches(b200kkt_handle* h, std::vector<int>& batch_list, std::vector<
          b.level = l;
          b.begin = static_cast<int>(batch_list.size());
          const int cls = size_class(P.f[ids[i]]);
-         while (i < ids.size() && size_class(P.f[ids[i]]) == cls) {
+         b.shared = P.shared[ids[i]] != 0;
+         while (i < ids.size() && size_class(P.f[ids[i]]) == cls && (P.shared[ids[i]] != 0) == b.shared) {
             const int s = ids[i];
             batch_list.push_back(s);
             b.k.push_back(P.k[s]);
@@ -172,15 +174,33 @@ void build_cut_schedule(b200kkt_handle* h) {
       const int p = P.parent[s];
       if (P.owner[s] != h->rank && P.owner[p] != h->rank) continue;
       h->cut_levels[P.level[s]].fronts.push_back(s);
-      h->comm_bytes_factor += 8 * cb_doubles(P, s);
       h->comm_bytes_solve += 2 * 8 * static_cast<int64_t>(P.f[s] - P.k[s]);
-      if (P.owner[p] == h->rank) h->wait_level[P.level[p]] = std::max(h->wait_level[P.level[p]], P.level[s]);
+   }
+   // factorization: a front below a shared parent is needed by every rank (broadcast by its owner); below a parent owned by
+   // another rank it goes there alone; a shared front spreads its own contribution block when it is done (enqueue_shared_batch)
+   for (int32_t l = 0; l < P.nlevels; ++l) {
+      for (int32_t t = P.level_ptr[l]; t < P.level_ptr[l + 1]; ++t) {
+         const int s = P.level_fronts[t];
+         const int p = P.parent[s];
+         if (p < 0 || P.shared[s] || P.f[s] == P.k[s]) continue;
+         if (P.shared[p]) {
+            h->cut_levels[l].factor_bcast.push_back(s);
+            h->comm_bytes_factor += 8 * cb_doubles(P, s);
+            if (P.owner[s] != h->rank) h->wait_level[P.level[p]] = std::max(h->wait_level[P.level[p]], l);
+         } else if (P.owner[s] != P.owner[p] && (P.owner[s] == h->rank || P.owner[p] == h->rank)) {
+            h->cut_levels[l].factor_p2p.push_back(s);
+            h->comm_bytes_factor += 8 * cb_doubles(P, s);
+            if (P.owner[p] == h->rank) h->wait_level[P.level[p]] = std::max(h->wait_level[P.level[p]], l);
+         }
+      }
+      std::sort(h->cut_levels[l].factor_p2p.begin(), h->cut_levels[l].factor_p2p.end());
+      std::sort(h->cut_levels[l].factor_bcast.begin(), h->cut_levels[l].factor_bcast.end());
    }
    std::vector<int> cut_list;
    for (int l = 0; l < P.nlevels; ++l) {
       b200kkt_handle::CutLevel& CL = h->cut_levels[l];
+      if (!CL.factor_p2p.empty() || !CL.factor_bcast.empty()) CK(cudaEventCreateWithFlags(&h->ev_comm[l], cudaEventDisableTiming));
       if (CL.fronts.empty()) continue;
-      CK(cudaEventCreateWithFlags(&h->ev_comm[l], cudaEventDisableTiming));
       CL.out_begin = static_cast<int>(cut_list.size());
       for (const int s : CL.fronts) if (P.owner[s] == h->rank) cut_list.push_back(s);
       CL.out_count = static_cast<int>(cut_list.size()) - CL.out_begin;
@@ -195,14 +215,16 @@ void build_cut_schedule(b200kkt_handle* h) {
    h->d_col_owner = dev_upload(h, col_owner);
 }
 
-// NCCL group with the transfers of the cut fronts of tree level l: `what` 0 = contribution blocks child -> parent (factorization),
-// 1 = boundary partial sums child -> parent (forward solve), 2 = boundary solution parent -> child (backward solve)
+// NCCL group with the transfers of the cut fronts of tree level l: `what` 0 = contribution blocks child -> parent (factorization;
+// to every rank when the parent is a shared front), 1 = boundary partial sums child -> parent (forward solve), 2 = boundary
+// solution parent -> child (backward solve)
 void enqueue_cut_transfers(b200kkt_handle* h, int l, int what, double* pool, cudaStream_t st) {
    const Plan& P = h->plan;
    const b200kkt_handle::CutLevel& CL = h->cut_levels[l];
-   if (CL.fronts.empty()) return;
+   const std::vector<int>& list = what == 0 ? CL.factor_p2p : CL.fronts;
+   if (list.empty() && (what != 0 || CL.factor_bcast.empty())) return;
    CKN(comm_group_start(e__));
-   for (const int s : CL.fronts) {
+   for (const int s : list) {
       const bool mine = P.owner[s] == h->rank;
       const int peer = mine ? P.owner[P.parent[s]] : P.owner[s];
       const int64_t count = what == 0 ? cb_doubles(P, s) : static_cast<int64_t>(P.f[s] - P.k[s]);
@@ -212,7 +234,121 @@ void enqueue_cut_transfers(b200kkt_handle* h, int l, int what, double* pool, cud
       if (send) CKN(comm_send_f64(h->comm, ptr, static_cast<size_t>(count), peer, st, e__));
       else CKN(comm_recv_f64(h->comm, ptr, static_cast<size_t>(count), peer, st, e__));
    }
+   if (what == 0)
+      for (const int s : CL.factor_bcast)
+         CKN(comm_bcast_bytes(h->comm, pool + P.cb_off[s], static_cast<size_t>(cb_doubles(P, s)) * sizeof(double), P.owner[s], st, e__));
    CKN(comm_group_end(e__));
+}
+
+// K2-K4 of a batch of SHARED fronts (subtree partition; every rank runs this with the same batch).  The trailing matrix of a
+// front is cut into column chunks of share_chunk_panels outer panels, chunk c belongs to rank c mod num_gpus.  A rank updates only
+// its chunks; the rank that owns the chunk of outer panel p factors that panel and broadcasts it (L columns, W panel, inverted
+// diagonal blocks, D, pivot types and orders) over NVLink, one panel ahead of the updates that need it, so the transfer and the
+// latency-bound panel chain hide behind the FP64 tensor-core work of the other ranks.  At the end the contribution block is put
+// together on every rank (each chunk broadcast by its owner): the parent front, shared too, assembles it everywhere.
+void enqueue_shared_batch(b200kkt_handle* h, const Batch& b, const int* list, cudaStream_t st) {
+   const Plan& P = h->plan;
+   int64_t& L = h->launches;
+   const int G = h->num_gpus, me = h->rank, CH = std::max(1, h->share_chunk_panels);
+   cudaStream_t pst = h->panel_stream[0], cs = h->comm_stream;
+   FactorArrays Wbuf[2] = {h->W, h->W};
+   Wbuf[1].wpool += h->wpool_size;
+   const int npan = (b.max_k + NBO - 1) / NBO;
+   const int nchunks = (b.max_f + CH * NBO - 1) / (CH * NBO);
+   auto panel_owner = [&](int p) { return (p / CH) % G; };
+   auto chain = [&](int p, cudaStream_t s_) {
+      const int J0 = p * NBO, nf = b.count_k_greater(J0);
+      L += launch_diagpanel(h->F, list, nf, b.max_k, J0, Wbuf[p & 1], h->null_pivot_tol, s_);
+      L += launch_trsmpanel(h->F, list, nf, b.pmaxf[nf - 1], b.max_k, J0, Wbuf[p & 1], s_);
+   };
+   auto bcast_panel = [&](int p) {
+      const int J0 = p * NBO, nf = b.count_k_greater(J0), root = panel_owner(p);
+      CKN(comm_group_start(e__));
+      for (int t = 0; t < nf; ++t) {
+         const int s = h->batch_fronts_host[b.begin + t];
+         const size_t kc = static_cast<size_t>(std::min(NBO, P.k[s] - J0)), ld = static_cast<size_t>(P.ld[s]);
+         const int64_t q = P.sn_first[s] + J0;
+         CKN(comm_bcast_bytes(h->comm, h->W.lpool + P.front_off[s] + static_cast<int64_t>(ld) * J0, ld * kc * sizeof(double), root, cs, e__));
+         CKN(comm_bcast_bytes(h->comm, Wbuf[p & 1].wpool + h->woff_host[s], ld * kc * sizeof(double), root, cs, e__));
+         if (h->xoff_host[s] >= 0)
+            CKN(comm_bcast_bytes(h->comm, h->W.xinv + h->xoff_host[s] + static_cast<int64_t>(J0 / NBI) * XINV_BLOCK_DOUBLES,
+                                 ((kc + NBI - 1) / NBI) * XINV_BLOCK_DOUBLES * sizeof(double), root, cs, e__));
+         CKN(comm_bcast_bytes(h->comm, h->W.dd + q, kc * sizeof(double), root, cs, e__));
+         CKN(comm_bcast_bytes(h->comm, h->W.de + q, kc * sizeof(double), root, cs, e__));
+         CKN(comm_bcast_bytes(h->comm, h->W.ptype + q, kc * sizeof(int), root, cs, e__));
+         CKN(comm_bcast_bytes(h->comm, h->W.lperm + q, kc * sizeof(int), root, cs, e__));
+         CKN(comm_bcast_bytes(h->comm, h->W.blkflag + q, kc * sizeof(int), root, cs, e__));
+      }
+      CKN(comm_group_end(e__));
+   };
+   auto update = [&](int p, int lo, int hi) {
+      if (lo >= hi || lo >= b.max_f) return;
+      const int J0 = p * NBO, nf = b.count_k_greater(J0);
+      UpdateRange R;
+      R.abs_lo = lo;
+      R.abs_hi = hi;
+      L += launch_update(h->F, list, nf, b.pmaxf[nf - 1], 1, 0, J0, Wbuf[p & 1], b.big_tiles, st, R);
+   };
+   auto link = [&](cudaEvent_t ev, cudaStream_t from, cudaStream_t to) {
+      CK(cudaEventRecord(ev, from));
+      CK(cudaStreamWaitEvent(to, ev, 0));
+   };
+   // panel 0
+   if (panel_owner(0) == me) chain(0, st);
+   link(h->ev_sh_main, st, cs);
+   bcast_panel(0);
+   link(h->ev_sh_comm, cs, st);
+   for (int p = 0; p < npan; ++p) {
+      const bool next = p + 1 < npan;
+      const bool next_mine = next && panel_owner(p + 1) == me;
+      if (next) {
+         if (next_mine) {
+            update(p, (p + 1) * NBO, (p + 2) * NBO);   // the next panel's own columns first ...
+            link(h->ev_sh_main, st, pst);
+            chain(p + 1, pst);                         // ... factored on the panel stream while the rest is updated here
+            link(h->ev_sh_panel, pst, cs);
+         } else {
+            link(h->ev_sh_main, st, cs);               // the W buffer of panel p + 1 is free: the updates of panel p - 1 are done
+         }
+         bcast_panel(p + 1);
+         CK(cudaEventRecord(h->ev_sh_comm, cs));
+      }
+      // a front whose last panel is p and whose pivot count is not a multiple of NBO has contribution-block columns inside
+      // panel p's own column range
+      bool stragglers = false;
+      for (const int kf : b.k) stragglers = stragglers || (kf > p * NBO && kf < (p + 1) * NBO);
+      for (int c = p / CH; c < nchunks; ++c) {
+         if (c % G != me) continue;
+         const int lo = std::max(c * CH, p) * NBO, hi = (c + 1) * CH * NBO;   // the kernel starts at the end of the K range
+         if (next_mine && lo <= (p + 1) * NBO && (p + 2) * NBO <= hi) {
+            if (stragglers) update(p, lo, (p + 1) * NBO);
+            update(p, (p + 2) * NBO, hi);
+         } else if (lo >= (p + 1) * NBO || stragglers || hi > (p + 1) * NBO) {
+            update(p, lo, hi);
+         }
+      }
+      if (next) CK(cudaStreamWaitEvent(st, h->ev_sh_comm, 0));
+   }
+   L += launch_permute_rows(h->F, list, b.count_k_greater(NBO), b.max_k, h->W, st);
+   // contribution blocks: every chunk to every rank
+   if (b.has_cb) {
+      link(h->ev_sh_main, st, cs);
+      CKN(comm_group_start(e__));
+      for (int t = 0; t < b.count; ++t) {
+         const int s = h->batch_fronts_host[b.begin + t];
+         const int64_t k = P.k[s], r = P.f[s] - k;
+         if (r <= 0) continue;
+         auto col_start = [&](int64_t j) { return j * r - (j * (j - 1)) / 2; };   // packed lower triangle: first entry of column j
+         for (int c = static_cast<int>(k / (CH * NBO)); c < nchunks; ++c) {
+            const int64_t a = std::max<int64_t>(static_cast<int64_t>(c) * CH * NBO - k, 0), e = std::min<int64_t>(static_cast<int64_t>(c + 1) * CH * NBO - k, r);
+            if (a >= e) continue;
+            CKN(comm_bcast_bytes(h->comm, h->W.cbpool + P.cb_off[s] + col_start(a), static_cast<size_t>(col_start(e) - col_start(a)) * sizeof(double),
+                                 c % G, cs, e__));
+         }
+      }
+      CKN(comm_group_end(e__));
+      link(h->ev_sh_comm, cs, st);
+   }
 }
 
 void upload_plan(b200kkt_handle* h) {
@@ -242,6 +378,8 @@ void upload_plan(b200kkt_handle* h) {
    h->F.child_idx = dev_upload(h, P.child_idx);
    h->F.woff = dev_upload(h, woff);
    h->F.xoff = dev_upload(h, xoff);
+   h->woff_host = woff;
+   h->xoff_host = xoff;
    h->d_perm = dev_upload(h, P.perm);
    h->d_batch_list = dev_upload(h, batch_list);
    h->batch_fronts_host = batch_list;
@@ -357,8 +495,7 @@ void enqueue_factor(b200kkt_handle* h) {
    L += launch_matrix_inf_norm(h->C, h->d_values, h->d_norms + 0, st);
    // K1 assembly into the zeroed factor pool
    CK(cudaMemsetAsync(h->W.lpool, 0, static_cast<size_t>(P.pool_size) * sizeof(double), st));
-   // subtree partition: pivot positions of other ranks' fronts carry no pivot type here (K6 skips them)
-   if (h->partitioned()) CK(cudaMemsetAsync(h->W.ptype, 0xFF, static_cast<size_t>(P.N) * sizeof(int), st));
+
    const bool prof = h->profile_updates != 0 && !h->use_graph;
    auto prof_begin = [&](double flops, int kind) {
       b200kkt_handle::ProfiledLaunch p{nullptr, nullptr, flops, kind};
@@ -378,7 +515,8 @@ void enqueue_factor(b200kkt_handle* h) {
       // contribution blocks of cut fronts that a front of this level assembles: wait until they have arrived
       if (h->partitioned() && h->wait_level[l] >= 0) CK(cudaStreamWaitEvent(h->stream, h->ev_comm[h->wait_level[l]], 0));
       const int nb = h->level_batch_ptr[l + 1] - h->level_batch_ptr[l];
-      const int nside = multi ? std::min(nb - 1, static_cast<int>(b200kkt_handle::NUM_AUX)) : 0;
+      const bool level_shared = nb > 0 && h->batches[h->level_batch_ptr[l]].shared;   // shared batches come first; they own the streams
+      const int nside = (multi && !level_shared) ? std::min(nb - 1, static_cast<int>(b200kkt_handle::NUM_AUX)) : 0;
       if (nside > 0) {
          CK(cudaEventRecord(h->ev_fork, h->stream));
          for (int a = 0; a < nside; ++a) CK(cudaStreamWaitEvent(h->aux[a], h->ev_fork, 0));
@@ -392,6 +530,10 @@ void enqueue_factor(b200kkt_handle* h) {
          // W panels: panel p of a front lives in buffer p & 3 (two panels of a pair + the pair factored ahead)
          FactorArrays Wbuf[4] = {h->W, h->W, h->W, h->W};
          for (int t = 1; t < 4; ++t) Wbuf[t].wpool += t * h->wpool_size;
+         if (b.shared) {
+            enqueue_shared_batch(h, b, list, st);
+            continue;
+         }
          const bool ahead = h->lookahead != 0 && !prof && b.max_k > NBO && b.max_f >= 2048;
          cudaStream_t pst = h->panel_stream[lane];
          const bool prof_this = prof && b.max_f >= 1024;
@@ -488,7 +630,7 @@ void enqueue_factor(b200kkt_handle* h) {
       }
       // K9: the cut fronts of this level hand their contribution blocks to the parent's rank over NVLink, on the
       // communication stream, while this rank goes on with its next levels
-      if (h->partitioned() && !h->cut_levels[l].fronts.empty()) {
+      if (h->partitioned() && h->ev_comm[l] != nullptr) {
          CK(cudaEventRecord(h->ev_level_done, h->stream));
          CK(cudaStreamWaitEvent(h->comm_stream, h->ev_level_done, 0));
          enqueue_cut_transfers(h, l, 0, h->W.cbpool, h->comm_stream);
@@ -502,7 +644,7 @@ void enqueue_factor(b200kkt_handle* h) {
    }
    // K6 inertia (partitioned: this rank's pivots, then summed over ranks)
    CK(cudaMemsetAsync(h->d_counters, 0, 8 * sizeof(int), st));
-   L += launch_inertia(P.N, h->W, h->d_counters, st);
+   L += launch_inertia(P.N, h->W, h->d_counters, st, h->partitioned() ? h->d_col_owner : nullptr, h->rank);
    if (h->partitioned()) CKN(comm_allreduce_sum_i32(h->comm, h->d_counters, 8, st, e__));
    CK(cudaMemcpyAsync(h->h_counters, h->d_counters, 8 * sizeof(int), cudaMemcpyDeviceToHost, st));
 }
@@ -763,6 +905,9 @@ int b200kkt_create(b200kkt_handle** out, int device, int num_gpus) {
          if (h->num_gpus > 1) {
             CK(cudaStreamCreateWithPriority(&h->comm_stream, cudaStreamNonBlocking, prio_greatest));
             CK(cudaEventCreateWithFlags(&h->ev_level_done, cudaEventDisableTiming));
+            CK(cudaEventCreateWithFlags(&h->ev_sh_main, cudaEventDisableTiming));
+            CK(cudaEventCreateWithFlags(&h->ev_sh_panel, cudaEventDisableTiming));
+            CK(cudaEventCreateWithFlags(&h->ev_sh_comm, cudaEventDisableTiming));
          }
          CK(cudaMallocHost(reinterpret_cast<void**>(&h->h_counters), 8 * sizeof(int)));
          CK(cudaMallocHost(reinterpret_cast<void**>(&h->h_norms), 4 * sizeof(unsigned long long)));
@@ -790,6 +935,7 @@ int b200kkt_destroy(b200kkt_handle* h) {
       b200kkt::comm_destroy(h->comm);
       if (h->comm_stream != nullptr) cudaStreamDestroy(h->comm_stream);
       if (h->ev_level_done != nullptr) cudaEventDestroy(h->ev_level_done);
+      for (cudaEvent_t e : {h->ev_sh_main, h->ev_sh_panel, h->ev_sh_comm}) if (e != nullptr) cudaEventDestroy(e);
       if (h->h_counters != nullptr) cudaFreeHost(h->h_counters);
       if (h->h_norms != nullptr) cudaFreeHost(h->h_norms);
       if (h->ev0 != nullptr) cudaEventDestroy(h->ev0);
@@ -829,12 +975,13 @@ int b200kkt_comm_init(b200kkt_handle* h, int rank, int world, const char id[128]
    });
 }
 
-int b200kkt_plan_partition(const b200kkt_handle* h, int32_t* owner, int64_t* num_cut, int32_t* cut_fronts, double* part_flops,
+int b200kkt_plan_partition(const b200kkt_handle* h, int32_t* owner, int8_t* shared, int64_t* num_cut, int32_t* cut_fronts, double* part_flops,
                            double* critical_flops) {
    if (h == nullptr) return B200KKT_EINVAL;
    if (!h->analysed) return fail(h, B200KKT_EINVAL, "plan getter before analyse");
    const Plan& P = h->plan;
    if (owner != nullptr) std::copy(P.owner.begin(), P.owner.end(), owner);
+   if (shared != nullptr) std::copy(P.shared.begin(), P.shared.end(), shared);
    if (num_cut != nullptr) *num_cut = static_cast<int64_t>(P.cut_edges.size());
    if (cut_fronts != nullptr) std::copy(P.cut_edges.begin(), P.cut_edges.end(), cut_fronts);
    if (part_flops != nullptr) std::copy(P.part_flops.begin(), P.part_flops.end(), part_flops);
@@ -870,6 +1017,10 @@ int b200kkt_set_option(b200kkt_handle* h, const char* name, double value) {
    else if (n == "lookahead") h->lookahead = static_cast<int>(value);
    else if (n == "pair_panels") h->pair_panels = static_cast<int>(value);
    else if (n == "pair_min_front") h->pair_min_front = static_cast<int>(value);
+   else if (n == "share_top_fronts") h->share_top_fronts = static_cast<int>(value);
+   else if (n == "share_chunk_panels") h->share_chunk_panels = std::max(1, static_cast<int>(value));
+   else if (n == "share_min_pivots") h->share_min_pivots = std::max(2 * NBO, static_cast<int>(value));
+   else if (n == "share_min_flops") h->share_min_flops = value;
    else if (n == "debug_skip") h->debug_skip = static_cast<int>(value);   // timing experiments only: 1 no K4, 2 no panel kernels, 4 no K5
    else return fail(h, B200KKT_EINVAL, "unknown option: " + n);
    // numeric options are baked into the captured graphs
@@ -901,7 +1052,9 @@ int b200kkt_analyse(b200kkt_handle* h, uint64_t n, uint64_t nnz, uint64_t reg_si
       }
       analyse(static_cast<int64_t>(n), static_cast<int64_t>(nnz), static_cast<int64_t>(reg_size), static_cast<int64_t>(num_primal), row, col,
               opt, h->plan);
-      map_subtrees(h->plan, h->num_gpus);
+      h->plan.share_min_pivots = h->share_min_pivots;
+      h->plan.share_min_flops = h->share_min_flops;
+      map_subtrees(h->plan, h->num_gpus, h->share_top_fronts != 0);
       fill_plan_stats(h);
       if (h->has_device) upload_plan(h);
       h->analysed = true;

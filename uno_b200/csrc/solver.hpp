@@ -23,6 +23,7 @@ struct Batch {
    int max_f = 0, max_k = 0;
    bool has_children = false;
    bool has_cb = false;
+   bool shared = false;   // fronts factorized by all ranks together (subtree partition, fronts above the cut)
    int big_tiles = 0;   // K4 tile mode (see launch_update)
    std::vector<int> k;            // per front of the batch (descending)
    std::vector<int> pmaxf;        // prefix maximum of f in batch order
@@ -120,7 +121,9 @@ struct b200kkt_handle {
    int rank = 0;
    bool partitioned() const { return num_gpus > 1; }
    struct CutLevel {                      // cut fronts of one tree level that touch this rank, ascending front index
-      std::vector<int> fronts;
+      std::vector<int> fronts;            // solve: point to point between owner(front) and owner(parent)
+      std::vector<int> factor_p2p;        // factorization: the subset whose parent is not a shared front
+      std::vector<int> factor_bcast;      // factorization: fronts below a shared parent, broadcast by their owner (every rank takes part)
       int out_begin = 0, out_count = 0;   // ranges in d_cut_list: fronts this rank owns (sends CB / boundary sums, receives x)
       int in_begin = 0, in_count = 0;     // fronts whose parent this rank owns
    };
@@ -129,6 +132,12 @@ struct b200kkt_handle {
    std::vector<cudaEvent_t> ev_comm;      // per level: transfers of that level's cut fronts done (null where there are none)
    cudaStream_t comm_stream = nullptr;
    cudaEvent_t ev_level_done = nullptr;
+   int share_top_fronts = 1;              // big fronts above the cut are factorized by all ranks together
+   int share_chunk_panels = 2;            // column chunk of a shared front, in outer panels; chunk c belongs to rank c mod num_gpus
+   int share_min_pivots = 1024;
+   double share_min_flops = 5e10;
+   cudaEvent_t ev_sh_main = nullptr, ev_sh_panel = nullptr, ev_sh_comm = nullptr;
+   std::vector<int64_t> woff_host, xoff_host;   // this rank's W-panel and inverted-block offsets per front
    int* d_cut_list = nullptr;
    signed char* d_col_owner = nullptr;
    int64_t comm_bytes_factor = 0, comm_bytes_solve = 0;   // per factorization / per sweep, sent + received by this rank

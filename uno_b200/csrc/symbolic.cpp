@@ -675,11 +675,12 @@ void analyse(int64_t N, int64_t nnz, int64_t reg_size, int64_t num_primal, const
 // Subtree-to-GPU mapping: independent elimination subtrees go to different ranks,
 // the separators above the cut to the owner of their heaviest child.
 // ------------------------------------------------------------------------------------------------
-void map_subtrees(Plan& P, int parts) {
+void map_subtrees(Plan& P, int parts, bool share_top_fronts) {
    const int32_t nsn = P.nsn;
    parts = std::max(1, parts);
    P.num_parts = parts;
    P.owner.assign(static_cast<size_t>(nsn), 0);
+   P.shared.assign(static_cast<size_t>(nsn), 0);
    P.cut_edges.clear();
    P.part_flops.assign(static_cast<size_t>(parts), 0.0);
    std::vector<double> own(static_cast<size_t>(nsn)), sub(static_cast<size_t>(nsn));
@@ -736,6 +737,9 @@ void map_subtrees(Plan& P, int parts) {
          }
          if (best >= 0) P.owner[s] = P.owner[best];
       }
+      if (share_top_fronts)
+         for (int32_t s = 0; s < nsn; ++s)
+            if (above[s] && P.k[s] >= P.share_min_pivots && own[s] >= P.share_min_flops) P.shared[s] = 1;
       // top-down (parents have higher numbers): everything not placed yet follows its parent
       for (int32_t s = nsn - 1; s >= 0; --s) {
          if (P.owner[s] >= 0) continue;
@@ -748,7 +752,8 @@ void map_subtrees(Plan& P, int parts) {
    }
    // cut edges in the order every rank walks them, work per rank, critical path
    for (int32_t s = 0; s < nsn; ++s) {
-      P.part_flops[P.owner[s]] += own[s] - 1.0;
+      if (P.shared[s]) for (int p = 0; p < parts; ++p) P.part_flops[p] += (own[s] - 1.0) / parts;
+      else P.part_flops[P.owner[s]] += own[s] - 1.0;
       if (P.parent[s] >= 0 && P.owner[P.parent[s]] != P.owner[s]) P.cut_edges.push_back(s);
    }
    // critical path estimate: a front can start when all its children are done; children on the same rank run one after the
@@ -767,7 +772,7 @@ void map_subtrees(Plan& P, int parts) {
                longest = std::max(longest, by_rank[P.owner[c]]);
             }
          }
-         finish[s] = own[s] - 1.0 + longest;
+         finish[s] = (own[s] - 1.0) / (P.shared[s] ? parts : 1) + longest;
          if (P.parent[s] < 0) P.critical_flops = std::max(P.critical_flops, finish[s]);
       }
    }

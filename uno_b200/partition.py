@@ -55,7 +55,10 @@ def summarize(plan: dict, part: dict, total_flops: float) -> dict:
     f, k = plan["f"], plan["k"]
     cut = part["cut_fronts"]
     r = (f - k)[cut].astype(np.int64)
+    sh = np.flatnonzero(part["shared"])
     return {"parts": int(len(part["part_flops"])), "cut_fronts": int(len(cut)),
+            "shared_fronts": [(int(f[s]), int(k[s])) for s in sh],
+            "shared_flops_share": float(sum(float(k[s]) ** 3 / 3 + float(k[s]) ** 2 * float(f[s] - k[s]) + float(k[s]) * float(f[s] - k[s]) ** 2 for s in sh) / total_flops),
             "flops_share_per_rank": [float(x / total_flops) for x in part["part_flops"]],
             "critical_path_share": float(part["critical_flops"] / total_flops),
             "contribution_block_bytes_total": int((8 * r * (r + 1) // 2).sum())}
