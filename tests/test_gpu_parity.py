@@ -285,3 +285,23 @@ def test_schedule_and_kernel_variants_agree(options):
         assert all(np.array_equal(u, w) for u, w in zip(a, b))
         assert np.array_equal(x, xr)
     assert np.max(np.abs(x - xr)) <= X_TOL * np.max(np.abs(xr))
+
+
+@pytest.mark.gpu
+def test_partitioned_two_gpus_matches_single_gpu():
+    """the same system on two GPUs (subtrees mapped to the ranks, top fronts shared, NCCL over NVLink) gives the
+    inertia and, to rounding, the solution of the one-GPU run; both ranks return the same x bit for bit.  Needs two devices:
+    one process per GPU under torchrun (tests/gpu_partition.py does the comparison and exits non-zero on a mismatch)."""
+    import subprocess
+    import sys
+    import torch
+    if torch.cuda.device_count() < 2:
+        pytest.skip("needs two CUDA devices (run with gpurun --gpus 2)")
+    root = Path(__file__).resolve().parent.parent
+    cmd = [sys.executable, "-m", "torch.distributed.run", "--nnodes=1", "--nproc-per-node", "2", "--master-addr", "127.0.0.1", "--master-port", "29533",
+           str(root / "tests" / "gpu_partition.py"), "ocp3d:16", "bnd3d:20", "ocp3d:32", "share_min_pivots=512", "share_min_flops=1e9"]
+    r = subprocess.run(cmd, capture_output=True, text=True, timeout=600)
+    lines = [json.loads(l) for l in r.stdout.splitlines() if l.startswith("{")]
+    assert r.returncode == 0, r.stdout[-2000:] + r.stderr[-2000:]
+    assert len(lines) == 6 and all(l["ok"] for l in lines)
+    assert any(l["shared_fronts"] > 0 for l in lines)        # the shared-front path ran, not only the subtree exchange

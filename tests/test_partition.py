@@ -67,6 +67,36 @@ def test_subtree_map_invariants(lib, name, parts):
     h.close()
 
 
+def test_shared_top_fronts(lib):
+    """Big fronts above the cut are factorized by all ranks together: they sit above every cut front on the way to the root,
+    their work is split evenly in the per-rank figures, and switching the option off gives the plain subtree map."""
+    from uno_b200 import KKTSolver
+    from uno_b200 import generators as G
+    kkt = G.ocp_distributed(24, 3, seed=0)
+    h = KKTSolver(device=-1, num_gpus=2, share_min_pivots=512, share_min_flops=1e8)
+    h.do_symbolic_analysis(kkt.dim, kkt.row, kkt.col, kkt.reg_size, kkt.n)
+    plan, part, st = h.plan(), h.partition(), h.stats()
+    shared = np.flatnonzero(part["shared"])
+    assert len(shared) >= 1 and np.all(plan["k"][shared] >= 512)
+    below = np.zeros(plan["num_fronts"], dtype=bool)          # fronts with a cut front or a shared front at or below them
+    below[part["cut_fronts"]] = True
+    below[shared] = True
+    for s in range(plan["num_fronts"]):
+        p = plan["parent"][s]
+        if p >= 0 and below[s]:
+            below[p] = True
+    for s in shared:                                           # a shared front never sits inside one rank's private subtree
+        p = plan["parent"][s]
+        assert p < 0 or below[p]
+    assert abs(part["part_flops"].sum() - st["flops_factor"]) <= 1e-9 * st["flops_factor"]
+    h2 = KKTSolver(device=-1, num_gpus=2, share_top_fronts=0)
+    h2.do_symbolic_analysis(kkt.dim, kkt.row, kkt.col, kkt.reg_size, kkt.n)
+    part2 = h2.partition()
+    assert not part2["shared"].any() and np.array_equal(part2["owner"], part["owner"])
+    assert part["critical_flops"] < part2["critical_flops"]   # sharing the top shortens the critical path
+    h.close(); h2.close()
+
+
 def test_map_is_deterministic(lib):
     from uno_b200 import KKTSolver
     kkt = _systems()["ocp3d_12"]

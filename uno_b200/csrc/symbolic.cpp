@@ -775,6 +775,8 @@ void map_subtrees(Plan& P, int parts, bool share_top_fronts) {
          finish[s] = (own[s] - 1.0) / (P.shared[s] ? parts : 1) + longest;
          if (P.parent[s] < 0) P.critical_flops = std::max(P.critical_flops, finish[s]);
       }
+      // never shorter than the busiest rank's own load
+      for (const double w : P.part_flops) P.critical_flops = std::max(P.critical_flops, w);
    }
    std::stable_sort(P.cut_edges.begin(), P.cut_edges.end(), [&](int32_t a, int32_t b) {
       return P.level[a] != P.level[b] ? P.level[a] < P.level[b] : a < b;
