@@ -305,6 +305,10 @@ def main():
         part_info = partition.summarize(solver.plan(), solver.partition(), st0["flops_factor"])
         part_info["comm_bytes_per_factorization_rank0"] = int(solver.stats()["comm_bytes_factor"])
         part_info["comm_bytes_per_solve_sweep_rank0"] = int(solver.stats()["comm_bytes_sweep"])
+        # one profiled factorization (rank 0's main stream): time inside the shared-front batches, of which waiting for a panel
+        part_info["shared_phase"] = {"seconds": sp["t_shared_profiled"], "stall_seconds": sp["t_shared_stall_profiled"],
+                                     "aggregate_tflops": sp["flops_shared_profiled"] / max(sp["t_shared_profiled"], 1e-12) / 1e12,
+                                     "factor_seconds_profiled_run": sp["t_factor_last"]}
     if rank != 0:
         if world > 1:
             dist.barrier()

@@ -60,6 +60,9 @@ typedef struct b200kkt_stats {
    int64_t num_parts, part_rank, num_cut_fronts;
    double flops_own, flops_critical;
    int64_t comm_bytes_factor, comm_bytes_sweep;
+   /* option "profile_updates" on a multi-GPU handle: main-stream time inside the shared-front batches of the last factorization,
+    * their flops (whole fronts, all ranks), and the part of that time spent waiting for a factored panel to arrive */
+   double t_shared_profiled, flops_shared_profiled, t_shared_stall_profiled;
 } b200kkt_stats;
 
 /* Handle life cycle.  Replaces JOB=-1 / JOB=-2 (MUMPSSolver.cpp:16-49).

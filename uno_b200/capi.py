@@ -39,6 +39,7 @@ class Stats(C.Structure):
         ("num_parts", C.c_int64), ("part_rank", C.c_int64), ("num_cut_fronts", C.c_int64),
         ("flops_own", C.c_double), ("flops_critical", C.c_double),
         ("comm_bytes_factor", C.c_int64), ("comm_bytes_sweep", C.c_int64),
+        ("t_shared_profiled", C.c_double), ("flops_shared_profiled", C.c_double), ("t_shared_stall_profiled", C.c_double),
     ]
 
     def as_dict(self):

@@ -293,6 +293,25 @@ void enqueue_shared_batch(b200kkt_handle* h, const Batch& b, const int* list, cu
       CK(cudaEventRecord(ev, from));
       CK(cudaStreamWaitEvent(to, ev, 0));
    };
+   // option profile_updates: time of the whole batch (kind 2) and of the waits for a broadcast panel (kind 3) on the main stream
+   const bool prof = h->profile_updates != 0;
+   auto prof_begin = [&](double flops, int kind) {
+      if (!prof) return;
+      b200kkt_handle::ProfiledLaunch pl{nullptr, nullptr, flops, kind};
+      CK(cudaEventCreate(&pl.a));
+      CK(cudaEventCreate(&pl.b));
+      CK(cudaEventRecord(pl.a, st));
+      h->profiled.push_back(pl);
+   };
+   auto prof_end = [&](size_t idx) { if (prof) CK(cudaEventRecord(h->profiled[idx].b, st)); };
+   double batch_flops = 0.0;
+   for (int t = 0; t < b.count; ++t) {
+      const int s = h->batch_fronts_host[b.begin + t];
+      const double kd = P.k[s], rd = P.f[s] - P.k[s];
+      batch_flops += kd * kd * kd / 3.0 + kd * kd * rd + kd * rd * rd;
+   }
+   prof_begin(batch_flops, 2);
+   const size_t prof_batch = h->profiled.size() - 1;
    // panel 0
    if (panel_owner(0) == me) chain(0, st);
    link(h->ev_sh_main, st, cs);
@@ -305,13 +324,14 @@ void enqueue_shared_batch(b200kkt_handle* h, const Batch& b, const int* list, cu
          if (next_mine) {
             update(p, (p + 1) * NBO, (p + 2) * NBO);   // the next panel's own columns first ...
             link(h->ev_sh_main, st, pst);
+            CK(cudaStreamWaitEvent(pst, h->ev_sh_bcast[(p + 1) & 1], 0));   // the broadcast of panel p - 1 has left this W buffer
             chain(p + 1, pst);                         // ... factored on the panel stream while the rest is updated here
             link(h->ev_sh_panel, pst, cs);
          } else {
             link(h->ev_sh_main, st, cs);               // the W buffer of panel p + 1 is free: the updates of panel p - 1 are done
          }
          bcast_panel(p + 1);
-         CK(cudaEventRecord(h->ev_sh_comm, cs));
+         CK(cudaEventRecord(h->ev_sh_bcast[(p + 1) & 1], cs));
       }
       // a front whose last panel is p and whose pivot count is not a multiple of NBO has contribution-block columns inside
       // panel p's own column range
@@ -327,7 +347,13 @@ void enqueue_shared_batch(b200kkt_handle* h, const Batch& b, const int* list, cu
             update(p, lo, hi);
          }
       }
-      if (next) CK(cudaStreamWaitEvent(st, h->ev_sh_comm, 0));
+      // the next step needs panel p + 1: its owner has it as soon as its own panel chain is through (the broadcast goes on
+      // behind), the others when the broadcast has arrived
+      if (next) {
+         prof_begin(0.0, 3);
+         CK(cudaStreamWaitEvent(st, next_mine ? h->ev_sh_panel : h->ev_sh_bcast[(p + 1) & 1], 0));
+         prof_end(h->profiled.size() - 1);
+      }
    }
    L += launch_permute_rows(h->F, list, b.count_k_greater(NBO), b.max_k, h->W, st);
    // contribution blocks: every chunk to every rank
@@ -349,6 +375,7 @@ void enqueue_shared_batch(b200kkt_handle* h, const Batch& b, const int* list, cu
       CKN(comm_group_end(e__));
       link(h->ev_sh_comm, cs, st);
    }
+   prof_end(prof_batch);
 }
 
 void upload_plan(b200kkt_handle* h) {
@@ -694,18 +721,22 @@ void run_factor(b200kkt_handle* h) {
    CK(cudaEventElapsedTime(&ms, h->ev0, h->ev1));
    h->stats.t_factor_last = ms * 1e-3;
    if (!h->profiled.empty()) {
-      double tu = 0.0, fu = 0.0, ta = 0.0;
+      double tu = 0.0, fu = 0.0, ta = 0.0, tsh = 0.0, fsh = 0.0, tstall = 0.0;
       int64_t nu = 0;
       for (auto& p : h->profiled) {
          float pm = 0.f;
          cudaEventElapsedTime(&pm, p.a, p.b);
-         if (p.kind == 0) { tu += pm * 1e-3; fu += p.flops; ++nu; } else ta += pm * 1e-3;
+         if (p.kind == 0) { tu += pm * 1e-3; fu += p.flops; ++nu; }
+         else if (p.kind == 1) ta += pm * 1e-3;
+         else if (p.kind == 2) { tsh += pm * 1e-3; fsh += p.flops; }
+         else tstall += pm * 1e-3;
          cudaEventDestroy(p.a);
          cudaEventDestroy(p.b);
       }
       h->profiled.clear();
       h->stats.t_update_profiled = tu; h->stats.flops_update_profiled = fu; h->stats.n_update_profiled = nu;
       h->stats.t_assemble_profiled = ta;
+      h->stats.t_shared_profiled = tsh; h->stats.flops_shared_profiled = fsh; h->stats.t_shared_stall_profiled = tstall;
    }
    h->inertia[0] = static_cast<uint64_t>(h->h_counters[0]);
    h->inertia[1] = static_cast<uint64_t>(h->h_counters[1]);
@@ -908,6 +939,8 @@ int b200kkt_create(b200kkt_handle** out, int device, int num_gpus) {
             CK(cudaEventCreateWithFlags(&h->ev_sh_main, cudaEventDisableTiming));
             CK(cudaEventCreateWithFlags(&h->ev_sh_panel, cudaEventDisableTiming));
             CK(cudaEventCreateWithFlags(&h->ev_sh_comm, cudaEventDisableTiming));
+            CK(cudaEventCreateWithFlags(&h->ev_sh_bcast[0], cudaEventDisableTiming));
+            CK(cudaEventCreateWithFlags(&h->ev_sh_bcast[1], cudaEventDisableTiming));
          }
          CK(cudaMallocHost(reinterpret_cast<void**>(&h->h_counters), 8 * sizeof(int)));
          CK(cudaMallocHost(reinterpret_cast<void**>(&h->h_norms), 4 * sizeof(unsigned long long)));
@@ -935,7 +968,7 @@ int b200kkt_destroy(b200kkt_handle* h) {
       b200kkt::comm_destroy(h->comm);
       if (h->comm_stream != nullptr) cudaStreamDestroy(h->comm_stream);
       if (h->ev_level_done != nullptr) cudaEventDestroy(h->ev_level_done);
-      for (cudaEvent_t e : {h->ev_sh_main, h->ev_sh_panel, h->ev_sh_comm}) if (e != nullptr) cudaEventDestroy(e);
+      for (cudaEvent_t e : {h->ev_sh_main, h->ev_sh_panel, h->ev_sh_comm, h->ev_sh_bcast[0], h->ev_sh_bcast[1]}) if (e != nullptr) cudaEventDestroy(e);
       if (h->h_counters != nullptr) cudaFreeHost(h->h_counters);
       if (h->h_norms != nullptr) cudaFreeHost(h->h_norms);
       if (h->ev0 != nullptr) cudaEventDestroy(h->ev0);
