@@ -306,6 +306,12 @@ def main():
         part_info["comm_bytes_per_factorization_rank0"] = int(solver.stats()["comm_bytes_factor"])
         part_info["comm_bytes_per_solve_sweep_rank0"] = int(solver.stats()["comm_bytes_sweep"])
         # one profiled factorization (rank 0's main stream): time inside the shared-front batches, of which waiting for a panel
+        mine = {"rank": rank, "factor_s": sp["t_factor_last"], "before_shared_s": sp["t_before_shared_profiled"], "transfer_wait_s": sp["t_transfer_wait_profiled"],
+                "shared_s": sp["t_shared_profiled"], "panel_wait_s": sp["t_shared_stall_profiled"], "k4_local_s": sp["t_update_profiled"],
+                "k4_local_tflops": sp["flops_update_profiled"] / max(sp["t_update_profiled"], 1e-12) / 1e12}
+        per_rank = [None] * world
+        dist.all_gather_object(per_rank, mine)
+        part_info["profiled_factorization_per_rank"] = per_rank
         part_info["shared_phase"] = {"seconds": sp["t_shared_profiled"], "stall_seconds": sp["t_shared_stall_profiled"],
                                      "aggregate_tflops": sp["flops_shared_profiled"] / max(sp["t_shared_profiled"], 1e-12) / 1e12,
                                      "factor_seconds_profiled_run": sp["t_factor_last"]}

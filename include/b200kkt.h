@@ -63,6 +63,9 @@ typedef struct b200kkt_stats {
    /* option "profile_updates" on a multi-GPU handle: main-stream time inside the shared-front batches of the last factorization,
     * their flops (whole fronts, all ranks), and the part of that time spent waiting for a factored panel to arrive */
    double t_shared_profiled, flops_shared_profiled, t_shared_stall_profiled;
+   /* same option: time from the start of the factorization to the first shared batch (this rank's subtrees + transfers), and the
+    * part of the factorization the main stream spent waiting for contribution blocks from other ranks */
+   double t_before_shared_profiled, t_transfer_wait_profiled;
 } b200kkt_stats;
 
 /* Handle life cycle.  Replaces JOB=-1 / JOB=-2 (MUMPSSolver.cpp:16-49).

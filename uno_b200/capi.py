@@ -40,6 +40,7 @@ class Stats(C.Structure):
         ("flops_own", C.c_double), ("flops_critical", C.c_double),
         ("comm_bytes_factor", C.c_int64), ("comm_bytes_sweep", C.c_int64),
         ("t_shared_profiled", C.c_double), ("flops_shared_profiled", C.c_double), ("t_shared_stall_profiled", C.c_double),
+        ("t_before_shared_profiled", C.c_double), ("t_transfer_wait_profiled", C.c_double),
     ]
 
     def as_dict(self):

@@ -540,7 +540,11 @@ void enqueue_factor(b200kkt_handle* h) {
    const bool multi = h->multi_stream != 0 && !prof;
    for (int l = 0; l < P.nlevels; ++l) {
       // contribution blocks of cut fronts that a front of this level assembles: wait until they have arrived
-      if (h->partitioned() && h->wait_level[l] >= 0) CK(cudaStreamWaitEvent(h->stream, h->ev_comm[h->wait_level[l]], 0));
+      if (h->partitioned() && h->wait_level[l] >= 0) {
+         if (prof) prof_begin(0.0, 4);   // kind 4: main stream waiting for contribution blocks from other ranks
+         CK(cudaStreamWaitEvent(h->stream, h->ev_comm[h->wait_level[l]], 0));
+         if (prof) prof_end();
+      }
       const int nb = h->level_batch_ptr[l + 1] - h->level_batch_ptr[l];
       const bool level_shared = nb > 0 && h->batches[h->level_batch_ptr[l]].shared;   // shared batches come first; they own the streams
       const int nside = (multi && !level_shared) ? std::min(nb - 1, static_cast<int>(b200kkt_handle::NUM_AUX)) : 0;
@@ -721,21 +725,27 @@ void run_factor(b200kkt_handle* h) {
    CK(cudaEventElapsedTime(&ms, h->ev0, h->ev1));
    h->stats.t_factor_last = ms * 1e-3;
    if (!h->profiled.empty()) {
-      double tu = 0.0, fu = 0.0, ta = 0.0, tsh = 0.0, fsh = 0.0, tstall = 0.0;
+      double tu = 0.0, fu = 0.0, ta = 0.0, tsh = 0.0, fsh = 0.0, tstall = 0.0, twait = 0.0;
+      h->stats.t_before_shared_profiled = 0.0;
       int64_t nu = 0;
       for (auto& p : h->profiled) {
          float pm = 0.f;
          cudaEventElapsedTime(&pm, p.a, p.b);
          if (p.kind == 0) { tu += pm * 1e-3; fu += p.flops; ++nu; }
          else if (p.kind == 1) ta += pm * 1e-3;
-         else if (p.kind == 2) { tsh += pm * 1e-3; fsh += p.flops; }
-         else tstall += pm * 1e-3;
+         else if (p.kind == 2) {
+            if (tsh == 0.0) { float t0 = 0.f; cudaEventElapsedTime(&t0, h->ev0, p.a); h->stats.t_before_shared_profiled = t0 * 1e-3; }
+            tsh += pm * 1e-3; fsh += p.flops;
+         }
+         else if (p.kind == 3) tstall += pm * 1e-3;
+         else twait += pm * 1e-3;
          cudaEventDestroy(p.a);
          cudaEventDestroy(p.b);
       }
       h->profiled.clear();
       h->stats.t_update_profiled = tu; h->stats.flops_update_profiled = fu; h->stats.n_update_profiled = nu;
       h->stats.t_assemble_profiled = ta;
+      h->stats.t_transfer_wait_profiled = twait;
       h->stats.t_shared_profiled = tsh; h->stats.flops_shared_profiled = fsh; h->stats.t_shared_stall_profiled = tstall;
    }
    h->inertia[0] = static_cast<uint64_t>(h->h_counters[0]);

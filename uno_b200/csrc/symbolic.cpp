@@ -151,6 +151,90 @@ void kkt_pairing(int64_t N, const Graph& g, const std::vector<char>& is_con, std
 
 }  // namespace
 
+// fronts grouped by level (P.level given), big fronts first inside a level
+void build_level_lists(Plan& P) {
+   const int32_t nsn = P.nsn;
+   P.nlevels = 0;
+   for (int32_t s = 0; s < nsn; ++s) P.nlevels = std::max(P.nlevels, P.level[s] + 1);
+   P.level_ptr.assign(static_cast<size_t>(P.nlevels) + 1, 0);
+   for (int32_t s = 0; s < nsn; ++s) ++P.level_ptr[P.level[s] + 1];
+   for (int32_t l = 0; l < P.nlevels; ++l) P.level_ptr[l + 1] += P.level_ptr[l];
+   P.level_fronts.resize(nsn);
+   {
+      std::vector<int32_t> fillp(P.level_ptr.begin(), P.level_ptr.end() - 1);
+      for (int32_t s = 0; s < nsn; ++s) P.level_fronts[fillp[P.level[s]]++] = s;
+      for (int32_t l = 0; l < P.nlevels; ++l) {
+         std::stable_sort(P.level_fronts.begin() + P.level_ptr[l], P.level_fronts.begin() + P.level_ptr[l + 1],
+                          [&](int32_t a, int32_t b) { return P.f[a] != P.f[b] ? P.f[a] > P.f[b] : P.k[a] > P.k[b]; });
+      }
+   }
+}
+
+// offsets of the contribution blocks in the transient arena (P.level_ptr / P.level_fronts given)
+void build_cb_arena(Plan& P) {
+   const int32_t nsn = P.nsn;
+   // ---- contribution-block arena: first-fit over the level-order schedule ------------------------
+   // A block lives from the level of its front until the level of its parent (where it is consumed by
+   // the extend-add); the numeric phase runs level by level, so the offsets can be fixed here.
+   {
+      P.cb_off.assign(nsn, 0);
+      std::map<int64_t, int64_t> free_list;   // offset -> size, coalesced
+      int64_t top = 0;
+      auto cb_size = [&](int32_t s) {
+         const int64_t r = P.f[s] - P.k[s];
+         return (r * (r + 1) / 2 + 1) & ~int64_t(1);   // packed lower triangle, even number of doubles
+      };
+      auto alloc = [&](int64_t size) {
+         for (auto it = free_list.begin(); it != free_list.end(); ++it) {
+            if (it->second >= size) {
+               const int64_t o = it->first, rest = it->second - size;
+               free_list.erase(it);
+               if (rest > 0) free_list.emplace(o + size, rest);
+               return o;
+            }
+         }
+         // grow: extend a free block that touches the top, if any
+         if (!free_list.empty()) {
+            auto last = std::prev(free_list.end());
+            if (last->first + last->second == top) {
+               const int64_t o = last->first;
+               free_list.erase(last);
+               top = o + size;
+               return o;
+            }
+         }
+         const int64_t o = top;
+         top += size;
+         return o;
+      };
+      auto release = [&](int64_t o, int64_t size) {
+         auto it = free_list.emplace(o, size).first;
+         auto nx = std::next(it);
+         if (nx != free_list.end() && it->first + it->second == nx->first) { it->second += nx->second; free_list.erase(nx); }
+         if (it != free_list.begin()) {
+            auto pv = std::prev(it);
+            if (pv->first + pv->second == it->first) { pv->second += it->second; free_list.erase(it); }
+         }
+      };
+      for (int32_t l = 0; l < P.nlevels; ++l) {
+         for (int32_t t = P.level_ptr[l]; t < P.level_ptr[l + 1]; ++t) {
+            const int32_t s = P.level_fronts[t];
+            const int64_t sz = cb_size(s);
+            if (sz > 0) P.cb_off[s] = alloc(sz);
+         }
+         for (int32_t t = P.level_ptr[l]; t < P.level_ptr[l + 1]; ++t) {
+            const int32_t s = P.level_fronts[t];
+            for (int32_t ci = P.child_ptr[s]; ci < P.child_ptr[s + 1]; ++ci) {
+               const int32_t c = P.child_idx[ci];
+               const int64_t sz = cb_size(c);
+               if (sz > 0) release(P.cb_off[c], sz);
+            }
+         }
+      }
+      P.cb_pool_size = top;
+   }
+}
+
 void analyse(int64_t N, int64_t nnz, int64_t reg_size, int64_t num_primal, const uint64_t* row, const uint64_t* col,
              const AnalyseOptions& opt, Plan& P) {
    if (N <= 0) throw std::runtime_error("analyse: empty matrix");
@@ -515,20 +599,7 @@ void analyse(int64_t N, int64_t nnz, int64_t reg_size, int64_t num_primal, const
       const int32_t p = P.parent[s];
       if (p != -1) P.level[p] = std::max(P.level[p], P.level[s] + 1);
    }
-   P.nlevels = 0;
-   for (int32_t s = 0; s < nsn; ++s) P.nlevels = std::max(P.nlevels, P.level[s] + 1);
-   P.level_ptr.assign(static_cast<size_t>(P.nlevels) + 1, 0);
-   for (int32_t s = 0; s < nsn; ++s) ++P.level_ptr[P.level[s] + 1];
-   for (int32_t l = 0; l < P.nlevels; ++l) P.level_ptr[l + 1] += P.level_ptr[l];
-   P.level_fronts.resize(nsn);
-   {
-      std::vector<int32_t> fillp(P.level_ptr.begin(), P.level_ptr.end() - 1);
-      for (int32_t s = 0; s < nsn; ++s) P.level_fronts[fillp[P.level[s]]++] = s;
-      for (int32_t l = 0; l < P.nlevels; ++l) {
-         std::stable_sort(P.level_fronts.begin() + P.level_ptr[l], P.level_fronts.begin() + P.level_ptr[l + 1],
-                          [&](int32_t a, int32_t b) { return P.f[a] != P.f[b] ? P.f[a] > P.f[b] : P.k[a] > P.k[b]; });
-      }
-   }
+   build_level_lists(P);
    // ---- factor pool layout and work figures ----------------------------------------------------
    P.front_off.resize(nsn);
    P.ldc.resize(nsn);
@@ -547,66 +618,7 @@ void analyse(int64_t N, int64_t nnz, int64_t reg_size, int64_t num_primal, const
       P.max_k = std::max(P.max_k, P.k[s]);
    }
    P.pool_size = off;
-   // ---- contribution-block arena: first-fit over the level-order schedule ------------------------
-   // A block lives from the level of its front until the level of its parent (where it is consumed by
-   // the extend-add); the numeric phase runs level by level, so the offsets can be fixed here.
-   {
-      P.cb_off.assign(nsn, 0);
-      std::map<int64_t, int64_t> free_list;   // offset -> size, coalesced
-      int64_t top = 0;
-      auto cb_size = [&](int32_t s) {
-         const int64_t r = P.f[s] - P.k[s];
-         return (r * (r + 1) / 2 + 1) & ~int64_t(1);   // packed lower triangle, even number of doubles
-      };
-      auto alloc = [&](int64_t size) {
-         for (auto it = free_list.begin(); it != free_list.end(); ++it) {
-            if (it->second >= size) {
-               const int64_t o = it->first, rest = it->second - size;
-               free_list.erase(it);
-               if (rest > 0) free_list.emplace(o + size, rest);
-               return o;
-            }
-         }
-         // grow: extend a free block that touches the top, if any
-         if (!free_list.empty()) {
-            auto last = std::prev(free_list.end());
-            if (last->first + last->second == top) {
-               const int64_t o = last->first;
-               free_list.erase(last);
-               top = o + size;
-               return o;
-            }
-         }
-         const int64_t o = top;
-         top += size;
-         return o;
-      };
-      auto release = [&](int64_t o, int64_t size) {
-         auto it = free_list.emplace(o, size).first;
-         auto nx = std::next(it);
-         if (nx != free_list.end() && it->first + it->second == nx->first) { it->second += nx->second; free_list.erase(nx); }
-         if (it != free_list.begin()) {
-            auto pv = std::prev(it);
-            if (pv->first + pv->second == it->first) { pv->second += it->second; free_list.erase(it); }
-         }
-      };
-      for (int32_t l = 0; l < P.nlevels; ++l) {
-         for (int32_t t = P.level_ptr[l]; t < P.level_ptr[l + 1]; ++t) {
-            const int32_t s = P.level_fronts[t];
-            const int64_t sz = cb_size(s);
-            if (sz > 0) P.cb_off[s] = alloc(sz);
-         }
-         for (int32_t t = P.level_ptr[l]; t < P.level_ptr[l + 1]; ++t) {
-            const int32_t s = P.level_fronts[t];
-            for (int32_t ci = P.child_ptr[s]; ci < P.child_ptr[s + 1]; ++ci) {
-               const int32_t c = P.child_idx[ci];
-               const int64_t sz = cb_size(c);
-               if (sz > 0) release(P.cb_off[c], sz);
-            }
-         }
-      }
-      P.cb_pool_size = top;
-   }
+   build_cb_arena(P);
    const auto t2 = clk::now();
    P.t_symbolic = secs(t1, t2);
 
@@ -748,6 +760,29 @@ void map_subtrees(Plan& P, int parts, bool share_top_fronts) {
          for (int p = 1; p < parts; ++p) if (load[p] < load[best]) best = p;
          load[best] += sub[s];
          P.owner[s] = best;
+      }
+   }
+   // Level schedule of a partitioned run: every rank walks the levels in ascending order, so a shared front must not sit at a
+   // lower level than some rank's unfinished private subtree (that rank would stop for the shared front, the others would wait
+   // for its subtree afterwards).  Fronts with a shared front at or below them are lifted above all purely private fronts.
+   if (parts > 1) {
+      std::vector<char> top(static_cast<size_t>(nsn), 0);
+      bool any = false;
+      for (int32_t s = 0; s < nsn; ++s) {
+         if (P.shared[s]) top[s] = 1;
+         if (top[s]) { any = true; if (P.parent[s] >= 0) top[P.parent[s]] = 1; }
+      }
+      if (any) {
+         int32_t lsub = -1;
+         for (int32_t s = 0; s < nsn; ++s) if (!top[s]) lsub = std::max(lsub, P.level[s]);
+         for (int32_t s = 0; s < nsn; ++s) {   // children first
+            if (!top[s]) continue;
+            int32_t lv = lsub + 1;
+            for (int32_t ci = P.child_ptr[s]; ci < P.child_ptr[s + 1]; ++ci) lv = std::max(lv, P.level[P.child_idx[ci]] + 1);
+            P.level[s] = lv;
+         }
+         build_level_lists(P);
+         build_cb_arena(P);
       }
    }
    // cut edges in the order every rank walks them, work per rank, critical path
