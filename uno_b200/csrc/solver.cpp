@@ -134,6 +134,28 @@ void build_batches(b200kkt_handle* h, std::vector<int>& batch_list, std::vector<
             ++i;
          }
          b.count = static_cast<int>(b.k.size());
+         if (b.shared) {
+            // deal the fronts (k descending) round-robin into num_gpus sub-lists and lay the sub-lists out one after the other
+            const int G = std::max(1, h->num_gpus);
+            std::vector<int> dealt;
+            for (int g = 0; g < G && g < b.count; ++g) {
+               Batch sb;
+               sb.level = l; sb.shared = true; sb.shift = g;
+               sb.begin = b.begin + static_cast<int>(dealt.size());
+               for (int t = g; t < b.count; t += G) {
+                  const int s = batch_list[static_cast<size_t>(b.begin + t)];
+                  dealt.push_back(s);
+                  sb.k.push_back(P.k[s]);
+                  sb.max_f = std::max(sb.max_f, P.f[s]);
+                  sb.pmaxf.push_back(sb.max_f);
+                  sb.max_k = std::max(sb.max_k, P.k[s]);
+                  if (P.f[s] > P.k[s]) sb.has_cb = true;
+               }
+               sb.count = static_cast<int>(sb.k.size());
+               b.subs.push_back(std::move(sb));
+            }
+            std::copy(dealt.begin(), dealt.end(), batch_list.begin() + b.begin);
+         }
          // W panels; a batch that runs the panel kernels (some front with more than NBI pivots) also gets room for the
          // inverted diagonal blocks of the current outer panel behind every W panel
          for (int t = 0; t < b.count; ++t) {
@@ -146,6 +168,7 @@ void build_batches(b200kkt_handle* h, std::vector<int>& batch_list, std::vector<
             }
          }
          b.big_tiles = (b.max_f > 256) ? h->update_tile_mode : 0;
+         for (Batch& sb : b.subs) sb.big_tiles = b.big_tiles;
          h->batches.push_back(std::move(b));
       }
       wpool_size = std::max(wpool_size, level_w);
@@ -246,7 +269,7 @@ void enqueue_cut_transfers(b200kkt_handle* h, int l, int what, double* pool, cud
 // diagonal blocks, D, pivot types and orders) over NVLink, one panel ahead of the updates that need it, so the transfer and the
 // latency-bound panel chain hide behind the FP64 tensor-core work of the other ranks.  At the end the contribution block is put
 // together on every rank (each chunk broadcast by its owner): the parent front, shared too, assembles it everywhere.
-void enqueue_shared_batch(b200kkt_handle* h, const Batch& b, const int* list, cudaStream_t st) {
+void enqueue_shared_batch(b200kkt_handle* h, const Batch& b, const int* /*list*/, cudaStream_t st) {
    const Plan& P = h->plan;
    int64_t& L = h->launches;
    const int G = h->num_gpus, me = h->rank, CH = std::max(1, h->share_chunk_panels);
@@ -254,40 +277,46 @@ void enqueue_shared_batch(b200kkt_handle* h, const Batch& b, const int* list, cu
    FactorArrays Wbuf[2] = {h->W, h->W};
    Wbuf[1].wpool += h->wpool_size;
    const int npan = (b.max_k + NBO - 1) / NBO;
-   const int nchunks = (b.max_f + CH * NBO - 1) / (CH * NBO);
-   auto panel_owner = [&](int p) { return (p / CH) % G; };
-   auto chain = [&](int p, cudaStream_t s_) {
-      const int J0 = p * NBO, nf = b.count_k_greater(J0);
-      L += launch_diagpanel(h->F, list, nf, b.max_k, J0, Wbuf[p & 1], h->null_pivot_tol, s_);
-      L += launch_trsmpanel(h->F, list, nf, b.pmaxf[nf - 1], b.max_k, J0, Wbuf[p & 1], s_);
+   auto sub_list = [&](const Batch& sb) { return h->d_batch_list + sb.begin; };
+   auto has_panel = [&](const Batch& sb, int p) { return p * NBO < sb.max_k; };
+   auto panel_owner = [&](const Batch& sb, int p) { return (p / CH + sb.shift) % G; };
+   auto chain = [&](const Batch& sb, int p, cudaStream_t s_) {
+      const int J0 = p * NBO, nf = sb.count_k_greater(J0);
+      L += launch_diagpanel(h->F, sub_list(sb), nf, sb.max_k, J0, Wbuf[p & 1], h->null_pivot_tol, s_);
+      L += launch_trsmpanel(h->F, sub_list(sb), nf, sb.pmaxf[nf - 1], sb.max_k, J0, Wbuf[p & 1], s_);
    };
-   auto bcast_panel = [&](int p) {
-      const int J0 = p * NBO, nf = b.count_k_greater(J0), root = panel_owner(p);
+   // one NCCL group per step: panel p of every sub-list, each from the rank that factored it
+   auto bcast_panels = [&](int p) {
+      const int J0 = p * NBO;
       CKN(comm_group_start(e__));
-      for (int t = 0; t < nf; ++t) {
-         const int s = h->batch_fronts_host[b.begin + t];
-         const size_t kc = static_cast<size_t>(std::min(NBO, P.k[s] - J0)), ld = static_cast<size_t>(P.ld[s]);
-         const int64_t q = P.sn_first[s] + J0;
-         CKN(comm_bcast_bytes(h->comm, h->W.lpool + P.front_off[s] + static_cast<int64_t>(ld) * J0, ld * kc * sizeof(double), root, cs, e__));
-         CKN(comm_bcast_bytes(h->comm, Wbuf[p & 1].wpool + h->woff_host[s], ld * kc * sizeof(double), root, cs, e__));
-         if (h->xoff_host[s] >= 0)
-            CKN(comm_bcast_bytes(h->comm, h->W.xinv + h->xoff_host[s] + static_cast<int64_t>(J0 / NBI) * XINV_BLOCK_DOUBLES,
-                                 ((kc + NBI - 1) / NBI) * XINV_BLOCK_DOUBLES * sizeof(double), root, cs, e__));
-         CKN(comm_bcast_bytes(h->comm, h->W.dd + q, kc * sizeof(double), root, cs, e__));
-         CKN(comm_bcast_bytes(h->comm, h->W.de + q, kc * sizeof(double), root, cs, e__));
-         CKN(comm_bcast_bytes(h->comm, h->W.ptype + q, kc * sizeof(int), root, cs, e__));
-         CKN(comm_bcast_bytes(h->comm, h->W.lperm + q, kc * sizeof(int), root, cs, e__));
-         CKN(comm_bcast_bytes(h->comm, h->W.blkflag + q, kc * sizeof(int), root, cs, e__));
+      for (const Batch& sb : b.subs) {
+         if (!has_panel(sb, p)) continue;
+         const int nf = sb.count_k_greater(J0), root = panel_owner(sb, p);
+         for (int t = 0; t < nf; ++t) {
+            const int s = h->batch_fronts_host[sb.begin + t];
+            const size_t kc = static_cast<size_t>(std::min(NBO, P.k[s] - J0)), ld = static_cast<size_t>(P.ld[s]);
+            const int64_t q = P.sn_first[s] + J0;
+            CKN(comm_bcast_bytes(h->comm, h->W.lpool + P.front_off[s] + static_cast<int64_t>(ld) * J0, ld * kc * sizeof(double), root, cs, e__));
+            CKN(comm_bcast_bytes(h->comm, Wbuf[p & 1].wpool + h->woff_host[s], ld * kc * sizeof(double), root, cs, e__));
+            if (h->xoff_host[s] >= 0)
+               CKN(comm_bcast_bytes(h->comm, h->W.xinv + h->xoff_host[s] + static_cast<int64_t>(J0 / NBI) * XINV_BLOCK_DOUBLES,
+                                    ((kc + NBI - 1) / NBI) * XINV_BLOCK_DOUBLES * sizeof(double), root, cs, e__));
+            CKN(comm_bcast_bytes(h->comm, h->W.dd + q, kc * sizeof(double), root, cs, e__));
+            CKN(comm_bcast_bytes(h->comm, h->W.de + q, kc * sizeof(double), root, cs, e__));
+            CKN(comm_bcast_bytes(h->comm, h->W.ptype + q, kc * sizeof(int), root, cs, e__));
+            CKN(comm_bcast_bytes(h->comm, h->W.lperm + q, kc * sizeof(int), root, cs, e__));
+            CKN(comm_bcast_bytes(h->comm, h->W.blkflag + q, kc * sizeof(int), root, cs, e__));
+         }
       }
       CKN(comm_group_end(e__));
    };
-   auto update = [&](int p, int lo, int hi) {
-      if (lo >= hi || lo >= b.max_f) return;
-      const int J0 = p * NBO, nf = b.count_k_greater(J0);
+   auto update = [&](const Batch& sb, int p, int lo, int hi) {
+      if (lo >= hi || lo >= sb.max_f) return;
+      const int J0 = p * NBO, nf = sb.count_k_greater(J0);
       UpdateRange R;
       R.abs_lo = lo;
       R.abs_hi = hi;
-      L += launch_update(h->F, list, nf, b.pmaxf[nf - 1], 1, 0, J0, Wbuf[p & 1], b.big_tiles, st, R);
+      L += launch_update(h->F, sub_list(sb), nf, sb.pmaxf[nf - 1], 1, 0, J0, Wbuf[p & 1], sb.big_tiles, st, R);
    };
    auto link = [&](cudaEvent_t ev, cudaStream_t from, cudaStream_t to) {
       CK(cudaEventRecord(ev, from));
@@ -312,64 +341,77 @@ void enqueue_shared_batch(b200kkt_handle* h, const Batch& b, const int* list, cu
    }
    prof_begin(batch_flops, 2);
    const size_t prof_batch = h->profiled.size() - 1;
-   // panel 0
-   if (panel_owner(0) == me) chain(0, st);
+   // panel 0 of every sub-list
+   for (const Batch& sb : b.subs) if (panel_owner(sb, 0) == me) chain(sb, 0, st);
    link(h->ev_sh_main, st, cs);
-   bcast_panel(0);
+   bcast_panels(0);
    link(h->ev_sh_comm, cs, st);
    for (int p = 0; p < npan; ++p) {
       const bool next = p + 1 < npan;
-      const bool next_mine = next && panel_owner(p + 1) == me;
+      bool chained = false;
       if (next) {
-         if (next_mine) {
-            update(p, (p + 1) * NBO, (p + 2) * NBO);   // the next panel's own columns first ...
+         // the sub-lists whose panel p + 1 is mine: that panel's own columns first, then the panel on the panel stream while
+         // the rest is updated here
+         for (const Batch& sb : b.subs)
+            if (has_panel(sb, p + 1) && panel_owner(sb, p + 1) == me) { update(sb, p, (p + 1) * NBO, (p + 2) * NBO); chained = true; }
+         if (chained) {
             link(h->ev_sh_main, st, pst);
             CK(cudaStreamWaitEvent(pst, h->ev_sh_bcast[(p + 1) & 1], 0));   // the broadcast of panel p - 1 has left this W buffer
-            chain(p + 1, pst);                         // ... factored on the panel stream while the rest is updated here
+            for (const Batch& sb : b.subs)
+               if (has_panel(sb, p + 1) && panel_owner(sb, p + 1) == me) chain(sb, p + 1, pst);
             link(h->ev_sh_panel, pst, cs);
-         } else {
-            link(h->ev_sh_main, st, cs);               // the W buffer of panel p + 1 is free: the updates of panel p - 1 are done
          }
-         bcast_panel(p + 1);
+         link(h->ev_sh_main, st, cs);                  // the W buffer of panel p + 1 is free: the updates of panel p - 1 are done
+         bcast_panels(p + 1);
          CK(cudaEventRecord(h->ev_sh_bcast[(p + 1) & 1], cs));
       }
-      // a front whose last panel is p and whose pivot count is not a multiple of NBO has contribution-block columns inside
-      // panel p's own column range
-      bool stragglers = false;
-      for (const int kf : b.k) stragglers = stragglers || (kf > p * NBO && kf < (p + 1) * NBO);
-      for (int c = p / CH; c < nchunks; ++c) {
-         if (c % G != me) continue;
-         const int lo = std::max(c * CH, p) * NBO, hi = (c + 1) * CH * NBO;   // the kernel starts at the end of the K range
-         if (next_mine && lo <= (p + 1) * NBO && (p + 2) * NBO <= hi) {
-            if (stragglers) update(p, lo, (p + 1) * NBO);
-            update(p, (p + 2) * NBO, hi);
-         } else if (lo >= (p + 1) * NBO || stragglers || hi > (p + 1) * NBO) {
-            update(p, lo, hi);
+      for (const Batch& sb : b.subs) {
+         if (!has_panel(sb, p)) continue;
+         const bool next_mine = next && has_panel(sb, p + 1) && panel_owner(sb, p + 1) == me;
+         // a front whose last panel is p and whose pivot count is not a multiple of NBO has contribution-block columns inside
+         // panel p's own column range
+         bool stragglers = false;
+         for (const int kf : sb.k) stragglers = stragglers || (kf > p * NBO && kf < (p + 1) * NBO);
+         const int nchunks = (sb.max_f + CH * NBO - 1) / (CH * NBO);
+         for (int c = p / CH; c < nchunks; ++c) {
+            if ((c + sb.shift) % G != me) continue;
+            const int lo = std::max(c * CH, p) * NBO, hi = (c + 1) * CH * NBO;   // the kernel starts at the end of the K range
+            if (next_mine && lo <= (p + 1) * NBO && (p + 2) * NBO <= hi) {
+               if (stragglers) update(sb, p, lo, (p + 1) * NBO);
+               update(sb, p, (p + 2) * NBO, hi);
+            } else if (lo >= (p + 1) * NBO || stragglers || hi > (p + 1) * NBO) {
+               update(sb, p, lo, hi);
+            }
          }
       }
-      // the next step needs panel p + 1: its owner has it as soon as its own panel chain is through (the broadcast goes on
-      // behind), the others when the broadcast has arrived
+      // the next step needs panel p + 1 of every sub-list: a rank that factored all it needs itself (one sub-list) goes on as
+      // soon as its panel chain is through (the broadcast goes on behind), the others when the broadcast has arrived
       if (next) {
          prof_begin(0.0, 3);
-         CK(cudaStreamWaitEvent(st, next_mine ? h->ev_sh_panel : h->ev_sh_bcast[(p + 1) & 1], 0));
+         const bool all_mine = chained && b.subs.size() == 1;
+         if (chained) CK(cudaStreamWaitEvent(st, h->ev_sh_panel, 0));
+         if (!all_mine) CK(cudaStreamWaitEvent(st, h->ev_sh_bcast[(p + 1) & 1], 0));
          prof_end(h->profiled.size() - 1);
       }
    }
-   L += launch_permute_rows(h->F, list, b.count_k_greater(NBO), b.max_k, h->W, st);
+   for (const Batch& sb : b.subs) L += launch_permute_rows(h->F, sub_list(sb), sb.count_k_greater(NBO), sb.max_k, h->W, st);
    // contribution blocks: every chunk to every rank
    if (b.has_cb) {
       link(h->ev_sh_main, st, cs);
       CKN(comm_group_start(e__));
-      for (int t = 0; t < b.count; ++t) {
-         const int s = h->batch_fronts_host[b.begin + t];
-         const int64_t k = P.k[s], r = P.f[s] - k;
-         if (r <= 0) continue;
-         auto col_start = [&](int64_t j) { return j * r - (j * (j - 1)) / 2; };   // packed lower triangle: first entry of column j
-         for (int c = static_cast<int>(k / (CH * NBO)); c < nchunks; ++c) {
-            const int64_t a = std::max<int64_t>(static_cast<int64_t>(c) * CH * NBO - k, 0), e = std::min<int64_t>(static_cast<int64_t>(c + 1) * CH * NBO - k, r);
-            if (a >= e) continue;
-            CKN(comm_bcast_bytes(h->comm, h->W.cbpool + P.cb_off[s] + col_start(a), static_cast<size_t>(col_start(e) - col_start(a)) * sizeof(double),
-                                 c % G, cs, e__));
+      for (const Batch& sb : b.subs) {
+         const int nchunks = (sb.max_f + CH * NBO - 1) / (CH * NBO);
+         for (int t = 0; t < sb.count; ++t) {
+            const int s = h->batch_fronts_host[sb.begin + t];
+            const int64_t k = P.k[s], r = P.f[s] - k;
+            if (r <= 0) continue;
+            auto col_start = [&](int64_t j) { return j * r - (j * (j - 1)) / 2; };   // packed lower triangle: first entry of column j
+            for (int c = static_cast<int>(k / (CH * NBO)); c < nchunks; ++c) {
+               const int64_t a = std::max<int64_t>(static_cast<int64_t>(c) * CH * NBO - k, 0), e = std::min<int64_t>(static_cast<int64_t>(c + 1) * CH * NBO - k, r);
+               if (a >= e) continue;
+               CKN(comm_bcast_bytes(h->comm, h->W.cbpool + P.cb_off[s] + col_start(a), static_cast<size_t>(col_start(e) - col_start(a)) * sizeof(double),
+                                    (c + sb.shift) % G, cs, e__));
+            }
          }
       }
       CKN(comm_group_end(e__));

@@ -24,6 +24,10 @@ struct Batch {
    bool has_children = false;
    bool has_cb = false;
    bool shared = false;   // fronts factorized by all ranks together (subtree partition, fronts above the cut)
+   // shared batch: its fronts dealt round-robin into num_gpus sub-lists (each k descending, contiguous in the batch list);
+   // sub-list g rotates the chunk ownership by g, so the panels of one step are factored by different ranks side by side
+   std::vector<Batch> subs;
+   int shift = 0;         // of a sub-list: chunk c belongs to rank (c + shift) mod num_gpus
    int big_tiles = 0;   // K4 tile mode (see launch_update)
    std::vector<int> k;            // per front of the batch (descending)
    std::vector<int> pmaxf;        // prefix maximum of f in batch order
