@@ -80,7 +80,7 @@ def build(optional: bool = False, verbose: bool = False) -> Path | None:
             rel = src.relative_to(REF).with_suffix("")
             jobs.append((src, OBJ / ("ref__" + "__".join(rel.parts) + ".o"), ()))
     own = [PLUGIN / "B200Solver.cpp", PLUGIN / "SymmetricIndefiniteLinearSolverFactory.cpp", PLUGIN / "uno_driver.cpp",
-           PLUGIN / "models" / "AnalyticModel.cpp", ROOT / "oracle" / "uno_oracle" / "OracleSolver.cpp"]
+           PLUGIN / "models" / "AnalyticModel.cpp", PLUGIN / "models" / "NLModel.cpp", ROOT / "oracle" / "uno_oracle" / "OracleSolver.cpp"]
     for src in own:
         jobs.append((src, OBJ / ("own__" + src.stem + ".o"), ()))
     jobs.append((ROOT / "oracle" / "kkt_oracle.cpp", OBJ / "own__kkt_oracle.o", ("-O3", "-mavx2", "-mfma", "-fopenmp")))

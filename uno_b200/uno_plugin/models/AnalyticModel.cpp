@@ -7,8 +7,8 @@
 namespace uno {
    AnalyticModel::AnalyticModel(const std::string& name, std::vector<double> variable_lower, std::vector<double> variable_upper,
          std::vector<double> constraint_lower, std::vector<double> constraint_upper, std::vector<double> initial_point,
-         size_t first_linear_constraint) :
-         Model(name, variable_lower.size(), constraint_lower.size(), 1.),
+         size_t first_linear_constraint, double objective_sign) :
+         Model(name, variable_lower.size(), constraint_lower.size(), objective_sign),
          variable_lower(std::move(variable_lower)), variable_upper(std::move(variable_upper)),
          constraint_lower(std::move(constraint_lower)), constraint_upper(std::move(constraint_upper)),
          initial_point(std::move(initial_point)),

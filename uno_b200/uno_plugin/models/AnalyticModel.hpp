@@ -24,7 +24,7 @@ namespace uno {
    public:
       AnalyticModel(const std::string& name, std::vector<double> variable_lower, std::vector<double> variable_upper,
             std::vector<double> constraint_lower, std::vector<double> constraint_upper, std::vector<double> initial_point,
-            size_t first_linear_constraint);
+            size_t first_linear_constraint, double objective_sign = 1.);
 
       void evaluate_constraint_jacobian(const Vector<double>& x, RectangularMatrix<double>& constraint_jacobian) const override;
 
