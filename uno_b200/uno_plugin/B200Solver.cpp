@@ -7,8 +7,12 @@
 //   solve_indefinite_system(matrix, rhs, result) <-> JOB=3  (:91-96)
 //   solve_indefinite_system(statistics, subproblem, ...)    (:98-122)
 //   inertia queries         <-> INFOG(12), INFOG(28)        (:124-147)
+#include <algorithm>
+#include <chrono>
+#include <cstdio>
 #include <cstdlib>
 #include <cstring>
+#include <thread>
 #include "B200Solver.hpp"
 #include "b200kkt.h"
 
@@ -187,10 +191,49 @@ namespace uno {
       KKTBackend make_b200_backend() {
          KKTBackend backend;
          backend.name = "B200";
+         // Several GPUs: N copies of the Uno process run the same iteration (SPMD, like MUMPS over MPI ranks), one GPU each:
+         //   B200KKT_WORLD = N, B200KKT_RANK = 0..N-1, B200KKT_COMM_FILE = a path all ranks can reach (NCCL id hand-over).
+         // Every solver instance gets its own communicator; the instances are created in the same order on every rank.
+         const char* world_variable = std::getenv("B200KKT_WORLD");
+         const char* rank_variable = std::getenv("B200KKT_RANK");
+         const int world = (world_variable != nullptr) ? std::max(1, std::atoi(world_variable)) : 1;
+         const int rank = (rank_variable != nullptr) ? std::atoi(rank_variable) : 0;
          const char* device_variable = std::getenv("B200KKT_DEVICE");
-         const int device = (device_variable != nullptr) ? std::atoi(device_variable) : 0;
+         const int device = (device_variable != nullptr) ? std::atoi(device_variable) : ((world > 1) ? rank : 0);
          b200kkt_handle* handle = nullptr;
-         const int status = b200kkt_create(&handle, device, 1);
+         int status = b200kkt_create(&handle, device, world);
+         if (status == B200KKT_OK && world > 1) {
+            static int instance_counter = 0;
+            const char* file_variable = std::getenv("B200KKT_COMM_FILE");
+            if (file_variable == nullptr) {
+               b200kkt_destroy(handle);
+               throw std::runtime_error("B200: B200KKT_WORLD > 1 needs B200KKT_COMM_FILE (path for the NCCL id hand-over)");
+            }
+            const std::string path = std::string(file_variable) + "." + std::to_string(instance_counter++);
+            char id[128];
+            if (rank == 0) {
+               status = b200kkt_comm_unique_id(id);
+               if (status == B200KKT_OK) {
+                  const std::string temporary = path + ".tmp";
+                  std::FILE* file = std::fopen(temporary.c_str(), "wb");
+                  if (file == nullptr || std::fwrite(id, 1, sizeof(id), file) != sizeof(id)) status = B200KKT_EINVAL;
+                  if (file != nullptr) std::fclose(file);
+                  if (status == B200KKT_OK && std::rename(temporary.c_str(), path.c_str()) != 0) status = B200KKT_EINVAL;   // atomic publish
+               }
+            }
+            else {
+               status = B200KKT_EINVAL;
+               for (int attempt = 0; attempt < 6000 && status != B200KKT_OK; ++attempt) {   // up to 60 s
+                  std::FILE* file = std::fopen(path.c_str(), "rb");
+                  if (file != nullptr) {
+                     if (std::fread(id, 1, sizeof(id), file) == sizeof(id)) status = B200KKT_OK;
+                     std::fclose(file);
+                  }
+                  if (status != B200KKT_OK) std::this_thread::sleep_for(std::chrono::milliseconds(10));
+               }
+            }
+            if (status == B200KKT_OK) status = b200kkt_comm_init(handle, rank, world, id);
+         }
          if (status != B200KKT_OK) {
             std::string message = "B200: cannot create a solver handle on CUDA device " + std::to_string(device);
             if (handle != nullptr) {
