@@ -213,7 +213,9 @@ void build_cut_schedule(b200kkt_handle* h) {
          } else if (P.owner[s] != P.owner[p] && (P.owner[s] == h->rank || P.owner[p] == h->rank)) {
             h->cut_levels[l].factor_p2p.push_back(s);
             h->comm_bytes_factor += 8 * cb_doubles(P, s);
-            if (P.owner[p] == h->rank) h->wait_level[P.level[p]] = std::max(h->wait_level[P.level[p]], l);
+            // the receiver assembles the block at the parent's level; the sender must not pass that level either before the
+            // block has left: the arena region is free for its later fronts from there on
+            h->wait_level[P.level[p]] = std::max(h->wait_level[P.level[p]], l);
          }
       }
       std::sort(h->cut_levels[l].factor_p2p.begin(), h->cut_levels[l].factor_p2p.end());
