@@ -277,13 +277,128 @@ class PartitionedEmulation(EmulatedFactorization):
             s = int(s)
             if rank in (int(self.owner[s]), int(self.owner[plan["parent"][s]])):
                 self.cut_at[int(plan["level"][s])].append(s)
+        self.shared = np.asarray(part.get("shared", np.zeros(len(self.owner), dtype=bool)), dtype=bool)
+        self.world = int(len(part["part_flops"]))
         self.dd[:] = 0.0
         self.ptype[:] = -1                           # other ranks' pivots: skipped by the inertia count
+        parent = plan["parent"]
         for l in range(nlev):
             for s in self.level_fronts[l]:
-                if self.owner[s] == rank:
-                    self.factor_front(int(s))
-            self._transfer(l, lambda s: self.fronts[s]["cb"], self._store_cb, up=True)
+                s = int(s)
+                if self.shared[s]:
+                    self.factor_shared_front(s)      # every rank, same order
+                elif self.owner[s] == rank:
+                    self.factor_front(s)
+            # factorization transfers of the level (solver.cpp: build_cut_schedule): below a shared parent the block goes to every
+            # rank, below a parent on another rank to that rank alone; shared fronts spread their own block themselves
+            p2p_fronts = [s for s in self.cut_at[l] if not self.shared[s] and not self.shared[parent[s]]]
+            self._transfer(l, lambda s: self.fronts[s]["cb"], self._store_cb, up=True, fronts=p2p_fronts)
+            for s in self.level_fronts[l]:
+                s = int(s)
+                if self.shared[s] or parent[s] < 0 or not self.shared[parent[s]] or self._r(s) == 0:
+                    continue
+                r = self._r(s)
+                cb = self.fronts[s]["cb"] if self.owner[s] == rank else np.zeros((r, r))
+                self._store_cb_keep_L(s, self.transport.bcast(cb, int(self.owner[s])))
+        # pivots of shared fronts are counted by their owner only
+        self.count_mask = np.repeat(self.owner == rank, plan["k"])
+
+    # ---- a front shared by all ranks (solver.cpp: enqueue_shared_batch) ---------------------------------------------------------
+    NBO_E = 64       # outer panel of the emulation (the library: 256); a multiple of NBI
+    CHUNK = 2        # column chunk in outer panels (option share_chunk_panels)
+
+    def _store_cb_keep_L(self, s, a):
+        old = self.fronts[s]
+        self.fronts[s] = {"L": None if old is None else old["L"], "cb": a}
+
+    def factor_shared_front(self, s):
+        plan, pool, tol = self.plan, self.assembled, self.null_tol
+        k, f, ld, off, first = plan["k"], plan["f"], plan["ld"], plan["pool_offset"], plan["first_col"]
+        G, me, NBO, CH = self.world, self.rank, self.NBO_E, self.CHUNK
+        shift = s % G                                      # the library rotates by the front's place in its batch
+        fs, ks = int(f[s]), int(k[s])
+        F = np.zeros((fs, fs))
+        F[:, :ks] = pool[off[s] : off[s] + ld[s] * ks].reshape(ks, ld[s]).T[:fs, :]
+        F = np.tril(F) + np.tril(F, -1).T
+        for ch in self.children[s]:                        # every rank assembles the whole front (K5 everywhere)
+            loc = self.child_map(ch)
+            self.relmap[ch] = loc
+            F[np.ix_(loc, loc)] += self.fronts[ch]["cb"]
+        chunk_of = (np.arange(fs) // (CH * NBO))
+        mine_col = ((chunk_of + shift) % G) == me          # columns of the trailing matrix this rank updates
+        lower = np.tril(np.ones((fs, fs), dtype=bool))
+        lp = np.arange(ks)
+        q0 = first[s]
+        npan = (ks + NBO - 1) // NBO
+        for p in range(npan):
+            J0, J1 = p * NBO, min((p + 1) * NBO, ks)
+            root = ((p // CH) + shift) % G
+            perms = []
+            Wp = np.zeros((fs - J1, J1 - J0))
+            if root == me:
+                for j0 in range(J0, J1, NBI):
+                    j1 = min(j0 + NBI, J1)
+                    nbw = j1 - j0
+                    B = F[j0:j1, j0:j1]
+                    B = np.tril(B) + np.tril(B, -1).T      # only the lower triangle of a rank's own columns is kept current
+                    pb, d, e, ty = bk_block(B, nbw, tol)
+                    L11 = np.tril(B, -1) + np.eye(nbw)
+                    self.dd[q0 + j0 : q0 + j1], self.de[q0 + j0 : q0 + j1], self.ptype[q0 + j0 : q0 + j1] = d, e, ty
+                    perms.append(pb.copy())
+                    lp[j0:j1] = lp[j0:j1][pb]
+                    F[j0:j1, J0:j0] = F[j0:j1, J0:j0][pb, :]          # the panel's own earlier columns follow at once
+                    X = F[j1:, j0:j1][:, pb]
+                    Wm = np.linalg.solve(L11, X.T).T
+                    D = np.diag(d) + np.diag(e[:-1], -1) + np.diag(e[:-1], 1)
+                    Lm = np.linalg.solve(D, Wm.T).T
+                    null = ty == 3
+                    Lm[:, null] = 0.0
+                    Wm[:, null] = 0.0
+                    F[j0:j1, j0:j1] = np.tril(B, -1) + np.diag(d)
+                    F[j1:, j0:j1] = Lm
+                    if j1 < J1:                                       # inside the panel: left-looking on the panel's own columns
+                        U = Wm[: , :] @ Lm[: J1 - j1, :].T
+                        blk = F[j1:, j1:J1]
+                        m = np.tril(np.ones_like(blk, dtype=bool))
+                        blk[m] -= U[m]
+                        F[j1:, j1:J1] = blk
+                    Wp[:, j0 - J0 : j1 - J0] = Wm[J1 - j1 :, :]
+            # the factored panel to every rank: L columns (with the diagonal block), W panel, D, pivot types and orders
+            panel = self.transport.bcast(F[J0:, J0:J1].copy(), root)
+            Wp = self.transport.bcast(Wp, root)
+            dinfo = np.stack([self.dd[q0 + J0 : q0 + J1], self.de[q0 + J0 : q0 + J1], self.ptype[q0 + J0 : q0 + J1].astype(float), lp[J0:J1].astype(float)])
+            dinfo = self.transport.bcast(dinfo, root)
+            nblk = (J1 - J0 + NBI - 1) // NBI
+            pm = np.zeros((nblk, NBI))
+            for bi, pb in enumerate(perms):
+                pm[bi, : len(pb)] = pb
+            pm = self.transport.bcast(pm, root).astype(int)
+            if root != me:
+                F[J0:, J0:J1] = panel
+                self.dd[q0 + J0 : q0 + J1], self.de[q0 + J0 : q0 + J1] = dinfo[0], dinfo[1]
+                self.ptype[q0 + J0 : q0 + J1] = dinfo[2].astype(np.int32)
+                lp[J0:J1] = dinfo[3].astype(int)
+            # rows of the L columns left of the panel follow the panel's interchanges (k_permute_rows, on every rank)
+            for bi, j0 in enumerate(range(J0, J1, NBI)):
+                j1 = min(j0 + NBI, J1)
+                F[j0:j1, :J0] = F[j0:j1, :J0][pm[bi, : j1 - j0], :]
+            # trailing update of this rank's column chunks, lower triangle only
+            if J1 < fs:
+                Lp = F[J1:, J0:J1]
+                U = Wp @ Lp.T
+                m = lower[J1:, J1:] & mine_col[None, J1:]
+                T = F[J1:, J1:]
+                T[m] -= U[m]
+                F[J1:, J1:] = T
+        self.lperm[q0 : q0 + ks] = lp
+        # contribution block: every chunk from its owner (sum of the owned columns over the ranks = gather)
+        r = fs - ks
+        cb = None
+        if r > 0:
+            M = np.where(lower[ks:, ks:] & mine_col[None, ks:], F[ks:, ks:], 0.0)
+            M = self.transport.allreduce_sum(M)
+            cb = np.tril(M) + np.tril(M, -1).T
+        self.fronts[s] = {"L": F[:, :ks].copy(), "cb": cb}
 
     def _r(self, s):
         return int(self.plan["f"][s] - self.plan["k"][s])
@@ -291,9 +406,9 @@ class PartitionedEmulation(EmulatedFactorization):
     def _store_cb(self, s, a):
         self.fronts[s] = {"L": None, "cb": a}
 
-    def _transfer(self, l, payload, store, up):
+    def _transfer(self, l, payload, store, up, fronts=None):
         sends, recvs, targets = [], [], []
-        for s in self.cut_at[l]:
+        for s in (self.cut_at[l] if fronts is None else fronts):
             mine = self.owner[s] == self.rank
             peer = int(self.owner[self.plan["parent"][s]] if mine else self.owner[s])
             if mine == up:
@@ -314,6 +429,8 @@ class PartitionedEmulation(EmulatedFactorization):
     def inertia(self):
         pos = neg = zero = 0
         for q in range(self.n):
+            if not self.count_mask[q]:       # k_inertia with the owner mask
+                continue
             t = self.ptype[q]
             if t == 0:
                 if self.dd[q] > 0: pos += 1

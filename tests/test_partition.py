@@ -138,6 +138,11 @@ class GlooTransport:
         dist.all_reduce(t)
         return t.numpy()
 
+    def bcast(self, a, root):
+        t = torch.from_numpy(np.array(a, dtype=np.float64))
+        dist.broadcast(t, src=root)
+        return t.numpy()
+
 
 def _free_port():
     with socket.socket() as s:
@@ -172,6 +177,65 @@ def _worker(rank, world, port, out):
         host.close()
     out.put(res)
     dist.destroy_process_group()
+
+
+def _worker_shared(rank, world, port, out):
+    os.environ.update(MASTER_ADDR="127.0.0.1", MASTER_PORT=str(port), RANK=str(rank), WORLD_SIZE=str(world))
+    dist.init_process_group("gloo", rank=rank, world_size=world)
+    sys.path.insert(0, str(ROOT))
+    sys.path.insert(0, str(ROOT / "tests"))
+    import emulator
+    from helpers import backward_error
+    from uno_b200 import KKTSolver
+    from uno_b200 import generators as G
+    kkt = G.ocp_boundary_3d(26, seed=4)     # shared fronts (2001, 649) - contribution block, 649 is no multiple of the panel width - and the root
+    host = KKTSolver(device=-1, num_gpus=world, share_min_pivots=512, share_min_flops=1e8)
+    host.do_symbolic_analysis(kkt.dim, kkt.row, kkt.col, kkt.reg_size, kkt.n)
+    plan, part = host.plan(), host.partition()
+    perm, scatter = host.permutation()
+    emu = emulator.PartitionedEmulation(plan, part, rank, GlooTransport(), perm, scatter, kkt, kkt.val)
+    ine = emu.inertia()
+    x = emu.solve(kkt.rhs)
+    shared = np.flatnonzero(part["shared"])
+    out.put({"rank": rank, "inertia": ine, "expected": (kkt.n, kkt.m, 0), "berr": float(backward_error(kkt, kkt.val, x)), "checksum": float(np.sum(x)),
+             "shared": [(int(plan["f"][s]), int(plan["k"][s])) for s in shared], "levels_ok": _shared_levels_above_private(plan, part)})
+    host.close()
+    dist.destroy_process_group()
+
+
+def _shared_levels_above_private(plan, part):
+    """Every front with a shared front at or below it sits above all purely private fronts (partitioned level schedule)."""
+    nsn = plan["num_fronts"]
+    top = np.array(part["shared"], dtype=bool).copy()
+    for s in range(nsn):                       # children are numbered before their parents
+        if top[s] and plan["parent"][s] >= 0:
+            top[plan["parent"][s]] = True
+    if not top.any() or top.all():
+        return True
+    return bool(plan["level"][top].min() > plan["level"][~top].max())
+
+
+def test_shared_front_protocol_world_size_two_gloo(lib):
+    """The shared-front factorization (column chunks per rank, rotated ownership, panels factored by the chunk owner and broadcast,
+    straggler columns of a last panel, contribution block gathered on every rank) run by two gloo ranks through the numpy emulation:
+    exact inertia, backward error, the same solution on both ranks."""
+    world = 2
+    ctx = mp.get_context("spawn")
+    out = ctx.Queue()
+    port = _free_port()
+    procs = [ctx.Process(target=_worker_shared, args=(r, world, port, out)) for r in range(world)]
+    for p in procs:
+        p.start()
+    res = sorted((out.get(timeout=600) for _ in range(world)), key=lambda r: r["rank"])
+    for p in procs:
+        p.join(timeout=60)
+        assert p.exitcode == 0
+    for r in res:
+        assert len(r["shared"]) >= 1 and any(k < f for f, k in r["shared"])      # at least one shared front with a contribution block
+        assert tuple(r["inertia"]) == tuple(r["expected"])
+        assert r["berr"] <= 1e-12
+        assert r["levels_ok"]
+    assert res[0]["checksum"] == res[1]["checksum"]
 
 
 def test_partitioned_protocol_world_size_two_gloo(lib):
