@@ -49,6 +49,16 @@ struct CudaError {
       if ((expr) != 0) throw std::runtime_error(e__);                \
    } while (0)
 
+// an NCCL group that is closed on every path out of the scope (an exception between start and end must not leave it open)
+struct CommGroup {
+   bool open = false;
+   CommGroup() { std::string e; if (comm_group_start(e) != 0) throw std::runtime_error(e); open = true; }
+   void end() { if (open) { open = false; std::string e; if (comm_group_end(e) != 0) throw std::runtime_error(e); } }
+   ~CommGroup() { if (open) { std::string e; comm_group_end(e); } }
+   CommGroup(const CommGroup&) = delete;
+   CommGroup& operator=(const CommGroup&) = delete;
+};
+
 int fail(const b200kkt_handle* h, int code, const std::string& msg) {
    if (h != nullptr) h->err = msg;
    return code;
@@ -248,7 +258,7 @@ void enqueue_cut_transfers(b200kkt_handle* h, int l, int what, double* pool, cud
    const b200kkt_handle::CutLevel& CL = h->cut_levels[l];
    const std::vector<int>& list = what == 0 ? CL.factor_p2p : CL.fronts;
    if (list.empty() && (what != 0 || CL.factor_bcast.empty())) return;
-   CKN(comm_group_start(e__));
+   CommGroup group;
    for (const int s : list) {
       const bool mine = P.owner[s] == h->rank;
       const int peer = mine ? P.owner[P.parent[s]] : P.owner[s];
@@ -262,7 +272,7 @@ void enqueue_cut_transfers(b200kkt_handle* h, int l, int what, double* pool, cud
    if (what == 0)
       for (const int s : CL.factor_bcast)
          CKN(comm_bcast_bytes(h->comm, pool + P.cb_off[s], static_cast<size_t>(cb_doubles(P, s)) * sizeof(double), P.owner[s], st, e__));
-   CKN(comm_group_end(e__));
+   group.end();
 }
 
 // K2-K4 of a batch of SHARED fronts (subtree partition; every rank runs this with the same batch).  The trailing matrix of a
@@ -290,7 +300,7 @@ void enqueue_shared_batch(b200kkt_handle* h, const Batch& b, const int* /*list*/
    // one NCCL group per step: panel p of every sub-list, each from the rank that factored it
    auto bcast_panels = [&](int p) {
       const int J0 = p * NBO;
-      CKN(comm_group_start(e__));
+      CommGroup group;
       for (const Batch& sb : b.subs) {
          if (!has_panel(sb, p)) continue;
          const int nf = sb.count_k_greater(J0), root = panel_owner(sb, p);
@@ -310,7 +320,7 @@ void enqueue_shared_batch(b200kkt_handle* h, const Batch& b, const int* /*list*/
             CKN(comm_bcast_bytes(h->comm, h->W.blkflag + q, kc * sizeof(int), root, cs, e__));
          }
       }
-      CKN(comm_group_end(e__));
+      group.end();
    };
    auto update = [&](const Batch& sb, int p, int lo, int hi) {
       if (lo >= hi || lo >= sb.max_f) return;
@@ -400,7 +410,7 @@ void enqueue_shared_batch(b200kkt_handle* h, const Batch& b, const int* /*list*/
    // contribution blocks: every chunk to every rank
    if (b.has_cb) {
       link(h->ev_sh_main, st, cs);
-      CKN(comm_group_start(e__));
+      CommGroup group;
       for (const Batch& sb : b.subs) {
          const int nchunks = (sb.max_f + CH * NBO - 1) / (CH * NBO);
          for (int t = 0; t < sb.count; ++t) {
@@ -416,7 +426,7 @@ void enqueue_shared_batch(b200kkt_handle* h, const Batch& b, const int* /*list*/
             }
          }
       }
-      CKN(comm_group_end(e__));
+      group.end();
       link(h->ev_sh_comm, cs, st);
    }
    prof_end(prof_batch);
