@@ -289,6 +289,25 @@ def main():
     e2e_value = replicas.aggregate_throughput(args.steps, units, replicas.max_over_ranks(time.perf_counter() - t0, dist, "cuda"))
     x_ok = bool(np.isfinite(h_x.numpy()).all())
 
+    # secondary metric of SURVEY 8(d): one step of the caller's inertia-correction loop = refactorization after only the leading
+    # regularization slots changed (uploads reg_size doubles) + inertia.  One GPU only (on several it is a collective).
+    inertia_loop = None
+    if world == 1 and kkt.reg_size > 0:
+        try:
+            reg = np.ascontiguousarray(kkt.val[:kkt.reg_size])
+            solver.refactorize_shifted(reg)
+            reps = max(1, min(args.steps, 2))
+            torch.cuda.synchronize()
+            t0 = time.perf_counter()
+            for _ in range(reps):
+                solver.refactorize_shifted(reg)
+                ine_r = solver.get_inertia()
+            torch.cuda.synchronize()
+            inertia_loop = {"value": reps / (time.perf_counter() - t0), "unit": "refactorize_shifted+inertia/s", "h2d_bytes_per_step": int(8 * kkt.reg_size),
+                            "d2h_bytes_per_step": 32, "inertia": list(ine_r), "steps": reps}
+        except Exception as exc:   # a reported extra, never the reason for a missing bench line
+            inertia_loop = {"value": None, "error": str(exc)}
+
     def profile_k4():
         # roofline of the dominant kernel (K4): one extra, un-graphed factorization with event pairs around its big-front launches
         solver.set_option("use_graph", 0)
@@ -357,6 +376,7 @@ def main():
         "e2e": {"value": e2e_value, "unit": UNIT, "h2d_bytes_per_step": int(8 * kkt.nnz + 8 * kkt.dim), "d2h_bytes_per_step": int(8 * kkt.dim + 32 + 32),
                 "finite": x_ok},
         "roofline": roofline,
+        "inertia_loop_step": inertia_loop,
         "breakdown": {"factor_ms": 1e3 * t_fact / args.steps, "solve_ms": 1e3 * t_solve / args.steps, "refine_steps": refine / args.steps,
                       "inertia": list(ine), "expected_inertia": [kkt.n, kkt.m, 0], "backward_error": berr},
     }
