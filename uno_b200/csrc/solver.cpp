@@ -748,7 +748,8 @@ double bits_to_double(unsigned long long b) {
 void run_factor(b200kkt_handle* h) {
    cudaStream_t st = h->stream;
    CK(cudaEventRecord(h->ev0, st));
-   if (h->use_graph && !h->partitioned()) {   // partitioned: NCCL calls between the levels, launched directly
+   // partitioned: NCCL calls between the levels are launched directly unless partition_graph asks for their capture too
+   if (h->use_graph && (!h->partitioned() || h->partition_graph != 0)) {
       if (h->factor_graph == nullptr) {
          const int64_t before = h->launches;
          cudaGraph_t graph = nullptr;
@@ -885,7 +886,7 @@ void run_solve(b200kkt_handle* h, const double* d_b, double* d_x, double* backwa
    double berr = 0.0, prev = 0.0;
    int steps = 0;
    for (int it = 0; it <= h->refine_max_steps; ++it) {
-      if (h->use_graph && !h->partitioned()) {
+      if (h->use_graph && (!h->partitioned() || h->partition_graph != 0)) {
          // the sweep is a long chain of short kernels: replayed as a CUDA graph (re-captured when the output vector moves)
          if (h->solve_graph == nullptr || h->solve_graph_x != d_x || h->solve_graph_scale != h->d_scale_final) {
             if (h->solve_graph != nullptr) { cudaGraphExecDestroy(h->solve_graph); h->solve_graph = nullptr; }
@@ -1114,6 +1115,7 @@ int b200kkt_set_option(b200kkt_handle* h, const char* name, double value) {
    else if (n == "lookahead") h->lookahead = static_cast<int>(value);
    else if (n == "pair_panels") h->pair_panels = static_cast<int>(value);
    else if (n == "pair_min_front") h->pair_min_front = static_cast<int>(value);
+   else if (n == "partition_graph") h->partition_graph = static_cast<int>(value);
    else if (n == "share_top_fronts") h->share_top_fronts = static_cast<int>(value);
    else if (n == "share_chunk_panels") h->share_chunk_panels = std::max(1, static_cast<int>(value));
    else if (n == "share_min_pivots") h->share_min_pivots = std::max(2 * NBO, static_cast<int>(value));

@@ -136,6 +136,7 @@ struct b200kkt_handle {
    std::vector<cudaEvent_t> ev_comm;      // per level: transfers of that level's cut fronts done (null where there are none)
    cudaStream_t comm_stream = nullptr;
    cudaEvent_t ev_level_done = nullptr;
+   int partition_graph = 0;               // experimental, off: capture the partitioned factorization / solve sweep (NCCL calls included) in CUDA graphs
    int share_top_fronts = 1;              // big fronts above the cut are factorized by all ranks together
    int share_chunk_panels = 2;            // column chunk of a shared front, in outer panels; chunk c belongs to rank c mod num_gpus
    int share_min_pivots = 1024;
