@@ -130,6 +130,20 @@ __global__ void __launch_bounds__(256) k_boundary_unpack(FrontArrays F, const in
    for (int i = threadIdx.x; i < r; i += 256) xg[rows[i]] = slot[i];
 }
 
+// rows [row0, row0 + nrows) of ncols columns of a column-major panel (leading dimension ld) to / from a dense nrows x ncols
+// staging block: a factored panel of a shared front is broadcast without the rows above its diagonal block
+__global__ void __launch_bounds__(256) k_rows_pack(const double* __restrict__ src, const int64_t ld, const int row0, const int nrows,
+                                                   double* __restrict__ dst) {
+   const int i = blockIdx.x * 256 + threadIdx.x, c = blockIdx.y;
+   if (i < nrows) dst[static_cast<int64_t>(c) * nrows + i] = src[static_cast<int64_t>(c) * ld + row0 + i];
+}
+
+__global__ void __launch_bounds__(256) k_rows_unpack(const double* __restrict__ src, const int64_t ld, const int row0, const int nrows,
+                                                     double* __restrict__ dst) {
+   const int i = blockIdx.x * 256 + threadIdx.x, c = blockIdx.y;
+   if (i < nrows) dst[static_cast<int64_t>(c) * ld + row0 + i] = src[static_cast<int64_t>(c) * nrows + i];
+}
+
 // solution entries of pivots owned by other ranks are zeroed before the sum over ranks puts the vector together
 __global__ void k_keep_owned(int64_t n, const signed char* __restrict__ col_owner, const int rank, double* __restrict__ xg) {
    const int64_t g = blockIdx.x * static_cast<int64_t>(blockDim.x) + threadIdx.x;
@@ -2474,6 +2488,18 @@ int launch_boundary_pack(const FrontArrays& F, const int* d_list, int nfronts, c
 int launch_boundary_unpack(const FrontArrays& F, const int* d_list, int nfronts, const double* cpool, double* xg, cudaStream_t st) {
    if (nfronts <= 0) return 0;
    k_boundary_unpack<<<nfronts, 256, 0, st>>>(F, d_list, cpool, xg);
+   return 1;
+}
+
+int launch_rows_pack(const double* panel, int64_t ld, int row0, int nrows, int ncols, double* staging, cudaStream_t st) {
+   if (nrows <= 0 || ncols <= 0) return 0;
+   k_rows_pack<<<dim3((nrows + 255) / 256, ncols), 256, 0, st>>>(panel, ld, row0, nrows, staging);
+   return 1;
+}
+
+int launch_rows_unpack(const double* staging, int64_t ld, int row0, int nrows, int ncols, double* panel, cudaStream_t st) {
+   if (nrows <= 0 || ncols <= 0) return 0;
+   k_rows_unpack<<<dim3((nrows + 255) / 256, ncols), 256, 0, st>>>(staging, ld, row0, nrows, panel);
    return 1;
 }
 

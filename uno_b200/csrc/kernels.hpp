@@ -137,6 +137,9 @@ int launch_solve_scatter_add(int64_t n, const int* perm, const double* scale, co
 int launch_boundary_pack(const FrontArrays& F, const int* d_list, int nfronts, const double* xg, double* cpool, cudaStream_t st);
 int launch_boundary_unpack(const FrontArrays& F, const int* d_list, int nfronts, const double* cpool, double* xg, cudaStream_t st);
 int launch_keep_owned(int64_t n, const signed char* col_owner, int rank, double* xg, cudaStream_t st);
+// rows [row0, row0 + nrows) of ncols panel columns (leading dimension ld) <-> dense nrows x ncols staging block
+int launch_rows_pack(const double* panel, int64_t ld, int row0, int nrows, int ncols, double* staging, cudaStream_t st);
+int launch_rows_unpack(const double* staging, int64_t ld, int row0, int nrows, int ncols, double* panel, cudaStream_t st);
 // K8 residual r = b - K x on the COO-order values, and infinity norms as ordered bit patterns
 int launch_residual(const CsrArrays& A, const double* values, const double* x, const double* b, double* r, cudaStream_t st);
 int launch_absmax(const double* v, int64_t n, unsigned long long* out_bits, cudaStream_t st);

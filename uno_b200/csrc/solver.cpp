@@ -298,8 +298,28 @@ void enqueue_shared_batch(b200kkt_handle* h, const Batch& b, const int* /*list*/
       L += launch_trsmpanel(h->F, sub_list(sb), nf, sb.pmaxf[nf - 1], sb.max_k, J0, Wbuf[p & 1], s_);
    };
    // one NCCL group per step: panel p of every sub-list, each from the rank that factored it
+   // option share_trim_rows (experimental, off): only rows >= J0 of the L columns and of the W panel travel, through two staging
+   // blocks in the W buffers this path does not use (2 and 3); pack on the root before the group, unpack on the others behind it
+   const bool trim = h->share_trim_rows != 0;
+   double* stage_l = h->W.wpool + 2 * h->wpool_size;
+   double* stage_w = h->W.wpool + 3 * h->wpool_size;
+   auto for_panel_fronts = [&](int p, auto&& fn) {
+      const int J0 = p * NBO;
+      for (const Batch& sb : b.subs) {
+         if (!has_panel(sb, p)) continue;
+         const int nf = sb.count_k_greater(J0), root = panel_owner(sb, p);
+         for (int t = 0; t < nf; ++t) fn(h->batch_fronts_host[sb.begin + t], root);
+      }
+   };
    auto bcast_panels = [&](int p) {
       const int J0 = p * NBO;
+      if (trim)
+         for_panel_fronts(p, [&](int s, int root) {
+            if (root != me) return;
+            const int kc = std::min(NBO, P.k[s] - J0), nrows = P.f[s] - J0;
+            L += launch_rows_pack(h->W.lpool + P.front_off[s] + static_cast<int64_t>(P.ld[s]) * J0, P.ld[s], J0, nrows, kc, stage_l + h->woff_host[s], cs);
+            L += launch_rows_pack(Wbuf[p & 1].wpool + h->woff_host[s], P.ld[s], J0, nrows, kc, stage_w + h->woff_host[s], cs);
+         });
       CommGroup group;
       for (const Batch& sb : b.subs) {
          if (!has_panel(sb, p)) continue;
@@ -308,8 +328,15 @@ void enqueue_shared_batch(b200kkt_handle* h, const Batch& b, const int* /*list*/
             const int s = h->batch_fronts_host[sb.begin + t];
             const size_t kc = static_cast<size_t>(std::min(NBO, P.k[s] - J0)), ld = static_cast<size_t>(P.ld[s]);
             const int64_t q = P.sn_first[s] + J0;
-            CKN(comm_bcast_bytes(h->comm, h->W.lpool + P.front_off[s] + static_cast<int64_t>(ld) * J0, ld * kc * sizeof(double), root, cs, e__));
-            CKN(comm_bcast_bytes(h->comm, Wbuf[p & 1].wpool + h->woff_host[s], ld * kc * sizeof(double), root, cs, e__));
+            if (trim) {
+               const size_t count = static_cast<size_t>(P.f[s] - J0) * kc;
+               CKN(comm_bcast_bytes(h->comm, stage_l + h->woff_host[s], count * sizeof(double), root, cs, e__));
+               CKN(comm_bcast_bytes(h->comm, stage_w + h->woff_host[s], count * sizeof(double), root, cs, e__));
+            }
+            else {
+               CKN(comm_bcast_bytes(h->comm, h->W.lpool + P.front_off[s] + static_cast<int64_t>(ld) * J0, ld * kc * sizeof(double), root, cs, e__));
+               CKN(comm_bcast_bytes(h->comm, Wbuf[p & 1].wpool + h->woff_host[s], ld * kc * sizeof(double), root, cs, e__));
+            }
             if (h->xoff_host[s] >= 0)
                CKN(comm_bcast_bytes(h->comm, h->W.xinv + h->xoff_host[s] + static_cast<int64_t>(J0 / NBI) * XINV_BLOCK_DOUBLES,
                                     ((kc + NBI - 1) / NBI) * XINV_BLOCK_DOUBLES * sizeof(double), root, cs, e__));
@@ -321,6 +348,13 @@ void enqueue_shared_batch(b200kkt_handle* h, const Batch& b, const int* /*list*/
          }
       }
       group.end();
+      if (trim)
+         for_panel_fronts(p, [&](int s, int root) {
+            if (root == me) return;
+            const int kc = std::min(NBO, P.k[s] - J0), nrows = P.f[s] - J0;
+            L += launch_rows_unpack(stage_l + h->woff_host[s], P.ld[s], J0, nrows, kc, h->W.lpool + P.front_off[s] + static_cast<int64_t>(P.ld[s]) * J0, cs);
+            L += launch_rows_unpack(stage_w + h->woff_host[s], P.ld[s], J0, nrows, kc, Wbuf[p & 1].wpool + h->woff_host[s], cs);
+         });
    };
    auto update = [&](const Batch& sb, int p, int lo, int hi) {
       if (lo >= hi || lo >= sb.max_f) return;
@@ -1116,6 +1150,7 @@ int b200kkt_set_option(b200kkt_handle* h, const char* name, double value) {
    else if (n == "pair_panels") h->pair_panels = static_cast<int>(value);
    else if (n == "pair_min_front") h->pair_min_front = static_cast<int>(value);
    else if (n == "partition_graph") h->partition_graph = static_cast<int>(value);
+   else if (n == "share_trim_rows") h->share_trim_rows = static_cast<int>(value);
    else if (n == "share_top_fronts") h->share_top_fronts = static_cast<int>(value);
    else if (n == "share_chunk_panels") h->share_chunk_panels = std::max(1, static_cast<int>(value));
    else if (n == "share_min_pivots") h->share_min_pivots = std::max(2 * NBO, static_cast<int>(value));
