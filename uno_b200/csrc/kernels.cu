@@ -1246,8 +1246,22 @@ __global__ void __launch_bounds__(WARPS_M* WARPS_N * 32, MINB) k_update(FrontArr
       if (R.abs_hi > 0) { c0 = max(c0, R.abs_lo); c1 = min(c1, R.abs_hi); }
    }
    if (c0 >= c1 || r0 >= f || K <= 0) return;
+   int ntile = (c0 & ~1) + blockIdx.z * BN;
+   if (mode != 0 && R.cyc_cols > 0) {
+      // this rank's column chunks only: grid z = (own chunk, tile inside the chunk)
+      const int tiles_per_chunk = R.cyc_cols / BN;
+      int chunk = c0 / R.cyc_cols;
+      chunk += ((R.cyc_me - R.cyc_shift - chunk) % R.cyc_g + R.cyc_g) % R.cyc_g;   // first own chunk at or behind the range start
+      chunk += static_cast<int>(blockIdx.z / tiles_per_chunk) * R.cyc_g;
+      const int lo = chunk * R.cyc_cols;
+      if (lo >= c1) return;
+      ntile = lo + static_cast<int>(blockIdx.z % tiles_per_chunk) * BN;
+      c0 = max(c0, lo);
+      c1 = min(c1, lo + R.cyc_cols);
+      if (ntile + BN <= c0) return;
+   }
    const int m0 = (r0 & ~1) + blockIdx.y * BM;
-   const int n0 = (c0 & ~1) + blockIdx.z * BN;
+   const int n0 = ntile;
    if (m0 >= f || n0 >= c1) return;
    if (m0 + BM <= n0) return;   // tile entirely above the diagonal
 
@@ -2357,6 +2371,7 @@ int launch_update(const FrontArrays& F, const int* d_list, int nfronts, int max_
    // columns: a later part starts clo panels in; the first part may have to cover a whole trailing matrix (last-panel fronts)
    int cols = (mode == 0) ? NBO : ((R.policy == 1 || R.chi < 0) ? rows - R.clo * NBO : std::min(rows - R.clo * NBO, (R.chi - R.clo) * NBO + 2));
    if (mode == 1 && R.abs_hi > 0) cols = std::min(cols, R.abs_hi - std::max(R.abs_lo, r0 & ~1) + 2);
+   if (mode == 1 && R.cyc_cols > 0) cols = R.cyc_nchunks * R.cyc_cols;
    if (cols <= 0) return 0;
    if (tile_mode == 6) {
       dim3 grid(nfronts, (rows + 127) / 128, (cols + 63) / 64);

@@ -93,6 +93,10 @@ struct UpdateRange {
    // abs_hi > 0: additionally only columns [abs_lo, abs_hi) of the front (absolute front columns, multiples of NBO) - the column
    // chunks one rank owns when a front is shared by several GPUs
    int abs_lo = 0, abs_hi = 0;
+   // cyc_cols > 0 (mode 1): only the column chunks of cyc_cols columns that belong to this rank - chunk c with
+   // (c + cyc_shift) mod cyc_g == cyc_me - all of them in ONE launch (grid z runs over cyc_nchunks own chunks from the first one at
+   // or behind the start of the column range); cyc_cols is a multiple of the tile width
+   int cyc_cols = 0, cyc_g = 1, cyc_me = 0, cyc_shift = 0, cyc_nchunks = 0;
 };
 int launch_update(const FrontArrays& F, const int* d_list, int nfronts, int max_f, int mode, int j0, int J0, const FactorArrays& W,
                   int tile_mode, cudaStream_t st, const UpdateRange& R = UpdateRange());

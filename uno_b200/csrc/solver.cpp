@@ -419,7 +419,24 @@ void enqueue_shared_batch(b200kkt_handle* h, const Batch& b, const int* /*list*/
          bool stragglers = false;
          for (const int kf : sb.k) stragglers = stragglers || (kf > p * NBO && kf < (p + 1) * NBO);
          const int nchunks = (sb.max_f + CH * NBO - 1) / (CH * NBO);
-         for (int c = p / CH; c < nchunks; ++c) {
+         // option share_one_launch (experimental, off): every own chunk behind the one that holds panel p + 1 in ONE launch (the W
+         // panel is then read once per step, not once per chunk); the chunks up to there go through the range launches below
+         int range_end = nchunks;
+         if (h->share_one_launch != 0) {
+            const int cfirst = (next_mine ? (p + 1) / CH : p / CH) + (next_mine ? 1 : 0);
+            int own = 0;
+            for (int c = cfirst; c < nchunks; ++c) own += ((c + sb.shift) % G == me) ? 1 : 0;
+            if (own > 0) {
+               const int J0 = p * NBO, nf = sb.count_k_greater(J0);
+               UpdateRange R;
+               R.abs_lo = cfirst * CH * NBO;
+               R.abs_hi = nchunks * CH * NBO;
+               R.cyc_cols = CH * NBO; R.cyc_g = G; R.cyc_me = me; R.cyc_shift = sb.shift; R.cyc_nchunks = own;
+               L += launch_update(h->F, sub_list(sb), nf, sb.pmaxf[nf - 1], 1, 0, J0, Wbuf[p & 1], sb.big_tiles, st, R);
+            }
+            range_end = std::min(nchunks, cfirst);
+         }
+         for (int c = p / CH; c < range_end; ++c) {
             if ((c + sb.shift) % G != me) continue;
             const int lo = std::max(c * CH, p) * NBO, hi = (c + 1) * CH * NBO;   // the kernel starts at the end of the K range
             if (next_mine && lo <= (p + 1) * NBO && (p + 2) * NBO <= hi) {
@@ -1151,6 +1168,7 @@ int b200kkt_set_option(b200kkt_handle* h, const char* name, double value) {
    else if (n == "pair_min_front") h->pair_min_front = static_cast<int>(value);
    else if (n == "partition_graph") h->partition_graph = static_cast<int>(value);
    else if (n == "share_trim_rows") h->share_trim_rows = static_cast<int>(value);
+   else if (n == "share_one_launch") h->share_one_launch = static_cast<int>(value);
    else if (n == "share_top_fronts") h->share_top_fronts = static_cast<int>(value);
    else if (n == "share_chunk_panels") h->share_chunk_panels = std::max(1, static_cast<int>(value));
    else if (n == "share_min_pivots") h->share_min_pivots = std::max(2 * NBO, static_cast<int>(value));
