@@ -126,8 +126,12 @@ def run_oracle_sample(G, name, seed, steps, warmup, full_flops=None):
     """CPU oracle on a bounded sample of the workload; returns the cpu_baseline object."""
     from oracle import oracle as O
     from uno_b200 import KKTSolver
-    has_blas = O.bind_openblas()
     cores = os.cpu_count() or 1
+    # "all the host threads it can use": torchrun exports OMP_NUM_THREADS=1, which the BLAS bound below would obey
+    if os.environ.get("OMP_NUM_THREADS", "1") == "1":
+        os.environ["OMP_NUM_THREADS"] = str(cores)
+    os.environ.setdefault("OPENBLAS_NUM_THREADS", str(cores))
+    has_blas = O.bind_openblas()
     kkt = WORKLOADS[name][2](G, seed)
     # same ordering as the GPU solver (north_star: "same METIS ordering"): host-only handle, symbolic phase only
     host = KKTSolver(device=-1)
@@ -191,7 +195,8 @@ def main():
         host.close()
         cb = run_oracle_sample(G, args.workload, 0, max(1, args.steps), max(0, min(args.warmup, 1)), full_flops)
         line = {"impl": "reference", "metric": METRIC, "value": cb["value"], "unit": UNIT, "n_gpus": args.gpus, "steps": args.steps, "warmup": args.warmup,
-                "ms_per_step": 1e3 / cb["value"], "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f64", "data": "synthetic",
+                "ms_per_step": 1e3 / cb["value"], "higher_is_better": True, "scaling": "strong" if (args.gpus > 1 and args.multi == "partition") else "weak",
+                "vs_baseline": None, "dtype": "f64", "data": "synthetic",
                 "config": {"workload": f"{args.workload}: {WORKLOADS[args.workload][0]}", "parallelism": "host cores"},
                 "cpu_baseline": cb, "e2e": {"value": cb["value"], "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0}, "gpu_launches": 0}
         print(json.dumps(line))
