@@ -21,6 +21,12 @@ from uno_b200 import KKTSolver, partition  # noqa: E402
 from uno_b200 import generators as G  # noqa: E402
 
 
+def emit(record):
+    """One write per line: the ranks share the launcher's stdout, a separate newline write can land behind another rank's line."""
+    sys.stdout.write(json.dumps(record) + "\n")
+    sys.stdout.flush()
+
+
 def main():
     names = [a for a in sys.argv[1:] if "=" not in a] or ["ocp3d:16", "bnd3d:20", "opf", "ocp3d:32"]
     options = {a.split("=")[0]: float(a.split("=")[1]) for a in sys.argv[1:] if "=" in a}   # e.g. share_min_pivots=512
@@ -71,13 +77,13 @@ def main():
         ok = ine == ine1 and berr <= 1e-12 and diff <= 1e-6 and same
         ok_all &= ok
         part = multi.partition()
-        print(json.dumps({"rank": rank, "case": kkt.name, "N": kkt.dim, "ok": ok, "inertia": ine, "inertia_1gpu": ine1, "berr": berr, "berr_1gpu": berr1,
+        emit({"rank": rank, "case": kkt.name, "N": kkt.dim, "ok": ok, "inertia": ine, "inertia_1gpu": ine1, "berr": berr, "berr_1gpu": berr1,
                           "x_rel_diff_vs_1gpu": diff, "x_identical_on_all_ranks": same, "cut_fronts": int(st["num_cut_fronts"]),
                           "share": st["flops_own"] / st["flops_factor"], "critical_share": st["flops_critical"] / st["flops_factor"],
                           "factor_ms": 1e3 * stm["t_factor_last"], "solve_ms": 1e3 * stm["t_solve_last"], "factor_ms_1gpu": 1e3 * st1["t_factor_last"],
                           "solve_ms_1gpu": 1e3 * st1["t_solve_last"], "wall_ms": 1e3 * min(times), "comm_MB_factor": stm["comm_bytes_factor"] / 1e6,
                           "owners": np.bincount(part["owner"], minlength=world).tolist(), "shared_fronts": int(part["shared"].sum()),
-                          "speedup_factor": st1["t_factor_last"] / stm["t_factor_last"]}), flush=True)
+                          "speedup_factor": st1["t_factor_last"] / stm["t_factor_last"]})
         multi.close(); single.close()
     dist.barrier()
     dist.destroy_process_group()

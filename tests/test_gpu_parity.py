@@ -301,7 +301,7 @@ def test_partitioned_two_gpus_matches_single_gpu():
     cmd = [sys.executable, "-m", "torch.distributed.run", "--nnodes=1", "--nproc-per-node", "2", "--master-addr", "127.0.0.1", "--master-port", "29533",
            str(root / "tests" / "gpu_partition.py"), "ocp3d:16", "bnd3d:20", "ocp3d:32", "share_min_pivots=512", "share_min_flops=1e9"]
     r = subprocess.run(cmd, capture_output=True, text=True, timeout=600)
-    lines = [json.loads(l) for l in r.stdout.splitlines() if l.startswith("{")]
+    lines = [json.loads(l) for l in r.stdout.replace("}{", "}\n{").splitlines() if l.startswith("{")]
     assert r.returncode == 0, r.stdout[-2000:] + r.stderr[-2000:]
     assert len(lines) == 6 and all(l["ok"] for l in lines)
     assert any(l["shared_fronts"] > 0 for l in lines)        # the shared-front path ran, not only the subtree exchange
