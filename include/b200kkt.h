@@ -66,6 +66,9 @@ typedef struct b200kkt_stats {
    /* same option: time from the start of the factorization to the first shared batch (this rank's subtrees + transfers), and the
     * part of the factorization the main stream spent waiting for contribution blocks from other ranks */
    double t_before_shared_profiled, t_transfer_wait_profiled;
+   /* delayed pivots: columns moved into an ancestor front since the analysis, host re-plans since the analysis and during the
+    * last factorization (each re-plan is followed by a new factorization attempt) */
+   int64_t num_delayed_total, num_replans_total, num_replans_last;
 } b200kkt_stats;
 
 /* Handle life cycle.  Replaces JOB=-1 / JOB=-2 (MUMPSSolver.cpp:16-49).
@@ -94,7 +97,15 @@ int b200kkt_plan_partition(const b200kkt_handle* h, int32_t* owner, int8_t* shar
 
 /* Options (defaults need no user action).  Names: "ordering" (0 METIS, 1 natural),
  * "kkt_pairing", "relax_small", "relax_mid", "relax_big", "scaling_sweeps", "null_pivot_tol",
- * "refine_max_steps", "refine_tol", "use_graph", "profile_updates". */
+ * "refine_max_steps", "refine_tol", "use_graph", "profile_updates", and for the delayed pivots
+ * "delay_tol" (1e-14), "growth_limit" (0 = off), "max_replans" (8).
+ *
+ * Delayed pivots (what dmumps_c JOB=2 does with threshold pivoting; MUMPSSolver.cpp:85-89 with ICNTL(24)=1 at :36): the pivot
+ * search of a front is confined to its fully-summed block.  A column whose candidates there are all below null_pivot_tol is a
+ * zero eigenvalue only if the rest of its front column is below delay_tol as well; otherwise the factorization reports it, the
+ * host moves it into an ancestor front (same elimination order for everything else, plan rebuilt, values stay on the device) and
+ * factorizes again.  The moves persist, so later factorizations of the same pattern start from the adapted plan.
+ * b200kkt_get_permutation / plan getters return the adapted plan. */
 int b200kkt_set_option(b200kkt_handle* h, const char* name, double value);
 /* Optional user ordering for the next analyse (perm[new] = old, length N); NULL clears it. */
 int b200kkt_set_user_permutation(b200kkt_handle* h, const int64_t* perm, uint64_t n);
@@ -147,6 +158,9 @@ int b200kkt_plan_rows(const b200kkt_handle* h, int64_t* rows_off, int32_t* rows)
 /* Debug/parity: run scaling + assembly only and copy the assembled front pool (pool_doubles) and
  * the row scaling (length N, may be NULL) back to the host. */
 int b200kkt_debug_assemble(b200kkt_handle* h, const double* values, double* pool_out, double* scale_out);
+/* Debug/parity: move the pivot columns at `positions` (current numbering) into the parent front (further up on repeated calls for
+ * the same column), exactly as a factorization does for the columns it flags.  Works on host-only handles. */
+int b200kkt_debug_delay_columns(b200kkt_handle* h, uint64_t count, const int64_t* positions);
 /* Debug/parity: after factorize, copy back the factored pool, D (diag, offdiag: length N each, new
  * numbering incl. in-front pivoting), pivot types (0 1x1, 1/2 first/second of 2x2, 3 null) and the
  * in-front pivot permutation.  Any pointer may be NULL. */

@@ -100,11 +100,14 @@ def bk_block(B, n, tol):
 
 
 class EmulatedFactorization:
-    def __init__(self, plan, perm, scatter, kkt, values, sweeps=3, null_tol=1e-14, defer=False):
+    def __init__(self, plan, perm, scatter, kkt, values, sweeps=3, null_tol=1e-14, defer=False, delay_tol=1e-14, growth_limit=0.0):
         self.plan = plan
         self.perm = np.asarray(perm)
         self.n = kkt.dim
         self.null_tol = null_tol
+        self.delay_tol = delay_tol
+        self.growth_limit = growth_limit
+        self.delayed = []            # plan columns flagged for a delay (kernels.cu: flag_delay)
         self.scale = equilibrate(kkt, values, sweeps)
         nsn = plan["num_fronts"]
         pool = np.zeros(plan["pool_doubles"])
@@ -172,6 +175,15 @@ class EmulatedFactorization:
                 D = np.diag(d) + np.diag(e[:-1], -1) + np.diag(e[:-1], 1)
                 Lm = np.linalg.solve(D, Wm.T).T
                 null = ty == 3
+                # a null pivot whose column still has entries outside the block is not null: the column has to leave the front
+                if Wm.shape[0] > 0:
+                    for c in np.flatnonzero(null):
+                        if np.max(np.abs(Wm[:, c])) > self.delay_tol:
+                            self.delayed.append(int(first[s] + lp[j0 + c]))
+                    if self.growth_limit > 0:
+                        for c in np.flatnonzero(~null):
+                            if np.max(np.abs(Lm[:, c])) > self.growth_limit:
+                                self.delayed.append(int(first[s] + lp[j0 + c]))
                 Lm[:, null] = 0.0
                 Wm[:, null] = 0.0
                 F[j0:j1, j0:j1] = np.tril(B, -1) + np.diag(d)
@@ -256,6 +268,22 @@ class EmulatedFactorization:
         x = np.zeros(self.n)
         x[self.perm] = xg
         return x * self.scale
+
+
+def factor_with_delays(solver, kkt, values, max_replans=8, **kw):
+    """The library's run_factor loop (solver.cpp) on the emulation: factorize, move the flagged columns into ancestor fronts
+    through the library's own re-plan (b200kkt_debug_delay_columns), factorize again.  Returns (emulation, number of re-plans)."""
+    replans = 0
+    while True:
+        perm, scat = solver.permutation()
+        emu = EmulatedFactorization(solver.plan(), perm, scat, kkt, values, **kw)
+        plan = emu.plan
+        sn_of = np.searchsorted(plan["first_col"], np.asarray(emu.delayed, dtype=np.int64), side="right") - 1
+        cols = [q for q, s in zip(emu.delayed, sn_of) if plan["parent"][s] >= 0]
+        if not cols or replans >= max_replans:
+            return emu, replans
+        solver.debug_delay_columns(sorted(set(cols)))
+        replans += 1
 
 
 class PartitionedEmulation(EmulatedFactorization):

@@ -20,7 +20,7 @@ EXPORTED_SYMBOLS = [
     "b200kkt_solve_device", "b200kkt_get_permutation", "b200kkt_get_stats", "b200kkt_last_error", "b200kkt_plan_sizes",
     "b200kkt_plan_fronts", "b200kkt_plan_rows", "b200kkt_debug_assemble", "b200kkt_debug_factor", "b200kkt_get_stream",
     "b200kkt_debug_bench_update", "b200kkt_debug_phase_cycles", "b200kkt_debug_bench_bk",
-    "b200kkt_comm_unique_id", "b200kkt_comm_init", "b200kkt_plan_partition",
+    "b200kkt_comm_unique_id", "b200kkt_comm_init", "b200kkt_plan_partition", "b200kkt_debug_delay_columns",
 ]
 
 
@@ -41,6 +41,7 @@ class Stats(C.Structure):
         ("comm_bytes_factor", C.c_int64), ("comm_bytes_sweep", C.c_int64),
         ("t_shared_profiled", C.c_double), ("flops_shared_profiled", C.c_double), ("t_shared_stall_profiled", C.c_double),
         ("t_before_shared_profiled", C.c_double), ("t_transfer_wait_profiled", C.c_double),
+        ("num_delayed_total", C.c_int64), ("num_replans_total", C.c_int64), ("num_replans_last", C.c_int64),
     ]
 
     def as_dict(self):
@@ -81,6 +82,7 @@ def load_library():
     lib.b200kkt_plan_rows.argtypes = [H, C.c_void_p, C.c_void_p]
     lib.b200kkt_debug_assemble.argtypes = [H, C.c_void_p, C.c_void_p, C.c_void_p]
     lib.b200kkt_debug_factor.argtypes = [H] + [C.c_void_p] * 5
+    lib.b200kkt_debug_delay_columns.argtypes = [H, C.c_uint64, C.c_void_p]
     lib.b200kkt_comm_unique_id.argtypes = [C.c_void_p]
     lib.b200kkt_comm_init.argtypes = [H, C.c_int, C.c_int, C.c_void_p]
     lib.b200kkt_plan_partition.argtypes = [H, C.c_void_p, C.c_void_p, P(C.c_int64), C.c_void_p, C.c_void_p, P(C.c_double)]
@@ -271,6 +273,10 @@ class KKTSolver:
         self._check(self._lib.b200kkt_plan_rows(self._h, _ptr(rows_off), _ptr(rows)), "plan_rows")
         out.update(k=k, f=f, ld=ld, pool_offset=off, parent=parent, level=level, first_col=first, rows_off=rows_off, rows=rows)
         return out
+
+    def debug_delay_columns(self, positions):
+        p = np.ascontiguousarray(positions, dtype=np.int64)
+        self._check(self._lib.b200kkt_debug_delay_columns(self._h, p.size, _ptr(p)), "debug_delay_columns")
 
     def debug_assemble(self, values, want_scale=True):
         v = np.ascontiguousarray(values, dtype=np.float64)

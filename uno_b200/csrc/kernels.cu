@@ -214,6 +214,11 @@ __device__ __forceinline__ void dmma8x8x4(double& c0, double& c1, const double a
    asm volatile("mma.sync.aligned.m8n8k4.row.col.f64.f64.f64.f64 {%0,%1}, {%2}, {%3}, {%0,%1};\n" : "+d"(c0), "+d"(c1) : "d"(a), "d"(b));
 }
 
+// a pivot column that has to leave its front (see FactorArrays::delay); counted once
+__device__ __forceinline__ void flag_delay(const FactorArrays& W, const int plan_col) {
+   if (atomicExch(W.delay + plan_col, 1) == 0) atomicAdd(W.ndelay, 1);
+}
+
 struct alignas(16) BkShared {
    double B[NBI][NBI + 2];   // full symmetric diagonal block (rows 16-byte aligned); after factorization: strict lower = L11
    double d[NBI], e[NBI];
@@ -375,52 +380,13 @@ __device__ void bk_factor_block(BkShared& S, const int n, const int lane, const 
    __syncwarp();
 }
 
-// Lane t computes column t of X = L11^{-1} (unit lower triangular, strict lower part in S.B) by forward
-// substitution, then X2 = D^{-1} X (1x1 and 2x2 blocks; null pivots give zero rows in both).  Results go to
-// shared memory ([c][t], row stride NBI + 1) and, row-major 32 x 32 each, to the front's scratch for kernel B.
-__device__ void invert_block(const BkShared& S, const int n, const int t, double* Xs, double* X2s, double* Xg) {
-   double x[NBI];
-#pragma unroll
-   for (int i = 0; i < NBI; ++i) x[i] = (i == t) ? 1.0 : 0.0;
-#pragma unroll
-   for (int j = 0; j < NBI - 1; ++j) {
-      const double xj = x[j];
-#pragma unroll
-      for (int i = j + 1; i < NBI; ++i) x[i] = fma(-S.B[i][j], xj, x[i]);   // S.B[i][j] = 0 above the diagonal of L? no: strict lower only is read
-   }
-   double x2[NBI];
-#pragma unroll
-   for (int i = 0; i < NBI; ++i) {
-      const int ty = S.type[i];
-      if (ty == 0) {
-         x2[i] = x[i] / S.d[i];
-      } else if (ty == 1) {
-         if (i + 1 < NBI) {
-            const double a = S.d[i], b = S.e[i], c = S.d[i + 1];
-            const double det = a * c - b * b;
-            x2[i] = (c * x[i] - b * x[i + 1]) / det;
-            x2[i + 1] = (a * x[i + 1] - b * x[i]) / det;
-         }
-      } else if (ty == 3) {
-         x[i] = 0.0;
-         x2[i] = 0.0;
-      }
-   }
-#pragma unroll
-   for (int i = 0; i < NBI; ++i) {
-      const bool in = i < n && t < n;
-      const double v = in ? x[i] : 0.0, v2 = in ? x2[i] : 0.0;
-      Xs[i * (NBI + 1) + t] = v;
-      X2s[i * (NBI + 1) + t] = v2;
-      Xg[i * NBI + t] = v;
-      Xg[NBI * NBI + i * NBI + t] = v2;
-   }
-}
-
 // Row-per-thread triangular solve against one factored NBI x NBI diagonal block held in shared memory:
 //   w <- w L11^{-T},  l = w D^{-1}   (null pivots: both zero)
-__device__ __forceinline__ void row_trsm(double (&w)[NBI], double (&l)[NBI], const double (*L11)[NBI + 1], const double* sd, const double* se,
-                                         const int* stype) {
+// Returns a bit mask of the block's pivot positions that must be delayed because of this row: a null pivot whose Schur entry in
+// this row is above delay_tol, or (growth guard) an L entry above growth_limit.
+__device__ __forceinline__ unsigned row_trsm(double (&w)[NBI], double (&l)[NBI], const double (*L11)[NBI + 1], const double* sd, const double* se,
+                                             const int* stype, const double delay_tol, const double growth_limit) {
+   unsigned mask = 0u;
    // right-looking order: once w[t] is final it is eliminated from all later columns at once, so the
    // dependent chain is NBI fused multiply-adds long instead of NBI^2 / 2
 #pragma unroll
@@ -442,10 +408,16 @@ __device__ __forceinline__ void row_trsm(double (&w)[NBI], double (&l)[NBI], con
             l[c + 1] = (a * w[c + 1] - b * w[c]) / det;
          }
       } else if (ty == 3) {
+         if (fabs(w[c]) > delay_tol) mask |= 1u << c;
          l[c] = 0.0;
          w[c] = 0.0;
       }
    }
+   if (growth_limit > 0.0) {
+#pragma unroll
+      for (int c = 0; c < NBI; ++c) if (fabs(l[c]) > growth_limit) mask |= 1u << c;
+   }
+   return mask;
 }
 
 // ------------------------------------------------------------------------------------------------
@@ -641,7 +613,7 @@ __device__ void bk_factor_block4(Bk4Shared& S, const int n, const int tid, const
 }
 
 // X (rows of the inverse in registers) -> X2 = D^{-1} X; both to shared memory ([c][t], row stride XB_LD) for the
-// update group and, row-major NBI x NBI each, to the front's scratch for kernel B.  Null pivots: zero rows.
+// update group and, row-major NBI x NBI each, to the front's scratch for kernel B.  Null pivots: zero row in X2 only.
 __device__ void publish_inverse(const Bk4Shared& S, const int n, const int tid, double (&x)[8], double* Xx, double* Xl, double* Xg) {
    const int lane = tid & 31, c0 = 8 * (tid >> 5);
    const int ty = S.type[lane];
@@ -655,7 +627,7 @@ __device__ void publish_inverse(const Bk4Shared& S, const int n, const int tid, 
       if (ty == 0) v2 = v / pa;
       else if (ty == 1) v2 = (pc * v - pb * dn) / det;
       else if (ty == 2) v2 = (pa * v - pb * up) / det;
-      else { v = 0.0; v2 = 0.0; }
+      else v2 = 0.0;   // null pivot: X keeps its row (w = a X^T is then the column's Schur entry, tested for a delay), X2 = 0
       if (lane >= n || c0 + c >= n) { v = 0.0; v2 = 0.0; }
       Xx[lane * XB_LD + c0 + c] = v;
       Xl[lane * XB_LD + c0 + c] = v2;
@@ -666,15 +638,18 @@ __device__ void publish_inverse(const Bk4Shared& S, const int n, const int tid, 
 
 constexpr int DP_THREADS = 256;
 constexpr int DP_LD = NBO - NBI + 4;   // rows of the in-panel W/L staging ([c][row]); DP_LD mod 16 == 4: conflict-free fragments
+constexpr int DP_PB = 2 * NBI + 1;     // per buffer: pivot order of the block, its "nontrivial" flag, its pivot types
 constexpr int DP_SMEM = static_cast<int>((sizeof(Bk4Shared) + 15) & ~size_t(15)) +
-                        (4 * NBI * XB_LD + 2 * NBI * DP_LD) * static_cast<int>(sizeof(double)) + 2 * (NBI + 1) * static_cast<int>(sizeof(int)) + 16;
+                        (4 * NBI * XB_LD + 2 * NBI * DP_LD) * static_cast<int>(sizeof(double)) + 2 * DP_PB * static_cast<int>(sizeof(int)) + 16;
 
 // rows [row0, row0 + 8 MT) of the diagonal block against the inner block at j0: w = a X^T, l = a X2^T with
 // a = A[row, j0 + p[.]] (the block's pivot order); results to the staging (row index rel0 + ...) and l to the factor panel
 template <int MT>
 __device__ __forceinline__ void panel_rows_trsm(double* __restrict__ A, const int ld, const int row0, const int rowend, const int j0, const int nbw,
                                                 const int* __restrict__ pb, const double* __restrict__ Xx, const double* __restrict__ Xl,
-                                                double* __restrict__ Ws, double* __restrict__ Ls, const int rel0, const int lane) {
+                                                double* __restrict__ Ws, double* __restrict__ Ls, const int rel0, const int lane,
+                                                const FactorArrays& W, const int colbase) {
+   const int* __restrict__ tyb = pb + NBI + 1;   // pivot types of the block
    const int g = lane >> 2, q = lane & 3;
    double af[MT][8];
 #pragma unroll
@@ -711,7 +686,15 @@ __device__ __forceinline__ void panel_rows_trsm(double* __restrict__ A, const in
 #pragma unroll
          for (int e = 0; e < 2; ++e) {
             const int cc = 8 * nt + 2 * q + e, rel = rel0 + 8 * mt + g;
-            Ws[cc * DP_LD + rel] = cw[mt][e];
+            double wv = cw[mt][e];
+            const bool rin = row0 + 8 * mt + g < rowend && cc < nbw;
+            if (tyb[cc] == 3) {
+               if (rin && fabs(wv) > W.delay_tol) flag_delay(W, colbase + pb[cc]);
+               wv = 0.0;
+            } else if (rin && W.growth_limit > 0.0 && fabs(cl[mt][e]) > W.growth_limit) {
+               flag_delay(W, colbase + pb[cc]);
+            }
+            Ws[cc * DP_LD + rel] = wv;
             Ls[cc * DP_LD + rel] = cl[mt][e];
          }
    }
@@ -731,7 +714,7 @@ __global__ void __launch_bounds__(DP_THREADS) k_diagpanel(FrontArrays F, const i
    double* XB = reinterpret_cast<double*>(dp_smem + ((sizeof(Bk4Shared) + 15) & ~size_t(15)));   // [buffer][X | X2][c][t]
    double* Ws = XB + 4 * NBI * XB_LD;                                                           // [c][row]
    double* Ls = Ws + NBI * DP_LD;
-   int* pbuf = reinterpret_cast<int*>(Ls + NBI * DP_LD);   // [buffer][NBI + 1]: pivot order of the block, then its "nontrivial" flag
+   int* pbuf = reinterpret_cast<int*>(Ls + NBI * DP_LD);   // [buffer][DP_PB]: pivot order of the block, its "nontrivial" flag, its pivot types
    const int s = list[blockIdx.x];
    const int k = F.k[s], ld = F.ld[s], first = F.first[s];
    const int J1 = min(J0 + NBO, k);
@@ -774,8 +757,8 @@ __global__ void __launch_bounds__(DP_THREADS) k_diagpanel(FrontArrays F, const i
             W.ptype[q] = S.type[tid];
             W.lperm[q] = j0 + S.p[tid];
          }
-         int* pb = pbuf + (b & 1) * (NBI + 1);
-         if (tid < NBI) pb[tid] = S.p[tid];
+         int* pb = pbuf + (b & 1) * DP_PB;
+         if (tid < NBI) { pb[tid] = S.p[tid]; pb[NBI + 1 + tid] = (tid < nbw) ? S.type[tid] : 0; }
          if (tid == 0) { W.blkflag[first + j0] = S.nontrivial; pb[NBI] = S.nontrivial; }
          named_arrive<2, DP_THREADS>();
       }
@@ -789,10 +772,10 @@ __global__ void __launch_bounds__(DP_THREADS) k_diagpanel(FrontArrays F, const i
          named_sync<2, DP_THREADS>();
          const double* Xx = XB + (b & 1) * 2 * NBI * XB_LD;
          const double* Xl = Xx + NBI * XB_LD;
-         const int* pb = pbuf + (b & 1) * (NBI + 1);
+         const int* pb = pbuf + (b & 1) * DP_PB;
          if (rem > 0) {
             // the next NBI rows first: 8 per warp
-            panel_rows_trsm<1>(A, ld, j1 + 8 * ww, J1, j0, nbw, pb, Xx, Xl, Ws, Ls, 8 * ww, lane);
+            panel_rows_trsm<1>(A, ld, j1 + 8 * ww, J1, j0, nbw, pb, Xx, Xl, Ws, Ls, 8 * ww, lane, W, first + j0);
             named_sync<4, BK4_THREADS>();
             {
                // next inner block: S.B = A[j1.., j1..] - Ws Ls^T, exactly symmetric (the lower triangle is mirrored)
@@ -829,7 +812,7 @@ __global__ void __launch_bounds__(DP_THREADS) k_diagpanel(FrontArrays F, const i
             named_arrive<3, DP_THREADS>();
             // the remaining rows, 32 per warp pass
             for (int slab = 1 + ww; 32 * slab < rem; slab += 4)
-               panel_rows_trsm<4>(A, ld, j1 + 32 * slab, J1, j0, nbw, pb, Xx, Xl, Ws, Ls, 32 * slab, lane);
+               panel_rows_trsm<4>(A, ld, j1 + 32 * slab, J1, j0, nbw, pb, Xx, Xl, Ws, Ls, 32 * slab, lane, W, first + j0);
             named_sync<4, BK4_THREADS>();
             // rank-NBI update of the rest of the diagonal block: 32 x 32 tiles of the lower triangle, tile (0,0) is done
             const int T32 = (rem + 31) >> 5;
@@ -978,7 +961,12 @@ __global__ void __launch_bounds__(TP_THREADS) k_trsmpanel(FrontArrays F, const i
             }
          }
       }
-      row_trsm(w, l, L11, sd, se, stype);
+      unsigned dmask = row_trsm(w, l, L11, sd, se, stype, W.delay_tol, W.growth_limit);
+      while (dmask) {
+         const int c = __ffs(dmask) - 1;
+         dmask &= dmask - 1u;
+         if (c < nbw) flag_delay(W, first + j0 + sp[c]);
+      }
 #pragma unroll
       for (int c = 0; c < NBI; ++c) {
          if (c < nbw) {
@@ -1000,7 +988,7 @@ constexpr int TD_LDW = NBO + 4;          // row stride of Wsm: 4 mod 16 -> confl
 constexpr int TD_LDP = NBO - NBI + 4;    // row stride of the staged L rows of the block
 constexpr int TD_LDT = NBI + 4;          // row stride of T, X, X2
 constexpr int TD_SMEM = static_cast<int>(sizeof(double)) * (TD_ROWS * TD_LDW + NBI * TD_LDP + TD_ROWS * TD_LDT + 2 * NBI * TD_LDT) +
-                        NBI * static_cast<int>(sizeof(int));
+                        2 * NBI * static_cast<int>(sizeof(int));
 
 __global__ void __launch_bounds__(TD_THREADS) k_trsmpanel_mma(FrontArrays F, const int* __restrict__ list, const int J0, FactorArrays W) {
    extern __shared__ __align__(16) unsigned char td_smem[];
@@ -1010,6 +998,7 @@ __global__ void __launch_bounds__(TD_THREADS) k_trsmpanel_mma(FrontArrays F, con
    double* Xb = T + TD_ROWS * TD_LDT;                                // [c][t]: X = L11^{-1}
    double* X2b = Xb + NBI * TD_LDT;                                  // D^{-1} X
    int* sp = reinterpret_cast<int*>(X2b + NBI * TD_LDT);
+   int* sty = sp + NBI;
    const int s = list[blockIdx.x];
    const int k = F.k[s], f = F.f[s], ld = F.ld[s], first = F.first[s];
    const int J1 = min(J0 + NBO, k);
@@ -1023,7 +1012,10 @@ __global__ void __launch_bounds__(TD_THREADS) k_trsmpanel_mma(FrontArrays F, con
       const int nbw = min(NBI, k - j0);
       const int kprev = j0 - J0;
       __syncthreads();
-      if (tid < NBI) sp[tid] = (tid < nbw) ? (W.lperm[first + j0 + tid] - j0) : tid;
+      if (tid < NBI) {
+         sp[tid] = (tid < nbw) ? (W.lperm[first + j0 + tid] - j0) : tid;
+         sty[tid] = (tid < nbw) ? W.ptype[first + j0 + tid] : 0;
+      }
       __syncthreads();
       // stage: inverted diagonal block, the block rows' earlier L entries, the CTA's rows of the block columns (pivot order)
       {
@@ -1123,10 +1115,19 @@ __global__ void __launch_bounds__(TD_THREADS) k_trsmpanel_mma(FrontArrays F, con
 #pragma unroll
             for (int h = 0; h < 2; ++h) {
                const int c = b * 8 + 2 * (lane & 3) + h;
-               Wsm[r * TD_LDW + kprev + c] = aw[a][b][h];
-               if (i < f && c < nbw) {
+               double wv = aw[a][b][h];
+               const bool in = i < f && c < nbw;
+               if (sty[c] == 3) {
+                  // null pivot: X kept its row, so w is the column's Schur entry in this row
+                  if (in && fabs(wv) > W.delay_tol) flag_delay(W, first + j0 + sp[c]);
+                  wv = 0.0;
+               } else if (in && W.growth_limit > 0.0 && fabs(al[a][b][h]) > W.growth_limit) {
+                  flag_delay(W, first + j0 + sp[c]);
+               }
+               Wsm[r * TD_LDW + kprev + c] = wv;
+               if (in) {
                   A[i + static_cast<int64_t>(ld) * (j0 + c)] = al[a][b][h];
-                  Wp[i + static_cast<int64_t>(ld) * (kprev + c)] = aw[a][b][h];
+                  Wp[i + static_cast<int64_t>(ld) * (kprev + c)] = wv;
                }
             }
       }

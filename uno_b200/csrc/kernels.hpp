@@ -58,6 +58,14 @@ struct FactorArrays {
    int* ptype;       // 0: 1x1, 1/2: first/second column of a 2x2, 3: null pivot (row/column dropped)
    int* lperm;       // pivot position q = first+j holds original local column lperm[q] (0..k)
    int* blkflag;     // per inner block (indexed by its first pivot position): non-identity permutation
+   // delayed pivots: delay[c] = 1 when plan column c (current numbering) could not be eliminated inside its front - every
+   // fully-summed candidate in its pivot block is below the null-pivot tolerance while the column still has entries above
+   // delay_tol in rows outside the block (or an L entry above growth_limit, when that guard is on); *ndelay counts them.
+   // The host then moves these columns into an ancestor front and factorizes again (solver.cpp: run_factor).
+   int* delay;
+   int* ndelay;
+   double delay_tol;
+   double growth_limit;   // 0: guard off
 };
 
 // K1' equilibration sweep (power-of-two Ruiz step) and K-infinity norm

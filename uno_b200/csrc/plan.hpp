@@ -70,6 +70,12 @@ struct Plan {
    std::vector<int32_t> csr_col;    // 2*nnz - ndiag
    std::vector<int32_t> csr_slot;
 
+   // kept for re-planning with delayed pivots: symmetric off-diagonal adjacency (original numbering, sorted, unique) and the
+   // COO pattern in 32-bit indices
+   std::vector<int64_t> adj_ptr;
+   std::vector<int32_t> adj_idx;
+   std::vector<int32_t> coo_row, coo_col;
+
    // exact work figures
    int64_t nnz_L = 0;               // sum k*f - k(k-1)/2
    double flops = 0.0;              // sum k^3/3 + k^2 r + k r^2
@@ -99,6 +105,12 @@ struct Plan {
 // Throws std::runtime_error on malformed input (index out of range, lower-triangular entry).
 void analyse(int64_t N, int64_t nnz, int64_t reg_size, int64_t num_primal,
              const uint64_t* row, const uint64_t* col, const AnalyseOptions& opt, Plan& plan);
+
+// Rebuilds everything that follows from (P.perm, P.sn_first, P.nsn); see symbolic.cpp.
+void build_structures(Plan& plan);
+// Delayed pivots: the columns at positions cols[i] (current numbering) move into the ancestor front up[i] levels above their own
+// and become its last pivots; the plan is rebuilt.  map_subtrees must be called again afterwards.
+void delay_columns(Plan& plan, const std::vector<int32_t>& cols, const std::vector<int32_t>& up);
 
 // Proportional mapping of the assembly tree onto `parts` ranks: the tree is opened from the roots (heaviest subtree first)
 // until the open subtrees can be packed evenly, the subtrees are packed by decreasing flop count (LPT), and every front above

@@ -572,7 +572,9 @@ void upload_plan(b200kkt_handle* h) {
    h->W.ptype = dev_alloc<int>(h, n + 1);
    h->W.lperm = dev_alloc<int>(h, n + 1);
    h->W.blkflag = dev_alloc<int>(h, n + 1);
-   h->d_values = dev_alloc<double>(h, static_cast<size_t>(P.nnz));
+   h->W.delay = dev_alloc<int>(h, n + 1);
+   if (h->keep_values != nullptr) { h->d_values = h->keep_values; h->plan_allocs.push_back(h->keep_values); h->keep_values = nullptr; }
+   else h->d_values = dev_alloc<double>(h, static_cast<size_t>(P.nnz));
    h->d_scale = dev_alloc<double>(h, n);
    h->d_scale_tmp = dev_alloc<double>(h, n);
    h->d_zg = dev_alloc<double>(h, n);
@@ -583,6 +585,7 @@ void upload_plan(b200kkt_handle* h) {
    h->d_x = dev_alloc<double>(h, n);
    h->d_r = dev_alloc<double>(h, n);
    h->d_counters = dev_alloc<int>(h, 8);
+   h->W.ndelay = h->d_counters + 5;
    h->d_norms = dev_alloc<unsigned long long>(h, 4);
    h->d_scale_final = h->d_scale;
    build_cut_schedule(h);
@@ -614,6 +617,10 @@ void enqueue_factor(b200kkt_handle* h) {
    const Plan& P = h->plan;
    cudaStream_t st = h->stream;
    int64_t& L = h->launches;
+   h->W.delay_tol = h->delay_tol;
+   h->W.growth_limit = h->growth_limit;
+   CK(cudaMemsetAsync(h->d_counters, 0, 8 * sizeof(int), st));
+   CK(cudaMemsetAsync(h->W.delay, 0, static_cast<size_t>(P.N) * sizeof(int), st));
    // K1' equilibration
    L += launch_fill(h->d_scale, P.N, 1.0, st);
    double* cur = h->d_scale;
@@ -778,8 +785,7 @@ void enqueue_factor(b200kkt_handle* h) {
       CK(cudaEventRecord(h->ev_level_done, h->comm_stream));
       CK(cudaStreamWaitEvent(h->stream, h->ev_level_done, 0));
    }
-   // K6 inertia (partitioned: this rank's pivots, then summed over ranks)
-   CK(cudaMemsetAsync(h->d_counters, 0, 8 * sizeof(int), st));
+   // K6 inertia (partitioned: this rank's pivots, then summed over ranks); counter 5 = columns flagged for a delay
    L += launch_inertia(P.N, h->W, h->d_counters, st, h->partitioned() ? h->d_col_owner : nullptr, h->rank);
    if (h->partitioned()) CKN(comm_allreduce_sum_i32(h->comm, h->d_counters, 8, st, e__));
    CK(cudaMemcpyAsync(h->h_counters, h->d_counters, 8 * sizeof(int), cudaMemcpyDeviceToHost, st));
@@ -796,7 +802,7 @@ double bits_to_double(unsigned long long b) {
 }
 
 // run the numeric factorization on values already resident in h->d_values
-void run_factor(b200kkt_handle* h) {
+void run_factor_once(b200kkt_handle* h) {
    cudaStream_t st = h->stream;
    CK(cudaEventRecord(h->ev0, st));
    // partitioned: NCCL calls between the levels are launched directly unless partition_graph asks for their capture too
@@ -858,6 +864,69 @@ void run_factor(b200kkt_handle* h) {
    h->inertia[1] = static_cast<uint64_t>(h->h_counters[1]);
    h->inertia[2] = static_cast<uint64_t>(h->h_counters[2]);
    h->factorized = true;
+}
+
+// Move the given columns (positions in the current numbering) into ancestor fronts and rebuild plan, schedules and device
+// arrays; the resident values stay.  How far a column travels grows with the number of times it has been delayed before:
+// parent, then 4 levels, then the root of its tree (where every row is fully summed and the verdict is final).
+void replan_with_delays(b200kkt_handle* h, const std::vector<int32_t>& cols) {
+   Plan& P = h->plan;
+   if (h->delay_count.size() != static_cast<size_t>(P.N)) h->delay_count.assign(static_cast<size_t>(P.N), 0);
+   std::vector<int32_t> up(cols.size());
+   for (size_t i = 0; i < cols.size(); ++i) {
+      unsigned char& c = h->delay_count[static_cast<size_t>(P.perm[cols[i]])];
+      up[i] = (c == 0) ? 1 : ((c == 1) ? 4 : (1 << 30));
+      if (c < 255) ++c;
+   }
+   const double t_order = P.t_order;
+   const std::string ordering_used = P.ordering_used;
+   const int64_t num_pairs = P.num_pairs;
+   delay_columns(P, cols, up);
+   P.t_order = t_order; P.ordering_used = ordering_used; P.num_pairs = num_pairs;
+   P.share_min_pivots = h->share_min_pivots;
+   P.share_min_flops = h->share_min_flops;
+   map_subtrees(P, h->num_gpus, h->share_top_fronts != 0);
+   const bool resident = h->values_resident;
+   if (h->has_device) {
+      CK(cudaStreamSynchronize(h->stream));
+      // keep the value array: take it out of the list free_plan_device walks
+      for (auto it = h->plan_allocs.begin(); it != h->plan_allocs.end(); ++it)
+         if (*it == h->d_values) { h->plan_allocs.erase(it); break; }
+      h->keep_values = h->d_values;
+      free_plan_device(h);
+   }
+   const double t_upload = h->stats.t_upload;
+   fill_plan_stats(h);
+   if (h->has_device) {
+      upload_plan(h);
+      h->stats.t_upload += t_upload;
+   }
+   h->analysed = true;
+   h->values_resident = resident;
+   h->delayed_total += static_cast<int64_t>(cols.size());
+   ++h->replans_total;
+}
+
+void run_factor(b200kkt_handle* h) {
+   h->replans_last = 0;
+   for (int attempt = 0;; ++attempt) {
+      run_factor_once(h);
+      const int flagged = h->h_counters[5];
+      if (flagged <= 0 || attempt >= h->max_replans) break;
+      // columns that could not be eliminated in their fronts: collect, re-plan, factorize again
+      const Plan& P = h->plan;
+      cudaStream_t st = h->stream;
+      if (h->partitioned()) CKN(comm_allreduce_sum_i32(h->comm, h->W.delay, static_cast<size_t>(P.N), st, e__));
+      std::vector<int> flags(static_cast<size_t>(P.N));
+      CK(cudaMemcpyAsync(flags.data(), h->W.delay, flags.size() * sizeof(int), cudaMemcpyDeviceToHost, st));
+      CK(cudaStreamSynchronize(st));
+      std::vector<int32_t> cols;
+      for (int64_t q = 0; q < P.N; ++q)
+         if (flags[static_cast<size_t>(q)] != 0 && P.parent[P.sn_of[q]] >= 0) cols.push_back(static_cast<int32_t>(q));
+      if (cols.empty()) break;   // only root fronts: the null pivots are final
+      replan_with_delays(h, cols);
+      ++h->replans_last;
+   }
 }
 
 }  // namespace
@@ -1157,6 +1226,9 @@ int b200kkt_set_option(b200kkt_handle* h, const char* name, double value) {
    else if (n == "metis_ufactor") h->aopt.metis_ufactor = static_cast<int>(value);
    else if (n == "scaling_sweeps") h->scaling_sweeps = std::max(0, static_cast<int>(value));
    else if (n == "null_pivot_tol") h->null_pivot_tol = value;
+   else if (n == "delay_tol") h->delay_tol = value;
+   else if (n == "growth_limit") h->growth_limit = value;
+   else if (n == "max_replans") h->max_replans = std::max(0, static_cast<int>(value));
    else if (n == "refine_max_steps") h->refine_max_steps = std::max(0, static_cast<int>(value));
    else if (n == "refine_tol") h->refine_tol = value;
    else if (n == "use_graph") h->use_graph = static_cast<int>(value);
@@ -1194,6 +1266,8 @@ int b200kkt_analyse(b200kkt_handle* h, uint64_t n, uint64_t nnz, uint64_t reg_si
    if (h == nullptr || (nnz > 0 && (row == nullptr || col == nullptr))) return B200KKT_EINVAL;
    if (h->has_device) { cudaSetDevice(h->device); free_plan_device(h); }
    h->analysed = false;
+   h->delay_count.clear();
+   h->delayed_total = h->replans_total = h->replans_last = 0;
    if (h->has_device && h->partitioned() && !h->comm.active())
       return fail(h, B200KKT_EINVAL, "multi-GPU handle: b200kkt_comm_init must be called before b200kkt_analyse");
    const int rc = guarded(h, [&] {
@@ -1300,6 +1374,9 @@ int b200kkt_get_stats(const b200kkt_handle* h, b200kkt_stats* stats) {
    stats->comm_bytes_factor = h->comm_bytes_factor;
    stats->comm_bytes_sweep = h->comm_bytes_solve;
    if (h->factorized) { stats->num_null_pivots_last = h->h_counters[2]; stats->num_two_by_two_last = h->h_counters[3]; }
+   stats->num_delayed_total = h->delayed_total;
+   stats->num_replans_total = h->replans_total;
+   stats->num_replans_last = h->replans_last;
    return B200KKT_OK;
 }
 
@@ -1370,6 +1447,21 @@ int b200kkt_debug_assemble(b200kkt_handle* h, const double* values, double* pool
       if (scale_out != nullptr) CK(cudaMemcpyAsync(scale_out, cur, static_cast<size_t>(P.N) * sizeof(double), cudaMemcpyDeviceToHost, st));
       CK(cudaStreamSynchronize(st));
       CK(cudaGetLastError());
+   });
+}
+
+int b200kkt_debug_delay_columns(b200kkt_handle* h, uint64_t count, const int64_t* positions) {
+   if (h == nullptr || (count > 0 && positions == nullptr)) return B200KKT_EINVAL;
+   if (!h->analysed) return fail(h, B200KKT_EINVAL, "debug_delay_columns before analyse");
+   return guarded(h, [&] {
+      if (h->has_device) CK(cudaSetDevice(h->device));
+      std::vector<int32_t> cols;
+      for (uint64_t i = 0; i < count; ++i) {
+         if (positions[i] < 0 || positions[i] >= h->plan.N) throw std::runtime_error("debug_delay_columns: position out of range");
+         if (h->plan.parent[h->plan.sn_of[positions[i]]] >= 0) cols.push_back(static_cast<int32_t>(positions[i]));
+      }
+      if (!cols.empty()) replan_with_delays(h, cols);
+      h->factorized = false;
    });
 }
 

@@ -47,6 +47,14 @@ struct b200kkt_handle {
    std::vector<int64_t> user_perm;
    int scaling_sweeps = 3;
    double null_pivot_tol = 1e-14;
+   // delayed pivots (kernels.hpp: FactorArrays::delay): a column that cannot be eliminated inside its front is moved into an
+   // ancestor front by re-planning on the host and the factorization is repeated; the moves persist for later factorizations
+   double delay_tol = 1e-14;         // scaled Schur entry outside the pivot block above which a null pivot is not null but delayed
+   double growth_limit = 0.0;        // > 0: also delay a column with an L entry above this (guard against unbounded growth)
+   int max_replans = 8;              // per factorization; beyond it the remaining columns are reported as null pivots
+   std::vector<unsigned char> delay_count;   // per ORIGINAL column: times delayed so far (1st: parent, 2nd: 4 levels, then the root)
+   int64_t delayed_total = 0, replans_total = 0, replans_last = 0;
+   double* keep_values = nullptr;    // the resident value array survives a re-plan
    int refine_max_steps = 6;
    double refine_tol = 1e-15;
    int use_graph = 1;

@@ -522,6 +522,27 @@ void analyse(int64_t N, int64_t nnz, int64_t reg_size, int64_t num_primal, const
       P.nsn = nsn;
    }
    P.perm = final_order;
+   // kept for re-planning (delayed pivots): the adjacency and the COO pattern in 32-bit indices
+   P.adj_ptr = std::move(g.ptr);
+   P.adj_idx = std::move(g.idx);
+   P.coo_row.resize(static_cast<size_t>(nnz));
+   P.coo_col.resize(static_cast<size_t>(nnz));
+   for (int64_t e = 0; e < nnz; ++e) { P.coo_row[e] = static_cast<int32_t>(row[e]); P.coo_col[e] = static_cast<int32_t>(col[e]); }
+   build_structures(P);
+   P.t_symbolic = secs(t1, clk::now()) - P.t_maps;   // etree, supernodes and front structures; the maps are timed apart
+}
+
+// Everything that follows from the elimination order and the supernode partition (P.perm, P.sn_first, P.nsn): front row
+// structures, extend-add maps, level schedule, pool layout, work figures, the assembly scatter map and the CSR of the residual.
+// Valid for ANY partition of the order into contiguous column ranges (a front is treated as dense), which is what lets the
+// numeric phase move a pivot column into an ancestor front (delay_columns) without a new ordering.
+void build_structures(Plan& P) {
+   const int64_t N = P.N, nnz = P.nnz;
+   const auto t1 = clk::now();
+   struct { const std::vector<int64_t>& ptr; const std::vector<int32_t>& idx; } g{P.adj_ptr, P.adj_idx};
+   const std::vector<int32_t>& row = P.coo_row;
+   const std::vector<int32_t>& col = P.coo_col;
+   P.nnz_L = 0; P.flops = 0.0; P.flops_tc = 0.0; P.sum_r = 0; P.max_f = 0; P.max_k = 0;
    P.iperm.resize(static_cast<size_t>(N));
    for (int64_t i = 0; i < N; ++i) P.iperm[P.perm[i]] = static_cast<int32_t>(i);
    P.sn_of.resize(static_cast<size_t>(N));
@@ -681,6 +702,40 @@ void analyse(int64_t N, int64_t nnz, int64_t reg_size, int64_t num_primal, const
       }
    }
    P.t_maps = secs(t2, clk::now());
+}
+
+// Delayed pivots.  Column cols[i] (a position in the current numbering) leaves its front and becomes the LAST pivot of the
+// ancestor front up[i] levels above (capped at the root of its tree; a column of a root front stays).  Fronts that lose all
+// their pivots disappear.  Everything derived from the partition is rebuilt; the elimination order of all other columns is kept.
+void delay_columns(Plan& P, const std::vector<int32_t>& cols, const std::vector<int32_t>& up) {
+   const int32_t nsn = P.nsn;
+   std::vector<std::vector<int32_t>> arrivals(static_cast<size_t>(nsn));
+   std::vector<char> leaves(static_cast<size_t>(P.N), 0);
+   for (size_t i = 0; i < cols.size(); ++i) {
+      const int32_t q = cols[i];
+      if (q < 0 || q >= P.N) throw std::runtime_error("delay_columns: position out of range");
+      if (leaves[q]) continue;
+      int32_t t = P.sn_of[q];
+      for (int32_t u = 0; u < std::max(1, up[i]) && P.parent[t] >= 0; ++u) t = P.parent[t];
+      if (t == P.sn_of[q]) continue;   // root front: nowhere to go
+      leaves[q] = 1;
+      arrivals[t].push_back(P.perm[q]);
+   }
+   std::vector<int32_t> order;
+   order.reserve(static_cast<size_t>(P.N));
+   std::vector<int32_t> first;
+   for (int32_t s = 0; s < nsn; ++s) {
+      const size_t before = order.size();
+      for (int32_t q = P.sn_first[s]; q < P.sn_first[s + 1]; ++q) if (!leaves[q]) order.push_back(P.perm[q]);
+      order.insert(order.end(), arrivals[s].begin(), arrivals[s].end());
+      if (order.size() > before) first.push_back(static_cast<int32_t>(before));
+   }
+   if (static_cast<int64_t>(order.size()) != P.N) throw std::runtime_error("delay_columns: internal error (order incomplete)");
+   first.push_back(static_cast<int32_t>(P.N));
+   P.perm = std::move(order);
+   P.sn_first = std::move(first);
+   P.nsn = static_cast<int32_t>(P.sn_first.size()) - 1;
+   build_structures(P);
 }
 
 // ------------------------------------------------------------------------------------------------
