@@ -69,6 +69,8 @@ typedef struct b200kkt_stats {
    /* delayed pivots: columns moved into an ancestor front since the analysis, host re-plans since the analysis and during the
     * last factorization (each re-plan is followed by a new factorization attempt) */
    int64_t num_delayed_total, num_replans_total, num_replans_last;
+   /* componentwise backward error of the last solve: max_i |b - K x|_i / (|K| |x| + |b|)_i (Oettli-Prager; MUMPS' omega_1) */
+   double backward_error_componentwise_last;
 } b200kkt_stats;
 
 /* Handle life cycle.  Replaces JOB=-1 / JOB=-2 (MUMPSSolver.cpp:16-49).
@@ -98,13 +100,15 @@ int b200kkt_plan_partition(const b200kkt_handle* h, int32_t* owner, int8_t* shar
 /* Options (defaults need no user action).  Names: "ordering" (0 METIS, 1 natural),
  * "kkt_pairing", "relax_small", "relax_mid", "relax_big", "scaling_sweeps", "null_pivot_tol",
  * "refine_max_steps", "refine_tol", "use_graph", "profile_updates", and for the delayed pivots
- * "delay_tol" (1e-14), "growth_limit" (0 = off), "max_replans" (8).
+ * "delay_tol" (1e-12), "growth_limit" (0 = off), "max_replans" (8), "adaptive_growth" (1), "adaptive_growth_limit" (1e8).
  *
  * Delayed pivots (what dmumps_c JOB=2 does with threshold pivoting; MUMPSSolver.cpp:85-89 with ICNTL(24)=1 at :36): the pivot
  * search of a front is confined to its fully-summed block.  A column whose candidates there are all below null_pivot_tol is a
  * zero eigenvalue only if the rest of its front column is below delay_tol as well; otherwise the factorization reports it, the
  * host moves it into an ancestor front (same elimination order for everything else, plan rebuilt, values stay on the device) and
  * factorizes again.  The moves persist, so later factorizations of the same pattern start from the adapted plan.
+ * growth_limit > 0 treats a column with an L entry above the limit the same way (what the threshold test CNTL(1) is for);
+ * adaptive_growth arms that guard for one factorization after a solve that needed more than two refinement steps.
  * b200kkt_get_permutation / plan getters return the adapted plan. */
 int b200kkt_set_option(b200kkt_handle* h, const char* name, double value);
 /* Optional user ordering for the next analyse (perm[new] = old, length N); NULL clears it. */
@@ -132,7 +136,10 @@ int b200kkt_inertia(const b200kkt_handle* h, uint64_t* n_pos, uint64_t* n_neg, u
 
 /* Solve with the last factorization plus iterative refinement.  Replaces
  * solve_indefinite_system(matrix, rhs, result) -> JOB=3 (MUMPSSolver.cpp:91-96).
- * backward_error (may be NULL) receives ||b-Kx||_inf / (||K||_inf ||x||_inf + ||b||_inf). */
+ * backward_error (may be NULL) receives ||b-Kx||_inf / (||K||_inf ||x||_inf + ||b||_inf); the componentwise measure
+ * max_i |b-Kx|_i / (|K||x|+|b|)_i is in b200kkt_stats.backward_error_componentwise_last.  Refinement runs until both are below
+ * their tolerances ("refine_tol" 1e-13, "refine_tol_componentwise" 1e-13) or stagnate.  A non-finite residual or pivot is an
+ * error (B200KKT_EINTERNAL), as MUMPS' INFOG(1) < 0 would be. */
 int b200kkt_solve(b200kkt_handle* h, const double* rhs, double* x, double* backward_error);
 int b200kkt_solve_device(b200kkt_handle* h, const double* d_rhs, double* d_x, double* backward_error);
 

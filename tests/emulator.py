@@ -100,7 +100,7 @@ def bk_block(B, n, tol):
 
 
 class EmulatedFactorization:
-    def __init__(self, plan, perm, scatter, kkt, values, sweeps=3, null_tol=1e-14, defer=False, delay_tol=1e-14, growth_limit=0.0):
+    def __init__(self, plan, perm, scatter, kkt, values, sweeps=3, null_tol=1e-14, defer=False, delay_tol=1e-12, growth_limit=0.0):
         self.plan = plan
         self.perm = np.asarray(perm)
         self.n = kkt.dim

@@ -236,6 +236,44 @@ def test_hessian_only_positive_definite_path():
     assert backward_error(kkt, v, s.solve_indefinite_system(kkt.rhs)) <= BERR_TOL
 
 
+def test_config3_delayed_pivots_give_the_exact_inertia():
+    """BASELINE configs[2] at full size (10k buses, delta_w = 100, delta_c = 0).  Three multiplier columns have no pivot inside
+    the fully-summed block of their front (J restricted to the front is rank deficient): the factorization flags them, the host
+    moves them into an ancestor front and factorizes again.  Structural inertia (n, m, 0); round 1 reported (51000, 46997, 3)."""
+    kkt = G.opf_like(delta_w=100.0)
+    s = gpu_solver(kkt)
+    s.do_numerical_factorization(kkt.val)
+    st = s.stats()
+    assert s.get_inertia() == (kkt.n, kkt.m, 0) == (51000, 47000, 0)
+    assert st["num_delayed_total"] >= 1 and st["num_replans_total"] >= 1 and st["num_null_pivots_last"] == 0
+    x, berr = s.solve_indefinite_system(kkt.rhs, return_backward_error=True)
+    assert berr <= BERR_TOL and backward_error(kkt, kkt.val, x) <= BERR_TOL
+    assert s.stats()["backward_error_componentwise_last"] <= BERR_TOL
+    # the moves persist: the next factorization of the same pattern starts from the adapted plan
+    s.do_numerical_factorization(kkt.val)
+    assert s.stats()["num_replans_last"] == 0 and s.get_inertia() == (kkt.n, kkt.m, 0)
+    assert np.array_equal(x, s.solve_indefinite_system(kkt.rhs))
+    # and so does the inertia-loop fast path
+    s.refactorize_shifted(kkt.val[: kkt.reg_size])
+    assert s.get_inertia() == (kkt.n, kkt.m, 0)
+
+
+def test_non_finite_values_are_an_error_not_an_inertia():
+    """MUMPS would return INFOG(1) < 0; a NaN pivot must never be counted as a negative eigenvalue."""
+    kkt = G.ocp_distributed(8, 2, seed=5)
+    s = gpu_solver(kkt)
+    bad = kkt.val.copy()
+    bad[kkt.reg_size + 3] = np.nan
+    with pytest.raises(B200KKTError):
+        s.do_numerical_factorization(bad)
+    s.do_numerical_factorization(kkt.val)          # the handle stays usable
+    assert s.get_inertia() == (kkt.n, kkt.m, 0)
+    rhs = kkt.rhs.copy()
+    rhs[0] = np.inf
+    with pytest.raises(B200KKTError):
+        s.solve_indefinite_system(rhs)
+
+
 @pytest.mark.parametrize("make,name", [(lambda: G.ocp_distributed(256, 2), "config2"), (lambda: G.ocp_distributed(32, 3), "3d_k32")])
 def test_full_size_properties(make, name):
     """At BASELINE sizes the oracle is too slow: check structural inertia (convex OCP: exactly (n, m, 0)),

@@ -42,6 +42,7 @@ class Stats(C.Structure):
         ("t_shared_profiled", C.c_double), ("flops_shared_profiled", C.c_double), ("t_shared_stall_profiled", C.c_double),
         ("t_before_shared_profiled", C.c_double), ("t_transfer_wait_profiled", C.c_double),
         ("num_delayed_total", C.c_int64), ("num_replans_total", C.c_int64), ("num_replans_last", C.c_int64),
+        ("backward_error_componentwise_last", C.c_double),
     ]
 
     def as_dict(self):

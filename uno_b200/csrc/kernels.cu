@@ -82,13 +82,27 @@ __global__ void k_assemble(AssemblyArrays M, const double* __restrict__ values, 
    pool[M.dst[d]] = s;
 }
 
+// r = b - K x, and the componentwise backward error of Oettli-Prager / Arioli-Demmel-Duff (what MUMPS reports as omega_1):
+// omega = max_i |r_i| / (|K| |x| + |b|)_i over the rows whose denominator is not zero, as an ordered bit pattern
 __global__ void k_residual(CsrArrays A, const double* __restrict__ values, const double* __restrict__ x,
-                           const double* __restrict__ b, double* __restrict__ r) {
+                           const double* __restrict__ b, double* __restrict__ r, unsigned long long* __restrict__ omega_bits) {
    const int64_t i = blockIdx.x * static_cast<int64_t>(blockDim.x) + threadIdx.x;
-   if (i >= A.n) return;
-   double s = 0.0;
-   for (int t = A.ptr[i]; t < A.ptr[i + 1]; ++t) s += values[A.slot[t]] * x[A.col[t]];
-   r[i] = b[i] - s;
+   double w = 0.0;
+   if (i < A.n) {
+      double s = 0.0, a = 0.0;
+      for (int t = A.ptr[i]; t < A.ptr[i + 1]; ++t) {
+         const double v = values[A.slot[t]], xv = x[A.col[t]];
+         s += v * xv;
+         a = fma(fabs(v), fabs(xv), a);
+      }
+      const double bi = b[i], ri = bi - s;
+      r[i] = ri;
+      a += fabs(bi);
+      if (a > 0.0) w = fabs(ri) / a;
+      if (w != w) w = __longlong_as_double(0x7ff0000000000000LL);
+   }
+   for (int o = 16; o; o >>= 1) w = fmax(w, __shfl_xor_sync(0xffffffffu, w, o));
+   if ((threadIdx.x & 31) == 0 && w > 0.0) atomicMax(omega_bits, ordered_bits(w));
 }
 
 __global__ void k_solve_gather(int64_t n, const int* __restrict__ perm, const double* __restrict__ scale,
@@ -1616,16 +1630,18 @@ __global__ void __maxnreg__(200) k_update_ws(FrontArrays F, const int* __restric
 // K6 inertia from the D blocks
 // ------------------------------------------------------------------------------------------------
 __global__ void k_inertia(int64_t n, FactorArrays W, int* counters, const signed char* __restrict__ col_owner, const int rank) {
-   int pos = 0, neg = 0, zero = 0, two = 0;
+   int pos = 0, neg = 0, zero = 0, two = 0, bad = 0;
    for (int64_t q = blockIdx.x * static_cast<int64_t>(blockDim.x) + threadIdx.x; q < n; q += static_cast<int64_t>(gridDim.x) * blockDim.x) {
       if (col_owner != nullptr && col_owner[q] != rank) continue;
       const int ty = W.ptype[q];
       if (ty == 0) {
-         if (W.dd[q] > 0.0) ++pos; else ++neg;
+         const double d = W.dd[q];
+         if (d > 0.0) ++pos; else if (d < 0.0) ++neg; else ++bad;   // NaN (or an exact zero that slipped through): an error, not a sign
       } else if (ty == 1) {
          const double a = W.dd[q], b = W.de[q], c = W.dd[q + 1];
          const double det = a * c - b * b;
          if (det < 0.0) { ++pos; ++neg; }
+         else if (!(det >= 0.0)) bad += 2;
          else if (a > 0.0) pos += 2;
          else neg += 2;
          ++two;
@@ -1638,12 +1654,14 @@ __global__ void k_inertia(int64_t n, FactorArrays W, int* counters, const signed
       neg += __shfl_xor_sync(0xffffffffu, neg, o);
       zero += __shfl_xor_sync(0xffffffffu, zero, o);
       two += __shfl_xor_sync(0xffffffffu, two, o);
+      bad += __shfl_xor_sync(0xffffffffu, bad, o);
    }
    if ((threadIdx.x & 31) == 0) {
       if (pos) atomicAdd(counters + 0, pos);
       if (neg) atomicAdd(counters + 1, neg);
       if (zero) atomicAdd(counters + 2, zero);
       if (two) atomicAdd(counters + 3, two);
+      if (bad) atomicAdd(counters + 6, bad);
    }
 }
 
@@ -2524,8 +2542,9 @@ int launch_keep_owned(int64_t n, const signed char* col_owner, int rank, double*
    return 1;
 }
 
-int launch_residual(const CsrArrays& A, const double* values, const double* x, const double* b, double* r, cudaStream_t st) {
-   k_residual<<<grid1d(A.n, 256), 256, 0, st>>>(A, values, x, b, r);
+int launch_residual(const CsrArrays& A, const double* values, const double* x, const double* b, double* r, unsigned long long* omega_bits,
+                    cudaStream_t st) {
+   k_residual<<<grid1d(A.n, 256), 256, 0, st>>>(A, values, x, b, r, omega_bits);
    return 1;
 }
 

@@ -586,7 +586,7 @@ void upload_plan(b200kkt_handle* h) {
    h->d_r = dev_alloc<double>(h, n);
    h->d_counters = dev_alloc<int>(h, 8);
    h->W.ndelay = h->d_counters + 5;
-   h->d_norms = dev_alloc<unsigned long long>(h, 4);
+   h->d_norms = dev_alloc<unsigned long long>(h, 8);
    h->d_scale_final = h->d_scale;
    build_cut_schedule(h);
    CK(cudaMemsetAsync(h->W.wpool, 0, static_cast<size_t>(std::max<int64_t>(4 * h->wpool_size, 1)) * sizeof(double), h->stream));
@@ -617,8 +617,7 @@ void enqueue_factor(b200kkt_handle* h) {
    const Plan& P = h->plan;
    cudaStream_t st = h->stream;
    int64_t& L = h->launches;
-   h->W.delay_tol = h->delay_tol;
-   h->W.growth_limit = h->growth_limit;
+   h->W.delay_tol = std::max(h->delay_tol, h->null_pivot_tol);   // what is null inside the block is null outside it too
    CK(cudaMemsetAsync(h->d_counters, 0, 8 * sizeof(int), st));
    CK(cudaMemsetAsync(h->W.delay, 0, static_cast<size_t>(P.N) * sizeof(int), st));
    // K1' equilibration
@@ -864,6 +863,8 @@ void run_factor_once(b200kkt_handle* h) {
    h->inertia[1] = static_cast<uint64_t>(h->h_counters[1]);
    h->inertia[2] = static_cast<uint64_t>(h->h_counters[2]);
    h->factorized = true;
+   // NaN/Inf in the values ends up in the D blocks: an error (MUMPS: INFOG(1) < 0), never a sign of an eigenvalue
+   if (h->h_counters[6] > 0) { h->factorized = false; throw std::runtime_error("factorize: non-finite pivots (the matrix values hold NaN/Inf)"); }
 }
 
 // Move the given columns (positions in the current numbering) into ancestor fronts and rebuild plan, schedules and device
@@ -909,6 +910,11 @@ void replan_with_delays(b200kkt_handle* h, const std::vector<int32_t>& cols) {
 
 void run_factor(b200kkt_handle* h) {
    h->replans_last = 0;
+   const double limit = h->growth_limit > 0.0 ? h->growth_limit : ((h->growth_armed && h->adaptive_growth != 0) ? h->adaptive_growth_limit : 0.0);
+   h->growth_armed = false;
+   if (limit != h->growth_baked && h->factor_graph != nullptr) { cudaGraphExecDestroy(h->factor_graph); h->factor_graph = nullptr; }
+   h->growth_baked = limit;
+   h->W.growth_limit = limit;
    for (int attempt = 0;; ++attempt) {
       run_factor_once(h);
       const int flagged = h->h_counters[5];
@@ -1003,8 +1009,9 @@ void run_solve(b200kkt_handle* h, const double* d_b, double* d_x, double* backwa
       }
       L += launch_solve_scatter_add(P.N, h->d_perm, h->d_scale_final, h->d_xg, d_x, st);
    };
-   double berr = 0.0, prev = 0.0;
+   double berr = 0.0, omega = 0.0, prev = 0.0;
    int steps = 0;
+   bool finite = true;
    for (int it = 0; it <= h->refine_max_steps; ++it) {
       if (h->use_graph && (!h->partitioned() || h->partition_graph != 0)) {
          // the sweep is a long chain of short kernels: replayed as a CUDA graph (re-captured when the output vector moves)
@@ -1028,21 +1035,25 @@ void run_solve(b200kkt_handle* h, const double* d_b, double* d_x, double* backwa
          enqueue_sweep();
       }
       // K8 residual and backward error
-      L += launch_residual(h->C, h->d_values, d_x, d_b, h->d_r, st);
       CK(cudaMemsetAsync(h->d_norms + 1, 0, 2 * sizeof(unsigned long long), st));
+      CK(cudaMemsetAsync(h->d_norms + 4, 0, sizeof(unsigned long long), st));
+      L += launch_residual(h->C, h->d_values, d_x, d_b, h->d_r, h->d_norms + 4, st);
       L += launch_absmax(h->d_r, P.N, h->d_norms + 1, st);
       L += launch_absmax(d_x, P.N, h->d_norms + 2, st);
-      CK(cudaMemcpyAsync(h->h_norms, h->d_norms, 4 * sizeof(unsigned long long), cudaMemcpyDeviceToHost, st));
+      CK(cudaMemcpyAsync(h->h_norms, h->d_norms, 5 * sizeof(unsigned long long), cudaMemcpyDeviceToHost, st));
       CK(cudaStreamSynchronize(st));
       const double knorm = bits_to_double(h->h_norms[0]), rnorm = bits_to_double(h->h_norms[1]);
       const double xnorm = bits_to_double(h->h_norms[2]), bnorm = bits_to_double(h->h_norms[3]);
       const double denom = knorm * xnorm + bnorm;
       berr = (denom > 0.0) ? rnorm / denom : 0.0;
+      omega = bits_to_double(h->h_norms[4]);
       steps = it;
-      if (!(berr > h->refine_tol)) break;                  // converged (also leaves on berr == 0)
-      if (!std::isfinite(berr)) break;
-      if (it > 0 && berr > 0.5 * prev) break;              // stagnation
-      prev = berr;
+      // both measures drive the refinement: the normwise one (north star) and the componentwise one (the measure MUMPS reports)
+      const double metric = std::max(berr / h->refine_tol, omega / h->refine_tol_componentwise);
+      if (!std::isfinite(metric)) { finite = false; break; }
+      if (!(metric > 1.0)) break;                          // converged (also leaves on a zero residual)
+      if (it > 0 && metric > 0.5 * prev) break;            // stagnation
+      prev = metric;
    }
    CK(cudaEventRecord(h->ev1, st));
    CK(cudaStreamSynchronize(st));
@@ -1052,7 +1063,11 @@ void run_solve(b200kkt_handle* h, const double* d_b, double* d_x, double* backwa
    h->stats.t_solve_last = ms * 1e-3;
    h->stats.refine_steps_last = steps;
    h->stats.backward_error_last = berr;
+   h->stats.backward_error_componentwise_last = omega;
+   if (steps > 2) h->growth_armed = true;   // see adaptive_growth
    if (backward_error != nullptr) *backward_error = berr;
+   // a factorization or right-hand side with NaN/Inf in it is an error, not a converged solve (MUMPS: INFOG(1) < 0)
+   if (!finite) throw std::runtime_error("solve: non-finite residual (the factorization or the right-hand side holds NaN/Inf)");
 }
 
 template <typename Fn>
@@ -1128,7 +1143,7 @@ int b200kkt_create(b200kkt_handle** out, int device, int num_gpus) {
             CK(cudaEventCreateWithFlags(&h->ev_sh_bcast[1], cudaEventDisableTiming));
          }
          CK(cudaMallocHost(reinterpret_cast<void**>(&h->h_counters), 8 * sizeof(int)));
-         CK(cudaMallocHost(reinterpret_cast<void**>(&h->h_norms), 4 * sizeof(unsigned long long)));
+         CK(cudaMallocHost(reinterpret_cast<void**>(&h->h_norms), 8 * sizeof(unsigned long long)));
          const int e = init_kernel_attributes();
          if (e != 0) throw CudaError{static_cast<cudaError_t>(e), "cudaFuncSetAttribute(k_update)"};
          h->has_device = true;
@@ -1229,6 +1244,9 @@ int b200kkt_set_option(b200kkt_handle* h, const char* name, double value) {
    else if (n == "delay_tol") h->delay_tol = value;
    else if (n == "growth_limit") h->growth_limit = value;
    else if (n == "max_replans") h->max_replans = std::max(0, static_cast<int>(value));
+   else if (n == "adaptive_growth") h->adaptive_growth = static_cast<int>(value);
+   else if (n == "adaptive_growth_limit") h->adaptive_growth_limit = value;
+   else if (n == "refine_tol_componentwise") h->refine_tol_componentwise = value;
    else if (n == "refine_max_steps") h->refine_max_steps = std::max(0, static_cast<int>(value));
    else if (n == "refine_tol") h->refine_tol = value;
    else if (n == "use_graph") h->use_graph = static_cast<int>(value);

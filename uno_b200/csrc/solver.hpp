@@ -49,14 +49,21 @@ struct b200kkt_handle {
    double null_pivot_tol = 1e-14;
    // delayed pivots (kernels.hpp: FactorArrays::delay): a column that cannot be eliminated inside its front is moved into an
    // ancestor front by re-planning on the host and the factorization is repeated; the moves persist for later factorizations
-   double delay_tol = 1e-14;         // scaled Schur entry outside the pivot block above which a null pivot is not null but delayed
+   double delay_tol = 1e-12;         // scaled Schur entry outside the pivot block above which a null pivot is not null but delayed
    double growth_limit = 0.0;        // > 0: also delay a column with an L entry above this (guard against unbounded growth)
+   // the guard switches itself on for ONE factorization (limit adaptive_growth_limit) after a solve that needed more than two
+   // refinement steps: restricted pivoting let L grow; the columns responsible move up and stay there
+   int adaptive_growth = 1;
+   double adaptive_growth_limit = 1e8;
+   bool growth_armed = false;
+   double growth_baked = 0.0;        // the limit the captured factor graph was built with
    int max_replans = 8;              // per factorization; beyond it the remaining columns are reported as null pivots
    std::vector<unsigned char> delay_count;   // per ORIGINAL column: times delayed so far (1st: parent, 2nd: 4 levels, then the root)
    int64_t delayed_total = 0, replans_total = 0, replans_last = 0;
    double* keep_values = nullptr;    // the resident value array survives a re-plan
    int refine_max_steps = 6;
    double refine_tol = 1e-15;
+   double refine_tol_componentwise = 1e-13;   // on max_i |r_i| / (|K||x| + |b|)_i
    int use_graph = 1;
    int profile_updates = 0;
    struct ProfiledLaunch { cudaEvent_t a, b; double flops; int kind; };
