@@ -103,6 +103,10 @@ struct Oracle {
    int64_t n2x2 = 0, ndelayed = 0;
    double nnzL = 0, flops = 0, t_analyse = 0, t_factor = 0, t_solve = 0;
    double u = 0.01, null_tol = 1e-20;
+   // 0: threshold test against the whole front column (MUMPS' rule, many delayed pivots on KKT matrices);
+   // 1: against the fully-summed rows only ("restricted" pivoting: a column is delayed only when the fully-summed block has no
+   //    acceptable pivot for it) - used where mode 0 is too slow (BASELINE sizes) and as the same-flops CPU baseline
+   int pivot_mode = 0;
    std::string err;
 };
 
@@ -309,7 +313,10 @@ void factor_front(Oracle& o, int s, const double* val, Work& w) {
       std::vector<double>().swap(C.cb);
    }
    F.d.assign(nfs, 1.0); F.e.assign(nfs, 0.0); F.ptype.assign(nfs, 0);
-   const int NB = 64;
+   // big fronts: wider blocks (fewer passes over the trailing matrix) and the in-block column work spread over the threads;
+   // small fronts are factored one per thread by the level loop (nested regions stay serial)
+   const int NB = nf >= 4096 ? 128 : 64;
+   const bool par = nf >= 1024;
    w.W.assign(ld * NB, 0.0);
    double* W = w.W.data();
    int ne = 0, active_end = nfs, since_retry = 0;
@@ -325,11 +332,19 @@ void factor_front(Oracle& o, int s, const double* val, Work& w) {
             const int c = cand;
             double lam_all = 0.0, lam_fs = 0.0;
             int r = -1;
-            for (int i = ne; i < nf; ++i) {
+            for (int i = ne; i < bend; ++i) {
                if (i == c) continue;
                const double v = std::fabs(lower(A, nf, i, c));
-               if (v > lam_all) lam_all = v;
-               if (i < bend && v > lam_fs) { lam_fs = v; r = i; }
+               if (v > lam_fs) { lam_fs = v; r = i; }
+            }
+            lam_all = lam_fs;
+            const int scan_end = o.pivot_mode == 1 ? active_end : nf;
+            {
+               const double* colc = A + ld * c;
+               double m = 0.0;
+#pragma omp parallel for reduction(max : m) if (par)
+               for (int i = bend; i < scan_end; ++i) m = std::max(m, std::fabs(colc[i]));
+               lam_all = std::max(lam_all, m);
             }
             const double acc = A[c + ld * c];
             int step = 0;
@@ -339,7 +354,7 @@ void factor_front(Oracle& o, int s, const double* val, Work& w) {
                const double b = lower(A, nf, r, c), dd = A[r + ld * r];
                const double det = acc * dd - b * b;
                double lc = 0.0, lr = 0.0;
-               for (int i = ne; i < nf; ++i) {
+               for (int i = ne; i < scan_end; ++i) {
                   if (i == c || i == r) continue;
                   lc = std::max(lc, std::fabs(lower(A, nf, i, c)));
                   lr = std::max(lr, std::fabs(lower(A, nf, i, r)));
@@ -353,6 +368,7 @@ void factor_front(Oracle& o, int s, const double* val, Work& w) {
                const double piv = A[ne + ld * ne];
                double* wc = W + ld * (ne - bstart);
                for (int i = ne + 1; i < nf; ++i) { wc[i] = A[i + ld * ne]; A[i + ld * ne] = wc[i] / piv; }
+#pragma omp parallel for schedule(static) if (par)
                for (int j = ne + 1; j < bend; ++j) {
                   const double wj = wc[j];
                   if (wj == 0.0) continue;
@@ -378,6 +394,7 @@ void factor_front(Oracle& o, int s, const double* val, Work& w) {
                }
                w1[ne + 1] = 0.0; w2[ne + 1] = 0.0;
                A[ne + 1 + ld * ne] = 0.0;
+#pragma omp parallel for schedule(static) if (par)
                for (int j = ne + 2; j < bend; ++j) {
                   const double x1 = w1[j], x2 = w2[j];
                   double* cj = A + ld * j;
@@ -557,6 +574,11 @@ int oracle_set_blas(const char* path, const char* prefix) {
 int oracle_analyse(void* p, int64_t n, int64_t nnz, const uint64_t* row, const uint64_t* col, const int64_t* perm) {
    Oracle& o = *static_cast<Oracle*>(p);
    try { analyse(o, n, nnz, row, col, perm); return 0; } catch (const std::exception& e) { o.err = e.what(); return -1; }
+}
+
+int oracle_set_pivot_mode(void* p, int mode) {
+   static_cast<Oracle*>(p)->pivot_mode = mode;
+   return 0;
 }
 
 int oracle_set_parameters(void* p, double threshold_u, double null_tol) {

@@ -43,6 +43,7 @@ def _load():
         lib.oracle_set_blas.argtypes = [C.c_char_p, C.c_char_p]
         lib.oracle_analyse.argtypes = [C.c_void_p, C.c_int64, C.c_int64, C.c_void_p, C.c_void_p, C.c_void_p]
         lib.oracle_set_parameters.argtypes = [C.c_void_p, C.c_double, C.c_double]
+        lib.oracle_set_pivot_mode.argtypes = [C.c_void_p, C.c_int]
         lib.oracle_factorize.argtypes = [C.c_void_p, C.c_void_p, C.c_int]
         lib.oracle_inertia.argtypes = [C.c_void_p, C.POINTER(C.c_uint64), C.POINTER(C.c_uint64), C.POINTER(C.c_uint64)]
         lib.oracle_solve.argtypes = [C.c_void_p, C.c_void_p, C.c_void_p]
@@ -75,10 +76,13 @@ def _p(a):
 class OracleSolver:
     """CPU multifrontal LDL^T with threshold pivoting and delayed pivots (see kkt_oracle.cpp)."""
 
-    def __init__(self, threshold_u: float = 0.01, null_tol: float = 2.2e-21, threads: int = 1):
+    def __init__(self, threshold_u: float = 0.01, null_tol: float = 2.2e-21, threads: int = 1, restricted: bool = False):
+        """restricted = False: threshold test against the whole front column (MUMPS' rule); True: against the fully-summed
+        rows only (few delayed pivots: the mode for BASELINE-size checks and for the same-flops CPU baseline)."""
         self._lib = _load()
         self._h = C.c_void_p(self._lib.oracle_create())
         self._lib.oracle_set_parameters(self._h, threshold_u, null_tol)
+        self._lib.oracle_set_pivot_mode(self._h, 1 if restricted else 0)
         self.threads = threads
         self.n = 0
 
