@@ -108,7 +108,8 @@ int b200kkt_plan_partition(const b200kkt_handle* h, int32_t* owner, int8_t* shar
  * host moves it into an ancestor front (same elimination order for everything else, plan rebuilt, values stay on the device) and
  * factorizes again.  The moves persist, so later factorizations of the same pattern start from the adapted plan.
  * growth_limit > 0 treats a column with an L entry above the limit the same way (what the threshold test CNTL(1) is for);
- * adaptive_growth arms that guard for one factorization after a solve that needed more than two refinement steps.
+ * adaptive_growth arms that guard for one factorization after a solve whose first sweep missed a normwise backward error of
+ * "adaptive_growth_trigger" (1e-12).
  * b200kkt_get_permutation / plan getters return the adapted plan. */
 int b200kkt_set_option(b200kkt_handle* h, const char* name, double value);
 /* Optional user ordering for the next analyse (perm[new] = old, length N); NULL clears it. */
@@ -137,8 +138,8 @@ int b200kkt_inertia(const b200kkt_handle* h, uint64_t* n_pos, uint64_t* n_neg, u
 /* Solve with the last factorization plus iterative refinement.  Replaces
  * solve_indefinite_system(matrix, rhs, result) -> JOB=3 (MUMPSSolver.cpp:91-96).
  * backward_error (may be NULL) receives ||b-Kx||_inf / (||K||_inf ||x||_inf + ||b||_inf); the componentwise measure
- * max_i |b-Kx|_i / (|K||x|+|b|)_i is in b200kkt_stats.backward_error_componentwise_last.  Refinement runs until both are below
- * their tolerances ("refine_tol" 1e-13, "refine_tol_componentwise" 1e-13) or stagnate.  A non-finite residual or pivot is an
+ * max_i |b-Kx|_i / (|K||x|+|b|)_i (Arioli-Demmel-Duff omega_1, omega_2 for rows with a denominator at rounding level) is in b200kkt_stats.backward_error_componentwise_last.  Refinement runs until both are below
+ * their tolerances ("refine_tol" 1e-13, "refine_tol_componentwise" 1e-12) or stagnate.  A non-finite residual or pivot is an
  * error (B200KKT_EINTERNAL), as MUMPS' INFOG(1) < 0 would be. */
 int b200kkt_solve(b200kkt_handle* h, const double* rhs, double* x, double* backward_error);
 int b200kkt_solve_device(b200kkt_handle* h, const double* d_rhs, double* d_x, double* backward_error);

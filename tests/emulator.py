@@ -107,6 +107,7 @@ class EmulatedFactorization:
         self.null_tol = null_tol
         self.delay_tol = delay_tol
         self.growth_limit = growth_limit
+        self.delayed_size = []       # largest Schur entry outside the block of each null-flagged column
         self.delayed = []            # plan columns flagged for a delay (kernels.cu: flag_delay)
         self.scale = equilibrate(kkt, values, sweeps)
         nsn = plan["num_fronts"]
@@ -180,6 +181,7 @@ class EmulatedFactorization:
                     for c in np.flatnonzero(null):
                         if np.max(np.abs(Wm[:, c])) > self.delay_tol:
                             self.delayed.append(int(first[s] + lp[j0 + c]))
+                            self.delayed_size.append(float(np.max(np.abs(Wm[:, c]))))
                     if self.growth_limit > 0:
                         for c in np.flatnonzero(~null):
                             if np.max(np.abs(Lm[:, c])) > self.growth_limit:

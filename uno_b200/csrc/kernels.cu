@@ -82,24 +82,32 @@ __global__ void k_assemble(AssemblyArrays M, const double* __restrict__ values, 
    pool[M.dst[d]] = s;
 }
 
-// r = b - K x, and the componentwise backward error of Oettli-Prager / Arioli-Demmel-Duff (what MUMPS reports as omega_1):
-// omega = max_i |r_i| / (|K| |x| + |b|)_i over the rows whose denominator is not zero, as an ordered bit pattern
+// r = b - K x, and the componentwise backward error of Arioli, Demmel and Duff (SIAM J. Matrix Anal. 1989) - what MUMPS reports
+// as RINFOG(7)/(8): rows whose denominator (|K||x| + |b|)_i is safely above rounding level give omega_1 = |r_i| / (|K||x| + |b|)_i,
+// the others (denominator below 1000 n eps (|K_i|_inf |x|_inf + |b_i|)) give omega_2 = |r_i| / ((|K||x|)_i + |K_i|_1 |x|_inf).
+// The maximum of both over all rows goes to *omega_bits as an ordered bit pattern; |x|_inf is read from *xnorm_bits.
 __global__ void k_residual(CsrArrays A, const double* __restrict__ values, const double* __restrict__ x,
-                           const double* __restrict__ b, double* __restrict__ r, unsigned long long* __restrict__ omega_bits) {
+                           const double* __restrict__ b, double* __restrict__ r, const unsigned long long* __restrict__ xnorm_bits,
+                           unsigned long long* __restrict__ omega_bits) {
    const int64_t i = blockIdx.x * static_cast<int64_t>(blockDim.x) + threadIdx.x;
    double w = 0.0;
    if (i < A.n) {
-      double s = 0.0, a = 0.0;
+      const double xnorm = __longlong_as_double(static_cast<long long>(*xnorm_bits));
+      double s = 0.0, a = 0.0, rowmax = 0.0, rowsum = 0.0;
       for (int t = A.ptr[i]; t < A.ptr[i + 1]; ++t) {
-         const double v = values[A.slot[t]], xv = x[A.col[t]];
+         const double v = values[A.slot[t]], xv = x[A.col[t]], av = fabs(v);
          s += v * xv;
-         a = fma(fabs(v), fabs(xv), a);
+         a = fma(av, fabs(xv), a);
+         rowmax = fmax(rowmax, av);
+         rowsum += av;
       }
       const double bi = b[i], ri = bi - s;
       r[i] = ri;
-      a += fabs(bi);
-      if (a > 0.0) w = fabs(ri) / a;
-      if (w != w) w = __longlong_as_double(0x7ff0000000000000LL);
+      const double d1 = a + fabs(bi);
+      const double tau = 1000.0 * static_cast<double>(A.n) * 2.220446049250313e-16 * (rowmax * xnorm + fabs(bi));
+      const double den = (d1 > tau) ? d1 : (a + rowsum * xnorm);
+      if (den > 0.0) w = fabs(ri) / den;
+      if (w != w || ri != ri) w = __longlong_as_double(0x7ff0000000000000LL);
    }
    for (int o = 16; o; o >>= 1) w = fmax(w, __shfl_xor_sync(0xffffffffu, w, o));
    if ((threadIdx.x & 31) == 0 && w > 0.0) atomicMax(omega_bits, ordered_bits(w));
@@ -2542,9 +2550,9 @@ int launch_keep_owned(int64_t n, const signed char* col_owner, int rank, double*
    return 1;
 }
 
-int launch_residual(const CsrArrays& A, const double* values, const double* x, const double* b, double* r, unsigned long long* omega_bits,
-                    cudaStream_t st) {
-   k_residual<<<grid1d(A.n, 256), 256, 0, st>>>(A, values, x, b, r, omega_bits);
+int launch_residual(const CsrArrays& A, const double* values, const double* x, const double* b, double* r,
+                    const unsigned long long* xnorm_bits, unsigned long long* omega_bits, cudaStream_t st) {
+   k_residual<<<grid1d(A.n, 256), 256, 0, st>>>(A, values, x, b, r, xnorm_bits, omega_bits);
    return 1;
 }
 

@@ -154,8 +154,8 @@ int launch_rows_pack(const double* panel, int64_t ld, int row0, int nrows, int n
 int launch_rows_unpack(const double* staging, int64_t ld, int row0, int nrows, int ncols, double* panel, cudaStream_t st);
 // K8 residual r = b - K x on the COO-order values, and infinity norms as ordered bit patterns
 // (with the componentwise backward error max_i |r_i| / (|K||x| + |b|)_i: atomicMax on *omega_bits)
-int launch_residual(const CsrArrays& A, const double* values, const double* x, const double* b, double* r, unsigned long long* omega_bits,
-                    cudaStream_t st);
+int launch_residual(const CsrArrays& A, const double* values, const double* x, const double* b, double* r,
+                    const unsigned long long* xnorm_bits, unsigned long long* omega_bits, cudaStream_t st);
 int launch_absmax(const double* v, int64_t n, unsigned long long* out_bits, cudaStream_t st);
 
 }  // namespace b200kkt

@@ -10,6 +10,8 @@
 #include <algorithm>
 #include <chrono>
 #include <cmath>
+#include <cstdio>
+#include <cstdlib>
 #include <cstring>
 #include <exception>
 #include <new>
@@ -1009,7 +1011,8 @@ void run_solve(b200kkt_handle* h, const double* d_b, double* d_x, double* backwa
       }
       L += launch_solve_scatter_add(P.N, h->d_perm, h->d_scale_final, h->d_xg, d_x, st);
    };
-   double berr = 0.0, omega = 0.0, prev = 0.0;
+   double berr = 0.0, omega = 0.0, prev = 0.0, prev_omega = 0.0, first_berr = 0.0;
+   static const bool trace = std::getenv("B200KKT_TRACE_REFINE") != nullptr;
    int steps = 0;
    bool finite = true;
    for (int it = 0; it <= h->refine_max_steps; ++it) {
@@ -1037,9 +1040,9 @@ void run_solve(b200kkt_handle* h, const double* d_b, double* d_x, double* backwa
       // K8 residual and backward error
       CK(cudaMemsetAsync(h->d_norms + 1, 0, 2 * sizeof(unsigned long long), st));
       CK(cudaMemsetAsync(h->d_norms + 4, 0, sizeof(unsigned long long), st));
-      L += launch_residual(h->C, h->d_values, d_x, d_b, h->d_r, h->d_norms + 4, st);
-      L += launch_absmax(h->d_r, P.N, h->d_norms + 1, st);
       L += launch_absmax(d_x, P.N, h->d_norms + 2, st);
+      L += launch_residual(h->C, h->d_values, d_x, d_b, h->d_r, h->d_norms + 2, h->d_norms + 4, st);
+      L += launch_absmax(h->d_r, P.N, h->d_norms + 1, st);
       CK(cudaMemcpyAsync(h->h_norms, h->d_norms, 5 * sizeof(unsigned long long), cudaMemcpyDeviceToHost, st));
       CK(cudaStreamSynchronize(st));
       const double knorm = bits_to_double(h->h_norms[0]), rnorm = bits_to_double(h->h_norms[1]);
@@ -1049,11 +1052,15 @@ void run_solve(b200kkt_handle* h, const double* d_b, double* d_x, double* backwa
       omega = bits_to_double(h->h_norms[4]);
       steps = it;
       // both measures drive the refinement: the normwise one (north star) and the componentwise one (the measure MUMPS reports)
-      const double metric = std::max(berr / h->refine_tol, omega / h->refine_tol_componentwise);
-      if (!std::isfinite(metric)) { finite = false; break; }
-      if (!(metric > 1.0)) break;                          // converged (also leaves on a zero residual)
-      if (it > 0 && metric > 0.5 * prev) break;            // stagnation
-      prev = metric;
+      if (!std::isfinite(berr) || !std::isfinite(omega)) { finite = false; break; }
+      if (it == 0) first_berr = berr;
+      if (trace) std::fprintf(stderr, "[b200kkt] refine step %d: normwise %.3e componentwise %.3e\n", it, berr, omega);
+      const bool need_n = berr > h->refine_tol, need_c = omega > h->refine_tol_componentwise;
+      if (!need_n && !need_c) break;                       // converged (also leaves on a zero residual)
+      // stagnation: no measure that still has to come down has halved
+      if (it > 0 && (!need_n || berr > 0.5 * prev) && (!need_c || omega > 0.5 * prev_omega)) break;
+      prev = berr;
+      prev_omega = omega;
    }
    CK(cudaEventRecord(h->ev1, st));
    CK(cudaStreamSynchronize(st));
@@ -1064,7 +1071,7 @@ void run_solve(b200kkt_handle* h, const double* d_b, double* d_x, double* backwa
    h->stats.refine_steps_last = steps;
    h->stats.backward_error_last = berr;
    h->stats.backward_error_componentwise_last = omega;
-   if (steps > 2) h->growth_armed = true;   // see adaptive_growth
+   if (first_berr > h->adaptive_growth_trigger) h->growth_armed = true;   // see adaptive_growth
    if (backward_error != nullptr) *backward_error = berr;
    // a factorization or right-hand side with NaN/Inf in it is an error, not a converged solve (MUMPS: INFOG(1) < 0)
    if (!finite) throw std::runtime_error("solve: non-finite residual (the factorization or the right-hand side holds NaN/Inf)");
@@ -1246,6 +1253,7 @@ int b200kkt_set_option(b200kkt_handle* h, const char* name, double value) {
    else if (n == "max_replans") h->max_replans = std::max(0, static_cast<int>(value));
    else if (n == "adaptive_growth") h->adaptive_growth = static_cast<int>(value);
    else if (n == "adaptive_growth_limit") h->adaptive_growth_limit = value;
+   else if (n == "adaptive_growth_trigger") h->adaptive_growth_trigger = value;
    else if (n == "refine_tol_componentwise") h->refine_tol_componentwise = value;
    else if (n == "refine_max_steps") h->refine_max_steps = std::max(0, static_cast<int>(value));
    else if (n == "refine_tol") h->refine_tol = value;

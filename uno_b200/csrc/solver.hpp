@@ -51,10 +51,12 @@ struct b200kkt_handle {
    // ancestor front by re-planning on the host and the factorization is repeated; the moves persist for later factorizations
    double delay_tol = 1e-12;         // scaled Schur entry outside the pivot block above which a null pivot is not null but delayed
    double growth_limit = 0.0;        // > 0: also delay a column with an L entry above this (guard against unbounded growth)
-   // the guard switches itself on for ONE factorization (limit adaptive_growth_limit) after a solve that needed more than two
-   // refinement steps: restricted pivoting let L grow; the columns responsible move up and stay there
+   // the guard switches itself on for ONE factorization (limit adaptive_growth_limit) after a solve whose first sweep missed
+   // adaptive_growth_trigger in the normwise backward error: restricted pivoting let L grow; the columns responsible move up
+   // and stay there, so the following factorizations of the pattern deliver the accuracy without the extra sweeps
    int adaptive_growth = 1;
    double adaptive_growth_limit = 1e8;
+   double adaptive_growth_trigger = 1e-12;
    bool growth_armed = false;
    double growth_baked = 0.0;        // the limit the captured factor graph was built with
    int max_replans = 8;              // per factorization; beyond it the remaining columns are reported as null pivots
@@ -63,7 +65,7 @@ struct b200kkt_handle {
    double* keep_values = nullptr;    // the resident value array survives a re-plan
    int refine_max_steps = 6;
    double refine_tol = 1e-15;
-   double refine_tol_componentwise = 1e-13;   // on max_i |r_i| / (|K||x| + |b|)_i
+   double refine_tol_componentwise = 1e-12;   // on max_i |r_i| / (|K||x| + |b|)_i
    int use_graph = 1;
    int profile_updates = 0;
    struct ProfiledLaunch { cudaEvent_t a, b; double flops; int kind; };
