@@ -32,6 +32,8 @@
 #include <cstdio>
 #include <cstring>
 #include <dlfcn.h>
+#include <map>
+#include <memory>
 #include <numeric>
 #include <stdexcept>
 #include <string>
@@ -49,14 +51,17 @@ namespace {
 
 // ---- optional BLAS (OpenBLAS shipped inside scipy), loaded at run time ---------------------------
 typedef void (*cblas_dgemm_t)(int, int, int, int, int, int, double, const double*, int, const double*, int, double, double*, int);
+typedef void (*cblas_dtrsm_t)(int, int, int, int, int, int, int, double, const double*, int, double*, int);
 typedef void (*set_threads_t)(int);
 cblas_dgemm_t g_dgemm = nullptr;
+cblas_dtrsm_t g_dtrsm = nullptr;
 set_threads_t g_set_threads = nullptr;
 
 // C[m x n] -= A[m x k] * B[n x k]^T, all column-major
 void gemm_nt_sub(int m, int n, int k, const double* A, int lda, const double* B, int ldb, double* C, int ldc) {
    if (m <= 0 || n <= 0 || k <= 0) return;
-   if (g_dgemm != nullptr) {
+   // a BLAS call costs a thread wake-up: only products that are worth it go there
+   if (g_dgemm != nullptr && static_cast<double>(m) * n * k >= 2.0e6) {
       g_dgemm(102 /*ColMajor*/, 111 /*NoTrans*/, 112 /*Trans*/, m, n, k, -1.0, A, lda, B, ldb, 1.0, C, ldc);
       return;
    }
@@ -67,6 +72,25 @@ void gemm_nt_sub(int m, int n, int k, const double* A, int lda, const double* B,
          if (b == 0.0) continue;
          const double* a = A + static_cast<size_t>(lda) * p;
          for (int i = 0; i < m; ++i) c[i] -= a[i] * b;
+      }
+   }
+}
+
+// B[m x n] <- B * T^{-T}, T unit lower triangular n x n (its diagonal is not read), all column-major
+void trsm_right_lower_trans_unit(int m, int n, const double* T, int ldt, double* B, int ldb) {
+   if (m <= 0 || n <= 0) return;
+   if (g_dtrsm != nullptr && static_cast<double>(m) * n * n >= 2.0e6) {
+      g_dtrsm(102 /*ColMajor*/, 142 /*Right*/, 122 /*Lower*/, 112 /*Trans*/, 132 /*Unit*/, m, n, 1.0, T, ldt, B, ldb);
+      return;
+   }
+   // X T^T = B: column p of X is final once columns q < p are; then it leaves all later columns
+   for (int p = 0; p < n; ++p) {
+      const double* xp = B + static_cast<size_t>(ldb) * p;
+      for (int q = p + 1; q < n; ++q) {
+         const double t = T[q + static_cast<size_t>(ldt) * p];
+         if (t == 0.0) continue;
+         double* xq = B + static_cast<size_t>(ldb) * q;
+         for (int i = 0; i < m; ++i) xq[i] -= xp[i] * t;
       }
    }
 }
@@ -86,7 +110,29 @@ struct Front {
    // contribution block handed to the parent (freed once consumed)
    int ncb = 0, ndelay = 0;
    std::vector<int> cb_idx;
-   std::vector<double> cb;
+   std::unique_ptr<double[]> cb;       // ncb x ncb, lower triangle valid; from / back to the oracle's buffer pool
+   size_t cb_cap = 0;
+};
+
+// Contribution blocks come and go with every front: fresh allocations of that size are mmap'ed and page-faulted in each time,
+// which costs more than the arithmetic.  Buffers are recycled instead (best fit by capacity).
+struct BufferPool {
+   std::multimap<size_t, std::unique_ptr<double[]>> free_list;
+   std::unique_ptr<double[]> take(size_t need, size_t& cap) {
+      std::unique_ptr<double[]> out;
+#pragma omp critical(oracle_pool)
+      {
+         auto it = free_list.lower_bound(need);
+         if (it != free_list.end() && it->first <= 2 * need + 4096) { cap = it->first; out = std::move(it->second); free_list.erase(it); }
+      }
+      if (!out) { cap = need; out.reset(new double[need > 0 ? need : 1]); }
+      return out;
+   }
+   void give(std::unique_ptr<double[]>& buf, size_t cap) {
+      if (!buf) return;
+#pragma omp critical(oracle_pool)
+      free_list.emplace(cap, std::move(buf));
+   }
 };
 
 struct Oracle {
@@ -99,6 +145,7 @@ struct Oracle {
    std::vector<int> order;             // fronts, children before parents
    std::vector<std::vector<int>> levels;
    std::vector<double> scale;
+   BufferPool pool;
    uint64_t pos = 0, neg = 0, zero = 0;
    int64_t n2x2 = 0, ndelayed = 0;
    double nnzL = 0, flops = 0, t_analyse = 0, t_factor = 0, t_solve = 0;
@@ -216,7 +263,8 @@ void analyse(Oracle& o, int64_t N, int64_t nnz, const uint64_t* row, const uint6
    const int ns = static_cast<int>(sfirst.size()) - 1;
    std::vector<int> snof(N);
    for (int s = 0; s < ns; ++s) for (int j = sfirst[s]; j < sfirst[s + 1]; ++j) snof[j] = s;
-   o.fronts.assign(ns, Front());
+   o.fronts.clear();
+   o.fronts.resize(ns);
    std::vector<int> mark(N, -1);
    for (int s = 0; s < ns; ++s) {
       Front& F = o.fronts[s];
@@ -290,8 +338,12 @@ void factor_front(Oracle& o, int s, const double* val, Work& w) {
    const int nf = static_cast<int>(F.idx.size());
    F.nf = nf;
    const size_t ld = static_cast<size_t>(nf);
-   w.A.assign(ld * nf, 0.0);
+   // only the lower triangle is ever read: it alone is cleared (the BLAS strips may leave anything above the diagonal)
+   if (w.A.size() < ld * nf) w.A.resize(ld * nf);
    double* A = w.A.data();
+   const bool big = nf >= 1024;
+#pragma omp parallel for schedule(static, 16) if (big)
+   for (int j = 0; j < nf; ++j) std::memset(A + ld * j + j, 0, sizeof(double) * static_cast<size_t>(nf - j));
    for (int t = 0; t < nf; ++t) w.loc[F.idx[t]] = t;
    // original entries of the own columns (equilibrated)
    for (int j = F.first; j < F.first + F.ncol; ++j) {
@@ -305,120 +357,169 @@ void factor_front(Oracle& o, int s, const double* val, Work& w) {
    for (int c : F.children) {
       Front& C = o.fronts[c];
       const int ncb = C.ncb;
+      // every (ci, cj) lands on its own entry of the parent: the child's columns can be added side by side
+#pragma omp parallel for schedule(dynamic, 16) if (big && ncb >= 256)
       for (int cj = 0; cj < ncb; ++cj) {
          const int gj = w.loc[C.cb_idx[cj]];
-         const double* col = C.cb.data() + static_cast<size_t>(ncb) * cj;
+         const double* col = C.cb.get() + static_cast<size_t>(ncb) * cj;
          for (int ci = cj; ci < ncb; ++ci) lower(A, nf, w.loc[C.cb_idx[ci]], gj) += col[ci];
       }
-      std::vector<double>().swap(C.cb);
+      o.pool.give(C.cb, C.cb_cap);
    }
    F.d.assign(nfs, 1.0); F.e.assign(nfs, 0.0); F.ptype.assign(nfs, 0);
    // big fronts: wider blocks (fewer passes over the trailing matrix) and the in-block column work spread over the threads;
    // small fronts are factored one per thread by the level loop (nested regions stay serial)
-   const int NB = nf >= 4096 ? 128 : 64;
+   const int NB = nf >= 2048 ? 256 : (nf >= 256 ? 128 : 64);   // outer block: K of the BLAS-3 trailing update
+   const int NBI = 32;                                         // inner block
    const bool par = nf >= 1024;
-   w.W.assign(ld * NB, 0.0);
+   if (w.W.size() < ld * NB) w.W.resize(ld * NB);
    double* W = w.W.data();
+   // Restricted pivoting never looks at the rows that are not fully summed (R = [rlim, nf)): they stay out of the column-by-column
+   // work and are brought in once per outer block with BLAS-3 calls (W_R = A_R L_PP^{-T}, L_R = W_R D^{-1}).
+   const int rlim = (o.pivot_mode == 1) ? nfs : nf;
    int ne = 0, active_end = nfs, since_retry = 0;
    double u = o.u;
    bool forcing = false;
    const double tol = o.null_tol;
    while (true) {
+      // Two-level blocking.  Outer block [ostart, obend): its pivots update everything right of it in ONE BLAS-3 call per strip.
+      // Inner block [ne, ibend): factored right-looking, column by column, on NBI columns that stay in cache; when it is done its
+      // pivots update the rest of the outer block (a small dgemm), so every candidate column is up to date when it is tested.
+      // Interchanges only ever involve positions below obend, hence the rows of W used by the outer update never move.
       while (ne < active_end) {
-         const int bstart = ne, bend = std::min(ne + NB, active_end);
-         int cand = ne;
-         while (cand < bend) {
-            // column maxima of candidate c over the not yet eliminated part of the front
-            const int c = cand;
-            double lam_all = 0.0, lam_fs = 0.0;
-            int r = -1;
-            for (int i = ne; i < bend; ++i) {
-               if (i == c) continue;
-               const double v = std::fabs(lower(A, nf, i, c));
-               if (v > lam_fs) { lam_fs = v; r = i; }
-            }
-            lam_all = lam_fs;
-            const int scan_end = o.pivot_mode == 1 ? active_end : nf;
-            {
-               const double* colc = A + ld * c;
-               double m = 0.0;
-#pragma omp parallel for reduction(max : m) if (par)
-               for (int i = bend; i < scan_end; ++i) m = std::max(m, std::fabs(colc[i]));
-               lam_all = std::max(lam_all, m);
-            }
-            const double acc = A[c + ld * c];
-            int step = 0;
-            if (std::fabs(acc) > tol && std::fabs(acc) >= u * lam_all) {
-               step = 1;
-            } else if (r >= 0 && lam_fs > 0.0) {
-               const double b = lower(A, nf, r, c), dd = A[r + ld * r];
-               const double det = acc * dd - b * b;
-               double lc = 0.0, lr = 0.0;
-               for (int i = ne; i < scan_end; ++i) {
-                  if (i == c || i == r) continue;
-                  lc = std::max(lc, std::fabs(lower(A, nf, i, c)));
-                  lr = std::max(lr, std::fabs(lower(A, nf, i, r)));
+         const int ostart = ne, obend = std::min(ne + NB, active_end);
+         int oend = obend;            // candidates that failed with nothing eliminated around them are parked in [oend, obend)
+         while (ne < oend) {
+            const int istart = ne, ibend = std::min(ne + NBI, oend);
+            int cand = ne;
+            while (cand < ibend) {
+               // column maxima of candidate c over the not yet eliminated part of the front
+               const int c = cand;
+               double lam_all = 0.0, lam_fs = 0.0;
+               int r = -1;
+               for (int i = ne; i < ibend; ++i) {
+                  if (i == c) continue;
+                  const double v = std::fabs(lower(A, nf, i, c));
+                  if (v > lam_fs) { lam_fs = v; r = i; }
                }
-               const double g1 = std::fabs(dd) * lc + std::fabs(b) * lr, g2 = std::fabs(b) * lc + std::fabs(acc) * lr;
-               if (std::fabs(det) > tol * tol && std::fabs(b) > tol && u * std::max(g1, g2) <= std::fabs(det)) step = 2;
-            }
-            if (step == 0) { ++cand; continue; }
-            if (step == 1) {
-               swap_sym(A, nf, ne, c, F.idx);
-               const double piv = A[ne + ld * ne];
-               double* wc = W + ld * (ne - bstart);
-               for (int i = ne + 1; i < nf; ++i) { wc[i] = A[i + ld * ne]; A[i + ld * ne] = wc[i] / piv; }
-#pragma omp parallel for schedule(static) if (par)
-               for (int j = ne + 1; j < bend; ++j) {
-                  const double wj = wc[j];
-                  if (wj == 0.0) continue;
-                  double* cj = A + ld * j;
-                  const double* lcol = A + ld * ne;
-                  for (int i = j; i < nf; ++i) cj[i] -= lcol[i] * wj;
+               lam_all = lam_fs;
+               const int scan_end = o.pivot_mode == 1 ? active_end : nf;
+               {
+                  const double* colc = A + ld * c;
+                  double m = 0.0;
+   #pragma omp parallel for reduction(max : m) if (par)
+                  for (int i = ibend; i < scan_end; ++i) m = std::max(m, std::fabs(colc[i]));
+                  lam_all = std::max(lam_all, m);
                }
-               F.d[ne] = piv; F.e[ne] = 0.0; F.ptype[ne] = 0;
-               ne += 1;
+               const double acc = A[c + ld * c];
+               int step = 0;
+               if (std::fabs(acc) > tol && std::fabs(acc) >= u * lam_all) {
+                  step = 1;
+               } else if (r >= 0 && lam_fs > 0.0) {
+                  const double b = lower(A, nf, r, c), dd = A[r + ld * r];
+                  const double det = acc * dd - b * b;
+                  double lc = 0.0, lr = 0.0;
+                  for (int i = ne; i < scan_end; ++i) {
+                     if (i == c || i == r) continue;
+                     lc = std::max(lc, std::fabs(lower(A, nf, i, c)));
+                     lr = std::max(lr, std::fabs(lower(A, nf, i, r)));
+                  }
+                  const double g1 = std::fabs(dd) * lc + std::fabs(b) * lr, g2 = std::fabs(b) * lc + std::fabs(acc) * lr;
+                  if (std::fabs(det) > tol * tol && std::fabs(b) > tol && u * std::max(g1, g2) <= std::fabs(det)) step = 2;
+               }
+               if (step == 0) { ++cand; continue; }
+               if (step == 1) {
+                  swap_sym(A, nf, ne, c, F.idx);
+                  const double piv = A[ne + ld * ne];
+                  double* wc = W + ld * (ne - ostart);
+                  for (int i = ne + 1; i < rlim; ++i) { wc[i] = A[i + ld * ne]; A[i + ld * ne] = wc[i] / piv; }
+   #pragma omp parallel for schedule(static) if (par)
+                  for (int j = ne + 1; j < ibend; ++j) {
+                     const double wj = wc[j];
+                     if (wj == 0.0) continue;
+                     double* cj = A + ld * j;
+                     const double* lcol = A + ld * ne;
+                     for (int i = j; i < rlim; ++i) cj[i] -= lcol[i] * wj;
+                  }
+                  F.d[ne] = piv; F.e[ne] = 0.0; F.ptype[ne] = 0;
+                  ne += 1;
+               } else {
+                  int rr = r;
+                  swap_sym(A, nf, ne, c, F.idx);
+                  if (rr == ne) rr = c;            // the partner sat at position ne and moved to c
+                  swap_sym(A, nf, ne + 1, rr, F.idx);
+                  const double a = A[ne + ld * ne], b = A[ne + 1 + ld * ne], dd = A[ne + 1 + ld * (ne + 1)];
+                  const double det = a * dd - b * b;
+                  double* w1 = W + ld * (ne - ostart);
+                  double* w2 = w1 + ld;
+                  for (int i = ne + 2; i < rlim; ++i) {
+                     w1[i] = A[i + ld * ne]; w2[i] = A[i + ld * (ne + 1)];
+                     A[i + ld * ne] = (dd * w1[i] - b * w2[i]) / det;
+                     A[i + ld * (ne + 1)] = (a * w2[i] - b * w1[i]) / det;
+                  }
+                  w1[ne + 1] = 0.0; w2[ne + 1] = 0.0;
+                  A[ne + 1 + ld * ne] = 0.0;
+   #pragma omp parallel for schedule(static) if (par)
+                  for (int j = ne + 2; j < ibend; ++j) {
+                     const double x1 = w1[j], x2 = w2[j];
+                     double* cj = A + ld * j;
+                     const double* l1 = A + ld * ne;
+                     const double* l2 = A + ld * (ne + 1);
+                     for (int i = j; i < rlim; ++i) cj[i] -= l1[i] * x1 + l2[i] * x2;
+                  }
+                  F.d[ne] = a; F.d[ne + 1] = dd; F.e[ne] = b; F.e[ne + 1] = 0.0; F.ptype[ne] = 1; F.ptype[ne + 1] = 2;
+                  ne += 2;
+               }
+               cand = std::max(cand + 1, ne);   // go on with untested candidates; failed ones are retried in the next block
+            }
+            const int inbw = ne - istart;
+            if (inbw > 0) {
+               // the inner block's pivots on the rest of the outer block; failed candidates [ne, ibend) stay in front (up to date)
+               gemm_nt_sub(rlim - ibend, obend - ibend, inbw, W + ibend + ld * (istart - ostart), nf, A + ibend + ld * istart, nf, A + ibend + ld * ibend, nf);
             } else {
-               int rr = r;
-               swap_sym(A, nf, ne, c, F.idx);
-               if (rr == ne) rr = c;            // the partner sat at position ne and moved to c
-               swap_sym(A, nf, ne + 1, rr, F.idx);
-               const double a = A[ne + ld * ne], b = A[ne + 1 + ld * ne], dd = A[ne + 1 + ld * (ne + 1)];
-               const double det = a * dd - b * b;
-               double* w1 = W + ld * (ne - bstart);
-               double* w2 = w1 + ld;
-               for (int i = ne + 2; i < nf; ++i) {
-                  w1[i] = A[i + ld * ne]; w2[i] = A[i + ld * (ne + 1)];
-                  A[i + ld * ne] = (dd * w1[i] - b * w2[i]) / det;
-                  A[i + ld * (ne + 1)] = (a * w2[i] - b * w1[i]) / det;
-               }
-               w1[ne + 1] = 0.0; w2[ne + 1] = 0.0;
-               A[ne + 1 + ld * ne] = 0.0;
-#pragma omp parallel for schedule(static) if (par)
-               for (int j = ne + 2; j < bend; ++j) {
-                  const double x1 = w1[j], x2 = w2[j];
-                  double* cj = A + ld * j;
-                  const double* l1 = A + ld * ne;
-                  const double* l2 = A + ld * (ne + 1);
-                  for (int i = j; i < nf; ++i) cj[i] -= l1[i] * x1 + l2[i] * x2;
-               }
-               F.d[ne] = a; F.d[ne + 1] = dd; F.e[ne] = b; F.e[ne + 1] = 0.0; F.ptype[ne] = 1; F.ptype[ne + 1] = 2;
-               ne += 2;
+               const int cnt = ibend - ne;
+               for (int t = 0; t < cnt; ++t) { const int a = ne + t, b = oend - 1 - t; if (a < b) swap_sym(A, nf, a, b, F.idx); }
+               oend -= cnt;
             }
-            cand = std::max(cand + 1, ne);   // go on with untested candidates; failed ones are retried in the next block
          }
-         const int nbw = ne - bstart;
+         const int nbw = ne - ostart;
+         if (nbw > 0 && rlim < nf) {
+            // rows R of the block's pivot columns: W_R = A_R L_PP^{-T} (A_R still as the outer block found it), L_R = W_R D^{-1}
+            const int mr = nf - rlim;
+            trsm_right_lower_trans_unit(mr, nbw, A + ostart + ld * ostart, nf, A + rlim + ld * ostart, nf);
+#pragma omp parallel for schedule(static) if (big)
+            for (int p = ostart; p < ne; ++p) {
+               if (F.ptype[p] == 2) continue;
+               double* wp = W + ld * (p - ostart);
+               double* ap = A + ld * p;
+               if (F.ptype[p] == 0) {
+                  const double piv = F.d[p];
+                  for (int i = rlim; i < nf; ++i) { wp[i] = ap[i]; ap[i] = wp[i] / piv; }
+               } else {
+                  double* wq = wp + ld;
+                  double* aq = ap + ld;
+                  const double a = F.d[p], b = F.e[p], dd = F.d[p + 1], det = a * dd - b * b;
+                  for (int i = rlim; i < nf; ++i) {
+                     wp[i] = ap[i]; wq[i] = aq[i];
+                     ap[i] = (dd * wp[i] - b * wq[i]) / det;
+                     aq[i] = (a * wq[i] - b * wp[i]) / det;
+                  }
+               }
+            }
+            // and rows R of the columns of this block that were not eliminated
+            gemm_nt_sub(mr, obend - ne, nbw, W + rlim, nf, A + ne + ld * ostart, nf, A + rlim + ld * ne, nf);
+         }
          if (nbw > 0) {
             since_retry += nbw;
-            // rank-nbw update of everything right of the block: C -= W * L^T, in 256-column strips (lower part only)
-            for (int c0 = bend; c0 < nf; c0 += 256) {
-               const int c1 = std::min(c0 + 256, nf);
-               gemm_nt_sub(nf - c0, c1 - c0, nbw, W + c0, nf, A + c0 + ld * bstart, nf, A + c0 + ld * c0, nf);
+            // rank-nbw update of everything right of the outer block: C -= W * L^T, in 512-column strips (lower part only)
+            for (int c0 = obend; c0 < nf; c0 += 512) {
+               const int c1 = std::min(c0 + 512, nf);
+               gemm_nt_sub(nf - c0, c1 - c0, nbw, W + c0, nf, A + c0 + ld * ostart, nf, A + c0 + ld * c0, nf);
             }
-            // failed candidates [ne, bend) stay in front of the next block (already up to date)
+            // parked candidates [ne, obend) stay in front of the next block (already up to date)
          } else {
             // nothing could be eliminated in this block: set its columns aside and go on
-            const int cnt = bend - ne;
+            const int cnt = obend - ne;
             for (int t = 0; t < cnt; ++t) { const int a = ne + t, b = active_end - 1 - t; if (a < b) swap_sym(A, nf, a, b, F.idx); }
             active_end -= cnt;
          }
@@ -436,13 +537,19 @@ void factor_front(Oracle& o, int s, const double* val, Work& w) {
       ne = nfs;
    }
    F.nelim = ne;
-   F.L.assign(ld * ne, 0.0);
+   // (only the part of a column at and below its diagonal is ever read: nothing is cleared)
+   if (F.L.size() != ld * ne) { std::vector<double>().swap(F.L); F.L.resize(ld * ne); }
+#pragma omp parallel for schedule(static, 8) if (big)
    for (int j = 0; j < ne; ++j) std::memcpy(F.L.data() + ld * j + j, A + ld * j + j, sizeof(double) * (nf - j));
    F.d.resize(ne); F.e.resize(ne); F.ptype.resize(ne);
    F.ncb = nf - ne; F.ndelay = nfs - ne;
    F.cb_idx.assign(F.idx.begin() + ne, F.idx.end());
-   F.cb.assign(static_cast<size_t>(F.ncb) * F.ncb, 0.0);
-   for (int j = ne; j < nf; ++j) std::memcpy(F.cb.data() + static_cast<size_t>(F.ncb) * (j - ne) + (j - ne), A + ld * j + j, sizeof(double) * (nf - j));
+   o.pool.give(F.cb, F.cb_cap);   // a root's block of the previous factorization
+   F.cb = o.pool.take(static_cast<size_t>(F.ncb) * F.ncb, F.cb_cap);
+   double* cbp = F.cb.get();
+   const int ncb_ = F.ncb;
+#pragma omp parallel for schedule(static, 8) if (big)
+   for (int j = ne; j < nf; ++j) std::memcpy(cbp + static_cast<size_t>(ncb_) * (j - ne) + (j - ne), A + ld * j + j, sizeof(double) * (nf - j));
 }
 
 void equilibrate(Oracle& o, const double* val, int sweeps) {
@@ -567,6 +674,7 @@ int oracle_set_blas(const char* path, const char* prefix) {
    if (lib == nullptr) return 0;
    const std::string pre = prefix == nullptr ? "" : prefix;
    g_dgemm = reinterpret_cast<cblas_dgemm_t>(dlsym(lib, (pre + "cblas_dgemm").c_str()));
+   g_dtrsm = reinterpret_cast<cblas_dtrsm_t>(dlsym(lib, (pre + "cblas_dtrsm").c_str()));
    g_set_threads = reinterpret_cast<set_threads_t>(dlsym(lib, (pre + "openblas_set_num_threads").c_str()));
    return g_dgemm != nullptr ? 1 : 0;
 }
