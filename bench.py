@@ -135,7 +135,7 @@ def run_oracle_sample(G, name, seed, steps, warmup, full_flops=None):
     kkt = WORKLOADS[name][2](G, seed)
     # same ordering as the GPU solver (north_star: "same METIS ordering"): host-only handle, symbolic phase only
     host = KKTSolver(device=-1)
-    host.do_symbolic_analysis(kkt.dim, kkt.row, kkt.col, kkt.reg_size, kkt.n)
+    host.do_symbolic_analysis(kkt.dim, kkt.row, kkt.col, kkt.reg_size, kkt.n, values=kkt.val)
     perm, _ = host.permutation()
     sample_flops = host.stats()["flops_factor"]
     host.close()
@@ -190,7 +190,7 @@ def main():
             args.workload = os.environ.get("B200KKT_REFERENCE_WORKLOAD", "ocp3d_k128")
         full = WORKLOADS[args.workload][1](G, 0)
         host = KKTSolver(device=-1)
-        host.do_symbolic_analysis(full.dim, full.row, full.col, full.reg_size, full.n)
+        host.do_symbolic_analysis(full.dim, full.row, full.col, full.reg_size, full.n, values=full.val)
         full_flops = host.stats()["flops_factor"]
         host.close()
         cb = run_oracle_sample(G, args.workload, 0, max(1, args.steps), max(0, min(args.warmup, 1)), full_flops)
@@ -220,7 +220,7 @@ def main():
         t0 = time.perf_counter()
         ok = True
         try:
-            solver.do_symbolic_analysis(kkt.dim, kkt.row, kkt.col, kkt.reg_size, kkt.n)
+            solver.do_symbolic_analysis(kkt.dim, kkt.row, kkt.col, kkt.reg_size, kkt.n, values=kkt.val)   # Uno analyses a filled matrix
         except Exception as exc:   # device pools do not fit
             ok = False
             fallback_note = f"{args.workload} did not fit this device ({exc}); fell back to ocp3d_k64"

@@ -115,6 +115,13 @@ int b200kkt_set_option(b200kkt_handle* h, const char* name, double value);
 /* Optional user ordering for the next analyse (perm[new] = old, length N); NULL clears it. */
 int b200kkt_set_user_permutation(b200kkt_handle* h, const int64_t* perm, uint64_t n);
 
+/* Optional hint for the next b200kkt_analyse: the matrix values (COO order, length nnz) as they are when the pattern is analysed -
+ * Uno hands do_symbolic_analysis a filled matrix (PrimalDualRegularization.hpp:145-149, Preprocessing.cpp:60), MUMPS ignores its
+ * values at JOB=1 (MUMPSSolver.cpp:72-83).  The KKT pairing then matches every multiplier row with the primal column of its
+ * largest equilibrated Jacobian entry, which keeps the 2 x 2 pivots well conditioned (far fewer refinement sweeps on problems
+ * whose weakly coupled variables - controls, slacks - have the lowest degree).  Copied; used by one analysis; NULL clears it. */
+int b200kkt_set_pairing_values(b200kkt_handle* h, const double* values, uint64_t nnz);
+
 /* Symbolic analysis.  Replaces do_symbolic_analysis -> JOB=1 (MUMPSSolver.cpp:72-83,149-157).
  * Re-callable with another pattern/dimension (Preprocessing.cpp:60 then
  * PrimalDualRegularization.hpp:147).  num_primal = number of primal rows n (rows >= n are

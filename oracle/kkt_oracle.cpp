@@ -357,12 +357,24 @@ void factor_front(Oracle& o, int s, const double* val, Work& w) {
    for (int c : F.children) {
       Front& C = o.fronts[c];
       const int ncb = C.ncb;
+      // positions of the child's rows in this front; when they ascend (the rule, unless delayed pivots came along) every
+      // entry (ci >= cj) stays below the diagonal and a child column is one indexed add into a parent column
+      std::vector<int> lc(static_cast<size_t>(ncb));
+      bool ascending = true;
+      for (int ci = 0; ci < ncb; ++ci) { lc[ci] = w.loc[C.cb_idx[ci]]; if (ci > 0 && lc[ci] <= lc[ci - 1]) ascending = false; }
+      const int* lcp = lc.data();
+      const double* cbase = C.cb.get();
       // every (ci, cj) lands on its own entry of the parent: the child's columns can be added side by side
 #pragma omp parallel for schedule(dynamic, 16) if (big && ncb >= 256)
       for (int cj = 0; cj < ncb; ++cj) {
-         const int gj = w.loc[C.cb_idx[cj]];
-         const double* col = C.cb.get() + static_cast<size_t>(ncb) * cj;
-         for (int ci = cj; ci < ncb; ++ci) lower(A, nf, w.loc[C.cb_idx[ci]], gj) += col[ci];
+         const int gj = lcp[cj];
+         const double* col = cbase + static_cast<size_t>(ncb) * cj;
+         if (ascending) {
+            double* dst = A + ld * gj;
+            for (int ci = cj; ci < ncb; ++ci) dst[lcp[ci]] += col[ci];
+         } else {
+            for (int ci = cj; ci < ncb; ++ci) lower(A, nf, lcp[ci], gj) += col[ci];
+         }
       }
       o.pool.give(C.cb, C.cb_cap);
    }

@@ -45,7 +45,7 @@ def main():
         else:
             kkt = G.opf_like(3000, 4050, 600, seed=0, delta_w=100.0)
         multi = partition.create_solver(dist, local, **options)
-        multi.do_symbolic_analysis(kkt.dim, kkt.row, kkt.col, kkt.reg_size, kkt.n)
+        multi.do_symbolic_analysis(kkt.dim, kkt.row, kkt.col, kkt.reg_size, kkt.n, values=kkt.val)
         st = multi.stats()
         times = []
         for it in range(3):
@@ -62,7 +62,7 @@ def main():
             multi.refactorize_shifted(kkt.val[:kkt.reg_size])
             assert multi.get_inertia() == ine
         single = KKTSolver(device=local)
-        single.do_symbolic_analysis(kkt.dim, kkt.row, kkt.col, kkt.reg_size, kkt.n)
+        single.do_symbolic_analysis(kkt.dim, kkt.row, kkt.col, kkt.reg_size, kkt.n, values=kkt.val)
         for it in range(2):
             single.do_numerical_factorization(kkt.val)
             ine1 = single.get_inertia()

@@ -23,7 +23,7 @@ X_TOL = 1e-4        # agreement with the oracle's solution (the reference's own 
 
 def gpu_solver(kkt, **opts):
     s = KKTSolver(device=0, **opts)
-    s.do_symbolic_analysis(kkt.dim, kkt.row, kkt.col, kkt.reg_size, kkt.n if kkt.m else 0)
+    s.do_symbolic_analysis(kkt.dim, kkt.row, kkt.col, kkt.reg_size, kkt.n if kkt.m else 0, values=kkt.val)
     return s
 
 

@@ -17,7 +17,7 @@ ROOT = Path(__file__).resolve().parent.parent
 
 def host_solver(kkt, **opts):
     s = KKTSolver(device=-1, **opts)
-    s.do_symbolic_analysis(kkt.dim, kkt.row, kkt.col, kkt.reg_size, kkt.n if kkt.m else 0)
+    s.do_symbolic_analysis(kkt.dim, kkt.row, kkt.col, kkt.reg_size, kkt.n if kkt.m else 0, values=kkt.val)
     return s
 
 

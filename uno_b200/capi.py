@@ -21,6 +21,7 @@ EXPORTED_SYMBOLS = [
     "b200kkt_plan_fronts", "b200kkt_plan_rows", "b200kkt_debug_assemble", "b200kkt_debug_factor", "b200kkt_get_stream",
     "b200kkt_debug_bench_update", "b200kkt_debug_phase_cycles", "b200kkt_debug_bench_bk",
     "b200kkt_comm_unique_id", "b200kkt_comm_init", "b200kkt_plan_partition", "b200kkt_debug_delay_columns",
+    "b200kkt_set_pairing_values",
 ]
 
 
@@ -84,6 +85,7 @@ def load_library():
     lib.b200kkt_debug_assemble.argtypes = [H, C.c_void_p, C.c_void_p, C.c_void_p]
     lib.b200kkt_debug_factor.argtypes = [H] + [C.c_void_p] * 5
     lib.b200kkt_debug_delay_columns.argtypes = [H, C.c_uint64, C.c_void_p]
+    lib.b200kkt_set_pairing_values.argtypes = [H, C.c_void_p, C.c_uint64]
     lib.b200kkt_comm_unique_id.argtypes = [C.c_void_p]
     lib.b200kkt_comm_init.argtypes = [H, C.c_int, C.c_int, C.c_void_p]
     lib.b200kkt_plan_partition.argtypes = [H, C.c_void_p, C.c_void_p, P(C.c_int64), C.c_void_p, C.c_void_p, P(C.c_double)]
@@ -191,10 +193,16 @@ class KKTSolver:
         self.capacity = int(number_hessian_nonzeros) + int(regularization_size)
         self.reg_size = int(regularization_size)
 
-    def do_symbolic_analysis(self, n, row, col, reg_size=0, num_primal=0):
+    def do_symbolic_analysis(self, n, row, col, reg_size=0, num_primal=0, values=None):
+        """values: the matrix values at analysis time (the reference's do_symbolic_analysis receives the filled matrix):
+        a hint for the KKT pairing only."""
         row = np.ascontiguousarray(row, dtype=np.uint64)
         col = np.ascontiguousarray(col, dtype=np.uint64)
         assert row.shape == col.shape
+        if values is not None:
+            v = np.ascontiguousarray(values, dtype=np.float64)
+            assert v.size == row.size
+            self._check(self._lib.b200kkt_set_pairing_values(self._h, _ptr(v), v.size), "set_pairing_values")
         self.n, self.nnz, self.reg_size = int(n), int(row.size), int(reg_size)
         self._check(self._lib.b200kkt_analyse(self._h, self.n, self.nnz, self.reg_size, int(num_primal), _ptr(row), _ptr(col)), "analyse")
 

@@ -57,6 +57,7 @@ __global__ void k_matrix_inf_norm(CsrArrays A, const double* __restrict__ values
    const int64_t i = blockIdx.x * static_cast<int64_t>(blockDim.x) + threadIdx.x;
    double s = 0.0;
    if (i < A.n) for (int t = A.ptr[i]; t < A.ptr[i + 1]; ++t) s += fabs(values[A.slot[t]]);
+   if (s != s) s = __longlong_as_double(0x7ff0000000000000LL);   // NaN in the values: reported as an infinite norm
    for (int o = 16; o; o >>= 1) s = fmax(s, __shfl_xor_sync(0xffffffffu, s, o));
    if ((threadIdx.x & 31) == 0 && s > 0.0) atomicMax(out_bits, ordered_bits(s));
 }

@@ -24,6 +24,11 @@ struct AnalyseOptions {
    double relax_big_zeros = 0.15;
    double relax_any_zeros = 0.03;
    const int64_t* user_perm = nullptr;   // ordering == 2: perm[new] = old, length N
+   // optional hint for the KKT pairing: matrix values in COO order (length nnz) as they are when the pattern is analysed (Uno
+   // analyses a filled matrix: PrimalDualRegularization.hpp:145-149).  A multiplier row is then matched with the primal column
+   // that carries its largest equilibrated Jacobian entry - the 2 x 2 pivot [[h, a], [a, -dc]] with the largest |a| - instead of
+   // the primal of lowest degree.  Only the pairing uses it; nullptr = structural rule.
+   const double* pair_values = nullptr;
    // METIS_NodeND tuning (0 = METIS default): separators tried per bisection, refinement iterations, allowed imbalance (1/1000)
    int metis_nseps = 0, metis_niter = 0, metis_ufactor = 0;
 };

@@ -790,6 +790,7 @@ void enqueue_factor(b200kkt_handle* h) {
    L += launch_inertia(P.N, h->W, h->d_counters, st, h->partitioned() ? h->d_col_owner : nullptr, h->rank);
    if (h->partitioned()) CKN(comm_allreduce_sum_i32(h->comm, h->d_counters, 8, st, e__));
    CK(cudaMemcpyAsync(h->h_counters, h->d_counters, 8 * sizeof(int), cudaMemcpyDeviceToHost, st));
+   CK(cudaMemcpyAsync(h->h_norms + 7, h->d_norms + 0, sizeof(unsigned long long), cudaMemcpyDeviceToHost, st));   // |K|_inf: inf <=> NaN/Inf in the values
 }
 
 }  // namespace
@@ -866,6 +867,7 @@ void run_factor_once(b200kkt_handle* h) {
    h->inertia[2] = static_cast<uint64_t>(h->h_counters[2]);
    h->factorized = true;
    // NaN/Inf in the values ends up in the D blocks: an error (MUMPS: INFOG(1) < 0), never a sign of an eigenvalue
+   if (!std::isfinite(bits_to_double(h->h_norms[7]))) h->h_counters[6] = 1;
    if (h->h_counters[6] > 0) { h->factorized = false; throw std::runtime_error("factorize: non-finite pivots (the matrix values hold NaN/Inf)"); }
 }
 
@@ -1287,6 +1289,13 @@ int b200kkt_set_user_permutation(b200kkt_handle* h, const int64_t* perm, uint64_
    return B200KKT_OK;
 }
 
+int b200kkt_set_pairing_values(b200kkt_handle* h, const double* values, uint64_t nnz) {
+   if (h == nullptr) return B200KKT_EINVAL;
+   if (values == nullptr) { h->pair_values.clear(); return B200KKT_OK; }
+   try { h->pair_values.assign(values, values + nnz); } catch (const std::bad_alloc&) { return fail(h, B200KKT_ENOMEM, "host allocation failed"); }
+   return B200KKT_OK;
+}
+
 int b200kkt_analyse(b200kkt_handle* h, uint64_t n, uint64_t nnz, uint64_t reg_size, uint64_t num_primal, const uint64_t* row,
                     const uint64_t* col) {
    if (h == nullptr || (nnz > 0 && (row == nullptr || col == nullptr))) return B200KKT_EINVAL;
@@ -1302,6 +1311,7 @@ int b200kkt_analyse(b200kkt_handle* h, uint64_t n, uint64_t nnz, uint64_t reg_si
          if (h->user_perm.size() != n) throw std::runtime_error("analyse: user permutation length differs from N");
          opt.user_perm = h->user_perm.data();
       }
+      if (h->pair_values.size() == nnz && nnz > 0) opt.pair_values = h->pair_values.data();
       analyse(static_cast<int64_t>(n), static_cast<int64_t>(nnz), static_cast<int64_t>(reg_size), static_cast<int64_t>(num_primal), row, col,
               opt, h->plan);
       h->plan.share_min_pivots = h->share_min_pivots;
@@ -1312,6 +1322,7 @@ int b200kkt_analyse(b200kkt_handle* h, uint64_t n, uint64_t nnz, uint64_t reg_si
       h->analysed = true;
    });
    if (rc != B200KKT_OK && h->has_device) free_plan_device(h);
+   std::vector<double>().swap(h->pair_values);   // a hint belongs to one analysis
    return rc;
 }
 

@@ -45,6 +45,7 @@ struct b200kkt_handle {
    // options
    b200kkt::AnalyseOptions aopt;
    std::vector<int64_t> user_perm;
+   std::vector<double> pair_values;          // pairing hint for the next analyse (b200kkt_set_pairing_values); cleared by it
    int scaling_sweeps = 3;
    double null_pivot_tol = 1e-14;
    // delayed pivots (kernels.hpp: FactorArrays::delay): a column that cannot be eliminated inside its front is moved into an

@@ -15,6 +15,7 @@
 
 #include <algorithm>
 #include <chrono>
+#include <cmath>
 #include <cstring>
 #include <map>
 #include <numeric>
@@ -80,8 +81,9 @@ Graph build_adjacency(int64_t N, int64_t nnz, const uint64_t* row, const uint64_
 
 // Match every constraint-like node with a distinct adjacent primal node (bipartite matching:
 // greedy by ascending primal degree, then augmenting paths).  partner[i] = matched node or -1.
-void kkt_pairing(int64_t N, const Graph& g, const std::vector<char>& is_con, std::vector<int32_t>& partner) {
+void kkt_pairing(int64_t N, const Graph& g, const std::vector<char>& is_con, std::vector<int32_t>& partner, const std::vector<float>& wgt) {
    partner.assign(static_cast<size_t>(N), -1);
+   const bool weighted = !wgt.empty();
    auto degree = [&](int32_t v) { return g.ptr[v + 1] - g.ptr[v]; };
    std::vector<int32_t> unmatched;
    int64_t first_con = 0;
@@ -92,12 +94,20 @@ void kkt_pairing(int64_t N, const Graph& g, const std::vector<char>& is_con, std
       // (states and their equations are usually numbered alike, which keeps the compressed graph grid-like)
       int32_t best = -1;
       int64_t best_deg = 0, best_dist = 0;
+      float best_w = 0.f;
       const int64_t ordinal = j - first_con;
       for (int64_t p = g.ptr[j]; p < g.ptr[j + 1]; ++p) {
          const int32_t v = g.idx[p];
          if (is_con[v] || partner[v] != -1) continue;
          const int64_t d = degree(v);
          const int64_t dist = (v > ordinal) ? v - ordinal : ordinal - v;
+         if (weighted) {
+            // largest equilibrated entry first (within a factor of two: the weights are estimates), then the structural rule
+            const float wv = wgt[static_cast<size_t>(p)];
+            const bool better = best == -1 || wv > 2.f * best_w || (wv >= 0.5f * best_w && (d < best_deg || (d == best_deg && dist < best_dist)));
+            if (better) { best = v; best_deg = d; best_dist = dist; best_w = std::max(best_w, wv); }
+            continue;
+         }
          if (best == -1 || d < best_deg || (d == best_deg && dist < best_dist)) { best = v; best_deg = d; best_dist = dist; }
       }
       if (best != -1) { partner[j] = best; partner[best] = static_cast<int32_t>(j); }
@@ -261,7 +271,39 @@ void analyse(int64_t N, int64_t nnz, int64_t reg_size, int64_t num_primal, const
       for (int64_t i = 0; i < N; ++i) if (!has_diag[i] && g.ptr[i + 1] > g.ptr[i]) { is_con[i] = 1; any_con = true; }
    }
    std::vector<int32_t> partner(static_cast<size_t>(N), -1);
-   if (opt.kkt_pairing && any_con) kkt_pairing(N, g, is_con, partner);
+   std::vector<float> wgt;
+   if (opt.kkt_pairing && any_con && opt.pair_values != nullptr) {
+      // |a_ij| s_i s_j per adjacency entry, s = 1 / sqrt(row maximum) (one equilibration sweep on the hint values)
+      std::vector<double> rmax(static_cast<size_t>(N), 0.0);
+      for (int64_t e = 0; e < nnz; ++e) {
+         const double a = std::fabs(opt.pair_values[e]);
+         if (!(a <= 1e300)) continue;
+         rmax[row[e]] = std::max(rmax[row[e]], a);
+         rmax[col[e]] = std::max(rmax[col[e]], a);
+      }
+      std::vector<double> acc(g.idx.size(), 0.0);
+      auto slot = [&](uint64_t r, uint64_t c) {
+         const auto b = g.idx.begin() + g.ptr[r], e2 = g.idx.begin() + g.ptr[r + 1];
+         return static_cast<size_t>(std::lower_bound(b, e2, static_cast<int32_t>(c)) - g.idx.begin());
+      };
+      for (int64_t e = 0; e < nnz; ++e) {
+         if (row[e] == col[e]) continue;
+         const double a = std::fabs(opt.pair_values[e]);
+         if (!(a <= 1e300)) continue;
+         acc[slot(row[e], col[e])] += a;
+         acc[slot(col[e], row[e])] += a;
+      }
+      wgt.resize(g.idx.size());
+      for (int64_t i = 0; i < N; ++i) {
+         const double si = rmax[i] > 0.0 ? 1.0 / std::sqrt(rmax[i]) : 1.0;
+         for (int64_t p = g.ptr[i]; p < g.ptr[i + 1]; ++p) {
+            const int32_t v = g.idx[p];
+            const double sv = rmax[v] > 0.0 ? 1.0 / std::sqrt(rmax[v]) : 1.0;
+            wgt[static_cast<size_t>(p)] = static_cast<float>(acc[static_cast<size_t>(p)] * si * sv);
+         }
+      }
+   }
+   if (opt.kkt_pairing && any_con) kkt_pairing(N, g, is_con, partner, wgt);
    for (int64_t i = 0; i < N; ++i) if (is_con[i] && partner[i] != -1) ++P.num_pairs;
 
    // ---- fill-reducing ordering on the pair-compressed graph -----------------------------------
@@ -276,6 +318,29 @@ void analyse(int64_t N, int64_t nnz, int64_t reg_size, int64_t num_primal, const
       else {
          const int32_t var = is_con[i] ? p : static_cast<int32_t>(i);
          cid[var] = id; cid[partner[var]] = id; cfirst.push_back(var);
+      }
+   }
+   // A vertex left alone whose only neighbour sits in a pair (a control or a slack that enters one constraint only) is a leaf of
+   // the elimination tree wherever it is ordered before that neighbour: it is taken out of the graph METIS sees (which is then
+   // the plain grid of pairs) and ordered first.
+   std::vector<int32_t> leaves_first;
+   if (opt.kkt_pairing && any_con && opt.ordering == 0) {
+      for (int64_t i = 0; i < N; ++i) {
+         if (partner[i] != -1 || g.ptr[i + 1] - g.ptr[i] != 1) continue;
+         if (partner[g.idx[g.ptr[i]]] == -1) continue;
+         leaves_first.push_back(static_cast<int32_t>(i));
+      }
+      if (!leaves_first.empty()) {
+         std::vector<char> gone(static_cast<size_t>(N), 0);
+         for (const int32_t v : leaves_first) gone[v] = 1;
+         std::vector<int32_t> remap(cfirst.size(), -1), cfirst2;
+         for (size_t c = 0; c < cfirst.size(); ++c) {
+            if (gone[cfirst[c]]) continue;
+            remap[c] = static_cast<int32_t>(cfirst2.size());
+            cfirst2.push_back(cfirst[c]);
+         }
+         for (int64_t i = 0; i < N; ++i) cid[i] = gone[i] ? -1 : remap[static_cast<size_t>(cid[i])];
+         cfirst.swap(cfirst2);
       }
    }
    const int64_t cN = static_cast<int64_t>(cfirst.size());
@@ -307,6 +372,7 @@ void analyse(int64_t N, int64_t nnz, int64_t reg_size, int64_t num_primal, const
             if (mnode != a) vwgt[c] = 2;
             for (int64_t p = g.ptr[mnode]; p < g.ptr[mnode + 1]; ++p) {
                const int32_t t = cid[g.idx[p]];
+               if (t < 0) continue;   // a leaf ordered first
                if (mark[t] != c) { mark[t] = static_cast<int32_t>(c); adjncy.push_back(t); }
             }
          }
@@ -328,6 +394,7 @@ void analyse(int64_t N, int64_t nnz, int64_t reg_size, int64_t num_primal, const
    std::vector<int32_t> order(static_cast<size_t>(N)), ipos(static_cast<size_t>(N));
    {
       int64_t out = 0;
+      for (const int32_t v : leaves_first) order[out++] = v;
       for (int64_t c = 0; c < cN; ++c) {
          const int32_t a = cfirst[corder[c]];
          order[out++] = a;

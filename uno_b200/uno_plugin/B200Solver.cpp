@@ -84,6 +84,9 @@ namespace uno {
             ++regularization_size;
          }
       }
+      if (this->backend.pairing_values != nullptr && matrix.number_nonzeros() == this->row_indices.size()) {
+         this->check(this->backend.pairing_values(this->backend.handle, matrix.data_pointer(), this->row_indices.size()), "pairing hint");
+      }
       this->check(this->backend.analyse(this->backend.handle, dimension, this->row_indices.size(), regularization_size, number_primal_rows,
             this->row_indices.data(), this->column_indices.data()), "symbolic analysis");
       this->analysed_dimension = dimension;
@@ -180,6 +183,9 @@ namespace uno {
             const uint64_t* rows, const uint64_t* columns) {
          return b200kkt_analyse(static_cast<b200kkt_handle*>(handle), dimension, number_nonzeros, regularization_size, number_primal, rows, columns);
       }
+      int b200_pairing_values(void* handle, const double* values, uint64_t number_nonzeros) {
+         return b200kkt_set_pairing_values(static_cast<b200kkt_handle*>(handle), values, number_nonzeros);
+      }
       int b200_factorize(void* handle, const double* values) { return b200kkt_factorize(static_cast<b200kkt_handle*>(handle), values); }
       int b200_refactorize(void* handle, const double* values) { return b200kkt_refactorize_shifted(static_cast<b200kkt_handle*>(handle), values); }
       int b200_inertia(const void* handle, uint64_t* positive, uint64_t* negative, uint64_t* zero) {
@@ -245,6 +251,7 @@ namespace uno {
          backend.handle = handle;
          backend.destroy = b200_destroy;
          backend.analyse = b200_analyse;
+         backend.pairing_values = b200_pairing_values;
          backend.factorize = b200_factorize;
          backend.refactorize_shifted = b200_refactorize;
          backend.inertia = b200_inertia;

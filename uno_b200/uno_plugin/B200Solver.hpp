@@ -35,6 +35,9 @@ namespace uno {
       int (*destroy)(void* handle){nullptr};
       int (*analyse)(void* handle, uint64_t dimension, uint64_t number_nonzeros, uint64_t regularization_size, uint64_t number_primal,
          const uint64_t* rows, const uint64_t* columns){nullptr};
+      // optional: the values the matrix holds when its pattern is analysed (a hint for the KKT pairing; the reference hands
+      // do_symbolic_analysis a filled matrix: PrimalDualRegularization.hpp:145-149)
+      int (*pairing_values)(void* handle, const double* values, uint64_t number_nonzeros){nullptr};
       int (*factorize)(void* handle, const double* values){nullptr};
       // optional fast path: only the leading regularization slots changed since the last factorization
       int (*refactorize_shifted)(void* handle, const double* regularization_values){nullptr};
