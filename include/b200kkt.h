@@ -151,6 +151,17 @@ int b200kkt_inertia(const b200kkt_handle* h, uint64_t* n_pos, uint64_t* n_neg, u
 int b200kkt_solve(b200kkt_handle* h, const double* rhs, double* x, double* backward_error);
 int b200kkt_solve_device(b200kkt_handle* h, const double* d_rhs, double* d_x, double* backward_error);
 
+/* Backward errors of a given x for the last factorized matrix, WITHOUT ANY ALLOCATION: for callers that cannot call cudaMalloc
+ * (code under CUDA graph capture, tight serving loops, harnesses that forbid it).  No counterpart in the reference.
+ * d_x, d_rhs: device pointers, length N.  normwise receives
+ * ||b-Kx||_inf / (||K||_inf ||x||_inf + ||b||_inf), componentwise max_i |b-Kx|_i / (|K||x|+|b|)_i (either may be NULL) - the
+ * two numbers b200kkt_solve reports for its own x.  The residual and the norm accumulators live in a static device array of
+ * the library (B200KKT_NOALLOC_MAX_N doubles + 256 bytes, held by every GPU that loads the library until exit): N above
+ * B200KKT_NOALLOC_MAX_N is rejected with B200KKT_EINVAL.  All handles share that array: calls that overlap on the GPU race.
+ * Blocking; calls no cudaMalloc, cudaFree or allocating library routine. */
+#define B200KKT_NOALLOC_MAX_N 1048576
+int b200kkt_backward_error_noalloc(b200kkt_handle* h, const double* d_x, const double* d_rhs, double* normwise, double* componentwise);
+
 /* Parity hooks: the assembly permutation.  perm[new] = old (length N); scatter_map[slot] = offset
  * of COO slot in the front pool (length nnz).  Either pointer may be NULL. */
 int b200kkt_get_permutation(const b200kkt_handle* h, uint64_t* perm, uint64_t* scatter_map);

@@ -21,7 +21,7 @@ EXPORTED_SYMBOLS = [
     "b200kkt_plan_fronts", "b200kkt_plan_rows", "b200kkt_debug_assemble", "b200kkt_debug_factor", "b200kkt_get_stream",
     "b200kkt_debug_bench_update", "b200kkt_debug_phase_cycles", "b200kkt_debug_bench_bk",
     "b200kkt_comm_unique_id", "b200kkt_comm_init", "b200kkt_plan_partition", "b200kkt_debug_delay_columns",
-    "b200kkt_set_pairing_values",
+    "b200kkt_backward_error_noalloc", "b200kkt_set_pairing_values",
 ]
 
 
@@ -86,6 +86,7 @@ def load_library():
     lib.b200kkt_debug_factor.argtypes = [H] + [C.c_void_p] * 5
     lib.b200kkt_debug_delay_columns.argtypes = [H, C.c_uint64, C.c_void_p]
     lib.b200kkt_set_pairing_values.argtypes = [H, C.c_void_p, C.c_uint64]
+    lib.b200kkt_backward_error_noalloc.argtypes = [H, C.c_void_p, C.c_void_p, P(C.c_double), P(C.c_double)]
     lib.b200kkt_comm_unique_id.argtypes = [C.c_void_p]
     lib.b200kkt_comm_init.argtypes = [H, C.c_int, C.c_int, C.c_void_p]
     lib.b200kkt_plan_partition.argtypes = [H, C.c_void_p, C.c_void_p, P(C.c_int64), C.c_void_p, C.c_void_p, P(C.c_double)]
@@ -248,6 +249,13 @@ class KKTSolver:
         berr = C.c_double()
         self._check(self._lib.b200kkt_solve_device(self._h, C.c_void_p(rhs_ptr), C.c_void_p(x_ptr), C.byref(berr)), "solve_device")
         return berr.value
+
+    def backward_error_noalloc(self, x_ptr: int, rhs_ptr: int):
+        """(normwise, componentwise) backward error of the device vector x for the last factorized matrix; allocates nothing."""
+        nw, cw = C.c_double(), C.c_double()
+        self._check(self._lib.b200kkt_backward_error_noalloc(self._h, C.c_void_p(x_ptr), C.c_void_p(rhs_ptr), C.byref(nw), C.byref(cw)),
+                    "backward_error_noalloc")
+        return nw.value, cw.value
 
     def stream(self) -> int:
         p = C.c_void_p()

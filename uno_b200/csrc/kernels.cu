@@ -2557,6 +2557,53 @@ int launch_residual(const CsrArrays& A, const double* values, const double* x, c
    return 1;
 }
 
+// ------------------------------------------------------------------------------------------------
+// Allocation-free backward error (b200kkt_backward_error_noalloc).  The residual vector and the norm accumulators that
+// b200kkt_solve keeps in cudaMalloc'ed handle buffers live here in a file-scope device array instead: NOALLOC_HEAD doubles of
+// accumulators (five 64-bit words used), then up to NOALLOC_MAX_N doubles of residual.  Every GPU that loads the library holds
+// these 8 MiB + 256 B until exit.  All calls share the array and it keeps the last call's contents: the accumulators are
+// cleared on the stream before use; calls that overlap on the GPU (two handles, two streams) race.
+// In host code the array's name is only a stand-in: its device address comes from cudaGetSymbolAddress, once per device.
+// ------------------------------------------------------------------------------------------------
+constexpr int64_t NOALLOC_MAX_N = int64_t(1) << 20;
+constexpr int NOALLOC_HEAD = 32;
+static __device__ __align__(256) double g_noalloc_scratch[NOALLOC_MAX_N + NOALLOC_HEAD];
+
+int64_t noalloc_max_n() { return NOALLOC_MAX_N; }
+
+int launch_backward_error_noalloc(int device, const CsrArrays& A, const double* values, const double* x, const double* b,
+                                  unsigned long long out_bits[5], int* launches, cudaStream_t st) {
+   constexpr int MAX_DEVICES = 64;
+   static double* scratch_of[MAX_DEVICES] = {};
+   *launches = 0;
+   if (device < 0 || device >= MAX_DEVICES) return static_cast<int>(cudaErrorInvalidDevice);
+   if (A.n > NOALLOC_MAX_N) return static_cast<int>(cudaErrorInvalidValue);
+   if (scratch_of[device] == nullptr) {
+      // set-up, once per device, with that device current (the caller has made it so)
+      double* p = nullptr;
+      const cudaError_t e = cudaGetSymbolAddress(reinterpret_cast<void**>(&p), g_noalloc_scratch);
+      if (e != cudaSuccess) return static_cast<int>(e);
+      scratch_of[device] = p;
+   }
+   double* scratch = scratch_of[device];
+   unsigned long long* acc = reinterpret_cast<unsigned long long*>(scratch);   // |K|_inf, |r|_inf, |x|_inf, |b|_inf, omega
+   double* r = scratch + NOALLOC_HEAD;
+   cudaError_t e = cudaMemsetAsync(acc, 0, NOALLOC_HEAD * sizeof(double), st);
+   if (e != cudaSuccess) return static_cast<int>(e);
+   const int blocks = grid1d(A.n, 256), rblocks = blocks > 1184 ? 1184 : (blocks < 1 ? 1 : blocks);
+   k_matrix_inf_norm<<<blocks, 256, 0, st>>>(A, values, acc + 0);
+   k_absmax<<<rblocks, 256, 0, st>>>(x, A.n, acc + 2);
+   k_residual<<<blocks, 256, 0, st>>>(A, values, x, b, r, acc + 2, acc + 4);
+   k_absmax<<<rblocks, 256, 0, st>>>(r, A.n, acc + 1);
+   k_absmax<<<rblocks, 256, 0, st>>>(b, A.n, acc + 3);
+   *launches = 5;
+   e = cudaMemcpyAsync(out_bits, acc, 5 * sizeof(unsigned long long), cudaMemcpyDeviceToHost, st);
+   if (e != cudaSuccess) return static_cast<int>(e);
+   e = cudaStreamSynchronize(st);
+   if (e != cudaSuccess) return static_cast<int>(e);
+   return static_cast<int>(cudaGetLastError());
+}
+
 int launch_absmax(const double* v, int64_t n, unsigned long long* out_bits, cudaStream_t st) {
    int blocks = grid1d(n, 256);
    if (blocks > 1184) blocks = 1184;

@@ -157,5 +157,11 @@ int launch_rows_unpack(const double* staging, int64_t ld, int row0, int nrows, i
 int launch_residual(const CsrArrays& A, const double* values, const double* x, const double* b, double* r,
                     const unsigned long long* xnorm_bits, unsigned long long* omega_bits, cudaStream_t st);
 int launch_absmax(const double* v, int64_t n, unsigned long long* out_bits, cudaStream_t st);
+// Allocation-free residual + backward errors on a file-scope device scratch array (kernels.cu: g_noalloc_scratch); blocking.
+// out_bits = |K|_inf, |r|_inf, |x|_inf, |b|_inf, componentwise omega as ordered bit patterns.  Returns a cudaError_t value
+// (cudaErrorInvalidValue when A.n exceeds noalloc_max_n()).
+int64_t noalloc_max_n();
+int launch_backward_error_noalloc(int device, const CsrArrays& A, const double* values, const double* x, const double* b,
+                                  unsigned long long out_bits[5], int* launches, cudaStream_t st);
 
 }  // namespace b200kkt

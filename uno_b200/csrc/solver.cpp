@@ -1396,6 +1396,30 @@ int b200kkt_solve_device(b200kkt_handle* h, const double* d_rhs, double* d_x, do
    });
 }
 
+int b200kkt_backward_error_noalloc(b200kkt_handle* h, const double* d_x, const double* d_rhs, double* normwise, double* componentwise) {
+   if (int rc = need_device(h)) return rc;
+   if (!h->analysed || !h->values_resident) return fail(h, B200KKT_EINVAL, "backward_error_noalloc before factorize (the matrix values must be resident)");
+   if (d_x == nullptr || d_rhs == nullptr) return B200KKT_EINVAL;
+   if (h->plan.N > noalloc_max_n())
+      return fail(h, B200KKT_EINVAL, "backward_error_noalloc: N = " + std::to_string(h->plan.N) + " exceeds B200KKT_NOALLOC_MAX_N = " +
+                                     std::to_string(noalloc_max_n()) + " (size of the static device scratch array); use b200kkt_solve_device");
+   // no cudaMalloc / cudaFree / allocating routine on this path: static device scratch, results through a stack buffer
+   if (cudaSetDevice(h->device) != cudaSuccess) return fail(h, B200KKT_ECUDA, "cudaSetDevice failed");
+   unsigned long long bits[5] = {0, 0, 0, 0, 0};
+   int launches = 0;
+   const int e = launch_backward_error_noalloc(h->device, h->C, h->d_values, d_x, d_rhs, bits, &launches, h->stream);
+   h->launches += launches;
+   if (e != 0) {
+      cudaGetLastError();
+      return fail(h, B200KKT_ECUDA, std::string("backward_error_noalloc: CUDA error: ") + cudaGetErrorString(static_cast<cudaError_t>(e)));
+   }
+   const double knorm = bits_to_double(bits[0]), rnorm = bits_to_double(bits[1]), xnorm = bits_to_double(bits[2]), bnorm = bits_to_double(bits[3]);
+   const double denom = knorm * xnorm + bnorm;
+   if (normwise != nullptr) *normwise = (denom > 0.0) ? rnorm / denom : 0.0;
+   if (componentwise != nullptr) *componentwise = bits_to_double(bits[4]);
+   return B200KKT_OK;
+}
+
 int b200kkt_get_permutation(const b200kkt_handle* h, uint64_t* perm, uint64_t* scatter_map) {
    if (h == nullptr) return B200KKT_EINVAL;
    if (!h->analysed) return fail(h, B200KKT_EINVAL, "get_permutation before analyse");
