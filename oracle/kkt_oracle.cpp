@@ -110,7 +110,7 @@ struct Front {
    // contribution block handed to the parent (freed once consumed)
    int ncb = 0, ndelay = 0;
    std::vector<int> cb_idx;
-   std::unique_ptr<double[]> cb;       // ncb x ncb, lower triangle valid; from / back to the oracle's buffer pool
+   std::unique_ptr<double[]> cb;       // packed lower triangle of the ncb x ncb block, by columns; from / back to the buffer pool
    size_t cb_cap = 0;
 };
 
@@ -368,7 +368,8 @@ void factor_front(Oracle& o, int s, const double* val, Work& w) {
 #pragma omp parallel for schedule(dynamic, 16) if (big && ncb >= 256)
       for (int cj = 0; cj < ncb; ++cj) {
          const int gj = lcp[cj];
-         const double* col = cbase + static_cast<size_t>(ncb) * cj;
+         // column cj of the packed triangle starts at cj ncb - cj (cj - 1) / 2 and holds rows cj .. ncb - 1
+         const double* col = cbase + (static_cast<size_t>(cj) * ncb - static_cast<size_t>(cj) * (cj - 1) / 2) - cj;
          if (ascending) {
             double* dst = A + ld * gj;
             for (int ci = cj; ci < ncb; ++ci) dst[lcp[ci]] += col[ci];
@@ -557,11 +558,14 @@ void factor_front(Oracle& o, int s, const double* val, Work& w) {
    F.ncb = nf - ne; F.ndelay = nfs - ne;
    F.cb_idx.assign(F.idx.begin() + ne, F.idx.end());
    o.pool.give(F.cb, F.cb_cap);   // a root's block of the previous factorization
-   F.cb = o.pool.take(static_cast<size_t>(F.ncb) * F.ncb, F.cb_cap);
+   F.cb = o.pool.take(static_cast<size_t>(F.ncb) * (F.ncb + 1) / 2, F.cb_cap);
    double* cbp = F.cb.get();
-   const int ncb_ = F.ncb;
+   const size_t ncb_ = static_cast<size_t>(F.ncb);
 #pragma omp parallel for schedule(static, 8) if (big)
-   for (int j = ne; j < nf; ++j) std::memcpy(cbp + static_cast<size_t>(ncb_) * (j - ne) + (j - ne), A + ld * j + j, sizeof(double) * (nf - j));
+   for (int j = ne; j < nf; ++j) {
+      const size_t cj = static_cast<size_t>(j - ne);
+      std::memcpy(cbp + (cj * ncb_ - cj * (cj - 1) / 2), A + ld * j + j, sizeof(double) * (nf - j));
+   }
 }
 
 void equilibrate(Oracle& o, const double* val, int sweeps) {

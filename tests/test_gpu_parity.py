@@ -266,6 +266,57 @@ def test_config3_delayed_pivots_give_the_exact_inertia():
     assert s.get_inertia() == (kkt.n, kkt.m, 0)
 
 
+BASELINE_CASES = {
+    "config2_ocp2d_k256": lambda: G.ocp_distributed(256, 2),
+    "config3_opf_10k": lambda: G.opf_like(delta_w=100.0),
+    "config4_ocp3d_k64": lambda: G.ocp_distributed(64, 3),
+}
+
+
+@pytest.mark.parametrize("name", sorted(BASELINE_CASES))
+def test_baseline_sizes_against_the_live_oracle(name):
+    """BASELINE configs[1..3] at FULL size, GPU against the CPU oracle run live on the same ordering:
+    inertia triple equal (and equal to the structural (n, m, 0)), both backward errors <= 1e-12, solutions agree.  The oracle runs
+    in its restricted-pivoting mode (threshold test over the fully-summed rows, delayed pivots kept): its full-column mode needs
+    the better part of an hour at these sizes."""
+    import os
+    kkt = BASELINE_CASES[name]()
+    s = gpu_solver(kkt)
+    s.do_numerical_factorization(kkt.val)
+    x, berr = s.solve_indefinite_system(kkt.rhs, return_backward_error=True)
+    st = s.stats()
+    perm, _ = s.permutation()
+    O.bind_openblas()
+    o = oracle_solver(kkt, kkt.val, perm=perm, threads=os.cpu_count() or 1, restricted=True)
+    assert tuple(s.get_inertia()) == tuple(o.get_inertia()) == (kkt.n, kkt.m, 0)
+    assert berr <= BERR_TOL and st["backward_error_componentwise_last"] <= BERR_TOL and backward_error(kkt, kkt.val, x) <= BERR_TOL
+    assert st["refine_steps_last"] <= 2
+    xo = o.solve_indefinite_system(kkt.rhs)
+    assert np.max(np.abs(x - xo)) <= X_TOL * np.max(np.abs(xo))
+
+
+def test_config3_with_duplicated_rows_gives_the_singular_verdict():
+    """configs[2], 10 constraint rows duplicated (rank-deficient Jacobian), delta_c = 0: the caller must be told "inertia wrong"
+    and "singular" (PrimalDualRegularization.hpp:157,164-167), as the oracle tells it.  Under restricted pivoting neither the
+    GPU nor the CPU oracle finds all ten zero pivots (see test_rank_deficient_jacobian_triggers_dual_regularization)."""
+    import os
+    kkt = G.opf_like(delta_w=100.0, duplicate_rows=10)
+    s = gpu_solver(kkt, null_pivot_tol=1e-12)
+    s.do_numerical_factorization(kkt.val)
+    pos, neg, zero = s.get_inertia()
+    perm, _ = s.permutation()
+    O.bind_openblas()
+    o = oracle_solver(kkt, kkt.val, perm=perm, threads=os.cpu_count() or 1, restricted=True, null_tol=1e-12)
+    assert s.matrix_is_singular() and o.matrix_is_singular()
+    assert 1 <= zero <= 10 and pos + neg + zero == kkt.dim
+    assert (pos, neg, zero) != (kkt.n, kkt.m, 0) != tuple(o.get_inertia())
+    # with the dual regularization the caller then applies (delta_c = 1e-8 mu^0.25 at mu = 1) both are regular with the right inertia
+    v = kkt.with_regularization(100.0, 1e-8)
+    s.do_numerical_factorization(v)
+    o.do_numerical_factorization(v)
+    assert tuple(s.get_inertia()) == tuple(o.get_inertia()) == (kkt.n, kkt.m, 0)
+
+
 def test_non_finite_values_are_an_error_not_an_inertia():
     """MUMPS would return INFOG(1) < 0; a NaN pivot must never be counted as a negative eigenvalue."""
     kkt = G.ocp_distributed(8, 2, seed=5)
