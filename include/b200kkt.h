@@ -138,6 +138,44 @@ int b200kkt_refactorize_shifted(b200kkt_handle* h, const double* reg_values);
 /* Same as factorize, values already resident in device memory. */
 int b200kkt_factorize_device(b200kkt_handle* h, const double* d_values);
 
+/* ---- the host steps either side of the factorization, on the device --------------------------------------------
+ * No counterpart inside the reference's linear solver: these replace HOST loops of its callers, for models whose derivative
+ * values live in device memory.  All pointers are device pointers; calls are enqueued on the handle's stream and, unless a
+ * scalar comes back, return without waiting.  Sums run in the order of the reference's loops without FMA contraction. */
+
+/* Layout of Uno's augmented-system COO (COOFormat.hpp:119-125, Subproblem.cpp:57-70, PrimalDualInteriorPointProblem.cpp:56-78):
+ * [num_primal_slots x (k,k) | num_dual_slots x (k,k) | model Lagrangian Hessian | one barrier diagonal per bounded variable,
+ *  ascending variable index | Jacobian entries (var, n + j), constraint by constraint]. */
+typedef struct b200kkt_kkt_layout {
+   uint64_t num_primal_slots, num_dual_slots, nnz_hessian, num_barrier, nnz_jacobian;
+} b200kkt_kkt_layout;
+
+/* Fills the handle's resident value array in one kernel: slots = (+delta_w, -delta_c) (COOFormat.hpp:101-110 as called from
+ * PrimalDualRegularization.hpp:178-179), Hessian and Jacobian values copied, barrier diagonals z_L/(x-l) + z_U/(x-u) computed
+ * (PrimalDualInteriorPointProblem.cpp:62-76; d_lower/d_upper hold +-inf where a bound is missing; d_barrier_variable[t] is the
+ * variable of barrier slot t).  Replaces the host fill + the 8 nnz byte upload of b200kkt_factorize. */
+int b200kkt_assemble_kkt_values_device(b200kkt_handle* h, const b200kkt_kkt_layout* layout, const double* d_hessian_values,
+                                       const int32_t* d_barrier_variable, const double* d_x, const double* d_lower, const double* d_upper,
+                                       const double* d_zl, const double* d_zu, const double* d_jacobian_values, double delta_w, double delta_c);
+/* One step of the inertia-correction loop with no PCIe traffic: slots [0, num_primal_slots) <- +delta_w, the other
+ * regularization slots <- -delta_c (PrimalDualRegularization.hpp:178-179,210-211); follow with b200kkt_factorize_resident. */
+int b200kkt_shift_diagonal_device(b200kkt_handle* h, uint64_t num_primal_slots, double delta_w, double delta_c);
+/* Numeric factorization of the resident values (b200kkt_factorize without the upload). */
+int b200kkt_factorize_resident(b200kkt_handle* h);
+/* The resident value array (nnz doubles, analysis order), e.g. for a model that writes its derivatives in place. */
+int b200kkt_get_values_device(b200kkt_handle* h, double** d_values);
+/* rhs = [-(gradient - J^T multipliers) ; -constraints] (Subproblem::assemble_augmented_rhs, Subproblem.cpp:80-99), the Jacobian
+ * read from the resident values.  gradient: n, constraints and multipliers: m, rhs: n + m (n = num_primal of the analysis). */
+int b200kkt_assemble_rhs_device(b200kkt_handle* h, const double* d_gradient, const double* d_constraints, const double* d_multipliers, double* d_rhs);
+/* y = K x with the resident values (SymmetricMatrix::product, SymmetricMatrix.hpp:99-109). */
+int b200kkt_symmetric_product_device(b200kkt_handle* h, const double* d_x, double* d_y);
+/* PrimalDualInteriorPointProblem::assemble_primal_dual_direction (PrimalDualInteriorPointProblem.cpp:173-194): dx = solution[0:n],
+ * dy = -solution[n:n+m], bound-dual directions (:262-277), the primal and dual fraction-to-boundary step lengths (:281-325,
+ * tau = max(tau_min, 1 - mu) is the caller's), and the scaling of (dx, dy) and (dz_L, dz_U) by them.  Blocking (two scalars return). */
+int b200kkt_unpack_direction_device(b200kkt_handle* h, double barrier_parameter, double tau, const double* d_solution, const double* d_x,
+                                    const double* d_lower, const double* d_upper, const double* d_zl, const double* d_zu, double* d_dx, double* d_dy,
+                                    double* d_dzl, double* d_dzu, double* primal_step_length, double* dual_step_length);
+
 /* Inertia of the last factorization.  Replaces get_inertia / number_negative_eigenvalues /
  * matrix_is_singular / rank, i.e. INFOG(12) and INFOG(28) (MUMPSSolver.cpp:124-147). */
 int b200kkt_inertia(const b200kkt_handle* h, uint64_t* n_pos, uint64_t* n_neg, uint64_t* n_zero);

@@ -49,3 +49,40 @@ def test_b200_is_default_linear_solver():
     import subprocess
     out = subprocess.run([str(DRIVER)], capture_output=True, text=True).stdout
     assert "Linear solvers: B200" in out
+
+
+def _expected_primal_regularization(k, shift, scale=1.0, initial=1e-4, increase=2.0):
+    """PrimalRegularization.hpp:90-129 with dense eigenvalues as the inertia: delta = 0 when the smallest diagonal entry is positive,
+    else initial - smallest; doubled (or set to `initial` when it was 0) until H + delta I is positive definite."""
+    import numpy as np
+    import scipy.sparse as sp
+    t = sp.diags([-np.ones(k - 1), np.zeros(k), -np.ones(k - 1)], [-1, 0, 1])
+    e = sp.identity(k)
+    H = scale * ((sp.kron(e, t) + sp.kron(t, e)).toarray() + (4.0 - shift) * np.eye(k * k))
+    smallest = scale * (4.0 - shift)
+    delta = 0.0 if smallest > 0.0 else initial - smallest
+    while np.linalg.eigvalsh(H + delta * np.eye(k * k)).min() <= 0.0:
+        delta = initial if delta == 0.0 else increase * delta
+    return delta
+
+
+@needs_driver
+@pytest.mark.parametrize("shift", [1.5, 0.1, 4.5])
+def test_primal_regularization_strategy_drives_the_oracle(shift):
+    """The reference's PrimalRegularization::regularize_hessian (byrd cadence, Hessian only, m = 0, lazy create + initialize_memory
+    of the solver by name: PrimalRegularization.hpp:79-129) run unchanged on an indefinite grid Hessian."""
+    r = run_driver("hessian:12", "ORACLE", extra=(f"shift={shift}",))
+    assert r["regularization_factors"] == [_expected_primal_regularization(12, shift), _expected_primal_regularization(12, shift, scale=2.0)]
+    assert r["inertia"] == [144, 0, 0] and r["residual"] <= 1e-10 * max(1.0, r["solution_norm"])
+
+
+@pytest.mark.gpu
+@needs_driver
+@pytest.mark.parametrize("shift", [1.5, 0.1, 4.5])
+def test_primal_regularization_strategy_drives_the_b200_solver(shift):
+    """the same strategy object, the B200 solver behind it - same shifts, inertia (n, 0, 0)."""
+    ref = run_driver("hessian:40", "ORACLE", extra=(f"shift={shift}",))
+    r = run_driver("hessian:40", "B200", extra=(f"shift={shift}",))
+    assert r["regularization_factors"] == ref["regularization_factors"]
+    assert r["inertia"] == ref["inertia"] == [1600, 0, 0]
+    assert r["residual"] <= 1e-10 * max(1.0, r["solution_norm"])

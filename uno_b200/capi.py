@@ -22,7 +22,14 @@ EXPORTED_SYMBOLS = [
     "b200kkt_debug_bench_update", "b200kkt_debug_phase_cycles", "b200kkt_debug_bench_bk",
     "b200kkt_comm_unique_id", "b200kkt_comm_init", "b200kkt_plan_partition", "b200kkt_debug_delay_columns",
     "b200kkt_backward_error_noalloc", "b200kkt_set_pairing_values",
+    "b200kkt_assemble_kkt_values_device", "b200kkt_shift_diagonal_device", "b200kkt_factorize_resident", "b200kkt_get_values_device",
+    "b200kkt_assemble_rhs_device", "b200kkt_symmetric_product_device", "b200kkt_unpack_direction_device",
 ]
+
+
+class KKTLayout(C.Structure):
+    _fields_ = [("num_primal_slots", C.c_uint64), ("num_dual_slots", C.c_uint64), ("nnz_hessian", C.c_uint64), ("num_barrier", C.c_uint64),
+                ("nnz_jacobian", C.c_uint64)]
 
 
 class Stats(C.Structure):
@@ -86,6 +93,14 @@ def load_library():
     lib.b200kkt_debug_factor.argtypes = [H] + [C.c_void_p] * 5
     lib.b200kkt_debug_delay_columns.argtypes = [H, C.c_uint64, C.c_void_p]
     lib.b200kkt_set_pairing_values.argtypes = [H, C.c_void_p, C.c_uint64]
+    VP = C.c_void_p
+    lib.b200kkt_assemble_kkt_values_device.argtypes = [H, P(KKTLayout), VP, VP, VP, VP, VP, VP, VP, VP, C.c_double, C.c_double]
+    lib.b200kkt_shift_diagonal_device.argtypes = [H, C.c_uint64, C.c_double, C.c_double]
+    lib.b200kkt_factorize_resident.argtypes = [H]
+    lib.b200kkt_get_values_device.argtypes = [H, P(C.c_void_p)]
+    lib.b200kkt_assemble_rhs_device.argtypes = [H, VP, VP, VP, VP]
+    lib.b200kkt_symmetric_product_device.argtypes = [H, VP, VP]
+    lib.b200kkt_unpack_direction_device.argtypes = [H, C.c_double, C.c_double] + [VP] * 10 + [P(C.c_double), P(C.c_double)]
     lib.b200kkt_backward_error_noalloc.argtypes = [H, C.c_void_p, C.c_void_p, P(C.c_double), P(C.c_double)]
     lib.b200kkt_comm_unique_id.argtypes = [C.c_void_p]
     lib.b200kkt_comm_init.argtypes = [H, C.c_int, C.c_int, C.c_void_p]
@@ -256,6 +271,37 @@ class KKTSolver:
         self._check(self._lib.b200kkt_backward_error_noalloc(self._h, C.c_void_p(x_ptr), C.c_void_p(rhs_ptr), C.byref(nw), C.byref(cw)),
                     "backward_error_noalloc")
         return nw.value, cw.value
+
+    # -- device-side host steps (all arguments are device pointers as integers) ---------------------------------
+    def assemble_kkt_values_device(self, layout, hess_ptr, barrier_var_ptr, x_ptr, lower_ptr, upper_ptr, zl_ptr, zu_ptr, jac_ptr, delta_w=0.0, delta_c=0.0):
+        lay = KKTLayout(*[int(v) for v in layout])
+        vp = lambda p: C.c_void_p(int(p) if p else None)  # noqa: E731
+        self._check(self._lib.b200kkt_assemble_kkt_values_device(self._h, C.byref(lay), vp(hess_ptr), vp(barrier_var_ptr), vp(x_ptr), vp(lower_ptr), vp(upper_ptr),
+                                                                 vp(zl_ptr), vp(zu_ptr), vp(jac_ptr), float(delta_w), float(delta_c)), "assemble_kkt_values_device")
+
+    def shift_diagonal_device(self, num_primal_slots, delta_w, delta_c):
+        self._check(self._lib.b200kkt_shift_diagonal_device(self._h, int(num_primal_slots), float(delta_w), float(delta_c)), "shift_diagonal_device")
+
+    def factorize_resident(self):
+        self._check(self._lib.b200kkt_factorize_resident(self._h), "factorize_resident")
+
+    def values_device(self) -> int:
+        p = C.c_void_p()
+        self._check(self._lib.b200kkt_get_values_device(self._h, C.byref(p)), "get_values_device")
+        return int(p.value or 0)
+
+    def assemble_rhs_device(self, gradient_ptr, constraints_ptr, multipliers_ptr, rhs_ptr):
+        self._check(self._lib.b200kkt_assemble_rhs_device(self._h, C.c_void_p(gradient_ptr), C.c_void_p(constraints_ptr), C.c_void_p(multipliers_ptr), C.c_void_p(rhs_ptr)),
+                    "assemble_rhs_device")
+
+    def symmetric_product_device(self, x_ptr, y_ptr):
+        self._check(self._lib.b200kkt_symmetric_product_device(self._h, C.c_void_p(x_ptr), C.c_void_p(y_ptr)), "symmetric_product_device")
+
+    def unpack_direction_device(self, mu, tau, sol, x, lower, upper, zl, zu, dx, dy, dzl, dzu):
+        ps, ds = C.c_double(), C.c_double()
+        args = [C.c_void_p(int(p) if p else None) for p in (sol, x, lower, upper, zl, zu, dx, dy, dzl, dzu)]
+        self._check(self._lib.b200kkt_unpack_direction_device(self._h, float(mu), float(tau), *args, C.byref(ps), C.byref(ds)), "unpack_direction_device")
+        return ps.value, ds.value
 
     def stream(self) -> int:
         p = C.c_void_p()

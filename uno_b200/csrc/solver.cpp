@@ -89,6 +89,7 @@ void free_plan_device(b200kkt_handle* h) {
    if (h->solve_graph != nullptr) { cudaGraphExecDestroy(h->solve_graph); h->solve_graph = nullptr; }
    for (void* p : h->plan_allocs) cudaFree(p);
    h->plan_allocs.clear();
+   h->d_jt_ptr = h->d_jt_slot = h->d_jt_con = nullptr;
    for (cudaEvent_t e : h->ev_comm) if (e != nullptr) cudaEventDestroy(e);
    h->ev_comm.clear();
    h->analysed = false;
@@ -1359,6 +1360,15 @@ int b200kkt_factorize_device(b200kkt_handle* h, const double* d_values) {
       if (d_values != h->d_values)
          CK(cudaMemcpyAsync(h->d_values, d_values, static_cast<size_t>(h->plan.nnz) * sizeof(double), cudaMemcpyDeviceToDevice, h->stream));
       h->values_resident = true;
+      run_factor(h);
+   });
+}
+
+int b200kkt_factorize_resident(b200kkt_handle* h) {
+   if (int rc = need_device(h)) return rc;
+   if (!h->analysed || !h->values_resident) return fail(h, B200KKT_EINVAL, "factorize_resident: no resident values (b200kkt_assemble_kkt_values_device or a factorize first)");
+   return guarded(h, [&] {
+      CK(cudaSetDevice(h->device));
       run_factor(h);
    });
 }

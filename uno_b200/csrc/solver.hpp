@@ -129,6 +129,10 @@ struct b200kkt_handle {
    double* d_b = nullptr;
    double* d_x = nullptr;
    double* d_r = nullptr;
+   // Jacobian entries of the analysed pattern grouped by variable (ipm.cu: right-hand side on the device); built on first use
+   int* d_jt_ptr = nullptr;
+   int* d_jt_slot = nullptr;
+   int* d_jt_con = nullptr;
    int* d_counters = nullptr;              // 8 ints
    unsigned long long* d_norms = nullptr;  // 4 x u64: |K|_inf, |r|_inf, |x|_inf, |b|_inf
    int* h_counters = nullptr;              // pinned mirrors

@@ -20,6 +20,11 @@
 #include "tools/Logger.hpp"
 #include "tools/UserCallbacks.hpp"
 #include "Uno.hpp"
+#include "ingredients/regularization_strategies/PrimalRegularization.hpp"
+#include "ingredients/regularization_strategies/UnstableRegularization.hpp"
+#include "ingredients/subproblem_solvers/DirectSymmetricIndefiniteLinearSolver.hpp"
+#include "symbolic/Range.hpp"
+#include "tools/Statistics.hpp"
 
 namespace uno {
    class SilentCallbacks : public UserCallbacks {
@@ -113,6 +118,77 @@ namespace uno {
    }
 } // namespace
 
+namespace uno {
+   // The reference's PrimalRegularization (byrd preset: Hessian-only convexification, PrimalRegularization.hpp:79-129), unchanged,
+   // with the two sizes that OptimizationProblem would give it and a window on the solver it creates lazily by name (:82-85).
+   class PrimalRegularizationHarness : public PrimalRegularization<double> {
+   public:
+      explicit PrimalRegularizationHarness(const Options& options): PrimalRegularization<double>(options) { }
+      void set_sizes(size_t dimension_, size_t number_nonzeros_) { this->dimension = dimension_; this->number_nonzeros = number_nonzeros_; }
+      DirectSymmetricIndefiniteLinearSolver<size_t, double>& solver() { return *this->optional_linear_solver; }
+   };
+
+   // `uno_driver hessian:<k> [shift=<s>] linear_solver=<name>`: H = 5-point Laplacian on a k x k grid minus s I (indefinite for s > 0),
+   // upper-triangular COO with n leading regularization slots; regularize_hessian is called twice (the second time on 2 H: the
+   // symbolic analysis is reused), then the regularized system is solved.  One JSON line.
+   int run_primal_regularization(const std::string& model_name, const Options& options) {
+      const size_t k = static_cast<size_t>(std::stoul(model_name.substr(std::string("hessian:").size())));
+      const double shift = options.get_string_optional("shift").has_value() ? std::stod(*options.get_string_optional("shift")) : 1.5;
+      const size_t n = k * k;
+      const size_t number_nonzeros = n + 2 * k * (k - 1);
+      SparseSymmetricMatrix<COOFormat<size_t, double>> hessian(n, number_nonzeros, n);
+      auto fill = [&](double factor) {
+         hessian.reset();
+         for (size_t j = 0; j < k; ++j) {
+            for (size_t i = 0; i < k; ++i) {
+               const size_t node = i + k * j;
+               // column by column, upper triangle (the order of AMPLModel.cpp:170-178)
+               if (j > 0) hessian.insert(node - k, node, -factor);
+               if (i > 0) hessian.insert(node - 1, node, -factor);
+               hessian.insert(node, node, factor * (4. - shift));
+            }
+         }
+      };
+      Statistics statistics;
+      statistics.add_column("regulariz", Statistics::double_width - 4, 1);
+      PrimalRegularizationHarness strategy(options);
+      strategy.set_sizes(n, number_nonzeros);
+      const Inertia expected_inertia{n, 0, 0};
+      double factors[2] = {0., 0.};
+      size_t positive = 0, negative = 0, zero = 0;
+      double residual = 0., solution_norm = 0.;
+      try {
+         for (int pass = 0; pass < 2; ++pass) {
+            fill(pass == 0 ? 1. : 2.);
+            strategy.regularize_hessian(statistics, hessian, Range(n), expected_inertia);
+            factors[pass] = strategy.get_primal_regularization_factor();
+         }
+         const Inertia inertia = strategy.solver().get_inertia();
+         positive = inertia.positive; negative = inertia.negative; zero = inertia.zero;
+         Vector<double> rhs(n), x(n), product(n);
+         for (size_t i = 0; i < n; ++i) rhs[i] = 1. + static_cast<double>(i % 7);
+         strategy.solver().solve_indefinite_system(hessian, rhs, x);
+         product.fill(0.);
+         for (const auto [row_index, column_index, value]: hessian) {
+            product[row_index] += value * x[column_index];
+            if (row_index != column_index) product[column_index] += value * x[row_index];
+         }
+         for (size_t i = 0; i < n; ++i) {
+            residual = std::max(residual, std::abs(rhs[i] - product[i]));
+            solution_norm = std::max(solution_norm, std::abs(x[i]));
+         }
+      }
+      catch (const UnstableRegularization&) {
+         std::printf("UNO_DRIVER_RESULT {\"model\": \"%s\", \"error\": \"UnstableRegularization\"}\n", model_name.c_str());
+         return 1;
+      }
+      std::printf("UNO_DRIVER_RESULT {\"model\": \"%s\", \"linear_solver\": \"%s\", \"n\": %zu, \"shift\": %.17g, \"regularization_factors\": [%.17g, %.17g], "
+            "\"inertia\": [%zu, %zu, %zu], \"residual\": %.6e, \"solution_norm\": %.6e}\n", model_name.c_str(), options.get_string("linear_solver").c_str(), n,
+            shift, factors[0], factors[1], positive, negative, zero, residual, solution_norm);
+      return 0;
+   }
+} // namespace
+
 int main(int argc, char* argv[]) {
    using namespace uno;
    try {
@@ -137,6 +213,7 @@ int main(int argc, char* argv[]) {
       options.overwrite_with(preset_options);
       options.overwrite_with(command_line_options);
       Logger::set_logger(options.get_string("logger"));
+      if (model_name.rfind("hessian:", 0) == 0) return run_primal_regularization(model_name, options);
       return run(model_name, options);
    }
    catch (std::exception& exception) {
