@@ -20,6 +20,9 @@ from __future__ import annotations
 import argparse
 import json
 import os
+
+# before anything loads libgomp: the CPU arm's OpenMP workers must sleep, not spin, while the (pthread) OpenBLAS threads run
+os.environ.setdefault("OMP_WAIT_POLICY", "passive")
 import subprocess
 import sys
 import threading

@@ -100,6 +100,8 @@ int b200kkt_plan_partition(const b200kkt_handle* h, int32_t* owner, int8_t* shar
 /* Options (defaults need no user action).  Names: "ordering" (0 METIS, 1 natural),
  * "kkt_pairing", "relax_small", "relax_mid", "relax_big", "scaling_sweeps", "null_pivot_tol",
  * "refine_max_steps", "refine_tol", "use_graph", "profile_updates", and for the delayed pivots
+ * "positive_definite_target" (0; 1 = Cholesky-type LDL^T without pivot search for the Hessian-convexification path of
+ * PrimalRegularization.hpp:90-129, SURVEY 8(f) rank 4: a pivot that is not positive shows up in the inertia), and
  * "delay_tol" (1e-12), "growth_limit" (0 = off), "max_replans" (8), "adaptive_growth" (1), "adaptive_growth_limit" (1e8).
  *
  * Delayed pivots (what dmumps_c JOB=2 does with threshold pivoting; MUMPSSolver.cpp:85-89 with ICNTL(24)=1 at :36): the pivot

@@ -1,5 +1,9 @@
+import os
 import sys
 from pathlib import Path
+
+# before anything loads libgomp (torch does): the oracle's OpenMP workers must sleep, not spin, next to the OpenBLAS threads
+os.environ.setdefault("OMP_WAIT_POLICY", "passive")
 
 import pytest
 

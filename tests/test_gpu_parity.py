@@ -333,6 +333,40 @@ def test_non_finite_values_are_an_error_not_an_inertia():
         s.solve_indefinite_system(rhs)
 
 
+def test_positive_definite_target_skips_the_pivot_search():
+    """Cholesky-type LDL^T (no search, no interchanges, 1 x 1 pivots) for the Hessian-convexification path.
+    Same verdicts as the pivoting factorization along the caller's shift sequence (PrimalRegularization.hpp:90-129), same
+    solution once the matrix is positive definite."""
+    import scipy.sparse as sp
+    k = 48
+    n = k * k
+    t = sp.diags([-np.ones(k - 1), np.zeros(k), -np.ones(k - 1)], [-1, 0, 1])
+    H = sp.triu(sp.kron(sp.identity(k), t) + sp.kron(t, sp.identity(k)) + 2.5 * sp.identity(n)).tocoo()     # 5-point stencil, diagonal 2.5: indefinite
+    row = np.concatenate([np.arange(n), H.row]).astype(np.uint64)
+    col = np.concatenate([np.arange(n), H.col]).astype(np.uint64)
+    kkt = G.KKTSystem("hessian", n, 0, n, row, col, np.concatenate([np.zeros(n), H.data]), np.random.default_rng(1).standard_normal(n))
+    ref, pd = gpu_solver(kkt), gpu_solver(kkt, positive_definite_target=1)
+    delta, verdicts = 0.0, []
+    while True:
+        v = kkt.with_regularization(delta, 0.0)
+        ref.do_numerical_factorization(v)
+        pd.do_numerical_factorization(v)
+        ok_ref, ok_pd = ref.get_inertia() == (n, 0, 0), pd.get_inertia() == (n, 0, 0)
+        assert ok_ref == ok_pd
+        verdicts.append(ok_pd)
+        if ok_pd:
+            break
+        delta = 1e-4 if delta == 0.0 else 2.0 * delta
+    assert len(verdicts) > 5 and delta > 1.0
+    _, _, _, ptype, lperm = pd.debug_factor(want_pool=False)
+    first = pd.plan()["first_col"]
+    assert np.all(ptype == 0)                                                   # 1 x 1 pivots only ...
+    assert np.array_equal(lperm, np.arange(n) - np.repeat(first, pd.plan()["k"]))   # ... in the given order
+    x, berr = pd.solve_indefinite_system(kkt.rhs, return_backward_error=True)
+    xr = ref.solve_indefinite_system(kkt.rhs)
+    assert berr <= BERR_TOL and np.max(np.abs(x - xr)) <= 1e-10 * np.max(np.abs(xr))
+
+
 @pytest.mark.parametrize("make,name", [(lambda: G.ocp_distributed(256, 2), "config2"), (lambda: G.ocp_distributed(32, 3), "3d_k32")])
 def test_full_size_properties(make, name):
     """At BASELINE sizes the oracle is too slow: check structural inertia (convex OCP: exactly (n, m, 0)),

@@ -282,7 +282,7 @@ __device__ __forceinline__ double warp_max(const double v) {
 // multiply-adds and 32 stores per lane instead of 64 loads + 32 stores, and the division overlaps the loads.
 // During the factorization column j of L lives in M[j][i] (i > j); the block is transposed at the end so that
 // callers find L11 in the strict lower triangle S.B[i][j].
-__device__ void bk_factor_block(BkShared& S, const int n, const int lane, const double tol) {
+__device__ void bk_factor_block(BkShared& S, const int n, const int lane, const double tol, const bool nopiv = false) {
    S.p[lane] = lane;
    S.d[lane] = 1.0;
    S.e[lane] = 0.0;
@@ -306,7 +306,9 @@ __device__ void bk_factor_block(BkShared& S, const int n, const int lane, const 
       if (lam >= 0.0) r = __ffs(__ballot_sync(0xffffffffu, v == lam)) - 1; else lam = 0.0;
       int kp = j, step = 1;
       bool isnull = false;
-      if (!(fmax(absajj, lam) > tol)) {
+      if (nopiv) {
+         isnull = !(absajj > tol);   // pivots in the given order; a non-positive one is the caller's answer
+      } else if (!(fmax(absajj, lam) > tol)) {
          isnull = true;
       } else if (absajj >= BK_ALPHA * lam) {
          // 1x1 pivot, no interchange
@@ -486,7 +488,7 @@ __device__ __forceinline__ double fast_div(const double x, const double d, const
 // Bunch-Kaufman by four warps: lane i owns row i, warp w the columns [8w, 8w + 8) of the Schur complement
 // (registers a[]) and of the inverse (registers x[]).  The mirror in shared memory serves everything that is
 // indexed by a run-time column: pivot search, pivot row broadcast, interchanges.  One barrier per step.
-__device__ void bk_factor_block4(Bk4Shared& S, const int n, const int tid, const double tol, double (&x)[8]) {
+__device__ void bk_factor_block4(Bk4Shared& S, const int n, const int tid, const double tol, double (&x)[8], const bool nopiv) {
    const int lane = tid & 31, w = tid >> 5, c0 = 8 * w;
    if (w == 0) {
       S.p[lane] = lane; S.d[lane] = 1.0; S.e[lane] = 0.0; S.type[lane] = 0;
@@ -513,7 +515,9 @@ __device__ void bk_factor_block4(Bk4Shared& S, const int n, const int tid, const
       if (lam >= 0.0) r = __ffs(__ballot_sync(0xffffffffu, v == lam)) - 1; else lam = 0.0;
       int kp = j, step = 1;
       bool isnull = false, looked = false;
-      if (!(fmax(absajj, lam) > tol)) {
+      if (nopiv) {
+         isnull = !(absajj > tol);
+      } else if (!(fmax(absajj, lam) > tol)) {
          isnull = true;
       } else if (absajj >= BK_ALPHA * lam) {
          // 1x1 pivot, no interchange
@@ -765,7 +769,7 @@ __global__ void __launch_bounds__(DP_THREADS) k_diagpanel(FrontArrays F, const i
             named_sync<3, DP_THREADS>();   // the update group has written this block into S.B
          }
          double x[8];
-         bk_factor_block4(S, nbw, tid, null_tol, x);
+         bk_factor_block4(S, nbw, tid, null_tol, x, W.no_pivot != 0);
          double* Xx = XB + (b & 1) * 2 * NBI * XB_LD;
          publish_inverse(S, nbw, tid, x, Xx, Xx + NBI * XB_LD, Xg + b * 2 * NBI * NBI);
          // the factored block back to the panel: D on the diagonal, L11 below it
@@ -1177,7 +1181,7 @@ __global__ void __launch_bounds__(64) k_diag32(FrontArrays F, const int* __restr
       S.B[r][c] = v;
    }
    __syncthreads();
-   if (tid < 32) bk_factor_block(S, nbw, tid, null_tol);
+   if (tid < 32) bk_factor_block(S, nbw, tid, null_tol, W.no_pivot != 0);
    __syncthreads();
    for (int idx = tid; idx < NBI * NBI; idx += 64) {
       const int r = idx % NBI, c = idx / NBI;

@@ -66,6 +66,10 @@ struct FactorArrays {
    int* ndelay;
    double delay_tol;
    double growth_limit;   // 0: guard off
+   // 1: positive-definite target (the byrd preset's Hessian convexification, PrimalRegularization.hpp:90-129):
+   // pivots are taken in the given order, 1 x 1 only, no search, no interchanges - a Cholesky-type LDL^T.  A pivot that is not
+   // positive simply shows up in the inertia, which is all that caller asks ("is H + delta I positive definite yet?").
+   int no_pivot;
 };
 
 // K1' equilibration sweep (power-of-two Ruiz step) and K-infinity norm

@@ -621,6 +621,8 @@ void enqueue_factor(b200kkt_handle* h) {
    cudaStream_t st = h->stream;
    int64_t& L = h->launches;
    h->W.delay_tol = std::max(h->delay_tol, h->null_pivot_tol);   // what is null inside the block is null outside it too
+   h->W.no_pivot = h->positive_definite_target != 0 ? 1 : 0;
+   if (h->W.no_pivot) h->W.delay_tol = 1e300;                    // nothing is postponed: a failed pivot is the verdict "not positive definite"
    CK(cudaMemsetAsync(h->d_counters, 0, 8 * sizeof(int), st));
    CK(cudaMemsetAsync(h->W.delay, 0, static_cast<size_t>(P.N) * sizeof(int), st));
    // K1' equilibration
@@ -915,7 +917,7 @@ void replan_with_delays(b200kkt_handle* h, const std::vector<int32_t>& cols) {
 
 void run_factor(b200kkt_handle* h) {
    h->replans_last = 0;
-   const double limit = h->growth_limit > 0.0 ? h->growth_limit : ((h->growth_armed && h->adaptive_growth != 0) ? h->adaptive_growth_limit : 0.0);
+   const double limit = h->positive_definite_target != 0 ? 0.0 : h->growth_limit > 0.0 ? h->growth_limit : ((h->growth_armed && h->adaptive_growth != 0) ? h->adaptive_growth_limit : 0.0);
    h->growth_armed = false;
    if (limit != h->growth_baked && h->factor_graph != nullptr) { cudaGraphExecDestroy(h->factor_graph); h->factor_graph = nullptr; }
    h->growth_baked = limit;
@@ -1254,6 +1256,7 @@ int b200kkt_set_option(b200kkt_handle* h, const char* name, double value) {
    else if (n == "delay_tol") h->delay_tol = value;
    else if (n == "growth_limit") h->growth_limit = value;
    else if (n == "max_replans") h->max_replans = std::max(0, static_cast<int>(value));
+   else if (n == "positive_definite_target") h->positive_definite_target = static_cast<int>(value);
    else if (n == "adaptive_growth") h->adaptive_growth = static_cast<int>(value);
    else if (n == "adaptive_growth_limit") h->adaptive_growth_limit = value;
    else if (n == "adaptive_growth_trigger") h->adaptive_growth_trigger = value;

@@ -55,6 +55,7 @@ struct b200kkt_handle {
    // the guard switches itself on for ONE factorization (limit adaptive_growth_limit) after a solve whose first sweep missed
    // adaptive_growth_trigger in the normwise backward error: restricted pivoting let L grow; the columns responsible move up
    // and stay there, so the following factorizations of the pattern deliver the accuracy without the extra sweeps
+   int positive_definite_target = 0;   // kernels.hpp: FactorArrays::no_pivot
    int adaptive_growth = 1;
    double adaptive_growth_limit = 1e8;
    double adaptive_growth_trigger = 1e-12;

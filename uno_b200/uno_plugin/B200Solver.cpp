@@ -57,6 +57,12 @@ namespace uno {
       this->analysed_regularization_size = regularization_size;
       this->rhs.resize(dimension);
       this->solution.resize(dimension);
+      // An instance sized without constraints is the one PrimalRegularization creates for the Hessian convexification
+      // (PrimalRegularization.hpp:82-85: initialize_memory(dimension, 0, ...)): every matrix it sees is meant to become positive
+      // definite and only "inertia == (n, 0, 0)?" is asked, so the factorization can skip the pivot search.
+      if (this->backend.set_option != nullptr) {
+         this->check(this->backend.set_option(this->backend.handle, "positive_definite_target", number_constraints == 0 ? 1. : 0.), "option");
+      }
    }
 
    void KKTSolverAdapter::do_symbolic_analysis(const SymmetricMatrix<size_t, double>& matrix) {
@@ -186,6 +192,7 @@ namespace uno {
       int b200_pairing_values(void* handle, const double* values, uint64_t number_nonzeros) {
          return b200kkt_set_pairing_values(static_cast<b200kkt_handle*>(handle), values, number_nonzeros);
       }
+      int b200_set_option(void* handle, const char* name, double value) { return b200kkt_set_option(static_cast<b200kkt_handle*>(handle), name, value); }
       int b200_factorize(void* handle, const double* values) { return b200kkt_factorize(static_cast<b200kkt_handle*>(handle), values); }
       int b200_refactorize(void* handle, const double* values) { return b200kkt_refactorize_shifted(static_cast<b200kkt_handle*>(handle), values); }
       int b200_inertia(const void* handle, uint64_t* positive, uint64_t* negative, uint64_t* zero) {
@@ -252,6 +259,7 @@ namespace uno {
          backend.destroy = b200_destroy;
          backend.analyse = b200_analyse;
          backend.pairing_values = b200_pairing_values;
+         backend.set_option = b200_set_option;
          backend.factorize = b200_factorize;
          backend.refactorize_shifted = b200_refactorize;
          backend.inertia = b200_inertia;

@@ -38,6 +38,8 @@ namespace uno {
       // optional: the values the matrix holds when its pattern is analysed (a hint for the KKT pairing; the reference hands
       // do_symbolic_analysis a filled matrix: PrimalDualRegularization.hpp:145-149)
       int (*pairing_values)(void* handle, const double* values, uint64_t number_nonzeros){nullptr};
+      // optional: named numeric options of the backend (include/b200kkt.h: b200kkt_set_option)
+      int (*set_option)(void* handle, const char* name, double value){nullptr};
       int (*factorize)(void* handle, const double* values){nullptr};
       // optional fast path: only the leading regularization slots changed since the last factorization
       int (*refactorize_shifted)(void* handle, const double* regularization_values){nullptr};
