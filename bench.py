@@ -146,6 +146,7 @@ def measure_cpu(G, name, slot, steps, warmup):
     res.update({"workload": kkt.name, "N": kkt.dim, "factor_flops": info["flops"], "factor_gflops": info["flops"] / res["factor_seconds"] / 1e9,
                 "value": 1.0 / res["seconds_per_step"], "steps": steps, "warmup": warmup, "cores": cores, "cpu": CA.cpu_model(),
                 "expected_inertia": [kkt.n, kkt.m, 0], "plan": info})
+    res["host_dgemm_peak_gflops"] = CA.host_dgemm_peak_gflops()
     mp = CA.mumps_probe()
     res["mumps"] = mp["note"] if not mp["available"] else CA.run_mumps(mp["exe"], kkt, perm, cores)
     return res
@@ -159,6 +160,8 @@ def cpu_baseline_object(res, what):
                       f"OpenBLAS dgemm/dtrsm {'bound' if res['openblas'] else 'NOT bound (plain loops)'}, same ordering as the GPU run; inertia {res['inertia']}",
             "seconds_per_step": res["seconds_per_step"], "factor_seconds": res["factor_seconds"], "factor_gflops": res["factor_gflops"],
             "steps": res["steps"], "warmup": res["warmup"], "inertia": res["inertia"], "backward_error_first_sweep": res["backward_error_first_sweep"],
+            "host_dgemm_peak_gflops": res["host_dgemm_peak_gflops"],
+            "dgemm_peak_note": "numpy (OpenBLAS) DGEMM 4096^3 on all host cores, best of 3: no CPU factorization of F flops on this box can take less than F / this",
             "mumps": res["mumps"]}
 
 
@@ -215,6 +218,12 @@ def main():
             res = measure_cpu(G, requested, 1, more, 1) if more > 1 else one
             if more > 1:
                 runs.append(res)
+        # not a measurement of the workload, a floor: the requested workload's factor flops at 100 % of the host's measured DGEMM peak
+        floor = None
+        if args.workload == "ocp3d_k128" and requested != args.workload:
+            floor = {"workload": args.workload, "factor_flops_estimate": full_flops_estimate, "host_dgemm_peak_gflops": res["host_dgemm_peak_gflops"],
+                     "seconds_at_dgemm_peak": full_flops_estimate / (res["host_dgemm_peak_gflops"] * 1e9),
+                     "note": "lower bound on ANY CPU factorization of the b200 arm's workload on this box; the b200 arm's ms_per_step divides into it"}
         cb = cpu_baseline_object(res, "reference arm")
         line = {"impl": "reference", "metric": METRIC, "value": res["value"], "unit": UNIT, "n_gpus": args.gpus, "steps": res["steps"], "warmup": res["warmup"],
                 "steps_requested": args.steps, "warmup_requested": args.warmup,
@@ -223,6 +232,7 @@ def main():
                 "config": {"workload": f"{requested}: {WORKLOADS[requested][0]}", "N": res["N"], "factor_flops": res["factor_flops"],
                            "parallelism": f"host cores ({res['cores']} threads)", "note": res.get("note")},
                 "cpu_baseline": cb, "e2e": {"value": res["value"], "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0}, "gpu_launches": 0,
+                "cpu_time_floor_for_requested_workload": None if floor is None else floor,
                 "measured_runs": [{k: r[k] for k in ("workload", "N", "factor_flops", "seconds_per_step", "factor_seconds", "factor_gflops", "steps", "warmup", "inertia")} for r in runs],
                 "wall_seconds_total": time.perf_counter() - t_start}
         assert res["inertia"] == res["expected_inertia"], (res["inertia"], res["expected_inertia"])
@@ -424,6 +434,10 @@ def main():
             # bounded sample of the workload (slot 2 of WORKLOADS), measured; value = the sample's own factorize+solve/s
             res_cpu = measure_cpu(G, args.workload, 2, 1, 0)
             line["cpu_baseline"] = cpu_baseline_object(res_cpu, "bounded sample of the workload")
+            floor_s = st0["flops_factor"] / (res_cpu["host_dgemm_peak_gflops"] * 1e9)
+            line["cpu_baseline"]["time_floor_this_workload"] = {
+                "seconds_at_host_dgemm_peak": floor_s, "b200_seconds_per_step": elapsed / args.steps, "speedup_lower_bound": floor_s / (elapsed / args.steps),
+                "note": "this workload's exact factor flops at 100 % of the host's measured DGEMM peak: a floor for any CPU solver on this box, MUMPS included"}
         except Exception as exc:   # the oracle is only a reported baseline
             line["cpu_baseline"] = {"value": None, "unit": UNIT, "cores": os.cpu_count(), "kind": "port", "sample": f"failed: {exc}"}
     print(json.dumps(line))

@@ -97,6 +97,20 @@ def run_oracle(kkt, perm, steps: int, warmup: int, threads: int):
             "backward_error_first_sweep": berr, "delayed_pivots": int(st["delayed"]), "openblas": bool(has_blas), "analyse_seconds": t_analyse}
 
 
+def host_dgemm_peak_gflops(n: int = 4096, repeats: int = 3) -> float:
+    """DGEMM n^3 on all host cores through numpy's BLAS, best of `repeats`: the ceiling of ANY CPU factorization on this box."""
+    rng = np.random.default_rng(0)
+    a = rng.standard_normal((n, n))
+    b = rng.standard_normal((n, n))
+    a @ b
+    best = 1e300
+    for _ in range(repeats):
+        t0 = time.perf_counter()
+        a @ b
+        best = min(best, time.perf_counter() - t0)
+    return 2.0 * n ** 3 / best / 1e9
+
+
 def cpu_model() -> str:
     try:
         for line in Path("/proc/cpuinfo").read_text().splitlines():

@@ -135,6 +135,19 @@ struct BufferPool {
    }
 };
 
+// per-thread scratch, kept from one factorization to the next.  The dense buffers are raw memory: they are never cleared as a
+// whole (only the lower triangle of a front is), and they grow geometrically so that a rising sequence of front sizes does not
+// re-allocate (and page-fault) at every step.
+struct Work {
+   std::vector<int> loc;
+   std::unique_ptr<double[]> A, W;
+   size_t capA = 0, capW = 0;
+   static double* ensure(std::unique_ptr<double[]>& buf, size_t& cap, size_t need) {
+      if (need > cap) { cap = need + need / 2; buf.reset(); buf.reset(new double[cap]); }
+      return buf.get();
+   }
+};
+
 struct Oracle {
    int64_t N = 0, nnz = 0;
    std::vector<int> perm, iperm;       // perm[new] = old
@@ -146,6 +159,7 @@ struct Oracle {
    std::vector<std::vector<int>> levels;
    std::vector<double> scale;
    BufferPool pool;
+   std::vector<Work> works;
    uint64_t pos = 0, neg = 0, zero = 0;
    int64_t n2x2 = 0, ndelayed = 0;
    double nnzL = 0, flops = 0, t_analyse = 0, t_factor = 0, t_solve = 0;
@@ -308,11 +322,6 @@ void analyse(Oracle& o, int64_t N, int64_t nnz, const uint64_t* row, const uint6
 namespace {
 
 // ---- numeric phase: multifrontal LDL^T, threshold pivoting, delayed pivots -----------------------
-struct Work {
-   std::vector<int> loc;
-   std::vector<double> A, W;
-};
-
 inline double& lower(double* A, int nf, int i, int j) { return (i >= j) ? A[i + static_cast<size_t>(nf) * j] : A[j + static_cast<size_t>(nf) * i]; }
 
 // symmetric interchange of indices a < b in a lower-stored nf x nf matrix
@@ -339,8 +348,7 @@ void factor_front(Oracle& o, int s, const double* val, Work& w) {
    F.nf = nf;
    const size_t ld = static_cast<size_t>(nf);
    // only the lower triangle is ever read: it alone is cleared (the BLAS strips may leave anything above the diagonal)
-   if (w.A.size() < ld * nf) w.A.resize(ld * nf);
-   double* A = w.A.data();
+   double* A = Work::ensure(w.A, w.capA, ld * nf);
    const bool big = nf >= 1024;
 #pragma omp parallel for schedule(static, 16) if (big)
    for (int j = 0; j < nf; ++j) std::memset(A + ld * j + j, 0, sizeof(double) * static_cast<size_t>(nf - j));
@@ -385,8 +393,7 @@ void factor_front(Oracle& o, int s, const double* val, Work& w) {
    const int NB = nf >= 2048 ? 256 : (nf >= 256 ? 128 : 64);   // outer block: K of the BLAS-3 trailing update
    const int NBI = 32;                                         // inner block
    const bool par = nf >= 1024;
-   if (w.W.size() < ld * NB) w.W.resize(ld * NB);
-   double* W = w.W.data();
+   double* W = Work::ensure(w.W, w.capW, ld * NB);
    // Restricted pivoting never looks at the rows that are not fully summed (R = [rlim, nf)): they stay out of the column-by-column
    // work and are brought in once per outer block with BLAS-3 calls (W_R = A_R L_PP^{-T}, L_R = W_R D^{-1}).
    const int rlim = (o.pivot_mode == 1) ? nfs : nf;
@@ -591,24 +598,35 @@ void factorize(Oracle& o, const double* val, int nthreads) {
 #ifdef _OPENMP
    omp_set_num_threads(nthreads);
 #endif
-   std::vector<Work> works(nthreads);
-   for (auto& w : works) w.loc.assign(o.N, -1);
+   std::vector<Work>& works = o.works;
+   if (static_cast<int>(works.size()) != nthreads) { works.clear(); works.resize(nthreads); }
+   for (auto& w : works) if (static_cast<int64_t>(w.loc.size()) != o.N) w.loc.assign(o.N, -1);
+   // The fronts of a level are independent.  Small and medium ones go one per thread (single-threaded BLAS inside); the big ones
+   // follow one after the other with every thread inside the front (threaded BLAS, threaded assembly and copies).
+   std::vector<int> side, big_ones;
    for (const auto& level : o.levels) {
-      const int nl = static_cast<int>(level.size());
-      if (nl >= 2 * nthreads && nthreads > 1) {
+      side.clear(); big_ones.clear();
+      for (const int f : level) {
+         const size_t nf0 = static_cast<size_t>(o.fronts[f].ncol) + o.fronts[f].bnd.size();
+         (nthreads > 1 && nf0 < 3000 ? side : big_ones).push_back(f);
+      }
+      if (side.size() == 1) { big_ones.push_back(side[0]); side.clear(); }
+      const int ns = static_cast<int>(side.size());
+      if (ns > 0) {
          if (g_set_threads != nullptr) g_set_threads(1);
 #pragma omp parallel for schedule(dynamic, 1)
-         for (int t = 0; t < nl; ++t) {
+         for (int t = 0; t < ns; ++t) {
 #ifdef _OPENMP
             Work& w = works[omp_get_thread_num()];
 #else
             Work& w = works[0];
 #endif
-            factor_front(o, level[t], val, w);
+            factor_front(o, side[t], val, w);
          }
-      } else {
+      }
+      if (!big_ones.empty()) {
          if (g_set_threads != nullptr) g_set_threads(nthreads);
-         for (int t = 0; t < nl; ++t) factor_front(o, level[t], val, works[0]);
+         for (const int f : big_ones) factor_front(o, f, val, works[0]);
       }
    }
    o.pos = o.neg = o.zero = 0; o.n2x2 = 0; o.ndelayed = 0;
