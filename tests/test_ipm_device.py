@@ -109,7 +109,8 @@ def test_rhs_product_and_direction_match_the_reference_loops_bit_for_bit():
     np.add.at(rhs, row[jac][keep], jy[keep] * vals[jac][keep])
     rhs[n:] = -c
     d_rhs = torch.empty(n + m, dtype=torch.float64, device="cuda")
-    s.assemble_rhs_device(dev(torch, g).data_ptr(), dev(torch, c).data_ptr(), dev(torch, y).data_ptr(), d_rhs.data_ptr())
+    d_g, d_c, d_y = dev(torch, g), dev(torch, c), dev(torch, y)          # keep the tensors alive: their memory is what the call reads
+    s.assemble_rhs_device(d_g.data_ptr(), d_c.data_ptr(), d_y.data_ptr(), d_rhs.data_ptr())
     assert np.array_equal(d_rhs.cpu().numpy(), rhs)
 
     # ---- SymmetricMatrix::product (SymmetricMatrix.hpp:99-109) ------------------------------------------------------------------
@@ -123,9 +124,10 @@ def test_rhs_product_and_direction_match_the_reference_loops_bit_for_bit():
     mask[1::2] = off
     prod = np.zeros(n + m)
     np.add.at(prod, tgt[mask], contrib[mask])
-    d_y = torch.empty(n + m, dtype=torch.float64, device="cuda")
-    s.symmetric_product_device(dev(torch, xv).data_ptr(), d_y.data_ptr())
-    assert np.array_equal(d_y.cpu().numpy(), prod)
+    d_prod = torch.empty(n + m, dtype=torch.float64, device="cuda")
+    d_xv = dev(torch, xv)
+    s.symmetric_product_device(d_xv.data_ptr(), d_prod.data_ptr())
+    assert np.array_equal(d_prod.cpu().numpy(), prod)
 
     # ---- assemble_primal_dual_direction (PrimalDualInteriorPointProblem.cpp:173-194, 262-325) --------------------------------
     mu, tau = 0.1, max(0.99, 1.0 - 0.1)

@@ -681,7 +681,7 @@ void enqueue_factor(b200kkt_handle* h) {
             enqueue_shared_batch(h, b, list, st);
             continue;
          }
-         const bool ahead = h->lookahead != 0 && !prof && b.max_k > NBO && b.max_f >= 2048;
+         const bool ahead = h->lookahead != 0 && !prof && b.max_k > NBO && b.max_f >= h->lookahead_min_front;
          cudaStream_t pst = h->panel_stream[lane];
          const bool prof_this = prof && b.max_f >= 1024;
          auto trailing_flops = [&](int Jbeg, int kpanels, int nf) {
@@ -1268,6 +1268,7 @@ int b200kkt_set_option(b200kkt_handle* h, const char* name, double value) {
    else if (n == "multi_stream") h->multi_stream = static_cast<int>(value);
    else if (n == "update_tile_mode") h->update_tile_mode = static_cast<int>(value);
    else if (n == "lookahead") h->lookahead = static_cast<int>(value);
+   else if (n == "lookahead_min_front") h->lookahead_min_front = static_cast<int>(value);
    else if (n == "pair_panels") h->pair_panels = static_cast<int>(value);
    else if (n == "pair_min_front") h->pair_min_front = static_cast<int>(value);
    else if (n == "partition_graph") h->partition_graph = static_cast<int>(value);

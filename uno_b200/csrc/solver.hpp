@@ -97,6 +97,7 @@ struct b200kkt_handle {
    cudaStream_t panel_stream[NUM_AUX + 1] = {nullptr, nullptr, nullptr, nullptr};
    cudaEvent_t ev_next_cols[NUM_AUX + 1] = {nullptr, nullptr, nullptr, nullptr}, ev_panel[NUM_AUX + 1] = {nullptr, nullptr, nullptr, nullptr};
    int lookahead = 1;
+   int lookahead_min_front = 2048;   // fronts of at least this order (with more than one outer panel) factor the next panel ahead
    int pair_panels = 1;      // trailing updates of very big fronts take two outer panels at once (K <= 512): +3 % on 128^3, -3 % on 64^3
    int pair_min_front = 16384;
    int debug_skip = 0;
