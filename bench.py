@@ -253,7 +253,9 @@ def main():
         desc = WORKLOADS[args.workload][0]
         # partition: every rank holds the same system (SPMD, like the reference's MUMPS over MPI); replicas: one system per rank
         kkt = WORKLOADS[args.workload][1](G, 0 if parted else replicas.rank_seed(rank))
-        solver = partition.create_solver(dist, local_rank) if parted else KKTSolver(device=local_rank)
+        # B200KKT_OPTIONS="name=value,name=value": solver options for experiments (recorded in config.options)
+        extra_options = {kv.split("=")[0]: float(kv.split("=")[1]) for kv in os.environ.get("B200KKT_OPTIONS", "").split(",") if "=" in kv}
+        solver = partition.create_solver(dist, local_rank, **extra_options) if parted else KKTSolver(device=local_rank, **extra_options)
         t0 = time.perf_counter()
         ok = True
         try:
@@ -418,7 +420,7 @@ def main():
                     f"{world} independent replicas (one KKT system per GPU, no data-path collective)"),
                    "partition": part_info,
                    "l2": f"front pool {st0['pool_doubles'] * 8 / 1e9:.1f} GB per step >> 126 MB L2 (inputs larger than L2, no explicit flush)",
-                   "analysis_seconds_untimed": t_analyse, "ordering": "METIS_NodeND on the KKT-pair-compressed graph", "fallback": fallback_note},
+                   "options": extra_options or None, "analysis_seconds_untimed": t_analyse, "ordering": "METIS_NodeND on the KKT-pair-compressed graph", "fallback": fallback_note},
         "clocks": clocks, "gpu_launches": int(launches),
         "e2e": {"value": e2e_value, "unit": UNIT, "h2d_bytes_per_step": int(8 * kkt.nnz + 8 * kkt.dim), "d2h_bytes_per_step": int(8 * kkt.dim + 32 + 32),
                 "finite": x_ok},
