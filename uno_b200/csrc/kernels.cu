@@ -83,6 +83,49 @@ __global__ void k_assemble(AssemblyArrays M, const double* __restrict__ values, 
    pool[M.dst[d]] = s;
 }
 
+// K1 + zero-fill in one pass over the pool.  Persistent CTAs take tiles of ASM_TILE doubles.  A tile without destinations (the
+// rule: one pool entry in a few hundred is an original entry) is streamed out as zeros; a tile with destinations is built in
+// shared memory - zeros, then each destination by one thread that sums its sources in ascending slot order - and streamed out.
+// Stores are 16 bytes per lane, 512 contiguous bytes per warp.
+__global__ void __launch_bounds__(256) k_assemble_fill(AssemblyArrays M, const double* __restrict__ values, const double* __restrict__ scale,
+                                                       double* __restrict__ pool) {
+   __shared__ __align__(16) double tile[ASM_TILE];
+   const int tid = threadIdx.x;
+   const double2 zero2 = make_double2(0.0, 0.0);
+   for (int64_t t = blockIdx.x; t < M.ntiles; t += gridDim.x) {
+      const int64_t base = t * ASM_TILE;
+      const int64_t left = M.pool_doubles - base;
+      const int count = left < ASM_TILE ? static_cast<int>(left) : ASM_TILE;
+      const int d0 = M.tile_ptr[t], d1 = M.tile_ptr[t + 1];
+      double2* out = reinterpret_cast<double2*>(pool + base);   // tiles start on 16 KB boundaries of an allocation aligned to 256 bytes
+      if (d0 == d1) {
+         if (count == ASM_TILE) {
+#pragma unroll
+            for (int i = 0; i < ASM_TILE / 2 / 256; ++i) out[tid + 256 * i] = zero2;
+         } else {
+            for (int i = tid; i < count; i += 256) pool[base + i] = 0.0;
+         }
+         continue;
+      }
+#pragma unroll
+      for (int i = 0; i < ASM_TILE / 2 / 256; ++i) reinterpret_cast<double2*>(tile)[tid + 256 * i] = zero2;
+      __syncthreads();
+      for (int d = d0 + tid; d < d1; d += 256) {
+         double s = 0.0;
+         for (int q = M.seg[d]; q < M.seg[d + 1]; ++q) s += values[M.src[q]] * scale[M.row[q]] * scale[M.col[q]];
+         tile[M.dst[d] - base] = s;
+      }
+      __syncthreads();
+      if (count == ASM_TILE) {
+#pragma unroll
+         for (int i = 0; i < ASM_TILE / 2 / 256; ++i) out[tid + 256 * i] = reinterpret_cast<const double2*>(tile)[tid + 256 * i];
+      } else {
+         for (int i = tid; i < count; i += 256) pool[base + i] = tile[i];
+      }
+      __syncthreads();   // the tile buffer is reused
+   }
+}
+
 // r = b - K x, and the componentwise backward error of Arioli, Demmel and Duff (SIAM J. Matrix Anal. 1989) - what MUMPS reports
 // as RINFOG(7)/(8): rows whose denominator (|K||x| + |b|)_i is safely above rounding level give omega_1 = |r_i| / (|K||x| + |b|)_i,
 // the others (denominator below 1000 n eps (|K_i|_inf |x|_inf + |b_i|)) give omega_2 = |r_i| / ((|K||x|)_i + |K_i|_1 |x|_inf).
@@ -2267,6 +2310,13 @@ int launch_matrix_inf_norm(const CsrArrays& A, const double* values, unsigned lo
 int launch_assemble(const AssemblyArrays& M, const double* values, const double* scale, double* pool, cudaStream_t st) {
    if (M.ndst <= 0) return 0;
    k_assemble<<<grid1d(M.ndst, 256), 256, 0, st>>>(M, values, scale, pool);
+   return 1;
+}
+
+int launch_assemble_fill(const AssemblyArrays& M, const double* values, const double* scale, double* pool, cudaStream_t st) {
+   if (M.ntiles <= 0) return 0;
+   const int64_t want = (M.ntiles + 0) < 148 * 8 ? M.ntiles : 148 * 8;   // persistent: 8 CTAs of 256 threads per SM
+   k_assemble_fill<<<static_cast<unsigned>(want), 256, 0, st>>>(M, values, scale, pool);
    return 1;
 }
 

@@ -39,7 +39,12 @@ struct AssemblyArrays {
    const int* src;
    const int* row;
    const int* col;
+   // fused zero-fill + assembly: the pool in tiles of ASM_TILE doubles; destinations [tile_ptr[t], tile_ptr[t + 1]) fall into tile t
+   int64_t ntiles;
+   int64_t pool_doubles;
+   const int* tile_ptr;
 };
+constexpr int ASM_TILE = 2048;   // doubles per tile (16 KB): what one CTA builds in shared memory and streams out
 
 struct CsrArrays {
    int64_t n;
@@ -78,6 +83,9 @@ int launch_fill(double* p, int64_t n, double v, cudaStream_t st);
 int launch_matrix_inf_norm(const CsrArrays& A, const double* values, unsigned long long* out_bits, cudaStream_t st);
 // K1 assembly: scatter COO values (scaled) into the zeroed factor pool, duplicates summed in slot order
 int launch_assemble(const AssemblyArrays& M, const double* values, const double* scale, double* lpool, cudaStream_t st);
+// K1 fused with the zero-fill of the factor pool: every tile of the pool is written exactly once, zeros and assembled entries
+// together (full 32-byte sectors, no read-modify-write of a pool that a separate memset has just written)
+int launch_assemble_fill(const AssemblyArrays& M, const double* values, const double* scale, double* lpool, cudaStream_t st);
 
 // K5: zero the contribution blocks of the listed fronts and extend-add all their children into them
 int launch_prepare(const FrontArrays& F, const int* d_list, int nfronts, int max_f, const FactorArrays& W, cudaStream_t st);

@@ -558,6 +558,20 @@ void upload_plan(b200kkt_handle* h) {
    h->M.src = dev_upload(h, P.asm_src);
    h->M.row = dev_upload(h, P.asm_row);
    h->M.col = dev_upload(h, P.asm_col);
+   {
+      // tiles of the pool for the fused zero-fill + assembly; asm_dst ascends
+      h->M.pool_doubles = P.pool_size;
+      h->M.ntiles = (P.pool_size + ASM_TILE - 1) / ASM_TILE;
+      std::vector<int> tile_ptr(static_cast<size_t>(h->M.ntiles) + 1, 0);
+      size_t d = 0;
+      for (int64_t t = 0; t < h->M.ntiles; ++t) {
+         tile_ptr[static_cast<size_t>(t)] = static_cast<int>(d);
+         const int64_t end = (t + 1) * ASM_TILE;
+         while (d < P.asm_dst.size() && P.asm_dst[d] < end) ++d;
+      }
+      tile_ptr[static_cast<size_t>(h->M.ntiles)] = static_cast<int>(P.asm_dst.size());
+      h->M.tile_ptr = dev_upload(h, tile_ptr);
+   }
    h->C.n = P.N;
    h->C.ptr = dev_upload(h, P.csr_ptr);
    h->C.col = dev_upload(h, P.csr_col);
@@ -636,8 +650,9 @@ void enqueue_factor(b200kkt_handle* h) {
    h->d_scale_final = cur;
    CK(cudaMemsetAsync(h->d_norms, 0, 4 * sizeof(unsigned long long), st));
    L += launch_matrix_inf_norm(h->C, h->d_values, h->d_norms + 0, st);
-   // K1 assembly into the zeroed factor pool
-   CK(cudaMemsetAsync(h->W.lpool, 0, static_cast<size_t>(P.pool_size) * sizeof(double), st));
+   // K1 assembly: one pass writes the whole factor pool, zeros and assembled entries together (option fused_assembly = 0: memset
+   // + scatter, the round-1 path)
+   if (!h->fused_assembly) CK(cudaMemsetAsync(h->W.lpool, 0, static_cast<size_t>(P.pool_size) * sizeof(double), st));
 
    const bool prof = h->profile_updates != 0 && !h->use_graph;
    auto prof_begin = [&](double flops, int kind) {
@@ -649,7 +664,7 @@ void enqueue_factor(b200kkt_handle* h) {
    };
    auto prof_end = [&] { CK(cudaEventRecord(h->profiled.back().b, st)); };
    if (prof) prof_begin(0.0, 1);
-   L += launch_assemble(h->M, h->d_values, cur, h->W.lpool, st);
+   L += h->fused_assembly ? launch_assemble_fill(h->M, h->d_values, cur, h->W.lpool, st) : launch_assemble(h->M, h->d_values, cur, h->W.lpool, st);
    if (prof) prof_end();
    // K2-K5 level by level; the batches of one level are independent and go round-robin over the
    // handle's streams (fork/join with events, which stream capture turns into graph edges)
@@ -1268,6 +1283,7 @@ int b200kkt_set_option(b200kkt_handle* h, const char* name, double value) {
    else if (n == "multi_stream") h->multi_stream = static_cast<int>(value);
    else if (n == "update_tile_mode") h->update_tile_mode = static_cast<int>(value);
    else if (n == "lookahead") h->lookahead = static_cast<int>(value);
+   else if (n == "fused_assembly") h->fused_assembly = static_cast<int>(value);
    else if (n == "lookahead_min_front") h->lookahead_min_front = static_cast<int>(value);
    else if (n == "pair_panels") h->pair_panels = static_cast<int>(value);
    else if (n == "pair_min_front") h->pair_min_front = static_cast<int>(value);
@@ -1516,8 +1532,8 @@ int b200kkt_debug_assemble(b200kkt_handle* h, const double* values, double* pool
          std::swap(cur, nxt);
       }
       h->d_scale_final = cur;
-      CK(cudaMemsetAsync(h->W.lpool, 0, static_cast<size_t>(P.pool_size) * sizeof(double), st));
-      h->launches += launch_assemble(h->M, h->d_values, cur, h->W.lpool, st);
+      if (!h->fused_assembly) CK(cudaMemsetAsync(h->W.lpool, 0, static_cast<size_t>(P.pool_size) * sizeof(double), st));
+      h->launches += h->fused_assembly ? launch_assemble_fill(h->M, h->d_values, cur, h->W.lpool, st) : launch_assemble(h->M, h->d_values, cur, h->W.lpool, st);
       if (pool_out != nullptr) CK(cudaMemcpyAsync(pool_out, h->W.lpool, static_cast<size_t>(P.pool_size) * sizeof(double), cudaMemcpyDeviceToHost, st));
       if (scale_out != nullptr) CK(cudaMemcpyAsync(scale_out, cur, static_cast<size_t>(P.N) * sizeof(double), cudaMemcpyDeviceToHost, st));
       CK(cudaStreamSynchronize(st));

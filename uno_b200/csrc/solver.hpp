@@ -96,6 +96,7 @@ struct b200kkt_handle {
    // look-ahead: the next outer panel of a front is factored on a panel stream while the rest of the trailing update runs
    cudaStream_t panel_stream[NUM_AUX + 1] = {nullptr, nullptr, nullptr, nullptr};
    cudaEvent_t ev_next_cols[NUM_AUX + 1] = {nullptr, nullptr, nullptr, nullptr}, ev_panel[NUM_AUX + 1] = {nullptr, nullptr, nullptr, nullptr};
+   int fused_assembly = 1;   // K1 and the zero-fill of the factor pool in one pass (kernels.cu: k_assemble_fill)
    int lookahead = 1;
    int lookahead_min_front = 2048;   // fronts of at least this order (with more than one outer panel) factor the next panel ahead
    int pair_panels = 1;      // trailing updates of very big fronts take two outer panels at once (K <= 512): +3 % on 128^3, -3 % on 64^3
@@ -161,8 +162,8 @@ struct b200kkt_handle {
    cudaStream_t comm_stream = nullptr;
    cudaEvent_t ev_level_done = nullptr;
    int partition_graph = 0;               // experimental, off: capture the partitioned factorization / solve sweep (NCCL calls included) in CUDA graphs
-   int share_one_launch = 0;              // experimental, off: a rank updates all its column chunks of one step in one K4 launch
-   int share_trim_rows = 0;               // experimental, off: broadcast only the rows of a factored panel at and below its diagonal block
+   int share_one_launch = 1;              // a rank updates all its column chunks of one step in one K4 launch (8 GPUs, 128^3: 1.407 -> 1.359 s with both)
+   int share_trim_rows = 1;               // broadcast only the rows of a factored panel at and below its diagonal block
    int share_top_fronts = 1;              // big fronts above the cut are factorized by all ranks together
    int share_chunk_panels = 2;            // column chunk of a shared front, in outer panels; chunk c belongs to rank c mod num_gpus
    int share_min_pivots = 1024;
