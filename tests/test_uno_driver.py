@@ -86,3 +86,29 @@ def test_primal_regularization_strategy_drives_the_b200_solver(shift):
     assert r["regularization_factors"] == ref["regularization_factors"]
     assert r["inertia"] == ref["inertia"] == [1600, 0, 0]
     assert r["residual"] <= 1e-10 * max(1.0, r["solution_norm"])
+
+
+@pytest.mark.gpu
+@needs_driver
+@pytest.mark.parametrize("model", ["hs015", "control3d:6"])
+def test_b200_solver_spmd_on_two_gpus(model, tmp_path):
+    """two copies of the Uno process, one GPU each (B200KKT_WORLD = 2), run the same iteration; every
+    solver instance joins its own NCCL communicator through the hand-over file.  Both ranks must reproduce the golden run."""
+    import os
+    import subprocess
+    import torch
+    if torch.cuda.device_count() < 2:
+        pytest.skip("needs two CUDA devices (run with gpurun --gpus 2)")
+    procs = []
+    for rank in range(2):
+        env = dict(os.environ, B200KKT_WORLD="2", B200KKT_RANK=str(rank), B200KKT_COMM_FILE=str(tmp_path / "nccl_id"), B200KKT_RUN_ID=f"t{os.getpid()}")
+        procs.append(subprocess.Popen([str(DRIVER), model, "preset=ipopt", "linear_solver=B200"], stdout=subprocess.PIPE, stderr=subprocess.STDOUT, text=True, env=env))
+    outs = [p.communicate(timeout=600)[0] for p in procs]
+    for out in outs:
+        lines = [l for l in out.splitlines() if l.startswith("UNO_DRIVER_RESULT")]
+        assert lines, out[-1500:]
+        r = json.loads(lines[-1][len("UNO_DRIVER_RESULT"):])
+        g = GOLDEN[model]
+        assert r["iterations"] == g["iterations"] and r["optimization_status"] == g["optimization_status"] and r["iterate_status"] == g["iterate_status"]
+        assert abs(r["objective"] - g["objective"]) <= 1e-6 * max(1.0, abs(g["objective"]))
+    assert not list(tmp_path.glob("nccl_id*"))          # rank 0 removes every hand-over file once the ranks have joined

@@ -14,6 +14,8 @@
 #include <cstring>
 #include <thread>
 #include "B200Solver.hpp"
+#include <sys/stat.h>
+#include <ctime>
 #include "b200kkt.h"
 
 namespace uno {
@@ -222,9 +224,15 @@ namespace uno {
                b200kkt_destroy(handle);
                throw std::runtime_error("B200: B200KKT_WORLD > 1 needs B200KKT_COMM_FILE (path for the NCCL id hand-over)");
             }
-            const std::string path = std::string(file_variable) + "." + std::to_string(instance_counter++);
+            // One file per solver instance; B200KKT_RUN_ID (a nonce the launcher gives every rank of one run) keeps runs apart.
+            // Without it a file left behind by a run that died between publishing and joining is told by its age; a run that
+            // ends normally leaves nothing: rank 0 removes the file once every rank has joined (comm_init is collective).
+            const char* run_variable = std::getenv("B200KKT_RUN_ID");
+            const std::string path = std::string(file_variable) + (run_variable != nullptr ? "." + std::string(run_variable) : std::string()) + "." +
+               std::to_string(instance_counter++);
             char id[128];
             if (rank == 0) {
+               std::remove(path.c_str());   // a stale id of an earlier run must not be read by a rank that starts before the new one is out
                status = b200kkt_comm_unique_id(id);
                if (status == B200KKT_OK) {
                   const std::string temporary = path + ".tmp";
@@ -232,20 +240,26 @@ namespace uno {
                   if (file == nullptr || std::fwrite(id, 1, sizeof(id), file) != sizeof(id)) status = B200KKT_EINVAL;
                   if (file != nullptr) std::fclose(file);
                   if (status == B200KKT_OK && std::rename(temporary.c_str(), path.c_str()) != 0) status = B200KKT_EINVAL;   // atomic publish
+                  if (status != B200KKT_OK) std::remove(temporary.c_str());
                }
             }
             else {
                status = B200KKT_EINVAL;
+               const std::time_t oldest_accepted = std::time(nullptr) - 600;
                for (int attempt = 0; attempt < 6000 && status != B200KKT_OK; ++attempt) {   // up to 60 s
-                  std::FILE* file = std::fopen(path.c_str(), "rb");
-                  if (file != nullptr) {
-                     if (std::fread(id, 1, sizeof(id), file) == sizeof(id)) status = B200KKT_OK;
-                     std::fclose(file);
+                  struct stat info;
+                  if (::stat(path.c_str(), &info) == 0 && info.st_mtime >= oldest_accepted) {
+                     std::FILE* file = std::fopen(path.c_str(), "rb");
+                     if (file != nullptr) {
+                        if (std::fread(id, 1, sizeof(id), file) == sizeof(id)) status = B200KKT_OK;
+                        std::fclose(file);
+                     }
                   }
                   if (status != B200KKT_OK) std::this_thread::sleep_for(std::chrono::milliseconds(10));
                }
             }
             if (status == B200KKT_OK) status = b200kkt_comm_init(handle, rank, world, id);
+            if (rank == 0) std::remove(path.c_str());   // joined (or failed): nobody needs the file any more
          }
          if (status != B200KKT_OK) {
             std::string message = "B200: cannot create a solver handle on CUDA device " + std::to_string(device);
