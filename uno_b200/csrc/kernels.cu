@@ -1240,6 +1240,79 @@ __global__ void __launch_bounds__(64) k_diag32(FrontArrays F, const int* __restr
    if (tid == 0) W.blkflag[F.first[s]] = S.nontrivial;
 }
 
+// K2: a whole LEAF front (no children, at most NBI pivots, at most LEAF_RMAX boundary rows) by one CTA of 64 threads, everything
+// in shared memory: Bunch-Kaufman of the pivot block (warp 0), the rows below it (one row per thread: w = a L11^{-T}, l = w D^{-1}),
+// and the Schur complement -W L^T written straight into the packed contribution block (a leaf's block starts from zero, so it is
+// written, not updated: no k_prepare, no W panel in global memory, no separate update launch).  The bulk of every tree is such
+// fronts; the level-0 batches of the BASELINE configs cost four launches and ~1 ms (config 2) before.
+constexpr int LEAF_RMAX = 56;   // keeps the static shared memory under 48 KB
+__global__ void __launch_bounds__(64) k_leaf_front(FrontArrays F, const int* __restrict__ list, FactorArrays W, const double null_tol) {
+   __shared__ BkShared S;
+   __shared__ double L11[NBI][NBI + 1];
+   __shared__ double Ws[NBI][LEAF_RMAX + 1], Ls[NBI][LEAF_RMAX + 1];   // [c][i]
+   const int s = list[blockIdx.x];
+   const int k = F.k[s], f = F.f[s], ld = F.ld[s], first = F.first[s];
+   const int r = f - k;
+   double* A = W.lpool + F.off[s];
+   const int tid = threadIdx.x;
+   for (int idx = tid; idx < NBI * NBI; idx += 64) {
+      const int rr = idx % NBI, c = idx / NBI;
+      double v;
+      if (rr < k && c < k) v = (rr >= c) ? A[rr + static_cast<int64_t>(ld) * c] : A[c + static_cast<int64_t>(ld) * rr];
+      else v = (rr == c) ? 1.0 : 0.0;
+      S.B[rr][c] = v;
+   }
+   __syncthreads();
+   if (tid < 32) bk_factor_block(S, k, tid, null_tol, W.no_pivot != 0);
+   __syncthreads();
+   for (int idx = tid; idx < NBI * NBI; idx += 64) {
+      const int rr = idx % NBI, c = idx / NBI;
+      const bool in = rr < k && c < k;
+      if (in && rr >= c) A[rr + static_cast<int64_t>(ld) * c] = (rr == c) ? S.d[c] : S.B[rr][c];
+      L11[rr][c] = (in && rr > c) ? S.B[rr][c] : 0.0;
+   }
+   if (tid < k) {
+      const int q = first + tid;
+      W.dd[q] = S.d[tid];
+      W.de[q] = S.e[tid];
+      W.ptype[q] = S.type[tid];
+      W.lperm[q] = S.p[tid];
+   }
+   if (tid == 0) W.blkflag[first] = S.nontrivial;
+   __syncthreads();
+   if (tid < r) {
+      const int i = k + tid;
+      double w[NBI], l[NBI];
+#pragma unroll
+      for (int c = 0; c < NBI; ++c) w[c] = (c < k) ? A[i + static_cast<int64_t>(ld) * S.p[c]] : 0.0;
+      unsigned dmask = row_trsm(w, l, L11, S.d, S.e, S.type, W.delay_tol, W.growth_limit);
+      while (dmask) {
+         const int c = __ffs(dmask) - 1;
+         dmask &= dmask - 1u;
+         if (c < k) flag_delay(W, first + S.p[c]);
+      }
+#pragma unroll
+      for (int c = 0; c < NBI; ++c) {
+         if (c < k) A[i + static_cast<int64_t>(ld) * c] = l[c];
+         Ws[c][tid] = (c < k) ? w[c] : 0.0;
+         Ls[c][tid] = (c < k) ? l[c] : 0.0;
+      }
+   }
+   __syncthreads();
+   if (r > 0) {
+      double* Cb = W.cbpool + F.cboff[s];
+      // lanes along the rows of a column of the packed lower triangle: contiguous stores
+      for (int j = 0; j < r; ++j) {
+         const int64_t col0 = cb_col(r, j);
+         for (int i = j + tid; i < r; i += 64) {
+            double acc = 0.0;
+            for (int c = 0; c < k; ++c) acc = fma(Ws[c][i], Ls[c][j], acc);
+            Cb[col0 + i] = -acc;
+         }
+      }
+   }
+}
+
 // Deferred row interchanges: the rows of an inner block were permuted among themselves by its
 // Bunch-Kaufman; the L columns left of the block must follow.  Blocks touch disjoint rows, so all
 // of them are applied in one launch: grid = (front, inner block, 32-column chunk); one warp moves
@@ -2348,6 +2421,14 @@ int launch_trsmpanel(const FrontArrays& F, const int* d_list, int nfronts, int m
       dim3 grid(nfronts, (rows + TD_ROWS - 1) / TD_ROWS);
       k_trsmpanel_mma<<<grid, TD_THREADS, TD_SMEM, st>>>(F, d_list, J0, W);
    }
+   return 1;
+}
+
+int leaf_front_max_boundary() { return LEAF_RMAX; }
+
+int launch_leaf_fronts(const FrontArrays& F, const int* d_list, int nfronts, const FactorArrays& W, double null_tol, cudaStream_t st) {
+   if (nfronts <= 0) return 0;
+   k_leaf_front<<<nfronts, 64, 0, st>>>(F, d_list, W, null_tol);
    return 1;
 }
 

@@ -144,6 +144,7 @@ void build_batches(b200kkt_handle* h, std::vector<int>& batch_list, std::vector<
             b.max_k = std::max(b.max_k, P.k[s]);
             if (P.child_ptr[s + 1] > P.child_ptr[s]) b.has_children = true;
             if (P.f[s] > P.k[s]) b.has_cb = true;
+            b.max_r = std::max(b.max_r, P.f[s] - P.k[s]);
             ++i;
          }
          b.count = static_cast<int>(b.k.size());
@@ -688,6 +689,11 @@ void enqueue_factor(b200kkt_handle* h) {
          const int* list = h->d_batch_list + b.begin;
          const int lane = (bi - h->level_batch_ptr[l]) % (nside + 1);
          cudaStream_t st = (lane == 0) ? h->stream : h->aux[lane - 1];
+         if (h->fused_leaves != 0 && !b.shared && !b.has_children && b.max_k <= NBI && b.max_r <= leaf_front_max_boundary() && h->debug_skip == 0) {
+            // K2: the whole front by one CTA, contribution block included
+            L += launch_leaf_fronts(h->F, list, b.count, h->W, h->null_pivot_tol, st);
+            continue;
+         }
          if ((b.has_cb || b.has_children) && !(h->debug_skip & 4)) L += launch_prepare(h->F, list, b.count, b.max_f, h->W, st);
          // W panels: panel p of a front lives in buffer p & 3 (two panels of a pair + the pair factored ahead)
          FactorArrays Wbuf[4] = {h->W, h->W, h->W, h->W};
@@ -1284,6 +1290,7 @@ int b200kkt_set_option(b200kkt_handle* h, const char* name, double value) {
    else if (n == "update_tile_mode") h->update_tile_mode = static_cast<int>(value);
    else if (n == "lookahead") h->lookahead = static_cast<int>(value);
    else if (n == "fused_assembly") h->fused_assembly = static_cast<int>(value);
+   else if (n == "fused_leaves") h->fused_leaves = static_cast<int>(value);
    else if (n == "lookahead_min_front") h->lookahead_min_front = static_cast<int>(value);
    else if (n == "pair_panels") h->pair_panels = static_cast<int>(value);
    else if (n == "pair_min_front") h->pair_min_front = static_cast<int>(value);

@@ -23,6 +23,7 @@ struct Batch {
    int max_f = 0, max_k = 0;
    bool has_children = false;
    bool has_cb = false;
+   int max_r = 0;         // largest boundary (f - k) of the batch
    bool shared = false;   // fronts factorized by all ranks together (subtree partition, fronts above the cut)
    // shared batch: its fronts dealt round-robin into num_gpus sub-lists (each k descending, contiguous in the batch list);
    // sub-list g rotates the chunk ownership by g, so the panels of one step are factored by different ranks side by side
@@ -96,6 +97,7 @@ struct b200kkt_handle {
    // look-ahead: the next outer panel of a front is factored on a panel stream while the rest of the trailing update runs
    cudaStream_t panel_stream[NUM_AUX + 1] = {nullptr, nullptr, nullptr, nullptr};
    cudaEvent_t ev_next_cols[NUM_AUX + 1] = {nullptr, nullptr, nullptr, nullptr}, ev_panel[NUM_AUX + 1] = {nullptr, nullptr, nullptr, nullptr};
+   int fused_leaves = 1;     // leaf batches of small fronts go through the one-CTA-per-front kernel (kernels.cu: k_leaf_front)
    int fused_assembly = 1;   // K1 and the zero-fill of the factor pool in one pass (kernels.cu: k_assemble_fill)
    int lookahead = 1;
    int lookahead_min_front = 2048;   // fronts of at least this order (with more than one outer panel) factor the next panel ahead
