@@ -41,7 +41,7 @@ WORKLOADS = {
     # name: (description, generator, cpu-sample generator)
     "ocp3d_k128": ("BASELINE configs[4]: synthetic 3D PDE-constrained optimal control KKT, 128^3 grid, boundary control "
                    "(2.2 M primal rows + 2.1 M multipliers), whole system on ONE B200",
-                   lambda G, seed: G.ocp_boundary_3d(128, seed=seed), lambda G, seed: G.ocp_boundary_3d(56, seed=seed)),
+                   lambda G, seed: G.ocp_boundary_3d(128, seed=seed), lambda G, seed: G.ocp_boundary_3d(48, seed=seed)),
     "ocp3d_k64": ("BASELINE configs[3]: synthetic 3D PDE-constrained optimal control KKT, 64^3 grid, 7-point, distributed control",
                   lambda G, seed: G.ocp_distributed(64, 3, seed=seed), lambda G, seed: G.ocp_distributed(48, 3, seed=seed)),
     "ocp2d_k256": ("BASELINE configs[1]: synthetic 2D PDE-constrained optimal control KKT, 256x256 grid",

@@ -1246,7 +1246,9 @@ __global__ void __launch_bounds__(64) k_diag32(FrontArrays F, const int* __restr
 // written, not updated: no k_prepare, no W panel in global memory, no separate update launch).  The bulk of every tree is such
 // fronts; the level-0 batches of the BASELINE configs cost four launches and ~1 ms (config 2) before.
 constexpr int LEAF_RMAX = 56;   // keeps the static shared memory under 48 KB
-__global__ void __launch_bounds__(64) k_leaf_front(FrontArrays F, const int* __restrict__ list, FactorArrays W, const double null_tol) {
+// accumulate = 1: the batch has fronts with children; k_prepare has zeroed the contribution blocks and extend-added the children
+// (into the factor panel and into the block), so the Schur complement is subtracted from the block instead of written.
+__global__ void __launch_bounds__(64) k_leaf_front(FrontArrays F, const int* __restrict__ list, FactorArrays W, const double null_tol, const int accumulate) {
    __shared__ BkShared S;
    __shared__ double L11[NBI][NBI + 1];
    __shared__ double Ws[NBI][LEAF_RMAX + 1], Ls[NBI][LEAF_RMAX + 1];   // [c][i]
@@ -1307,7 +1309,7 @@ __global__ void __launch_bounds__(64) k_leaf_front(FrontArrays F, const int* __r
          for (int i = j + tid; i < r; i += 64) {
             double acc = 0.0;
             for (int c = 0; c < k; ++c) acc = fma(Ws[c][i], Ls[c][j], acc);
-            Cb[col0 + i] = -acc;
+            Cb[col0 + i] = accumulate ? Cb[col0 + i] - acc : -acc;
          }
       }
    }
@@ -2426,9 +2428,9 @@ int launch_trsmpanel(const FrontArrays& F, const int* d_list, int nfronts, int m
 
 int leaf_front_max_boundary() { return LEAF_RMAX; }
 
-int launch_leaf_fronts(const FrontArrays& F, const int* d_list, int nfronts, const FactorArrays& W, double null_tol, cudaStream_t st) {
+int launch_leaf_fronts(const FrontArrays& F, const int* d_list, int nfronts, const FactorArrays& W, double null_tol, bool accumulate, cudaStream_t st) {
    if (nfronts <= 0) return 0;
-   k_leaf_front<<<nfronts, 64, 0, st>>>(F, d_list, W, null_tol);
+   k_leaf_front<<<nfronts, 64, 0, st>>>(F, d_list, W, null_tol, accumulate ? 1 : 0);
    return 1;
 }
 

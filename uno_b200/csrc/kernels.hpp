@@ -99,7 +99,8 @@ int launch_trsmpanel(const FrontArrays& F, const int* d_list, int nfronts, int m
 // K2: leaf fronts (no children, k <= NBI, f - k <= leaf_front_max_boundary()) factored completely by one CTA each, contribution
 // block included; replaces prepare + diagpanel + trsmpanel + update for such a batch
 int leaf_front_max_boundary();
-int launch_leaf_fronts(const FrontArrays& F, const int* d_list, int nfronts, const FactorArrays& W, double null_tol, cudaStream_t st);
+// (accumulate: the batch went through launch_prepare first - fronts with children - and the block is updated, not written)
+int launch_leaf_fronts(const FrontArrays& F, const int* d_list, int nfronts, const FactorArrays& W, double null_tol, bool accumulate, cudaStream_t st);
 // rows of the L columns left of each inner block follow the block's interchanges (all blocks at once)
 int launch_permute_rows(const FrontArrays& F, const int* d_list, int nfronts, int max_k, const FactorArrays& W, cudaStream_t st);
 // K4 Schur-complement update C -= W * L^T with FP64 tensor-core MMA.

@@ -689,9 +689,11 @@ void enqueue_factor(b200kkt_handle* h) {
          const int* list = h->d_batch_list + b.begin;
          const int lane = (bi - h->level_batch_ptr[l]) % (nside + 1);
          cudaStream_t st = (lane == 0) ? h->stream : h->aux[lane - 1];
-         if (h->fused_leaves != 0 && !b.shared && !b.has_children && b.max_k <= NBI && b.max_r <= leaf_front_max_boundary() && h->debug_skip == 0) {
-            // K2: the whole front by one CTA, contribution block included
-            L += launch_leaf_fronts(h->F, list, b.count, h->W, h->null_pivot_tol, st);
+         if (h->fused_leaves != 0 && !b.shared && b.max_k <= NBI && b.max_r <= leaf_front_max_boundary() && h->debug_skip == 0 &&
+             (!b.has_children || h->fused_leaves > 1)) {
+            // K2: the whole front by one CTA, contribution block included; fronts with children are extend-added first
+            if (b.has_children) L += launch_prepare(h->F, list, b.count, b.max_f, h->W, st);
+            L += launch_leaf_fronts(h->F, list, b.count, h->W, h->null_pivot_tol, b.has_children, st);
             continue;
          }
          if ((b.has_cb || b.has_children) && !(h->debug_skip & 4)) L += launch_prepare(h->F, list, b.count, b.max_f, h->W, st);

@@ -97,7 +97,7 @@ struct b200kkt_handle {
    // look-ahead: the next outer panel of a front is factored on a panel stream while the rest of the trailing update runs
    cudaStream_t panel_stream[NUM_AUX + 1] = {nullptr, nullptr, nullptr, nullptr};
    cudaEvent_t ev_next_cols[NUM_AUX + 1] = {nullptr, nullptr, nullptr, nullptr}, ev_panel[NUM_AUX + 1] = {nullptr, nullptr, nullptr, nullptr};
-   int fused_leaves = 1;     // leaf batches of small fronts go through the one-CTA-per-front kernel (kernels.cu: k_leaf_front)
+   int fused_leaves = 2;     // small-front batches go through the one-CTA-per-front kernel (kernels.cu: k_leaf_front): 1 = leaf batches only, 2 = all
    int fused_assembly = 1;   // K1 and the zero-fill of the factor pool in one pass (kernels.cu: k_assemble_fill)
    int lookahead = 1;
    int lookahead_min_front = 2048;   // fronts of at least this order (with more than one outer panel) factor the next panel ahead
