@@ -2030,9 +2030,10 @@ __global__ void __launch_bounds__(256) k_fwd_big_diag(FrontArrays F, const int* 
          cp_async_commit();
       }
       ys[tid] = (tid < nb) ? y[tid] : 0.0;
+      // warp w holds the inverse of inner block w (lane = row): all blocks are requested at once, block sb is applied by warp sb
       double2 xr[NBI / 2];
-      if (warp == 0) {
-         const double2* xp = reinterpret_cast<const double2*>(Xg + lane * NBI);
+      if (warp < nsb) {
+         const double2* xp = reinterpret_cast<const double2*>(Xg + static_cast<int64_t>(warp) * XINV_BLOCK_DOUBLES + lane * NBI);
 #pragma unroll
          for (int c = 0; c < NBI / 2; ++c) xr[c] = xp[c];
       }
@@ -2041,13 +2042,7 @@ __global__ void __launch_bounds__(256) k_fwd_big_diag(FrontArrays F, const int* 
       int off = 0;
       for (int sb = 0; sb < nsb; ++sb) {
          const int base = sb * NBI;
-         if (warp == 0) {
-            double2 xn[NBI / 2];
-            if (sb + 1 < nsb) {
-               const double2* xp = reinterpret_cast<const double2*>(Xg + static_cast<int64_t>(sb + 1) * XINV_BLOCK_DOUBLES + lane * NBI);
-#pragma unroll
-               for (int c = 0; c < NBI / 2; ++c) xn[c] = xp[c];
-            }
+         if (warp == sb) {
             double a0 = 0.0, a1 = 0.0, a2 = 0.0, a3 = 0.0;
 #pragma unroll
             for (int c = 0; c < NBI / 2; c += 2) {
@@ -2058,10 +2053,6 @@ __global__ void __launch_bounds__(256) k_fwd_big_diag(FrontArrays F, const int* 
             }
             __syncwarp();
             ys[base + lane] = (a0 + a1) + (a2 + a3);
-            if (sb + 1 < nsb) {
-#pragma unroll
-               for (int c = 0; c < NBI / 2; ++c) xr[c] = xn[c];
-            }
          }
          __syncthreads();
          if (sb + 1 < nsb) {
@@ -2269,9 +2260,10 @@ __global__ void __launch_bounds__(256) k_bwd_big_diag(FrontArrays F, const int* 
    }
    if (xoff >= 0) {
       // x_b = X_b^T t_b, blocks from last to first; lane c of warp 0 holds column c of the block's inverse, one block ahead
+      // warp w holds the inverse of inner block w (lane = column): all blocks requested at once, block sb applied by warp sb
       double xc[NBI];
-      if (warp == 0) {
-         const double* xp = Xg + static_cast<int64_t>(nsb - 1) * XINV_BLOCK_DOUBLES + lane;
+      if (warp < nsb) {
+         const double* xp = Xg + static_cast<int64_t>(warp) * XINV_BLOCK_DOUBLES + lane;
 #pragma unroll
          for (int r = 0; r < NBI; ++r) xc[r] = xp[r * NBI];
       }
@@ -2279,13 +2271,7 @@ __global__ void __launch_bounds__(256) k_bwd_big_diag(FrontArrays F, const int* 
       __syncthreads();
       for (int sb = nsb - 1; sb >= 0; --sb) {
          const int base = sb * NBI;
-         if (warp == 0) {
-            double xn[NBI];
-            if (sb > 0) {
-               const double* xp = Xg + static_cast<int64_t>(sb - 1) * XINV_BLOCK_DOUBLES + lane;
-#pragma unroll
-               for (int r = 0; r < NBI; ++r) xn[r] = xp[r * NBI];
-            }
+         if (warp == sb) {
             double a0 = 0.0, a1 = 0.0, a2 = 0.0, a3 = 0.0;
 #pragma unroll
             for (int r = 0; r < NBI; r += 4) {
@@ -2296,10 +2282,6 @@ __global__ void __launch_bounds__(256) k_bwd_big_diag(FrontArrays F, const int* 
             }
             __syncwarp();
             ys[base + lane] = (a0 + a1) + (a2 + a3);
-            if (sb > 0) {
-#pragma unroll
-               for (int r = 0; r < NBI; ++r) xc[r] = xn[r];
-            }
          }
          __syncthreads();
          if (sb > 0) {
