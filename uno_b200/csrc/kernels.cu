@@ -2370,9 +2370,22 @@ int launch_assemble(const AssemblyArrays& M, const double* values, const double*
    return 1;
 }
 
+// number of SMs of the current device (148 on a B200), asked once per device
+static int sm_count() {
+   static int cached[64] = {0};
+   int device = 0;
+   if (cudaGetDevice(&device) != cudaSuccess || device < 0 || device >= 64) return 148;
+   if (cached[device] == 0) {
+      int n = 0;
+      cached[device] = (cudaDeviceGetAttribute(&n, cudaDevAttrMultiProcessorCount, device) == cudaSuccess && n > 0) ? n : 148;
+   }
+   return cached[device];
+}
+
 int launch_assemble_fill(const AssemblyArrays& M, const double* values, const double* scale, double* pool, cudaStream_t st) {
    if (M.ntiles <= 0) return 0;
-   const int64_t want = (M.ntiles + 0) < 148 * 8 ? M.ntiles : 148 * 8;   // persistent: 8 CTAs of 256 threads per SM
+   const int64_t resident = static_cast<int64_t>(sm_count()) * 8;   // persistent: 8 CTAs of 256 threads per SM
+   const int64_t want = M.ntiles < resident ? M.ntiles : resident;
    k_assemble_fill<<<static_cast<unsigned>(want), 256, 0, st>>>(M, values, scale, pool);
    return 1;
 }
@@ -2530,7 +2543,7 @@ int launch_update(const FrontArrays& F, const int* d_list, int nfronts, int max_
       dim3 grid(nfronts, (rows + 127) / 128, (cols + 127) / 128);
       k_update<128, 128, 4, 4, 32, 1><<<grid, 512, smem_bytes(128, 128, 32), st>>>(F, d_list, mode, j0, J0, W, R);
    } else if (tile_mode == 3 && mode == 1 && R.kpanels == 1 && R.clo == 0 && R.chi < 0) {
-      k_update_ws<<<296, WS_THREADS, WS_SMEM, st>>>(F, d_list, nfronts, J0, W);
+      k_update_ws<<<2 * sm_count(), WS_THREADS, WS_SMEM, st>>>(F, d_list, nfronts, J0, W);   // persistent, two CTAs per SM
    } else if (tile_mode == 2 || tile_mode == 3) {
       // two co-resident CTAs per SM: the read-modify-write epilogue of one tile overlaps the K loop of the other
       dim3 grid(nfronts, (rows + 127) / 128, (cols + 63) / 64);
@@ -2547,7 +2560,7 @@ int launch_update(const FrontArrays& F, const int* d_list, int nfronts, int max_
 
 int launch_inertia(int64_t n, const FactorArrays& W, int* counters, cudaStream_t st, const signed char* col_owner, int rank) {
    int blocks = grid1d(n, 256);
-   if (blocks > 1184) blocks = 1184;
+   if (blocks > 8 * sm_count()) blocks = 8 * sm_count();
    k_inertia<<<blocks, 256, 0, st>>>(n, W, counters, col_owner, rank);
    return 1;
 }
@@ -2709,7 +2722,7 @@ int launch_backward_error_noalloc(int device, const CsrArrays& A, const double* 
    double* r = scratch + NOALLOC_HEAD;
    cudaError_t e = cudaMemsetAsync(acc, 0, NOALLOC_HEAD * sizeof(double), st);
    if (e != cudaSuccess) return static_cast<int>(e);
-   const int blocks = grid1d(A.n, 256), rblocks = blocks > 1184 ? 1184 : (blocks < 1 ? 1 : blocks);
+   const int blocks = grid1d(A.n, 256), rblocks = blocks > 8 * sm_count() ? 8 * sm_count() : (blocks < 1 ? 1 : blocks);
    k_matrix_inf_norm<<<blocks, 256, 0, st>>>(A, values, acc + 0);
    k_absmax<<<rblocks, 256, 0, st>>>(x, A.n, acc + 2);
    k_residual<<<blocks, 256, 0, st>>>(A, values, x, b, r, acc + 2, acc + 4);
@@ -2725,7 +2738,7 @@ int launch_backward_error_noalloc(int device, const CsrArrays& A, const double* 
 
 int launch_absmax(const double* v, int64_t n, unsigned long long* out_bits, cudaStream_t st) {
    int blocks = grid1d(n, 256);
-   if (blocks > 1184) blocks = 1184;
+   if (blocks > 8 * sm_count()) blocks = 8 * sm_count();
    if (blocks < 1) blocks = 1;
    k_absmax<<<blocks, 256, 0, st>>>(v, n, out_bits);
    return 1;
