@@ -404,6 +404,9 @@ def test_full_size_properties(make, name):
     {"lookahead": 1, "pair_panels": 1, "pair_min_front": 512},                    # two outer panels per trailing update
     {"lookahead": 0, "pair_panels": 1, "pair_min_front": 512},
     {"update_tile_mode": 1}, {"update_tile_mode": 2}, {"update_tile_mode": 3}, {"update_tile_mode": 6},
+    {"gather_lists": 0},                                                          # forward gather by the children loop instead of the precomputed lists
+    {"fused_assembly": 0},                                                        # memset + scatter instead of the fused K1
+    {"fused_leaves": 0}, {"fused_leaves": 1},                                     # small fronts through K3a/K3b/K4 instead of K2
 ])
 def test_schedule_and_kernel_variants_agree(options):
     """Streams, look-ahead, panel pairing and the K4 tile variants only reorder independent work (and, for pairing, the
@@ -419,7 +422,7 @@ def test_schedule_and_kernel_variants_agree(options):
     x, berr = s.solve_indefinite_system(kkt.rhs, return_backward_error=True)
     assert s.get_inertia() == ref.get_inertia() == (kkt.n, kkt.m, 0)
     assert berr <= BERR_TOL and berr_r <= BERR_TOL
-    if "pair_min_front" not in options and "update_tile_mode" not in options:
+    if "pair_min_front" not in options and "update_tile_mode" not in options and "fused_leaves" not in options:
         # pure re-scheduling: every entry of the factor sees the same operations in the same order
         a, b = ref.debug_factor(), s.debug_factor()
         assert all(np.array_equal(u, w) for u, w in zip(a, b))

@@ -1956,6 +1956,20 @@ __global__ void __launch_bounds__(256) k_fwd_big_gather(FrontArrays F, const int
    }
 }
 
+__global__ void __launch_bounds__(256) k_fwd_big_gather_list(FrontArrays F, GatherArrays Gt, const int* __restrict__ list, double* __restrict__ zg,
+                                                              double* __restrict__ cpool) {
+   const int s = list[blockIdx.x];
+   const int k = F.k[s], f = F.f[s];
+   const int d = blockIdx.y * 256 + threadIdx.x;
+   if (d >= f) return;
+   const int* __restrict__ ptr = Gt.ptr + Gt.off[s] + d;
+   // pivot rows start from their right-hand side entry, boundary rows from zero: the running sums of k_fwd_big_gather
+   double v = (d < k) ? zg[F.first[s] + d] : 0.0;
+   for (int t = ptr[0]; t < ptr[1]; ++t) v += cpool[Gt.src[t]];
+   if (d < k) zg[F.first[s] + d] = v;
+   else cpool[F.rel_off[s] + (d - k)] = v;
+}
+
 __global__ void __launch_bounds__(256) k_fwd_big_permute(FrontArrays F, const int* __restrict__ list, FactorArrays W,
                                                           const double* __restrict__ zg, double* __restrict__ z2) {
    const int s = list[blockIdx.x];
@@ -2584,6 +2598,14 @@ int launch_fwd_big_gather(const FrontArrays& F, const int* d_list, int nfronts, 
    if (nfronts <= 0) return 0;
    dim3 grid(nfronts, (max_f + GATHER_SPAN - 1) / GATHER_SPAN);
    k_fwd_big_gather<<<grid, 256, 0, st>>>(F, d_list, zg, cpool);
+   return 1;
+}
+
+int launch_fwd_big_gather_list(const FrontArrays& F, const GatherArrays& Gt, const int* d_list, int nfronts, int max_f, double* zg, double* cpool,
+                               cudaStream_t st) {
+   if (nfronts <= 0) return 0;
+   dim3 grid(nfronts, (max_f + 255) / 256);
+   k_fwd_big_gather_list<<<grid, 256, 0, st>>>(F, Gt, d_list, zg, cpool);
    return 1;
 }
 

@@ -144,6 +144,16 @@ int launch_backward_level(const FrontArrays& F, const int* d_list, int nfronts, 
 // Big fronts: many CTAs per front, NBS-wide panel steps.
 int launch_fwd_big_gather(const FrontArrays& F, const int* d_list, int nfronts, int max_f, const FactorArrays& W, double* zg, double* z2,
                           double* cpool, cudaStream_t st);
+// The same gather from a list precomputed at analysis: for row d of big front s (gather_off[s] >= 0) the child entries that land on
+// it are src[ptr[gather_off[s] + d] .. ptr[gather_off[s] + d + 1]) (offsets into cpool, children in ascending order: the summation
+// order of k_fwd_big_gather, hence bit-identical results) - one thread per row, no loop over the children, no barriers.
+struct GatherArrays {
+   const int64_t* off;   // per front; -1: no list
+   const int* ptr;
+   const int* src;
+};
+int launch_fwd_big_gather_list(const FrontArrays& F, const GatherArrays& Gt, const int* d_list, int nfronts, int max_f, double* zg, double* cpool,
+                               cudaStream_t st);
 int launch_fwd_big_permute(const FrontArrays& F, const int* d_list, int nfronts, int max_k, const FactorArrays& W, const double* zg,
                            double* z2, cudaStream_t st);
 int launch_fwd_big_diag(const FrontArrays& F, const int* d_list, int nfronts, int jp, const FactorArrays& W, double* z2, cudaStream_t st);

@@ -548,6 +548,47 @@ void upload_plan(b200kkt_handle* h) {
          }
       }
       h->d_solve_list = dev_upload(h, solve_list);
+      {
+         // gather lists of the big fronts (forward solve): per row of the front, where its children's boundary sums sit in cpool
+         std::vector<int64_t> goff(static_cast<size_t>(P.nsn), -1);
+         std::vector<int> gptr, gsrc, count;
+         int64_t total_rows = 0;
+         for (const auto& SL : h->solve_levels)
+            for (int t = 0; t < SL.big_count; ++t) {
+               const int s = solve_list[static_cast<size_t>(SL.big_begin + t)];
+               goff[s] = total_rows;
+               total_rows += P.f[s] + 1;
+            }
+         gptr.assign(static_cast<size_t>(total_rows) + 1, 0);
+         // pass 1: counts; pass 2: fill, children in ascending order (child_idx is ascending)
+         for (int pass = 0; pass < 2; ++pass) {
+            if (pass == 1) {
+               int64_t run = 0;
+               for (int32_t s = 0; s < P.nsn; ++s) {
+                  if (goff[s] < 0) continue;
+                  for (int d = 0; d <= P.f[s]; ++d) { const int c = gptr[static_cast<size_t>(goff[s] + d)]; gptr[static_cast<size_t>(goff[s] + d)] = static_cast<int>(run); run += (d < P.f[s]) ? c : 0; }
+               }
+               gsrc.resize(static_cast<size_t>(run));
+               count.assign(static_cast<size_t>(total_rows), 0);
+            }
+            for (int32_t s = 0; s < P.nsn; ++s) {
+               if (goff[s] < 0) continue;
+               for (int32_t ci = P.child_ptr[s]; ci < P.child_ptr[s + 1]; ++ci) {
+                  const int32_t c = P.child_idx[ci];
+                  const int64_t r0 = P.rel_off[c];
+                  for (int32_t i = 0; i < P.f[c] - P.k[c]; ++i) {
+                     const int64_t d = goff[s] + P.relmap[static_cast<size_t>(r0 + i)];
+                     if (pass == 0) ++gptr[static_cast<size_t>(d)];
+                     else gsrc[static_cast<size_t>(gptr[static_cast<size_t>(d)] + count[static_cast<size_t>(d)]++)] = static_cast<int>(r0 + i);
+                  }
+               }
+            }
+         }
+         if (P.sum_r >= (int64_t(1) << 31)) h->gather_lists = 0;   // 32-bit offsets into cpool
+         h->Gt.off = dev_upload(h, goff);
+         h->Gt.ptr = dev_upload(h, gptr);
+         h->Gt.src = dev_upload(h, gsrc);
+      }
       int max_big = 1;
       for (const auto& SL : h->solve_levels) max_big = std::max(max_big, SL.big_count);
       h->d_partial = dev_alloc<double>(h, static_cast<size_t>(max_big) * bwd_partial_doubles_per_front());
@@ -999,7 +1040,8 @@ void run_solve(b200kkt_handle* h, const double* d_b, double* d_x, double* backwa
          L += launch_forward_level(h->F, h->d_solve_list + SL.small_begin, SL.small_count, h->W, h->d_zg, h->d_z2, h->d_cpool, st);
          if (SL.big_count > 0) {
             const int* list = h->d_solve_list + SL.big_begin;
-            L += launch_fwd_big_gather(h->F, list, SL.big_count, SL.big_max_f, h->W, h->d_zg, h->d_z2, h->d_cpool, st);
+            if (h->gather_lists != 0) L += launch_fwd_big_gather_list(h->F, h->Gt, list, SL.big_count, SL.big_max_f, h->d_zg, h->d_cpool, st);
+            else L += launch_fwd_big_gather(h->F, list, SL.big_count, SL.big_max_f, h->W, h->d_zg, h->d_z2, h->d_cpool, st);
             L += launch_fwd_big_permute(h->F, list, SL.big_count, SL.big_max_k, h->W, h->d_zg, h->d_z2, st);
             for (int jp = 0; jp < SL.big_max_k; jp += NBS) {
                const int nf = count_greater(SL.big_k, jp);
@@ -1293,6 +1335,7 @@ int b200kkt_set_option(b200kkt_handle* h, const char* name, double value) {
    else if (n == "lookahead") h->lookahead = static_cast<int>(value);
    else if (n == "fused_assembly") h->fused_assembly = static_cast<int>(value);
    else if (n == "fused_leaves") h->fused_leaves = static_cast<int>(value);
+   else if (n == "gather_lists") h->gather_lists = static_cast<int>(value);
    else if (n == "lookahead_min_front") h->lookahead_min_front = static_cast<int>(value);
    else if (n == "pair_panels") h->pair_panels = static_cast<int>(value);
    else if (n == "pair_min_front") h->pair_min_front = static_cast<int>(value);

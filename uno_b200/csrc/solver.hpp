@@ -120,6 +120,8 @@ struct b200kkt_handle {
    b200kkt::AssemblyArrays M{};
    b200kkt::CsrArrays C{};
    b200kkt::FactorArrays W{};
+   b200kkt::GatherArrays Gt{};               // gather lists of the big fronts' forward solve (kernels.hpp)
+   int gather_lists = 1;
    int* d_perm = nullptr;
    int* d_batch_list = nullptr;
    int* d_solve_list = nullptr;
