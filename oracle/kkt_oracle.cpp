@@ -30,6 +30,7 @@
 #include <cmath>
 #include <cstdint>
 #include <cstdio>
+#include <cstdlib>
 #include <cstring>
 #include <dlfcn.h>
 #include <map>
@@ -93,6 +94,42 @@ void trsm_right_lower_trans_unit(int m, int n, const double* T, int ldt, double*
          for (int i = 0; i < m; ++i) xq[i] -= xp[i] * t;
       }
    }
+}
+
+#ifdef _OPENMP
+inline bool in_team() { return omp_in_parallel() != 0; }
+#else
+inline bool in_team() { return true; }
+#endif
+
+// The same product cut into tiles that the OpenMP team works through, single-threaded BLAS inside each tile: ONE thread pool.
+// (A threaded BLAS keeps its own workers spinning after every call, and they fight the OpenMP loops around it for the cores.)
+// lower: C is a diagonal block of the front (rows and columns from the same origin) and only its lower part is needed.
+void gemm_nt_sub_team(int m, int n, int k, const double* A, int lda, const double* B, int ldb, double* C, int ldc, bool lower) {
+   if (m <= 0 || n <= 0 || k <= 0) return;
+   const int TM = 768, TN = 256;
+   const int nj = (n + TN - 1) / TN, ni = (m + TM - 1) / TM;
+   const bool team = !in_team() && static_cast<double>(m) * n * k >= 4.0e7;
+#pragma omp parallel for collapse(2) schedule(dynamic, 1) if (team)
+   for (int tj = 0; tj < nj; ++tj) {
+      for (int ti = 0; ti < ni; ++ti) {
+         const int j0 = tj * TN, j1 = std::min(n, j0 + TN);
+         int i0 = ti * TM;
+         const int i1 = std::min(m, i0 + TM);
+         if (lower) { if (i1 <= j0) continue; i0 = std::max(i0, j0); }
+         gemm_nt_sub(i1 - i0, j1 - j0, k, A + i0, lda, B + j0, ldb, C + i0 + static_cast<size_t>(ldc) * j0, ldc);
+      }
+   }
+}
+
+// rows of B are independent in B T^{-T}: the team takes them in chunks
+void trsm_right_lower_trans_unit_team(int m, int n, const double* T, int ldt, double* B, int ldb) {
+   if (m <= 0 || n <= 0) return;
+   const int TM = 512;
+   const int ni = (m + TM - 1) / TM;
+   const bool team = !in_team() && static_cast<double>(m) * n * n >= 4.0e7;
+#pragma omp parallel for schedule(dynamic, 1) if (team)
+   for (int ti = 0; ti < ni; ++ti) trsm_right_lower_trans_unit(std::min(TM, m - ti * TM), n, T, ldt, B + ti * TM, ldb);
 }
 
 struct Front {
@@ -177,6 +214,17 @@ namespace {
 
 using clk = std::chrono::steady_clock;
 double since(clk::time_point t0) { return std::chrono::duration<double>(clk::now() - t0).count(); }
+
+// ORACLE_PROFILE=1: where the wall clock of a factorization goes (big fronts run one at a time, so plain sums are exact for them)
+enum { T_SIDE, T_ASM, T_EXTADD, T_PIVOT, T_INNER_GEMM, T_ROWS, T_OUTER_GEMM, T_COPY, T_COUNT };
+double g_prof[T_COUNT];
+double g_prof_nf2 = 0, g_prof_nfne = 0, g_prof_cb2 = 0; int g_prof_big = 0;
+bool g_prof_on = false;
+struct Tick {
+   int cat; clk::time_point t0; bool on;
+   Tick(int c, bool enable) : cat(c), on(enable && g_prof_on) { if (on) t0 = clk::now(); }
+   ~Tick() { if (on) g_prof[cat] += since(t0); }
+};
 
 // ---- symbolic phase (independent of the product's) -----------------------------------------------
 void analyse(Oracle& o, int64_t N, int64_t nnz, const uint64_t* row, const uint64_t* col, const int64_t* user_perm) {
@@ -264,14 +312,23 @@ void analyse(Oracle& o, int64_t N, int64_t nnz, const uint64_t* row, const uint6
    std::vector<int> nchild(N, 0);
    for (int j = 0; j < N; ++j) if (parent[j] != -1) ++nchild[parent[j]];
    std::vector<int> sfirst;
+   double sn_zeros = 0.0;   // explicit zeros the current supernode already stores
    for (int j = 0; j < N; ++j) {
-      bool glue = j > 0 && parent[j - 1] == j && nchild[j] == 1 && cc[j - 1] == cc[j] + 1;
-      if (!glue && j > 0 && parent[j - 1] == j && !sfirst.empty()) {
-         // relaxed: previous supernode is a child chain ending at j-1; glue when the merged block stays small
-         const int k_prev = j - sfirst.back();
-         if (k_prev + 1 <= 24 && cc[j - 1] - 1 <= cc[j] + 8) glue = true;
+      bool glue = false;
+      if (j > 0 && parent[j - 1] == j && !sfirst.empty()) {
+         // column j joins the supernode that ends at its child j-1.  struct(j) holds struct(j-1) \ {j-1}; the `extra` rows it
+         // brings on top (from its other children or its own entries) become explicit zeros in every column already there.
+         const double k_prev = j - sfirst.back();
+         const double extra = cc[j] - (cc[j - 1] - 1);
+         const double znew = sn_zeros + k_prev * extra;
+         const double kn = k_prev + 1.0, fn = k_prev + cc[j];
+         const double nnz_merged = kn * fn - 0.5 * kn * (kn - 1.0);
+         if (extra == 0.0) glue = true;                                   // nested: a fundamental supernode (or as good as one)
+         else if (kn <= 24 && extra <= 8) glue = true;                    // small blocks: anything for fewer, wider fronts
+         else if (znew <= 0.12 * nnz_merged) glue = true;                 // relaxed amalgamation: separators broken up by small side trees
+         if (glue) sn_zeros = znew;
       }
-      if (!glue) sfirst.push_back(j);
+      if (!glue) { sfirst.push_back(j); sn_zeros = 0.0; }
    }
    sfirst.push_back(static_cast<int>(N));
    const int ns = static_cast<int>(sfirst.size()) - 1;
@@ -350,6 +407,12 @@ void factor_front(Oracle& o, int s, const double* val, Work& w) {
    // only the lower triangle is ever read: it alone is cleared (the BLAS strips may leave anything above the diagonal)
    double* A = Work::ensure(w.A, w.capA, ld * nf);
    const bool big = nf >= 1024;
+#ifdef _OPENMP
+   const bool solo = !omp_in_parallel();
+#else
+   const bool solo = true;
+#endif
+   std::unique_ptr<Tick> tick(new Tick(T_ASM, solo));
 #pragma omp parallel for schedule(static, 16) if (big)
    for (int j = 0; j < nf; ++j) std::memset(A + ld * j + j, 0, sizeof(double) * static_cast<size_t>(nf - j));
    for (int t = 0; t < nf; ++t) w.loc[F.idx[t]] = t;
@@ -361,6 +424,7 @@ void factor_front(Oracle& o, int s, const double* val, Work& w) {
          lower(A, nf, w.loc[o.crow[p]], lj) += val[e] * o.scale[o.urow[e]] * o.scale[o.ucol[e]];
       }
    }
+   tick.reset(); tick.reset(new Tick(T_EXTADD, solo));
    // extend-add of the children's contribution blocks (delayed pivots included)
    for (int c : F.children) {
       Front& C = o.fronts[c];
@@ -387,6 +451,7 @@ void factor_front(Oracle& o, int s, const double* val, Work& w) {
       }
       o.pool.give(C.cb, C.cb_cap);
    }
+   tick.reset();
    F.d.assign(nfs, 1.0); F.e.assign(nfs, 0.0); F.ptype.assign(nfs, 0);
    // big fronts: wider blocks (fewer passes over the trailing matrix) and the in-block column work spread over the threads;
    // small fronts are factored one per thread by the level loop (nested regions stay serial)
@@ -412,6 +477,7 @@ void factor_front(Oracle& o, int s, const double* val, Work& w) {
          while (ne < oend) {
             const int istart = ne, ibend = std::min(ne + NBI, oend);
             int cand = ne;
+            tick.reset(new Tick(T_PIVOT, solo));
             while (cand < ibend) {
                // column maxima of candidate c over the not yet eliminated part of the front
                const int c = cand;
@@ -493,9 +559,11 @@ void factor_front(Oracle& o, int s, const double* val, Work& w) {
                cand = std::max(cand + 1, ne);   // go on with untested candidates; failed ones are retried in the next block
             }
             const int inbw = ne - istart;
+            tick.reset(); tick.reset(new Tick(T_INNER_GEMM, solo));
             if (inbw > 0) {
                // the inner block's pivots on the rest of the outer block; failed candidates [ne, ibend) stay in front (up to date)
-               gemm_nt_sub(rlim - ibend, obend - ibend, inbw, W + ibend + ld * (istart - ostart), nf, A + ibend + ld * istart, nf, A + ibend + ld * ibend, nf);
+               gemm_nt_sub_team(rlim - ibend, obend - ibend, inbw, W + ibend + ld * (istart - ostart), nf, A + ibend + ld * istart, nf, A + ibend + ld * ibend, nf,
+                                false);
             } else {
                const int cnt = ibend - ne;
                for (int t = 0; t < cnt; ++t) { const int a = ne + t, b = oend - 1 - t; if (a < b) swap_sym(A, nf, a, b, F.idx); }
@@ -503,10 +571,11 @@ void factor_front(Oracle& o, int s, const double* val, Work& w) {
             }
          }
          const int nbw = ne - ostart;
+         tick.reset(); tick.reset(new Tick(T_ROWS, solo));
          if (nbw > 0 && rlim < nf) {
             // rows R of the block's pivot columns: W_R = A_R L_PP^{-T} (A_R still as the outer block found it), L_R = W_R D^{-1}
             const int mr = nf - rlim;
-            trsm_right_lower_trans_unit(mr, nbw, A + ostart + ld * ostart, nf, A + rlim + ld * ostart, nf);
+            trsm_right_lower_trans_unit_team(mr, nbw, A + ostart + ld * ostart, nf, A + rlim + ld * ostart, nf);
 #pragma omp parallel for schedule(static) if (big)
             for (int p = ostart; p < ne; ++p) {
                if (F.ptype[p] == 2) continue;
@@ -527,15 +596,13 @@ void factor_front(Oracle& o, int s, const double* val, Work& w) {
                }
             }
             // and rows R of the columns of this block that were not eliminated
-            gemm_nt_sub(mr, obend - ne, nbw, W + rlim, nf, A + ne + ld * ostart, nf, A + rlim + ld * ne, nf);
+            gemm_nt_sub_team(mr, obend - ne, nbw, W + rlim, nf, A + ne + ld * ostart, nf, A + rlim + ld * ne, nf, false);
          }
+         tick.reset(); tick.reset(new Tick(T_OUTER_GEMM, solo));
          if (nbw > 0) {
             since_retry += nbw;
-            // rank-nbw update of everything right of the outer block: C -= W * L^T, in 512-column strips (lower part only)
-            for (int c0 = obend; c0 < nf; c0 += 512) {
-               const int c1 = std::min(c0 + 512, nf);
-               gemm_nt_sub(nf - c0, c1 - c0, nbw, W + c0, nf, A + c0 + ld * ostart, nf, A + c0 + ld * c0, nf);
-            }
+            // rank-nbw update of everything right of the outer block: C -= W * L^T, tile by tile (lower part only)
+            gemm_nt_sub_team(nf - obend, nf - obend, nbw, W + obend, nf, A + obend + ld * ostart, nf, A + obend + ld * obend, nf, true);
             // parked candidates [ne, obend) stay in front of the next block (already up to date)
          } else {
             // nothing could be eliminated in this block: set its columns aside and go on
@@ -544,6 +611,7 @@ void factor_front(Oracle& o, int s, const double* val, Work& w) {
             active_end -= cnt;
          }
       }
+      tick.reset();
       if (active_end < nfs && since_retry > 0) { active_end = nfs; since_retry = 0; continue; }   // retry postponed columns
       if (is_root && ne < nfs && !forcing) { forcing = true; u = 0.0; active_end = nfs; since_retry = 0; continue; }
       break;
@@ -557,6 +625,8 @@ void factor_front(Oracle& o, int s, const double* val, Work& w) {
       ne = nfs;
    }
    F.nelim = ne;
+   tick.reset(new Tick(T_COPY, solo));
+   if (solo && g_prof_on) { g_prof_nf2 += double(nf) * nf; g_prof_nfne += double(nf) * ne; g_prof_big += 1; for (int c : F.children) g_prof_cb2 += double(o.fronts[c].ncb) * o.fronts[c].ncb; }
    // (only the part of a column at and below its diagonal is ever read: nothing is cleared)
    if (F.L.size() != ld * ne) { std::vector<double>().swap(F.L); F.L.resize(ld * ne); }
 #pragma omp parallel for schedule(static, 8) if (big)
@@ -593,11 +663,14 @@ void equilibrate(Oracle& o, const double* val, int sweeps) {
 
 void factorize(Oracle& o, const double* val, int nthreads) {
    const auto t0 = clk::now();
+   g_prof_on = std::getenv("ORACLE_PROFILE") != nullptr;
+   std::fill(g_prof, g_prof + T_COUNT, 0.0); g_prof_nf2 = g_prof_nfne = g_prof_cb2 = 0; g_prof_big = 0;
    equilibrate(o, val, 3);
    if (nthreads < 1) nthreads = 1;
 #ifdef _OPENMP
    omp_set_num_threads(nthreads);
 #endif
+   if (g_set_threads != nullptr) g_set_threads(1);   // every BLAS call runs in the calling OpenMP thread (see gemm_nt_sub_team)
    std::vector<Work>& works = o.works;
    if (static_cast<int>(works.size()) != nthreads) { works.clear(); works.resize(nthreads); }
    for (auto& w : works) if (static_cast<int64_t>(w.loc.size()) != o.N) w.loc.assign(o.N, -1);
@@ -613,7 +686,7 @@ void factorize(Oracle& o, const double* val, int nthreads) {
       if (side.size() == 1) { big_ones.push_back(side[0]); side.clear(); }
       const int ns = static_cast<int>(side.size());
       if (ns > 0) {
-         if (g_set_threads != nullptr) g_set_threads(1);
+         Tick side_tick(T_SIDE, true);
 #pragma omp parallel for schedule(dynamic, 1)
          for (int t = 0; t < ns; ++t) {
 #ifdef _OPENMP
@@ -625,7 +698,6 @@ void factorize(Oracle& o, const double* val, int nthreads) {
          }
       }
       if (!big_ones.empty()) {
-         if (g_set_threads != nullptr) g_set_threads(nthreads);
          for (const int f : big_ones) factor_front(o, f, val, works[0]);
       }
    }
@@ -642,6 +714,11 @@ void factorize(Oracle& o, const double* val, int nthreads) {
       }
    }
    o.t_factor = since(t0);
+   if (g_prof_on)
+      std::fprintf(stderr, "oracle profile: total %.3f s | levels of small fronts %.3f | big fronts: assemble %.3f extend-add %.3f pivot columns %.3f "
+                   "inner gemm %.3f boundary rows %.3f outer gemm %.3f copy-out %.3f\n", o.t_factor, g_prof[T_SIDE], g_prof[T_ASM], g_prof[T_EXTADD],
+                   g_prof[T_PIVOT], g_prof[T_INNER_GEMM], g_prof[T_ROWS], g_prof[T_OUTER_GEMM], g_prof[T_COPY]);
+   if (g_prof_on) std::fprintf(stderr, "oracle profile: %d big fronts, sum nf^2 %.3g, sum nf*ne %.3g, sum child ncb^2 %.3g doubles\n", g_prof_big, g_prof_nf2, g_prof_nfne, g_prof_cb2);
 }
 
 void solve(Oracle& o, const double* rhs, double* x) {
