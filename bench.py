@@ -21,8 +21,9 @@ import argparse
 import json
 import os
 
-# before anything loads libgomp: the CPU arm's OpenMP workers must sleep, not spin, while the (pthread) OpenBLAS threads run
-os.environ.setdefault("OMP_WAIT_POLICY", "passive")
+# before anything loads libgomp: the CPU arm's OpenMP workers spin for about a millisecond after a region, then sleep - the pivot
+# loop of a big front opens thousands of short regions back to back; every BLAS call of the oracle runs inside its OpenMP threads
+os.environ.setdefault("GOMP_SPINCOUNT", "3000000")
 import subprocess
 import sys
 import threading
@@ -41,7 +42,7 @@ WORKLOADS = {
     # name: (description, generator, cpu-sample generator)
     "ocp3d_k128": ("BASELINE configs[4]: synthetic 3D PDE-constrained optimal control KKT, 128^3 grid, boundary control "
                    "(2.2 M primal rows + 2.1 M multipliers), whole system on ONE B200",
-                   lambda G, seed: G.ocp_boundary_3d(128, seed=seed), lambda G, seed: G.ocp_boundary_3d(48, seed=seed)),
+                   lambda G, seed: G.ocp_boundary_3d(128, seed=seed), lambda G, seed: G.ocp_boundary_3d(64, seed=seed)),
     "ocp3d_k64": ("BASELINE configs[3]: synthetic 3D PDE-constrained optimal control KKT, 64^3 grid, 7-point, distributed control",
                   lambda G, seed: G.ocp_distributed(64, 3, seed=seed), lambda G, seed: G.ocp_distributed(48, 3, seed=seed)),
     "ocp2d_k256": ("BASELINE configs[1]: synthetic 2D PDE-constrained optimal control KKT, 256x256 grid",
@@ -131,7 +132,6 @@ def cpu_threads():
     if os.environ.get("OMP_NUM_THREADS", "1") == "1":
         os.environ["OMP_NUM_THREADS"] = str(cores)
     os.environ.setdefault("OPENBLAS_NUM_THREADS", str(cores))
-    os.environ.setdefault("OMP_WAIT_POLICY", "passive")
     return cores
 
 
@@ -190,26 +190,34 @@ def main():
         if rank != 0:
             return 0
         # The CPU arm MEASURES: it runs the workload its line names, in full.  The b200 arm's default workload (128^3, 2e14 factor
-        # flops, ~150 GB of factors) is run only when the 64^3 measurement taken first predicts that one step fits the time budget
-        # and the host memory; otherwise the line reports the 64^3 run - config.workload says so - and the driver's same_config
-        # check reads false, which is the truth.
+        # flops, ~110 GB of factors and workspace on the host) is run - one step - when its bounded sample (the same generator at
+        # 64^3), measured first, predicts that the step fits the time budget and the host memory.  Otherwise the line reports
+        # BASELINE configs[3] (64^3, distributed control) - config.workload says so - and the driver's same_config check reads
+        # false, which is the truth.
         from oracle import cpu_arm as CA
         requested = args.workload
-        budget = float(os.environ.get("B200KKT_REFERENCE_BUDGET_S", "1500"))
+        budget = float(os.environ.get("B200KKT_REFERENCE_BUDGET_S", "600"))
         t_start = time.perf_counter()
         runs = []
         if requested == "ocp3d_k128":
-            r64 = measure_cpu(G, "ocp3d_k64", 1, 1, 0)
-            runs.append(r64)
-            full_flops_estimate = 63.0 * r64["factor_flops"]          # plans of round 1: 1.97e14 / 3.14e12
-            predicted = full_flops_estimate / (r64["factor_gflops"] * 1e9) + 6.0 * (time.perf_counter() - t_start)   # + generator, ordering, analysis
-            if predicted <= budget and CA.host_memory_available_gb() >= 175.0:
+            sample = measure_cpu(G, "ocp3d_k128", 2, 1, 1)
+            runs.append(sample)
+            full_flops_estimate = 2.07e14                                # the b200 arm's plan (profiles/r02_bench_k128_v2.json)
+            # the oracle's rate grows with the front sizes, so the sample's rate is a cautious one; + generator, ordering, analysis
+            predicted = full_flops_estimate / (sample["factor_gflops"] * 1e9) + 150.0
+            if predicted <= budget and CA.host_memory_available_gb() >= 150.0:
                 res = measure_cpu(G, "ocp3d_k128", 1, 1, 0)
                 runs.append(res)
             else:
-                res = r64
-                res["note"] = (f"ocp3d_k128 not run: predicted {predicted:.0f} s per step against a budget of {budget:.0f} s "
-                               f"(B200KKT_REFERENCE_BUDGET_S), host memory available {CA.host_memory_available_gb():.0f} GB")
+                note = (f"ocp3d_k128 not run: predicted {predicted:.0f} s for one step (sample: {sample['factor_gflops']:.0f} GFLOP/s) against a budget of "
+                        f"{budget:.0f} s (B200KKT_REFERENCE_BUDGET_S), host memory available {CA.host_memory_available_gb():.0f} GB")
+                one = measure_cpu(G, "ocp3d_k64", 1, 1, 0)
+                runs.append(one)
+                more = int(min(max(args.steps, 1), max(1.0, 0.25 * budget / max(one["seconds_per_step"], 1e-3))))
+                res = measure_cpu(G, "ocp3d_k64", 1, more, 1) if more > 1 else one
+                if more > 1:
+                    runs.append(res)
+                res["note"] = note
                 requested = "ocp3d_k64"
         else:
             one = measure_cpu(G, requested, 1, 1, 0)

@@ -180,7 +180,7 @@ struct Work {
    std::unique_ptr<double[]> A, W;
    size_t capA = 0, capW = 0;
    static double* ensure(std::unique_ptr<double[]>& buf, size_t& cap, size_t need) {
-      if (need > cap) { cap = need + need / 2; buf.reset(); buf.reset(new double[cap]); }
+      if (need > cap) { cap = need + (need < (size_t(1) << 27) ? need / 2 : need / 16); buf.reset(); buf.reset(new double[cap]); }
       return buf.get();
    }
 };
@@ -218,6 +218,7 @@ double since(clk::time_point t0) { return std::chrono::duration<double>(clk::now
 // ORACLE_PROFILE=1: where the wall clock of a factorization goes (big fronts run one at a time, so plain sums are exact for them)
 enum { T_SIDE, T_ASM, T_EXTADD, T_PIVOT, T_INNER_GEMM, T_ROWS, T_OUTER_GEMM, T_COPY, T_COUNT };
 double g_prof[T_COUNT];
+double g_prof_cls[5]; long g_prof_cnt[5];
 double g_prof_nf2 = 0, g_prof_nfne = 0, g_prof_cb2 = 0; int g_prof_big = 0;
 bool g_prof_on = false;
 struct Tick {
@@ -665,6 +666,7 @@ void factorize(Oracle& o, const double* val, int nthreads) {
    const auto t0 = clk::now();
    g_prof_on = std::getenv("ORACLE_PROFILE") != nullptr;
    std::fill(g_prof, g_prof + T_COUNT, 0.0); g_prof_nf2 = g_prof_nfne = g_prof_cb2 = 0; g_prof_big = 0;
+   for (int c = 0; c < 5; ++c) { g_prof_cls[c] = 0; g_prof_cnt[c] = 0; }
    equilibrate(o, val, 3);
    if (nthreads < 1) nthreads = 1;
 #ifdef _OPENMP
@@ -694,6 +696,15 @@ void factorize(Oracle& o, const double* val, int nthreads) {
 #else
             Work& w = works[0];
 #endif
+            if (g_prof_on) {
+               const auto tf = clk::now();
+               factor_front(o, side[t], val, w);
+               const double dt = since(tf);
+               const int nf = o.fronts[side[t]].nf;
+               const int cls = nf < 32 ? 0 : nf < 128 ? 1 : nf < 512 ? 2 : nf < 1500 ? 3 : 4;
+#pragma omp critical(oracle_prof)
+               { g_prof_cls[cls] += dt; g_prof_cnt[cls] += 1; }
+            } else
             factor_front(o, side[t], val, w);
          }
       }
@@ -718,6 +729,8 @@ void factorize(Oracle& o, const double* val, int nthreads) {
       std::fprintf(stderr, "oracle profile: total %.3f s | levels of small fronts %.3f | big fronts: assemble %.3f extend-add %.3f pivot columns %.3f "
                    "inner gemm %.3f boundary rows %.3f outer gemm %.3f copy-out %.3f\n", o.t_factor, g_prof[T_SIDE], g_prof[T_ASM], g_prof[T_EXTADD],
                    g_prof[T_PIVOT], g_prof[T_INNER_GEMM], g_prof[T_ROWS], g_prof[T_OUTER_GEMM], g_prof[T_COPY]);
+   if (g_prof_on) std::fprintf(stderr, "oracle profile: small fronts by size (<32, <128, <512, <1500, rest): thread-seconds %.3f %.3f %.3f %.3f %.3f, counts %ld %ld %ld %ld %ld\n",
+      g_prof_cls[0], g_prof_cls[1], g_prof_cls[2], g_prof_cls[3], g_prof_cls[4], g_prof_cnt[0], g_prof_cnt[1], g_prof_cnt[2], g_prof_cnt[3], g_prof_cnt[4]);
    if (g_prof_on) std::fprintf(stderr, "oracle profile: %d big fronts, sum nf^2 %.3g, sum nf*ne %.3g, sum child ncb^2 %.3g doubles\n", g_prof_big, g_prof_nf2, g_prof_nfne, g_prof_cb2);
 }
 

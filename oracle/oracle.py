@@ -33,8 +33,8 @@ _lib = None
 def _load():
     global _lib
     if _lib is None:
-        # the OpenMP workers must sleep, not spin, while the (pthread) OpenBLAS threads run, and the other way round
-        os.environ.setdefault("OMP_WAIT_POLICY", "passive")
+        # workers spin for about a millisecond after a parallel region, then sleep (the pivot loop opens short regions back to back)
+        os.environ.setdefault("GOMP_SPINCOUNT", "3000000")
         if not LIB.exists():
             build()
         lib = C.CDLL(str(LIB))

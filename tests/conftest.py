@@ -2,8 +2,8 @@ import os
 import sys
 from pathlib import Path
 
-# before anything loads libgomp (torch does): the oracle's OpenMP workers must sleep, not spin, next to the OpenBLAS threads
-os.environ.setdefault("OMP_WAIT_POLICY", "passive")
+# before anything loads libgomp: the oracle's OpenMP workers spin briefly between the short regions of its pivot loop, then sleep
+os.environ.setdefault("GOMP_SPINCOUNT", "3000000")
 
 import pytest
 
