@@ -147,6 +147,7 @@ def measure_cpu(G, name, slot, steps, warmup):
                 "value": 1.0 / res["seconds_per_step"], "steps": steps, "warmup": warmup, "cores": cores, "cpu": CA.cpu_model(),
                 "expected_inertia": [kkt.n, kkt.m, 0], "plan": info})
     res["host_dgemm_peak_gflops"] = CA.host_dgemm_peak_gflops()
+    res["peak_rss_gb"] = CA.peak_rss_gb()
     mp = CA.mumps_probe()
     res["mumps"] = mp["note"] if not mp["available"] else CA.run_mumps(mp["exe"], kkt, perm, cores)
     return res
@@ -205,12 +206,16 @@ def main():
             full_flops_estimate = 2.07e14                                # the b200 arm's plan (profiles/r02_bench_k128_v2.json)
             # the oracle's rate grows with the front sizes, so the sample's rate is a cautious one; + generator, ordering, analysis
             predicted = full_flops_estimate / (sample["factor_gflops"] * 1e9) + 150.0
-            if predicted <= budget and CA.host_memory_available_gb() >= 150.0:
+            # memory: the sample's resident peak scaled by the factor sizes of the two plans (9.37e9 against 4.86e8 entries);
+            # a host driven out of memory is worse than a line that names the smaller configuration
+            predicted_gb = 1.05 * sample["peak_rss_gb"] * 9.37e9 / 4.86e8
+            if predicted <= budget and predicted_gb <= 0.75 * CA.host_memory_available_gb():
                 res = measure_cpu(G, "ocp3d_k128", 1, 1, 0)
                 runs.append(res)
             else:
                 note = (f"ocp3d_k128 not run: predicted {predicted:.0f} s for one step (sample: {sample['factor_gflops']:.0f} GFLOP/s) against a budget of "
-                        f"{budget:.0f} s (B200KKT_REFERENCE_BUDGET_S), host memory available {CA.host_memory_available_gb():.0f} GB")
+                        f"{budget:.0f} s (B200KKT_REFERENCE_BUDGET_S); predicted {predicted_gb:.0f} GB of host memory (sample peak "
+                        f"{sample['peak_rss_gb']:.1f} GB x factor-size ratio) against {CA.host_memory_available_gb():.0f} GB available, limit 75 %")
                 one = measure_cpu(G, "ocp3d_k64", 1, 1, 0)
                 runs.append(one)
                 more = int(min(max(args.steps, 1), max(1.0, 0.25 * budget / max(one["seconds_per_step"], 1e-3))))
@@ -446,8 +451,30 @@ def main():
     if world == 1 and not args.no_cpu_baseline:
         try:
             # bounded sample of the workload (slot 2 of WORKLOADS), measured; value = the sample's own factorize+solve/s
-            res_cpu = measure_cpu(G, args.workload, 2, 1, 0)
+            res_cpu = measure_cpu(G, args.workload, 2, 2, 1)
             line["cpu_baseline"] = cpu_baseline_object(res_cpu, "bounded sample of the workload")
+            # the SAME sample through this arm's host-buffer path (factorize + inertia + solve, copies inside): a measured ratio on one
+            # identical system, next to the two arms' lines
+            solver.close()
+            sk = WORKLOADS[args.workload][2](G, 0)
+            s2 = KKTSolver(device=local_rank, **extra_options)
+            s2.do_symbolic_analysis(sk.dim, sk.row, sk.col, sk.reg_size, sk.n, values=sk.val)
+            t_s2 = []
+            for it in range(args.warmup + args.steps):
+                torch.cuda.synchronize()
+                t0s = time.perf_counter()
+                s2.do_numerical_factorization(sk.val)
+                ine2 = s2.get_inertia()
+                x2 = s2.solve_indefinite_system(sk.rhs)
+                t_s2.append(time.perf_counter() - t0s)
+            t_gpu = float(np.mean(t_s2[args.warmup:]))
+            if list(ine2) != list(res_cpu["inertia"]):
+                raise SystemExit(f"bench: inertia of the sample differs between the arms: {ine2} against {res_cpu['inertia']}")
+            line["cpu_baseline"]["b200_on_the_same_sample"] = {
+                "value": 1.0 / t_gpu, "unit": UNIT, "ms_per_step": 1e3 * t_gpu, "steps": args.steps, "warmup": args.warmup, "inertia": list(ine2),
+                "backward_error": s2.stats()["backward_error_last"], "speedup_measured": res_cpu["seconds_per_step"] / t_gpu,
+                "note": "host buffers in and out, wall clock around the three calls; same system, same ordering, same inertia as cpu_baseline.value"}
+            s2.close()
             floor_s = st0["flops_factor"] / (res_cpu["host_dgemm_peak_gflops"] * 1e9)
             line["cpu_baseline"]["time_floor_this_workload"] = {
                 "seconds_at_host_dgemm_peak": floor_s, "b200_seconds_per_step": elapsed / args.steps, "speedup_lower_bound": floor_s / (elapsed / args.steps),

@@ -63,9 +63,15 @@ def host_memory_available_gb() -> float:
     return 0.0
 
 
-def oracle_memory_gb(info) -> float:
-    """Factor storage + the (packed) contribution blocks alive at the peak + the dense workspace of the largest front."""
-    return 8e-9 * (info["pool_doubles"] + 1.3 * info["cb_arena_doubles"] + 1.05 * info["max_front"] ** 2) + 2.0
+def peak_rss_gb() -> float:
+    """Resident-set high-water mark of this process (the oracle's factors, contribution blocks and workspaces live in it)."""
+    try:
+        for line in Path("/proc/self/status").read_text().splitlines():
+            if line.startswith("VmHWM:"):
+                return float(line.split()[1]) / 1e6
+    except OSError:
+        pass
+    return 0.0
 
 
 def run_oracle(kkt, perm, steps: int, warmup: int, threads: int):
