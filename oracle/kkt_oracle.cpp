@@ -734,22 +734,54 @@ void factorize(Oracle& o, const double* val, int nthreads) {
    if (g_prof_on) std::fprintf(stderr, "oracle profile: %d big fronts, sum nf^2 %.3g, sum nf*ne %.3g, sum child ncb^2 %.3g doubles\n", g_prof_big, g_prof_nf2, g_prof_nfne, g_prof_cb2);
 }
 
+// One right-hand side: every factor entry is read once per sweep (memory-bound).  Small fronts run as they are; a big front is
+// swept in blocks of SB pivot columns - the triangle of the block by one thread, the rows below it shared out over the team.
 void solve(Oracle& o, const double* rhs, double* x) {
    const auto t0 = clk::now();
    const int64_t N = o.N;
-   std::vector<double> y(N), xs;
+   constexpr int SB = 64;
+   std::vector<double> y(N), xs, part;
    for (int64_t g = 0; g < N; ++g) y[g] = rhs[o.perm[g]] * o.scale[o.perm[g]];
    const int ns = static_cast<int>(o.fronts.size());
+#ifdef _OPENMP
+   const int nth = omp_get_max_threads();
+#else
+   const int nth = 1;
+#endif
    for (int s = 0; s < ns; ++s) {
       const Front& F = o.fronts[s];
       const int nf = F.nf, ne = F.nelim;
       xs.resize(nf);
       for (int t = 0; t < nf; ++t) xs[t] = y[F.idx[t]];
-      for (int j = 0; j < ne; ++j) {
-         const double yj = xs[j];
-         if (yj == 0.0) continue;
-         const double* l = F.L.data() + static_cast<size_t>(nf) * j;
-         for (int i = j + 1; i < nf; ++i) xs[i] -= l[i] * yj;
+      const double* L = F.L.data();
+      const size_t ld = static_cast<size_t>(nf);
+      double* xp = xs.data();
+      if (static_cast<double>(nf) * ne < 2.0e5 || nth == 1) {
+         for (int j = 0; j < ne; ++j) {
+            const double yj = xp[j];
+            if (yj == 0.0) continue;
+            const double* l = L + ld * j;
+            for (int i = j + 1; i < nf; ++i) xp[i] -= l[i] * yj;
+         }
+      } else {
+         for (int jb = 0; jb < ne; jb += SB) {
+            const int je = std::min(jb + SB, ne);
+            for (int j = jb; j < je; ++j) {
+               const double yj = xp[j];
+               const double* l = L + ld * j;
+               for (int i = j + 1; i < je; ++i) xp[i] -= l[i] * yj;
+            }
+#pragma omp parallel for schedule(static)
+            for (int c = 0; c < nth; ++c) {
+               const int64_t rows = nf - je;
+               const int i0 = je + static_cast<int>(rows * c / nth), i1 = je + static_cast<int>(rows * (c + 1) / nth);
+               for (int j = jb; j < je; ++j) {
+                  const double yj = xp[j];
+                  const double* l = L + ld * j;
+                  for (int i = i0; i < i1; ++i) xp[i] -= l[i] * yj;
+               }
+            }
+         }
       }
       for (int t = 0; t < nf; ++t) y[F.idx[t]] = xs[t];
    }
@@ -767,16 +799,47 @@ void solve(Oracle& o, const double* rhs, double* x) {
          } else if (F.ptype[j] == 3) a = 0.0;
       }
    }
+   part.resize(static_cast<size_t>(nth) * SB);
    for (int s = ns - 1; s >= 0; --s) {
       const Front& F = o.fronts[s];
       const int nf = F.nf, ne = F.nelim;
       xs.resize(nf);
       for (int t = 0; t < nf; ++t) xs[t] = y[F.idx[t]];
-      for (int j = ne - 1; j >= 0; --j) {
-         const double* l = F.L.data() + static_cast<size_t>(nf) * j;
-         double acc = xs[j];
-         for (int i = j + 1; i < nf; ++i) acc -= l[i] * xs[i];
-         xs[j] = acc;
+      const double* L = F.L.data();
+      const size_t ld = static_cast<size_t>(nf);
+      double* xp = xs.data();
+      if (static_cast<double>(nf) * ne < 2.0e5 || nth == 1) {
+         for (int j = ne - 1; j >= 0; --j) {
+            const double* l = L + ld * j;
+            double acc = xp[j];
+            for (int i = j + 1; i < nf; ++i) acc -= l[i] * xp[i];
+            xp[j] = acc;
+         }
+      } else {
+         const int nblk = (ne + SB - 1) / SB;
+         for (int b = nblk - 1; b >= 0; --b) {
+            const int jb = b * SB, je = std::min(jb + SB, ne);
+            double* pp = part.data();
+            // the rows below the block: every thread's share of the je - jb dot products
+#pragma omp parallel for schedule(static)
+            for (int c = 0; c < nth; ++c) {
+               const int64_t rows = nf - je;
+               const int i0 = je + static_cast<int>(rows * c / nth), i1 = je + static_cast<int>(rows * (c + 1) / nth);
+               for (int j = jb; j < je; ++j) {
+                  const double* l = L + ld * j;
+                  double acc = 0.0;
+                  for (int i = i0; i < i1; ++i) acc += l[i] * xp[i];
+                  pp[static_cast<size_t>(c) * SB + (j - jb)] = acc;
+               }
+            }
+            for (int j = je - 1; j >= jb; --j) {
+               const double* l = L + ld * j;
+               double acc = xp[j];
+               for (int c = 0; c < nth; ++c) acc -= pp[static_cast<size_t>(c) * SB + (j - jb)];
+               for (int i = j + 1; i < je; ++i) acc -= l[i] * xp[i];
+               xp[j] = acc;
+            }
+         }
       }
       for (int j = 0; j < ne; ++j) y[F.idx[j]] = xs[j];
    }
