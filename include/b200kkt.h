@@ -71,6 +71,9 @@ typedef struct b200kkt_stats {
    int64_t num_delayed_total, num_replans_total, num_replans_last;
    /* componentwise backward error of the last solve: max_i |b - K x|_i / (|K| |x| + |b|)_i (Oettli-Prager; MUMPS' omega_1) */
    double backward_error_componentwise_last;
+   /* device storage in doubles.  pool_doubles (above) and cb_arena_doubles are what THIS rank allocates; with num_parts > 1 and the
+    * option partition_memory (default 1) that is the fronts it owns plus the shared ones, the *_global figures are the whole system */
+   int64_t cb_arena_doubles, pool_doubles_global, cb_arena_doubles_global;
 } b200kkt_stats;
 
 /* Handle life cycle.  Replaces JOB=-1 / JOB=-2 (MUMPSSolver.cpp:16-49).
@@ -93,7 +96,11 @@ int b200kkt_comm_init(b200kkt_handle* h, int rank, int world, const char id[128]
  * then names the rank that solves with it), the cut fronts (owner differs from the parent's; at most number of fronts entries,
  * *num_cut receives the count), factor flops per rank (length num_gpus), flops on the critical path.
  * Works on host-only handles; any pointer may be NULL.
- * Options: "share_top_fronts" (1), "share_min_pivots" (1024), "share_min_flops" (5e10), "share_chunk_panels" (2). */
+ * Options: "share_top_fronts" (1), "share_min_pivots" (1024), "share_min_flops" (5e10), "share_chunk_panels" (2),
+ * "partition_memory" (1): a rank allocates factor columns only for the fronts it owns and the shared ones, and room in the
+ * contribution-block arena only for the blocks it produces, consumes or helps to broadcast (b200kkt_stats: pool_doubles,
+ * cb_arena_doubles against the *_global figures); 0 = every rank allocates the whole system's pools (round-1 behaviour).
+ * "debug_rank" (host-only handles): the rank whose storage the plan of the next analysis describes. */
 int b200kkt_plan_partition(const b200kkt_handle* h, int32_t* owner, int8_t* shared, int64_t* num_cut, int32_t* cut_fronts,
                            double* part_flops, double* critical_flops);
 

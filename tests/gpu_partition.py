@@ -83,7 +83,9 @@ def main():
                           "factor_ms": 1e3 * stm["t_factor_last"], "solve_ms": 1e3 * stm["t_solve_last"], "factor_ms_1gpu": 1e3 * st1["t_factor_last"],
                           "solve_ms_1gpu": 1e3 * st1["t_solve_last"], "wall_ms": 1e3 * min(times), "comm_MB_factor": stm["comm_bytes_factor"] / 1e6,
                           "owners": np.bincount(part["owner"], minlength=world).tolist(), "shared_fronts": int(part["shared"].sum()),
-                          "speedup_factor": st1["t_factor_last"] / stm["t_factor_last"]})
+                          "speedup_factor": st1["t_factor_last"] / stm["t_factor_last"],
+                          "pool_MB": 8e-6 * st["pool_doubles"], "pool_MB_whole_system": 8e-6 * st["pool_doubles_global"],
+                          "arena_MB": 8e-6 * st["cb_arena_doubles"], "arena_MB_whole_system": 8e-6 * st["cb_arena_doubles_global"]})
         multi.close(); single.close()
     dist.barrier()
     dist.destroy_process_group()

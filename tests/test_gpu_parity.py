@@ -448,3 +448,4 @@ def test_partitioned_two_gpus_matches_single_gpu():
     assert r.returncode == 0, r.stdout[-2000:] + r.stderr[-2000:]
     assert len(lines) == 6 and all(l["ok"] for l in lines)
     assert any(l["shared_fronts"] > 0 for l in lines)        # the shared-front path ran, not only the subtree exchange
+    assert all(l["pool_MB"] < l["pool_MB_whole_system"] for l in lines)      # every rank allocates its own part of the factors only

@@ -97,6 +97,41 @@ def test_shared_top_fronts(lib):
     h.close(); h2.close()
 
 
+@pytest.mark.parametrize("parts", [2, 4])
+def test_storage_is_partitioned_per_rank(lib, parts):
+    """partition_memory (default): a rank's factor pool holds the fronts it owns and the shared ones, back to back in front order;
+    the other fronts have no storage (an offset far outside the pool), and no rank's pool or arena exceeds the whole system's."""
+    from uno_b200 import KKTSolver
+    from uno_b200 import generators as G
+    kkt = G.ocp_distributed(24, 3, seed=0)
+    ref = KKTSolver(device=-1, num_gpus=parts, share_min_pivots=512, share_min_flops=1e8, partition_memory=0)
+    ref.do_symbolic_analysis(kkt.dim, kkt.row, kkt.col, kkt.reg_size, kkt.n)
+    gplan, gst = ref.plan(), ref.stats()
+    assert gst["pool_doubles"] == gst["pool_doubles_global"] and gst["cb_arena_doubles"] == gst["cb_arena_doubles_global"]
+    size = gplan["ld"].astype(np.int64) * gplan["k"]
+    assert gst["pool_doubles"] == size.sum()
+    pools, distinct = [], []
+    for r in range(parts):
+        h = KKTSolver(device=-1, num_gpus=parts, share_min_pivots=512, share_min_flops=1e8, debug_rank=r)
+        h.do_symbolic_analysis(kkt.dim, kkt.row, kkt.col, kkt.reg_size, kkt.n)
+        plan, part, st = h.plan(), h.partition(), h.stats()
+        assert st["part_rank"] == r and np.array_equal(part["owner"], ref.partition()["owner"])
+        held = (part["owner"] == r) | (part["shared"] != 0)
+        off = plan["pool_offset"]
+        assert np.all(off[~held] < 0)
+        expect = np.concatenate([[0], np.cumsum(size[held])])
+        assert np.array_equal(off[held], expect[:-1]) and st["pool_doubles"] == expect[-1]
+        assert st["pool_doubles_global"] == gst["pool_doubles"] and st["cb_arena_doubles_global"] == gst["cb_arena_doubles"]
+        assert 0 < st["pool_doubles"] < gst["pool_doubles"] and 0 < st["cb_arena_doubles"] <= gst["cb_arena_doubles"]
+        assert st["assembly_distinct"] <= gst["assembly_distinct"]
+        pools.append(st["pool_doubles"]); distinct.append(st["assembly_distinct"])
+        h.close()
+    shared_doubles = size[ref.partition()["shared"] != 0].sum()
+    assert sum(pools) == gst["pool_doubles"] + (parts - 1) * shared_doubles       # owned parts are disjoint, shared fronts are on every rank
+    assert sum(distinct) >= gst["assembly_distinct"]
+    ref.close()
+
+
 def test_map_is_deterministic(lib):
     from uno_b200 import KKTSolver
     kkt = _systems()["ocp3d_12"]
@@ -163,7 +198,7 @@ def _worker(rank, world, port, out):
     res = {"rank": rank, "uid_ok": uid == bytes(range(128))}
     k = 8 if world == 2 else 12
     for name, kkt in (("ocp3d", G.ocp_distributed(k, 3, seed=1)), ("bnd3d", G.ocp_boundary_3d(k, seed=2))):
-        host = KKTSolver(device=-1, num_gpus=world)
+        host = KKTSolver(device=-1, num_gpus=world, partition_memory=0)      # the emulation keeps the whole system's pool on every rank
         host.do_symbolic_analysis(kkt.dim, kkt.row, kkt.col, kkt.reg_size, kkt.n)
         plan, part = host.plan(), host.partition()
         perm, scatter = host.permutation()
@@ -190,7 +225,7 @@ def _worker_shared(rank, world, port, out):
     from uno_b200 import KKTSolver
     from uno_b200 import generators as G
     kkt = G.ocp_boundary_3d(26, seed=4)     # shared fronts (2001, 649) - contribution block, 649 is no multiple of the panel width - and the root
-    host = KKTSolver(device=-1, num_gpus=world, share_min_pivots=512, share_min_flops=1e8)
+    host = KKTSolver(device=-1, num_gpus=world, share_min_pivots=512, share_min_flops=1e8, partition_memory=0)
     host.do_symbolic_analysis(kkt.dim, kkt.row, kkt.col, kkt.reg_size, kkt.n)
     plan, part = host.plan(), host.partition()
     perm, scatter = host.permutation()

@@ -51,6 +51,7 @@ class Stats(C.Structure):
         ("t_before_shared_profiled", C.c_double), ("t_transfer_wait_profiled", C.c_double),
         ("num_delayed_total", C.c_int64), ("num_replans_total", C.c_int64), ("num_replans_last", C.c_int64),
         ("backward_error_componentwise_last", C.c_double),
+        ("cb_arena_doubles", C.c_int64), ("pool_doubles_global", C.c_int64), ("cb_arena_doubles_global", C.c_int64),
     ]
 
     def as_dict(self):

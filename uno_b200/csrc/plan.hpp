@@ -60,6 +60,7 @@ struct Plan {
 
    int64_t pool_size = 0;           // factor pool, doubles: sum ld*k
    int64_t cb_pool_size = 0;        // contribution-block arena, doubles (peak of the level-order schedule)
+   int64_t pool_size_global = 0, cb_pool_size_global = 0;   // the same for the whole system, before localize_storage
 
    // Assembly ("assembly permutation"): COO slot -> pool offset, and the same map grouped by
    // destination so that duplicates are summed in ascending slot order without atomics.
@@ -121,5 +122,6 @@ void delay_columns(Plan& plan, const std::vector<int32_t>& cols, const std::vect
 // until the open subtrees can be packed evenly, the subtrees are packed by decreasing flop count (LPT), and every front above
 // the cut goes to the owner of its heaviest child.  Deterministic: every rank computes the same map from the same plan.
 void map_subtrees(Plan& plan, int parts, bool share_top_fronts = true);
+void localize_storage(Plan& plan, int rank);
 
 }  // namespace b200kkt

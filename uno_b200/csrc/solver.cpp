@@ -663,6 +663,7 @@ void fill_plan_stats(b200kkt_handle* h) {
    s.num_fronts = P.nsn; s.num_levels = P.nlevels; s.max_front = P.max_f; s.max_pivots = P.max_k;
    s.num_pairs = P.num_pairs;
    s.nnz_factor = P.nnz_L; s.pool_doubles = P.pool_size;
+   s.cb_arena_doubles = P.cb_pool_size; s.pool_doubles_global = P.pool_size_global; s.cb_arena_doubles_global = P.cb_pool_size_global;
    s.assembly_distinct = static_cast<int64_t>(P.asm_dst.size());
    s.flops_factor = P.flops; s.flops_tensor = P.flops_tc;
    s.t_ordering = P.t_order; s.t_symbolic = P.t_symbolic; s.t_maps = P.t_maps;
@@ -958,6 +959,7 @@ void replan_with_delays(b200kkt_handle* h, const std::vector<int32_t>& cols) {
    P.share_min_pivots = h->share_min_pivots;
    P.share_min_flops = h->share_min_flops;
    map_subtrees(P, h->num_gpus, h->share_top_fronts != 0);
+   if (h->partitioned() && h->partition_memory) localize_storage(P, h->rank);
    const bool resident = h->values_resident;
    if (h->has_device) {
       CK(cudaStreamSynchronize(h->stream));
@@ -1341,6 +1343,11 @@ int b200kkt_set_option(b200kkt_handle* h, const char* name, double value) {
    else if (n == "pair_min_front") h->pair_min_front = static_cast<int>(value);
    else if (n == "partition_graph") h->partition_graph = static_cast<int>(value);
    else if (n == "share_trim_rows") h->share_trim_rows = static_cast<int>(value);
+   else if (n == "partition_memory") h->partition_memory = static_cast<int>(value);
+   else if (n == "debug_rank") {   // host-only handles (plan inspection in the CPU tests): the rank whose storage the plan describes
+      if (h->has_device) return fail(h, B200KKT_EINVAL, "debug_rank: only for host-only handles (a device handle gets its rank from comm_init)");
+      h->rank = std::max(0, std::min(h->num_gpus - 1, static_cast<int>(value)));
+   }
    else if (n == "share_one_launch") h->share_one_launch = static_cast<int>(value);
    else if (n == "share_top_fronts") h->share_top_fronts = static_cast<int>(value);
    else if (n == "share_chunk_panels") h->share_chunk_panels = std::max(1, static_cast<int>(value));
@@ -1390,6 +1397,7 @@ int b200kkt_analyse(b200kkt_handle* h, uint64_t n, uint64_t nnz, uint64_t reg_si
       h->plan.share_min_pivots = h->share_min_pivots;
       h->plan.share_min_flops = h->share_min_flops;
       map_subtrees(h->plan, h->num_gpus, h->share_top_fronts != 0);
+      if (h->partitioned() && h->partition_memory) localize_storage(h->plan, h->rank);
       fill_plan_stats(h);
       if (h->has_device) upload_plan(h);
       h->analysed = true;

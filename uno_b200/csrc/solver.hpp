@@ -167,6 +167,7 @@ struct b200kkt_handle {
    cudaEvent_t ev_level_done = nullptr;
    int partition_graph = 0;               // experimental, off: capture the partitioned factorization / solve sweep (NCCL calls included) in CUDA graphs
    int share_one_launch = 1;              // a rank updates all its column chunks of one step in one K4 launch (8 GPUs, 128^3: 1.407 -> 1.359 s with both)
+   int partition_memory = 1;              // multi-GPU: a rank allocates the factor pool and the contribution-block arena for its own and the shared fronts only
    int share_trim_rows = 1;               // broadcast only the rows of a factored panel at and below its diagonal block
    int share_top_fronts = 1;              // big fronts above the cut are factorized by all ranks together
    int share_chunk_panels = 2;            // column chunk of a shared front, in outer panels; chunk c belongs to rank c mod num_gpus

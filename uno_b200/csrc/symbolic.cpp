@@ -180,8 +180,9 @@ void build_level_lists(Plan& P) {
    }
 }
 
-// offsets of the contribution blocks in the transient arena (P.level_ptr / P.level_fronts given)
-void build_cb_arena(Plan& P) {
+// offsets of the contribution blocks in the transient arena (P.level_ptr / P.level_fronts given); `keep` (optional) marks the
+// fronts whose block this rank ever holds - the others get no room
+void build_cb_arena(Plan& P, const std::vector<char>* keep = nullptr) {
    const int32_t nsn = P.nsn;
    // ---- contribution-block arena: first-fit over the level-order schedule ------------------------
    // A block lives from the level of its front until the level of its parent (where it is consumed by
@@ -229,14 +230,14 @@ void build_cb_arena(Plan& P) {
       for (int32_t l = 0; l < P.nlevels; ++l) {
          for (int32_t t = P.level_ptr[l]; t < P.level_ptr[l + 1]; ++t) {
             const int32_t s = P.level_fronts[t];
-            const int64_t sz = cb_size(s);
+            const int64_t sz = (keep == nullptr || (*keep)[s]) ? cb_size(s) : 0;
             if (sz > 0) P.cb_off[s] = alloc(sz);
          }
          for (int32_t t = P.level_ptr[l]; t < P.level_ptr[l + 1]; ++t) {
             const int32_t s = P.level_fronts[t];
             for (int32_t ci = P.child_ptr[s]; ci < P.child_ptr[s + 1]; ++ci) {
                const int32_t c = P.child_idx[ci];
-               const int64_t sz = cb_size(c);
+               const int64_t sz = (keep == nullptr || (*keep)[c]) ? cb_size(c) : 0;
                if (sz > 0) release(P.cb_off[c], sz);
             }
          }
@@ -706,7 +707,9 @@ void build_structures(Plan& P) {
       P.max_k = std::max(P.max_k, P.k[s]);
    }
    P.pool_size = off;
+   P.pool_size_global = off;
    build_cb_arena(P);
+   P.cb_pool_size_global = P.cb_pool_size;
    const auto t2 = clk::now();
    P.t_symbolic = secs(t1, t2);
 
@@ -938,6 +941,58 @@ void map_subtrees(Plan& P, int parts, bool share_top_fronts) {
    std::stable_sort(P.cut_edges.begin(), P.cut_edges.end(), [&](int32_t a, int32_t b) {
       return P.level[a] != P.level[b] ? P.level[a] < P.level[b] : a < b;
    });
+}
+
+// Per-rank storage of a partitioned run (after map_subtrees).  A rank stores the factor columns of the fronts it owns and of
+// the shared fronts (every rank keeps those: it applies them in the solves), and holds a contribution block only if it
+// produces it, consumes it (parent owned here) or takes part in its broadcast (front or parent shared).  The factor pool is
+// compacted over the stored fronts - their order is kept, so the assembly destinations stay ascending - and the scatter map
+// loses the entries of the other fronts.  A front without storage gets an offset far outside the pool: touching it faults.
+void localize_storage(Plan& P, int rank) {
+   const int32_t nsn = P.nsn;
+   if (P.num_parts <= 1 || nsn == 0) return;
+   std::vector<char> hold(static_cast<size_t>(nsn)), cbkeep(static_cast<size_t>(nsn));
+   for (int32_t s = 0; s < nsn; ++s) {
+      hold[s] = (P.owner[s] == rank || P.shared[s]) ? 1 : 0;
+      const int32_t p = P.parent[s];
+      cbkeep[s] = (hold[s] || (p >= 0 && (P.shared[p] || P.owner[p] == rank))) ? 1 : 0;
+   }
+   const std::vector<int64_t> old_off = P.front_off;
+   constexpr int64_t NO_STORAGE = -(int64_t(1) << 45);
+   int64_t off = 0;
+   for (int32_t s = 0; s < nsn; ++s) {
+      if (!hold[s]) { P.front_off[s] = NO_STORAGE; continue; }
+      P.front_off[s] = off;
+      off += static_cast<int64_t>(P.ld[s]) * P.k[s];
+   }
+   P.pool_size = off;
+   // assembly map: segments of the fronts stored here, re-based
+   {
+      std::vector<int64_t> dst;
+      std::vector<int32_t> seg, src, arow, acol;
+      const size_t nd = P.asm_dst.size();
+      int32_t s = 0;
+      for (size_t d = 0; d < nd; ++d) {
+         const int64_t o = P.asm_dst[d];
+         while (s + 1 < nsn && old_off[s + 1] <= o) ++s;          // destinations ascend; empty fronts share an offset with their successor
+         if (!hold[s]) continue;
+         dst.push_back(o - old_off[s] + P.front_off[s]);
+         seg.push_back(static_cast<int32_t>(src.size()));
+         for (int32_t t = P.asm_seg[d]; t < P.asm_seg[d + 1]; ++t) {
+            src.push_back(P.asm_src[t]);
+            arow.push_back(P.asm_row[t]);
+            acol.push_back(P.asm_col[t]);
+         }
+      }
+      seg.push_back(static_cast<int32_t>(src.size()));
+      P.asm_dst.swap(dst); P.asm_seg.swap(seg); P.asm_src.swap(src); P.asm_row.swap(arow); P.asm_col.swap(acol);
+      for (int64_t e = 0; e < P.nnz; ++e) {     // the per-entry view of the same map (b200kkt_get_permutation)
+         const int32_t fs = P.sn_of[std::min(P.iperm[P.coo_row[e]], P.iperm[P.coo_col[e]])];
+         P.scatter[e] = hold[fs] ? P.scatter[e] - old_off[fs] + P.front_off[fs] : -1;
+      }
+   }
+   P.cb_pool_size_global = P.cb_pool_size;   // map_subtrees may have re-levelled the shared fronts
+   build_cb_arena(P, &cbkeep);
 }
 
 }  // namespace b200kkt
