@@ -31,6 +31,10 @@ struct AnalyseOptions {
    const double* pair_values = nullptr;
    // METIS_NodeND tuning (0 = METIS default): separators tried per bisection, refinement iterations, allowed imbalance (1/1000)
    int metis_nseps = 0, metis_niter = 0, metis_ufactor = 0;
+   // graphs of at least parallel_ordering_min_nodes (compressed) nodes: the top parallel_ordering_depth levels of the nested
+   // dissection are split here and their halves ordered by parallel processes (2^depth of them at the bottom); 0 = METIS_NodeND alone
+   int parallel_ordering_depth = 3;
+   int64_t parallel_ordering_min_nodes = 150000;
 };
 
 struct Plan {

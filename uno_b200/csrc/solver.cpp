@@ -1318,6 +1318,8 @@ int b200kkt_set_option(b200kkt_handle* h, const char* name, double value) {
    else if (n == "metis_nseps") h->aopt.metis_nseps = static_cast<int>(value);
    else if (n == "metis_niter") h->aopt.metis_niter = static_cast<int>(value);
    else if (n == "metis_ufactor") h->aopt.metis_ufactor = static_cast<int>(value);
+   else if (n == "parallel_ordering_depth") h->aopt.parallel_ordering_depth = std::max(0, std::min(6, static_cast<int>(value)));
+   else if (n == "parallel_ordering_min_nodes") h->aopt.parallel_ordering_min_nodes = static_cast<int64_t>(value);
    else if (n == "scaling_sweeps") h->scaling_sweeps = std::max(0, static_cast<int>(value));
    else if (n == "null_pivot_tol") h->null_pivot_tol = value;
    else if (n == "delay_tol") h->delay_tol = value;

@@ -16,16 +16,26 @@
 #include <algorithm>
 #include <chrono>
 #include <cmath>
+#include <cstdio>
+#include <cstdlib>
+#include <cerrno>
 #include <cstring>
+#include <limits>
 #include <map>
+#include <set>
 #include <numeric>
 #include <stdexcept>
+#include <sys/types.h>
+#include <sys/wait.h>
+#include <unistd.h>
 
 extern "C" {
 // CUDA ships libmetis_static.a (METIS 5.x, 64-bit idx_t) without a header.
 int METIS_NodeND(int64_t* nvtxs, int64_t* xadj, int64_t* adjncy, int64_t* vwgt, int64_t* options,
                  int64_t* perm, int64_t* iperm);
 int METIS_SetDefaultOptions(int64_t* options);
+int METIS_ComputeVertexSeparator(int64_t* nvtxs, int64_t* xadj, int64_t* adjncy, int64_t* vwgt, int64_t* options, int64_t* sepsize,
+                                 int64_t* part);
 }
 
 namespace b200kkt {
@@ -162,6 +172,138 @@ void kkt_pairing(int64_t N, const Graph& g, const std::vector<char>& is_con, std
 }  // namespace
 
 // fronts grouped by level (P.level given), big fronts first inside a level
+// ------------------------------------------------------------------------------------------------
+// Nested dissection with the top levels of the recursion done here, the halves of every split side by side.
+// METIS keeps process-wide state (its random number generator), so concurrent calls from threads would make the ordering
+// depend on the interleaving - and every rank of a partitioned run must compute the SAME ordering.  The halves therefore run
+// in forked PROCESSES: each has a private copy of that state, the result is a function of the graph alone.  A child only runs
+// METIS on host memory and writes its answer to a pipe; it never touches the CUDA context it inherited and leaves with _exit.
+// ------------------------------------------------------------------------------------------------
+struct NdGraph {
+   std::vector<int64_t> xadj, adjncy, vwgt;
+   std::vector<int64_t> ids;   // node of the top-level graph behind each local node
+};
+
+bool nd_serial(NdGraph& G, const std::vector<int64_t>& options, std::vector<int64_t>& order) {
+   int64_t n = static_cast<int64_t>(G.ids.size());
+   order.resize(static_cast<size_t>(n));
+   if (n == 0) return true;
+   if (n < 3 || G.adjncy.empty()) { order = G.ids; return true; }
+   std::vector<int64_t> perm(static_cast<size_t>(n)), iperm(static_cast<size_t>(n)), opts(options);
+   if (METIS_NodeND(&n, G.xadj.data(), G.adjncy.data(), G.vwgt.data(), opts.data(), perm.data(), iperm.data()) != 1) return false;
+   for (int64_t i = 0; i < n; ++i) order[static_cast<size_t>(i)] = G.ids[static_cast<size_t>(perm[static_cast<size_t>(i)])];
+   return true;
+}
+
+void nd_induce(const NdGraph& G, const std::vector<int64_t>& part, int64_t which, NdGraph& out) {
+   const int64_t n = static_cast<int64_t>(G.ids.size());
+   std::vector<int64_t> local(static_cast<size_t>(n), -1);
+   int64_t m = 0;
+   for (int64_t v = 0; v < n; ++v) if (part[static_cast<size_t>(v)] == which) local[static_cast<size_t>(v)] = m++;
+   out.xadj.assign(static_cast<size_t>(m) + 1, 0);
+   out.vwgt.resize(static_cast<size_t>(m));
+   out.ids.resize(static_cast<size_t>(m));
+   out.adjncy.clear();
+   for (int64_t v = 0; v < n; ++v) {
+      const int64_t lv = local[static_cast<size_t>(v)];
+      if (lv < 0) continue;
+      out.vwgt[static_cast<size_t>(lv)] = G.vwgt[static_cast<size_t>(v)];
+      out.ids[static_cast<size_t>(lv)] = G.ids[static_cast<size_t>(v)];
+      for (int64_t p = G.xadj[static_cast<size_t>(v)]; p < G.xadj[static_cast<size_t>(v) + 1]; ++p) {
+         const int64_t lw = local[static_cast<size_t>(G.adjncy[static_cast<size_t>(p)])];
+         if (lw >= 0) out.adjncy.push_back(lw);
+      }
+      out.xadj[static_cast<size_t>(lv) + 1] = static_cast<int64_t>(out.adjncy.size());
+   }
+}
+
+bool write_all(int fd, const void* buf, size_t bytes) {
+   const char* p = static_cast<const char*>(buf);
+   while (bytes > 0) {
+      const ssize_t w = ::write(fd, p, bytes);
+      if (w < 0) { if (errno == EINTR) continue; return false; }
+      p += w; bytes -= static_cast<size_t>(w);
+   }
+   return true;
+}
+
+bool read_all(int fd, void* buf, size_t bytes) {
+   char* p = static_cast<char*>(buf);
+   while (bytes > 0) {
+      const ssize_t r = ::read(fd, p, bytes);
+      if (r < 0) { if (errno == EINTR) continue; return false; }
+      if (r == 0) return false;
+      p += r; bytes -= static_cast<size_t>(r);
+   }
+   return true;
+}
+
+// elimination order of G (top-level node ids): separator last, the two sides before it, `depth` levels of splits done here
+bool nd_process_parallel(NdGraph& G, int depth, const std::vector<int64_t>& options, std::vector<int64_t>& order) {
+   int64_t n = static_cast<int64_t>(G.ids.size());
+   if (depth <= 0 || n < 20000) return nd_serial(G, options, order);
+   std::vector<int64_t> part(static_cast<size_t>(n)), opts(options);
+   int64_t sepsize = 0;
+   if (METIS_ComputeVertexSeparator(&n, G.xadj.data(), G.adjncy.data(), G.vwgt.data(), opts.data(), &sepsize, part.data()) != 1) return false;
+   NdGraph A, B;
+   nd_induce(G, part, 0, A);
+   nd_induce(G, part, 1, B);
+   std::vector<int64_t> sep;
+   for (int64_t v = 0; v < n; ++v) if (part[static_cast<size_t>(v)] == 2) sep.push_back(G.ids[static_cast<size_t>(v)]);
+   if (A.ids.empty() || B.ids.empty()) return nd_serial(G, options, order);   // no real split: leave it to METIS
+   { NdGraph empty; std::swap(G.xadj, empty.xadj); std::swap(G.adjncy, empty.adjncy); std::swap(G.vwgt, empty.vwgt); }   // the halves carry on
+   std::vector<int64_t> order_a, order_b;
+   int fds[2];
+   pid_t child = -1;
+   if (::pipe(fds) == 0) {
+      child = ::fork();
+      if (child == 0) {
+         ::close(fds[0]);
+         std::vector<int64_t> mine;
+         const bool ok = nd_process_parallel(A, depth - 1, options, mine) && mine.size() == A.ids.size();
+         const int64_t head = ok ? static_cast<int64_t>(mine.size()) : -1;
+         const bool sent = write_all(fds[1], &head, sizeof head) && (!ok || write_all(fds[1], mine.data(), mine.size() * sizeof(int64_t)));
+         ::close(fds[1]);
+         ::_exit(sent && ok ? 0 : 1);
+      }
+      if (child < 0) { ::close(fds[0]); ::close(fds[1]); }
+   }
+   bool ok_b = nd_process_parallel(B, depth - 1, options, order_b);
+   bool ok_a = false;
+   if (child > 0) {
+      ::close(fds[1]);
+      int64_t head = -1;
+      if (read_all(fds[0], &head, sizeof head) && head == static_cast<int64_t>(A.ids.size())) {
+         order_a.resize(static_cast<size_t>(head));
+         ok_a = read_all(fds[0], order_a.data(), order_a.size() * sizeof(int64_t));
+      }
+      ::close(fds[0]);
+      int status = 0;
+      while (::waitpid(child, &status, 0) < 0 && errno == EINTR) {}
+      ok_a = ok_a && WIFEXITED(status) && WEXITSTATUS(status) == 0;
+   }
+   if (!ok_a) ok_a = nd_process_parallel(A, 0, options, order_a);   // no child (or it failed): this process does that half too
+   if (!ok_a || !ok_b) return false;
+   order.clear();
+   order.reserve(static_cast<size_t>(n));
+   order.insert(order.end(), order_a.begin(), order_a.end());
+   order.insert(order.end(), order_b.begin(), order_b.end());
+   order.insert(order.end(), sep.begin(), sep.end());
+   return true;
+}
+
+// B200KKT_TRACE_ANALYSE=1: wall clock of the sections of the symbolic phase on stderr
+struct Trace {
+   bool on = std::getenv("B200KKT_TRACE_ANALYSE") != nullptr;
+   clk::time_point t = clk::now();
+   void mark(const char* what) {
+      if (!on) return;
+      const auto n = clk::now();
+      std::fprintf(stderr, "[b200kkt analyse] %-28s %8.3f s\n", what, secs(t, n));
+      t = n;
+   }
+};
+
 void build_level_lists(Plan& P) {
    const int32_t nsn = P.nsn;
    P.nlevels = 0;
@@ -184,32 +326,43 @@ void build_level_lists(Plan& P) {
 // fronts whose block this rank ever holds - the others get no room
 void build_cb_arena(Plan& P, const std::vector<char>* keep = nullptr) {
    const int32_t nsn = P.nsn;
-   // ---- contribution-block arena: first-fit over the level-order schedule ------------------------
+   // ---- contribution-block arena: best fit over the level-order schedule -------------------------
    // A block lives from the level of its front until the level of its parent (where it is consumed by
    // the extend-add); the numeric phase runs level by level, so the offsets can be fixed here.
    {
       P.cb_off.assign(nsn, 0);
-      std::map<int64_t, int64_t> free_list;   // offset -> size, coalesced
+      // free blocks, coalesced: by offset (to merge neighbours) and by size (best fit in O(log n): the level-order schedule
+      // frees and takes hundreds of thousands of small blocks, a first-fit walk over the list was most of the analysis time)
+      std::map<int64_t, int64_t> free_list;                    // offset -> size
+      std::set<std::pair<int64_t, int64_t>> by_size;           // (size, offset): the smallest block that fits, lowest address first
       int64_t top = 0;
       auto cb_size = [&](int32_t s) {
          const int64_t r = P.f[s] - P.k[s];
          return (r * (r + 1) / 2 + 1) & ~int64_t(1);   // packed lower triangle, even number of doubles
       };
+      auto drop = [&](std::map<int64_t, int64_t>::iterator it) {
+         by_size.erase({it->second, it->first});
+         free_list.erase(it);
+      };
+      auto add = [&](int64_t o, int64_t size) {
+         free_list.emplace(o, size);
+         by_size.emplace(size, o);   // (size, offset)
+      };
       auto alloc = [&](int64_t size) {
-         for (auto it = free_list.begin(); it != free_list.end(); ++it) {
-            if (it->second >= size) {
-               const int64_t o = it->first, rest = it->second - size;
-               free_list.erase(it);
-               if (rest > 0) free_list.emplace(o + size, rest);
-               return o;
-            }
+         auto fit = by_size.lower_bound({size, std::numeric_limits<int64_t>::min()});
+         if (fit != by_size.end()) {
+            const int64_t o = fit->second, rest = fit->first - size;
+            by_size.erase(fit);
+            free_list.erase(o);
+            if (rest > 0) add(o + size, rest);
+            return o;
          }
          // grow: extend a free block that touches the top, if any
          if (!free_list.empty()) {
             auto last = std::prev(free_list.end());
             if (last->first + last->second == top) {
                const int64_t o = last->first;
-               free_list.erase(last);
+               drop(last);
                top = o + size;
                return o;
             }
@@ -219,13 +372,14 @@ void build_cb_arena(Plan& P, const std::vector<char>* keep = nullptr) {
          return o;
       };
       auto release = [&](int64_t o, int64_t size) {
-         auto it = free_list.emplace(o, size).first;
-         auto nx = std::next(it);
-         if (nx != free_list.end() && it->first + it->second == nx->first) { it->second += nx->second; free_list.erase(nx); }
-         if (it != free_list.begin()) {
-            auto pv = std::prev(it);
-            if (pv->first + pv->second == it->first) { pv->second += it->second; free_list.erase(it); }
+         auto nx = free_list.lower_bound(o);
+         if (nx != free_list.end() && o + size == nx->first) { size += nx->second; drop(nx); }
+         auto pv = free_list.lower_bound(o);
+         if (pv != free_list.begin()) {
+            --pv;
+            if (pv->first + pv->second == o) { o = pv->first; size += pv->second; drop(pv); }
          }
+         add(o, size);
       };
       for (int32_t l = 0; l < P.nlevels; ++l) {
          for (int32_t t = P.level_ptr[l]; t < P.level_ptr[l + 1]; ++t) {
@@ -257,7 +411,9 @@ void analyse(int64_t N, int64_t nnz, int64_t reg_size, int64_t num_primal, const
    P.num_primal = num_primal;
    const auto t0 = clk::now();
 
+   Trace tro;
    Graph g = build_adjacency(N, nnz, row, col);
+   tro.mark("adjacency");
 
    // ---- constraint-like nodes and KKT pairing --------------------------------------------------
    std::vector<char> is_con(static_cast<size_t>(N), 0);
@@ -305,6 +461,7 @@ void analyse(int64_t N, int64_t nnz, int64_t reg_size, int64_t num_primal, const
       }
    }
    if (opt.kkt_pairing && any_con) kkt_pairing(N, g, is_con, partner, wgt);
+   tro.mark("KKT pairing");
    for (int64_t i = 0; i < N; ++i) if (is_con[i] && partner[i] != -1) ++P.num_pairs;
 
    // ---- fill-reducing ordering on the pair-compressed graph -----------------------------------
@@ -387,8 +544,28 @@ void analyse(int64_t N, int64_t nnz, int64_t reg_size, int64_t num_primal, const
          if (opt.metis_nseps > 0) options[15] = opt.metis_nseps;
          if (opt.metis_ufactor > 0) options[16] = opt.metis_ufactor;
          int64_t n = cN;
-         const int rc = METIS_NodeND(&n, xadj.data(), adjncy.data(), vwgt.data(), options.data(), mperm.data(), miperm.data());
-         if (rc == 1) { corder = mperm; P.ordering_used = "metis_nodend"; }
+         tro.mark("compressed graph");
+         bool done = false;
+         if (opt.parallel_ordering_depth > 0 && cN >= opt.parallel_ordering_min_nodes) {
+            // big graphs: the top levels of the dissection here, their halves in parallel processes (same ordering on every run)
+            NdGraph G;
+            G.xadj = xadj; G.adjncy = adjncy; G.vwgt = vwgt;
+            G.ids.resize(static_cast<size_t>(cN));
+            std::iota(G.ids.begin(), G.ids.end(), 0);
+            std::vector<int64_t> ord;
+            if (nd_process_parallel(G, opt.parallel_ordering_depth, options, ord) && static_cast<int64_t>(ord.size()) == cN) {
+               std::vector<char> seen(static_cast<size_t>(cN), 0);
+               bool valid = true;
+               for (const int64_t v : ord) { if (v < 0 || v >= cN || seen[static_cast<size_t>(v)]) { valid = false; break; } seen[static_cast<size_t>(v)] = 1; }
+               if (valid) { corder = ord; P.ordering_used = "metis_nested_dissection_process_parallel"; done = true; }
+            }
+            tro.mark("nested dissection (parallel)");
+         }
+         if (!done) {
+            const int rc = METIS_NodeND(&n, xadj.data(), adjncy.data(), vwgt.data(), options.data(), mperm.data(), miperm.data());
+            tro.mark("METIS_NodeND");
+            if (rc == 1) { corder = mperm; P.ordering_used = "metis_nodend"; }
+         }
       }
    }
    // expand: primal first, then its matched constraint
@@ -405,6 +582,9 @@ void analyse(int64_t N, int64_t nnz, int64_t reg_size, int64_t num_primal, const
    }
    const auto t1 = clk::now();
    P.t_order = secs(t0, t1);
+   Trace tra;
+   tra.t = t0;
+   tra.mark("pairing + ordering");
 
    // ---- elimination tree (Liu) ----------------------------------------------------------------
    std::vector<int32_t> parent(static_cast<size_t>(N), -1);
@@ -423,6 +603,7 @@ void analyse(int64_t N, int64_t nnz, int64_t reg_size, int64_t num_primal, const
          }
       }
    }
+   tra.mark("elimination tree");
    // ---- postorder and relabel -----------------------------------------------------------------
    {
       std::vector<int32_t> head(static_cast<size_t>(N), -1), next(static_cast<size_t>(N), -1), post(static_cast<size_t>(N));
@@ -455,6 +636,7 @@ void analyse(int64_t N, int64_t nnz, int64_t reg_size, int64_t num_primal, const
       parent.swap(parent2);
       for (int64_t i = 0; i < N; ++i) ipos[order[i]] = static_cast<int32_t>(i);
    }
+   tra.mark("postorder");
    // ---- column counts (Gilbert-Ng-Peyton, postordered so post = identity) ----------------------
    std::vector<int32_t> colcount(static_cast<size_t>(N), 0);
    {
@@ -487,6 +669,7 @@ void analyse(int64_t N, int64_t nnz, int64_t reg_size, int64_t num_primal, const
       }
       for (int64_t j = 0; j < N; ++j) if (parent[j] != -1) colcount[parent[j]] += colcount[j];
    }
+   tra.mark("column counts");
    // ---- fundamental supernodes ----------------------------------------------------------------
    std::vector<int32_t> sfirst0;   // first column of each fundamental supernode
    {
@@ -552,6 +735,7 @@ void analyse(int64_t N, int64_t nnz, int64_t reg_size, int64_t num_primal, const
          }
       }
    }
+   tra.mark("supernodes, amalgamation");
    // ---- final numbering: postorder of the merged tree, pairs first inside each supernode -------
    std::vector<int32_t> rep(static_cast<size_t>(ns0));
    for (int32_t s = ns0 - 1; s >= 0; --s) rep[s] = (merged_into[s] == -1) ? s : rep[merged_into[s]];
@@ -596,6 +780,7 @@ void analyse(int64_t N, int64_t nnz, int64_t reg_size, int64_t num_primal, const
    P.coo_row.resize(static_cast<size_t>(nnz));
    P.coo_col.resize(static_cast<size_t>(nnz));
    for (int64_t e = 0; e < nnz; ++e) { P.coo_row[e] = static_cast<int32_t>(row[e]); P.coo_col[e] = static_cast<int32_t>(col[e]); }
+   tra.mark("final numbering");
    build_structures(P);
    P.t_symbolic = secs(t1, clk::now()) - P.t_maps;   // etree, supernodes and front structures; the maps are timed apart
 }
@@ -659,6 +844,9 @@ void build_structures(Plan& P) {
       P.child_idx.resize(static_cast<size_t>(P.child_ptr[nsn]));
       for (int32_t s = 0; s < nsn; ++s) std::copy(kids[s].begin(), kids[s].end(), P.child_idx.begin() + P.child_ptr[s]);
    }
+   Trace tr;
+   tr.t = t1;
+   tr.mark("front row structures");
    // ---- extend-add maps -------------------------------------------------------------------------
    P.rel_off.assign(static_cast<size_t>(nsn) + 1, 0);
    for (int32_t s = 0; s < nsn; ++s) P.rel_off[s + 1] = P.rel_off[s] + (P.f[s] - P.k[s]);
@@ -682,6 +870,7 @@ void build_structures(Plan& P) {
          P.relmap[P.rel_off[s] + i] = loc;
       }
    }
+   tr.mark("extend-add maps");
    // ---- level schedule ------------------------------------------------------------------------
    P.level.assign(nsn, 0);
    for (int32_t s = 0; s < nsn; ++s) {
@@ -708,13 +897,16 @@ void build_structures(Plan& P) {
    }
    P.pool_size = off;
    P.pool_size_global = off;
+   tr.mark("levels, pool layout");
    build_cb_arena(P);
+   tr.mark("contribution-block arena");
    P.cb_pool_size_global = P.cb_pool_size;
    const auto t2 = clk::now();
    P.t_symbolic = secs(t1, t2);
 
    // ---- assembly scatter map --------------------------------------------------------------------
    P.scatter.resize(static_cast<size_t>(nnz));
+   std::vector<int32_t> front_count(static_cast<size_t>(nsn) + 1, 0);
    for (int64_t e = 0; e < nnz; ++e) {
       const int32_t pr = P.iperm[row[e]], pc = P.iperm[col[e]];
       const int32_t lo = std::min(pr, pc), hi = std::max(pr, pc);
@@ -730,14 +922,20 @@ void build_structures(Plan& P) {
          lrow = P.k[s] + static_cast<int32_t>(it - pb);
       }
       P.scatter[e] = P.front_off[s] + static_cast<int64_t>(lo - P.sn_first[s]) * P.ld[s] + lrow;
+      ++front_count[static_cast<size_t>(s) + 1];
    }
    {
+      // entries by destination, ties by slot: the destinations of a front are one range of the pool, so the entries are first
+      // dealt to their fronts (in slot order), then ordered inside each front - short sorts that stay in cache
       std::vector<int32_t> idx(static_cast<size_t>(nnz));
-      std::iota(idx.begin(), idx.end(), 0);
-      std::sort(idx.begin(), idx.end(), [&](int32_t a, int32_t b) {
-         if (P.scatter[a] != P.scatter[b]) return P.scatter[a] < P.scatter[b];
-         return a < b;
-      });
+      for (int32_t s = 0; s < nsn; ++s) front_count[static_cast<size_t>(s) + 1] += front_count[s];
+      {
+         std::vector<int32_t> fillp(front_count.begin(), front_count.end() - 1);
+         for (int64_t e = 0; e < nnz; ++e) idx[static_cast<size_t>(fillp[P.sn_of[std::min(P.iperm[row[e]], P.iperm[col[e]])]]++)] = static_cast<int32_t>(e);
+      }
+      for (int32_t s = 0; s < nsn; ++s)
+         std::stable_sort(idx.begin() + front_count[s], idx.begin() + front_count[static_cast<size_t>(s) + 1],
+                          [&](int32_t a, int32_t b) { return P.scatter[a] < P.scatter[b]; });
       P.asm_src = idx;
       P.asm_row.resize(static_cast<size_t>(nnz));
       P.asm_col.resize(static_cast<size_t>(nnz));
@@ -772,6 +970,7 @@ void build_structures(Plan& P) {
       }
    }
    P.t_maps = secs(t2, clk::now());
+   tr.mark("scatter map, CSR");
 }
 
 // Delayed pivots.  Column cols[i] (a position in the current numbering) leaves its front and becomes the LAST pivot of the
