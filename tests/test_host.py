@@ -159,3 +159,24 @@ def test_stats_struct_layout_matches_header():
     names = re.findall(r"\b([a-z_0-9]+)\s*[,;]", re.sub(r"/\*.*?\*/", "", body, flags=re.S))
     assert names == [n for n, _ in capi.Stats._fields_]
     assert ctypes.sizeof(capi.Stats) == 8 * len(names)
+
+
+def test_process_parallel_ordering_is_a_deterministic_permutation_of_serial_quality(lib):
+    """Big graphs: the top levels of the nested dissection are split by the library and their halves ordered by forked processes
+    (METIS has process-wide state, so threads would make the ordering depend on the interleaving).  The result must be a
+    permutation, the same on every run - every rank of a partitioned run computes it on its own - and as good as METIS_NodeND's."""
+    from uno_b200 import KKTSolver
+    from uno_b200 import generators as G
+    kkt = G.ocp_distributed(40, 3, seed=0)                       # 128 000 nodes after KKT pairing
+    runs = []
+    for depth in (3, 3, 0):
+        s = KKTSolver(device=-1, parallel_ordering_depth=depth, parallel_ordering_min_nodes=50000)
+        s.do_symbolic_analysis(kkt.dim, kkt.row, kkt.col, kkt.reg_size, kkt.n, values=kkt.val)
+        perm, _ = s.permutation()
+        st = s.stats()
+        runs.append((perm.copy(), st["flops_factor"], s.plan()["ordering"] if "ordering" in s.plan() else None))
+        s.close()
+    assert np.array_equal(np.sort(runs[0][0]), np.arange(kkt.dim))
+    assert np.array_equal(runs[0][0], runs[1][0])
+    assert not np.array_equal(runs[0][0], runs[2][0])            # the serial path is another ordering ...
+    assert runs[0][1] <= 1.15 * runs[2][1]                       # ... of the same quality
