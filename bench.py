@@ -135,13 +135,18 @@ def cpu_threads():
     return cores
 
 
-def measure_cpu(G, name, slot, steps, warmup):
+def measure_cpu(G, name, slot, steps, warmup, memory_fraction=None):
     """One MEASURED CPU run (oracle/cpu_arm.py): workload `name` itself (slot 1) or its bounded sample (slot 2), same ordering as the
-    GPU run (computed by a child process), all host cores.  Nothing is projected."""
+    GPU run (computed by a child process), all host cores.  Nothing is projected.  memory_fraction: refuse (MemoryError) when the
+    oracle's storage, estimated from the plan, exceeds that share of the available host memory."""
     from oracle import cpu_arm as CA
     cores = cpu_threads()
     kkt = WORKLOADS[name][slot](G, 0)
     perm, info = CA.ordering_from_child(name, slot)
+    if memory_fraction is not None:
+        need, have = CA.oracle_memory_estimate_gb(info), CA.host_memory_available_gb()
+        if need > memory_fraction * have:
+            raise MemoryError(f"the CPU oracle needs about {need:.0f} GB for {name}, {have:.0f} GB of host memory available, limit {100 * memory_fraction:.0f} %")
     res = CA.run_oracle(kkt, perm, steps, warmup, cores)
     res.update({"workload": kkt.name, "N": kkt.dim, "factor_flops": info["flops"], "factor_gflops": info["flops"] / res["factor_seconds"] / 1e9,
                 "value": 1.0 / res["seconds_per_step"], "steps": steps, "warmup": warmup, "cores": cores, "cpu": CA.cpu_model(),
@@ -197,25 +202,29 @@ def main():
         # false, which is the truth.
         from oracle import cpu_arm as CA
         requested = args.workload
-        budget = float(os.environ.get("B200KKT_REFERENCE_BUDGET_S", "600"))
+        budget = float(os.environ.get("B200KKT_REFERENCE_BUDGET_S", "900"))
         t_start = time.perf_counter()
         runs = []
         if requested == "ocp3d_k128":
             sample = measure_cpu(G, "ocp3d_k128", 2, 1, 1)
             runs.append(sample)
-            full_flops_estimate = 2.07e14                                # the b200 arm's plan (profiles/r02_bench_k128_v2.json)
+            full_flops_estimate = 2.014e14                               # the b200 arm's plan (profiles/r02_bench_k128_v3.json)
             # the oracle's rate grows with the front sizes, so the sample's rate is a cautious one; + generator, ordering, analysis
             predicted = full_flops_estimate / (sample["factor_gflops"] * 1e9) + 150.0
-            # memory: the sample's resident peak scaled by the factor sizes of the two plans (9.37e9 against 4.86e8 entries);
-            # a host driven out of memory is worse than a line that names the smaller configuration
-            predicted_gb = 1.05 * sample["peak_rss_gb"] * 9.37e9 / 4.86e8
-            if predicted <= budget and predicted_gb <= 0.75 * CA.host_memory_available_gb():
-                res = measure_cpu(G, "ocp3d_k128", 1, 1, 0)
-                runs.append(res)
+            # memory: estimated from the plan before the run (80 % of what the host has), and watched by the oracle during it (it
+            # stops with an error while the host can still take it): a host driven out of memory is worse than a line that names
+            # the smaller configuration
+            res, note = None, None
+            if predicted <= budget:
+                try:
+                    res = measure_cpu(G, "ocp3d_k128", 1, 1, 0, memory_fraction=0.8)
+                    runs.append(res)
+                except (MemoryError, RuntimeError) as exc:
+                    note = f"ocp3d_k128 not measured: {exc}"
             else:
                 note = (f"ocp3d_k128 not run: predicted {predicted:.0f} s for one step (sample: {sample['factor_gflops']:.0f} GFLOP/s) against a budget of "
-                        f"{budget:.0f} s (B200KKT_REFERENCE_BUDGET_S); predicted {predicted_gb:.0f} GB of host memory (sample peak "
-                        f"{sample['peak_rss_gb']:.1f} GB x factor-size ratio) against {CA.host_memory_available_gb():.0f} GB available, limit 75 %")
+                        f"{budget:.0f} s (B200KKT_REFERENCE_BUDGET_S)")
+            if res is None:
                 one = measure_cpu(G, "ocp3d_k64", 1, 1, 0)
                 runs.append(one)
                 more = int(min(max(args.steps, 1), max(1.0, 0.25 * budget / max(one["seconds_per_step"], 1e-3))))

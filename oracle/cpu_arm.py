@@ -36,7 +36,7 @@ perm, _ = s.permutation()
 st = s.stats()
 np.save({out!r}, perm)
 print(json.dumps({{"flops": st["flops_factor"], "nnz_factor": st["nnz_factor"], "pool_doubles": st["pool_doubles"], "max_front": st["max_front"],
-                  "cb_arena_doubles": s.plan()["cb_arena_doubles"]}}))
+                  "cb_arena_doubles": s.plan()["cb_arena_doubles"], "N": kkt.dim}}))
 """
 
 
@@ -74,31 +74,41 @@ def peak_rss_gb() -> float:
     return 0.0
 
 
+def oracle_memory_estimate_gb(info) -> float:
+    """Host memory of one oracle factorization, from the plan of the same ordering: the packed factors, the dense workspace of the
+    largest front, the contribution blocks alive at the peak (the oracle sweeps the top of the tree in postorder, which keeps fewer
+    alive than the level-order arena of the GPU plan), the generator's and the analysis' own arrays.  Checked against the resident
+    peak of the 64^3 boundary-control sample: 7.8 GB estimated, 7.5 GB measured."""
+    return 8e-9 * (info["nnz_factor"] + 1.07 * info["max_front"] ** 2 + 0.8 * info["cb_arena_doubles"]) + 1.5e-6 * info.get("N", 0) + 0.5
+
+
 def run_oracle(kkt, perm, steps: int, warmup: int, threads: int):
     """factorize + inertia + solve per step, wall clock.  Returns (seconds per step, list of times, inertia, backward error, stats)."""
     from oracle import oracle as O
     has_blas = O.bind_openblas()
     o = O.OracleSolver(threshold_u=0.01, threads=threads, restricted=True)
-    t0 = time.perf_counter()
-    o.do_symbolic_analysis(kkt.dim, kkt.row, kkt.col, perm)
-    t_analyse = time.perf_counter() - t0
-    times, t_factor = [], []
-    x = None
-    for it in range(warmup + steps):
+    try:
         t0 = time.perf_counter()
-        o.do_numerical_factorization(kkt.val)
-        t1 = time.perf_counter()
-        ine = o.get_inertia()
-        x = o.solve_indefinite_system(kkt.rhs)
-        t2 = time.perf_counter()
-        if it >= warmup:
-            times.append(t2 - t0)
-            t_factor.append(t1 - t0)
+        o.do_symbolic_analysis(kkt.dim, kkt.row, kkt.col, perm)
+        t_analyse = time.perf_counter() - t0
+        times, t_factor = [], []
+        x = None
+        for it in range(warmup + steps):
+            t0 = time.perf_counter()
+            o.do_numerical_factorization(kkt.val)      # raises when the host is about to run out of memory (the oracle watches it)
+            t1 = time.perf_counter()
+            ine = o.get_inertia()
+            x = o.solve_indefinite_system(kkt.rhs)
+            t2 = time.perf_counter()
+            if it >= warmup:
+                times.append(t2 - t0)
+                t_factor.append(t1 - t0)
+        st = o.stats()
+    finally:
+        o.close()                                      # factors, workspaces and pools go back to the host
     A = kkt.to_scipy()
     r = kkt.rhs - A @ x
     berr = float(np.abs(r).max() / (abs(A).sum(axis=1).max() * np.abs(x).max() + np.abs(kkt.rhs).max()))
-    st = o.stats()
-    o.close()
     return {"seconds_per_step": float(np.mean(times)), "factor_seconds": float(np.mean(t_factor)), "times": times, "inertia": list(ine),
             "backward_error_first_sweep": berr, "delayed_pivots": int(st["delayed"]), "openblas": bool(has_blas), "analyse_seconds": t_analyse}
 

@@ -141,7 +141,8 @@ struct Front {
    // numeric result
    int nf = 0, nelim = 0;
    std::vector<int> idx;               // global ids of the front rows in final local order
-   std::vector<double> L;              // nf x nelim, column-major, unit diagonal implied
+   std::unique_ptr<double[]> L;        // columns of L packed one after the other, column j holding rows j .. nf-1 (unit diagonal implied)
+   size_t L_size = 0;
    std::vector<double> d, e;           // D blocks: d diagonal, e[j] != 0 -> 2x2 block (j, j+1)
    std::vector<char> ptype;            // 0 1x1, 1/2 first/second of 2x2, 3 null
    // contribution block handed to the parent (freed once consumed)
@@ -153,30 +154,34 @@ struct Front {
 
 // Contribution blocks come and go with every front: fresh allocations of that size are mmap'ed and page-faulted in each time,
 // which costs more than the arithmetic.  Buffers are recycled instead (best fit by capacity).
+// One pool per thread (a block is taken by the thread that factors the front and given to the pool of the thread that consumes
+// it); big blocks are not kept - their allocation is nothing next to the work on such a front, and the memory goes back at once.
 struct BufferPool {
+   static constexpr size_t KEEP_BELOW = size_t(1) << 22;   // doubles (32 MB)
    std::multimap<size_t, std::unique_ptr<double[]>> free_list;
    std::unique_ptr<double[]> take(size_t need, size_t& cap) {
       std::unique_ptr<double[]> out;
-#pragma omp critical(oracle_pool)
-      {
-         auto it = free_list.lower_bound(need);
-         if (it != free_list.end() && it->first <= 2 * need + 4096) { cap = it->first; out = std::move(it->second); free_list.erase(it); }
-      }
+      auto it = free_list.lower_bound(need);
+      if (it != free_list.end() && it->first <= 2 * need + 4096) { cap = it->first; out = std::move(it->second); free_list.erase(it); }
       if (!out) { cap = need; out.reset(new double[need > 0 ? need : 1]); }
       return out;
    }
    void give(std::unique_ptr<double[]>& buf, size_t cap) {
       if (!buf) return;
-#pragma omp critical(oracle_pool)
+      if (cap >= KEEP_BELOW) { buf.reset(); return; }
       free_list.emplace(cap, std::move(buf));
    }
 };
+
+// offset of column j of a packed factor block of nf rows: entry (i, j), i >= j, sits at lpos(nf, j) + i
+inline size_t lpos(int nf, int j) { return static_cast<size_t>(j) * nf - static_cast<size_t>(j) * (j + 1) / 2; }
 
 // per-thread scratch, kept from one factorization to the next.  The dense buffers are raw memory: they are never cleared as a
 // whole (only the lower triangle of a front is), and they grow geometrically so that a rising sequence of front sizes does not
 // re-allocate (and page-fault) at every step.
 struct Work {
    std::vector<int> loc;
+   BufferPool pool;
    std::unique_ptr<double[]> A, W;
    size_t capA = 0, capW = 0;
    static double* ensure(std::unique_ptr<double[]>& buf, size_t& cap, size_t need) {
@@ -195,8 +200,11 @@ struct Oracle {
    std::vector<int> order;             // fronts, children before parents
    std::vector<std::vector<int>> levels;
    std::vector<double> scale;
-   BufferPool pool;
    std::vector<Work> works;
+   std::vector<int> first_desc;        // fronts are numbered in postorder: the subtree of s is [first_desc[s], s]
+   std::vector<double> sub_flops;      // static estimate of the work in the subtree of s
+   std::vector<int> sub_maxnf;         // largest front in it
+   double min_free_gb = 12.0;          // ORACLE_MIN_FREE_GB: a factorization stops (with an error) before the host runs out of memory
    uint64_t pos = 0, neg = 0, zero = 0;
    int64_t n2x2 = 0, ndelayed = 0;
    double nnzL = 0, flops = 0, t_analyse = 0, t_factor = 0, t_solve = 0;
@@ -368,9 +376,20 @@ void analyse(Oracle& o, int64_t N, int64_t nnz, const uint64_t* row, const uint6
       o.crow[p] = std::max(a, b); o.cslot[p] = static_cast<int>(e);
    }
    o.nnzL = 0; o.flops = 0;
-   for (const Front& F : o.fronts) {
+   o.first_desc.resize(ns); o.sub_flops.assign(ns, 0.0); o.sub_maxnf.assign(ns, 0);
+   for (int s = 0; s < ns; ++s) {
+      const Front& F = o.fronts[s];
       const double k = F.ncol, r = static_cast<double>(F.bnd.size());
-      o.nnzL += k * (k + r) - k * (k - 1) / 2; o.flops += k * k * k / 3 + k * k * r + k * r * r;
+      const double fl = k * k * k / 3 + k * k * r + k * r * r;
+      o.nnzL += k * (k + r) - k * (k - 1) / 2; o.flops += fl;
+      // supernodes follow the postordered columns, so children come before parents and a subtree is a range of indices
+      o.first_desc[s] = s; o.sub_flops[s] += fl + 1.0; o.sub_maxnf[s] = std::max(o.sub_maxnf[s], F.ncol + static_cast<int>(F.bnd.size()));
+      for (const int c : F.children) { o.first_desc[s] = std::min(o.first_desc[s], o.first_desc[c]); }
+      if (F.parent != -1) {
+         if (F.parent <= s) throw std::runtime_error("oracle: fronts are not in postorder");
+         o.sub_flops[F.parent] += o.sub_flops[s];
+         o.sub_maxnf[F.parent] = std::max(o.sub_maxnf[F.parent], o.sub_maxnf[s]);
+      }
    }
    o.t_analyse = since(t0);
 }
@@ -394,6 +413,24 @@ void swap_sym(double* A, int nf, int a, int b, std::vector<int>& idx) {
    std::swap(idx[a], idx[b]);
 }
 
+// what the host can still give: MemAvailable, and the room left under a cgroup limit if there is one
+double host_free_gb() {
+   double avail = 1e30;
+   if (FILE* f = std::fopen("/proc/meminfo", "r")) {
+      char line[256];
+      while (std::fgets(line, sizeof line, f) != nullptr) {
+         long long kb = 0;
+         if (std::sscanf(line, "MemAvailable: %lld kB", &kb) == 1) { avail = 1e-6 * static_cast<double>(kb); break; }
+      }
+      std::fclose(f);
+   }
+   long long limit = -1, current = -1;
+   if (FILE* f = std::fopen("/sys/fs/cgroup/memory.max", "r")) { if (std::fscanf(f, "%lld", &limit) != 1) limit = -1; std::fclose(f); }
+   if (FILE* f = std::fopen("/sys/fs/cgroup/memory.current", "r")) { if (std::fscanf(f, "%lld", &current) != 1) current = -1; std::fclose(f); }
+   if (limit > 0 && current >= 0 && limit < (1LL << 60)) avail = std::min(avail, 1e-9 * static_cast<double>(limit - current));
+   return avail;
+}
+
 void factor_front(Oracle& o, int s, const double* val, Work& w) {
    Front& F = o.fronts[s];
    const bool is_root = F.parent == -1;
@@ -405,14 +442,23 @@ void factor_front(Oracle& o, int s, const double* val, Work& w) {
    const int nf = static_cast<int>(F.idx.size());
    F.nf = nf;
    const size_t ld = static_cast<size_t>(nf);
-   // only the lower triangle is ever read: it alone is cleared (the BLAS strips may leave anything above the diagonal)
-   double* A = Work::ensure(w.A, w.capA, ld * nf);
    const bool big = nf >= 1024;
 #ifdef _OPENMP
    const bool solo = !omp_in_parallel();
 #else
    const bool solo = true;
 #endif
+   // a front of this size asks for gigabytes: stop with an error while the host can still take it (a box driven out of memory
+   // loses everything; the caller falls back to a smaller configuration)
+   if (solo && nf >= 4096) {
+      const double need_gb = 8e-9 * (static_cast<double>(nf) * nf * (ld * nf > w.capA ? 1.7 : 0.6));
+      const double free_gb = host_free_gb();
+      if (free_gb - need_gb < o.min_free_gb)
+         throw std::runtime_error("oracle: host memory nearly exhausted (" + std::to_string(free_gb) + " GB available, front of " + std::to_string(nf) +
+                                  " rows needs about " + std::to_string(need_gb) + " GB more): factorization stopped");
+   }
+   // only the lower triangle is ever read: it alone is cleared (the BLAS strips may leave anything above the diagonal)
+   double* A = Work::ensure(w.A, w.capA, ld * nf);
    std::unique_ptr<Tick> tick(new Tick(T_ASM, solo));
 #pragma omp parallel for schedule(static, 16) if (big)
    for (int j = 0; j < nf; ++j) std::memset(A + ld * j + j, 0, sizeof(double) * static_cast<size_t>(nf - j));
@@ -450,7 +496,7 @@ void factor_front(Oracle& o, int s, const double* val, Work& w) {
             for (int ci = cj; ci < ncb; ++ci) lower(A, nf, lcp[ci], gj) += col[ci];
          }
       }
-      o.pool.give(C.cb, C.cb_cap);
+      w.pool.give(C.cb, C.cb_cap);
    }
    tick.reset();
    F.d.assign(nfs, 1.0); F.e.assign(nfs, 0.0); F.ptype.assign(nfs, 0);
@@ -629,14 +675,16 @@ void factor_front(Oracle& o, int s, const double* val, Work& w) {
    tick.reset(new Tick(T_COPY, solo));
    if (solo && g_prof_on) { g_prof_nf2 += double(nf) * nf; g_prof_nfne += double(nf) * ne; g_prof_big += 1; for (int c : F.children) g_prof_cb2 += double(o.fronts[c].ncb) * o.fronts[c].ncb; }
    // (only the part of a column at and below its diagonal is ever read: nothing is cleared)
-   if (F.L.size() != ld * ne) { std::vector<double>().swap(F.L); F.L.resize(ld * ne); }
+   const size_t lsize = lpos(nf, ne) + static_cast<size_t>(ne);   // ne nf - ne (ne - 1) / 2
+   if (F.L_size != lsize) { F.L.reset(); F.L.reset(new double[lsize > 0 ? lsize : 1]); F.L_size = lsize; }
+   double* Lp = F.L.get();
 #pragma omp parallel for schedule(static, 8) if (big)
-   for (int j = 0; j < ne; ++j) std::memcpy(F.L.data() + ld * j + j, A + ld * j + j, sizeof(double) * (nf - j));
+   for (int j = 0; j < ne; ++j) std::memcpy(Lp + lpos(nf, j) + j, A + ld * j + j, sizeof(double) * (nf - j));
    F.d.resize(ne); F.e.resize(ne); F.ptype.resize(ne);
    F.ncb = nf - ne; F.ndelay = nfs - ne;
    F.cb_idx.assign(F.idx.begin() + ne, F.idx.end());
-   o.pool.give(F.cb, F.cb_cap);   // a root's block of the previous factorization
-   F.cb = o.pool.take(static_cast<size_t>(F.ncb) * (F.ncb + 1) / 2, F.cb_cap);
+   w.pool.give(F.cb, F.cb_cap);   // a root's block of the previous factorization
+   F.cb = w.pool.take(static_cast<size_t>(F.ncb) * (F.ncb + 1) / 2, F.cb_cap);
    double* cbp = F.cb.get();
    const size_t ncb_ = static_cast<size_t>(F.ncb);
 #pragma omp parallel for schedule(static, 8) if (big)
@@ -676,42 +724,50 @@ void factorize(Oracle& o, const double* val, int nthreads) {
    std::vector<Work>& works = o.works;
    if (static_cast<int>(works.size()) != nthreads) { works.clear(); works.resize(nthreads); }
    for (auto& w : works) if (static_cast<int64_t>(w.loc.size()) != o.N) w.loc.assign(o.N, -1);
-   // The fronts of a level are independent.  Small and medium ones go one per thread (single-threaded BLAS inside); the big ones
-   // follow one after the other with every thread inside the front (threaded BLAS, threaded assembly and copies).
-   std::vector<int> side, big_ones;
-   for (const auto& level : o.levels) {
-      side.clear(); big_ones.clear();
-      for (const int f : level) {
-         const size_t nf0 = static_cast<size_t>(o.fronts[f].ncol) + o.fronts[f].bnd.size();
-         (nthreads > 1 && nf0 < 3000 ? side : big_ones).push_back(f);
-      }
-      if (side.size() == 1) { big_ones.push_back(side[0]); side.clear(); }
-      const int ns = static_cast<int>(side.size());
-      if (ns > 0) {
-         Tick side_tick(T_SIDE, true);
+   if (const char* e = std::getenv("ORACLE_MIN_FREE_GB")) o.min_free_gb = std::atof(e);
+   // Two phases.  Below a cut, whole subtrees go one per thread, each swept in postorder with single-threaded BLAS: no
+   // synchronisation, the contribution blocks stay in that thread's cache and pool.  Above it, the fronts follow one another in
+   // postorder with every thread inside the front (tiled BLAS, threaded assembly and copies): at most one stack of contribution
+   // blocks is alive, which is what lets the 128^3 system fit the host.  A subtree qualifies if it is a small share of the work
+   // and its largest front fits a per-thread workspace.
+   const int ns = static_cast<int>(o.fronts.size());
+   const double share = o.flops / (8.0 * nthreads);
+   auto below = [&](int f) { return nthreads > 1 && o.sub_flops[f] <= share && o.sub_maxnf[f] <= 8192; };
+   std::vector<int> roots;
+   for (int f = 0; f < ns; ++f) if (below(f) && (o.fronts[f].parent == -1 || !below(o.fronts[f].parent))) roots.push_back(f);
+   std::sort(roots.begin(), roots.end(), [&](int a, int b) { return o.sub_flops[a] != o.sub_flops[b] ? o.sub_flops[a] > o.sub_flops[b] : a < b; });
+   const int nroots = static_cast<int>(roots.size());
+   if (nroots > 0) {
+      Tick side_tick(T_SIDE, true);
+      bool starved = false;
 #pragma omp parallel for schedule(dynamic, 1)
-         for (int t = 0; t < ns; ++t) {
+      for (int t = 0; t < nroots; ++t) {
 #ifdef _OPENMP
-            Work& w = works[omp_get_thread_num()];
+         Work& w = works[omp_get_thread_num()];
 #else
-            Work& w = works[0];
+         Work& w = works[0];
 #endif
+         if (starved) continue;
+         if (o.sub_maxnf[roots[t]] >= 2048 && host_free_gb() < o.min_free_gb) { starved = true; continue; }
+         for (int f = o.first_desc[roots[t]]; f <= roots[t]; ++f) {
             if (g_prof_on) {
                const auto tf = clk::now();
-               factor_front(o, side[t], val, w);
+               factor_front(o, f, val, w);
                const double dt = since(tf);
-               const int nf = o.fronts[side[t]].nf;
+               const int nf = o.fronts[f].nf;
                const int cls = nf < 32 ? 0 : nf < 128 ? 1 : nf < 512 ? 2 : nf < 1500 ? 3 : 4;
 #pragma omp critical(oracle_prof)
                { g_prof_cls[cls] += dt; g_prof_cnt[cls] += 1; }
-            } else
-            factor_front(o, side[t], val, w);
+            } else {
+               factor_front(o, f, val, w);
+            }
          }
       }
-      if (!big_ones.empty()) {
-         for (const int f : big_ones) factor_front(o, f, val, works[0]);
-      }
+      if (starved) throw std::runtime_error("oracle: host memory nearly exhausted during the subtree phase: factorization stopped");
+      // the per-thread workspaces of the subtree phase are not needed above the cut
+      if (o.flops > 2.0e13) for (size_t t = 1; t < works.size(); ++t) { works[t].A.reset(); works[t].capA = 0; works[t].W.reset(); works[t].capW = 0; }
    }
+   for (int f = 0; f < ns; ++f) if (!below(f)) factor_front(o, f, val, works[0]);
    o.pos = o.neg = o.zero = 0; o.n2x2 = 0; o.ndelayed = 0;
    for (const Front& F : o.fronts) {
       o.ndelayed += F.ndelay;
@@ -753,14 +809,13 @@ void solve(Oracle& o, const double* rhs, double* x) {
       const int nf = F.nf, ne = F.nelim;
       xs.resize(nf);
       for (int t = 0; t < nf; ++t) xs[t] = y[F.idx[t]];
-      const double* L = F.L.data();
-      const size_t ld = static_cast<size_t>(nf);
+      const double* L = F.L.get();
       double* xp = xs.data();
       if (static_cast<double>(nf) * ne < 2.0e5 || nth == 1) {
          for (int j = 0; j < ne; ++j) {
             const double yj = xp[j];
             if (yj == 0.0) continue;
-            const double* l = L + ld * j;
+            const double* l = L + lpos(nf, j);
             for (int i = j + 1; i < nf; ++i) xp[i] -= l[i] * yj;
          }
       } else {
@@ -768,7 +823,7 @@ void solve(Oracle& o, const double* rhs, double* x) {
             const int je = std::min(jb + SB, ne);
             for (int j = jb; j < je; ++j) {
                const double yj = xp[j];
-               const double* l = L + ld * j;
+               const double* l = L + lpos(nf, j);
                for (int i = j + 1; i < je; ++i) xp[i] -= l[i] * yj;
             }
 #pragma omp parallel for schedule(static)
@@ -777,7 +832,7 @@ void solve(Oracle& o, const double* rhs, double* x) {
                const int i0 = je + static_cast<int>(rows * c / nth), i1 = je + static_cast<int>(rows * (c + 1) / nth);
                for (int j = jb; j < je; ++j) {
                   const double yj = xp[j];
-                  const double* l = L + ld * j;
+                  const double* l = L + lpos(nf, j);
                   for (int i = i0; i < i1; ++i) xp[i] -= l[i] * yj;
                }
             }
@@ -805,12 +860,11 @@ void solve(Oracle& o, const double* rhs, double* x) {
       const int nf = F.nf, ne = F.nelim;
       xs.resize(nf);
       for (int t = 0; t < nf; ++t) xs[t] = y[F.idx[t]];
-      const double* L = F.L.data();
-      const size_t ld = static_cast<size_t>(nf);
+      const double* L = F.L.get();
       double* xp = xs.data();
       if (static_cast<double>(nf) * ne < 2.0e5 || nth == 1) {
          for (int j = ne - 1; j >= 0; --j) {
-            const double* l = L + ld * j;
+            const double* l = L + lpos(nf, j);
             double acc = xp[j];
             for (int i = j + 1; i < nf; ++i) acc -= l[i] * xp[i];
             xp[j] = acc;
@@ -826,14 +880,14 @@ void solve(Oracle& o, const double* rhs, double* x) {
                const int64_t rows = nf - je;
                const int i0 = je + static_cast<int>(rows * c / nth), i1 = je + static_cast<int>(rows * (c + 1) / nth);
                for (int j = jb; j < je; ++j) {
-                  const double* l = L + ld * j;
+                  const double* l = L + lpos(nf, j);
                   double acc = 0.0;
                   for (int i = i0; i < i1; ++i) acc += l[i] * xp[i];
                   pp[static_cast<size_t>(c) * SB + (j - jb)] = acc;
                }
             }
             for (int j = je - 1; j >= jb; --j) {
-               const double* l = L + ld * j;
+               const double* l = L + lpos(nf, j);
                double acc = xp[j];
                for (int c = 0; c < nth; ++c) acc -= pp[static_cast<size_t>(c) * SB + (j - jb)];
                for (int i = j + 1; i < je; ++i) acc -= l[i] * xp[i];
