@@ -91,3 +91,64 @@ def test_oracle_rank_deficient_jacobian_reports_zero_pivots():
     # with dual regularization the matrix is nonsingular again and the inertia is (n, m, 0)
     v = kkt.with_regularization(100.0, 1e-6)
     assert oracle_run(kkt, v, null_tol=1e-12).get_inertia() == (kkt.n, kkt.m, 0)
+
+
+def _inertia_of_block_diagonal(d):
+    """Inertia of LAPACK's block-diagonal D (1x1 and 2x2 blocks) from the eigenvalues of its blocks."""
+    n = d.shape[0]
+    pos = neg = zero = 0
+    i = 0
+    while i < n:
+        if i + 1 < n and d[i + 1, i] != 0.0:
+            w = np.linalg.eigvalsh(d[i:i + 2, i:i + 2])
+            i += 2
+        else:
+            w = np.array([d[i, i]])
+            i += 1
+        pos += int((w > 0).sum()); neg += int((w < 0).sum()); zero += int((w == 0).sum())
+    return pos, neg, zero
+
+
+@pytest.mark.parametrize("restricted", [False, True])
+@pytest.mark.parametrize("name", ["ocp2d_26", "opf_400", "bnd3d_9"])
+def test_oracle_against_lapack_bunch_kaufman(name, restricted):
+    """An anchor outside this repository: LAPACK's dsytrf (Bunch-Kaufman partial pivoting, the dense kernel of the algorithm family
+    MUMPS belongs to) through scipy.linalg.ldl on KKT systems of 1500 - 2100 rows.  Same inertia (Sylvester: it is a property of the
+    matrix, so any stable LDL^T must agree) and the same solution to rounding, in both pivoting modes of the oracle."""
+    import scipy.linalg as sla
+    kkt = {"ocp2d_26": lambda: G.ocp_distributed(26, 2, seed=3), "opf_400": lambda: G.opf_like(400, 540, 80, seed=4, delta_w=10.0),
+           "bnd3d_9": lambda: G.ocp_boundary_3d(9, seed=5)}[name]()
+    # the OPF-like matrix gets the dual regularization the interior-point loop would give it (without it rcond ~ 1e-17 and the sign
+    # of one eigenvalue is rounding noise: LAPACK and the oracle's restricted mode then differ by one)
+    v = kkt.with_regularization(10.0, 1e-8) if name == "opf_400" else kkt.val
+    a = kkt.to_scipy(v).toarray()
+    _, d, _ = sla.ldl(a, lower=True)
+    s = oracle_run(kkt, v, restricted=restricted)
+    assert tuple(s.get_inertia()) == _inertia_of_block_diagonal(d) == (kkt.n, kkt.m, 0)
+    x = s.solve_indefinite_system(kkt.rhs)
+    import warnings
+    with warnings.catch_warnings():
+        warnings.simplefilter("ignore")          # the OPF-like matrix without dual regularization has rcond ~ 1e-17
+        x_lapack = sla.solve(a, kkt.rhs, assume_a="sym")
+    assert backward_error(kkt, v, x) < 1e-13
+    # two backward-stable solutions differ by about cond * eps; the barrier diagonals of these systems span 1e-8 .. 1e8
+    assert np.max(np.abs(x - x_lapack)) <= 1e-6 * np.max(np.abs(x_lapack))
+
+
+def test_oracle_against_superlu_at_baseline_config_1():
+    """Second outside anchor, at a BASELINE size: SuperLU (scipy.sparse.linalg.splu, an unrelated sparse LU with its own ordering and
+    partial pivoting) on the 256 x 256 control problem, N = 196 608: same solution to rounding times the condition number."""
+    import scipy.sparse.linalg as spla
+    kkt = G.ocp_distributed(256, 2, seed=0)
+    lu = spla.splu(kkt.to_scipy().tocsc())
+    x_lu = lu.solve(kkt.rhs)
+    assert backward_error(kkt, kkt.val, x_lu) < 1e-10
+    # MUMPS' rule (threshold test against the whole front column, 225 000 delayed pivots here): backward error at rounding level.
+    # Restricted mode (no delays) on the oracle's own ordering, no refinement: 2e-11 - the accuracy that the product's value-aware
+    # pairing and refinement are there to recover (DESIGN 2.2).
+    for restricted, berr_max, diff_max in ((False, 1e-15, 1e-7), (True, 1e-9, 1e-4)):
+        s = oracle_run(kkt, restricted=restricted, threads=4)
+        assert tuple(s.get_inertia()) == (kkt.n, kkt.m, 0)
+        x = s.solve_indefinite_system(kkt.rhs)
+        assert backward_error(kkt, kkt.val, x) < berr_max
+        assert np.max(np.abs(x - x_lu)) <= diff_max * np.max(np.abs(x_lu))
