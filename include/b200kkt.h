@@ -119,7 +119,14 @@ int b200kkt_plan_partition(const b200kkt_handle* h, int32_t* owner, int8_t* shar
  * growth_limit > 0 treats a column with an L entry above the limit the same way (what the threshold test CNTL(1) is for);
  * adaptive_growth arms that guard for one factorization after a solve whose first sweep missed a normwise backward error of
  * "adaptive_growth_trigger" (1e-12).
- * b200kkt_get_permutation / plan getters return the adapted plan. */
+ * b200kkt_get_permutation / plan getters return the adapted plan.
+ *
+ * Kernel and schedule variants (all default to the fastest measured; every one has a parity case in tests/test_gpu_parity.py):
+ * "fused_assembly" (1: K1 fused with the zero-fill of the pool), "fused_leaves" (2: small fronts whole by one CTA, K2),
+ * "gather_lists" (1: forward gather of the big fronts through lists built at analysis), "small_solve_ctas" (1: 64-thread CTAs for
+ * levels of small fronts in the solve sweeps), "lookahead", "lookahead_min_front", "pair_panels", "pair_min_front", "multi_stream",
+ * "update_tile_mode".  Host analysis: "parallel_ordering_depth" (3: levels of the nested dissection split by the library, halves
+ * ordered by forked processes; 0 = METIS_NodeND alone), "parallel_ordering_min_nodes" (150000), "metis_niter/nseps/ufactor". */
 int b200kkt_set_option(b200kkt_handle* h, const char* name, double value);
 /* Optional user ordering for the next analyse (perm[new] = old, length N); NULL clears it. */
 int b200kkt_set_user_permutation(b200kkt_handle* h, const int64_t* perm, uint64_t n);

@@ -405,6 +405,7 @@ def test_full_size_properties(make, name):
     {"lookahead": 0, "pair_panels": 1, "pair_min_front": 512},
     {"update_tile_mode": 1}, {"update_tile_mode": 2}, {"update_tile_mode": 3}, {"update_tile_mode": 6},
     {"gather_lists": 0},                                                          # forward gather by the children loop instead of the precomputed lists
+    {"small_solve_ctas": 0},                                                      # 256-thread CTAs on every level of the small-front sweeps
     {"fused_assembly": 0},                                                        # memset + scatter instead of the fused K1
     {"fused_leaves": 0}, {"fused_leaves": 1},                                     # small fronts through K3a/K3b/K4 instead of K2
 ])

@@ -1245,13 +1245,19 @@ __global__ void __launch_bounds__(64) k_diag32(FrontArrays F, const int* __restr
 // and the Schur complement -W L^T written straight into the packed contribution block (a leaf's block starts from zero, so it is
 // written, not updated: no k_prepare, no W panel in global memory, no separate update launch).  The bulk of every tree is such
 // fronts; the level-0 batches of the BASELINE configs cost four launches and ~1 ms (config 2) before.
-constexpr int LEAF_RMAX = 56;   // keeps the static shared memory under 48 KB
+constexpr int LEAF_RMAX = 56;   // keeps the shared memory under 48 KB
+// The W / L staging ([c][i], row stride rmax + 1) is dynamic shared memory sized from the batch's largest boundary: the leaf levels
+// (boundaries of 10 - 20 rows, thousands of fronts per launch) then fit 8 CTAs per SM instead of 4.
 // accumulate = 1: the batch has fronts with children; k_prepare has zeroed the contribution blocks and extend-added the children
 // (into the factor panel and into the block), so the Schur complement is subtracted from the block instead of written.
-__global__ void __launch_bounds__(64) k_leaf_front(FrontArrays F, const int* __restrict__ list, FactorArrays W, const double null_tol, const int accumulate) {
+__global__ void __launch_bounds__(64) k_leaf_front(FrontArrays F, const int* __restrict__ list, FactorArrays W, const double null_tol, const int accumulate,
+                                                   const int rmax) {
    __shared__ BkShared S;
    __shared__ double L11[NBI][NBI + 1];
-   __shared__ double Ws[NBI][LEAF_RMAX + 1], Ls[NBI][LEAF_RMAX + 1];   // [c][i]
+   extern __shared__ __align__(16) double leaf_dyn[];
+   const int lds = rmax + 1;
+   double* Ws = leaf_dyn;                 // [c][i]
+   double* Ls = leaf_dyn + NBI * lds;
    const int s = list[blockIdx.x];
    const int k = F.k[s], f = F.f[s], ld = F.ld[s], first = F.first[s];
    const int r = f - k;
@@ -1296,8 +1302,8 @@ __global__ void __launch_bounds__(64) k_leaf_front(FrontArrays F, const int* __r
 #pragma unroll
       for (int c = 0; c < NBI; ++c) {
          if (c < k) A[i + static_cast<int64_t>(ld) * c] = l[c];
-         Ws[c][tid] = (c < k) ? w[c] : 0.0;
-         Ls[c][tid] = (c < k) ? l[c] : 0.0;
+         Ws[c * lds + tid] = (c < k) ? w[c] : 0.0;
+         Ls[c * lds + tid] = (c < k) ? l[c] : 0.0;
       }
    }
    __syncthreads();
@@ -1308,7 +1314,7 @@ __global__ void __launch_bounds__(64) k_leaf_front(FrontArrays F, const int* __r
          const int64_t col0 = cb_col(r, j);
          for (int i = j + tid; i < r; i += 64) {
             double acc = 0.0;
-            for (int c = 0; c < k; ++c) acc = fma(Ws[c][i], Ls[c][j], acc);
+            for (int c = 0; c < k; ++c) acc = fma(Ws[c * lds + i], Ls[c * lds + j], acc);
             Cb[col0 + i] = accumulate ? Cb[col0 + i] - acc : -acc;
          }
       }
@@ -1810,16 +1816,16 @@ __global__ void __launch_bounds__(256) k_forward(FrontArrays F, const int* __res
    const int r = f - k;
    const double* A = W.lpool + F.off[s];
    double* cb = cpool + F.rel_off[s];
-   const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+   const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5, nt = blockDim.x;
 
-   for (int i = tid; i < r; i += 256) cb[i] = 0.0;
+   for (int i = tid; i < r; i += nt) cb[i] = 0.0;
    __syncthreads();
    for (int ci = F.child_ptr[s]; ci < F.child_ptr[s + 1]; ++ci) {
       const int c = F.child_idx[ci];
       const int rc = F.f[c] - F.k[c];
       const int* __restrict__ rel = F.relmap + F.rel_off[c];
       const double* cc = cpool + F.rel_off[c];
-      for (int i = tid; i < rc; i += 256) {
+      for (int i = tid; i < rc; i += nt) {
          const int loc = rel[i];
          const double v = cc[i];
          if (loc < k) zg[first + loc] += v; else cb[loc - k] += v;
@@ -1827,12 +1833,12 @@ __global__ void __launch_bounds__(256) k_forward(FrontArrays F, const int* __res
       __syncthreads();
    }
    double* y = z2 + first;
-   for (int j = tid; j < k; j += 256) y[j] = zg[first + W.lperm[first + j]];
+   for (int j = tid; j < k; j += nt) y[j] = zg[first + W.lperm[first + j]];
    __syncthreads();
 
    for (int jb = 0; jb < k; jb += NBI) {
       const int nb = min(NBI, k - jb);
-      for (int idx = tid; idx < NBI * NBI; idx += 256) {
+      for (int idx = tid; idx < NBI * NBI; idx += nt) {
          const int rr = idx % NBI, c = idx / NBI;
          Ls[rr][c] = (rr < nb && c < nb && rr > c) ? A[(jb + rr) + static_cast<int64_t>(ld) * (jb + c)] : 0.0;
       }
@@ -1847,7 +1853,7 @@ __global__ void __launch_bounds__(256) k_forward(FrontArrays F, const int* __res
          yp[lane] = (lane < nb) ? yv : 0.0;
       }
       __syncthreads();
-      for (int i = jb + nb + tid; i < f; i += 256) {
+      for (int i = jb + nb + tid; i < f; i += nt) {
          double acc = 0.0;
          for (int c = 0; c < nb; ++c) acc += A[i + static_cast<int64_t>(ld) * (jb + c)] * yp[c];
          if (i < k) y[i] -= acc; else cb[i - k] -= acc;
@@ -1867,10 +1873,10 @@ __global__ void __launch_bounds__(256) k_backward(FrontArrays F, const int* __re
    double* xb = cpool + F.rel_off[s];
    const int* __restrict__ rows = F.rows + F.rows_off[s];
    double* y = z2 + first;
-   const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+   const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5, nt = blockDim.x, nwarps = blockDim.x >> 5;
 
-   for (int i = tid; i < r; i += 256) xb[i] = xg[rows[k + i]];
-   for (int j = tid; j < k; j += 256) {
+   for (int i = tid; i < r; i += nt) xb[i] = xg[rows[k + i]];
+   for (int j = tid; j < k; j += nt) {
       const int q = first + j;
       const int ty = W.ptype[q];
       if (ty == 0) {
@@ -1892,14 +1898,14 @@ __global__ void __launch_bounds__(256) k_backward(FrontArrays F, const int* __re
       const int jb = bi * NBI;
       const int nb = min(NBI, k - jb);
       // red[c] = sum_{i >= jb+nb} L[i][jb+c] * x(i)
-      for (int c = warp; c < nb; c += 8) {
+      for (int c = warp; c < nb; c += nwarps) {
          const double* col = A + static_cast<int64_t>(ld) * (jb + c);
          double acc = 0.0;
          for (int i = jb + nb + lane; i < f; i += 32) acc += col[i] * ((i < k) ? y[i] : xb[i - k]);
          for (int o = 16; o; o >>= 1) acc += __shfl_xor_sync(0xffffffffu, acc, o);
          if (lane == 0) red[c] = acc;
       }
-      for (int idx = tid; idx < NBI * NBI; idx += 256) {
+      for (int idx = tid; idx < NBI * NBI; idx += nt) {
          const int rr = idx % NBI, c = idx / NBI;
          Ls[rr][c] = (rr < nb && c < nb && rr > c) ? A[(jb + rr) + static_cast<int64_t>(ld) * (jb + c)] : 0.0;
       }
@@ -1914,7 +1920,7 @@ __global__ void __launch_bounds__(256) k_backward(FrontArrays F, const int* __re
       }
       __syncthreads();
    }
-   for (int j = tid; j < k; j += 256) xg[first + W.lperm[first + j]] = y[j];
+   for (int j = tid; j < k; j += nt) xg[first + W.lperm[first + j]] = y[j];
 }
 
 // ------------------------------------------------------------------------------------------------
@@ -2437,9 +2443,12 @@ int launch_trsmpanel(const FrontArrays& F, const int* d_list, int nfronts, int m
 
 int leaf_front_max_boundary() { return LEAF_RMAX; }
 
-int launch_leaf_fronts(const FrontArrays& F, const int* d_list, int nfronts, const FactorArrays& W, double null_tol, bool accumulate, cudaStream_t st) {
+int launch_leaf_fronts(const FrontArrays& F, const int* d_list, int nfronts, int max_r, const FactorArrays& W, double null_tol, bool accumulate,
+                       cudaStream_t st) {
    if (nfronts <= 0) return 0;
-   k_leaf_front<<<nfronts, 64, 0, st>>>(F, d_list, W, null_tol, accumulate ? 1 : 0);
+   const int rmax = std::max(1, std::min(max_r, LEAF_RMAX));
+   const size_t smem = static_cast<size_t>(2 * NBI * (rmax + 1)) * sizeof(double);
+   k_leaf_front<<<nfronts, 64, smem, st>>>(F, d_list, W, null_tol, accumulate ? 1 : 0, rmax);
    return 1;
 }
 
@@ -2579,17 +2588,18 @@ int launch_inertia(int64_t n, const FactorArrays& W, int* counters, cudaStream_t
    return 1;
 }
 
+// threads: 256, or 64 for a level of small fronts (one CTA per front: four times as many fronts in flight per SM)
 int launch_forward_level(const FrontArrays& F, const int* d_list, int nfronts, const FactorArrays& W, double* zg, double* z2, double* cpool,
-                         cudaStream_t st) {
+                         cudaStream_t st, int threads) {
    if (nfronts <= 0) return 0;
-   k_forward<<<nfronts, 256, 0, st>>>(F, d_list, W, zg, z2, cpool);
+   k_forward<<<nfronts, threads, 0, st>>>(F, d_list, W, zg, z2, cpool);
    return 1;
 }
 
 int launch_backward_level(const FrontArrays& F, const int* d_list, int nfronts, const FactorArrays& W, double* z2, double* xg, double* cpool,
-                          cudaStream_t st) {
+                          cudaStream_t st, int threads) {
    if (nfronts <= 0) return 0;
-   k_backward<<<nfronts, 256, 0, st>>>(F, d_list, W, z2, xg, cpool);
+   k_backward<<<nfronts, threads, 0, st>>>(F, d_list, W, z2, xg, cpool);
    return 1;
 }
 

@@ -100,7 +100,8 @@ int launch_trsmpanel(const FrontArrays& F, const int* d_list, int nfronts, int m
 // block included; replaces prepare + diagpanel + trsmpanel + update for such a batch
 int leaf_front_max_boundary();
 // (accumulate: the batch went through launch_prepare first - fronts with children - and the block is updated, not written)
-int launch_leaf_fronts(const FrontArrays& F, const int* d_list, int nfronts, const FactorArrays& W, double null_tol, bool accumulate, cudaStream_t st);
+int launch_leaf_fronts(const FrontArrays& F, const int* d_list, int nfronts, int max_r, const FactorArrays& W, double null_tol, bool accumulate,
+                       cudaStream_t st);
 // rows of the L columns left of each inner block follow the block's interchanges (all blocks at once)
 int launch_permute_rows(const FrontArrays& F, const int* d_list, int nfronts, int max_k, const FactorArrays& W, cudaStream_t st);
 // K4 Schur-complement update C -= W * L^T with FP64 tensor-core MMA.
@@ -138,9 +139,9 @@ int launch_inertia(int64_t n, const FactorArrays& W, int* counters, cudaStream_t
 
 // K7 solves, one level at a time.  Small fronts: one CTA per front.
 int launch_forward_level(const FrontArrays& F, const int* d_list, int nfronts, const FactorArrays& W, double* zg, double* z2,
-                         double* cpool, cudaStream_t st);
+                         double* cpool, cudaStream_t st, int threads = 256);
 int launch_backward_level(const FrontArrays& F, const int* d_list, int nfronts, const FactorArrays& W, double* z2, double* xg,
-                          double* cpool, cudaStream_t st);
+                          double* cpool, cudaStream_t st, int threads = 256);
 // Big fronts: many CTAs per front, NBS-wide panel steps.
 int launch_fwd_big_gather(const FrontArrays& F, const int* d_list, int nfronts, int max_f, const FactorArrays& W, double* zg, double* z2,
                           double* cpool, cudaStream_t st);

@@ -533,7 +533,7 @@ void upload_plan(b200kkt_handle* h) {
             const int s = P.level_fronts[t];
             if (P.owner[s] != h->rank) continue;
             const bool is_big = P.k[s] > NBS || static_cast<int64_t>(P.f[s]) * P.k[s] > 98304;
-            if (is_big) big.push_back(s); else solve_list.push_back(s);
+            if (is_big) big.push_back(s); else { solve_list.push_back(s); SL.small_max_f = std::max(SL.small_max_f, P.f[s]); }
          }
          SL.small_count = static_cast<int>(solve_list.size()) - SL.small_begin;
          std::stable_sort(big.begin(), big.end(), [&](int a, int b) { return P.k[a] > P.k[b]; });
@@ -735,7 +735,7 @@ void enqueue_factor(b200kkt_handle* h) {
              (!b.has_children || h->fused_leaves > 1)) {
             // K2: the whole front by one CTA, contribution block included; fronts with children are extend-added first
             if (b.has_children) L += launch_prepare(h->F, list, b.count, b.max_f, h->W, st);
-            L += launch_leaf_fronts(h->F, list, b.count, h->W, h->null_pivot_tol, b.has_children, st);
+            L += launch_leaf_fronts(h->F, list, b.count, b.max_r, h->W, h->null_pivot_tol, b.has_children, st);
             continue;
          }
          if ((b.has_cb || b.has_children) && !(h->debug_skip & 4)) L += launch_prepare(h->F, list, b.count, b.max_f, h->W, st);
@@ -1039,7 +1039,8 @@ void run_solve(b200kkt_handle* h, const double* d_b, double* d_x, double* backwa
       L += launch_solve_gather(P.N, h->d_perm, h->d_scale_final, h->d_r, h->d_zg, st);
       for (int l = 0; l < P.nlevels; ++l) {
          const b200kkt_handle::SolveLevel& SL = h->solve_levels[l];
-         L += launch_forward_level(h->F, h->d_solve_list + SL.small_begin, SL.small_count, h->W, h->d_zg, h->d_z2, h->d_cpool, st);
+         L += launch_forward_level(h->F, h->d_solve_list + SL.small_begin, SL.small_count, h->W, h->d_zg, h->d_z2, h->d_cpool, st,
+                                   (h->small_solve_ctas != 0 && SL.small_max_f <= 96) ? 64 : 256);
          if (SL.big_count > 0) {
             const int* list = h->d_solve_list + SL.big_begin;
             if (h->gather_lists != 0) L += launch_fwd_big_gather_list(h->F, h->Gt, list, SL.big_count, SL.big_max_f, h->d_zg, h->d_cpool, st);
@@ -1063,7 +1064,8 @@ void run_solve(b200kkt_handle* h, const double* d_b, double* d_x, double* backwa
             enqueue_cut_transfers(h, l, 2, h->d_cpool, st);
             L += launch_boundary_unpack(h->F, h->d_cut_list + CL.out_begin, CL.out_count, h->d_cpool, h->d_xg, st);
          }
-         L += launch_backward_level(h->F, h->d_solve_list + SL.small_begin, SL.small_count, h->W, h->d_z2, h->d_xg, h->d_cpool, st);
+         L += launch_backward_level(h->F, h->d_solve_list + SL.small_begin, SL.small_count, h->W, h->d_z2, h->d_xg, h->d_cpool, st,
+                                    (h->small_solve_ctas != 0 && SL.small_max_f <= 96) ? 64 : 256);
          if (SL.big_count > 0) {
             const int* list = h->d_solve_list + SL.big_begin;
             L += launch_bwd_big_begin(h->F, list, SL.big_count, SL.big_max_f, h->W, h->d_z2, h->d_xg, h->d_cpool, st);
@@ -1340,6 +1342,7 @@ int b200kkt_set_option(b200kkt_handle* h, const char* name, double value) {
    else if (n == "fused_assembly") h->fused_assembly = static_cast<int>(value);
    else if (n == "fused_leaves") h->fused_leaves = static_cast<int>(value);
    else if (n == "gather_lists") h->gather_lists = static_cast<int>(value);
+   else if (n == "small_solve_ctas") h->small_solve_ctas = static_cast<int>(value);
    else if (n == "lookahead_min_front") h->lookahead_min_front = static_cast<int>(value);
    else if (n == "pair_panels") h->pair_panels = static_cast<int>(value);
    else if (n == "pair_min_front") h->pair_min_front = static_cast<int>(value);

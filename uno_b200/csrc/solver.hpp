@@ -83,6 +83,7 @@ struct b200kkt_handle {
    // (k descending; NBS-wide panel steps over many CTAs)
    struct SolveLevel {
       int small_begin = 0, small_count = 0;
+      int small_max_f = 0;                 // largest small front of the level: picks the CTA size of the one-CTA-per-front sweeps
       int big_begin = 0, big_count = 0;
       int big_max_f = 0, big_max_k = 0;
       std::vector<int> big_k;              // descending
@@ -122,6 +123,7 @@ struct b200kkt_handle {
    b200kkt::FactorArrays W{};
    b200kkt::GatherArrays Gt{};               // gather lists of the big fronts' forward solve (kernels.hpp)
    int gather_lists = 1;
+   int small_solve_ctas = 1;  // levels whose small fronts have at most 96 rows run the one-CTA-per-front sweeps with 64-thread CTAs (same arithmetic, more fronts in flight)
    int* d_perm = nullptr;
    int* d_batch_list = nullptr;
    int* d_solve_list = nullptr;
