@@ -446,7 +446,8 @@ def main():
                     f"{world} independent replicas (one KKT system per GPU, no data-path collective)"),
                    "partition": part_info,
                    "l2": f"front pool {st0['pool_doubles'] * 8 / 1e9:.1f} GB per step >> 126 MB L2 (inputs larger than L2, no explicit flush)",
-                   "options": extra_options or None, "analysis_seconds_untimed": t_analyse, "ordering": "METIS_NodeND on the KKT-pair-compressed graph", "fallback": fallback_note},
+                   "options": extra_options or None, "analysis_seconds_untimed": t_analyse, "ordering": "METIS nested dissection on the KKT-pair-compressed graph (graphs of 150 000 nodes and more: top three levels split by the library, "
+                               "halves ordered by parallel processes; smaller ones: METIS_NodeND)", "fallback": fallback_note},
         "clocks": clocks, "gpu_launches": int(launches),
         "e2e": {"value": e2e_value, "unit": UNIT, "h2d_bytes_per_step": int(8 * kkt.nnz + 8 * kkt.dim), "d2h_bytes_per_step": int(8 * kkt.dim + 32 + 32),
                 "finite": x_ok},
