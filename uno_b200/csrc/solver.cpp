@@ -958,6 +958,7 @@ void replan_with_delays(b200kkt_handle* h, const std::vector<int32_t>& cols) {
    P.t_order = t_order; P.ordering_used = ordering_used; P.num_pairs = num_pairs;
    P.share_min_pivots = h->share_min_pivots;
    P.share_min_flops = h->share_min_flops;
+   P.partition_slack = h->partition_slack;
    map_subtrees(P, h->num_gpus, h->share_top_fronts != 0);
    if (h->partitioned() && h->partition_memory) localize_storage(P, h->rank);
    const bool resident = h->values_resident;
@@ -1358,6 +1359,7 @@ int b200kkt_set_option(b200kkt_handle* h, const char* name, double value) {
    else if (n == "share_chunk_panels") h->share_chunk_panels = std::max(1, static_cast<int>(value));
    else if (n == "share_min_pivots") h->share_min_pivots = std::max(2 * NBO, static_cast<int>(value));
    else if (n == "share_min_flops") h->share_min_flops = value;
+   else if (n == "partition_slack") h->partition_slack = std::max(1.0, value);
    else if (n == "debug_skip") h->debug_skip = static_cast<int>(value);   // timing experiments only: 1 no K4, 2 no panel kernels, 4 no K5
    else return fail(h, B200KKT_EINVAL, "unknown option: " + n);
    // numeric options are baked into the captured graphs
@@ -1401,6 +1403,7 @@ int b200kkt_analyse(b200kkt_handle* h, uint64_t n, uint64_t nnz, uint64_t reg_si
               opt, h->plan);
       h->plan.share_min_pivots = h->share_min_pivots;
       h->plan.share_min_flops = h->share_min_flops;
+      h->plan.partition_slack = h->partition_slack;
       map_subtrees(h->plan, h->num_gpus, h->share_top_fronts != 0);
       if (h->partitioned() && h->partition_memory) localize_storage(h->plan, h->rank);
       fill_plan_stats(h);

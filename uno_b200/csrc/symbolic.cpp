@@ -1039,7 +1039,7 @@ void map_subtrees(Plan& P, int parts, bool share_top_fronts) {
       // stop when the heaviest open subtree fits its share (with 5 % slack) or cannot be opened any further
       while (!open.empty()) {
          const int32_t top = open.front();
-         const bool enough = static_cast<int>(open.size()) >= parts && sub[top] <= 1.05 * open_weight / parts;
+         const bool enough = static_cast<int>(open.size()) >= parts && sub[top] <= P.partition_slack * open_weight / parts;
          if (enough || P.child_ptr[top + 1] == P.child_ptr[top]) break;
          std::pop_heap(open.begin(), open.end(), heavier);
          open.pop_back();
