@@ -96,7 +96,7 @@ int b200kkt_comm_init(b200kkt_handle* h, int rank, int world, const char id[128]
  * then names the rank that solves with it), the cut fronts (owner differs from the parent's; at most number of fronts entries,
  * *num_cut receives the count), factor flops per rank (length num_gpus), flops on the critical path.
  * Works on host-only handles; any pointer may be NULL.
- * Options: "share_top_fronts" (1), "share_min_pivots" (1024), "share_min_flops" (5e10), "share_chunk_panels" (2),
+ * Options:  "share_top_fronts" (1), "share_min_pivots" (1024), "share_min_flops" (5e10), "share_chunk_panels" (2), "partition_slack" (1.15),
  * "partition_memory" (1): a rank allocates factor columns only for the fronts it owns and the shared ones, and room in the
  * contribution-block arena only for the blocks it produces, consumes or helps to broadcast (b200kkt_stats: pool_doubles,
  * cb_arena_doubles against the *_global figures); 0 = every rank allocates the whole system's pools (round-1 behaviour).

@@ -105,7 +105,7 @@ struct Plan {
    std::vector<char> shared;         // nsn
    int64_t share_min_pivots = 1024;  // a front above the cut is shared when it has at least this many pivots ...
    double share_min_flops = 5e10;    // ... and this much work
-   double partition_slack = 1.05;    // the tree is opened until the heaviest open subtree is at most this multiple of an even share
+   double partition_slack = 1.15;    // the tree is opened until the heaviest open subtree is at most this multiple of an even share
    std::vector<int32_t> cut_edges;   // fronts s with owner[s] != owner[parent[s]], ascending (level[s], s)
    std::vector<double> part_flops;   // factor flops per rank
    double critical_flops = 0.0;      // factor flops on the longest chain of dependent work (subtree + top fronts above it)

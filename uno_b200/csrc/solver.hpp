@@ -175,7 +175,7 @@ struct b200kkt_handle {
    int share_chunk_panels = 2;            // column chunk of a shared front, in outer panels; chunk c belongs to rank c mod num_gpus
    int share_min_pivots = 1024;
    double share_min_flops = 5e10;
-   double partition_slack = 1.05;
+   double partition_slack = 1.15;
    cudaEvent_t ev_sh_main = nullptr, ev_sh_panel = nullptr, ev_sh_comm = nullptr, ev_sh_bcast[2] = {nullptr, nullptr};
    std::vector<int64_t> woff_host, xoff_host;   // this rank's W-panel and inverted-block offsets per front
    int* d_cut_list = nullptr;
