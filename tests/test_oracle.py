@@ -152,3 +152,26 @@ def test_oracle_against_superlu_at_baseline_config_1():
         x = s.solve_indefinite_system(kkt.rhs)
         assert backward_error(kkt, kkt.val, x) < berr_max
         assert np.max(np.abs(x - x_lu)) <= diff_max * np.max(np.abs(x_lu))
+
+
+@pytest.mark.parametrize("restricted", [False, True])
+@pytest.mark.parametrize("n,m,seed", [(60, 40, 0), (200, 120, 1), (500, 499, 2)])
+def test_oracle_null_pivot_count_on_a_saddle_point_matrix_without_hessian(n, m, seed, restricted):
+    """INFOG(28) (MUMPSSolver.cpp:138) on a matrix whose rank deficiency is known in closed form: [[0, A^T], [A, 0]] with A of full
+    row rank m has m positive, m negative and n - m zero eigenvalues.  Every pivot of such a matrix is a 2x2 block or a null pivot,
+    which exercises the parts of the pivoting the regularized KKT systems rarely reach; the dense spectrum is the referee."""
+    import scipy.sparse as sp
+    a = (sp.random(m, n, density=min(0.15, 8.0 / n), random_state=seed, format="coo") + sp.eye(m, n)).tocoo()
+    row = list(range(n + m)) + [int(j) for j in a.col]
+    col = list(range(n + m)) + [int(n + i) for i in a.row]
+    val = [0.0] * (n + m) + [float(v) for v in a.data]
+    row, col, val = np.array(row, dtype=np.uint64), np.array(col, dtype=np.uint64), np.array(val)
+    k = sp.coo_matrix((val, (row.astype(np.int64), col.astype(np.int64))), shape=(n + m, n + m))
+    w = np.linalg.eigvalsh((k + sp.triu(k, 1).T).toarray())
+    tol = 1e-9 * np.abs(w).max()
+    dense = (int((w > tol).sum()), int((w < -tol).sum()), int((np.abs(w) <= tol).sum()))
+    assert dense == (m, m, n - m)
+    s = O.OracleSolver(restricted=restricted, null_tol=1e-12)
+    s.do_symbolic_analysis(n + m, row, col, None)
+    s.do_numerical_factorization(val)
+    assert tuple(s.get_inertia()) == dense
